@@ -1,0 +1,327 @@
+#!/usr/bin/env python
+"""bench.py - predicted node-timesteps/s of the Emulator rollout (BASELINE.json metric).
+
+  python bench.py --gpus 1 --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus 1 --steps K ...  # the reference math on host cores
+  torchrun ... bench.py --gpus N ...                       # one rank per GPU, weak scaling
+
+A step = one Emulator.predict over one batch of synthetic scenarios.  At N=1 the workload is
+BASELINE.json configs[1] (C2: shunqing GAT+Conv1D edge_fusion/resnet/flood, 60->60, B=4096).
+`value`   : inputs already resident in HBM, device-side timing (CUDA events), max over ranks.
+`e2e`     : the same through Emulator.predict with pinned HOST buffers (H2D + D2H inside).
+`roofline`: the dominant kernel family (the rows-GEMM) timed live with CUDA events.
+`cpu_baseline`: the NumPy oracle (a port - the reference needs TF/spektral, absent here) on a
+                bounded sample of the same workload, rank 0, N=1 only.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "predicted node-timesteps/sec (shunqing GAT rollout)"
+UNIT = "node-timesteps/s"
+
+
+def flops(em, B):
+    """Algorithmic FLOPs (2*MAC, CSR aggregation) of one predict; SURVEY.md 8(d) formula.
+    Returns (total, gemm_part) - gemm_part is what the rows-GEMM kernel family executes."""
+    E, H, S, P, k = em.embed_size, em.hidden_dim, em.n_sp_layer, em.n_tp_layer, em.kernel_size
+    N, M, Ti, To, F = em.n_node, em.n_edge, em.seq_in, em.seq_out, em.if_flood
+    act = 1 if em.act else 0
+    nnz_n, nnz_m = em.filter_csr.nnz, em.edge_filter_csr.nnz
+    gat = em.conv_kind == "gat"
+    tot = 2 * (B * Ti * (N * em.n_in + M * em.e_in) * E + B * To * (N * em.b_in + M * act) * E // 2)
+    gemm = 0
+    for blk, T in ((0, Ti), (1, To)):
+        cx, ce = (E, E) if blk == 0 else (H + E // 2, H + (E // 2) * act)
+        for l in range(S):
+            g = M * ce * (E // 2) + N * cx * (E // 2) + N * (cx + E // 2) * E + M * (ce + E // 2) * E
+            o = 2 * N * M * (E // 2) + (2 * (N + M) * E if gat else 0) + (nnz_n + nnz_m) * E
+            gemm += 2 * B * T * g
+            tot += 2 * B * T * (g + o)
+            cx = ce = E
+        for l in range(P):
+            c = E if l == 0 else H
+            per = {"Conv1D": k * c * H, "GRU": 3 * H * (c + H), "LSTM": 4 * H * (c + H)}[em.recurrent]
+            gpart = {"Conv1D": k * c * H, "GRU": 3 * H * c, "LSTM": 4 * H * c}[em.recurrent]
+            tot += 2 * B * (N + M) * T * per
+            gemm += 2 * B * (N + M) * T * gpart
+    heads_g = N * H * E + M * H * E + (N * (E * E // 2 + (F - 1) * (E // 2) ** 2) if F else 0)
+    heads_o = N * E * em.n_out + M * E * em.e_out + (N * (E // 2) if F else 0)
+    tot += 2 * B * To * (heads_g + heads_o)
+    gemm += 2 * B * To * heads_g
+    return float(tot), float(gemm)
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.gpu, self.rows, self.proc = gpu, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("bf16_tflops_sustained", 1399.6), d.get("hbm_gbs", 6554.6), "measured"
+    return 1400.0, 6650.0, "fallback"
+
+
+def cpu_baseline(workload, seconds=20.0):
+    """NumPy oracle (port) fp32 on a bounded sample of the workload; all BLAS threads."""
+    import cases   # noqa: F401  (tests/cases.py helpers are not needed; keep path set up)
+    from gnn_uds_b200 import configs, synthetic, weights as Wt
+    from oracle.emulator_oracle import OracleEmulator
+    args = configs.make_args(workload)
+    o = OracleEmulator(args.conv, args.resnet, args.recurrent, args, dtype=np.float32)
+    shim = cases.SpecShim(o)
+    o.set_weights(Wt.init_weights(Wt.layer_specs(shim), args.seed, node_edge_bias_std=0.05, bias_std=0.05))
+    rng = np.random.default_rng(args.seed)
+    n = synthetic.make_norms(o.n_node, o.n_edge, o.if_flood, rng, tide=o.tide)
+    o.set_norm(n["norm_x"], n["norm_b"], n["norm_y"], n["norm_r"], n["norm_e"])
+    shim.norm_x, shim.norm_b, shim.norm_e = n["norm_x"], n["norm_b"], n["norm_e"]
+    Bs = 1
+    inp = synthetic.make_inputs(shim, Bs, rng)
+    t0 = time.perf_counter(); o.predict(*inp); t1 = time.perf_counter() - t0      # warm-up + calibration
+    Bs = int(max(1, min(64, seconds / 3.0 / max(t1, 1e-3))))
+    inp = synthetic.make_inputs(shim, Bs, rng)
+    ts = []
+    for _ in range(3):
+        t0 = time.perf_counter(); o.predict(*inp); ts.append(time.perf_counter() - t0)
+    t = float(np.median(ts))
+    return {"value": Bs * o.seq_out * o.n_node / t, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+            "sample": "%s model, B=%d scenarios x %d steps, NumPy fp32 dense formulation, median of 3" % (workload, Bs, o.seq_out),
+            "ms_per_sample_call": t * 1e3}
+
+
+def run_reference(a):
+    """--impl reference: the reference's math on host cores (oracle port; TF/spektral are absent)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    ts = []
+    res = None
+    for i in range(a.warmup + a.steps):
+        res = cpu_baseline(a.workload, seconds=6.0)
+        if i >= a.warmup:
+            ts.append(res["value"])
+    v = float(np.mean(ts))
+    res["value"] = v
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": res["ms_per_sample_call"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": {"workload": a.workload},
+            "cpu_baseline": res, "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--workload", default="C2")
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--precision", default=os.environ.get("GNNUDS_PRECISION", "auto"))
+    ap.add_argument("--no-cpu", action="store_true")
+    a = ap.parse_args()
+    if a.impl == "reference":
+        return run_reference(a)
+
+    import torch
+    import torch.distributed as dist
+    from gnn_uds_b200 import configs, synthetic, _lib
+    import ctypes as C
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback for the product path)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    precision = a.precision
+    if precision == "auto":
+        precision = "bf16" if os.path.exists(os.path.join(ROOT, "gnn_uds_b200", "csrc", "tc_gemm.cuh")) else "fp32"
+    em, args, rng = configs.make_emulator(a.workload, device=local, precision=precision)
+    B = a.batch or args.B
+    N, M, Ti, To = em.n_node, em.n_edge, em.seq_in, em.seq_out
+    # scenarios are independent: every rank owns B of them (weak scaling), no data-path collective
+    rng = np.random.default_rng(args.seed + 1000 * rank)
+    Bg = min(B, 256)
+    states, b, act, ex = synthetic.make_inputs(em, Bg, rng)
+    rep = (B + Bg - 1) // Bg
+    tile = lambda t: None if t is None else np.ascontiguousarray(np.concatenate([t] * rep, 0)[:B])
+    states, b, act, ex = tile(states), tile(b), tile(act), tile(ex)
+    yc, ec = em.y_channels, em.ey_channels
+
+    # ---- device-resident arm -------------------------------------------------
+    dev = torch.device("cuda", local)
+    dx, db, dex = [torch.from_numpy(t).to(dev) for t in (states, b, ex)]
+    da = torch.from_numpy(act).to(dev) if act is not None else None
+    dy = torch.empty((B, To, N, yc), dtype=torch.float32, device=dev)
+    dey = torch.empty((B, To, M, ec), dtype=torch.float32, device=dev)
+    torch.cuda.synchronize()
+    in_bytes = sum(t.numel() * 4 for t in (dx, db, dex)) + (da.numel() * 4 if da is not None else 0)
+    l2_note = "inputs %.0f MB + activations per pass exceed the 126 MB L2" % (in_bytes / 1e6)
+
+    def step_dev():
+        em.predict_ptrs(dx.data_ptr(), db.data_ptr(), da.data_ptr() if da is not None else None, dex.data_ptr(), B,
+                        dy.data_ptr(), dey.data_ptr(), device=True)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(a.warmup, 3)):
+        step_dev()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = em.launch_count()
+    em.set_profiling(2)             # CUDA events on the library's own stream (torch events cannot see it); 2 = also per-GEMM pairs
+    tot_ms, gemm_ms = 0.0, 0.0
+    for _ in range(a.steps):
+        step_dev()
+        t, g = em.last_timing()
+        tot_ms += t; gemm_ms += g
+    barrier()
+    launches = em.launch_count() - l0
+    # the per-GEMM event pairs perturb the stream slightly; time the K steps again without them
+    em.set_profiling(False)
+    barrier()
+    t0 = time.perf_counter()
+    ev_ms = 0.0
+    em.set_profiling(1)             # whole-step event pair only
+    for _ in range(a.steps):
+        step_dev()
+        ev_ms += em.last_timing()[0]
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms = ev_ms                         # device time of exactly K steps (CUDA events, library stream)
+    t_all = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_all, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t_all.item()) / a.steps
+    value = world * B * To * N / (ms_per_step * 1e-3)
+
+    # ---- end-to-end arm: host (pinned) buffers through Emulator.predict ---------
+    def pinned(shape):
+        n = int(np.prod(shape))
+        p = C.c_void_p()
+        rc = em._lib.gnnuds_alloc_pinned(C.byref(p), n * 4)
+        assert rc == 0
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=(n,)).reshape(shape), p
+    hx, px = pinned(states.shape); hx[...] = states
+    hb, pb = pinned(b.shape); hb[...] = b
+    hex_, pex = pinned(ex.shape); hex_[...] = ex
+    ha, pa = (None, None)
+    if act is not None:
+        ha, pa = pinned(act.shape); ha[...] = act
+    hy, py = pinned((B, To, N, yc)); hey, pey = pinned((B, To, M, ec))
+
+    def step_e2e():
+        em.predict_ptrs(px, pb, pa, pex, B, py, pey, device=False)
+        return float(hy[0, 0, 0, 0])
+
+    em.set_profiling(False)
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        step_e2e()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    e_all = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e_all, op=dist.ReduceOp.MAX)
+    e2e_val = world * B * To * N * a.steps / float(e_all.item())
+    h2d = int(in_bytes)
+    d2h = int((dy.numel() + dey.numel()) * 4)
+
+    if rank == 0:
+        tot_f, gemm_f = flops(em, B)
+        tf_peak, hbm_peak, src = peaks()
+        gemm_ms_per_step = gemm_ms / a.steps
+        achieved = gemm_f / (gemm_ms_per_step * 1e-3) / 1e12 if gemm_ms_per_step > 0 else None
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if precision == "fp32" else "bf16(f32 acc)", "data": "synthetic",
+            "config": {"workload": "%s: %s %s+%s edge_fusion=%s resnet=%s if_flood=%d act=%s, N=%d M=%d, seq %d->%d, B=%d per GPU" % (
+                a.workload, args.__dict__.get("env_name", configs.WORKLOADS[a.workload]["net"]), em.conv_kind.upper(), em.recurrent,
+                em.edge_fusion, em.resnet, em.if_flood, bool(em.act), N, M, Ti, To, B),
+                "l2": l2_note, "precision": precision, "sharding": "scenarios over ranks, no data-path collective"},
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "note": "Emulator.predict_ptrs with pinned host buffers, wall clock incl. copies"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": "rows_gemm (all Dense/conv-linear/Conv1D launches of a step)",
+                         "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s",
+                         "frac": (achieved / tf_peak) if achieved else None, "traffic": None,
+                         "peak_source": "%s bf16_tflops_sustained" % src,
+                         "gemm_ms_per_step": gemm_ms_per_step, "gemm_flops_per_step": gemm_f,
+                         "total_flops_per_step": tot_f, "step_tflops": tot_f / (ms_per_step * 1e-3) / 1e12},
+            "wall_s_timed_region": wall,
+        }
+        if world == 1 and not a.no_cpu:
+            line["cpu_baseline"] = cpu_baseline(a.workload)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

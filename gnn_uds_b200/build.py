@@ -1,0 +1,36 @@
+"""Build libgnnuds.so in-tree with nvcc for sm_100a:  python -m gnn_uds_b200.build"""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "csrc", "gnnuds.cu")
+OUT = os.path.join(HERE, "libgnnuds.so")
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+         "-Xcompiler", "-fPIC", "-shared"]
+
+
+def sources():
+    d = os.path.join(HERE, "csrc")
+    return [os.path.join(d, f) for f in sorted(os.listdir(d))] + [os.path.join(os.path.dirname(HERE), "include", "gnnuds.h")]
+
+
+def build(force=False, verbose=False, defines=()):
+    if not force and os.path.exists(OUT) and all(os.path.getmtime(OUT) >= os.path.getmtime(s) for s in sources()):
+        return OUT
+    nvcc = os.environ.get("NVCC", "nvcc")
+    cmd = [nvcc] + FLAGS + ["-D%s" % d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, SRC, "-lcudart"]
+    if os.path.exists(os.path.join(HERE, "csrc", "tc_gemm.cuh")):
+        cmd.insert(1, "-DGNNUDS_WITH_TC")
+        cmd.append("-lcuda")
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("nvcc failed: %s" % " ".join(cmd))
+    if verbose:
+        sys.stderr.write(r.stderr)
+    return OUT
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -1,0 +1,1098 @@
+// libgnnuds.so - host orchestration + C ABI (include/gnnuds.h) of the B200-native
+// Emulator forward.  Mirrors surrogate/emulator.py::Emulator (build_network 166-341,
+// predict 566-602, post_proc 643-678, constrain 727-748) of Zhiyu014/GNN-UDS without
+// sharing code with it: the Keras graph becomes a fixed sequence of sm_100a kernels
+// over [B][T][N][C] activations.
+#include "../../include/gnnuds.h"
+#include "kernels.cuh"
+#ifdef GNNUDS_WITH_TC
+#include "tc_gemm.cuh"
+#endif
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace gu;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct LayerW { int t[4]; };   // tensor indices of one weighted layer
+
+struct SpatialW {
+  LayerW xe, ex, ne_n, ne_m, conv_x, conv_e;   // graph_base == 0
+  LayerW joint;                                // graph_base != 0
+  int cx, ce;
+};
+
+struct TensorDesc { int64_t numel; int d0, d1, d2; };
+
+}  // namespace
+
+struct gnnuds_handle {
+  gnnuds_config c{};
+  std::string err;
+  cudaStream_t stream = nullptr;
+  int sm_count = 148;
+  int64_t launches = 0;
+  bool has_graph = false, has_weights = false, has_norm = false;
+  int debug_stop = 0;
+  int profiling = 0;            // 0 off, 1 whole-call event pair, 2 also one pair per GEMM launch
+  float last_total_ms = 0.f, last_gemm_ms = 0.f;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> gemm_ev;
+  size_t gemm_ev_used = 0;
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+
+  // layout
+  std::vector<TensorDesc> tens;
+  LayerW emb_x, emb_b, emb_e, emb_a;
+  std::vector<SpatialW> sp[2];
+  std::vector<LayerW> tpx[2], tpe[2];
+  LayerW resx, rese, head_out, head_flood, head_e;
+  std::vector<LayerW> flood_chain;
+
+  // device parameters
+  float* d_blob = nullptr;
+  std::vector<int64_t> toff;
+  std::vector<float*> d_ne_matT[2];     // per spatial layer (block*S + l): N-side, M-side folded matrices
+  int ldm_n = 0, ldm_m = 0, ti_n = 0, ti_m = 0;
+
+  // graph
+  int *d_rp = nullptr, *d_ci = nullptr, *d_erp = nullptr, *d_eci = nullptr;
+  float *d_val = nullptr, *d_eval = nullptr;
+  int nnz = 0, ennz = 0, n_adj = 0;
+  int *d_edges = nullptr, *d_act_of_edge = nullptr, *d_act_out = nullptr, *d_act_in = nullptr;
+  int *d_inc_ptr = nullptr, *d_inc_edge = nullptr, *d_inc_sign = nullptr;
+  float *d_hmin = nullptr, *d_hmax = nullptr, *d_outfall = nullptr, *d_ehmax = nullptr;
+  std::vector<int> h_edges;
+
+  // norms (max,min) per item
+  float *d_nx = nullptr, *d_nb = nullptr, *d_ny = nullptr, *d_ne = nullptr;
+  int cx_n = 0, cb_n = 0, cy_n = 0, ce_n = 0;
+
+  // workspace
+  int64_t ws_chunk = 0;
+  float* d_ws = nullptr;
+  size_t ws_floats = 0;
+  float *XA, *XB, *EA, *EB, *HB, *XE, *EX, *NX, *NE, *TX0, *TX1, *TE0, *TE1, *BEMB, *AEMB, *RES, *RESE,
+      *OUTN, *OUTE, *SS, *SN;
+  float *in_x, *in_b, *in_a, *in_ex, *out_y, *out_ey;      // chunk staging on device
+  // rollout state
+  float *ro_x = nullptr, *ro_ex = nullptr, *ro_b = nullptr, *ro_a = nullptr;
+  int64_t ro_B = 0;
+
+  // live streams for debug_fetch
+  const float* dbg_ptr[2] = {nullptr, nullptr};
+  int64_t dbg_rows[2] = {0, 0};
+  int dbg_width[2] = {0, 0};
+
+  int ny() const { return 3 + (c.if_flood ? 1 : 0) + 1; }
+  int ldn() const { return c.n_out + (c.if_flood ? 1 : 0); }
+};
+
+namespace {
+
+int fail(gnnuds_handle* h, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (h) h->err = buf; else g_create_error = buf;
+  return code;
+}
+
+#define CU(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess)                                                                \
+      return fail(h, GNNUDS_E_CUDA, "%s -> %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+int conv_ntens(const gnnuds_config& c) { return c.conv == GNNUDS_CONV_GAT ? 4 : 2; }
+
+// ---- creation-order walk of build_network (emulator.py:195-336) ----------------------
+struct LayoutBuilder {
+  gnnuds_handle* h;
+  int add(int64_t n, int d0 = 0, int d1 = 0, int d2 = 0) {
+    h->tens.push_back({n, d0, d1, d2});
+    return (int)h->tens.size() - 1;
+  }
+  LayerW dense(int cin, int cout) {
+    LayerW l{};
+    l.t[0] = add((int64_t)cin * cout, cin, cout);
+    l.t[1] = add(cout, cout);
+    return l;
+  }
+  LayerW conv(int cin) {
+    const int E = h->c.embed;
+    LayerW l{};
+    if (h->c.conv == GNNUDS_CONV_GAT) {
+      l.t[0] = add((int64_t)cin * E, cin, 1, E);
+      l.t[1] = add(E, E, 1, 1);
+      l.t[2] = add(E, E, 1, 1);
+      l.t[3] = add(E, E);
+    } else {
+      l.t[0] = add((int64_t)cin * E, cin, E);
+      l.t[1] = add(E, E);
+    }
+    return l;
+  }
+  LayerW node_edge(int r, int cdim) {
+    LayerW l{};
+    l.t[0] = add((int64_t)r * cdim, r, cdim);
+    l.t[1] = add((int64_t)r * cdim, r, cdim);
+    return l;
+  }
+  void temporal(std::vector<LayerW>& v, int cin) {
+    const auto& c = h->c;
+    const int H = c.hidden;
+    for (int i = 0; i < c.n_tp_layer; ++i) {
+      const int ci = i == 0 ? cin : H;
+      LayerW l{};
+      if (c.recurrent == GNNUDS_REC_CONV1D) {
+        l.t[0] = add((int64_t)c.kernel_size * ci * H, c.kernel_size, ci, H);
+        l.t[1] = add(H, H);
+      } else if (c.recurrent == GNNUDS_REC_GRU) {
+        l.t[0] = add((int64_t)ci * 3 * H, ci, 3 * H);
+        l.t[1] = add((int64_t)H * 3 * H, H, 3 * H);
+        l.t[2] = add(2 * 3 * H, 2, 3 * H);
+      } else {
+        l.t[0] = add((int64_t)ci * 4 * H, ci, 4 * H);
+        l.t[1] = add((int64_t)H * 4 * H, H, 4 * H);
+        l.t[2] = add(4 * H, 4 * H);
+      }
+      v.push_back(l);
+    }
+  }
+  void spatial(std::vector<SpatialW>& v, int cx, int ce) {
+    const auto& c = h->c;
+    const int E = c.embed;
+    for (int l = 0; l < c.n_sp_layer; ++l) {
+      SpatialW s{};
+      s.cx = cx; s.ce = ce;
+      if (c.graph_base) {
+        s.joint = conv(cx);
+      } else {
+        s.xe = dense(ce, E / 2);                   // emulator.py:225
+        s.ex = dense(cx, E / 2);                   // :226
+        s.ne_n = node_edge(c.n_node, c.n_edge);    // :227
+        s.ne_m = node_edge(c.n_edge, c.n_node);    // :228
+        s.conv_x = conv(cx + E / 2);               // :229
+        s.conv_e = conv(ce + E / 2);               // :230
+      }
+      v.push_back(s);
+      cx = ce = E;
+    }
+  }
+  void build() {
+    const auto& c = h->c;
+    const int E = c.embed, H = c.hidden;
+    h->emb_x = dense(c.n_in, E);                   // :198
+    h->emb_b = dense(c.b_in, E / 2);               // :203
+    h->emb_e = dense(c.e_in, E);                   // :206
+    if (c.act) h->emb_a = dense(1, E / 2);         // :212
+    spatial(h->sp[0], E, E);
+    temporal(h->tpx[0], E);                        // :247
+    temporal(h->tpe[0], E);                        // :254
+    spatial(h->sp[1], H + E / 2, H + (c.act ? E / 2 : 0));
+    temporal(h->tpx[1], E);                        // :302
+    temporal(h->tpe[1], E);                        // :308
+    h->resx = dense(H, E);                         // :313 'dense_resx'
+    h->rese = dense(H, E);                         // :317
+    h->head_out = dense(E, c.n_out);               // :324
+    if (c.if_flood) {
+      int ci = E;
+      for (int i = 0; i < c.if_flood; ++i) { h->flood_chain.push_back(dense(ci, E / 2)); ci = E / 2; }   // :329
+      h->head_flood = dense(ci, 1);                // :330
+    }
+    h->head_e = dense(E, c.e_out);                 // :336
+  }
+};
+
+const float* W(const gnnuds_handle* h, int tensor) { return h->d_blob + h->toff[tensor]; }
+
+int grid_for(const gnnuds_handle* h, long long work_items, int per_block, int max_waves = 8) {
+  long long g = (work_items + per_block - 1) / per_block;
+  long long cap = (long long)h->sm_count * max_waves;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+// ---- launch helpers -------------------------------------------------------------------
+struct SegH { const float* p; int ld; int width; int shift; int pitch; int off; };
+
+int launch_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, const float* Wp, const float* bias, float* out,
+                int ldo, int Nout, int act, long long Bc, int Nn, int Td, int Ts, int pitch_d, int off_d) {
+  if (segs.size() > 4) return fail(h, GNNUDS_E_INVALID, "rows_gemm: more than 4 segments (kernel_size > 4?)");
+  GemmP p{};
+  p.nseg = (int)segs.size();
+  for (int i = 0; i < p.nseg; ++i) {
+    if (segs[i].width % 16) return fail(h, GNNUDS_E_INVALID, "rows_gemm: segment width %d not a multiple of 16", segs[i].width);
+    p.seg[i] = Seg{segs[i].p, segs[i].ld, segs[i].width, segs[i].shift, segs[i].pitch, segs[i].off};
+  }
+  p.W = Wp; p.bias = bias; p.out = out; p.ldo = ldo; p.Nout = Nout; p.act = act;
+  p.rows = Bc * Td * Nn; p.Nn = Nn; p.Td = Td; p.Ts = Ts; p.pitch_d = pitch_d; p.off_d = off_d;
+  if (p.rows == 0) return 0;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (h->profiling >= 2) {
+    if (h->gemm_ev_used == h->gemm_ev.size()) {
+      cudaEvent_t a, b;
+      CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
+      h->gemm_ev.push_back({a, b});
+    }
+    e0 = h->gemm_ev[h->gemm_ev_used].first; e1 = h->gemm_ev[h->gemm_ev_used].second;
+    ++h->gemm_ev_used;
+    CU(cudaEventRecord(e0, h->stream));
+  }
+  const unsigned gx = (unsigned)((p.rows + 127) / 128);
+  if (Nout % 128 == 0) {
+    rows_gemm_f32<128><<<dim3(gx, Nout / 128), 256, 0, h->stream>>>(p);
+  } else if (Nout % 64 == 0) {
+    rows_gemm_f32<64><<<dim3(gx, Nout / 64), 256, 0, h->stream>>>(p);
+  } else {
+    return fail(h, GNNUDS_E_INVALID, "rows_gemm: Nout %d not a multiple of 64", Nout);
+  }
+  ++h->launches;
+  if (h->profiling >= 2) CU(cudaEventRecord(e1, h->stream));
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int launch_embed(gnnuds_handle* h, const float* in, const float* nrm, int cn, int Nn_norm, const int* gather, int n_act,
+                 const LayerW& w, float* out, float* res, long long Bc, int T, int Nn, int K, int Eo, int act, int mode) {
+  EmbedP p{};
+  p.in = in; p.nmax = nrm; p.nmin = nrm ? nrm + (size_t)Nn_norm * cn : nullptr; p.cn = cn;
+  p.gather = gather; p.n_act = n_act;
+  p.W = W(h, w.t[0]); p.bias = W(h, w.t[1]); p.out = out; p.res = res;
+  p.rows = Bc * T * Nn; p.T = T; p.Nn = Nn; p.K = K; p.Eo = Eo; p.act = act; p.mode = mode;
+  if (p.rows == 0) return 0;
+  const int rpb = 256 / (Eo / 4);
+  embed_kernel<<<grid_for(h, p.rows, rpb, 16), 256, (size_t)(K * Eo + Eo) * sizeof(float), h->stream>>>(p);
+  ++h->launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+
+template <int TI>
+int launch_ne_t(gnnuds_handle* h, const NodeEdgeP& p, size_t smem) {
+  CU(cudaFuncSetAttribute(nodeedge_kernel<TI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int g = grid_for(h, (p.S + 1) / 2, 1, 1);
+  nodeedge_kernel<TI><<<g, 512, smem, h->stream>>>(p);
+  ++h->launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int launch_nodeedge(gnnuds_handle* h, const float* matT, int ldm, int TI, const float* in, float* out, long long S,
+                    int R_in, int R_out, int F) {
+  NodeEdgeP p{matT, in, out, S, R_in, R_out, F, ldm};
+  const size_t smem = ((size_t)R_in * ldm + 2 * (size_t)R_in * F) * sizeof(float);
+  if (smem > 227 * 1024) return fail(h, GNNUDS_E_INVALID, "NodeEdge matrix (%d x %d) does not fit shared memory", R_out, R_in);
+  switch (TI) {
+    case 4: return launch_ne_t<4>(h, p, smem);
+    case 8: return launch_ne_t<8>(h, p, smem);
+    case 12: return launch_ne_t<12>(h, p, smem);
+    case 16: return launch_ne_t<16>(h, p, smem);
+    default: return fail(h, GNNUDS_E_INVALID, "NodeEdge: rows per thread %d unsupported (graph too large for the NodeEdge path)", TI);
+  }
+}
+
+int launch_agg(gnnuds_handle* h, const float* hin, float* out, const int* rp, const int* ci, const float* val,
+               const LayerW& w, long long S, int R, int act) {
+  const auto& c = h->c;
+  const int E = c.embed;
+  const bool gat = c.conv == GNNUDS_CONV_GAT;
+  const float* bias = W(h, w.t[gat ? 3 : 1]);
+  const size_t smem = ((size_t)R * E + 2 * (size_t)R) * sizeof(float);
+  if (smem <= 200 * 1024) {
+    AggP p{hin, out, rp, ci, val, gat ? W(h, w.t[1]) : nullptr, gat ? W(h, w.t[2]) : nullptr, bias, S, R, E, act, gat ? 1 : 0};
+    CU(cudaFuncSetAttribute(agg_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    agg_small_kernel<<<grid_for(h, S, 1, 16), 256, smem, h->stream>>>(p);
+    ++h->launches;
+  } else {
+    if (gat) {
+      row_scores_kernel<<<grid_for(h, S * R, 8, 16), 256, 0, h->stream>>>(hin, W(h, w.t[1]), W(h, w.t[2]), h->SS, h->SN, S * R, E);
+      ++h->launches;
+    }
+    AggLargeP p{hin, out, rp, ci, val, h->SS, h->SN, bias, S, R, E, act, gat ? 1 : 0};
+    agg_large_kernel<<<grid_for(h, S * R, 8, 32), 256, 0, h->stream>>>(p);
+    ++h->launches;
+  }
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int launch_head(gnnuds_handle* h, const float* in, int ld, int K, const LayerW& w, float* out, int ldo, int col0,
+                int Nout, int act, long long rows) {
+  if (Nout > 4) return fail(h, GNNUDS_E_INVALID, "head wider than 4 columns (%d)", Nout);
+  HeadP p{in, ld, K, W(h, w.t[0]), W(h, w.t[1]), out, ldo, col0, Nout, act, rows};
+  if (rows == 0) return 0;
+  head_kernel<<<grid_for(h, rows, 8, 16), 256, (size_t)K * Nout * sizeof(float), h->stream>>>(p);
+  ++h->launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int act_code(const gnnuds_config& c) { return c.activation; }
+
+// ---- temporal stack (emulator.py:154-163) ------------------------------------------------
+// in: (Bc,Ts,Nn,cin) at `src`; result (Bc,Td,Nn,H) in *dst (one of t0/t1).
+int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const float* src, int cin, long long Bc, int Nn,
+                 int Ts, int Td, float* t0, float* t1, float** dst) {
+  const auto& c = h->c;
+  const int H = c.hidden, P = c.n_tp_layer;
+  const float* cur = src;
+  int cw = cin;
+  float* bufs[2] = {t0, t1};
+  for (int i = 0; i < P; ++i) {
+    const bool last = (i == P - 1);
+    const int Tdst = last ? Td : Ts;
+    float* o = bufs[i & 1];
+    int rc;
+    if (c.recurrent == GNNUDS_REC_CONV1D) {
+      std::vector<SegH> segs;
+      const int k = c.kernel_size, d = 1 << i;
+      for (int j = 0; j < k; ++j) segs.push_back({cur, cw, cw, (k - 1 - j) * d, Nn, 0});
+      rc = launch_gemm(h, segs, W(h, L[i].t[0]), W(h, L[i].t[1]), o, H, H, act_code(c), Bc, Nn, Tdst, Ts, Nn, 0);
+      if (rc) return rc;
+    } else {
+      const bool gru = c.recurrent == GNNUDS_REC_GRU;
+      const int G = (gru ? 3 : 4) * H;
+      // input projection for every time step
+      rc = launch_gemm(h, {{cur, cw, cw, 0, Nn, 0}}, W(h, L[i].t[0]), W(h, L[i].t[2]) /* b[0] or b */, h->HB, G, G,
+                       ACT_LINEAR, Bc, Nn, Ts, Ts, Nn, 0);
+      if (rc) return rc;
+      const long long nseq = Bc * Nn;
+      const int g = (int)((nseq + 31) / 32);
+      if (gru) {
+        GruP p{h->HB, W(h, L[i].t[1]), W(h, L[i].t[2]) + G, o, nseq, Nn, Ts, Tdst, H};
+        const size_t smem = ((size_t)H * G + 32 * H + 32 * G) * sizeof(float);
+        CU(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        gru_kernel<<<g, 256, smem, h->stream>>>(p);
+      } else {
+        LstmP p{h->HB, W(h, L[i].t[1]), o, nseq, Nn, Ts, Tdst, H};
+        const size_t smem = ((size_t)H * G + 64 * H + 32 * G) * sizeof(float);
+        CU(cudaFuncSetAttribute(lstm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        lstm_kernel<<<g, 256, smem, h->stream>>>(p);
+      }
+      ++h->launches;
+      CU(cudaGetLastError());
+    }
+    cur = o; cw = H;
+    // note: for non-final layers Tdst == Ts so the next layer reads a full-length sequence
+  }
+  *dst = const_cast<float*>(cur);
+  return 0;
+}
+
+struct Stream2 { std::vector<SegH> x, e; };   // current node / edge stream as concatenated segments
+
+// ---- spatial block (emulator.py:219-235 / 272-288), graph_base == 0 -----------------------
+int run_spatial(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) {
+  const auto& c = h->c;
+  const int E = c.embed, E2 = E / 2, N = c.n_node, M = c.n_edge;
+  const long long S = Bc * T;
+  const int act = act_code(c);
+  const int nt = conv_ntens(c);
+  (void)nt;
+  for (int l = 0; l < c.n_sp_layer; ++l) {
+    const SpatialW& w = h->sp[blk][l];
+    int rc;
+    // x_e = Dense(E/2)(e) ; e_x = Dense(E/2)(x)
+    if ((rc = launch_gemm(h, st.e, W(h, w.xe.t[0]), W(h, w.xe.t[1]), h->XE, E2, E2, act, Bc, M, T, T, M, 0))) return rc;
+    if ((rc = launch_gemm(h, st.x, W(h, w.ex.t[0]), W(h, w.ex.t[1]), h->EX, E2, E2, act, Bc, N, T, T, N, 0))) return rc;
+    // NodeEdge both directions
+    const int li = blk * c.n_sp_layer + l;
+    if ((rc = launch_nodeedge(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, h->XE, h->NX, S, M, N, E2))) return rc;
+    if ((rc = launch_nodeedge(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, h->EX, h->NE, S, N, M, E2))) return rc;
+    // conv on [x | NodeEdge(x_e)]
+    std::vector<SegH> sx = st.x; sx.push_back({h->NX, E2, E2, 0, N, 0});
+    std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
+    float* xo = (l & 1) ? h->XB : h->XA;
+    float* eo = (l & 1) ? h->EB : h->EA;
+    if ((rc = launch_gemm(h, sx, W(h, w.conv_x.t[0]), nullptr, h->HB, E, E, ACT_LINEAR, Bc, N, T, T, N, 0))) return rc;
+    if ((rc = launch_agg(h, h->HB, xo, h->d_rp, h->d_ci, h->d_val, w.conv_x, S, N, act))) return rc;
+    if ((rc = launch_gemm(h, se, W(h, w.conv_e.t[0]), nullptr, h->HB, E, E, ACT_LINEAR, Bc, M, T, T, M, 0))) return rc;
+    if ((rc = launch_agg(h, h->HB, eo, h->d_erp, h->d_eci, h->d_eval, w.conv_e, S, M, act))) return rc;
+    st.x = {{xo, E, E, 0, N, 0}};
+    st.e = {{eo, E, E, 0, M, 0}};
+    if (h->debug_stop == (blk ? 40 : 20) + l) return 1;
+  }
+  return 0;
+}
+
+void set_dbg(gnnuds_handle* h, const Stream2& st, long long rows_x, long long rows_e) {
+  h->dbg_ptr[0] = st.x[0].p; h->dbg_width[0] = st.x[0].width; h->dbg_rows[0] = rows_x;
+  h->dbg_ptr[1] = st.e[0].p; h->dbg_width[1] = st.e[0].width; h->dbg_rows[1] = rows_e;
+}
+
+// One forward over Bc scenarios whose inputs are already on the device.
+// normalised_io: inputs already normalised, outputs left normalised (ROLL_NORM rule).
+int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float* a, const float* ex, long long Bc,
+                  float* y, float* ey, bool normalised_io) {
+  const auto& c = h->c;
+  const int E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge, Ti = c.seq_in, To = c.seq_out;
+  const int act = act_code(c);
+  int rc;
+  if (c.graph_base) return fail(h, GNNUDS_E_INVALID, "graph_base != 0 forward not built in this revision");
+  // ---- K1 embedding ----
+  if ((rc = launch_embed(h, x, normalised_io ? nullptr : h->d_nx, h->cx_n, N, nullptr, 0, h->emb_x, h->XB, h->RES, Bc, Ti, N,
+                         c.n_in, E, act, 0))) return rc;
+  if ((rc = launch_embed(h, b, normalised_io ? nullptr : h->d_nb, h->cb_n, N, nullptr, 0, h->emb_b, h->BEMB, nullptr, Bc, To, N,
+                         c.b_in, E2, act, 0))) return rc;
+  if ((rc = launch_embed(h, ex, normalised_io ? nullptr : h->d_ne, h->ce_n, M, nullptr, 0, h->emb_e, h->EB, h->RESE, Bc, Ti, M,
+                         c.e_in, E, act, 0))) return rc;
+  if (c.act) {
+    if ((rc = launch_embed(h, a, nullptr, 0, 0, h->d_act_of_edge, c.n_act, h->emb_a, h->AEMB, nullptr, Bc, To, M, 1, E2, act, 2)))
+      return rc;
+  }
+  Stream2 st;
+  st.x = {{h->XB, E, E, 0, N, 0}};
+  st.e = {{h->EB, E, E, 0, M, 0}};
+  set_dbg(h, st, Bc * Ti * N, Bc * Ti * M);
+  if (h->debug_stop == 1) return 0;
+  // the first spatial layer writes XA/EA (l even), so the embedding lives in XB/EB
+  // ---- spatial block 1 ----
+  rc = run_spatial(h, 0, st, Bc, Ti);
+  set_dbg(h, st, Bc * Ti * N, Bc * Ti * M);
+  if (rc == 1) return 0;
+  if (rc) return rc;
+  if (h->debug_stop == 2) return 0;
+  // ---- temporal block 1 (keeps the last To steps, emulator.py:249,256) ----
+  float *xt = nullptr, *et = nullptr;
+  if ((rc = run_temporal(h, h->tpx[0], st.x[0].p, E, Bc, N, Ti, To, h->TX0, h->TX1, &xt))) return rc;
+  if ((rc = run_temporal(h, h->tpe[0], st.e[0].p, E, Bc, M, Ti, To, h->TE0, h->TE1, &et))) return rc;
+  // ---- boundary / control concat (emulator.py:260-262) ----
+  st.x = {{xt, H, H, 0, N, 0}, {h->BEMB, E2, E2, 0, N, 0}};
+  st.e = {{et, H, H, 0, M, 0}};
+  if (c.act) st.e.push_back({h->AEMB, E2, E2, 0, M, 0});
+  set_dbg(h, st, Bc * To * N, Bc * To * M);
+  if (h->debug_stop == 3) return 0;
+  // ---- spatial block 2 ----
+  rc = run_spatial(h, 1, st, Bc, To);
+  set_dbg(h, st, Bc * To * N, Bc * To * M);
+  if (rc == 1) return 0;
+  if (rc) return rc;
+  if (h->debug_stop == 4) return 0;
+  // ---- temporal block 2 ----
+  if ((rc = run_temporal(h, h->tpx[1], st.x[0].p, E, Bc, N, To, To, h->TX0, h->TX1, &xt))) return rc;
+  if ((rc = run_temporal(h, h->tpe[1], st.e[0].p, E, Bc, M, To, To, h->TE0, h->TE1, &et))) return rc;
+  st.x = {{xt, H, H, 0, N, 0}};
+  st.e = {{et, H, H, 0, M, 0}};
+  set_dbg(h, st, Bc * To * N, Bc * To * M);
+  if (h->debug_stop == 5) return 0;
+  // ---- K8 resnet + heads (emulator.py:312-338) ----
+  const int ract = c.resnet ? ACT_LINEAR : act;
+  if ((rc = launch_gemm(h, st.x, W(h, h->resx.t[0]), W(h, h->resx.t[1]), h->XA, E, E, ract, Bc, N, To, To, N, 0))) return rc;
+  if ((rc = launch_gemm(h, st.e, W(h, h->rese.t[0]), W(h, h->rese.t[1]), h->EA, E, E, ract, Bc, M, To, To, M, 0))) return rc;
+  if (c.resnet) {
+    cumsum_res_act_kernel<<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(h->XA, h->RES, Bc, To, N, E, act);
+    cumsum_res_act_kernel<<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(h->EA, h->RESE, Bc, To, M, E, act);
+    h->launches += 2;
+    CU(cudaGetLastError());
+  }
+  st.x = {{h->XA, E, E, 0, N, 0}};
+  st.e = {{h->EA, E, E, 0, M, 0}};
+  set_dbg(h, st, Bc * To * N, Bc * To * M);
+  if (h->debug_stop == 6) return 0;
+  const long long RXo = Bc * To * N, REo = Bc * To * M;
+  const int ldn = h->ldn();
+  if ((rc = launch_head(h, h->XA, E, E, h->head_out, h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID, RXo))) return rc;
+  if (c.if_flood) {
+    std::vector<SegH> cur = st.x;
+    float* bufs[2] = {h->EX, h->NX};
+    for (int i = 0; i < c.if_flood; ++i) {
+      if ((rc = launch_gemm(h, cur, W(h, h->flood_chain[i].t[0]), W(h, h->flood_chain[i].t[1]), bufs[i & 1], E2, E2, act, Bc, N,
+                            To, To, N, 0))) return rc;
+      cur = {{bufs[i & 1], E2, E2, 0, N, 0}};
+    }
+    if ((rc = launch_head(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return rc;
+  }
+  if ((rc = launch_head(h, h->EA, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
+  // ---- P1..P4 post-processing ----
+  PostP p{};
+  p.out_n = h->OUTN; p.ldn = ldn; p.out_e = h->OUTE; p.lde = c.e_out;
+  p.b_raw = b; p.a = c.act ? a : nullptr; p.n_act = c.n_act;
+  p.act_of_edge = h->d_act_of_edge; p.act_out_of_node = h->d_act_out; p.act_in_of_node = h->d_act_in;
+  p.inc_ptr = h->d_inc_ptr; p.inc_edge = h->d_inc_edge; p.inc_sign = h->d_inc_sign;
+  p.ymax = h->d_ny; p.ymin = h->d_ny + (size_t)N * h->cy_n; p.cy = h->cy_n;
+  p.emax = h->d_ne; p.emin = h->d_ne + (size_t)M * h->ce_n; p.ce = h->ce_n;
+  p.bmax = h->d_nb; p.bmin = h->d_nb + (size_t)N * h->cb_n; p.cb = h->cb_n;
+  p.hmin = h->d_hmin; p.hmax = h->d_hmax; p.is_outfall = h->d_outfall; p.ehmax = h->d_ehmax;
+  p.y = y; p.ey = ey; p.S = Bc * To; p.N = N; p.M = M; p.b_in = c.b_in; p.n_out = c.n_out; p.e_out = c.e_out;
+  p.ny = normalised_io ? 3 + (c.if_flood ? 1 : 0) : h->ny();
+  p.if_flood = c.if_flood ? 1 : 0; p.edge_fusion = c.edge_fusion; p.act = c.act; p.tide = c.tide;
+  p.normalised = normalised_io ? 1 : 0; p.epsilon = c.epsilon;
+  if (normalised_io && c.tide) return fail(h, GNNUDS_E_INVALID, "ROLL_NORM with tide not supported");
+  postproc_kernel<<<grid_for(h, p.S, 1, 16), 128, (size_t)M * sizeof(float), h->stream>>>(p);
+  ++h->launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int64_t floats_per_scenario(const gnnuds_config& c) {
+  const int64_t E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge;
+  const int64_t Tm = std::max(c.seq_in, c.seq_out);
+  const int64_t G = c.recurrent == GNNUDS_REC_GRU ? 3 * H : c.recurrent == GNNUDS_REC_LSTM ? 4 * H : 0;
+  const int64_t W2 = std::max(E2, H);
+  int64_t f = 0;
+  f += Tm * (N + M) * (2 * E + 2 * W2 + 2 * H);          // XA XB EA EB | XE EX NX NE | TX* TE*
+  f += Tm * std::max(N, M) * std::max(E, G) + Tm * std::max(N, M) * 2;   // HB, SS, SN
+  f += c.seq_out * (N + M) * E2;                         // BEMB AEMB
+  f += (N + M) * E;                                      // RES RESE
+  f += c.seq_out * (N + M) * 4;                          // OUTN OUTE
+  f += c.seq_in * (N * c.n_in + M * c.e_in) + c.seq_out * (N * c.b_in + std::max(c.n_act, 1));
+  f += c.seq_out * (N * 5 + M * 4);
+  return f + 64;
+}
+
+int ensure_workspace(gnnuds_handle* h, int64_t Bc) {
+  if (Bc <= h->ws_chunk && h->d_ws) return 0;
+  const auto& c = h->c;
+  if (h->d_ws) { cudaFree(h->d_ws); h->d_ws = nullptr; }
+  const int64_t E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge;
+  const int64_t Tm = std::max(c.seq_in, c.seq_out);
+  const int64_t G = c.recurrent == GNNUDS_REC_GRU ? 3 * H : c.recurrent == GNNUDS_REC_LSTM ? 4 * H : 0;
+  const int64_t W2 = std::max(E2, H);
+  const int64_t RX = Bc * Tm * N, RE = Bc * Tm * M, RM = Bc * Tm * std::max(N, M);
+  std::vector<std::pair<float**, int64_t>> plan = {
+      {&h->XA, RX * E}, {&h->XB, RX * E}, {&h->EA, RE * E}, {&h->EB, RE * E}, {&h->HB, RM * std::max(E, G)},
+      {&h->XE, RE * W2}, {&h->EX, RX * W2}, {&h->NX, RX * W2}, {&h->NE, RE * W2},
+      {&h->TX0, RX * H}, {&h->TX1, RX * H}, {&h->TE0, RE * H}, {&h->TE1, RE * H},
+      {&h->BEMB, Bc * c.seq_out * N * E2}, {&h->AEMB, Bc * c.seq_out * M * E2},
+      {&h->RES, Bc * N * E}, {&h->RESE, Bc * M * E},
+      {&h->OUTN, Bc * c.seq_out * N * 4}, {&h->OUTE, Bc * c.seq_out * M * 4}, {&h->SS, RM}, {&h->SN, RM},
+      {&h->in_x, Bc * c.seq_in * N * c.n_in}, {&h->in_b, Bc * c.seq_out * N * c.b_in},
+      {&h->in_a, Bc * c.seq_out * std::max(c.n_act, 1)}, {&h->in_ex, Bc * c.seq_in * M * c.e_in},
+      {&h->out_y, Bc * c.seq_out * N * 5}, {&h->out_ey, Bc * c.seq_out * M * 4}};
+  size_t total = 0;
+  for (auto& pr : plan) total += (size_t)((pr.second + 63) / 64 * 64);
+  CU(cudaMalloc(&h->d_ws, total * sizeof(float)));
+  CU(cudaMemsetAsync(h->d_ws, 0, total * sizeof(float), h->stream));
+  size_t off = 0;
+  for (auto& pr : plan) { *pr.first = h->d_ws + off; off += (size_t)((pr.second + 63) / 64 * 64); }
+  h->ws_floats = total;
+  h->ws_chunk = Bc;
+  return 0;
+}
+
+int64_t pick_chunk(const gnnuds_handle* h, int64_t B) {
+  const auto& c = h->c;
+  if (c.max_chunk > 0) return std::min<int64_t>(B, c.max_chunk);
+  const int64_t budget = (int64_t)(c.workspace_mb > 0 ? c.workspace_mb : 8192) * 1024 * 1024 / 4;
+  int64_t bc = budget / floats_per_scenario(c);
+  if (bc < 1) bc = 1;
+  return std::min(B, bc);
+}
+
+int check_ready(gnnuds_handle* h) {
+  if (!h) return GNNUDS_E_INVALID;
+  if (!h->has_graph) return fail(h, GNNUDS_E_STATE, "gnnuds_set_graph has not been called");
+  if (!h->has_weights) return fail(h, GNNUDS_E_STATE, "gnnuds_set_weights has not been called");
+  if (!h->has_norm) return fail(h, GNNUDS_E_STATE, "gnnuds_set_norm has not been called");
+  return 0;
+}
+
+void begin_timing(gnnuds_handle* h) { h->gemm_ev_used = 0; h->last_total_ms = 0.f; h->last_gemm_ms = 0.f; }
+
+int finish_timing(gnnuds_handle* h) {
+  if (!h->profiling) return 0;
+  float g = 0.f;
+  for (size_t i = 0; i < h->gemm_ev_used; ++i) {
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, h->gemm_ev[i].first, h->gemm_ev[i].second));
+    g += ms;
+  }
+  h->last_gemm_ms = g;
+  return 0;
+}
+
+template <typename T>
+int upload(gnnuds_handle* h, T** dst, const T* src, size_t n) {
+  if (*dst) { cudaFree(*dst); *dst = nullptr; }
+  if (!n) return 0;
+  CU(cudaMalloc(dst, n * sizeof(T)));
+  CU(cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+}  // namespace
+
+// =========================================================================================
+// C ABI
+// =========================================================================================
+extern "C" {
+
+const char* gnnuds_last_error(const gnnuds_handle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
+  gnnuds_handle* h = nullptr;
+  if (!cfg || !out) return fail(nullptr, GNNUDS_E_INVALID, "null argument");
+  if (cfg->abi_version != GNNUDS_ABI_VERSION) return fail(nullptr, GNNUDS_E_INVALID, "ABI version mismatch (%d vs %d)", cfg->abi_version, GNNUDS_ABI_VERSION);
+  const gnnuds_config& c = *cfg;
+  if (c.conv != GNNUDS_CONV_GCN && c.conv != GNNUDS_CONV_GAT)
+    return fail(nullptr, GNNUDS_E_INVALID, "conv kind %d unsupported (GCN/GAT only; NN-cat/Diffusion/General are not on the CUDA path)", c.conv);
+  if (c.recurrent < GNNUDS_REC_CONV1D || c.recurrent > GNNUDS_REC_LSTM) return fail(nullptr, GNNUDS_E_INVALID, "recurrent kind %d unsupported", c.recurrent);
+  if (c.embed % 32 || c.embed < 32 || c.embed > 256) return fail(nullptr, GNNUDS_E_INVALID, "embed_size %d must be a multiple of 32 in [32,256]", c.embed);
+  if (c.hidden % 16 || c.hidden > 128 || (c.recurrent != GNNUDS_REC_CONV1D && (c.hidden * 3) % 64)) return fail(nullptr, GNNUDS_E_INVALID, "hidden_dim %d unsupported", c.hidden);
+  if (c.hidden % 64) return fail(nullptr, GNNUDS_E_INVALID, "hidden_dim %d must be a multiple of 64", c.hidden);
+  if (c.n_in > 8 || c.e_in > 8 || c.b_in > 8 || c.n_in < 1) return fail(nullptr, GNNUDS_E_INVALID, "channel counts out of range");
+  if (c.seq_in < c.seq_out) return fail(nullptr, GNNUDS_E_INVALID, "seq_in < seq_out (emulator.py:249 needs seq_in >= seq_out)");
+  if (c.act && c.seq_in != c.seq_out) return fail(nullptr, GNNUDS_E_INVALID, "act requires seq_in == seq_out (emulator.py:191)");
+  if (c.recurrent == GNNUDS_REC_CONV1D && c.kernel_size > 4) return fail(nullptr, GNNUDS_E_INVALID, "kernel_size > 4 unsupported");
+  if (c.n_out + (c.if_flood ? 1 : 0) > 4 || c.e_out > 4) return fail(nullptr, GNNUDS_E_INVALID, "head widths out of range");
+  if (c.edge_fusion ? c.n_out != 1 : c.n_out != 3) return fail(nullptr, GNNUDS_E_INVALID, "n_out %d inconsistent with edge_fusion", c.n_out);
+  if (c.precision != GNNUDS_PREC_FP32
+#ifdef GNNUDS_WITH_TC
+      && c.precision != GNNUDS_PREC_BF16_TC
+#endif
+  ) return fail(nullptr, GNNUDS_E_INVALID, "precision %d not available in this build", c.precision);
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(nullptr, GNNUDS_E_CUDA, "no CUDA device: the gnn_uds_b200 product path has no CPU fallback");
+  if (c.device < 0 || c.device >= ndev) return fail(nullptr, GNNUDS_E_INVALID, "device %d out of range (%d devices)", c.device, ndev);
+  h = new gnnuds_handle();
+  h->c = c;
+  if (cudaSetDevice(c.device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    g_create_error = "cudaSetDevice/cudaStreamCreate failed";
+    delete h;
+    return GNNUDS_E_CUDA;
+  }
+  cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, c.device);
+  cudaEventCreate(&h->ev_a); cudaEventCreate(&h->ev_b);
+  LayoutBuilder lb{h};
+  lb.build();
+  *out = h;
+  return 0;
+}
+
+int gnnuds_destroy(gnnuds_handle* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->c.device);
+  cudaStreamSynchronize(h->stream);
+  void* ptrs[] = {h->d_blob, h->d_rp, h->d_ci, h->d_erp, h->d_eci, h->d_val, h->d_eval, h->d_edges, h->d_act_of_edge,
+                  h->d_act_out, h->d_act_in, h->d_inc_ptr, h->d_inc_edge, h->d_inc_sign, h->d_hmin, h->d_hmax,
+                  h->d_outfall, h->d_ehmax, h->d_nx, h->d_nb, h->d_ny, h->d_ne, h->d_ws, h->ro_x, h->ro_ex, h->ro_b, h->ro_a};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  for (int s = 0; s < 2; ++s) for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p);
+  for (auto& e : h->gemm_ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+  if (h->ev_a) cudaEventDestroy(h->ev_a);
+  if (h->ev_b) cudaEventDestroy(h->ev_b);
+  cudaStreamDestroy(h->stream);
+  delete h;
+  return 0;
+}
+
+int gnnuds_set_graph(gnnuds_handle* h, const gnnuds_graph* g) {
+  if (!h || !g) return GNNUDS_E_INVALID;
+  const auto& c = h->c;
+  CU(cudaSetDevice(c.device));
+  const int n_expect = c.graph_base ? c.n_node + c.n_edge : c.n_node;
+  if (g->n != n_expect) return fail(h, GNNUDS_E_INVALID, "adjacency has %d rows, expected %d", g->n, n_expect);
+  if (!c.graph_base && g->m != c.n_edge) return fail(h, GNNUDS_E_INVALID, "edge adjacency has %d rows, expected %d", g->m, c.n_edge);
+  if (c.conv == GNNUDS_CONV_GCN && (!g->val || (!c.graph_base && !g->e_val))) return fail(h, GNNUDS_E_INVALID, "GCN needs filter values");
+  for (int i = 0; i < g->nnz; ++i) if (g->col_idx[i] < 0 || g->col_idx[i] >= g->n) return fail(h, GNNUDS_E_INVALID, "col_idx out of range");
+  if (g->row_ptr[0] != 0 || g->row_ptr[g->n] != g->nnz) return fail(h, GNNUDS_E_INVALID, "row_ptr inconsistent with nnz");
+  int rc;
+  if ((rc = upload(h, &h->d_rp, g->row_ptr, (size_t)g->n + 1))) return rc;
+  if ((rc = upload(h, &h->d_ci, g->col_idx, (size_t)g->nnz))) return rc;
+  if (g->val) { if ((rc = upload(h, &h->d_val, g->val, (size_t)g->nnz))) return rc; }
+  h->nnz = g->nnz; h->n_adj = g->n;
+  if (!c.graph_base) {
+    for (int i = 0; i < g->e_nnz; ++i) if (g->e_col_idx[i] < 0 || g->e_col_idx[i] >= g->m) return fail(h, GNNUDS_E_INVALID, "e_col_idx out of range");
+    if (g->e_row_ptr[0] != 0 || g->e_row_ptr[g->m] != g->e_nnz) return fail(h, GNNUDS_E_INVALID, "e_row_ptr inconsistent with e_nnz");
+    if ((rc = upload(h, &h->d_erp, g->e_row_ptr, (size_t)g->m + 1))) return rc;
+    if ((rc = upload(h, &h->d_eci, g->e_col_idx, (size_t)g->e_nnz))) return rc;
+    if (g->e_val) { if ((rc = upload(h, &h->d_eval, g->e_val, (size_t)g->e_nnz))) return rc; }
+    h->ennz = g->e_nnz;
+  }
+  const int N = c.n_node, M = c.n_edge;
+  h->h_edges.assign(g->edges, g->edges + 2 * (size_t)M);
+  for (int i = 0; i < 2 * M; ++i) if (h->h_edges[i] < 0 || h->h_edges[i] >= N) return fail(h, GNNUDS_E_INVALID, "edge endpoint out of range");
+  if ((rc = upload(h, &h->d_edges, g->edges, (size_t)2 * M))) return rc;
+  std::vector<int> neg1e(M, -1), neg1n(N, -1);
+  if ((rc = upload(h, &h->d_act_of_edge, g->act_of_edge ? g->act_of_edge : neg1e.data(), (size_t)M))) return rc;
+  if ((rc = upload(h, &h->d_act_out, g->act_out_of_node ? g->act_out_of_node : neg1n.data(), (size_t)N))) return rc;
+  if ((rc = upload(h, &h->d_act_in, g->act_in_of_node ? g->act_in_of_node : neg1n.data(), (size_t)N))) return rc;
+  if (c.act && !g->act_of_edge) return fail(h, GNNUDS_E_INVALID, "act model needs act_of_edge");
+  // node -> incident edges (signed incidence, base.py:432-439); self loops cancel to 0
+  std::vector<int> ptr(N + 1, 0), ie, is;
+  for (int m = 0; m < M; ++m) {
+    const int u = h->h_edges[2 * m], v = h->h_edges[2 * m + 1];
+    if (u == v) continue;
+    ++ptr[u + 1]; ++ptr[v + 1];
+  }
+  for (int n = 0; n < N; ++n) ptr[n + 1] += ptr[n];
+  ie.resize(ptr[N]); is.resize(ptr[N]);
+  std::vector<int> fill(ptr.begin(), ptr.end() - 1);
+  for (int m = 0; m < M; ++m) {
+    const int u = h->h_edges[2 * m], v = h->h_edges[2 * m + 1];
+    if (u == v) continue;
+    ie[fill[u]] = m; is[fill[u]++] = +1;
+    ie[fill[v]] = m; is[fill[v]++] = -1;
+  }
+  int dummy = 0;
+  if ((rc = upload(h, &h->d_inc_ptr, ptr.data(), ptr.size()))) return rc;
+  if ((rc = upload(h, &h->d_inc_edge, ie.empty() ? &dummy : ie.data(), std::max<size_t>(ie.size(), 1)))) return rc;
+  if ((rc = upload(h, &h->d_inc_sign, is.empty() ? &dummy : is.data(), std::max<size_t>(is.size(), 1)))) return rc;
+  if ((rc = upload(h, &h->d_hmin, g->hmin, (size_t)N))) return rc;
+  if ((rc = upload(h, &h->d_hmax, g->hmax, (size_t)N))) return rc;
+  if ((rc = upload(h, &h->d_outfall, g->is_outfall, (size_t)N))) return rc;
+  if ((rc = upload(h, &h->d_ehmax, g->ehmax, (size_t)M))) return rc;
+  h->has_graph = true;
+  h->has_weights = false;   // folded NodeEdge matrices depend on the incidence
+  return 0;
+}
+
+int gnnuds_weight_layout(gnnuds_handle* h, int32_t* n_tensors, int64_t* sizes) {
+  if (!h || !n_tensors) return GNNUDS_E_INVALID;
+  *n_tensors = (int32_t)h->tens.size();
+  if (sizes) for (size_t i = 0; i < h->tens.size(); ++i) sizes[i] = h->tens[i].numel;
+  return 0;
+}
+
+int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, const int64_t* offsets,
+                       const int64_t* sizes, int32_t n_tensors) {
+  if (!h || !blob || !offsets || !sizes) return GNNUDS_E_INVALID;
+  if (!h->has_graph) return fail(h, GNNUDS_E_STATE, "set_graph must precede set_weights (NodeEdge folding needs the incidence)");
+  const auto& c = h->c;
+  CU(cudaSetDevice(c.device));
+  if (n_tensors != (int)h->tens.size()) return fail(h, GNNUDS_E_INVALID, "expected %d weight tensors, got %d", (int)h->tens.size(), n_tensors);
+  h->toff.resize(n_tensors);
+  for (int i = 0; i < n_tensors; ++i) {
+    if (sizes[i] != h->tens[i].numel) return fail(h, GNNUDS_E_INVALID, "weight tensor %d has %lld elements, expected %lld", i, (long long)sizes[i], (long long)h->tens[i].numel);
+    if (offsets[i] < 0 || offsets[i] + sizes[i] > n_floats) return fail(h, GNNUDS_E_INVALID, "weight tensor %d out of blob bounds", i);
+    if (offsets[i] % 4) return fail(h, GNNUDS_E_INVALID, "weight tensor %d offset not 16-byte aligned", i);
+    h->toff[i] = offsets[i];
+  }
+  for (int64_t i = 0; i < n_floats; ++i) if (!std::isfinite(blob[i])) return fail(h, GNNUDS_E_INVALID, "non-finite weight at blob[%lld]", (long long)i);
+  int rc;
+  if ((rc = upload(h, &h->d_blob, blob, (size_t)n_floats))) return rc;
+  // fold NodeEdge: mat = w * |inci| + b  (emulator.py:43), stored transposed + zero padded
+  if (!c.graph_base) {
+    const int N = c.n_node, M = c.n_edge, F = c.embed / 2;
+    const int IG = 256 / (F / 4);
+    auto ti_for = [&](int r_out) { int t = (r_out + IG - 1) / IG; t = (t + 3) / 4 * 4; return t; };
+    h->ti_n = ti_for(N); h->ti_m = ti_for(M);
+    h->ldm_n = IG * h->ti_n; h->ldm_m = IG * h->ti_m;
+    for (int s = 0; s < 2; ++s) { for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p); h->d_ne_matT[s].clear(); }
+    std::vector<float> inci((size_t)N * M, 0.f);
+    for (int m = 0; m < M; ++m) {
+      const int u = h->h_edges[2 * m], v = h->h_edges[2 * m + 1];
+      inci[(size_t)u * M + m] += 1.f; inci[(size_t)v * M + m] -= 1.f;
+    }
+    for (auto& v : inci) v = std::fabs(v);
+    for (int blk = 0; blk < 2; ++blk)
+      for (int l = 0; l < c.n_sp_layer; ++l) {
+        const SpatialW& w = h->sp[blk][l];
+        {  // N side: mat (N x M); matT[j=m][i=n]
+          const float* wt = blob + offsets[w.ne_n.t[0]]; const float* bs = blob + offsets[w.ne_n.t[1]];
+          std::vector<float> mt((size_t)M * h->ldm_n, 0.f);
+          for (int n = 0; n < N; ++n) for (int m = 0; m < M; ++m)
+            mt[(size_t)m * h->ldm_n + n] = wt[(size_t)n * M + m] * inci[(size_t)n * M + m] + bs[(size_t)n * M + m];
+          float* d = nullptr;
+          if ((rc = upload(h, &d, mt.data(), mt.size()))) return rc;
+          h->d_ne_matT[0].push_back(d);
+        }
+        {  // M side: mat (M x N) with |inci|^T; matT[j=n][i=m]
+          const float* wt = blob + offsets[w.ne_m.t[0]]; const float* bs = blob + offsets[w.ne_m.t[1]];
+          std::vector<float> mt((size_t)N * h->ldm_m, 0.f);
+          for (int m = 0; m < M; ++m) for (int n = 0; n < N; ++n)
+            mt[(size_t)n * h->ldm_m + m] = wt[(size_t)m * N + n] * inci[(size_t)n * M + m] + bs[(size_t)m * N + n];
+          float* d = nullptr;
+          if ((rc = upload(h, &d, mt.data(), mt.size()))) return rc;
+          h->d_ne_matT[1].push_back(d);
+        }
+      }
+  }
+  h->has_weights = true;
+  return 0;
+}
+
+int gnnuds_set_norm(gnnuds_handle* h, const float* norm_x, int32_t c_x, const float* norm_b, int32_t c_b,
+                    const float* norm_y, int32_t c_y, const float* norm_e, int32_t c_e) {
+  if (!h || !norm_x || !norm_b || !norm_y || !norm_e) return GNNUDS_E_INVALID;
+  const auto& c = h->c;
+  CU(cudaSetDevice(c.device));
+  if (c_x < c.n_in || c_b < c.b_in || c_e < c.e_in) return fail(h, GNNUDS_E_INVALID, "norm arrays have fewer channels than the inputs");
+  if (c_y < 3 + (c.if_flood ? 1 : 0)) return fail(h, GNNUDS_E_INVALID, "norm_y needs >= %d channels", 3 + (c.if_flood ? 1 : 0));
+  int rc;
+  if ((rc = upload(h, &h->d_nx, norm_x, (size_t)2 * c.n_node * c_x))) return rc;
+  if ((rc = upload(h, &h->d_nb, norm_b, (size_t)2 * c.n_node * c_b))) return rc;
+  if ((rc = upload(h, &h->d_ny, norm_y, (size_t)2 * c.n_node * c_y))) return rc;
+  if ((rc = upload(h, &h->d_ne, norm_e, (size_t)2 * c.n_edge * c_e))) return rc;
+  h->cx_n = c_x; h->cb_n = c_b; h->cy_n = c_y; h->ce_n = c_e;
+  h->has_norm = true;
+  return 0;
+}
+
+int gnnuds_output_dims(const gnnuds_handle* h, int32_t* y_channels, int32_t* ey_channels) {
+  if (!h) return GNNUDS_E_INVALID;
+  if (y_channels) *y_channels = h->ny();
+  if (ey_channels) *ey_channels = h->c.e_out;
+  return 0;
+}
+
+int gnnuds_predict(gnnuds_handle* h, const float* x, const float* b, const float* a, const float* ex, int64_t B,
+                   float* y, float* ey, int32_t where) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const auto& c = h->c;
+  if (!x || !b || !ex || !y || !ey || B < 0) return fail(h, GNNUDS_E_INVALID, "null buffer");
+  if (c.act && !a) return fail(h, GNNUDS_E_INVALID, "act model needs settings `a`");
+  CU(cudaSetDevice(c.device));
+  if (B == 0) return 0;
+  const int64_t Bc = pick_chunk(h, B);
+  if ((rc = ensure_workspace(h, Bc))) return rc;
+  const int N = c.n_node, M = c.n_edge, Ti = c.seq_in, To = c.seq_out;
+  const int64_t sx = (int64_t)Ti * N * c.n_in, sb = (int64_t)To * N * c.b_in, sa = (int64_t)To * c.n_act,
+                se = (int64_t)Ti * M * c.e_in, sy = (int64_t)To * N * h->ny(), sey = (int64_t)To * M * c.e_out;
+  begin_timing(h);
+  if (h->profiling) CU(cudaEventRecord(h->ev_a, h->stream));
+  for (int64_t b0 = 0; b0 < B; b0 += Bc) {
+    const int64_t nb = std::min(Bc, B - b0);
+    const float *px = x + b0 * sx, *pb = b + b0 * sb, *pa = a ? a + b0 * sa : nullptr, *pe = ex + b0 * se;
+    float *py = y + b0 * sy, *pey = ey + b0 * sey;
+    if (where == GNNUDS_MEM_HOST) {
+      CU(cudaMemcpyAsync(h->in_x, px, nb * sx * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+      CU(cudaMemcpyAsync(h->in_b, pb, nb * sb * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+      CU(cudaMemcpyAsync(h->in_ex, pe, nb * se * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+      if (pa) CU(cudaMemcpyAsync(h->in_a, pa, nb * sa * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+      if ((rc = forward_chunk(h, h->in_x, h->in_b, pa ? h->in_a : nullptr, h->in_ex, nb, h->out_y, h->out_ey, false))) return rc;
+      if (!h->debug_stop) {
+        CU(cudaMemcpyAsync(py, h->out_y, nb * sy * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaMemcpyAsync(pey, h->out_ey, nb * sey * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+      }
+    } else {
+      if ((rc = forward_chunk(h, px, pb, pa, pe, nb, py, pey, false))) return rc;
+    }
+    if (h->debug_stop) break;
+  }
+  if (h->profiling) CU(cudaEventRecord(h->ev_b, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (h->profiling) CU(cudaEventElapsedTime(&h->last_total_ms, h->ev_a, h->ev_b));
+  return finish_timing(h);
+}
+
+int gnnuds_simulate(gnnuds_handle* h, const float* states, const float* runoff, int32_t seq_r, const float* a,
+                    const float* edge_states, int64_t n_windows, float* y, float* ey, int32_t where) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const auto& c = h->c;
+  if (seq_r < c.seq_out) return fail(h, GNNUDS_E_INVALID, "runoff windows shorter than seq_out");
+  if (seq_r == c.seq_out) return gnnuds_predict(h, states, runoff, a, edge_states, n_windows, y, ey, where);
+  // runoff (T', seq_r, N, b_in): keep the first seq_out steps of every window (emulator.py:532)
+  if (where != GNNUDS_MEM_HOST) return fail(h, GNNUDS_E_INVALID, "simulate with seq_r > seq_out takes host buffers");
+  const size_t row = (size_t)c.n_node * c.b_in;
+  std::vector<float> r((size_t)n_windows * c.seq_out * row);
+  for (int64_t w = 0; w < n_windows; ++w)
+    std::memcpy(r.data() + (size_t)w * c.seq_out * row, runoff + (size_t)w * seq_r * row, (size_t)c.seq_out * row * sizeof(float));
+  return gnnuds_predict(h, states, r.data(), a, edge_states, n_windows, y, ey, where);
+}
+
+int gnnuds_rollout(gnnuds_handle* h, int32_t rule, const float* x0, const float* b, const float* a, const float* ex0,
+                   int64_t B, int32_t n_chunks, float* y, float* ey, int32_t where) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const auto& c = h->c;
+  if (rule < GNNUDS_ROLL_MPC || rule > GNNUDS_ROLL_NORM) return fail(h, GNNUDS_E_INVALID, "unknown feedback rule %d", rule);
+  if (c.seq_in != c.seq_out) return fail(h, GNNUDS_E_INVALID, "rollout needs seq_in == seq_out (mpc.py:573-579 feeds back seq_out steps)");
+  if (rule == GNNUDS_ROLL_MPC && !c.if_flood) return fail(h, GNNUDS_E_INVALID, "MPC feedback rule needs if_flood (mpc.py:575 drops two channels)");
+  if (!x0 || !b || !ex0 || !y || !ey || n_chunks < 1) return fail(h, GNNUDS_E_INVALID, "bad argument");
+  if (c.act && !a) return fail(h, GNNUDS_E_INVALID, "act model needs settings `a`");
+  CU(cudaSetDevice(c.device));
+  if (B == 0) return 0;
+  const bool norm_io = rule == GNNUDS_ROLL_NORM;
+  const int N = c.n_node, M = c.n_edge, T = c.seq_out;
+  const int nyc = norm_io ? 3 + (c.if_flood ? 1 : 0) : h->ny();
+  const int64_t Bc = pick_chunk(h, B);
+  if ((rc = ensure_workspace(h, Bc))) return rc;
+  // per-chunk device state: x, ex (one window), full-horizon b / a / y / ey slices
+  const int64_t Th = (int64_t)n_chunks * T;
+  const int64_t sx = (int64_t)T * N * c.n_in, se = (int64_t)T * M * c.e_in;
+  const int64_t sbh = Th * N * c.b_in, sah = Th * c.n_act, syh = Th * N * nyc, seyh = Th * M * c.e_out;
+  if (h->ro_B < Bc) {
+    for (float** p : {&h->ro_x, &h->ro_ex, &h->ro_b, &h->ro_a}) if (*p) { cudaFree(*p); *p = nullptr; }
+    h->ro_B = 0;
+  }
+  // (re)allocate horizon buffers every call: horizon may change
+  float *d_b = nullptr, *d_a = nullptr, *d_y = nullptr, *d_ey = nullptr;
+  auto cleanup = [&]() { for (float* p : {d_b, d_a, d_y, d_ey}) if (p) cudaFree(p); };
+  if (where == GNNUDS_MEM_HOST) {
+    if (cudaMalloc(&d_b, Bc * sbh * sizeof(float)) != cudaSuccess || cudaMalloc(&d_y, Bc * syh * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&d_ey, Bc * seyh * sizeof(float)) != cudaSuccess ||
+        (a && cudaMalloc(&d_a, std::max<int64_t>(Bc * sah, 1) * sizeof(float)) != cudaSuccess)) {
+      cleanup();
+      return fail(h, GNNUDS_E_NOMEM, "rollout horizon buffers");
+    }
+  }
+  if (!h->ro_x) {
+    if (cudaMalloc(&h->ro_x, Bc * sx * sizeof(float)) != cudaSuccess || cudaMalloc(&h->ro_ex, Bc * se * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&h->ro_b, Bc * T * N * c.b_in * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&h->ro_a, std::max<int64_t>(Bc * T * c.n_act, 1) * sizeof(float)) != cudaSuccess) {
+      cleanup();
+      return fail(h, GNNUDS_E_NOMEM, "rollout state buffers");
+    }
+    h->ro_B = Bc;
+  }
+  begin_timing(h);
+  if (h->profiling) cudaEventRecord(h->ev_a, h->stream);
+  rc = 0;
+  for (int64_t b0 = 0; b0 < B && !rc; b0 += Bc) {
+    const int64_t nb = std::min(Bc, B - b0);
+    const float *hb = b + b0 * sbh, *ha = a ? a + b0 * sah : nullptr;
+    float *hy = y + b0 * syh, *hey = ey + b0 * seyh;
+    const float *db, *da;
+    float *dy, *dey;
+    cudaMemcpyKind kin = where == GNNUDS_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+    cudaMemcpyAsync(h->ro_x, x0 + b0 * sx, nb * sx * sizeof(float), kin, h->stream);
+    cudaMemcpyAsync(h->ro_ex, ex0 + b0 * se, nb * se * sizeof(float), kin, h->stream);
+    if (where == GNNUDS_MEM_HOST) {
+      cudaMemcpyAsync(d_b, hb, nb * sbh * sizeof(float), kin, h->stream);
+      if (ha) cudaMemcpyAsync(d_a, ha, nb * sah * sizeof(float), kin, h->stream);
+      db = d_b; da = ha ? d_a : nullptr; dy = d_y; dey = d_ey;
+    } else {
+      db = hb; da = ha; dy = hy; dey = hey;
+    }
+    for (int k = 0; k < n_chunks && !rc; ++k) {
+      // slice chunk k of b / a into compact (nb,T,...) buffers
+      const long long Lb = (long long)N * c.b_in;
+      slice_time_kernel<<<grid_for(h, nb * T * Lb, 256, 16), 256, 0, h->stream>>>(db, h->ro_b, nb, (int)Th, k * T, T, Lb, 0);
+      ++h->launches;
+      if (da) {
+        slice_time_kernel<<<grid_for(h, nb * T * c.n_act, 256, 16), 256, 0, h->stream>>>(da, h->ro_a, nb, (int)Th, k * T, T, c.n_act, 0);
+        ++h->launches;
+      }
+      rc = forward_chunk(h, h->ro_x, h->ro_b, da ? h->ro_a : nullptr, h->ro_ex, nb, h->out_y, h->out_ey, norm_io);
+      if (rc) break;
+      // scatter outputs into the horizon tensors
+      slice_time_kernel<<<grid_for(h, nb * T * (long long)N * nyc, 256, 16), 256, 0, h->stream>>>(h->out_y, dy, nb, (int)Th, k * T, T, (long long)N * nyc, 1);
+      slice_time_kernel<<<grid_for(h, nb * T * (long long)M * c.e_out, 256, 16), 256, 0, h->stream>>>(h->out_ey, dey, nb, (int)Th, k * T, T, (long long)M * c.e_out, 1);
+      h->launches += 2;
+      if (k + 1 < n_chunks) {
+        FeedP p{};
+        p.y = h->out_y; p.ny = nyc; p.ey = h->out_ey; p.e_out = c.e_out; p.b = h->ro_b; p.b_in = c.b_in;
+        p.a = da ? h->ro_a : nullptr; p.n_act = c.n_act; p.act_of_edge = h->d_act_of_edge;
+        p.x = h->ro_x; p.n_in = c.n_in; p.ex = h->ro_ex; p.e_in = c.e_in;
+        p.S = nb * T; p.N = N; p.M = M; p.if_flood = c.if_flood ? 1 : 0; p.rule = rule;
+        feedback_kernel<<<grid_for(h, p.S * (N + M), 256, 16), 256, 0, h->stream>>>(p);
+        ++h->launches;
+      }
+      if (cudaGetLastError() != cudaSuccess) rc = fail(h, GNNUDS_E_CUDA, "rollout kernel launch failed");
+    }
+    if (!rc && where == GNNUDS_MEM_HOST) {
+      cudaMemcpyAsync(hy, d_y, nb * syh * sizeof(float), cudaMemcpyDeviceToHost, h->stream);
+      cudaMemcpyAsync(hey, d_ey, nb * seyh * sizeof(float), cudaMemcpyDeviceToHost, h->stream);
+    }
+  }
+  if (h->profiling) cudaEventRecord(h->ev_b, h->stream);
+  cudaError_t e = cudaStreamSynchronize(h->stream);
+  cleanup();
+  if (rc) return rc;
+  if (e != cudaSuccess) return fail(h, GNNUDS_E_CUDA, "rollout: %s", cudaGetErrorString(e));
+  if (h->profiling) cudaEventElapsedTime(&h->last_total_ms, h->ev_a, h->ev_b);
+  return finish_timing(h);
+}
+
+int gnnuds_objective(gnnuds_handle* h, const float* y, const float* q_in0, int64_t B, int32_t T, const float* flood_w,
+                     const float* wwtp_w, const float* rough_w, const float* gamma, float* obj, int32_t where) {
+  if (!h || !y || !q_in0 || !flood_w || !wwtp_w || !obj) return GNNUDS_E_INVALID;
+  const auto& c = h->c;
+  CU(cudaSetDevice(c.device));
+  if (B == 0) return 0;
+  const int N = c.n_node, nyc = h->ny();
+  float *dfw = nullptr, *dww = nullptr, *drw = nullptr, *dg = nullptr, *dy = nullptr, *dq = nullptr, *dobj = nullptr;
+  auto cleanup = [&]() { for (float* p : {dfw, dww, drw, dg, dy, dq, dobj}) if (p) cudaFree(p); };
+  int rc = 0;
+  auto up = [&](float** d, const float* s, size_t n) {
+    if (cudaMalloc(d, n * sizeof(float)) != cudaSuccess) return 1;
+    return cudaMemcpyAsync(*d, s, n * sizeof(float), cudaMemcpyHostToDevice, h->stream) != cudaSuccess ? 1 : 0;
+  };
+  rc |= up(&dfw, flood_w, N); rc |= up(&dww, wwtp_w, N);
+  if (rough_w) rc |= up(&drw, rough_w, N);
+  if (gamma) rc |= up(&dg, gamma, T);
+  const float *py = y, *pq = q_in0;
+  float* po = obj;
+  if (where == GNNUDS_MEM_HOST) {
+    rc |= up(&dy, y, (size_t)B * T * N * nyc); rc |= up(&dq, q_in0, (size_t)B * N);
+    if (cudaMalloc(&dobj, B * sizeof(float)) != cudaSuccess) rc = 1;
+    py = dy; pq = dq; po = dobj;
+  }
+  if (rc) { cleanup(); return fail(h, GNNUDS_E_NOMEM, "objective buffers"); }
+  ObjP p{py, nyc, pq, dfw, dww, drw, dg, po, B, T, N};
+  objective_kernel<<<grid_for(h, B, 1, 16), 128, 0, h->stream>>>(p);
+  ++h->launches;
+  if (where == GNNUDS_MEM_HOST) cudaMemcpyAsync(obj, dobj, B * sizeof(float), cudaMemcpyDeviceToHost, h->stream);
+  cudaError_t e = cudaStreamSynchronize(h->stream);
+  cleanup();
+  if (e != cudaSuccess) return fail(h, GNNUDS_E_CUDA, "objective: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+int gnnuds_alloc_pinned(void** p, int64_t bytes) {
+  if (!p) return GNNUDS_E_INVALID;
+  return cudaMallocHost(p, (size_t)bytes) == cudaSuccess ? 0 : GNNUDS_E_NOMEM;
+}
+int gnnuds_free_pinned(void* p) { return cudaFreeHost(p) == cudaSuccess ? 0 : GNNUDS_E_CUDA; }
+int gnnuds_alloc_device(gnnuds_handle* h, void** p, int64_t bytes) {
+  if (!h || !p) return GNNUDS_E_INVALID;
+  CU(cudaSetDevice(h->c.device));
+  return cudaMalloc(p, (size_t)bytes) == cudaSuccess ? 0 : fail(h, GNNUDS_E_NOMEM, "cudaMalloc(%lld) failed", (long long)bytes);
+}
+int gnnuds_free_device(gnnuds_handle* h, void* p) {
+  if (!h) return GNNUDS_E_INVALID;
+  CU(cudaSetDevice(h->c.device));
+  CU(cudaFree(p));
+  return 0;
+}
+int gnnuds_memcpy(gnnuds_handle* h, void* dst, const void* src, int64_t bytes, int32_t kind) {
+  if (!h) return GNNUDS_E_INVALID;
+  CU(cudaSetDevice(h->c.device));
+  CU(cudaMemcpyAsync(dst, src, (size_t)bytes, kind == 1 ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+int gnnuds_synchronize(gnnuds_handle* h) {
+  if (!h) return GNNUDS_E_INVALID;
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+int64_t gnnuds_launch_count(const gnnuds_handle* h) { return h ? h->launches : 0; }
+int gnnuds_last_timing(const gnnuds_handle* h, float* total_ms, float* gemm_ms) {
+  if (!h) return GNNUDS_E_INVALID;
+  if (total_ms) *total_ms = h->last_total_ms;
+  if (gemm_ms) *gemm_ms = h->last_gemm_ms;
+  return 0;
+}
+int gnnuds_set_profiling(gnnuds_handle* h, int32_t on) {
+  if (!h) return GNNUDS_E_INVALID;
+  h->profiling = on;
+  return 0;
+}
+int gnnuds_debug_stop_after(gnnuds_handle* h, int32_t stage) {
+  if (!h) return GNNUDS_E_INVALID;
+  h->debug_stop = stage;
+  return 0;
+}
+int gnnuds_debug_fetch(gnnuds_handle* h, int32_t which, float* out, int64_t max_floats, int64_t* rows, int32_t* width) {
+  if (!h || which < 0 || which > 1 || !h->dbg_ptr[which]) return GNNUDS_E_INVALID;
+  CU(cudaSetDevice(h->c.device));
+  const int64_t n = h->dbg_rows[which] * h->dbg_width[which];
+  if (rows) *rows = h->dbg_rows[which];
+  if (width) *width = h->dbg_width[which];
+  if (out) {
+    if (n > max_floats) return fail(h, GNNUDS_E_INVALID, "debug_fetch: buffer too small");
+    CU(cudaMemcpy(out, h->dbg_ptr[which], n * sizeof(float), cudaMemcpyDeviceToHost));
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,901 @@
+// Device kernels of the Emulator forward (sm_100a).  fp32 SIMT parity path.
+//
+// Activation layout everywhere: rows = (scenario b, time t, element n) flattened,
+// features contiguous -> [B][T][Nn][C].  In this layout the reference's
+// transpose/reshape pairs around the temporal nets (emulator.py:244-257,299-310)
+// disappear: a causal dilated Conv1D tap is the same GEMM reading rows shifted
+// by shift*Nn, and the GRU walks rows with stride Nn.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace gu {
+
+enum { ACT_LINEAR = 0, ACT_RELU = 1, ACT_TANH = 2, ACT_SIGMOID = 3, ACT_HARD_SIGMOID = 4 };
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+  switch (act) {
+    case ACT_RELU: return fmaxf(v, 0.f);
+    case ACT_TANH: return tanhf(v);
+    case ACT_SIGMOID: return 1.f / (1.f + expf(-v));
+    case ACT_HARD_SIGMOID: return fminf(fmaxf(0.2f * v + 0.5f, 0.f), 1.f);   // keras 2.x hard_sigmoid
+    default: return v;
+  }
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---------------------------------------------------------------------------
+// K1 embedding (emulator.py:195-213): Dense over a tiny channel count fused with
+// the min-max normalisation (emulator.py:803-810) and, for the control input,
+// with get_edge_action's scatter (emulator.py:385-398).
+// ---------------------------------------------------------------------------
+struct EmbedP {
+  const float* in;        // (Bc, T, Nn, K) raw physical values; mode 2: a (Bc, T, n_act)
+  const float* nmax;      // (Nn, cn) or null (no normalisation)
+  const float* nmin;
+  int cn;
+  const int* gather;      // mode 2: act_of_edge (Nn) column of a or -1
+  int n_act;
+  const float* W;         // (K, Eo)
+  const float* bias;      // (Eo)
+  float* out;             // (rows, Eo) activated
+  float* res;             // (Bc*Nn, Eo) pre-activation of the last time step, or null
+  long long rows;
+  int T, Nn, K, Eo, act, mode;   // mode 0: plain, 2: gathered control input (K == 1)
+};
+
+__global__ void __launch_bounds__(256) embed_kernel(EmbedP p) {
+  extern __shared__ float sm[];
+  float* Ws = sm;                      // K*Eo
+  float* bs = sm + p.K * p.Eo;         // Eo
+  for (int i = threadIdx.x; i < p.K * p.Eo; i += blockDim.x) Ws[i] = p.W[i];
+  for (int i = threadIdx.x; i < p.Eo; i += blockDim.x) bs[i] = p.bias[i];
+  __syncthreads();
+  const int g4 = p.Eo >> 2;                       // float4 groups per row
+  const int rows_per_blk = blockDim.x / g4;
+  const int lr = threadIdx.x / g4, c4 = threadIdx.x % g4;
+  if (lr >= rows_per_blk) return;
+  for (long long r = (long long)blockIdx.x * rows_per_blk + lr; r < p.rows;
+       r += (long long)gridDim.x * rows_per_blk) {
+    const int n = (int)(r % p.Nn);
+    const long long bt = r / p.Nn;
+    float xin[8];
+    if (p.mode == 2) {
+      const int k = p.gather[n];
+      xin[0] = (k >= 0) ? p.in[bt * p.n_act + k] : 1.f;
+    } else {
+      for (int c = 0; c < p.K; ++c) {
+        float v = p.in[r * p.K + c];
+        if (p.nmax) {
+          const float mx = p.nmax[n * p.cn + c], mn = p.nmin[n * p.cn + c];
+          v = (v - mn) / (mx - mn);
+        }
+        xin[c] = v;
+      }
+    }
+    float4 acc = *reinterpret_cast<const float4*>(bs + c4 * 4);
+    // keras Dense: x @ W + b, accumulate over input channels in order
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int c = 0; c < p.K; ++c) {
+      const float4 w = *reinterpret_cast<const float4*>(Ws + c * p.Eo + c4 * 4);
+      s.x = fmaf(xin[c], w.x, s.x); s.y = fmaf(xin[c], w.y, s.y);
+      s.z = fmaf(xin[c], w.z, s.z); s.w = fmaf(xin[c], w.w, s.w);
+    }
+    acc.x += s.x; acc.y += s.y; acc.z += s.z; acc.w += s.w;
+    if (p.res) {
+      const int t = (int)(bt % p.T);
+      if (t == p.T - 1) {
+        const long long b = bt / p.T;
+        *reinterpret_cast<float4*>(p.res + (b * p.Nn + n) * p.Eo + c4 * 4) = acc;
+      }
+    }
+    acc.x = apply_act(acc.x, p.act); acc.y = apply_act(acc.y, p.act);
+    acc.z = apply_act(acc.z, p.act); acc.w = apply_act(acc.w, p.act);
+    *reinterpret_cast<float4*>(p.out + r * p.Eo + c4 * 4) = acc;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// rows GEMM (fp32 SIMT): out[r,:] = act( sum_seg A_seg[src(r,seg), :] @ W_seg + bias ).
+// Covers every Dense, the GCN/GAT linear part on the concatenated [x | NodeEdge(x_e)]
+// input (two segments, emulator.py:227-230), the causal dilated Conv1D (k shifted
+// segments, emulator.py:156-157) and the GRU/LSTM input projections.
+// ---------------------------------------------------------------------------
+// Logical rows are (b, t, n), n < Nn.  A segment's physical row is
+// (b*Ts + t + (Ts-Td) - shift) * pitch + off + n (zero when the time index is negative);
+// the destination row is (b*Td + t) * pitch_d + off_d + n.  pitch/off let node and edge
+// rows share one joint buffer (graph_base != 0).
+struct Seg { const float* p; int ld; int width; int shift; int pitch; int off; };
+struct GemmP {
+  Seg seg[4]; int nseg;
+  const float* W;        // (sum width, Nout) row-major
+  const float* bias;     // (Nout) or null
+  float* out; int ldo; int Nout; int act;
+  long long rows;        // logical rows = Bc*Td*Nn
+  int Nn, Td, Ts;        // destination / source time lengths (Ts >= Td keeps the last Td steps)
+  int pitch_d, off_d;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(256) rows_gemm_f32(GemmP p) {
+  constexpr int BM = 128, BK = 16, TN = BN / 16;
+  __shared__ __align__(16) float As[2][BK][BM];
+  __shared__ __align__(16) float Ws[2][BK][BN];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const long long row0 = (long long)blockIdx.x * BM;
+  const int col0 = blockIdx.y * BN;
+
+  // loader mapping: one A row per thread-pair
+  const int lrow = tid & 127, lhalf = tid >> 7;
+  const long long r = row0 + lrow;
+  long long srow[4];
+  {
+    const int n = (int)(r % p.Nn);
+    const long long bt = r / p.Nn;
+    const int t = (int)(bt % p.Td);
+    const long long b = bt / p.Td;
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      srow[s] = -1;
+      if (s < p.nseg && r < p.rows) {
+        const int ts = t + (p.Ts - p.Td) - p.seg[s].shift;
+        if (ts >= 0) srow[s] = (b * p.Ts + ts) * p.seg[s].pitch + p.seg[s].off + n;
+      }
+    }
+  }
+  float acc[8][TN];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+  int nk = 0;
+  for (int s = 0; s < p.nseg; ++s) nk += p.seg[s].width / BK;
+
+  constexpr int WLD = BN * BK / 4 / 256;   // float4 loads of W per thread (1 for BN=64, 2 for BN=128)
+  float4 ra0, ra1;
+  float4 rw[WLD];
+
+  int seg_i = 0, seg_k = 0, kglob = 0;
+  auto load_tile = [&]() {
+    const Seg& sg = p.seg[seg_i];
+    const long long sr = seg_i == 0 ? srow[0] : seg_i == 1 ? srow[1] : seg_i == 2 ? srow[2] : srow[3];
+    if (sr >= 0) {
+      const float* ap = sg.p + sr * sg.ld + seg_k + lhalf * 8;
+      ra0 = *reinterpret_cast<const float4*>(ap);
+      ra1 = *reinterpret_cast<const float4*>(ap + 4);
+    } else {
+      ra0 = make_float4(0.f, 0.f, 0.f, 0.f); ra1 = ra0;
+    }
+#pragma unroll
+    for (int i = 0; i < WLD; ++i) {
+      const int idx = tid + i * 256;
+      const int kk = idx / (BN / 4), c4 = idx % (BN / 4);
+      rw[i] = *reinterpret_cast<const float4*>(p.W + (long long)(kglob + kk) * p.Nout + col0 + c4 * 4);
+    }
+    kglob += BK; seg_k += BK;
+    if (seg_k >= sg.width) { seg_k = 0; ++seg_i; }
+  };
+  auto store_tile = [&](int buf) {
+    const int k0 = lhalf * 8;
+    As[buf][k0 + 0][lrow] = ra0.x; As[buf][k0 + 1][lrow] = ra0.y;
+    As[buf][k0 + 2][lrow] = ra0.z; As[buf][k0 + 3][lrow] = ra0.w;
+    As[buf][k0 + 4][lrow] = ra1.x; As[buf][k0 + 5][lrow] = ra1.y;
+    As[buf][k0 + 6][lrow] = ra1.z; As[buf][k0 + 7][lrow] = ra1.w;
+#pragma unroll
+    for (int i = 0; i < WLD; ++i) {
+      const int idx = tid + i * 256;
+      const int kk = idx / (BN / 4), c4 = idx % (BN / 4);
+      *reinterpret_cast<float4*>(&Ws[buf][kk][c4 * 4]) = rw[i];
+    }
+  };
+
+  load_tile();
+  store_tile(0);
+  __syncthreads();
+  int cur = 0;
+  for (int it = 0; it < nk; ++it) {
+    if (it + 1 < nk) load_tile();
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      const float4 a0 = *reinterpret_cast<const float4*>(&As[cur][kk][ty * 8]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&As[cur][kk][ty * 8 + 4]);
+      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      float b[TN];
+#pragma unroll
+      for (int j4 = 0; j4 < TN / 4; ++j4) {
+        const float4 bv = *reinterpret_cast<const float4*>(&Ws[cur][kk][j4 * 64 + tx * 4]);
+        b[j4 * 4 + 0] = bv.x; b[j4 * 4 + 1] = bv.y; b[j4 * 4 + 2] = bv.z; b[j4 * 4 + 3] = bv.w;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    if (it + 1 < nk) store_tile(cur ^ 1);
+    __syncthreads();
+    cur ^= 1;
+  }
+
+#pragma unroll
+  for (int j4 = 0; j4 < TN / 4; ++j4) {
+    const int col = col0 + j4 * 64 + tx * 4;
+    float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.bias) bb = *reinterpret_cast<const float4*>(p.bias + col);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const long long rl = row0 + ty * 8 + i;
+      if (rl < p.rows) {
+        const long long rr = (rl / p.Nn) * p.pitch_d + p.off_d + (rl % p.Nn);
+        float4 v;
+        v.x = apply_act(acc[i][j4 * 4 + 0] + bb.x, p.act);
+        v.y = apply_act(acc[i][j4 * 4 + 1] + bb.y, p.act);
+        v.z = apply_act(acc[i][j4 * 4 + 2] + bb.z, p.act);
+        v.w = apply_act(acc[i][j4 * 4 + 3] + bb.w, p.act);
+        *reinterpret_cast<float4*>(p.out + rr * p.ldo + col) = v;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K2 NodeEdge (emulator.py:27-45): out[s] = (w*|inci| + b) @ in[s], the folded
+// dense (R_out x R_in) matrix resident in shared memory (transposed), SPB samples
+// per CTA pass, persistent over samples.
+// ---------------------------------------------------------------------------
+struct NodeEdgeP {
+  const float* matT;     // (R_in, ldm) transposed folded matrix, zero padded to ldm
+  const float* in;       // (S, R_in, F)
+  float* out;            // (S, R_out, F)
+  long long S;
+  int R_in, R_out, F, ldm;
+};
+
+template <int TI>
+__global__ void __launch_bounds__(512) nodeedge_kernel(NodeEdgeP p) {
+  extern __shared__ __align__(16) float sm[];
+  float* Ms = sm;                                   // R_in * ldm
+  float* Xs = sm + (size_t)p.R_in * p.ldm;          // 2 * R_in * F
+  const int tid = threadIdx.x;
+  for (int i = tid * 4; i < p.R_in * p.ldm; i += blockDim.x * 4)
+    *reinterpret_cast<float4*>(Ms + i) = *reinterpret_cast<const float4*>(p.matT + i);
+  const int half = tid >> 8, t = tid & 255;
+  const int FG = p.F >> 2;                          // float4 feature groups
+  const int fg = t % FG, ig = t / FG;
+  const int IG = 256 / FG;
+  const int i0 = ig * TI;
+  float* Xh = Xs + (size_t)half * p.R_in * p.F;
+  for (long long s0 = (long long)blockIdx.x * 2; s0 < p.S; s0 += (long long)gridDim.x * 2) {
+    const long long s = s0 + half;
+    __syncthreads();
+    if (s < p.S) {
+      const float* src = p.in + s * p.R_in * p.F;
+      for (int i = t * 4; i < p.R_in * p.F; i += 256 * 4)
+        *reinterpret_cast<float4*>(Xh + i) = *reinterpret_cast<const float4*>(src + i);
+    }
+    __syncthreads();
+    if (s >= p.S || ig >= IG || i0 >= p.R_out) continue;
+    float4 acc[TI];
+#pragma unroll
+    for (int i = 0; i < TI; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int j = 0; j < p.R_in; ++j) {
+      const float4 x = *reinterpret_cast<const float4*>(Xh + j * p.F + fg * 4);
+      const float* mrow = Ms + (size_t)j * p.ldm + i0;
+#pragma unroll
+      for (int i4 = 0; i4 < TI / 4; ++i4) {
+        const float4 m = *reinterpret_cast<const float4*>(mrow + i4 * 4);
+        const float mm[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float4& a = acc[i4 * 4 + q];
+          a.x = fmaf(mm[q], x.x, a.x); a.y = fmaf(mm[q], x.y, a.y);
+          a.z = fmaf(mm[q], x.z, a.z); a.w = fmaf(mm[q], x.w, a.w);
+        }
+      }
+    }
+    float* dst = p.out + s * p.R_out * p.F;
+#pragma unroll
+    for (int i = 0; i < TI; ++i)
+      if (i0 + i < p.R_out) *reinterpret_cast<float4*>(dst + (size_t)(i0 + i) * p.F + fg * 4) = acc[i];
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K4/K5 neighbour aggregation on CSR (spektral GCNConv / GATConv dense mode restated
+// sparse): one CTA per (b,t) sample, the sample's h = x@W tile staged in shared memory.
+//   GCN: out_i = act( sum_j val_ij h_j + bias )
+//   GAT: score_ij = leaky_relu(h_i.a_self + h_j.a_neigh, 0.2) over the nonzero pattern
+//        (diagonal forced), alpha = softmax_j, out_i = act( sum_j alpha_ij h_j + bias ).
+// The reference's -1e10 mask makes masked entries exactly 0 after exp, so the CSR softmax
+// over the pattern is the same function.
+// ---------------------------------------------------------------------------
+struct AggP {
+  const float* h;        // (S, R, E)
+  float* out;            // (S, R, E)
+  const int* row_ptr; const int* col_idx; const float* val;   // val null for GAT
+  const float* a_self; const float* a_neigh;                  // (E) GAT only
+  const float* bias;     // (E)
+  long long S; int R, E, act, gat;
+};
+
+__global__ void __launch_bounds__(256) agg_small_kernel(AggP p) {
+  extern __shared__ __align__(16) float sm[];
+  float* hs = sm;                          // R*E
+  float* ss = sm + (size_t)p.R * p.E;      // R
+  float* sn = ss + p.R;                    // R
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  const int E = p.E;
+  for (long long s = blockIdx.x; s < p.S; s += gridDim.x) {
+    const float* src = p.h + s * p.R * E;
+    __syncthreads();
+    for (int i = tid * 4; i < p.R * E; i += blockDim.x * 4)
+      *reinterpret_cast<float4*>(hs + i) = *reinterpret_cast<const float4*>(src + i);
+    __syncthreads();
+    if (p.gat) {
+      for (int i = warp; i < p.R; i += nwarp) {
+        float d1 = 0.f, d2 = 0.f;
+        for (int c = lane * 4; c < E; c += 128) {
+          const float4 hv = *reinterpret_cast<const float4*>(hs + (size_t)i * E + c);
+          const float4 a1 = *reinterpret_cast<const float4*>(p.a_self + c);
+          const float4 a2 = *reinterpret_cast<const float4*>(p.a_neigh + c);
+          d1 += hv.x * a1.x + hv.y * a1.y + hv.z * a1.z + hv.w * a1.w;
+          d2 += hv.x * a2.x + hv.y * a2.y + hv.z * a2.z + hv.w * a2.w;
+        }
+        d1 = warp_sum(d1); d2 = warp_sum(d2);
+        if (lane == 0) { ss[i] = d1; sn[i] = d2; }
+      }
+      __syncthreads();
+    }
+    float* dst = p.out + s * p.R * E;
+    for (int i = warp; i < p.R; i += nwarp) {
+      const int beg = p.row_ptr[i], end = p.row_ptr[i + 1];
+      float mx = -INFINITY;
+      if (p.gat) {
+        const float si = ss[i];
+        for (int q = beg + lane; q < end; q += 32) {
+          float sc = si + sn[p.col_idx[q]];
+          sc = sc > 0.f ? sc : 0.2f * sc;
+          mx = fmaxf(mx, sc);
+        }
+        mx = warp_max(mx);
+      }
+      for (int c0 = 0; c0 < E; c0 += 128) {
+        const int c = c0 + lane * 4;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        float den = 0.f;
+        for (int q0 = beg; q0 < end; q0 += 32) {
+          const int q = q0 + lane;
+          int cj = 0; float wj = 0.f;
+          if (q < end) {
+            cj = p.col_idx[q];
+            if (p.gat) {
+              float sc = ss[i] + sn[cj];
+              sc = sc > 0.f ? sc : 0.2f * sc;
+              wj = expf(sc - mx);
+            } else {
+              wj = p.val[q];
+            }
+          }
+          if (p.gat) den += wj;
+          const int cnt = min(32, end - q0);
+          for (int u = 0; u < cnt; ++u) {
+            const float w = __shfl_sync(0xffffffffu, wj, u);
+            const int j = __shfl_sync(0xffffffffu, cj, u);
+            if (c < E) {
+              const float4 hv = *reinterpret_cast<const float4*>(hs + (size_t)j * E + c);
+              acc.x = fmaf(w, hv.x, acc.x); acc.y = fmaf(w, hv.y, acc.y);
+              acc.z = fmaf(w, hv.z, acc.z); acc.w = fmaf(w, hv.w, acc.w);
+            }
+          }
+        }
+        if (p.gat) {
+          den = warp_sum(den);
+          const float inv = 1.f / den;
+          acc.x *= inv; acc.y *= inv; acc.z *= inv; acc.w *= inv;
+        }
+        if (c < E) {
+          const float4 bb = *reinterpret_cast<const float4*>(p.bias + c);
+          float4 v;
+          v.x = apply_act(acc.x + bb.x, p.act); v.y = apply_act(acc.y + bb.y, p.act);
+          v.z = apply_act(acc.z + bb.z, p.act); v.w = apply_act(acc.w + bb.w, p.act);
+          *reinterpret_cast<float4*>(dst + (size_t)i * E + c) = v;
+        }
+      }
+    }
+  }
+}
+
+// Large-graph path: h does not fit on chip; one warp per (sample,row),
+// 128-bit gathers of neighbour rows straight from HBM/L2.  Scores for GAT come from
+// row_scores_kernel.
+struct AggLargeP {
+  const float* h; float* out;
+  const int* row_ptr; const int* col_idx; const float* val;
+  const float* ss; const float* sn;     // (S*R) GAT scores or null
+  const float* bias;
+  long long S; int R, E, act, gat;
+};
+
+__global__ void __launch_bounds__(256) row_scores_kernel(const float* __restrict__ h, const float* __restrict__ a_self,
+                                                         const float* __restrict__ a_neigh, float* __restrict__ ss,
+                                                         float* __restrict__ sn, long long rows, int E) {
+  const int lane = threadIdx.x & 31;
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long r = w; r < rows; r += nw) {
+    float d1 = 0.f, d2 = 0.f;
+    for (int c = lane * 4; c < E; c += 128) {
+      const float4 hv = __ldg(reinterpret_cast<const float4*>(h + r * E + c));
+      const float4 a1 = *reinterpret_cast<const float4*>(a_self + c);
+      const float4 a2 = *reinterpret_cast<const float4*>(a_neigh + c);
+      d1 += hv.x * a1.x + hv.y * a1.y + hv.z * a1.z + hv.w * a1.w;
+      d2 += hv.x * a2.x + hv.y * a2.y + hv.z * a2.z + hv.w * a2.w;
+    }
+    d1 = warp_sum(d1); d2 = warp_sum(d2);
+    if (lane == 0) { ss[r] = d1; sn[r] = d2; }
+  }
+}
+
+__global__ void __launch_bounds__(256) agg_large_kernel(AggLargeP p) {
+  const int lane = threadIdx.x & 31;
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  const long long total = p.S * p.R;
+  const int E = p.E;
+  for (long long g = w; g < total; g += nw) {
+    const long long s = g / p.R;
+    const int i = (int)(g % p.R);
+    const float* hb = p.h + s * p.R * E;
+    const int beg = p.row_ptr[i], end = p.row_ptr[i + 1];
+    float mx = -INFINITY, si = 0.f;
+    if (p.gat) {
+      si = p.ss[s * p.R + i];
+      for (int q = beg + lane; q < end; q += 32) {
+        float sc = si + p.sn[s * p.R + p.col_idx[q]];
+        sc = sc > 0.f ? sc : 0.2f * sc;
+        mx = fmaxf(mx, sc);
+      }
+      mx = warp_max(mx);
+    }
+    for (int c0 = 0; c0 < E; c0 += 128) {
+      const int c = c0 + lane * 4;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      float den = 0.f;
+      for (int q0 = beg; q0 < end; q0 += 32) {
+        const int q = q0 + lane;
+        int cj = 0; float wj = 0.f;
+        if (q < end) {
+          cj = p.col_idx[q];
+          if (p.gat) {
+            float sc = si + p.sn[s * p.R + cj];
+            sc = sc > 0.f ? sc : 0.2f * sc;
+            wj = expf(sc - mx);
+          } else wj = p.val[q];
+        }
+        if (p.gat) den += wj;
+        const int cnt = min(32, end - q0);
+        for (int u = 0; u < cnt; ++u) {
+          const float wv = __shfl_sync(0xffffffffu, wj, u);
+          const int j = __shfl_sync(0xffffffffu, cj, u);
+          if (c < E) {
+            const float4 hv = __ldg(reinterpret_cast<const float4*>(hb + (size_t)j * E + c));
+            acc.x = fmaf(wv, hv.x, acc.x); acc.y = fmaf(wv, hv.y, acc.y);
+            acc.z = fmaf(wv, hv.z, acc.z); acc.w = fmaf(wv, hv.w, acc.w);
+          }
+        }
+      }
+      if (p.gat) {
+        den = warp_sum(den);
+        const float inv = 1.f / den;
+        acc.x *= inv; acc.y *= inv; acc.z *= inv; acc.w *= inv;
+      }
+      if (c < E) {
+        const float4 bb = *reinterpret_cast<const float4*>(p.bias + c);
+        float4 v;
+        v.x = apply_act(acc.x + bb.x, p.act); v.y = apply_act(acc.y + bb.y, p.act);
+        v.z = apply_act(acc.z + bb.z, p.act); v.w = apply_act(acc.w + bb.w, p.act);
+        *reinterpret_cast<float4*>(p.out + (s * p.R + i) * E + c) = v;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K6 GRU recurrence (keras GRU v2, reset_after=True): mx = x_t@K + b[0] comes from
+// rows_gemm; here h_t = z*h + (1-z)*tanh(mx_h + r*(h@R + b[1])_h) walks t in-kernel.
+// One CTA owns 32 (b,n) sequences; R (H x 3H) lives in shared memory.
+// ---------------------------------------------------------------------------
+struct GruP {
+  const float* mx;       // (Bc, Ts, Nn, 3H)
+  const float* R;        // (H, 3H)
+  const float* b1;       // (3H) recurrent bias
+  float* out;            // (Bc, Td, Nn, H) last Td steps
+  long long nseq;        // Bc*Nn
+  int Nn, Ts, Td, H;
+};
+
+__global__ void __launch_bounds__(256) gru_kernel(GruP p) {
+  extern __shared__ __align__(16) float sm[];
+  const int H = p.H, G = 3 * H;
+  float* Rs = sm;                    // H*G
+  float* hs = Rs + (size_t)H * G;    // 32*H
+  float* mh = hs + 32 * H;           // 32*G
+  const int tid = threadIdx.x;
+  for (int i = tid * 4; i < H * G; i += 256 * 4)
+    *reinterpret_cast<float4*>(Rs + i) = *reinterpret_cast<const float4*>(p.R + i);
+  for (int i = tid; i < 32 * H; i += 256) hs[i] = 0.f;
+  const int rr = tid >> 3, gg = tid & 7;             // 32 sequences x 8 column groups
+  const long long q = (long long)blockIdx.x * 32 + rr;
+  const bool live = q < p.nseq;
+  const long long b = live ? q / p.Nn : 0;
+  const int n = live ? (int)(q % p.Nn) : 0;
+  const int ncol4 = G / 32;                          // float4 column groups per thread (G=192 -> 6)
+  __syncthreads();
+  for (int t = 0; t < p.Ts; ++t) {
+    // mh[rr][:] = hs[rr][:] @ R + b1
+    for (int qq = 0; qq < ncol4; ++qq) {
+      const int col = qq * 32 + gg * 4;
+      float4 acc = *reinterpret_cast<const float4*>(p.b1 + col);
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < H; ++k) {
+        const float hv = hs[rr * H + k];
+        const float4 rv = *reinterpret_cast<const float4*>(Rs + (size_t)k * G + col);
+        s.x = fmaf(hv, rv.x, s.x); s.y = fmaf(hv, rv.y, s.y);
+        s.z = fmaf(hv, rv.z, s.z); s.w = fmaf(hv, rv.w, s.w);
+      }
+      acc.x += s.x; acc.y += s.y; acc.z += s.z; acc.w += s.w;
+      *reinterpret_cast<float4*>(mh + rr * G + col) = acc;
+    }
+    __syncthreads();
+    if (live) {
+      const float* mxr = p.mx + ((b * p.Ts + t) * p.Nn + n) * G;
+      for (int u = gg; u < H; u += 8) {
+        const float z = 1.f / (1.f + expf(-(mxr[u] + mh[rr * G + u])));
+        const float r = 1.f / (1.f + expf(-(mxr[H + u] + mh[rr * G + H + u])));
+        const float hh = tanhf(mxr[2 * H + u] + r * mh[rr * G + 2 * H + u]);
+        const float hn = z * hs[rr * H + u] + (1.f - z) * hh;
+        hs[rr * H + u] = hn;
+        const int td = t - (p.Ts - p.Td);
+        if (td >= 0) p.out[((b * p.Td + td) * p.Nn + n) * H + u] = hn;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// K6 LSTM recurrence (keras LSTM v2; gate order i,f,c,o): zx = x_t@K + b from rows_gemm.
+struct LstmP {
+  const float* zx; const float* R; float* out; long long nseq; int Nn, Ts, Td, H;
+};
+
+__global__ void __launch_bounds__(256) lstm_kernel(LstmP p) {
+  extern __shared__ __align__(16) float sm[];
+  const int H = p.H, G = 4 * H;
+  float* Rs = sm;                    // H*G
+  float* hs = Rs + (size_t)H * G;    // 32*H
+  float* cs = hs + 32 * H;           // 32*H
+  float* mh = cs + 32 * H;           // 32*G
+  const int tid = threadIdx.x;
+  for (int i = tid * 4; i < H * G; i += 256 * 4)
+    *reinterpret_cast<float4*>(Rs + i) = *reinterpret_cast<const float4*>(p.R + i);
+  for (int i = tid; i < 32 * H; i += 256) { hs[i] = 0.f; cs[i] = 0.f; }
+  const int rr = tid >> 3, gg = tid & 7;
+  const long long q = (long long)blockIdx.x * 32 + rr;
+  const bool live = q < p.nseq;
+  const long long b = live ? q / p.Nn : 0;
+  const int n = live ? (int)(q % p.Nn) : 0;
+  const int ncol4 = G / 32;
+  __syncthreads();
+  for (int t = 0; t < p.Ts; ++t) {
+    for (int qq = 0; qq < ncol4; ++qq) {
+      const int col = qq * 32 + gg * 4;
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < H; ++k) {
+        const float hv = hs[rr * H + k];
+        const float4 rv = *reinterpret_cast<const float4*>(Rs + (size_t)k * G + col);
+        s.x = fmaf(hv, rv.x, s.x); s.y = fmaf(hv, rv.y, s.y);
+        s.z = fmaf(hv, rv.z, s.z); s.w = fmaf(hv, rv.w, s.w);
+      }
+      *reinterpret_cast<float4*>(mh + rr * G + col) = s;
+    }
+    __syncthreads();
+    if (live) {
+      const float* zr = p.zx + ((b * p.Ts + t) * p.Nn + n) * G;
+      for (int u = gg; u < H; u += 8) {
+        const float ig = 1.f / (1.f + expf(-(zr[u] + mh[rr * G + u])));
+        const float fg = 1.f / (1.f + expf(-(zr[H + u] + mh[rr * G + H + u])));
+        const float cg = tanhf(zr[2 * H + u] + mh[rr * G + 2 * H + u]);
+        const float og = 1.f / (1.f + expf(-(zr[3 * H + u] + mh[rr * G + 3 * H + u])));
+        const float cn = fg * cs[rr * H + u] + ig * cg;
+        const float hn = og * tanhf(cn);
+        cs[rr * H + u] = cn; hs[rr * H + u] = hn;
+        const int td = t - (p.Ts - p.Td);
+        if (td >= 0) p.out[((b * p.Td + td) * p.Nn + n) * H + u] = hn;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K8 resnet: x = act(cumsum_t(x_out) + res) in place (emulator.py:315-320).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) cumsum_res_act_kernel(float* __restrict__ x, const float* __restrict__ res,
+                                                             long long Bc, int T, int Nn, int E, int act) {
+  const int e4 = E >> 2;
+  const long long total = Bc * Nn * e4;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total;
+       g += (long long)gridDim.x * blockDim.x) {
+    const int c4 = (int)(g % e4);
+    const long long bn = g / e4;
+    const int n = (int)(bn % Nn);
+    const long long b = bn / Nn;
+    const float4 r = *reinterpret_cast<const float4*>(res + bn * E + c4 * 4);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int t = 0; t < T; ++t) {
+      float* ptr = x + ((b * T + t) * Nn + n) * E + c4 * 4;
+      const float4 v = *reinterpret_cast<const float4*>(ptr);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      float4 o;
+      o.x = apply_act(acc.x + r.x, act); o.y = apply_act(acc.y + r.y, act);
+      o.z = apply_act(acc.z + r.z, act); o.w = apply_act(acc.w + r.w, act);
+      *reinterpret_cast<float4*>(ptr) = o;
+    }
+  }
+}
+
+// K8 narrow heads (n_out<=4 columns): one warp per row.
+struct HeadP {
+  const float* in; int ld; int K;
+  const float* W;       // (K, Nout)
+  const float* bias;
+  float* out; int ldo; int col0; int Nout; int act;
+  long long rows;
+};
+
+__global__ void __launch_bounds__(256) head_kernel(HeadP p) {
+  extern __shared__ float sm[];
+  float* Ws = sm;
+  for (int i = threadIdx.x; i < p.K * p.Nout; i += blockDim.x) Ws[i] = p.W[i];
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long r = w; r < p.rows; r += nw) {
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int k = lane; k < p.K; k += 32) {
+      const float v = p.in[r * p.ld + k];
+      for (int o = 0; o < p.Nout; ++o) acc[o] = fmaf(v, Ws[k * p.Nout + o], acc[o]);
+    }
+    for (int o = 0; o < p.Nout; ++o) {
+      const float s = warp_sum(acc[o]);
+      if (lane == 0) p.out[r * p.ldo + p.col0 + o] = apply_act(s + p.bias[o], p.act);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// P1..P4 fused epilogue: post_proc (emulator.py:643-678), de-normalisation + depth clip
+// (emulator.py:586-588) and constrain (emulator.py:727-748) for pump-free, offset-free
+// networks.  One CTA per (b,t) sample.
+// ---------------------------------------------------------------------------
+struct PostP {
+  const float* out_n;     // (S, N, ldn): [head cols..., flood prob] normalised
+  int ldn;
+  const float* out_e;     // (S, M, lde) tanh head
+  int lde;
+  const float* b_raw;     // (S, N, b_in) physical boundary
+  const float* a;         // (S, n_act) or null
+  int n_act;
+  const int* act_of_edge; const int* act_out_of_node; const int* act_in_of_node;
+  const int* inc_ptr; const int* inc_edge; const int* inc_sign;   // node -> incident edges
+  const float* ymax; const float* ymin; int cy;
+  const float* emax; const float* emin; int ce;
+  const float* bmax; const float* bmin; int cb;
+  const float* hmin; const float* hmax; const float* is_outfall; const float* ehmax;
+  float* y; float* ey;    // (S, N, ny), (S, M, e_out)
+  long long S;
+  int N, M, b_in, n_out, e_out, ny;
+  int if_flood, edge_fusion, act, tide, normalised;
+  float epsilon;
+};
+
+__global__ void __launch_bounds__(128) postproc_kernel(PostP p) {
+  extern __shared__ float efl[];     // M physical edge flows
+  for (long long s = blockIdx.x; s < p.S; s += gridDim.x) {
+    __syncthreads();
+    for (int m = threadIdx.x; m < p.M; m += blockDim.x) {
+      const float* src = p.out_e + (s * p.M + m) * p.lde;
+      float v[4];
+      for (int c = 0; c < p.e_out; ++c) v[c] = src[c];
+      if (p.act) {
+        const int k = p.act_of_edge[m];
+        const float ae = (k >= 0) ? p.a[s * p.n_act + k] : 1.f;
+        v[p.e_out - 1] *= ae;                                    // emulator.py:660
+      }
+      float phys[4];
+      for (int c = 0; c < p.e_out; ++c) {
+        const float mx = p.emax[m * p.ce + c], mn = p.emin[m * p.ce + c];
+        phys[c] = v[c] * (mx - mn) + mn;
+      }
+      efl[m] = phys[p.e_out - 1];
+      float* dst = p.ey + (s * p.M + m) * p.e_out;
+      if (p.normalised) {
+        for (int c = 0; c < p.e_out; ++c) dst[c] = v[c];
+      } else {
+        phys[0] = fminf(fmaxf(phys[0], 0.f), p.ehmax[m]);        // emulator.py:588
+        for (int c = 0; c < p.e_out; ++c) dst[c] = phys[c];
+      }
+    }
+    __syncthreads();
+    for (int n = threadIdx.x; n < p.N; n += blockDim.x) {
+      const float* src = p.out_n + (s * p.N + n) * p.ldn;
+      float yn[4];
+      float hN = src[0];
+      if (p.tide) {                                              // emulator.py:645-647
+        const float braw = p.b_raw[(s * p.N + n) * p.b_in + p.b_in - 1];
+        const float mx = p.bmax[n * p.cb + p.b_in - 1], mn = p.bmin[n * p.cb + p.b_in - 1];
+        hN = hN * (1.f - p.is_outfall[n]) + (braw - mn) / (mx - mn);
+      }
+      yn[0] = hN;
+      if (p.edge_fusion) {                                       // emulator.py:671-677
+        float op = 0.f, on = 0.f, ip = 0.f, in_ = 0.f;
+        for (int q = p.inc_ptr[n]; q < p.inc_ptr[n + 1]; ++q) {
+          const float f = efl[p.inc_edge[q]];
+          const float pos = fmaxf(f, 0.f), neg = fmaxf(-f, 0.f);
+          if (p.inc_sign[q] > 0) { op += pos; in_ += neg; } else { ip += pos; on += neg; }
+        }
+        const float m2 = p.ymax[n * p.cy + 2], m1 = p.ymax[n * p.cy + 1];
+        yn[2] = (op + on) * (m2 > 1e-3f ? 1.f / m2 : 0.f);
+        yn[1] = (ip + in_) * (m1 > 1e-3f ? 1.f / m1 : 0.f);
+      } else {
+        yn[1] = src[1]; yn[2] = src[2];
+        if (p.act) {                                             // emulator.py:661-670
+          const int ko = p.act_out_of_node[n], ki = p.act_in_of_node[n];
+          if (ko >= 0) yn[2] *= p.a[s * p.n_act + ko];
+          if (ki >= 0) yn[1] *= p.a[s * p.n_act + ki];
+        }
+      }
+      const float prob = p.if_flood ? src[p.n_out] : 0.f;
+      float* dst = p.y + (s * p.N + n) * p.ny;
+      if (p.normalised) {
+        dst[0] = yn[0]; dst[1] = yn[1]; dst[2] = yn[2];
+        if (p.if_flood) dst[3] = prob;
+        continue;
+      }
+      float yp[3];
+      for (int c = 0; c < 3; ++c) {
+        const float mx = p.ymax[n * p.cy + c], mn = p.ymin[n * p.cy + c];
+        yp[c] = yn[c] * (mx - mn) + mn;
+      }
+      float pr = prob;
+      if (p.if_flood) {
+        const float mx = p.ymax[n * p.cy + 3], mn = p.ymin[n * p.cy + 3];
+        pr = prob * (mx - mn) + mn;
+      }
+      // constrain (emulator.py:727-748)
+      float h = fminf(fmaxf(yp[0], p.hmin[n]), p.hmax[n]);
+      const float r = p.b_raw[(s * p.N + n) * p.b_in];
+      float qw = fmaxf(yp[1] + r - yp[2], 0.f) * (1.f - p.is_outfall[n]);
+      bool f = false;
+      if (p.if_flood) {
+        f = pr > 0.5f;
+        h = f ? p.hmax[n] : h;
+      }
+      if (p.epsilon > 0.f) qw *= ((p.hmax[n] - h) < p.epsilon) ? 1.f : 0.f;
+      else if (p.epsilon == 0.f) {}
+      else if (p.if_flood) qw *= f ? 1.f : 0.f;
+      dst[0] = h; dst[1] = yp[1]; dst[2] = yp[2];
+      if (p.if_flood) { dst[3] = pr; dst[4] = qw; } else dst[3] = qw;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Feedback between autoregressive chunks, on the device.
+//   MPC  (mpc.py:573-579):  x' = [h,q_us,q_ds,(q_w>0),r]      ex' = [ey, edge_action]
+//   MBRL (mbrl.py:338-343): x' = [h,q_us,q_ds,(prob>0.5),r]   ex' = [ey, edge_action]
+//   NORM (emulator.py:416-423): normalised y, flag = prob>0.5, b already normalised by the caller
+// ---------------------------------------------------------------------------
+struct FeedP {
+  const float* y; int ny;       // (S,N,ny)
+  const float* ey; int e_out;   // (S,M,e_out)
+  const float* b; int b_in;     // (S,N,b_in) raw boundary of the chunk just predicted
+  const float* a; int n_act; const int* act_of_edge;
+  float* x; int n_in;           // (S,N,n_in)
+  float* ex; int e_in;          // (S,M,e_in)
+  long long S; int N, M, if_flood, rule;
+};
+
+__global__ void __launch_bounds__(256) feedback_kernel(FeedP p) {
+  const long long tn = p.S * p.N, tm = p.S * p.M;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < tn + tm;
+       g += (long long)gridDim.x * blockDim.x) {
+    if (g < tn) {
+      const float* ys = p.y + g * p.ny;
+      float* xd = p.x + g * p.n_in;
+      xd[0] = ys[0]; xd[1] = ys[1]; xd[2] = ys[2];
+      int c = 3;
+      if (p.if_flood) {
+        float flag;
+        if (p.rule == 1) flag = ys[p.ny - 1] > 0.f ? 1.f : 0.f;      // q_w > 0
+        else flag = ys[3] > 0.5f ? 1.f : 0.f;                        // flood prob > 0.5
+        xd[c++] = flag;
+      }
+      for (int k = 0; k < p.b_in && c < p.n_in; ++k, ++c) xd[c] = p.b[g * p.b_in + k];
+    } else {
+      const long long ge = g - tn;
+      const int m = (int)(ge % p.M);
+      const long long s = ge / p.M;
+      const float* es = p.ey + ge * p.e_out;
+      float* ed = p.ex + ge * p.e_in;
+      for (int c = 0; c < p.e_out; ++c) ed[c] = es[c];
+      float ae = 1.f;
+      if (p.a) {
+        const int k = p.act_of_edge[m];
+        if (k >= 0) ae = p.a[s * p.n_act + k];
+      }
+      if (p.e_in > p.e_out) ed[p.e_out] = ae;
+    }
+  }
+}
+
+// gather/scatter of time slices: dst[b, t, :] = src[b, t0 + t, :] for row length L
+__global__ void __launch_bounds__(256) slice_time_kernel(const float* __restrict__ src, float* __restrict__ dst,
+                                                         long long B, int Tsrc, int t0, int Tdst, long long L,
+                                                         int scatter) {
+  const long long total = B * Tdst * L;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total;
+       g += (long long)gridDim.x * blockDim.x) {
+    const long long l = g % L;
+    const long long bt = g / L;
+    const int t = (int)(bt % Tdst);
+    const long long b = bt / Tdst;
+    const long long big = (b * Tsrc + t0 + t) * L + l;
+    if (scatter) dst[big] = src[g]; else dst[g] = src[big];
+  }
+}
+
+// R5 astlingen objective (envs/scenario/astlingen.py:75-99), one CTA per candidate.
+struct ObjP {
+  const float* y; int ny;     // (B,T,N,ny): q_w = last channel, q_in = channel 1
+  const float* q_in0;         // (B,N)
+  const float* flood_w; const float* wwtp_w; const float* rough_w; const float* gamma;
+  float* obj; long long B; int T, N;
+};
+
+__global__ void __launch_bounds__(128) objective_kernel(ObjP p) {
+  __shared__ float red[4];
+  for (long long b = blockIdx.x; b < p.B; b += gridDim.x) {
+    float acc = 0.f;
+    for (int g = threadIdx.x; g < p.T * p.N; g += blockDim.x) {
+      const int t = g / p.N, n = g % p.N;
+      const float* ys = p.y + ((b * p.T + t) * p.N + n) * p.ny;
+      const float gm = p.gamma ? p.gamma[t] : 1.f;
+      float v = ys[p.ny - 1] * p.flood_w[n] + ys[1] * p.wwtp_w[n];
+      if (p.rough_w) {
+        const float prev = (t == 0) ? p.q_in0[b * p.N + n] : (ys - (long long)p.N * p.ny)[1];
+        v += fabsf(ys[1] - prev) * p.rough_w[n];
+      }
+      acc += v * gm;
+    }
+    acc = warp_sum(acc);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) p.obj[b] = red[0] + red[1] + red[2] + red[3];
+  }
+}
+
+}  // namespace gu

@@ -1,0 +1,460 @@
+"""Drop-in ``Emulator`` for GNN-UDS running on hand-written sm_100a CUDA.
+
+Same construct / load / predict surface as the reference class
+``surrogate/emulator.py::Emulator`` (constructor emulator.py:48-127, ``load``
+833-852, ``set_norm``/``normalize`` 794-810, ``predict`` 566-602, ``predict_tf``
+604-641, ``simulate`` 521-564, ``get_edge_action`` 385-398), so that its callers
+(``main.py --test``, ``mpc.py`` population evaluation, ``mbrl.py`` rollouts) can
+switch by changing the import.  Forward only: ``fit_eval`` / ``fit_grad_norm`` /
+``optimizer`` / ``model`` raise ``NotImplementedError``.
+
+All arithmetic of the hot path runs in ``libgnnuds.so`` through ctypes
+(``include/gnnuds.h``); there is no CPU fallback - without the built extension
+or without a CUDA device construction fails.
+"""
+import ctypes as C
+import os
+from types import SimpleNamespace
+
+import numpy as np
+
+from . import _lib, graph as _graph, weights as _weights
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class _MSE:
+    """keras.losses.MeanSquaredError()(y_true, y_pred) (used at main.py:368-373)."""
+
+    def __call__(self, y_true, y_pred, sample_weight=None):
+        d = (np.asarray(y_pred, np.float64) - np.asarray(y_true, np.float64)) ** 2
+        d = d.mean(axis=-1)
+        if sample_weight is not None:
+            d = d * sample_weight
+        return np.float32(d.mean())
+
+
+class _BCE:
+    """keras.losses.BinaryCrossentropy() on probabilities (epsilon 1e-7 clip)."""
+
+    def __call__(self, y_true, y_pred, sample_weight=None):
+        p = np.clip(np.asarray(y_pred, np.float64), 1e-7, 1 - 1e-7)
+        t = np.asarray(y_true, np.float64)
+        d = -(t * np.log(p) + (1 - t) * np.log(1 - p)).mean(axis=-1)
+        if sample_weight is not None:
+            d = d * sample_weight
+        return np.float32(d.mean())
+
+
+class Emulator:
+    def __init__(self, conv=None, resnet=False, recurrent=None, args=None, device=0, precision="fp32",
+                 max_chunk=0, workspace_mb=0):
+        g = lambda k, d=None: getattr(args, k, d)
+        # ---- attribute parsing, emulator.py:49-127 ----
+        self.n_node, self.n_in = g("state_shape", (40, 4))
+        self.tide = bool(g("tide", False))
+        self.b_in = 2 if self.tide else 1
+        self.act = g("act", False)
+        self.act = self.act and self.act != "False"
+        self.n_out = self.n_in - 1
+        self.seq_in, self.seq_out = g("seq_in", 6), g("seq_out", 1)
+        self.embed_size, self.hidden_dim = g("embed_size", 64), g("hidden_dim", 64)
+        self.kernel_size = g("kernel_size", 3)
+        self.n_sp_layer, self.n_tp_layer = g("n_sp_layer", 3), g("n_tp_layer", 2)
+        self.dropout = g("dropout", 0.0)          # inactive at inference (emulator.py:542,582,621)
+        self.activation = g("activation", "relu")
+        self.balance = g("balance", False)
+        self.if_flood = int(g("if_flood", 0) or 0)
+        if self.if_flood:
+            self.n_in += 1
+        self.is_outfall = np.asarray(g("is_outfall", np.zeros(self.n_node)))
+        self.epsilon = float(g("epsilon", -1.0))
+        self.graph_base = int(g("graph_base", 0) or 0)
+        self.edge_fusion = bool(g("edge_fusion", False))
+        if not hasattr(args, "edges"):
+            raise AttributeError("args.edges is mandatory (emulator.py:76)")
+        self.edges = np.asarray(args.edges)
+        self.n_edge, self.e_in = g("edge_state_shape", (40, 4))
+        self.e_out = self.e_in - 1
+        self.ehmax = np.asarray(g("ehmax", np.full(self.n_edge, 0.5)), dtype=np.float64)
+        self.pump = np.asarray(g("pump", np.zeros(self.n_edge)), dtype=np.float64)
+        self.ewei = np.asarray(g("ewei", np.ones(self.n_edge)))
+        if g("node_edge") is None and self.graph_base == 0 and not hasattr(args, "edges"):
+            raise AttributeError("args.node_edge is mandatory (emulator.py:83)")
+        self.node_edge = g("node_edge")
+        if self.edge_fusion:
+            self.n_out -= 2
+        if self.act:
+            self.act_edges = np.asarray(args.act_edges)
+            self.use_adj = bool(g("use_adj", False))
+            if self.use_adj:
+                raise NotImplementedError("use_adj (dynamic adjacency, emulator.py:343-362) is not on the CUDA path")
+        self.area = np.asarray(g("area", np.zeros(self.n_node)), dtype=np.float64)
+        self.pump_in = np.asarray(g("pump_in", np.zeros(self.n_node)), dtype=np.float64)
+        self.pump_out = np.asarray(g("pump_out", np.zeros(self.n_node)), dtype=np.float64)
+        self.offset = np.asarray(g("offset", np.zeros(self.n_edge)), dtype=np.float64)
+        self.hmax = np.asarray(g("hmax", np.full(self.n_node, 1.5)), dtype=np.float64)
+        self.hmin = np.asarray(g("hmin", np.zeros(self.n_node)), dtype=np.float64)
+        self.nwei = np.asarray(g("nwei", np.ones(self.n_node)))
+        if float(self.pump.sum() + self.pump_in.sum() + self.pump_out.sum()) > 0:
+            raise NotImplementedError("pumped networks (emulator.py:590-598,656-667) are a 'next' row; not on the CUDA path yet")
+        if float(np.max(self.offset)) > 0:
+            raise NotImplementedError("inlet offsets (emulator.py:649-653) are a 'next' row; not on the CUDA path yet")
+        self.conv = False if conv in ["None", "False", "NoneType", None, False] else conv
+        if not self.conv:
+            raise NotImplementedError("NN-cat (conv=False, emulator.py:231-233) is a 'next' row; not on the CUDA path yet")
+        if "GCN" in self.conv:
+            self.conv_kind = "gcn"
+        elif "GAT" in self.conv:
+            self.conv_kind = "gat"
+        else:
+            raise AssertionError("Unknown Convolution layer %s" % str(conv))   # emulator.py:151
+        self.resnet = bool(resnet)
+        self.recurrent = recurrent
+        if recurrent not in ("Conv1D", "GRU", "LSTM"):
+            raise NotImplementedError("recurrent=%r is not on the CUDA path" % (recurrent,))
+        if self.activation not in _lib.ACT:
+            raise NotImplementedError("activation %r" % (self.activation,))
+        self.roll = int(g("roll", 0) or 0)
+        self.model_dir = g("model_dir")
+        self.mse = _MSE()
+        if self.if_flood:
+            self.bce = _BCE()
+        self.n_act = int(len(self.act_edges)) if self.act else 0
+        self.precision = precision
+        self.device = int(device)
+
+        # ---- filters: Emulator.get_conv (emulator.py:129-152) on CSR ----
+        adj_csr = g("adj_csr")
+        if adj_csr is None:
+            adj_csr = self._csr_from_dense(np.asarray(g("adj", np.eye(self.n_node))))
+        eadj_csr = g("edge_adj_csr")
+        if eadj_csr is None and not self.graph_base:
+            eadj_csr = self._csr_from_dense(np.asarray(g("edge_adj", np.eye(self.n_edge))))
+        self.adj_csr, self.edge_adj_csr = adj_csr, eadj_csr
+        if self.conv_kind == "gcn":
+            self.filter_csr = _graph.gcn_normalise(adj_csr)
+            self.edge_filter_csr = _graph.gcn_normalise(eadj_csr) if eadj_csr is not None else None
+        else:
+            self.filter_csr = _graph.gat_pattern(adj_csr)
+            self.edge_filter_csr = _graph.gat_pattern(eadj_csr) if eadj_csr is not None else None
+
+        # ---- native handle ----
+        self._lib = _lib.load()
+        cfg = _lib.Config()
+        cfg.abi_version = _lib.ABI_VERSION
+        cfg.n_node, cfg.n_edge = self.n_node, self.n_edge
+        cfg.n_in, cfg.b_in, cfg.e_in, cfg.n_out, cfg.e_out = self.n_in, self.b_in, self.e_in, self.n_out, self.e_out
+        cfg.seq_in, cfg.seq_out = self.seq_in, self.seq_out
+        cfg.embed, cfg.hidden, cfg.kernel_size = self.embed_size, self.hidden_dim, self.kernel_size
+        cfg.n_sp_layer, cfg.n_tp_layer = self.n_sp_layer, self.n_tp_layer
+        cfg.conv = _lib.CONV_GCN if self.conv_kind == "gcn" else _lib.CONV_GAT
+        cfg.recurrent = {"Conv1D": _lib.REC_CONV1D, "GRU": _lib.REC_GRU, "LSTM": _lib.REC_LSTM}[recurrent]
+        cfg.activation = _lib.ACT[self.activation]
+        cfg.resnet, cfg.if_flood, cfg.edge_fusion = int(self.resnet), self.if_flood, int(self.edge_fusion)
+        cfg.act, cfg.graph_base, cfg.tide, cfg.n_act = int(bool(self.act)), self.graph_base, int(self.tide), self.n_act
+        cfg.epsilon = self.epsilon
+        cfg.precision = {"fp32": _lib.PREC_FP32, "bf16": _lib.PREC_BF16_TC}[precision]
+        cfg.device, cfg.max_chunk, cfg.workspace_mb = self.device, int(max_chunk), int(workspace_mb)
+        self._cfg = cfg
+        self._h = C.c_void_p()
+        rc = self._lib.gnnuds_create(C.byref(cfg), C.byref(self._h))
+        if rc != 0:
+            raise _lib.GnnUdsError("gnnuds_create failed (%d): %s" % (rc, self._lib.gnnuds_last_error(None).decode()))
+        self._set_graph()
+        self.specs = _weights.layer_specs(self)
+        nt = C.c_int32()
+        _lib.check(self._h, self._lib.gnnuds_weight_layout(self._h, C.byref(nt), None))
+        sizes = (C.c_int64 * nt.value)()
+        _lib.check(self._h, self._lib.gnnuds_weight_layout(self._h, C.byref(nt), sizes))
+        mine = [int(np.prod(shp)) for s in self.specs for shp in s.shapes]
+        if mine != list(sizes):
+            raise _lib.GnnUdsError("host/device weight layouts disagree")
+        yc, ec = C.c_int32(), C.c_int32()
+        self._lib.gnnuds_output_dims(self._h, C.byref(yc), C.byref(ec))
+        self.y_channels, self.ey_channels = yc.value, ec.value
+        self.weights = None
+
+    # ------------------------------------------------------------------ plumbing
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            try:
+                self._lib.gnnuds_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+    @staticmethod
+    def _csr_from_dense(a):
+        rows = [{int(j): float(a[i, j]) for j in np.nonzero(a[i])[0]} for i in range(a.shape[0])]
+        return _graph.CSR(a.shape[0], rows)
+
+    # dense views that callers of the reference read off the object
+    @property
+    def filter(self):
+        d = self.filter_csr.to_dense()
+        return d if self.conv_kind == "gcn" else d.astype(int)
+
+    @property
+    def edge_filter(self):
+        d = self.edge_filter_csr.to_dense()
+        return d if self.conv_kind == "gcn" else d.astype(int)
+
+    def act_edge_index(self):
+        """emulator.py:386-388: edge indices driven by each setting column (dedup, order kept)."""
+        idx = [np.where((self.edges == e).all(1))[0] for e in self.act_edges]
+        idx = [i for e in idx for i in e]
+        return sorted(list(set(idx)), key=idx.index)
+
+    def _set_graph(self):
+        f, ef = self.filter_csr, self.edge_filter_csr
+        gcn = self.conv_kind == "gcn"
+        keep = dict(rp=_i32(f.row_ptr), ci=_i32(f.col_idx), val=_f32(f.val) if gcn else None,
+                    edges=_i32(self.edges), hmin=_f32(self.hmin), hmax=_f32(self.hmax),
+                    outf=_f32(self.is_outfall), ehmax=_f32(self.ehmax))
+        if ef is not None:
+            keep.update(erp=_i32(ef.row_ptr), eci=_i32(ef.col_idx), evl=_f32(ef.val) if gcn else None)
+        g = _lib.Graph()
+        pi, pf = C.POINTER(C.c_int32), C.POINTER(C.c_float)
+        cast_i = lambda a: None if a is None else a.ctypes.data_as(pi)
+        cast_f = lambda a: None if a is None else a.ctypes.data_as(pf)
+        g.row_ptr, g.col_idx, g.val, g.n, g.nnz = cast_i(keep["rp"]), cast_i(keep["ci"]), cast_f(keep["val"]), f.n, f.nnz
+        if ef is not None:
+            g.e_row_ptr, g.e_col_idx, g.e_val, g.m, g.e_nnz = cast_i(keep["erp"]), cast_i(keep["eci"]), cast_f(keep["evl"]), ef.n, ef.nnz
+        g.edges = cast_i(keep["edges"])
+        if self.act:
+            aoe = np.full(self.n_edge, -1, np.int32)
+            for k, m in enumerate(self.act_edge_index()):
+                aoe[m] = k
+            aout, ain = np.full(self.n_node, -1, np.int32), np.full(self.n_node, -1, np.int32)
+            for k, (u, v) in enumerate(self.act_edges):        # emulator.py:374-380 (last writer wins)
+                aout[u] = k
+                ain[v] = k
+            keep.update(aoe=aoe, aout=aout, ain=ain)
+            g.act_of_edge, g.act_out_of_node, g.act_in_of_node = cast_i(aoe), cast_i(aout), cast_i(ain)
+        g.hmin, g.hmax, g.is_outfall, g.ehmax = cast_f(keep["hmin"]), cast_f(keep["hmax"]), cast_f(keep["outf"]), cast_f(keep["ehmax"])
+        _lib.check(self._h, self._lib.gnnuds_set_graph(self._h, C.byref(g)))
+
+    # ------------------------------------------------------------------ weights / norms
+    def set_weights(self, weights):
+        """weights: list (creation order) of lists of arrays in Keras layout."""
+        _weights.check_shapes(self.specs, weights)
+        blob, offs, sizes = _weights.pack(weights)
+        _lib.check(self._h, self._lib.gnnuds_set_weights(
+            self._h, _ptr(blob), blob.size, offs.ctypes.data_as(C.POINTER(C.c_int64)),
+            sizes.ctypes.data_as(C.POINTER(C.c_int64)), len(offs)))
+        self.weights = [[np.array(w, dtype=np.float32) for w in l] for l in weights]
+
+    def init_weights(self, seed=0, **kw):
+        """Random-init weights with Keras' default initialisers (no trained weights ship)."""
+        self.set_weights(_weights.init_weights(self.specs, seed, **kw))
+
+    def set_norm(self, norm_x, norm_b, norm_y, norm_r, norm_e):        # emulator.py:794-800
+        self.norm_x, self.norm_b, self.norm_y, self.norm_r = norm_x, norm_b, norm_y, norm_r
+        if norm_e is not None:
+            self.norm_e = norm_e
+        self._push_norm()
+
+    def _push_norm(self):
+        if not all(hasattr(self, "norm_%s" % k) for k in "xbye"):
+            return
+        arrs = [_f32(getattr(self, "norm_%s" % k)) for k in "xbye"]
+        for a, n, nm in zip(arrs, (self.n_node, self.n_node, self.n_node, self.n_edge), "xbye"):
+            if a.ndim != 3 or a.shape[0] != 2 or a.shape[1] != n:
+                raise ValueError("norm_%s must have shape (2,%d,c), got %s" % (nm, n, a.shape))
+        _lib.check(self._h, self._lib.gnnuds_set_norm(
+            self._h, _ptr(arrs[0]), arrs[0].shape[2], _ptr(arrs[1]), arrs[1].shape[2],
+            _ptr(arrs[2]), arrs[2].shape[2], _ptr(arrs[3]), arrs[3].shape[2]))
+
+    def normalize(self, dat, item, inverse=False):                      # emulator.py:803-810
+        dim = dat.shape[-1]
+        normal = getattr(self, "norm_%s" % item)
+        maxi, mini = normal[0, ..., :dim], normal[1, ..., :dim]
+        return dat * (maxi - mini) + mini if inverse else (dat - mini) / (maxi - mini)
+
+    def load(self, model_dir=None, retrain=False):                      # emulator.py:833-852
+        from . import h5lite
+        model_dir = model_dir if model_dir is not None else self.model_dir
+        if model_dir.endswith(".h5") or model_dir.endswith(".npz"):
+            path, model_dir = model_dir, os.path.dirname(model_dir)
+        else:
+            path = os.path.join(model_dir, "model.h5")
+            if not os.path.exists(path) and os.path.exists(os.path.join(model_dir, "model.npz")):
+                path = os.path.join(model_dir, "model.npz")
+        if path.endswith(".npz"):
+            z = np.load(path)
+            weights, i = [], 0
+            for s in self.specs:
+                weights.append([z["w%d" % (i + j)] for j in range(len(s.shapes))])
+                i += len(s.shapes)
+        else:
+            weights = h5lite.load_keras_weights(path, self.specs)
+        self.set_weights(weights)
+        for item in "xbyre":
+            p = os.path.join(model_dir, "norm_%s.npy" % item)
+            if os.path.exists(p):
+                setattr(self, "norm_%s" % item, np.load(p))
+        self._push_norm()
+
+    def save(self, model_dir=None):                                     # emulator.py:814-826
+        from . import h5lite
+        model_dir = model_dir if model_dir is not None else self.model_dir
+        if model_dir.endswith(".h5"):
+            path, model_dir = model_dir, os.path.dirname(model_dir)
+        else:
+            path = os.path.join(model_dir, "model.h5")
+        os.makedirs(model_dir or ".", exist_ok=True)
+        h5lite.save_keras_weights(path, self.specs, self.weights)
+        for item in "xbyre":
+            if hasattr(self, "norm_%s" % item):
+                np.save(os.path.join(model_dir, "norm_%s.npy" % item), getattr(self, "norm_%s" % item))
+
+    # ------------------------------------------------------------------ inference surface
+    def get_edge_action(self, a, g=False):                              # emulator.py:385-398
+        a = np.asarray(a)
+        out = np.ones(a.shape[:-1] + (self.n_edge,), dtype=a.dtype)
+        out[..., self.act_edge_index()] = a
+        return out[..., None]
+
+    def _run_predict(self, x, b, a, ex):
+        B = x.shape[0]
+        y = np.empty((B, self.seq_out, self.n_node, self.y_channels), np.float32)
+        ey = np.empty((B, self.seq_out, self.n_edge, self.ey_channels), np.float32)
+        _lib.check(self._h, self._lib.gnnuds_predict(self._h, _ptr(x), _ptr(b), _ptr(a), _ptr(ex), B,
+                                                     _ptr(y), _ptr(ey), _lib.MEM_HOST))
+        return y, ey
+
+    def predict_ptrs(self, x, b, a, ex, B, y, ey, device=True):
+        """Raw-pointer entry (ints): buffers already laid out as gnnuds_predict documents, on the
+        handle's device (``device=True``, e.g. torch tensors' data_ptr()) or on the host."""
+        _lib.check(self._h, self._lib.gnnuds_predict(self._h, x, b, a, ex, int(B), y, ey,
+                                                     _lib.MEM_DEVICE if device else _lib.MEM_HOST))
+
+    def _prep(self, states, b, a, edge_state):
+        if edge_state is None:
+            raise ValueError("edge_state is required (emulator.py:579 reads it unconditionally)")
+        x = _f32(np.asarray(states)[:, -self.seq_in:, ...])
+        ex = _f32(np.asarray(edge_state)[:, -self.seq_in:, ...])
+        b = _f32(b)
+        if x.shape[1:] != (self.seq_in, self.n_node, self.n_in):
+            raise ValueError("states shape %s, expected (B,%d,%d,%d)" % (x.shape, self.seq_in, self.n_node, self.n_in))
+        if ex.shape[1:] != (self.seq_in, self.n_edge, self.e_in) or ex.shape[0] != x.shape[0]:
+            raise ValueError("edge_state shape %s" % (ex.shape,))
+        if b.shape[0] != x.shape[0] or b.shape[2:] != (self.n_node, self.b_in):
+            raise ValueError("b shape %s" % (b.shape,))
+        if self.act:
+            if a is None:
+                raise ValueError("settings `a` required for an act model")
+            a = _f32(a)
+            if a.shape[0] != x.shape[0] or a.shape[2] != self.n_act:
+                raise ValueError("a shape %s" % (a.shape,))
+        else:
+            a = None
+        return x, b, a, ex
+
+    def predict(self, states, b, a=None, edge_state=None):              # emulator.py:566-602
+        x, b, a, ex = self._prep(states, b, a, edge_state)
+        assert b.shape[1] == self.seq_out                               # emulator.py:570
+        if a is not None:
+            a = _f32(a[:, :self.seq_out])
+        return self._run_predict(x, b, a, ex)
+
+    def predict_tf(self, states, b, a=None, edge_state=None):           # emulator.py:604-641 (forward only)
+        return self.predict(states, b, a, edge_state)
+
+    def simulate(self, states, runoff, a=None, edge_states=None):       # emulator.py:521-564
+        """All T' teacher-forced windows as one batch (the reference loops batch-1 per index).
+        ``a=None`` is passed through when act is off (reference defect F9, emulator.py:545)."""
+        runoff = np.asarray(runoff)[:, :self.seq_out]
+        return self.predict(states, runoff, a, edge_states)
+
+    # ------------------------------------------------------------------ autoregressive loops
+    def rollout(self, states, b, a=None, edge_state=None, rule="mpc"):
+        """Chunked autoregressive rollout on the device.  rule: 'mpc' (mpc.py:565-582),
+        'mbrl' (mbrl.py:337-346) or 'norm' (emulator.py:400-438, normalised inputs/outputs)."""
+        code = {"mpc": _lib.ROLL_MPC, "mbrl": _lib.ROLL_MBRL, "norm": _lib.ROLL_NORM}[rule]
+        x, b, a, ex = self._prep(states, b, a, edge_state)
+        if b.shape[1] % self.seq_out:
+            raise ValueError("horizon %d is not a multiple of seq_out" % b.shape[1])
+        n_chunks = b.shape[1] // self.seq_out
+        B = x.shape[0]
+        nyc = self.y_channels if rule != "norm" else 3 + (1 if self.if_flood else 0)
+        y = np.empty((B, b.shape[1], self.n_node, nyc), np.float32)
+        ey = np.empty((B, b.shape[1], self.n_edge, self.ey_channels), np.float32)
+        _lib.check(self._h, self._lib.gnnuds_rollout(self._h, code, _ptr(x), _ptr(b), _ptr(a), _ptr(ex), B, n_chunks,
+                                                     _ptr(y), _ptr(ey), _lib.MEM_HOST))
+        if rule == "norm":
+            y = np.clip(y, 0, 1)                                        # emulator.py:437
+        return y, ey
+
+    def objective(self, preds, state, flood_w, wwtp_w, rough_w=None, gamma=None):
+        """astlingen.objective_pred_tf (envs/scenario/astlingen.py:75-99) on the device."""
+        y = _f32(preds)
+        B, T = y.shape[0], y.shape[1]
+        q0 = _f32(np.asarray(state)[:, -1, :, 1])
+        obj = np.empty(B, np.float32)
+        fw, ww = _f32(flood_w), _f32(wwtp_w)
+        rw = None if rough_w is None else _f32(rough_w)
+        gm = None if gamma is None else _f32(gamma)
+        _lib.check(self._h, self._lib.gnnuds_objective(self._h, _ptr(y), _ptr(q0), B, T, _ptr(fw), _ptr(ww), _ptr(rw),
+                                                       _ptr(gm), _ptr(obj), _lib.MEM_HOST))
+        return obj
+
+    # ------------------------------------------------------------------ instrumentation
+    def launch_count(self):
+        return int(self._lib.gnnuds_launch_count(self._h))
+
+    def set_profiling(self, level=1):
+        """0 off, 1 time whole calls, 2 also time every rows-GEMM launch (CUDA events on the library stream)."""
+        self._lib.gnnuds_set_profiling(self._h, int(level))
+
+    def last_timing(self):
+        t, g = C.c_float(), C.c_float()
+        self._lib.gnnuds_last_timing(self._h, C.byref(t), C.byref(g))
+        return t.value, g.value
+
+    def debug_stage(self, stage, states, b, a=None, edge_state=None):
+        """Test hook: run the forward up to `stage` and return the live (node, edge) streams."""
+        x, b, a, ex = self._prep(states, b, a, edge_state)
+        self._lib.gnnuds_debug_stop_after(self._h, int(stage))
+        try:
+            self._run_predict(x, b, a, ex)
+            outs = []
+            for which in (0, 1):
+                rows, width = C.c_int64(), C.c_int32()
+                _lib.check(self._h, self._lib.gnnuds_debug_fetch(self._h, which, None, 0, C.byref(rows), C.byref(width)))
+                buf = np.empty((rows.value, width.value), np.float32)
+                _lib.check(self._h, self._lib.gnnuds_debug_fetch(self._h, which, _ptr(buf), buf.size, C.byref(rows), C.byref(width)))
+                outs.append(buf)
+        finally:
+            self._lib.gnnuds_debug_stop_after(self._h, 0)
+        return outs
+
+    # ------------------------------------------------------------------ not on this path
+    def fit_eval(self, *a, **k):
+        raise NotImplementedError("training (emulator.py:457-484) is out of scope of the forward rollout path")
+
+    fit_grad_norm = fit_eval
+
+    @property
+    def model(self):
+        raise NotImplementedError("there is no Keras model object behind this Emulator")
+
+    @property
+    def optimizer(self):
+        raise NotImplementedError("there is no optimizer behind this Emulator")
+
+
+def make_args(**kw):
+    return SimpleNamespace(**kw)

@@ -1,0 +1,169 @@
+/*
+ * gnnuds.h - C ABI of the B200-native GNN-UDS Emulator rollout (libgnnuds.so).
+ *
+ * The reference (Zhiyu014/GNN-UDS) has no FFI; its boundary for this path is the
+ * Python class surrogate/emulator.py::Emulator.  Each entry point below names the
+ * reference interface it replaces (file:line under /root/reference/surrogate).
+ * The Python shim gnn_uds_b200/emulator.py binds these through ctypes
+ * (see INTEGRATION.md).
+ *
+ * Conventions: every call returns 0 on success, a negative GNNUDS_E_* code
+ * otherwise; nothing throws across the boundary; the library never takes
+ * ownership of caller memory; one handle = one CUDA device + one stream, not
+ * thread-safe; handles must not cross processes.  All arrays are C-contiguous,
+ * little-endian float32 / int32 unless stated.
+ */
+#ifndef GNNUDS_H
+#define GNNUDS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GNNUDS_ABI_VERSION 1
+
+enum {
+  GNNUDS_OK = 0,
+  GNNUDS_E_INVALID = -1,   /* bad argument / unsupported variant */
+  GNNUDS_E_STATE = -2,     /* call order (graph/weights/norm not set) */
+  GNNUDS_E_CUDA = -3,      /* CUDA runtime error, see gnnuds_last_error */
+  GNNUDS_E_NOMEM = -4
+};
+
+enum { GNNUDS_CONV_GCN = 1, GNNUDS_CONV_GAT = 2 };                 /* emulator.py:129-152 */
+enum { GNNUDS_REC_CONV1D = 1, GNNUDS_REC_GRU = 2, GNNUDS_REC_LSTM = 3 }; /* emulator.py:154-163 */
+enum { GNNUDS_ACT_LINEAR = 0, GNNUDS_ACT_RELU = 1, GNNUDS_ACT_TANH = 2, GNNUDS_ACT_SIGMOID = 3 };
+enum { GNNUDS_PREC_FP32 = 0,    /* fp32 SIMT, parity mode (<=1e-5 rel per step) */
+       GNNUDS_PREC_BF16_TC = 1  /* bf16 operands on tcgen05, fp32 accumulate */ };
+enum { GNNUDS_MEM_HOST = 0, GNNUDS_MEM_DEVICE = 1 };
+/* feedback rule of the autoregressive chunk loop */
+enum { GNNUDS_ROLL_MPC = 1,     /* mpc.py:565-582 */
+       GNNUDS_ROLL_MBRL = 2,    /* mbrl.py:337-346 */
+       GNNUDS_ROLL_NORM = 3     /* emulator.py:400-438 (normalised space) */ };
+
+/* POD mirror of the attributes Emulator.__init__ reads off `args` (emulator.py:48-127). */
+typedef struct gnnuds_config {
+  int32_t abi_version;     /* GNNUDS_ABI_VERSION */
+  int32_t n_node, n_edge;  /* state_shape[0], edge_state_shape[0] */
+  int32_t n_in;            /* node input channels incl. flood flag (emulator.py:49,69-70) */
+  int32_t b_in;            /* 1, or 2 with tide (emulator.py:52) */
+  int32_t e_in;            /* edge input channels (4) */
+  int32_t n_out;           /* node head width after the edge_fusion cut (emulator.py:56,85) */
+  int32_t e_out;           /* e_in - 1 */
+  int32_t seq_in, seq_out;
+  int32_t embed, hidden, kernel_size, n_sp_layer, n_tp_layer;
+  int32_t conv, recurrent, activation;
+  int32_t resnet, if_flood, edge_fusion, act, graph_base, tide;
+  int32_t n_act;           /* columns of the settings tensor `a` */
+  float   epsilon;         /* emulator.py:72, flood gating rule in constrain */
+  int32_t precision;       /* GNNUDS_PREC_* */
+  int32_t device;          /* CUDA ordinal */
+  int32_t max_chunk;       /* scenarios per internal pass; 0 = auto from workspace_mb */
+  int32_t workspace_mb;    /* activation workspace budget; 0 = 4096 */
+} gnnuds_config;
+
+/* per-network vectors, get_args (envs/scenario/base.py:277-332) + emulator.py:71-98 */
+typedef struct gnnuds_graph {
+  /* node adjacency filter in CSR (joint node+edge graph when graph_base != 0).
+     GAT: pattern of (adj>0) with forced diagonal, val = NULL.
+     GCN: val = gcn_filter(adj) (emulator.py:133, spektral.utils.gcn_filter). */
+  const int32_t* row_ptr; const int32_t* col_idx; const float* val; int32_t n; int32_t nnz;
+  /* edge (line-graph) adjacency filter, unused when graph_base != 0 */
+  const int32_t* e_row_ptr; const int32_t* e_col_idx; const float* e_val; int32_t m; int32_t e_nnz;
+  const int32_t* edges;        /* (n_edge,2) from,to  - base.py:349-365 */
+  const int32_t* act_of_edge;  /* (n_edge) column of `a` driving this edge or -1 - emulator.py:385-398 */
+  const int32_t* act_out_of_node; /* (n_node) column of `a` or -1 - emulator.py:364-383 (a_out) */
+  const int32_t* act_in_of_node;  /* (n_node) column of `a` or -1 (a_in) */
+  const float* hmin; const float* hmax; const float* is_outfall;   /* (n_node) */
+  const float* ehmax;                                               /* (n_edge) */
+} gnnuds_graph;
+
+typedef struct gnnuds_handle gnnuds_handle;
+
+/* Emulator.__init__ + build_network (emulator.py:48-127,166-341). */
+int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out);
+int gnnuds_destroy(gnnuds_handle* h);
+const char* gnnuds_last_error(const gnnuds_handle* h);   /* h may be NULL: create() errors */
+
+/* Graph tensors: Emulator.get_conv filters + vectors read in __init__. */
+int gnnuds_set_graph(gnnuds_handle* h, const gnnuds_graph* g);
+
+/* Number of weight tensors build_network creates, in creation order, and their sizes.
+   sizes may be NULL to query the count. */
+int gnnuds_weight_layout(gnnuds_handle* h, int32_t* n_tensors, int64_t* sizes);
+
+/* Emulator.load -> model.load_weights (emulator.py:833-839): all tensors in Keras
+   creation order and Keras layout, concatenated into one blob. offsets[i] is the
+   float offset of tensor i, sizes[i] its element count (checked). */
+int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats,
+                       const int64_t* offsets, const int64_t* sizes, int32_t n_tensors);
+
+/* Emulator.set_norm (emulator.py:794-800). norm_* are (2, n, c): [0]=max, [1]=min.
+   c_y is the channel count of norm_y (>= channels denormalised). norm_b/norm_e as given. */
+int gnnuds_set_norm(gnnuds_handle* h, const float* norm_x, int32_t c_x,
+                    const float* norm_b, int32_t c_b,
+                    const float* norm_y, int32_t c_y,
+                    const float* norm_e, int32_t c_e);
+
+/* Channels of the node output y ([h,q_us,q_ds,(flood_prob),q_w]) and edge output. */
+int gnnuds_output_dims(const gnnuds_handle* h, int32_t* y_channels, int32_t* ey_channels);
+
+/* Emulator.predict / predict_tf (emulator.py:566-641): physical units in, physical out.
+   x  (B, seq_in, n_node, n_in)   b (B, seq_out, n_node, b_in)
+   a  (B, seq_out, n_act) or NULL ex (B, seq_in, n_edge, e_in)
+   y  (B, seq_out, n_node, y_channels)   ey (B, seq_out, n_edge, e_out)
+   where = GNNUDS_MEM_HOST (copies inside) or GNNUDS_MEM_DEVICE (pointers on cfg.device). */
+int gnnuds_predict(gnnuds_handle* h, const float* x, const float* b, const float* a,
+                   const float* ex, int64_t B, float* y, float* ey, int32_t where);
+
+/* Emulator.simulate (emulator.py:521-564): T' teacher-forced windows evaluated as one batch.
+   runoff (T', seq_r, n_node, b_in) with seq_r >= seq_out (first seq_out steps used). */
+int gnnuds_simulate(gnnuds_handle* h, const float* states, const float* runoff, int32_t seq_r,
+                    const float* a, const float* edge_states, int64_t n_windows,
+                    float* y, float* ey, int32_t where);
+
+/* Autoregressive chunk loop, n_chunks forwards of seq_out steps with the feedback rule
+   `rule` applied on the device between chunks (mpc.py:565-582, mbrl.py:337-346,
+   emulator.py:400-438). Requires seq_in == seq_out for MPC/MBRL as in the reference.
+   x0 (B,seq_in,n_node,n_in)  b (B,n_chunks*seq_out,n_node,b_in)  a (B,n_chunks*seq_out,n_act)|NULL
+   ex0 (B,seq_in,n_edge,e_in)  y (B,n_chunks*seq_out,n_node,y_ch)  ey (B,n_chunks*seq_out,n_edge,e_out) */
+int gnnuds_rollout(gnnuds_handle* h, int32_t rule, const float* x0, const float* b, const float* a,
+                   const float* ex0, int64_t B, int32_t n_chunks, float* y, float* ey, int32_t where);
+
+/* astlingen.objective_pred_tf (envs/scenario/astlingen.py:75-99): per-candidate scalar.
+   y (B,T,n_node,y_ch) as returned by predict/rollout; q_in0 (B,n_node) = state[:,-1,:,1].
+   flood_w (n_node) weight of q_w per node (0 = not a target); wwtp_w (n_node) weight of
+   q_in[1:]; rough_w (n_node) weight of |diff_t q_in| (pass NULL for rough=False);
+   gamma (T) or NULL. obj (B). */
+int gnnuds_objective(gnnuds_handle* h, const float* y, const float* q_in0, int64_t B, int32_t T,
+                     const float* flood_w, const float* wwtp_w, const float* rough_w,
+                     const float* gamma, float* obj, int32_t where);
+
+/* Pinned host buffers for callers that want truly asynchronous copies. */
+int gnnuds_alloc_pinned(void** p, int64_t bytes);
+int gnnuds_free_pinned(void* p);
+/* Device buffers on the handle's device (for where = GNNUDS_MEM_DEVICE callers without torch). */
+int gnnuds_alloc_device(gnnuds_handle* h, void** p, int64_t bytes);
+int gnnuds_free_device(gnnuds_handle* h, void* p);
+int gnnuds_memcpy(gnnuds_handle* h, void* dst, const void* src, int64_t bytes, int32_t kind /*1 H2D,2 D2H*/);
+int gnnuds_synchronize(gnnuds_handle* h);
+
+/* Kernel launches issued by this handle since creation (bench.py "gpu_launches"). */
+int64_t gnnuds_launch_count(const gnnuds_handle* h);
+/* Device time (ms, CUDA events on the handle's stream) of the last predict/rollout call's
+   compute (copies excluded) and of its dominant GEMM kernels. */
+int gnnuds_last_timing(const gnnuds_handle* h, float* total_ms, float* gemm_ms);
+int gnnuds_set_profiling(gnnuds_handle* h, int32_t on);
+
+/* Test hook: stop the forward after `stage` (0 = off) and fetch the live node/edge
+   streams of the first chunk.  which: 0 node stream, 1 edge stream. */
+int gnnuds_debug_stop_after(gnnuds_handle* h, int32_t stage);
+int gnnuds_debug_fetch(gnnuds_handle* h, int32_t which, float* out, int64_t max_floats,
+                       int64_t* rows, int32_t* width);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GNNUDS_H */
