@@ -257,8 +257,12 @@ int launch_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, const float* Wp
     rows_gemm_f32<128><<<dim3(gx, Nout / 128), 256, 0, h->stream>>>(p);
   } else if (Nout % 64 == 0) {
     rows_gemm_f32<64><<<dim3(gx, Nout / 64), 256, 0, h->stream>>>(p);
+  } else if (Nout % 32 == 0) {
+    rows_gemm_f32_narrow<32><<<dim3(gx, Nout / 32), 256, 0, h->stream>>>(p);
+  } else if (Nout % 16 == 0) {
+    rows_gemm_f32_narrow<16><<<dim3(gx, Nout / 16), 256, 0, h->stream>>>(p);
   } else {
-    return fail(h, GNNUDS_E_INVALID, "rows_gemm: Nout %d not a multiple of 64", Nout);
+    return fail(h, GNNUDS_E_INVALID, "rows_gemm: Nout %d not a multiple of 16", Nout);
   }
   ++h->launches;
   if (h->profiling >= 2) CU(cudaEventRecord(e1, h->stream));

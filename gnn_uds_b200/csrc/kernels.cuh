@@ -249,6 +249,89 @@ __global__ void __launch_bounds__(256) rows_gemm_f32(GemmP p) {
   }
 }
 
+// Narrow-output variant (Nout a multiple of 16 or 32 but not 64: E/2 or H of small models).
+// Same row addressing as rows_gemm_f32; 128 rows x BN columns per CTA, BN/8 rows x 4 columns
+// per thread.
+template <int BN>
+__global__ void __launch_bounds__(256) rows_gemm_f32_narrow(GemmP p) {
+  constexpr int BM = 128, BK = 16, TX = BN / 4, TY = 256 / TX, RM = BM / TY;
+  __shared__ __align__(16) float As[BK][BM + 4];
+  __shared__ __align__(16) float Ws[BK][BN];
+  const int tid = threadIdx.x;
+  const int tx = tid % TX, ty = tid / TX;
+  const long long row0 = (long long)blockIdx.x * BM;
+  const int col0 = blockIdx.y * BN;
+  const int lrow = tid & 127, lhalf = tid >> 7;
+  const long long r = row0 + lrow;
+  long long srow[4];
+  {
+    const int n = (int)(r % p.Nn);
+    const long long bt = r / p.Nn;
+    const int t = (int)(bt % p.Td);
+    const long long b = bt / p.Td;
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      srow[s] = -1;
+      if (s < p.nseg && r < p.rows) {
+        const int ts = t + (p.Ts - p.Td) - p.seg[s].shift;
+        if (ts >= 0) srow[s] = (b * p.Ts + ts) * p.seg[s].pitch + p.seg[s].off + n;
+      }
+    }
+  }
+  float acc[RM][4];
+#pragma unroll
+  for (int i = 0; i < RM; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  int kglob = 0;
+  for (int s = 0; s < p.nseg; ++s) {
+    const Seg& sg = p.seg[s];
+    const long long sr = s == 0 ? srow[0] : s == 1 ? srow[1] : s == 2 ? srow[2] : srow[3];
+    for (int k0 = 0; k0 < sg.width; k0 += BK, kglob += BK) {
+      float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+      if (sr >= 0) {
+        const float* ap = sg.p + sr * sg.ld + k0 + lhalf * 8;
+        a0 = *reinterpret_cast<const float4*>(ap);
+        a1 = *reinterpret_cast<const float4*>(ap + 4);
+      }
+      __syncthreads();
+      const int kb = lhalf * 8;
+      As[kb + 0][lrow] = a0.x; As[kb + 1][lrow] = a0.y; As[kb + 2][lrow] = a0.z; As[kb + 3][lrow] = a0.w;
+      As[kb + 4][lrow] = a1.x; As[kb + 5][lrow] = a1.y; As[kb + 6][lrow] = a1.z; As[kb + 7][lrow] = a1.w;
+      if (tid < BK * BN / 4) {
+        const int kk = tid / (BN / 4), c4 = tid % (BN / 4);
+        *reinterpret_cast<float4*>(&Ws[kk][c4 * 4]) =
+            *reinterpret_cast<const float4*>(p.W + (long long)(kglob + kk) * p.Nout + col0 + c4 * 4);
+      }
+      __syncthreads();
+#pragma unroll
+      for (int kk = 0; kk < BK; ++kk) {
+        const float4 bv = *reinterpret_cast<const float4*>(&Ws[kk][tx * 4]);
+#pragma unroll
+        for (int i = 0; i < RM; ++i) {
+          const float a = As[kk][ty * RM + i];
+          acc[i][0] = fmaf(a, bv.x, acc[i][0]); acc[i][1] = fmaf(a, bv.y, acc[i][1]);
+          acc[i][2] = fmaf(a, bv.z, acc[i][2]); acc[i][3] = fmaf(a, bv.w, acc[i][3]);
+        }
+      }
+    }
+  }
+  const int col = col0 + tx * 4;
+  float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.bias) bb = *reinterpret_cast<const float4*>(p.bias + col);
+#pragma unroll
+  for (int i = 0; i < RM; ++i) {
+    const long long rl = row0 + ty * RM + i;
+    if (rl < p.rows) {
+      const long long rr = (rl / p.Nn) * p.pitch_d + p.off_d + (rl % p.Nn);
+      float4 v;
+      v.x = apply_act(acc[i][0] + bb.x, p.act); v.y = apply_act(acc[i][1] + bb.y, p.act);
+      v.z = apply_act(acc[i][2] + bb.z, p.act); v.w = apply_act(acc[i][3] + bb.w, p.act);
+      *reinterpret_cast<float4*>(p.out + rr * p.ldo + col) = v;
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // K2 NodeEdge (emulator.py:27-45): out[s] = (w*|inci| + b) @ in[s], the folded
 // dense (R_out x R_in) matrix resident in shared memory (transposed), SPB samples
