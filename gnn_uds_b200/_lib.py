@@ -50,7 +50,7 @@ SYMBOLS = [
     "gnnuds_set_weights", "gnnuds_set_norm", "gnnuds_output_dims", "gnnuds_predict", "gnnuds_simulate",
     "gnnuds_rollout", "gnnuds_objective", "gnnuds_alloc_pinned", "gnnuds_free_pinned", "gnnuds_alloc_device",
     "gnnuds_free_device", "gnnuds_memcpy", "gnnuds_synchronize", "gnnuds_launch_count", "gnnuds_last_timing",
-    "gnnuds_set_profiling", "gnnuds_debug_stop_after", "gnnuds_debug_fetch",
+    "gnnuds_set_profiling", "gnnuds_debug_stop_after", "gnnuds_debug_fetch", "gnnuds_debug_umma_selftest",
 ]
 
 
@@ -90,6 +90,7 @@ def load():
     lib.gnnuds_set_profiling.argtypes = [vp, i32]
     lib.gnnuds_debug_stop_after.argtypes = [vp, i32]
     lib.gnnuds_debug_fetch.argtypes = [vp, i32, vp, i64, P(i64), P(i32)]
+    lib.gnnuds_debug_umma_selftest.argtypes = [vp, i32, vp, i32, i32, vp, i32, i32, i32, i32, vp]
     for s in SYMBOLS:
         if s not in ("gnnuds_last_error", "gnnuds_launch_count"):
             getattr(lib, s).restype = i32

@@ -20,9 +20,6 @@ def build(force=False, verbose=False, defines=()):
         return OUT
     nvcc = os.environ.get("NVCC", "nvcc")
     cmd = [nvcc] + FLAGS + ["-D%s" % d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, SRC, "-lcudart"]
-    if os.path.exists(os.path.join(HERE, "csrc", "tc_gemm.cuh")):
-        cmd.insert(1, "-DGNNUDS_WITH_TC")
-        cmd.append("-lcuda")
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)

@@ -5,9 +5,7 @@
 // over [B][T][N][C] activations.
 #include "../../include/gnnuds.h"
 #include "kernels.cuh"
-#ifdef GNNUDS_WITH_TC
-#include "tc_gemm.cuh"
-#endif
+#include "tc_selftest.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -114,6 +112,25 @@ int fail(gnnuds_handle* h, int code, const char* fmt, ...) {
     if (e_ != cudaSuccess)                                                                \
       return fail(h, GNNUDS_E_CUDA, "%s -> %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
   } while (0)
+
+// ---- bf16 operand images for the tensor-core kernels (layout: csrc/umma.cuh) -------------
+inline uint16_t f2bf(float f) {
+  uint32_t u;
+  std::memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+// K-major panel image of mat[rows][cols] (element (r,k) = mat[r*ldr + k*ldk]); rows/cols beyond the
+// matrix are zero.  Byte offset of (r,k): (k/8)*pstride + r*16 + (k%8)*2.
+std::vector<uint16_t> pack_kmajor(const float* mat, int rows, int cols, long ldr, long ldk, int Rp, int Kp, int pstride) {
+  std::vector<uint16_t> img((size_t)(Kp / 8) * pstride / 2, 0);
+  for (int r = 0; r < rows; ++r)
+    for (int k = 0; k < cols; ++k)
+      img[((size_t)(k / 8) * pstride + (size_t)r * 16) / 2 + (k % 8)] = f2bf(mat[r * ldr + k * ldk]);
+  (void)Rp;
+  return img;
+}
 
 int conv_ntens(const gnnuds_config& c) { return c.conv == GNNUDS_CONV_GAT ? 4 : 2; }
 
@@ -654,11 +671,8 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   if (c.recurrent == GNNUDS_REC_CONV1D && c.kernel_size > 4) return fail(nullptr, GNNUDS_E_INVALID, "kernel_size > 4 unsupported");
   if (c.n_out + (c.if_flood ? 1 : 0) > 4 || c.e_out > 4) return fail(nullptr, GNNUDS_E_INVALID, "head widths out of range");
   if (c.edge_fusion ? c.n_out != 1 : c.n_out != 3) return fail(nullptr, GNNUDS_E_INVALID, "n_out %d inconsistent with edge_fusion", c.n_out);
-  if (c.precision != GNNUDS_PREC_FP32
-#ifdef GNNUDS_WITH_TC
-      && c.precision != GNNUDS_PREC_BF16_TC
-#endif
-  ) return fail(nullptr, GNNUDS_E_INVALID, "precision %d not available in this build", c.precision);
+  if (c.precision != GNNUDS_PREC_FP32 && c.precision != GNNUDS_PREC_BF16_TC)
+    return fail(nullptr, GNNUDS_E_INVALID, "precision %d unknown", c.precision);
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
     return fail(nullptr, GNNUDS_E_CUDA, "no CUDA device: the gnn_uds_b200 product path has no CPU fallback");
@@ -1086,6 +1100,37 @@ int gnnuds_debug_stop_after(gnnuds_handle* h, int32_t stage) {
   h->debug_stop = stage;
   return 0;
 }
+int gnnuds_debug_umma_selftest(gnnuds_handle* h, int32_t mode, const float* act, int32_t Ra, int32_t Ca, const float* mat,
+                               int32_t Rm, int32_t Km, int32_t shift, int32_t swap, float* out) {
+  if (!h || !act || !mat || !out) return GNNUDS_E_INVALID;
+  CU(cudaSetDevice(h->c.device));
+  const int Nout = mode == 0 ? Rm : Ca;
+  if (Ca % 16 || Km % 16 || Nout % 16 || Nout > 256 || Nout < 16) return fail(h, GNNUDS_E_INVALID, "selftest: bad shape");
+  if (mode == 0 && (Km != Ca || Ra < shift + 128 || shift < 0)) return fail(h, GNNUDS_E_INVALID, "selftest mode 0: bad shape");
+  if (mode == 1 && (Rm != 128 || Ra < Km)) return fail(h, GNNUDS_E_INVALID, "selftest mode 1: bad shape");
+  const int ps_img = Rm * 16;
+  std::vector<uint16_t> img = pack_kmajor(mat, Rm, Km, Km, 1, Rm, Km, ps_img);
+  float *d_act = nullptr, *d_out = nullptr;
+  uint16_t* d_img = nullptr;
+  int rc = 0;
+  if ((rc = upload(h, &d_act, act, (size_t)Ra * Ca))) return rc;
+  if ((rc = upload(h, &d_img, img.data(), img.size()))) { cudaFree(d_act); return rc; }
+  if (cudaMalloc(&d_out, (size_t)128 * Nout * sizeof(float)) != cudaSuccess) { cudaFree(d_act); cudaFree(d_img); return fail(h, GNNUDS_E_NOMEM, "selftest"); }
+  SelfTestP p{d_act, d_img, d_out, Ra, Ca, Rm, Km, shift, swap, mode, Nout};
+  const size_t smem = (((size_t)(Ca / 8) * (Ra + 1) * 16 + 127) & ~(size_t)127) + (size_t)(Km / 8) * ps_img + 256;
+  cudaError_t e = cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e == cudaSuccess) {
+    umma_selftest_kernel<<<1, 256, smem, h->stream>>>(p);
+    ++h->launches;
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  if (e == cudaSuccess) e = cudaMemcpy(out, d_out, (size_t)128 * Nout * sizeof(float), cudaMemcpyDeviceToHost);
+  cudaFree(d_act); cudaFree(d_img); cudaFree(d_out);
+  if (e != cudaSuccess) return fail(h, GNNUDS_E_CUDA, "selftest: %s", cudaGetErrorString(e));
+  return 0;
+}
+
 int gnnuds_debug_fetch(gnnuds_handle* h, int32_t which, float* out, int64_t max_floats, int64_t* rows, int32_t* width) {
   if (!h || which < 0 || which > 1 || !h->dbg_ptr[which]) return GNNUDS_E_INVALID;
   CU(cudaSetDevice(h->c.device));

@@ -163,6 +163,17 @@ int gnnuds_debug_stop_after(gnnuds_handle* h, int32_t stage);
 int gnnuds_debug_fetch(gnnuds_handle* h, int32_t which, float* out, int64_t max_floats,
                        int64_t* rows, int32_t* width);
 
+/* Test hook for the tcgen05 building blocks (csrc/umma.cuh), one CTA, host buffers:
+     mode 0: out(128,Rm)  = bf16(act[shift:shift+128, :Ca]) @ bf16(mat(Rm,Km=Ca))^T
+             activations as the K-major A operand (with a row shift, as the causal Conv1D taps
+             use it), the weight image as the K-major B operand;
+     mode 1: out(128,Ca)  = bf16(mat(128,Km)) @ bf16(act[:Km, :Ca])
+             the weight image as A, activations as the MN-major B operand (NodeEdge / aggregation).
+   swap != 0 exchanges the leading/stride byte offsets of every descriptor (diagnostic). */
+int gnnuds_debug_umma_selftest(gnnuds_handle* h, int32_t mode, const float* act, int32_t Ra, int32_t Ca,
+                               const float* mat, int32_t Rm, int32_t Km, int32_t shift, int32_t swap,
+                               float* out);
+
 #ifdef __cplusplus
 }
 #endif
