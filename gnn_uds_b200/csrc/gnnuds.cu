@@ -5,6 +5,7 @@
 // over [B][T][N][C] activations.
 #include "../../include/gnnuds.h"
 #include "kernels.cuh"
+#include "tc_gemm.cuh"
 #include "tc_selftest.cuh"
 
 #include <algorithm>
@@ -29,7 +30,7 @@ struct SpatialW {
   int cx, ce;
 };
 
-struct TensorDesc { int64_t numel; int d0, d1, d2; };
+struct TensorDesc { int64_t numel; int d0, d1, d2; int last() const { return d2 ? d2 : (d1 ? d1 : d0); } };
 
 }  // namespace
 
@@ -58,6 +59,10 @@ struct gnnuds_handle {
   // device parameters
   float* d_blob = nullptr;
   std::vector<int64_t> toff;
+  uint8_t* d_wimg = nullptr;            // bf16 K-major weight images of every GEMM layer (tensor-core path)
+  std::vector<long long> img_off;       // byte offset per tensor index, -1 = no image
+  bool tc() const { return c.precision == GNNUDS_PREC_BF16_TC; }
+  size_t es() const { return tc() ? 2 : 4; }   // bytes per stored activation element
   std::vector<float*> d_ne_matT[2];     // per spatial layer (block*S + l): N-side, M-side folded matrices
   int ldm_n = 0, ldm_m = 0, ti_n = 0, ti_m = 0;
 
@@ -287,8 +292,9 @@ int launch_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, const float* Wp
   return 0;
 }
 
+template <typename ST = float>
 int launch_embed(gnnuds_handle* h, const float* in, const float* nrm, int cn, int Nn_norm, const int* gather, int n_act,
-                 const LayerW& w, float* out, float* res, long long Bc, int T, int Nn, int K, int Eo, int act, int mode) {
+                 const LayerW& w, void* out, float* res, long long Bc, int T, int Nn, int K, int Eo, int act, int mode) {
   EmbedP p{};
   p.in = in; p.nmax = nrm; p.nmin = nrm ? nrm + (size_t)Nn_norm * cn : nullptr; p.cn = cn;
   p.gather = gather; p.n_act = n_act;
@@ -296,37 +302,39 @@ int launch_embed(gnnuds_handle* h, const float* in, const float* nrm, int cn, in
   p.rows = Bc * T * Nn; p.T = T; p.Nn = Nn; p.K = K; p.Eo = Eo; p.act = act; p.mode = mode;
   if (p.rows == 0) return 0;
   const int rpb = 256 / (Eo / 4);
-  embed_kernel<<<grid_for(h, p.rows, rpb, 16), 256, (size_t)(K * Eo + Eo) * sizeof(float), h->stream>>>(p);
+  embed_kernel<ST><<<grid_for(h, p.rows, rpb, 16), 256, (size_t)(K * Eo + Eo) * sizeof(float), h->stream>>>(p);
   ++h->launches;
   CU(cudaGetLastError());
   return 0;
 }
 
-template <int TI>
+template <int TI, typename T>
 int launch_ne_t(gnnuds_handle* h, const NodeEdgeP& p, size_t smem) {
-  CU(cudaFuncSetAttribute(nodeedge_kernel<TI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CU(cudaFuncSetAttribute(nodeedge_kernel<TI, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int g = grid_for(h, (p.S + 1) / 2, 1, 1);
-  nodeedge_kernel<TI><<<g, 512, smem, h->stream>>>(p);
+  nodeedge_kernel<TI, T><<<g, 512, smem, h->stream>>>(p);
   ++h->launches;
   CU(cudaGetLastError());
   return 0;
 }
 
-int launch_nodeedge(gnnuds_handle* h, const float* matT, int ldm, int TI, const float* in, float* out, long long S,
+template <typename T = float>
+int launch_nodeedge(gnnuds_handle* h, const float* matT, int ldm, int TI, const void* in, void* out, long long S,
                     int R_in, int R_out, int F) {
   NodeEdgeP p{matT, in, out, S, R_in, R_out, F, ldm};
   const size_t smem = ((size_t)R_in * ldm + 2 * (size_t)R_in * F) * sizeof(float);
   if (smem > 227 * 1024) return fail(h, GNNUDS_E_INVALID, "NodeEdge matrix (%d x %d) does not fit shared memory", R_out, R_in);
   switch (TI) {
-    case 4: return launch_ne_t<4>(h, p, smem);
-    case 8: return launch_ne_t<8>(h, p, smem);
-    case 12: return launch_ne_t<12>(h, p, smem);
-    case 16: return launch_ne_t<16>(h, p, smem);
+    case 4: return launch_ne_t<4, T>(h, p, smem);
+    case 8: return launch_ne_t<8, T>(h, p, smem);
+    case 12: return launch_ne_t<12, T>(h, p, smem);
+    case 16: return launch_ne_t<16, T>(h, p, smem);
     default: return fail(h, GNNUDS_E_INVALID, "NodeEdge: rows per thread %d unsupported (graph too large for the NodeEdge path)", TI);
   }
 }
 
-int launch_agg(gnnuds_handle* h, const float* hin, float* out, const int* rp, const int* ci, const float* val,
+template <typename T = float>
+int launch_agg(gnnuds_handle* h, const void* hin, void* out, const int* rp, const int* ci, const float* val,
                const LayerW& w, long long S, int R, int act) {
   const auto& c = h->c;
   const int E = c.embed;
@@ -335,28 +343,29 @@ int launch_agg(gnnuds_handle* h, const float* hin, float* out, const int* rp, co
   const size_t smem = ((size_t)R * E + 2 * (size_t)R) * sizeof(float);
   if (smem <= 200 * 1024) {
     AggP p{hin, out, rp, ci, val, gat ? W(h, w.t[1]) : nullptr, gat ? W(h, w.t[2]) : nullptr, bias, S, R, E, act, gat ? 1 : 0};
-    CU(cudaFuncSetAttribute(agg_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    agg_small_kernel<<<grid_for(h, S, 1, 16), 256, smem, h->stream>>>(p);
+    CU(cudaFuncSetAttribute(agg_small_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    agg_small_kernel<T><<<grid_for(h, S, 1, 16), 256, smem, h->stream>>>(p);
     ++h->launches;
   } else {
     if (gat) {
-      row_scores_kernel<<<grid_for(h, S * R, 8, 16), 256, 0, h->stream>>>(hin, W(h, w.t[1]), W(h, w.t[2]), h->SS, h->SN, S * R, E);
+      row_scores_kernel<T><<<grid_for(h, S * R, 8, 16), 256, 0, h->stream>>>(static_cast<const T*>(hin), W(h, w.t[1]), W(h, w.t[2]), h->SS, h->SN, S * R, E);
       ++h->launches;
     }
     AggLargeP p{hin, out, rp, ci, val, h->SS, h->SN, bias, S, R, E, act, gat ? 1 : 0};
-    agg_large_kernel<<<grid_for(h, S * R, 8, 32), 256, 0, h->stream>>>(p);
+    agg_large_kernel<T><<<grid_for(h, S * R, 8, 32), 256, 0, h->stream>>>(p);
     ++h->launches;
   }
   CU(cudaGetLastError());
   return 0;
 }
 
-int launch_head(gnnuds_handle* h, const float* in, int ld, int K, const LayerW& w, float* out, int ldo, int col0,
+template <typename T = float>
+int launch_head(gnnuds_handle* h, const void* in, int ld, int K, const LayerW& w, float* out, int ldo, int col0,
                 int Nout, int act, long long rows) {
   if (Nout > 4) return fail(h, GNNUDS_E_INVALID, "head wider than 4 columns (%d)", Nout);
   HeadP p{in, ld, K, W(h, w.t[0]), W(h, w.t[1]), out, ldo, col0, Nout, act, rows};
   if (rows == 0) return 0;
-  head_kernel<<<grid_for(h, rows, 8, 16), 256, (size_t)K * Nout * sizeof(float), h->stream>>>(p);
+  head_kernel<T><<<grid_for(h, rows, 8, 16), 256, (size_t)K * Nout * sizeof(float), h->stream>>>(p);
   ++h->launches;
   CU(cudaGetLastError());
   return 0;
@@ -396,13 +405,13 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const float* sr
       if (gru) {
         GruP p{h->HB, W(h, L[i].t[1]), W(h, L[i].t[2]) + G, o, nseq, Nn, Ts, Tdst, H};
         const size_t smem = ((size_t)H * G + 32 * H + 32 * G) * sizeof(float);
-        CU(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        gru_kernel<<<g, 256, smem, h->stream>>>(p);
+        CU(cudaFuncSetAttribute(gru_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        gru_kernel<float><<<g, 256, smem, h->stream>>>(p);
       } else {
         LstmP p{h->HB, W(h, L[i].t[1]), o, nseq, Nn, Ts, Tdst, H};
         const size_t smem = ((size_t)H * G + 64 * H + 32 * G) * sizeof(float);
-        CU(cudaFuncSetAttribute(lstm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        lstm_kernel<<<g, 256, smem, h->stream>>>(p);
+        CU(cudaFuncSetAttribute(lstm_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        lstm_kernel<float><<<g, 256, smem, h->stream>>>(p);
       }
       ++h->launches;
       CU(cudaGetLastError());
@@ -453,6 +462,31 @@ int run_spatial(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) {
 void set_dbg(gnnuds_handle* h, const Stream2& st, long long rows_x, long long rows_e) {
   h->dbg_ptr[0] = st.x[0].p; h->dbg_width[0] = st.x[0].width; h->dbg_rows[0] = rows_x;
   h->dbg_ptr[1] = st.e[0].p; h->dbg_width[1] = st.e[0].width; h->dbg_rows[1] = rows_e;
+}
+
+int run_postproc(gnnuds_handle* h, const float* b, const float* a, long long Bc, float* y, float* ey, bool normalised_io) {
+  const auto& c = h->c;
+  const int N = c.n_node, M = c.n_edge, To = c.seq_out;
+  const int ldn = h->ldn();
+  // ---- P1..P4 post-processing ----
+  PostP p{};
+  p.out_n = h->OUTN; p.ldn = ldn; p.out_e = h->OUTE; p.lde = c.e_out;
+  p.b_raw = b; p.a = c.act ? a : nullptr; p.n_act = c.n_act;
+  p.act_of_edge = h->d_act_of_edge; p.act_out_of_node = h->d_act_out; p.act_in_of_node = h->d_act_in;
+  p.inc_ptr = h->d_inc_ptr; p.inc_edge = h->d_inc_edge; p.inc_sign = h->d_inc_sign;
+  p.ymax = h->d_ny; p.ymin = h->d_ny + (size_t)N * h->cy_n; p.cy = h->cy_n;
+  p.emax = h->d_ne; p.emin = h->d_ne + (size_t)M * h->ce_n; p.ce = h->ce_n;
+  p.bmax = h->d_nb; p.bmin = h->d_nb + (size_t)N * h->cb_n; p.cb = h->cb_n;
+  p.hmin = h->d_hmin; p.hmax = h->d_hmax; p.is_outfall = h->d_outfall; p.ehmax = h->d_ehmax;
+  p.y = y; p.ey = ey; p.S = Bc * To; p.N = N; p.M = M; p.b_in = c.b_in; p.n_out = c.n_out; p.e_out = c.e_out;
+  p.ny = normalised_io ? 3 + (c.if_flood ? 1 : 0) : h->ny();
+  p.if_flood = c.if_flood ? 1 : 0; p.edge_fusion = c.edge_fusion; p.act = c.act; p.tide = c.tide;
+  p.normalised = normalised_io ? 1 : 0; p.epsilon = c.epsilon;
+  if (normalised_io && c.tide) return fail(h, GNNUDS_E_INVALID, "ROLL_NORM with tide not supported");
+  postproc_kernel<<<grid_for(h, p.S, 1, 16), 128, (size_t)M * sizeof(float), h->stream>>>(p);
+  ++h->launches;
+  CU(cudaGetLastError());
+  return 0;
 }
 
 // One forward over Bc scenarios whose inputs are already on the device.
@@ -515,8 +549,8 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
   if ((rc = launch_gemm(h, st.x, W(h, h->resx.t[0]), W(h, h->resx.t[1]), h->XA, E, E, ract, Bc, N, To, To, N, 0))) return rc;
   if ((rc = launch_gemm(h, st.e, W(h, h->rese.t[0]), W(h, h->rese.t[1]), h->EA, E, E, ract, Bc, M, To, To, M, 0))) return rc;
   if (c.resnet) {
-    cumsum_res_act_kernel<<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(h->XA, h->RES, Bc, To, N, E, act);
-    cumsum_res_act_kernel<<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(h->EA, h->RESE, Bc, To, M, E, act);
+    cumsum_res_act_kernel<float><<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(h->XA, h->RES, Bc, To, N, E, act);
+    cumsum_res_act_kernel<float><<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(h->EA, h->RESE, Bc, To, M, E, act);
     h->launches += 2;
     CU(cudaGetLastError());
   }
@@ -538,25 +572,267 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
     if ((rc = launch_head(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return rc;
   }
   if ((rc = launch_head(h, h->EA, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
-  // ---- P1..P4 post-processing ----
-  PostP p{};
-  p.out_n = h->OUTN; p.ldn = ldn; p.out_e = h->OUTE; p.lde = c.e_out;
-  p.b_raw = b; p.a = c.act ? a : nullptr; p.n_act = c.n_act;
-  p.act_of_edge = h->d_act_of_edge; p.act_out_of_node = h->d_act_out; p.act_in_of_node = h->d_act_in;
-  p.inc_ptr = h->d_inc_ptr; p.inc_edge = h->d_inc_edge; p.inc_sign = h->d_inc_sign;
-  p.ymax = h->d_ny; p.ymin = h->d_ny + (size_t)N * h->cy_n; p.cy = h->cy_n;
-  p.emax = h->d_ne; p.emin = h->d_ne + (size_t)M * h->ce_n; p.ce = h->ce_n;
-  p.bmax = h->d_nb; p.bmin = h->d_nb + (size_t)N * h->cb_n; p.cb = h->cb_n;
-  p.hmin = h->d_hmin; p.hmax = h->d_hmax; p.is_outfall = h->d_outfall; p.ehmax = h->d_ehmax;
-  p.y = y; p.ey = ey; p.S = Bc * To; p.N = N; p.M = M; p.b_in = c.b_in; p.n_out = c.n_out; p.e_out = c.e_out;
-  p.ny = normalised_io ? 3 + (c.if_flood ? 1 : 0) : h->ny();
-  p.if_flood = c.if_flood ? 1 : 0; p.edge_fusion = c.edge_fusion; p.act = c.act; p.tide = c.tide;
-  p.normalised = normalised_io ? 1 : 0; p.epsilon = c.epsilon;
-  if (normalised_io && c.tide) return fail(h, GNNUDS_E_INVALID, "ROLL_NORM with tide not supported");
-  postproc_kernel<<<grid_for(h, p.S, 1, 16), 128, (size_t)M * sizeof(float), h->stream>>>(p);
+  return run_postproc(h, b, a, Bc, y, ey, normalised_io);
+}
+
+// =========================================================================================
+// Tensor-core path (precision = GNNUDS_PREC_BF16_TC): bf16 activations in HBM, every dense
+// contraction on tcgen05 (csrc/tc_gemm.cuh), the GCN/GAT aggregation fused into the epilogue
+// of the conv GEMM when a sample's rows fit one CTA tile.
+// =========================================================================================
+struct AggArgs { int kind = 0; int R = 0; const int* rp = nullptr; const int* ci = nullptr; const float* val = nullptr;
+                 const float* a_self = nullptr; const float* a_neigh = nullptr; };
+
+int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor, const float* bias, void* out, int ldo,
+                   int Nout, int act, long long Bc, int Nn, int Td, int Ts, int pitch_d, int off_d,
+                   const AggArgs* agg = nullptr) {
+  if (segs.empty() || segs.size() > 4) return fail(h, GNNUDS_E_INVALID, "tc_gemm: 1..4 segments");
+  if (w_tensor < 0 || w_tensor >= (int)h->img_off.size() || h->img_off[w_tensor] < 0)
+    return fail(h, GNNUDS_E_STATE, "tc_gemm: no bf16 image for weight tensor %d", w_tensor);
+  TcGemmP p{};
+  p.nseg = (int)segs.size();
+  int Ktot = 0, kc = 64;
+  for (int i = 0; i < p.nseg; ++i) {
+    if (segs[i].width % 32) return fail(h, GNNUDS_E_INVALID, "tc_gemm: segment width %d not a multiple of 32", segs[i].width);
+    if (segs[i].width % 64) kc = 32;
+    if (segs[i].ld % 8) return fail(h, GNNUDS_E_INVALID, "tc_gemm: row pitch %d not a multiple of 8 elements", segs[i].ld);
+    p.seg[i] = TcSeg{static_cast<const bf16*>(static_cast<const void*>(segs[i].p)), segs[i].ld, segs[i].width, segs[i].shift,
+                     segs[i].pitch, segs[i].off};
+    Ktot += segs[i].width;
+  }
+  if (Nout % 32 || Nout > 256 || Nout < 32) return fail(h, GNNUDS_E_INVALID, "tc_gemm: Nout %d unsupported", Nout);
+  if ((long long)Ktot * Nout != h->tens[w_tensor].numel) return fail(h, GNNUDS_E_INVALID, "tc_gemm: weight %d shape mismatch", w_tensor);
+  const long long rows = Bc * Td * Nn;
+  if (rows == 0) return 0;
+  if (rows >= (1ll << 31)) return fail(h, GNNUDS_E_INVALID, "tc_gemm: %lld rows exceed the 32-bit row index", rows);
+  p.Wimg = h->d_wimg + h->img_off[w_tensor];
+  p.bias = bias; p.out = static_cast<bf16*>(out); p.ldo = ldo;
+  p.Nout = Nout; p.Ktot = Ktot; p.kc = kc; p.act = act;
+  p.rows = (unsigned)rows; p.Nn = Nn; p.Td = Td; p.Ts = Ts; p.pitch_d = pitch_d; p.off_d = off_d;
+  if (agg && agg->kind) {
+    const int R = agg->R;
+    const int g = R <= 128 ? 128 / R : 1;
+    p.rpt = g * R; p.MT = (p.rpt + 127) / 128;
+    p.agg = agg->kind; p.R = R; p.hs = Nout + 4;
+    p.row_ptr = agg->rp; p.col_idx = agg->ci; p.val = agg->val; p.a_self = agg->a_self; p.a_neigh = agg->a_neigh;
+    if (!bias) return fail(h, GNNUDS_E_INVALID, "tc_gemm: aggregation epilogue needs the conv bias");
+    if (Nn != R || pitch_d != Nn || off_d != 0) return fail(h, GNNUDS_E_INVALID, "tc_gemm: aggregation needs sample-contiguous rows");
+  } else {
+    p.rpt = 128; p.MT = 1;
+  }
+  if (p.MT * Nout > 256) return fail(h, GNNUDS_E_INVALID, "tc_gemm: accumulator tile %d x %d exceeds TMEM stage", p.MT * 128, Nout);
+  p.n_tiles = (unsigned)((rows + p.rpt - 1) / p.rpt);
+  p.w_bytes = (uint32_t)Ktot * Nout * 2;
+  p.pstrideA = (uint32_t)(128 * p.MT + 1) * 16u;
+  p.stage_bytes = 8u * p.pstrideA;
+  p.stage_off = (p.w_bytes + 127u) & ~127u;
+  const uint32_t h_bytes = p.agg ? (((uint32_t)p.rpt * p.hs * 4u + 127u) & ~127u) : 0u;
+  const uint32_t sc_bytes = p.agg ? (uint32_t)(4 * 128 * p.MT + 2 * Nout) * 4u : 0u;
+  const uint32_t fixed = p.stage_off + h_bytes + sc_bytes + 256u;
+  const uint32_t cap = 227u * 1024u;
+  if (fixed + 3u * p.stage_bytes > cap) return fail(h, GNNUDS_E_INVALID, "tc_gemm: tile does not fit shared memory");
+  p.NS = (int)std::min<uint32_t>(8u, (cap - fixed) / p.stage_bytes);
+  p.h_off = p.stage_off + (uint32_t)p.NS * p.stage_bytes;
+  p.sc_off = p.h_off + h_bytes;
+  p.bar_off = (p.sc_off + sc_bytes + 15u) & ~15u;
+  const size_t smem = p.bar_off + (size_t)(2 * p.NS + 6) * 8 + 16;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (h->profiling >= 2) {
+    if (h->gemm_ev_used == h->gemm_ev.size()) {
+      cudaEvent_t a, b;
+      CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
+      h->gemm_ev.push_back({a, b});
+    }
+    e0 = h->gemm_ev[h->gemm_ev_used].first; e1 = h->gemm_ev[h->gemm_ev_used].second;
+    ++h->gemm_ev_used;
+    CU(cudaEventRecord(e0, h->stream));
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    CU(cudaFuncSetAttribute(tc_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  const unsigned grid = std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count);
+  tc_rows_kernel<<<grid, TC_THREADS, smem, h->stream>>>(p);
   ++h->launches;
+  if (h->profiling >= 2) CU(cudaEventRecord(e1, h->stream));
   CU(cudaGetLastError());
   return 0;
+}
+
+int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const float* src, int cin, long long Bc, int Nn,
+                    int Ts, int Td, float* t0, float* t1, float** dst) {
+  const auto& c = h->c;
+  const int H = c.hidden, P = c.n_tp_layer;
+  const float* cur = src;
+  int cw = cin;
+  float* bufs[2] = {t0, t1};
+  for (int i = 0; i < P; ++i) {
+    const bool last = (i == P - 1);
+    const int Tdst = last ? Td : Ts;
+    float* o = bufs[i & 1];
+    int rc;
+    if (c.recurrent == GNNUDS_REC_CONV1D) {
+      std::vector<SegH> segs;
+      const int k = c.kernel_size, d = 1 << i;
+      for (int j = 0; j < k; ++j) segs.push_back({cur, cw, cw, (k - 1 - j) * d, Nn, 0});
+      if ((rc = launch_tc_gemm(h, segs, L[i].t[0], W(h, L[i].t[1]), o, H, H, act_code(c), Bc, Nn, Tdst, Ts, Nn, 0))) return rc;
+    } else {
+      const bool gru = c.recurrent == GNNUDS_REC_GRU;
+      const int G = (gru ? 3 : 4) * H;
+      if ((rc = launch_tc_gemm(h, {{cur, cw, cw, 0, Nn, 0}}, L[i].t[0], W(h, L[i].t[2]), h->HB, G, G, ACT_LINEAR, Bc, Nn, Ts, Ts,
+                               Nn, 0))) return rc;
+      const long long nseq = Bc * Nn;
+      const int g = (int)((nseq + 31) / 32);
+      if (gru) {
+        GruP p{h->HB, W(h, L[i].t[1]), W(h, L[i].t[2]) + G, o, nseq, Nn, Ts, Tdst, H};
+        const size_t smem = ((size_t)H * G + 32 * H + 32 * G) * sizeof(float);
+        CU(cudaFuncSetAttribute(gru_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        gru_kernel<bf16><<<g, 256, smem, h->stream>>>(p);
+      } else {
+        LstmP p{h->HB, W(h, L[i].t[1]), o, nseq, Nn, Ts, Tdst, H};
+        const size_t smem = ((size_t)H * G + 64 * H + 32 * G) * sizeof(float);
+        CU(cudaFuncSetAttribute(lstm_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        lstm_kernel<bf16><<<g, 256, smem, h->stream>>>(p);
+      }
+      ++h->launches;
+      CU(cudaGetLastError());
+    }
+    cur = o; cw = H;
+  }
+  *dst = const_cast<float*>(cur);
+  return 0;
+}
+
+// conv (GCN/GAT) over `segs`: linear part on tensor cores, aggregation fused when the sample fits a tile
+int run_conv_tc(gnnuds_handle* h, const std::vector<SegH>& segs, const LayerW& w, float* out, const int* rp, const int* ci,
+                const float* val, long long Bc, int T, int R, int act) {
+  const auto& c = h->c;
+  const int E = c.embed;
+  const bool gat = c.conv == GNNUDS_CONV_GAT;
+  const float* bias = W(h, w.t[gat ? 3 : 1]);
+  const int g = R <= 128 ? 128 / R : 1;
+  const int MT = (g * R + 127) / 128;
+  int Ktot = 0;
+  for (const auto& sg : segs) Ktot += sg.width;
+  const size_t need = (((size_t)Ktot * E * 2 + 127) & ~(size_t)127) + (((size_t)g * R * (E + 4) * 4 + 127) & ~(size_t)127) +
+                      (size_t)(4 * 128 * MT + 2 * E) * 4 + 256 + 3 * 8 * (size_t)(128 * MT + 1) * 16;
+  if (MT * E <= 256 && need <= 227 * 1024) {
+    AggArgs a;
+    a.kind = gat ? 2 : 1; a.R = R; a.rp = rp; a.ci = ci; a.val = val;
+    a.a_self = gat ? W(h, w.t[1]) : nullptr; a.a_neigh = gat ? W(h, w.t[2]) : nullptr;
+    return launch_tc_gemm(h, segs, w.t[0], bias, out, E, E, act, Bc, R, T, T, R, 0, &a);
+  }
+  int rc;
+  if ((rc = launch_tc_gemm(h, segs, w.t[0], nullptr, h->HB, E, E, ACT_LINEAR, Bc, R, T, T, R, 0))) return rc;
+  return launch_agg<bf16>(h, h->HB, out, rp, ci, val, w, Bc * T, R, act);
+}
+
+int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) {
+  const auto& c = h->c;
+  const int E = c.embed, E2 = E / 2, N = c.n_node, M = c.n_edge;
+  const long long S = Bc * T;
+  const int act = act_code(c);
+  for (int l = 0; l < c.n_sp_layer; ++l) {
+    const SpatialW& w = h->sp[blk][l];
+    int rc;
+    if ((rc = launch_tc_gemm(h, st.e, w.xe.t[0], W(h, w.xe.t[1]), h->XE, E2, E2, act, Bc, M, T, T, M, 0))) return rc;
+    if ((rc = launch_tc_gemm(h, st.x, w.ex.t[0], W(h, w.ex.t[1]), h->EX, E2, E2, act, Bc, N, T, T, N, 0))) return rc;
+    const int li = blk * c.n_sp_layer + l;
+    if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, h->XE, h->NX, S, M, N, E2))) return rc;
+    if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, h->EX, h->NE, S, N, M, E2))) return rc;
+    std::vector<SegH> sx = st.x; sx.push_back({h->NX, E2, E2, 0, N, 0});
+    std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
+    float* xo = (l & 1) ? h->XB : h->XA;
+    float* eo = (l & 1) ? h->EB : h->EA;
+    if ((rc = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, Bc, T, N, act))) return rc;
+    if ((rc = run_conv_tc(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, Bc, T, M, act))) return rc;
+    st.x = {{xo, E, E, 0, N, 0}};
+    st.e = {{eo, E, E, 0, M, 0}};
+    if (h->debug_stop == (blk ? 40 : 20) + l) return 1;
+  }
+  return 0;
+}
+
+int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const float* a, const float* ex, long long Bc,
+                     float* y, float* ey, bool normalised_io) {
+  const auto& c = h->c;
+  const int E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge, Ti = c.seq_in, To = c.seq_out;
+  const int act = act_code(c);
+  int rc;
+  if (c.graph_base) return fail(h, GNNUDS_E_INVALID, "graph_base != 0 forward not built in this revision");
+  if ((rc = launch_embed<bf16>(h, x, normalised_io ? nullptr : h->d_nx, h->cx_n, N, nullptr, 0, h->emb_x, h->XB, h->RES, Bc, Ti, N,
+                               c.n_in, E, act, 0))) return rc;
+  if ((rc = launch_embed<bf16>(h, b, normalised_io ? nullptr : h->d_nb, h->cb_n, N, nullptr, 0, h->emb_b, h->BEMB, nullptr, Bc, To, N,
+                               c.b_in, E2, act, 0))) return rc;
+  if ((rc = launch_embed<bf16>(h, ex, normalised_io ? nullptr : h->d_ne, h->ce_n, M, nullptr, 0, h->emb_e, h->EB, h->RESE, Bc, Ti, M,
+                               c.e_in, E, act, 0))) return rc;
+  if (c.act) {
+    if ((rc = launch_embed<bf16>(h, a, nullptr, 0, 0, h->d_act_of_edge, c.n_act, h->emb_a, h->AEMB, nullptr, Bc, To, M, 1, E2, act, 2)))
+      return rc;
+  }
+  Stream2 st;
+  st.x = {{h->XB, E, E, 0, N, 0}};
+  st.e = {{h->EB, E, E, 0, M, 0}};
+  set_dbg(h, st, Bc * Ti * N, Bc * Ti * M);
+  if (h->debug_stop == 1) return 0;
+  rc = run_spatial_tc(h, 0, st, Bc, Ti);
+  set_dbg(h, st, Bc * Ti * N, Bc * Ti * M);
+  if (rc == 1) return 0;
+  if (rc) return rc;
+  if (h->debug_stop == 2) return 0;
+  float *xt = nullptr, *et = nullptr;
+  if ((rc = run_temporal_tc(h, h->tpx[0], st.x[0].p, E, Bc, N, Ti, To, h->TX0, h->TX1, &xt))) return rc;
+  if ((rc = run_temporal_tc(h, h->tpe[0], st.e[0].p, E, Bc, M, Ti, To, h->TE0, h->TE1, &et))) return rc;
+  st.x = {{xt, H, H, 0, N, 0}, {h->BEMB, E2, E2, 0, N, 0}};
+  st.e = {{et, H, H, 0, M, 0}};
+  if (c.act) st.e.push_back({h->AEMB, E2, E2, 0, M, 0});
+  set_dbg(h, st, Bc * To * N, Bc * To * M);
+  if (h->debug_stop == 3) return 0;
+  rc = run_spatial_tc(h, 1, st, Bc, To);
+  set_dbg(h, st, Bc * To * N, Bc * To * M);
+  if (rc == 1) return 0;
+  if (rc) return rc;
+  if (h->debug_stop == 4) return 0;
+  if ((rc = run_temporal_tc(h, h->tpx[1], st.x[0].p, E, Bc, N, To, To, h->TX0, h->TX1, &xt))) return rc;
+  if ((rc = run_temporal_tc(h, h->tpe[1], st.e[0].p, E, Bc, M, To, To, h->TE0, h->TE1, &et))) return rc;
+  st.x = {{xt, H, H, 0, N, 0}};
+  st.e = {{et, H, H, 0, M, 0}};
+  set_dbg(h, st, Bc * To * N, Bc * To * M);
+  if (h->debug_stop == 5) return 0;
+  const int ract = c.resnet ? ACT_LINEAR : act;
+  if ((rc = launch_tc_gemm(h, st.x, h->resx.t[0], W(h, h->resx.t[1]), h->XA, E, E, ract, Bc, N, To, To, N, 0))) return rc;
+  if ((rc = launch_tc_gemm(h, st.e, h->rese.t[0], W(h, h->rese.t[1]), h->EA, E, E, ract, Bc, M, To, To, M, 0))) return rc;
+  if (c.resnet) {
+    cumsum_res_act_kernel<bf16><<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(reinterpret_cast<bf16*>(h->XA), h->RES, Bc, To, N, E, act);
+    cumsum_res_act_kernel<bf16><<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(reinterpret_cast<bf16*>(h->EA), h->RESE, Bc, To, M, E, act);
+    h->launches += 2;
+    CU(cudaGetLastError());
+  }
+  st.x = {{h->XA, E, E, 0, N, 0}};
+  st.e = {{h->EA, E, E, 0, M, 0}};
+  set_dbg(h, st, Bc * To * N, Bc * To * M);
+  if (h->debug_stop == 6) return 0;
+  const long long RXo = Bc * To * N, REo = Bc * To * M;
+  const int ldn = h->ldn();
+  if ((rc = launch_head<bf16>(h, h->XA, E, E, h->head_out, h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID, RXo))) return rc;
+  if (c.if_flood) {
+    std::vector<SegH> cur = st.x;
+    float* bufs[2] = {h->EX, h->NX};
+    for (int i = 0; i < c.if_flood; ++i) {
+      if ((rc = launch_tc_gemm(h, cur, h->flood_chain[i].t[0], W(h, h->flood_chain[i].t[1]), bufs[i & 1], E2, E2, act, Bc, N, To, To,
+                               N, 0))) return rc;
+      cur = {{bufs[i & 1], E2, E2, 0, N, 0}};
+    }
+    if ((rc = launch_head<bf16>(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return rc;
+  }
+  if ((rc = launch_head<bf16>(h, h->EA, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
+  return run_postproc(h, b, a, Bc, y, ey, normalised_io);
+}
+
+int forward_any(gnnuds_handle* h, const float* x, const float* b, const float* a, const float* ex, long long Bc, float* y,
+                float* ey, bool normalised_io) {
+  return h->tc() ? forward_chunk_tc(h, x, b, a, ex, Bc, y, ey, normalised_io) : forward_chunk(h, x, b, a, ex, Bc, y, ey, normalised_io);
 }
 
 int64_t floats_per_scenario(const gnnuds_config& c) {
@@ -584,23 +860,25 @@ int ensure_workspace(gnnuds_handle* h, int64_t Bc) {
   const int64_t G = c.recurrent == GNNUDS_REC_GRU ? 3 * H : c.recurrent == GNNUDS_REC_LSTM ? 4 * H : 0;
   const int64_t W2 = std::max(E2, H);
   const int64_t RX = Bc * Tm * N, RE = Bc * Tm * M, RM = Bc * Tm * std::max(N, M);
-  std::vector<std::pair<float**, int64_t>> plan = {
-      {&h->XA, RX * E}, {&h->XB, RX * E}, {&h->EA, RE * E}, {&h->EB, RE * E}, {&h->HB, RM * std::max(E, G)},
-      {&h->XE, RE * W2}, {&h->EX, RX * W2}, {&h->NX, RX * W2}, {&h->NE, RE * W2},
-      {&h->TX0, RX * H}, {&h->TX1, RX * H}, {&h->TE0, RE * H}, {&h->TE1, RE * H},
-      {&h->BEMB, Bc * c.seq_out * N * E2}, {&h->AEMB, Bc * c.seq_out * M * E2},
-      {&h->RES, Bc * N * E}, {&h->RESE, Bc * M * E},
-      {&h->OUTN, Bc * c.seq_out * N * 4}, {&h->OUTE, Bc * c.seq_out * M * 4}, {&h->SS, RM}, {&h->SN, RM},
-      {&h->in_x, Bc * c.seq_in * N * c.n_in}, {&h->in_b, Bc * c.seq_out * N * c.b_in},
-      {&h->in_a, Bc * c.seq_out * std::max(c.n_act, 1)}, {&h->in_ex, Bc * c.seq_in * M * c.e_in},
-      {&h->out_y, Bc * c.seq_out * N * 5}, {&h->out_ey, Bc * c.seq_out * M * 4}};
+  const int64_t a = (int64_t)h->es();      // activation element size (fp32 path 4, tensor-core path 2)
+  struct Item { float** p; int64_t bytes; };
+  std::vector<Item> plan = {
+      {&h->XA, RX * E * a}, {&h->XB, RX * E * a}, {&h->EA, RE * E * a}, {&h->EB, RE * E * a}, {&h->HB, RM * std::max(E, G) * a},
+      {&h->XE, RE * W2 * a}, {&h->EX, RX * W2 * a}, {&h->NX, RX * W2 * a}, {&h->NE, RE * W2 * a},
+      {&h->TX0, RX * H * a}, {&h->TX1, RX * H * a}, {&h->TE0, RE * H * a}, {&h->TE1, RE * H * a},
+      {&h->BEMB, Bc * c.seq_out * N * E2 * a}, {&h->AEMB, Bc * c.seq_out * M * E2 * a},
+      {&h->RES, Bc * N * E * 4}, {&h->RESE, Bc * M * E * 4},
+      {&h->OUTN, Bc * c.seq_out * N * 4 * 4}, {&h->OUTE, Bc * c.seq_out * M * 4 * 4}, {&h->SS, RM * 4}, {&h->SN, RM * 4},
+      {&h->in_x, Bc * c.seq_in * N * c.n_in * 4}, {&h->in_b, Bc * c.seq_out * N * c.b_in * 4},
+      {&h->in_a, Bc * c.seq_out * std::max(c.n_act, 1) * 4}, {&h->in_ex, Bc * c.seq_in * M * c.e_in * 4},
+      {&h->out_y, Bc * c.seq_out * N * 5 * 4}, {&h->out_ey, Bc * c.seq_out * M * 4 * 4}};
   size_t total = 0;
-  for (auto& pr : plan) total += (size_t)((pr.second + 63) / 64 * 64);
-  CU(cudaMalloc(&h->d_ws, total * sizeof(float)));
-  CU(cudaMemsetAsync(h->d_ws, 0, total * sizeof(float), h->stream));
+  for (auto& it : plan) total += (size_t)((it.bytes + 255) / 256 * 256);
+  CU(cudaMalloc(&h->d_ws, total));
+  CU(cudaMemsetAsync(h->d_ws, 0, total, h->stream));
   size_t off = 0;
-  for (auto& pr : plan) { *pr.first = h->d_ws + off; off += (size_t)((pr.second + 63) / 64 * 64); }
-  h->ws_floats = total;
+  for (auto& it : plan) { *it.p = reinterpret_cast<float*>(reinterpret_cast<char*>(h->d_ws) + off); off += (size_t)((it.bytes + 255) / 256 * 256); }
+  h->ws_floats = total / 4;
   h->ws_chunk = Bc;
   return 0;
 }
@@ -609,7 +887,7 @@ int64_t pick_chunk(const gnnuds_handle* h, int64_t B) {
   const auto& c = h->c;
   if (c.max_chunk > 0) return std::min<int64_t>(B, c.max_chunk);
   const int64_t budget = (int64_t)(c.workspace_mb > 0 ? c.workspace_mb : 8192) * 1024 * 1024 / 4;
-  int64_t bc = budget / floats_per_scenario(c);
+  int64_t bc = budget / floats_per_scenario(c) * (h->tc() ? 2 : 1);
   if (bc < 1) bc = 1;
   return std::min(B, bc);
 }
@@ -698,7 +976,7 @@ int gnnuds_destroy(gnnuds_handle* h) {
   cudaStreamSynchronize(h->stream);
   void* ptrs[] = {h->d_blob, h->d_rp, h->d_ci, h->d_erp, h->d_eci, h->d_val, h->d_eval, h->d_edges, h->d_act_of_edge,
                   h->d_act_out, h->d_act_in, h->d_inc_ptr, h->d_inc_edge, h->d_inc_sign, h->d_hmin, h->d_hmax,
-                  h->d_outfall, h->d_ehmax, h->d_nx, h->d_nb, h->d_ny, h->d_ne, h->d_ws, h->ro_x, h->ro_ex, h->ro_b, h->ro_a};
+                  h->d_outfall, h->d_ehmax, h->d_nx, h->d_nb, h->d_ny, h->d_ne, h->d_ws, h->ro_x, h->ro_ex, h->ro_b, h->ro_a, h->d_wimg};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p);
   for (auto& e : h->gemm_ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
@@ -794,6 +1072,35 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
   for (int64_t i = 0; i < n_floats; ++i) if (!std::isfinite(blob[i])) return fail(h, GNNUDS_E_INVALID, "non-finite weight at blob[%lld]", (long long)i);
   int rc;
   if ((rc = upload(h, &h->d_blob, blob, (size_t)n_floats))) return rc;
+  if (h->tc()) {
+    // bf16 K-major images (B operand = W^T) of every GEMM layer, one blob
+    std::vector<int> ids;
+    auto add = [&](const LayerW& l) { ids.push_back(l.t[0]); };
+    for (int blk = 0; blk < 2; ++blk) {
+      for (const SpatialW& w : h->sp[blk]) {
+        if (c.graph_base) add(w.joint); else { add(w.xe); add(w.ex); add(w.conv_x); add(w.conv_e); }
+      }
+      for (const LayerW& l : h->tpx[blk]) add(l);
+      for (const LayerW& l : h->tpe[blk]) add(l);
+    }
+    add(h->resx); add(h->rese);
+    for (const LayerW& l : h->flood_chain) add(l);
+    h->img_off.assign(n_tensors, -1);
+    std::vector<uint16_t> all;
+    for (int t : ids) {
+      const int Nout = h->tens[t].last();
+      const int Ktot = (int)(h->tens[t].numel / Nout);
+      if (Nout % 16 || Ktot % 16) return fail(h, GNNUDS_E_INVALID, "tensor-core path: weight %d is %d x %d (multiples of 16 needed)", t, Ktot, Nout);
+      std::vector<uint16_t> img = pack_kmajor(blob + offsets[t], Nout, Ktot, 1, Nout, Nout, Ktot, Nout * 16);
+      while (all.size() % 64) all.push_back(0);
+      h->img_off[t] = (long long)all.size() * 2;
+      all.insert(all.end(), img.begin(), img.end());
+    }
+    if (h->d_wimg) { cudaFree(h->d_wimg); h->d_wimg = nullptr; }
+    uint16_t* d = nullptr;
+    if ((rc = upload(h, &d, all.data(), all.size()))) return rc;
+    h->d_wimg = reinterpret_cast<uint8_t*>(d);
+  }
   // fold NodeEdge: mat = w * |inci| + b  (emulator.py:43), stored transposed + zero padded
   if (!c.graph_base) {
     const int N = c.n_node, M = c.n_edge, F = c.embed / 2;
@@ -884,13 +1191,13 @@ int gnnuds_predict(gnnuds_handle* h, const float* x, const float* b, const float
       CU(cudaMemcpyAsync(h->in_b, pb, nb * sb * sizeof(float), cudaMemcpyHostToDevice, h->stream));
       CU(cudaMemcpyAsync(h->in_ex, pe, nb * se * sizeof(float), cudaMemcpyHostToDevice, h->stream));
       if (pa) CU(cudaMemcpyAsync(h->in_a, pa, nb * sa * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-      if ((rc = forward_chunk(h, h->in_x, h->in_b, pa ? h->in_a : nullptr, h->in_ex, nb, h->out_y, h->out_ey, false))) return rc;
+      if ((rc = forward_any(h, h->in_x, h->in_b, pa ? h->in_a : nullptr, h->in_ex, nb, h->out_y, h->out_ey, false))) return rc;
       if (!h->debug_stop) {
         CU(cudaMemcpyAsync(py, h->out_y, nb * sy * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
         CU(cudaMemcpyAsync(pey, h->out_ey, nb * sey * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
       }
     } else {
-      if ((rc = forward_chunk(h, px, pb, pa, pe, nb, py, pey, false))) return rc;
+      if ((rc = forward_any(h, px, pb, pa, pe, nb, py, pey, false))) return rc;
     }
     if (h->debug_stop) break;
   }
@@ -989,7 +1296,7 @@ int gnnuds_rollout(gnnuds_handle* h, int32_t rule, const float* x0, const float*
         slice_time_kernel<<<grid_for(h, nb * T * c.n_act, 256, 16), 256, 0, h->stream>>>(da, h->ro_a, nb, (int)Th, k * T, T, c.n_act, 0);
         ++h->launches;
       }
-      rc = forward_chunk(h, h->ro_x, h->ro_b, da ? h->ro_a : nullptr, h->ro_ex, nb, h->out_y, h->out_ey, norm_io);
+      rc = forward_any(h, h->ro_x, h->ro_b, da ? h->ro_a : nullptr, h->ro_ex, nb, h->out_y, h->out_ey, norm_io);
       if (rc) break;
       // scatter outputs into the horizon tensors
       slice_time_kernel<<<grid_for(h, nb * T * (long long)N * nyc, 256, 16), 256, 0, h->stream>>>(h->out_y, dy, nb, (int)Th, k * T, T, (long long)N * nyc, 1);
@@ -1139,7 +1446,14 @@ int gnnuds_debug_fetch(gnnuds_handle* h, int32_t which, float* out, int64_t max_
   if (width) *width = h->dbg_width[which];
   if (out) {
     if (n > max_floats) return fail(h, GNNUDS_E_INVALID, "debug_fetch: buffer too small");
-    CU(cudaMemcpy(out, h->dbg_ptr[which], n * sizeof(float), cudaMemcpyDeviceToHost));
+    CU(cudaStreamSynchronize(h->stream));
+    if (h->tc()) {
+      std::vector<uint16_t> tmp((size_t)n);
+      CU(cudaMemcpy(tmp.data(), h->dbg_ptr[which], n * 2, cudaMemcpyDeviceToHost));
+      for (int64_t i = 0; i < n; ++i) { const uint32_t u = (uint32_t)tmp[i] << 16; std::memcpy(out + i, &u, 4); }
+    } else {
+      CU(cudaMemcpy(out, h->dbg_ptr[which], n * sizeof(float), cudaMemcpyDeviceToHost));
+    }
   }
   return 0;
 }

@@ -6,10 +6,33 @@
 // disappear: a causal dilated Conv1D tap is the same GEMM reading rows shifted
 // by shift*Nn, and the GRU walks rows with stride Nn.
 #pragma once
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 namespace gu {
+
+// Activation storage: float (fp32 parity path) or bf16 (tensor-core path).  Every kernel below
+// that touches an activation tensor is a template over the storage type and computes in fp32.
+typedef __nv_bfloat16 bf16;
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float4 ld4(const bf16* p) {
+  const uint2 u = *reinterpret_cast<const uint2*>(p);
+  return make_float4(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xFFFF0000u), __uint_as_float(u.y << 16),
+                     __uint_as_float(u.y & 0xFFFF0000u));
+}
+__device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void st4(bf16* p, float4 v) {
+  *reinterpret_cast<uint2*>(p) = make_uint2(pack2_bf16(v.x, v.y), pack2_bf16(v.z, v.w));
+}
+__device__ __forceinline__ float ld1(const float* p) { return *p; }
+__device__ __forceinline__ float ld1(const bf16* p) { return __bfloat162float(*p); }
+__device__ __forceinline__ void st1(float* p, float v) { *p = v; }
+__device__ __forceinline__ void st1(bf16* p, float v) { *p = __float2bfloat16_rn(v); }
 
 enum { ACT_LINEAR = 0, ACT_RELU = 1, ACT_TANH = 2, ACT_SIGMOID = 3, ACT_HARD_SIGMOID = 4 };
 
@@ -48,12 +71,13 @@ struct EmbedP {
   int n_act;
   const float* W;         // (K, Eo)
   const float* bias;      // (Eo)
-  float* out;             // (rows, Eo) activated
+  void* out;              // (rows, Eo) activated, storage type T
   float* res;             // (Bc*Nn, Eo) pre-activation of the last time step, or null
   long long rows;
   int T, Nn, K, Eo, act, mode;   // mode 0: plain, 2: gathered control input (K == 1)
 };
 
+template <typename T>
 __global__ void __launch_bounds__(256) embed_kernel(EmbedP p) {
   extern __shared__ float sm[];
   float* Ws = sm;                      // K*Eo
@@ -101,7 +125,7 @@ __global__ void __launch_bounds__(256) embed_kernel(EmbedP p) {
     }
     acc.x = apply_act(acc.x, p.act); acc.y = apply_act(acc.y, p.act);
     acc.z = apply_act(acc.z, p.act); acc.w = apply_act(acc.w, p.act);
-    *reinterpret_cast<float4*>(p.out + r * p.Eo + c4 * 4) = acc;
+    st4(static_cast<T*>(p.out) + r * p.Eo + c4 * 4, acc);
   }
 }
 
@@ -339,13 +363,13 @@ __global__ void __launch_bounds__(256) rows_gemm_f32_narrow(GemmP p) {
 // ---------------------------------------------------------------------------
 struct NodeEdgeP {
   const float* matT;     // (R_in, ldm) transposed folded matrix, zero padded to ldm
-  const float* in;       // (S, R_in, F)
-  float* out;            // (S, R_out, F)
+  const void* in;        // (S, R_in, F) storage type T
+  void* out;             // (S, R_out, F)
   long long S;
   int R_in, R_out, F, ldm;
 };
 
-template <int TI>
+template <int TI, typename T>
 __global__ void __launch_bounds__(512) nodeedge_kernel(NodeEdgeP p) {
   extern __shared__ __align__(16) float sm[];
   float* Ms = sm;                                   // R_in * ldm
@@ -363,9 +387,9 @@ __global__ void __launch_bounds__(512) nodeedge_kernel(NodeEdgeP p) {
     const long long s = s0 + half;
     __syncthreads();
     if (s < p.S) {
-      const float* src = p.in + s * p.R_in * p.F;
+      const T* src = static_cast<const T*>(p.in) + s * p.R_in * p.F;
       for (int i = t * 4; i < p.R_in * p.F; i += 256 * 4)
-        *reinterpret_cast<float4*>(Xh + i) = *reinterpret_cast<const float4*>(src + i);
+        *reinterpret_cast<float4*>(Xh + i) = ld4(src + i);
     }
     __syncthreads();
     if (s >= p.S || ig >= IG || i0 >= p.R_out) continue;
@@ -387,10 +411,10 @@ __global__ void __launch_bounds__(512) nodeedge_kernel(NodeEdgeP p) {
         }
       }
     }
-    float* dst = p.out + s * p.R_out * p.F;
+    T* dst = static_cast<T*>(p.out) + s * p.R_out * p.F;
 #pragma unroll
     for (int i = 0; i < TI; ++i)
-      if (i0 + i < p.R_out) *reinterpret_cast<float4*>(dst + (size_t)(i0 + i) * p.F + fg * 4) = acc[i];
+      if (i0 + i < p.R_out) st4(dst + (size_t)(i0 + i) * p.F + fg * 4, acc[i]);
   }
 }
 
@@ -404,14 +428,15 @@ __global__ void __launch_bounds__(512) nodeedge_kernel(NodeEdgeP p) {
 // over the pattern is the same function.
 // ---------------------------------------------------------------------------
 struct AggP {
-  const float* h;        // (S, R, E)
-  float* out;            // (S, R, E)
+  const void* h;         // (S, R, E) storage type T
+  void* out;             // (S, R, E)
   const int* row_ptr; const int* col_idx; const float* val;   // val null for GAT
   const float* a_self; const float* a_neigh;                  // (E) GAT only
   const float* bias;     // (E)
   long long S; int R, E, act, gat;
 };
 
+template <typename T>
 __global__ void __launch_bounds__(256) agg_small_kernel(AggP p) {
   extern __shared__ __align__(16) float sm[];
   float* hs = sm;                          // R*E
@@ -420,10 +445,10 @@ __global__ void __launch_bounds__(256) agg_small_kernel(AggP p) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
   const int E = p.E;
   for (long long s = blockIdx.x; s < p.S; s += gridDim.x) {
-    const float* src = p.h + s * p.R * E;
+    const T* src = static_cast<const T*>(p.h) + s * p.R * E;
     __syncthreads();
     for (int i = tid * 4; i < p.R * E; i += blockDim.x * 4)
-      *reinterpret_cast<float4*>(hs + i) = *reinterpret_cast<const float4*>(src + i);
+      *reinterpret_cast<float4*>(hs + i) = ld4(src + i);
     __syncthreads();
     if (p.gat) {
       for (int i = warp; i < p.R; i += nwarp) {
@@ -440,7 +465,7 @@ __global__ void __launch_bounds__(256) agg_small_kernel(AggP p) {
       }
       __syncthreads();
     }
-    float* dst = p.out + s * p.R * E;
+    T* dst = static_cast<T*>(p.out) + s * p.R * E;
     for (int i = warp; i < p.R; i += nwarp) {
       const int beg = p.row_ptr[i], end = p.row_ptr[i + 1];
       float mx = -INFINITY;
@@ -492,7 +517,7 @@ __global__ void __launch_bounds__(256) agg_small_kernel(AggP p) {
           float4 v;
           v.x = apply_act(acc.x + bb.x, p.act); v.y = apply_act(acc.y + bb.y, p.act);
           v.z = apply_act(acc.z + bb.z, p.act); v.w = apply_act(acc.w + bb.w, p.act);
-          *reinterpret_cast<float4*>(dst + (size_t)i * E + c) = v;
+          st4(dst + (size_t)i * E + c, v);
         }
       }
     }
@@ -503,14 +528,15 @@ __global__ void __launch_bounds__(256) agg_small_kernel(AggP p) {
 // 128-bit gathers of neighbour rows straight from HBM/L2.  Scores for GAT come from
 // row_scores_kernel.
 struct AggLargeP {
-  const float* h; float* out;
+  const void* h; void* out;   // storage type T
   const int* row_ptr; const int* col_idx; const float* val;
   const float* ss; const float* sn;     // (S*R) GAT scores or null
   const float* bias;
   long long S; int R, E, act, gat;
 };
 
-__global__ void __launch_bounds__(256) row_scores_kernel(const float* __restrict__ h, const float* __restrict__ a_self,
+template <typename T>
+__global__ void __launch_bounds__(256) row_scores_kernel(const T* __restrict__ h, const float* __restrict__ a_self,
                                                          const float* __restrict__ a_neigh, float* __restrict__ ss,
                                                          float* __restrict__ sn, long long rows, int E) {
   const int lane = threadIdx.x & 31;
@@ -519,7 +545,7 @@ __global__ void __launch_bounds__(256) row_scores_kernel(const float* __restrict
   for (long long r = w; r < rows; r += nw) {
     float d1 = 0.f, d2 = 0.f;
     for (int c = lane * 4; c < E; c += 128) {
-      const float4 hv = __ldg(reinterpret_cast<const float4*>(h + r * E + c));
+      const float4 hv = ld4(h + r * E + c);
       const float4 a1 = *reinterpret_cast<const float4*>(a_self + c);
       const float4 a2 = *reinterpret_cast<const float4*>(a_neigh + c);
       d1 += hv.x * a1.x + hv.y * a1.y + hv.z * a1.z + hv.w * a1.w;
@@ -530,6 +556,7 @@ __global__ void __launch_bounds__(256) row_scores_kernel(const float* __restrict
   }
 }
 
+template <typename T>
 __global__ void __launch_bounds__(256) agg_large_kernel(AggLargeP p) {
   const int lane = threadIdx.x & 31;
   const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -539,7 +566,7 @@ __global__ void __launch_bounds__(256) agg_large_kernel(AggLargeP p) {
   for (long long g = w; g < total; g += nw) {
     const long long s = g / p.R;
     const int i = (int)(g % p.R);
-    const float* hb = p.h + s * p.R * E;
+    const T* hb = static_cast<const T*>(p.h) + s * p.R * E;
     const int beg = p.row_ptr[i], end = p.row_ptr[i + 1];
     float mx = -INFINITY, si = 0.f;
     if (p.gat) {
@@ -572,7 +599,7 @@ __global__ void __launch_bounds__(256) agg_large_kernel(AggLargeP p) {
           const float wv = __shfl_sync(0xffffffffu, wj, u);
           const int j = __shfl_sync(0xffffffffu, cj, u);
           if (c < E) {
-            const float4 hv = __ldg(reinterpret_cast<const float4*>(hb + (size_t)j * E + c));
+            const float4 hv = ld4(hb + (size_t)j * E + c);
             acc.x = fmaf(wv, hv.x, acc.x); acc.y = fmaf(wv, hv.y, acc.y);
             acc.z = fmaf(wv, hv.z, acc.z); acc.w = fmaf(wv, hv.w, acc.w);
           }
@@ -588,7 +615,7 @@ __global__ void __launch_bounds__(256) agg_large_kernel(AggLargeP p) {
         float4 v;
         v.x = apply_act(acc.x + bb.x, p.act); v.y = apply_act(acc.y + bb.y, p.act);
         v.z = apply_act(acc.z + bb.z, p.act); v.w = apply_act(acc.w + bb.w, p.act);
-        *reinterpret_cast<float4*>(p.out + (s * p.R + i) * E + c) = v;
+        st4(static_cast<T*>(p.out) + (s * p.R + i) * E + c, v);
       }
     }
   }
@@ -600,14 +627,15 @@ __global__ void __launch_bounds__(256) agg_large_kernel(AggLargeP p) {
 // One CTA owns 32 (b,n) sequences; R (H x 3H) lives in shared memory.
 // ---------------------------------------------------------------------------
 struct GruP {
-  const float* mx;       // (Bc, Ts, Nn, 3H)
+  const void* mx;        // (Bc, Ts, Nn, 3H) storage type T
   const float* R;        // (H, 3H)
   const float* b1;       // (3H) recurrent bias
-  float* out;            // (Bc, Td, Nn, H) last Td steps
+  void* out;             // (Bc, Td, Nn, H) last Td steps
   long long nseq;        // Bc*Nn
   int Nn, Ts, Td, H;
 };
 
+template <typename T>
 __global__ void __launch_bounds__(256) gru_kernel(GruP p) {
   extern __shared__ __align__(16) float sm[];
   const int H = p.H, G = 3 * H;
@@ -642,15 +670,15 @@ __global__ void __launch_bounds__(256) gru_kernel(GruP p) {
     }
     __syncthreads();
     if (live) {
-      const float* mxr = p.mx + ((b * p.Ts + t) * p.Nn + n) * G;
+      const T* mxr = static_cast<const T*>(p.mx) + ((b * p.Ts + t) * p.Nn + n) * G;
       for (int u = gg; u < H; u += 8) {
-        const float z = 1.f / (1.f + expf(-(mxr[u] + mh[rr * G + u])));
-        const float r = 1.f / (1.f + expf(-(mxr[H + u] + mh[rr * G + H + u])));
-        const float hh = tanhf(mxr[2 * H + u] + r * mh[rr * G + 2 * H + u]);
+        const float z = 1.f / (1.f + expf(-(ld1(mxr + u) + mh[rr * G + u])));
+        const float r = 1.f / (1.f + expf(-(ld1(mxr + H + u) + mh[rr * G + H + u])));
+        const float hh = tanhf(ld1(mxr + 2 * H + u) + r * mh[rr * G + 2 * H + u]);
         const float hn = z * hs[rr * H + u] + (1.f - z) * hh;
         hs[rr * H + u] = hn;
         const int td = t - (p.Ts - p.Td);
-        if (td >= 0) p.out[((b * p.Td + td) * p.Nn + n) * H + u] = hn;
+        if (td >= 0) st1(static_cast<T*>(p.out) + ((b * p.Td + td) * p.Nn + n) * H + u, hn);
       }
     }
     __syncthreads();
@@ -659,9 +687,10 @@ __global__ void __launch_bounds__(256) gru_kernel(GruP p) {
 
 // K6 LSTM recurrence (keras LSTM v2; gate order i,f,c,o): zx = x_t@K + b from rows_gemm.
 struct LstmP {
-  const float* zx; const float* R; float* out; long long nseq; int Nn, Ts, Td, H;
+  const void* zx; const float* R; void* out; long long nseq; int Nn, Ts, Td, H;   // zx/out storage type T
 };
 
+template <typename T>
 __global__ void __launch_bounds__(256) lstm_kernel(LstmP p) {
   extern __shared__ __align__(16) float sm[];
   const int H = p.H, G = 4 * H;
@@ -694,17 +723,17 @@ __global__ void __launch_bounds__(256) lstm_kernel(LstmP p) {
     }
     __syncthreads();
     if (live) {
-      const float* zr = p.zx + ((b * p.Ts + t) * p.Nn + n) * G;
+      const T* zr = static_cast<const T*>(p.zx) + ((b * p.Ts + t) * p.Nn + n) * G;
       for (int u = gg; u < H; u += 8) {
-        const float ig = 1.f / (1.f + expf(-(zr[u] + mh[rr * G + u])));
-        const float fg = 1.f / (1.f + expf(-(zr[H + u] + mh[rr * G + H + u])));
-        const float cg = tanhf(zr[2 * H + u] + mh[rr * G + 2 * H + u]);
-        const float og = 1.f / (1.f + expf(-(zr[3 * H + u] + mh[rr * G + 3 * H + u])));
+        const float ig = 1.f / (1.f + expf(-(ld1(zr + u) + mh[rr * G + u])));
+        const float fg = 1.f / (1.f + expf(-(ld1(zr + H + u) + mh[rr * G + H + u])));
+        const float cg = tanhf(ld1(zr + 2 * H + u) + mh[rr * G + 2 * H + u]);
+        const float og = 1.f / (1.f + expf(-(ld1(zr + 3 * H + u) + mh[rr * G + 3 * H + u])));
         const float cn = fg * cs[rr * H + u] + ig * cg;
         const float hn = og * tanhf(cn);
         cs[rr * H + u] = cn; hs[rr * H + u] = hn;
         const int td = t - (p.Ts - p.Td);
-        if (td >= 0) p.out[((b * p.Td + td) * p.Nn + n) * H + u] = hn;
+        if (td >= 0) st1(static_cast<T*>(p.out) + ((b * p.Td + td) * p.Nn + n) * H + u, hn);
       }
     }
     __syncthreads();
@@ -714,8 +743,9 @@ __global__ void __launch_bounds__(256) lstm_kernel(LstmP p) {
 // ---------------------------------------------------------------------------
 // K8 resnet: x = act(cumsum_t(x_out) + res) in place (emulator.py:315-320).
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) cumsum_res_act_kernel(float* __restrict__ x, const float* __restrict__ res,
-                                                             long long Bc, int T, int Nn, int E, int act) {
+template <typename T>
+__global__ void __launch_bounds__(256) cumsum_res_act_kernel(T* __restrict__ x, const float* __restrict__ res,
+                                                             long long Bc, int Tn, int Nn, int E, int act) {
   const int e4 = E >> 2;
   const long long total = Bc * Nn * e4;
   for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total;
@@ -726,27 +756,28 @@ __global__ void __launch_bounds__(256) cumsum_res_act_kernel(float* __restrict__
     const long long b = bn / Nn;
     const float4 r = *reinterpret_cast<const float4*>(res + bn * E + c4 * 4);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int t = 0; t < T; ++t) {
-      float* ptr = x + ((b * T + t) * Nn + n) * E + c4 * 4;
-      const float4 v = *reinterpret_cast<const float4*>(ptr);
+    for (int t = 0; t < Tn; ++t) {
+      T* ptr = x + ((b * Tn + t) * Nn + n) * E + c4 * 4;
+      const float4 v = ld4(ptr);
       acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
       float4 o;
       o.x = apply_act(acc.x + r.x, act); o.y = apply_act(acc.y + r.y, act);
       o.z = apply_act(acc.z + r.z, act); o.w = apply_act(acc.w + r.w, act);
-      *reinterpret_cast<float4*>(ptr) = o;
+      st4(ptr, o);
     }
   }
 }
 
 // K8 narrow heads (n_out<=4 columns): one warp per row.
 struct HeadP {
-  const float* in; int ld; int K;
+  const void* in; int ld; int K;   // storage type T
   const float* W;       // (K, Nout)
   const float* bias;
   float* out; int ldo; int col0; int Nout; int act;
   long long rows;
 };
 
+template <typename T>
 __global__ void __launch_bounds__(256) head_kernel(HeadP p) {
   extern __shared__ float sm[];
   float* Ws = sm;
@@ -758,7 +789,7 @@ __global__ void __launch_bounds__(256) head_kernel(HeadP p) {
   for (long long r = w; r < p.rows; r += nw) {
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     for (int k = lane; k < p.K; k += 32) {
-      const float v = p.in[r * p.ld + k];
+      const float v = ld1(static_cast<const T*>(p.in) + r * p.ld + k);
       for (int o = 0; o < p.Nout; ++o) acc[o] = fmaf(v, Ws[k * p.Nout + o], acc[o]);
     }
     for (int o = 0; o < p.Nout; ++o) {
