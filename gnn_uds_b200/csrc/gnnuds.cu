@@ -580,8 +580,12 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
 // contraction on tcgen05 (csrc/tc_gemm.cuh), the GCN/GAT aggregation fused into the epilogue
 // of the conv GEMM when a sample's rows fit one CTA tile.
 // =========================================================================================
-struct AggArgs { int kind = 0; int R = 0; const int* rp = nullptr; const int* ci = nullptr; const float* val = nullptr;
+struct AggArgs { int kind = 0; int R = 0; int nnz = 0; const int* rp = nullptr; const int* ci = nullptr; const float* val = nullptr;
                  const float* a_self = nullptr; const float* a_neigh = nullptr; };
+
+uint32_t tc_agg_scratch_bytes(int MT, int Nout, int g, int R, int nnz, bool gat) {
+  return (uint32_t)(5 * 128 * MT + 3 * Nout + (gat ? g * nnz : nnz) + (R + 1) + nnz + 8) * 4u;
+}
 
 int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor, const float* bias, void* out, int ldo,
                    int Nout, int act, long long Bc, int Nn, int Td, int Ts, int pitch_d, int off_d,
@@ -605,6 +609,7 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
   const long long rows = Bc * Td * Nn;
   if (rows == 0) return 0;
   if (rows >= (1ll << 31)) return fail(h, GNNUDS_E_INVALID, "tc_gemm: %lld rows exceed the 32-bit row index", rows);
+  if (Nn >= (1 << 20) || Ts >= 4096) return fail(h, GNNUDS_E_INVALID, "tc_gemm: Nn %d / Ts %d exceed the packed row coordinates", Nn, Ts);
   p.Wimg = h->d_wimg + h->img_off[w_tensor];
   p.bias = bias; p.out = static_cast<bf16*>(out); p.ldo = ldo;
   p.Nout = Nout; p.Ktot = Ktot; p.kc = kc; p.act = act;
@@ -613,7 +618,8 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
     const int R = agg->R;
     const int g = R <= 128 ? 128 / R : 1;
     p.rpt = g * R; p.MT = (p.rpt + 127) / 128;
-    p.agg = agg->kind; p.R = R; p.hs = Nout + 4;
+    p.agg = agg->kind; p.R = R; p.hsb = (Nout + 8) * 2; p.nnz = agg->nnz;
+    if (Nout % 64) return fail(h, GNNUDS_E_INVALID, "tc_gemm: aggregation epilogue needs embed_size %% 64 == 0");
     p.row_ptr = agg->rp; p.col_idx = agg->ci; p.val = agg->val; p.a_self = agg->a_self; p.a_neigh = agg->a_neigh;
     if (!bias) return fail(h, GNNUDS_E_INVALID, "tc_gemm: aggregation epilogue needs the conv bias");
     if (Nn != R || pitch_d != Nn || off_d != 0) return fail(h, GNNUDS_E_INVALID, "tc_gemm: aggregation needs sample-contiguous rows");
@@ -623,11 +629,11 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
   if (p.MT * Nout > 256) return fail(h, GNNUDS_E_INVALID, "tc_gemm: accumulator tile %d x %d exceeds TMEM stage", p.MT * 128, Nout);
   p.n_tiles = (unsigned)((rows + p.rpt - 1) / p.rpt);
   p.w_bytes = (uint32_t)Ktot * Nout * 2;
-  p.pstrideA = (uint32_t)(128 * p.MT + 1) * 16u;
+  p.pstrideA = (uint32_t)(128 * p.MT) * 16u;
   p.stage_bytes = 8u * p.pstrideA;
   p.stage_off = (p.w_bytes + 127u) & ~127u;
-  const uint32_t h_bytes = p.agg ? (((uint32_t)p.rpt * p.hs * 4u + 127u) & ~127u) : 0u;
-  const uint32_t sc_bytes = p.agg ? (uint32_t)(4 * 128 * p.MT + 2 * Nout) * 4u : 0u;
+  const uint32_t h_bytes = p.agg ? (((uint32_t)p.rpt * p.hsb + 127u) & ~127u) : 0u;
+  const uint32_t sc_bytes = p.agg ? tc_agg_scratch_bytes(p.MT, Nout, p.rpt / p.R, p.R, p.nnz, p.agg == 2) : (uint32_t)Nout * 4u;
   const uint32_t fixed = p.stage_off + h_bytes + sc_bytes + 256u;
   const uint32_t cap = 227u * 1024u;
   if (fixed + 3u * p.stage_bytes > cap) return fail(h, GNNUDS_E_INVALID, "tc_gemm: tile does not fit shared memory");
@@ -706,7 +712,7 @@ int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const float*
 
 // conv (GCN/GAT) over `segs`: linear part on tensor cores, aggregation fused when the sample fits a tile
 int run_conv_tc(gnnuds_handle* h, const std::vector<SegH>& segs, const LayerW& w, float* out, const int* rp, const int* ci,
-                const float* val, long long Bc, int T, int R, int act) {
+                const float* val, int nnz, long long Bc, int T, int R, int act) {
   const auto& c = h->c;
   const int E = c.embed;
   const bool gat = c.conv == GNNUDS_CONV_GAT;
@@ -715,11 +721,11 @@ int run_conv_tc(gnnuds_handle* h, const std::vector<SegH>& segs, const LayerW& w
   const int MT = (g * R + 127) / 128;
   int Ktot = 0;
   for (const auto& sg : segs) Ktot += sg.width;
-  const size_t need = (((size_t)Ktot * E * 2 + 127) & ~(size_t)127) + (((size_t)g * R * (E + 4) * 4 + 127) & ~(size_t)127) +
-                      (size_t)(4 * 128 * MT + 2 * E) * 4 + 256 + 3 * 8 * (size_t)(128 * MT + 1) * 16;
-  if (MT * E <= 256 && need <= 227 * 1024) {
+  const size_t need = (((size_t)Ktot * E * 2 + 127) & ~(size_t)127) + (((size_t)g * R * (E + 8) * 2 + 127) & ~(size_t)127) +
+                      tc_agg_scratch_bytes(MT, E, g, R, nnz, gat) + 256 + 3 * 8 * (size_t)(128 * MT) * 16;
+  if (MT * E <= 256 && E % 64 == 0 && need <= 227 * 1024) {
     AggArgs a;
-    a.kind = gat ? 2 : 1; a.R = R; a.rp = rp; a.ci = ci; a.val = val;
+    a.kind = gat ? 2 : 1; a.R = R; a.nnz = nnz; a.rp = rp; a.ci = ci; a.val = val;
     a.a_self = gat ? W(h, w.t[1]) : nullptr; a.a_neigh = gat ? W(h, w.t[2]) : nullptr;
     return launch_tc_gemm(h, segs, w.t[0], bias, out, E, E, act, Bc, R, T, T, R, 0, &a);
   }
@@ -745,8 +751,8 @@ int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) 
     std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
     float* xo = (l & 1) ? h->XB : h->XA;
     float* eo = (l & 1) ? h->EB : h->EA;
-    if ((rc = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, Bc, T, N, act))) return rc;
-    if ((rc = run_conv_tc(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, Bc, T, M, act))) return rc;
+    if ((rc = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return rc;
+    if ((rc = run_conv_tc(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, Bc, T, M, act))) return rc;
     st.x = {{xo, E, E, 0, N, 0}};
     st.e = {{eo, E, E, 0, M, 0}};
     if (h->debug_stop == (blk ? 40 : 20) + l) return 1;

@@ -13,7 +13,7 @@
 //                           spektral GCN/GAT neighbour aggregation on the tile's h = x@W kept
 //                           in shared memory (h never goes to HBM)
 //   warps 8..11  producers  cp.async gathers of 128*MT rows x kc columns into the panel layout
-//                           of umma.cuh, NS-stage ring, fence.proxy.async + mbarrier hand-over
+//                           of umma.cuh, NS-stage ring, completion signalled by cp.async.mbarrier.arrive
 //   warp  12     MMA issuer one thread: tcgen05.mma (M=128, N=Nout, K=16), weights resident in
 //                           shared memory as a K-major bf16 image fetched once by a bulk copy;
 //                           accumulators double-buffered in TMEM so tile i's epilogue overlaps
@@ -29,7 +29,6 @@ namespace gu {
 constexpr int TC_EPI_WARPS = 8;
 constexpr int TC_PROD_WARPS = 4;
 constexpr int TC_THREADS = (TC_EPI_WARPS + TC_PROD_WARPS + 1) * 32;   // 416
-constexpr int TC_LAG = 2;                                             // cp.async groups in flight per producer thread
 
 struct TcSeg { const bf16* p; int ld, width, shift, pitch, off; };
 
@@ -43,7 +42,7 @@ struct TcGemmP {
   int rpt, MT; unsigned n_tiles; int NS;
   uint32_t w_bytes, stage_bytes, pstrideA, stage_off, h_off, sc_off, bar_off;
   // aggregation epilogue (agg: 0 none, 1 GCN, 2 GAT) over samples of R rows
-  int agg, R, hs;            // hs = row stride of the fp32 h tile in floats (Nout + 4)
+  int agg, R, hsb, nnz;      // hsb = row stride in bytes of the bf16 h tile ((Nout + 8) * 2)
   const int* row_ptr; const int* col_idx; const float* val;
   const float* a_self; const float* a_neigh;
 };
@@ -52,13 +51,56 @@ __device__ __forceinline__ void cp_async16(void* dst_smem, const void* src, uint
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(tc::smem_u32(dst_smem)), "l"(src), "r"(src_bytes)
                : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void cp_async16_full(void* dst_smem, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tc::smem_u32(dst_smem)), "l"(src) : "memory");
+}
+// one arrival on `bar` when all cp.async issued so far by this thread have landed (no wait, no extra count)
+__device__ __forceinline__ void cp_async_arrive(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(tc::smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc::smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_WARPS * 32) : "memory"); }
+
+// activation over a register tile; the branch is warp-uniform and sits outside the element loop
+template <int N>
+__device__ __forceinline__ void act_tile(float* v, int act) {
+  if (act == ACT_RELU) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] = fmaxf(v[i], 0.f);
+  } else if (act != ACT_LINEAR) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] = apply_act(v[i], act);
+  }
+}
+
+// NC (multiple of 16) consecutive fp32 accumulator columns of this thread's TMEM lane; all loads in flight, one wait
+template <int NC>
+__device__ __forceinline__ void tmem_load_cols(uint32_t taddr, float* v) {
+#pragma unroll
+  for (int i = 0; i < NC; i += 16) tc::tmem_ld16(taddr + (uint32_t)i, v + i);
+  tc::tmem_ld_wait();
+}
+
+// plain epilogue of NC columns: bias + activation -> bf16 -> HBM
+template <int NC>
+__device__ __forceinline__ void epi_store_cols(uint32_t taddr, int c0, bool valid, bf16* orow, const float* bias_s, int act) {
+  float v[NC];
+  tmem_load_cols<NC>(taddr + (uint32_t)c0, v);
+  if (valid) {
+#pragma unroll
+    for (int i = 0; i < NC; i += 4) {
+      const float4 bb = *reinterpret_cast<const float4*>(bias_s + c0 + i);
+      v[i] += bb.x; v[i + 1] += bb.y; v[i + 2] += bb.z; v[i + 3] += bb.w;
+    }
+    act_tile<NC>(v, act);
+#pragma unroll
+    for (int i = 0; i < NC; i += 8)
+      *reinterpret_cast<uint4*>(orow + c0 + i) = make_uint4(pack2_bf16(v[i], v[i + 1]), pack2_bf16(v[i + 2], v[i + 3]),
+                                                            pack2_bf16(v[i + 4], v[i + 5]), pack2_bf16(v[i + 6], v[i + 7]));
+  }
+}
 
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_constant__ TcGemmP p) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -91,49 +133,61 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
 
   if (warp >= TC_EPI_WARPS && warp < TC_EPI_WARPS + TC_PROD_WARPS) {
     // ================================ producers ================================
+    // one producer thread owns row (ptid + 128*m) of every M-tile: per stage it computes one source
+    // address per row and issues kc/8 cp.async of 16 bytes (a warp instruction writes 512 contiguous
+    // bytes of one panel); the row's (b,t,n) is worked out once per tile
     const int ptid = tid - TC_EPI_WARPS * 32;
     const int cpr = p.kc >> 3;                 // 16-byte chunks per row per stage (4 or 8)
-    const int rstep = (TC_PROD_WARPS * 32) / cpr;
-    const int c = ptid % cpr, r0 = ptid / cpr;
-    const int npass = (128 * p.MT) / rstep;
-    unsigned it = 0;
+    int stage = 0;
+    uint32_t ephase = 1;                       // parity to wait for on empty[]: passes at once on the first lap
+    uint32_t tq[2], tn[2];                     // per owned row: b*Ts + t + (Ts-Td) (~0 = no such row), (t << 20) | n
     for (unsigned tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
       const unsigned row_base = tile * (unsigned)p.rpt;
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        const int rloc = ptid + 128 * m;
+        const unsigned rl = row_base + rloc;
+        tq[m] = 0xFFFFFFFFu; tn[m] = 0;
+        if (m < p.MT && rloc < p.rpt && rl < p.rows) {
+          const unsigned n = rl % p.Nn, bt = rl / p.Nn;
+          const unsigned t = bt % p.Td, b = bt / p.Td;
+          tq[m] = b * p.Ts + t + (unsigned)(p.Ts - p.Td);
+          tn[m] = (t << 20) | n;
+        }
+      }
       for (int s = 0; s < p.nseg; ++s) {
         const TcSeg sg = p.seg[s];
-        for (int k0 = 0; k0 < sg.width; k0 += p.kc, ++it) {
-          const int stage = it % NS;
-          if (it >= (unsigned)NS) tc::mbar_wait(&empty[stage], ((it / NS) & 1) ^ 1);
-          uint8_t* sb = stages + (size_t)stage * p.stage_bytes + (size_t)c * p.pstrideA;
-          for (int i = 0; i < npass; ++i) {
-            const int rloc = r0 + i * rstep;
-            const unsigned rl = row_base + rloc;
-            const bf16* src = sg.p;
-            uint32_t nb = 0;
-            if (rloc < p.rpt && rl < p.rows) {
-              const unsigned n = rl % p.Nn, bt = rl / p.Nn;
-              const int t = bt % p.Td;
-              const unsigned b = bt / p.Td;
-              const int ts = t + (p.Ts - p.Td) - sg.shift;
-              if (ts >= 0) {
-                src = sg.p + ((size_t)(b * p.Ts + ts) * sg.pitch + sg.off + n) * sg.ld + k0 + c * 8;
-                nb = 16;
+        const int tofs = (p.Ts - p.Td) - sg.shift;
+        const bf16* rp[2];
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          const bool ok = tq[m] != 0xFFFFFFFFu && (int)(tn[m] >> 20) + tofs >= 0;
+          const size_t row = (size_t)(tq[m] - (unsigned)sg.shift) * (unsigned)sg.pitch + (unsigned)sg.off + (tn[m] & 0xFFFFFu);
+          rp[m] = ok ? sg.p + row * (unsigned)sg.ld : nullptr;
+        }
+        for (int k0 = 0; k0 < sg.width; k0 += p.kc) {
+          tc::mbar_wait(&empty[stage], ephase);
+          uint8_t* sb = stages + (size_t)stage * p.stage_bytes + ptid * 16;
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            if (m < p.MT) {
+              if (rp[m]) {
+                const bf16* src = rp[m] + k0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (j < cpr) cp_async16_full(sb + m * 2048 + j * p.pstrideA, src + j * 8);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (j < cpr) cp_async16(sb + m * 2048 + j * p.pstrideA, sg.p, 0u);
               }
             }
-            cp_async16(sb + rloc * 16, src, nb);
           }
-          cp_async_commit();
-          if (it >= TC_LAG) {
-            cp_async_wait<TC_LAG>();
-            tc::fence_async_smem();
-            mbar_arrive(&full[(it - TC_LAG) % NS]);
-          }
+          cp_async_arrive(&full[stage]);
+          if (++stage == NS) { stage = 0; ephase ^= 1; }
         }
       }
     }
-    cp_async_wait<0>();
-    tc::fence_async_smem();
-    for (unsigned j = it > TC_LAG ? it - TC_LAG : 0; j < it; ++j) mbar_arrive(&full[j % NS]);
   } else if (warp == TC_EPI_WARPS + TC_PROD_WARPS) {
     // ================================ MMA issuer ================================
     if (lane == 0) {
@@ -146,15 +200,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
       const uint32_t idesc = tc::idesc_bf16(128, p.Nout, 0, 0);
       const uint32_t w_addr = tc::smem_u32(Wsm), st_addr = tc::smem_u32(stages);
       const uint32_t pstrideW = (uint32_t)p.Nout * 16u;
-      unsigned it = 0, tile_it = 0;
+      unsigned tile_it = 0;
+      int stage = 0;
+      uint32_t fphase = 0;
       for (unsigned tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++tile_it) {
         const int as = tile_it & 1;
         if (tile_it >= 2) tc::mbar_wait(&tempty[as], ((tile_it >> 1) & 1) ^ 1);
         tc::tc_fence_after();
         const uint32_t acc = tmem + (uint32_t)as * 256u;
-        for (int ch = 0; ch < nchunk; ++ch, ++it) {
-          const int stage = it % NS;
-          tc::mbar_wait(&full[stage], (it / NS) & 1);
+        for (int ch = 0; ch < nchunk; ++ch) {
+          tc::mbar_wait(&full[stage], fphase);
+          tc::fence_async_smem();              // cp.async (generic proxy) writes -> tensor-core (async proxy) reads
           tc::tc_fence_after();
           const uint32_t sa = st_addr + (uint32_t)stage * p.stage_bytes;
           for (int ks = 0; ks < p.kc / 16; ++ks) {
@@ -166,6 +222,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
             }
           }
           tc::umma_commit(&empty[stage]);
+          if (++stage == NS) { stage = 0; fphase ^= 1; }
         }
         tc::umma_commit(&tfull[as]);
       }
@@ -175,14 +232,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
     const int q = warp & 3, hf = warp >> 2;
     const int half = p.Nout >> 1;
     const int RP = 128 * p.MT;
-    float* ssp = scbuf;                 // [2][RP]
-    float* snp = scbuf + 2 * RP;        // [2][RP]
-    float* asf = scbuf + 4 * RP;        // [Nout]
-    float* anf = asf + p.Nout;          // [Nout]
-    if (p.agg == 2) {
-      for (int i = tid; i < p.Nout; i += TC_EPI_WARPS * 32) { asf[i] = p.a_self[i]; anf[i] = p.a_neigh[i]; }
-      epi_bar_sync();
+    // score/graph scratch (agg): ssp[2][RP] snp[2][RP] asf[Nout] anf[Nout] inv[RP] alpha[g*nnz] | rp_s[R+1] ci_s[nnz]
+    float* bias_s = scbuf;              // [Nout], zeros when the layer has no bias
+    float* ssp = scbuf + p.Nout;
+    float* snp = ssp + 2 * RP;
+    float* asf = ssp + 4 * RP;
+    float* anf = asf + p.Nout;
+    float* inv_s = anf + p.Nout;
+    float* alpha = inv_s + RP;
+    const int gsamp = p.agg ? p.rpt / p.R : 0;
+    int* rp_s = reinterpret_cast<int*>(alpha + (p.agg == 2 ? gsamp * p.nnz : p.nnz));
+    int* ci_s = rp_s + p.R + 1;
+    for (int i = tid; i < p.Nout; i += TC_EPI_WARPS * 32) bias_s[i] = p.bias ? p.bias[i] : 0.f;
+    if (p.agg) {
+      for (int i = tid; i <= p.R; i += TC_EPI_WARPS * 32) rp_s[i] = p.row_ptr[i];
+      for (int i = tid; i < p.nnz; i += TC_EPI_WARPS * 32) { ci_s[i] = p.col_idx[i]; if (p.agg == 1) alpha[i] = p.val[i]; }
+      if (p.agg == 2)
+        for (int i = tid; i < p.Nout; i += TC_EPI_WARPS * 32) { asf[i] = p.a_self[i]; anf[i] = p.a_neigh[i]; }
     }
+    epi_bar_sync();
     unsigned tile_it = 0;
     for (unsigned tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++tile_it) {
       const int as = tile_it & 1;
@@ -199,6 +267,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
           const unsigned rl = row_base + rloc;
           const size_t rr = (size_t)(rl / p.Nn) * p.pitch_d + p.off_d + rl % p.Nn;
           bf16* orow = p.out + rr * p.ldo;
+          const int c0 = hf * half;
+          switch (half) {                                          // warp-uniform
+            case 16: epi_store_cols<16>(ta, c0, valid, orow, bias_s, p.act); break;
+            case 32: epi_store_cols<32>(ta, c0, valid, orow, bias_s, p.act); break;
+            case 64: epi_store_cols<64>(ta, c0, valid, orow, bias_s, p.act); break;
+            case 96: epi_store_cols<48>(ta, c0, valid, orow, bias_s, p.act); epi_store_cols<48>(ta, c0 + 48, valid, orow, bias_s, p.act); break;
+            case 128: epi_store_cols<64>(ta, c0, valid, orow, bias_s, p.act); epi_store_cols<64>(ta, c0 + 64, valid, orow, bias_s, p.act); break;
+            default:
+              for (int c = c0; c < c0 + half; c += 16) epi_store_cols<16>(ta, c, valid, orow, bias_s, p.act);
+          }
+        } else {
+          // h tile -> shared memory as bf16 rows; attention scores from the fp32 accumulators
+          float ps = 0.f, pn = 0.f;
+          uint8_t* hrow = reinterpret_cast<uint8_t*>(hbuf) + (size_t)rloc * p.hsb;
           for (int c0 = hf * half; c0 < (hf + 1) * half; c0 += 16) {
             float v[16];
             tc::tmem_ld16(ta + (uint32_t)c0, v);
@@ -206,26 +288,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
             if (valid) {
               uint32_t w[8];
 #pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                float a = v[2 * i], b = v[2 * i + 1];
-                if (p.bias) { a += p.bias[c0 + 2 * i]; b += p.bias[c0 + 2 * i + 1]; }
-                w[i] = pack2_bf16(apply_act(a, p.act), apply_act(b, p.act));
-              }
-              *reinterpret_cast<uint4*>(orow + c0) = make_uint4(w[0], w[1], w[2], w[3]);
-              *reinterpret_cast<uint4*>(orow + c0 + 8) = make_uint4(w[4], w[5], w[6], w[7]);
-            }
-          }
-        } else {
-          float ps = 0.f, pn = 0.f;
-          for (int c0 = hf * half; c0 < (hf + 1) * half; c0 += 16) {
-            float v[16];
-            tc::tmem_ld16(ta + (uint32_t)c0, v);
-            tc::tmem_ld_wait();
-            if (valid) {
-              float* hr = hbuf + (size_t)rloc * p.hs + c0;
-#pragma unroll
-              for (int i = 0; i < 4; ++i)
-                *reinterpret_cast<float4*>(hr + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+              for (int i = 0; i < 8; ++i) w[i] = pack2_bf16(v[2 * i], v[2 * i + 1]);
+              *reinterpret_cast<uint4*>(hrow + c0 * 2) = make_uint4(w[0], w[1], w[2], w[3]);
+              *reinterpret_cast<uint4*>(hrow + c0 * 2 + 16) = make_uint4(w[4], w[5], w[6], w[7]);
               if (p.agg == 2) {
 #pragma unroll
                 for (int i = 0; i < 16; ++i) { ps = fmaf(v[i], asf[c0 + i], ps); pn = fmaf(v[i], anf[c0 + i], pn); }
@@ -239,67 +304,68 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
       mbar_arrive(&tempty[as]);
       if (p.agg) {
         epi_bar_sync();
-        // neighbour aggregation: one warp per output row, lanes over features (float4)
-        const int E = p.Nout;
-        for (int rloc = warp; rloc < nvalid; rloc += TC_EPI_WARPS) {
-          const int s = rloc / p.R, i = rloc - s * p.R;
-          const int beg = p.row_ptr[i], end = p.row_ptr[i + 1];
-          const float* hb = hbuf + (size_t)s * p.R * p.hs;
-          float mx = -INFINITY, si = 0.f;
-          if (p.agg == 2) {
-            si = ssp[rloc] + ssp[RP + rloc];
-            for (int qq = beg + lane; qq < end; qq += 32) {
-              const int j = s * p.R + p.col_idx[qq];
-              float sc = si + snp[j] + snp[RP + j];
+        const int R = p.R;
+        if (p.agg == 2) {
+          // edge softmax: one thread per row over its <= few dozen neighbours
+          for (int rloc = tid; rloc < nvalid; rloc += TC_EPI_WARPS * 32) {
+            int s = 0, i = rloc;
+            while (i >= R) { i -= R; ++s; }
+            const int beg = rp_s[i], end = rp_s[i + 1];
+            const float si = ssp[rloc] + ssp[RP + rloc];
+            const float* sn0 = snp + s * R;
+            float mx = -INFINITY;
+            for (int qq = beg; qq < end; ++qq) {
+              const int j = ci_s[qq];
+              float sc = si + sn0[j] + sn0[RP + j];
               sc = sc > 0.f ? sc : 0.2f * sc;
               mx = fmaxf(mx, sc);
             }
-            mx = warp_max(mx);
-          }
-          const unsigned rl = row_base + rloc;
-          const size_t rr = (size_t)(rl / p.Nn) * p.pitch_d + p.off_d + rl % p.Nn;
-          for (int c0 = 0; c0 < E; c0 += 128) {
-            const int c = c0 + lane * 4;
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
             float den = 0.f;
-            for (int q0 = beg; q0 < end; q0 += 32) {
-              const int qq = q0 + lane;
-              int cj = 0; float wj = 0.f;
-              if (qq < end) {
-                cj = p.col_idx[qq];
-                if (p.agg == 2) {
-                  const int j = s * p.R + cj;
-                  float sc = si + snp[j] + snp[RP + j];
-                  sc = sc > 0.f ? sc : 0.2f * sc;
-                  wj = expf(sc - mx);
-                } else {
-                  wj = p.val[qq];
-                }
-              }
-              if (p.agg == 2) den += wj;
-              const int cnt = min(32, end - q0);
-              for (int u = 0; u < cnt; ++u) {
-                const float w = __shfl_sync(0xffffffffu, wj, u);
-                const int j = __shfl_sync(0xffffffffu, cj, u);
-                if (c < E) {
-                  const float4 hv = *reinterpret_cast<const float4*>(hb + (size_t)j * p.hs + c);
-                  acc.x = fmaf(w, hv.x, acc.x); acc.y = fmaf(w, hv.y, acc.y);
-                  acc.z = fmaf(w, hv.z, acc.z); acc.w = fmaf(w, hv.w, acc.w);
-                }
-              }
+            float* al = alpha + s * p.nnz;
+            for (int qq = beg; qq < end; ++qq) {
+              const int j = ci_s[qq];
+              float sc = si + sn0[j] + sn0[RP + j];
+              sc = sc > 0.f ? sc : 0.2f * sc;
+              const float w = __expf(sc - mx);
+              al[qq] = w;
+              den += w;
             }
-            if (p.agg == 2) {
-              den = warp_sum(den);
-              const float inv = 1.f / den;
-              acc.x *= inv; acc.y *= inv; acc.z *= inv; acc.w *= inv;
+            inv_s[rloc] = 1.f / den;
+          }
+          epi_bar_sync();
+        }
+        // weighted neighbour sum: 8 lanes per output row (E/8 features each), 4 rows per warp pass
+        const int lg = lane >> 3, gl = lane & 7;
+        for (int rloc = warp * 4 + lg; rloc < nvalid; rloc += TC_EPI_WARPS * 4) {
+          int s = 0, i = rloc;
+          while (i >= R) { i -= R; ++s; }
+          const int beg = rp_s[i], end = rp_s[i + 1];
+          const uint8_t* hb = reinterpret_cast<const uint8_t*>(hbuf) + (size_t)s * R * p.hsb + gl * 16;
+          const float* al = alpha + (p.agg == 2 ? s * p.nnz : 0);
+          const float scale = p.agg == 2 ? inv_s[rloc] : 1.f;
+          bf16* orow = p.out + (size_t)(row_base + rloc) * p.ldo + gl * 8;
+          const float* bp = bias_s + gl * 8;
+          // lane gl owns features [64k + 8gl, 64k + 8gl + 8): a lane group reads 128 contiguous bytes
+          for (int e0 = 0; e0 < p.Nout; e0 += 64) {
+            float acc[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+            for (int qq = beg; qq < end; ++qq) {
+              const float w = al[qq];
+              const uint4 u = *reinterpret_cast<const uint4*>(hb + (size_t)ci_s[qq] * p.hsb + e0 * 2);
+              float hv[8];
+              tc::unpack8_bf16(u, hv);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) acc[k] = fmaf(w, hv[k], acc[k]);
             }
-            if (c < E) {
-              const float4 bb = *reinterpret_cast<const float4*>(p.bias + c);
-              float4 v;
-              v.x = apply_act(acc.x + bb.x, p.act); v.y = apply_act(acc.y + bb.y, p.act);
-              v.z = apply_act(acc.z + bb.z, p.act); v.w = apply_act(acc.w + bb.w, p.act);
-              st4(p.out + rr * p.ldo + c, v);
-            }
+            const float4 b0 = *reinterpret_cast<const float4*>(bp + e0), b1 = *reinterpret_cast<const float4*>(bp + e0 + 4);
+            acc[0] = fmaf(acc[0], scale, b0.x); acc[1] = fmaf(acc[1], scale, b0.y);
+            acc[2] = fmaf(acc[2], scale, b0.z); acc[3] = fmaf(acc[3], scale, b0.w);
+            acc[4] = fmaf(acc[4], scale, b1.x); acc[5] = fmaf(acc[5], scale, b1.y);
+            acc[6] = fmaf(acc[6], scale, b1.z); acc[7] = fmaf(acc[7], scale, b1.w);
+            act_tile<8>(acc, p.act);
+            *reinterpret_cast<uint4*>(orow + e0) = make_uint4(pack2_bf16(acc[0], acc[1]), pack2_bf16(acc[2], acc[3]),
+                                                              pack2_bf16(acc[4], acc[5]), pack2_bf16(acc[6], acc[7]));
           }
         }
         epi_bar_sync();
