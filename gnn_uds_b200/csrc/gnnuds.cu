@@ -12,6 +12,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -61,6 +62,7 @@ struct gnnuds_handle {
   std::vector<int64_t> toff;
   uint8_t* d_wimg = nullptr;            // bf16 K-major weight images of every GEMM layer (tensor-core path)
   std::vector<long long> img_off;       // byte offset per tensor index, -1 = no image
+  bool tma_on = true;                   // GNNUDS_NO_TMA=1 forces the cp.async producers (diagnostics)
   bool tc() const { return c.precision == GNNUDS_PREC_BF16_TC; }
   size_t es() const { return tc() ? 2 : 4; }   // bytes per stored activation element
   std::vector<float*> d_ne_matT[2];     // per spatial layer (block*S + l): N-side, M-side folded matrices
@@ -583,6 +585,35 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
 struct AggArgs { int kind = 0; int R = 0; int nnz = 0; const int* rp = nullptr; const int* ci = nullptr; const float* val = nullptr;
                  const float* a_self = nullptr; const float* a_neigh = nullptr; };
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda at link time)
+typedef CUresult (*tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+tmap_encode_fn tmap_encoder() {
+  static tmap_encode_fn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<tmap_encode_fn>(f);
+  }
+  return fn;
+}
+
+// {8 elements, rows, width/8 panels} view of a [rows][ld] bf16 buffer, box {8, boxrows, kc/8}
+bool make_rows_tmap(CUtensorMap* m, const void* base, long long rows, int ld, int width, int boxrows, int kc) {
+  tmap_encode_fn enc = tmap_encoder();
+  if (!enc) return false;
+  cuuint64_t dims[3] = {8, (cuuint64_t)rows, (cuuint64_t)(width / 8)};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, 16};
+  cuuint32_t box[3] = {8, (cuuint32_t)boxrows, (cuuint32_t)(kc / 8)};
+  cuuint32_t es[3] = {1, 1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 uint32_t tc_agg_scratch_bytes(int MT, int Nout, int g, int R, int nnz, bool gat) {
   return (uint32_t)(5 * 128 * MT + 3 * Nout + (gat ? g * nnz : nnz) + (R + 1) + nnz + 8) * 4u;
 }
@@ -629,16 +660,23 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
   if (p.MT * Nout > 256) return fail(h, GNNUDS_E_INVALID, "tc_gemm: accumulator tile %d x %d exceeds TMEM stage", p.MT * 128, Nout);
   p.n_tiles = (unsigned)((rows + p.rpt - 1) / p.rpt);
   p.w_bytes = (uint32_t)Ktot * Nout * 2;
-  p.pstrideA = (uint32_t)(128 * p.MT) * 16u;
+  p.boxrows = std::min(128 * p.MT, (p.rpt + 7) / 8 * 8);
+  p.pstrideA = (uint32_t)p.boxrows * 16u;
   p.stage_bytes = 8u * p.pstrideA;
+  for (int i = 0; i < p.nseg; ++i) {
+    const SegH& sg = segs[i];
+    p.use_tma[i] = 0;
+    if (h->tma_on && sg.shift == 0 && Ts == Td && sg.pitch == Nn && sg.off == 0 && (reinterpret_cast<uintptr_t>(sg.p) & 15) == 0)
+      p.use_tma[i] = make_rows_tmap(&p.tmap[i], sg.p, rows, sg.ld, sg.width, p.boxrows, kc) ? 1 : 0;
+  }
   p.stage_off = (p.w_bytes + 127u) & ~127u;
   const uint32_t h_bytes = p.agg ? (((uint32_t)p.rpt * p.hsb + 127u) & ~127u) : 0u;
   const uint32_t sc_bytes = p.agg ? tc_agg_scratch_bytes(p.MT, Nout, p.rpt / p.R, p.R, p.nnz, p.agg == 2) : (uint32_t)Nout * 4u;
-  const uint32_t fixed = p.stage_off + h_bytes + sc_bytes + 256u;
+  const uint32_t fixed = p.stage_off + h_bytes + sc_bytes + 256u + 4096u;
   const uint32_t cap = 227u * 1024u;
   if (fixed + 3u * p.stage_bytes > cap) return fail(h, GNNUDS_E_INVALID, "tc_gemm: tile does not fit shared memory");
   p.NS = (int)std::min<uint32_t>(8u, (cap - fixed) / p.stage_bytes);
-  p.h_off = p.stage_off + (uint32_t)p.NS * p.stage_bytes;
+  p.h_off = p.stage_off + (uint32_t)p.NS * p.stage_bytes + 4096u;
   p.sc_off = p.h_off + h_bytes;
   p.bar_off = (p.sc_off + sc_bytes + 15u) & ~15u;
   const size_t smem = p.bar_off + (size_t)(2 * p.NS + 6) * 8 + 16;
@@ -722,7 +760,7 @@ int run_conv_tc(gnnuds_handle* h, const std::vector<SegH>& segs, const LayerW& w
   int Ktot = 0;
   for (const auto& sg : segs) Ktot += sg.width;
   const size_t need = (((size_t)Ktot * E * 2 + 127) & ~(size_t)127) + (((size_t)g * R * (E + 8) * 2 + 127) & ~(size_t)127) +
-                      tc_agg_scratch_bytes(MT, E, g, R, nnz, gat) + 256 + 3 * 8 * (size_t)(128 * MT) * 16;
+                      tc_agg_scratch_bytes(MT, E, g, R, nnz, gat) + 256 + 4096 + 3 * 8 * (size_t)std::min(128 * MT, (g * R + 7) / 8 * 8) * 16;
   if (MT * E <= 256 && E % 64 == 0 && need <= 227 * 1024) {
     AggArgs a;
     a.kind = gat ? 2 : 1; a.R = R; a.nnz = nnz; a.rp = rp; a.ci = ci; a.val = val;
@@ -970,6 +1008,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   }
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, c.device);
   cudaEventCreate(&h->ev_a); cudaEventCreate(&h->ev_b);
+  h->tma_on = !(getenv("GNNUDS_NO_TMA") && getenv("GNNUDS_NO_TMA")[0] == '1');
   LayoutBuilder lb{h};
   lb.build();
   *out = h;

@@ -21,6 +21,8 @@
 // A tile is rpt logical rows in MT M-tiles: 128 arbitrary rows (plain), or g whole (b,t)
 // samples of R rows when the epilogue aggregates over the graph.
 #pragma once
+#include <cuda.h>
+
 #include "kernels.cuh"
 #include "umma.cuh"
 
@@ -33,6 +35,12 @@ constexpr int TC_THREADS = (TC_EPI_WARPS + TC_PROD_WARPS + 1) * 32;   // 416
 struct TcSeg { const bf16* p; int ld, width, shift, pitch, off; };
 
 struct TcGemmP {
+  // one tensor map per segment whose rows are contiguous in the tile order (no time shift, no
+  // pitch): {8 elements, rows, C/8 panels} with box {8, boxrows, kc/8}, so a single TMA instruction
+  // lands a whole pipeline stage in the panel layout.  Other segments use the cp.async producers.
+  CUtensorMap tmap[4];
+  int use_tma[4];
+  int boxrows;               // rows per panel in a stage (multiple of 8, >= rows of a tile, <= 256)
   TcSeg seg[4]; int nseg;
   const uint8_t* Wimg;       // bf16 K-major image of W^T: element (n,k) at (k/8)*Nout*16 + n*16 + (k%8)*2
   const float* bias;         // (Nout) or null
@@ -138,6 +146,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
     // bytes of one panel); the row's (b,t,n) is worked out once per tile
     const int ptid = tid - TC_EPI_WARPS * 32;
     const int cpr = p.kc >> 3;                 // 16-byte chunks per row per stage (4 or 8)
+    if (ptid == 0)
+      for (int s = 0; s < p.nseg; ++s) if (p.use_tma[s]) tc::tma_prefetch_desc(&p.tmap[s]);
     int stage = 0;
     uint32_t ephase = 1;                       // parity to wait for on empty[]: passes at once on the first lap
     uint32_t tq[2], tn[2];                     // per owned row: b*Ts + t + (Ts-Td) (~0 = no such row), (t << 20) | n
@@ -167,10 +177,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
         }
         for (int k0 = 0; k0 < sg.width; k0 += p.kc) {
           tc::mbar_wait(&empty[stage], ephase);
+          if (p.use_tma[s]) {
+            if (ptid == 0) {
+              tc::mbar_expect_tx(&full[stage], (uint32_t)p.boxrows * 16u * (uint32_t)cpr);
+              tc::tma_load_3d(stages + (size_t)stage * p.stage_bytes, &p.tmap[s], 0, (int)row_base, k0 >> 3, &full[stage]);
+            } else {
+              mbar_arrive(&full[stage]);
+            }
+            if (++stage == NS) { stage = 0; ephase ^= 1; }
+            continue;
+          }
           uint8_t* sb = stages + (size_t)stage * p.stage_bytes + ptid * 16;
 #pragma unroll
           for (int m = 0; m < 2; ++m) {
-            if (m < p.MT) {
+            if (m < p.MT && ptid + 128 * m < p.boxrows) {
               if (rp[m]) {
                 const bf16* src = rp[m] + k0;
 #pragma unroll
@@ -198,6 +218,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
       }
       tc::mbar_wait(wbar, 0);
       const uint32_t idesc = tc::idesc_bf16(128, p.Nout, 0, 0);
+      bool any_cp = false;
+      for (int s = 0; s < p.nseg; ++s) any_cp |= !p.use_tma[s];
       const uint32_t w_addr = tc::smem_u32(Wsm), st_addr = tc::smem_u32(stages);
       const uint32_t pstrideW = (uint32_t)p.Nout * 16u;
       unsigned tile_it = 0;
@@ -210,7 +232,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
         const uint32_t acc = tmem + (uint32_t)as * 256u;
         for (int ch = 0; ch < nchunk; ++ch) {
           tc::mbar_wait(&full[stage], fphase);
-          tc::fence_async_smem();              // cp.async (generic proxy) writes -> tensor-core (async proxy) reads
+          if (any_cp) tc::fence_async_smem();  // cp.async (generic proxy) writes -> tensor-core (async proxy) reads
           tc::tc_fence_after();
           const uint32_t sa = st_addr + (uint32_t)stage * p.stage_bytes;
           for (int ks = 0; ks < p.kc / 16; ++ks) {
