@@ -26,10 +26,22 @@ WORKLOADS = {
     "C3b": dict(net="astlingen", conv="GAT", recurrent="Conv1D", resnet=True, seq_in=5, seq_out=5, embed_size=128,
                 hidden_dim=64, n_sp_layer=3, n_tp_layer=3, length=1.0, order=1, edge_fusion=True, if_flood=3,
                 act="conti", B=8192, seed=44, chunks=12),
+    # configs[4]: synthetic drainage tree, graph_base=1 joint graph (NodeEdge is impossible at this size),
+    # GCN+GRU, 10->10; act (4 controlled links) so both streams enter block 2 with H+E/2 channels as the
+    # reference's concat on axis -2 needs (emulator.py:273).  HBM-bound CSR gather path.
+    "C5": dict(net="tree:100000", conv="GCN", recurrent="GRU", resnet=True, seq_in=10, seq_out=10, embed_size=128,
+               hidden_dim=64, n_sp_layer=2, n_tp_layer=2, length=0, order=1, graph_base=1, act="conti", B=256, seed=46),
+    "C5s": dict(net="tree:2000", conv="GCN", recurrent="GRU", resnet=True, seq_in=10, seq_out=10, embed_size=128,
+                hidden_dim=64, n_sp_layer=2, n_tp_layer=2, length=0, order=1, graph_base=1, act="conti", B=8, seed=46),
 }
 
 
 def load_net(name):
+    if name.startswith("tree:"):
+        n = int(name.split(":")[1])
+        net = synthetic.random_tree(n, np.random.default_rng(1000 + n))
+        step = max(1, (n - 1) // 4)
+        return net, [net.links[i] for i in range(step // 2, n - 1, step)][:4]
     z = np.load(os.path.join(_GOLD, name + "_net.npz"))
     net = G.Network([str(s) for s in z["nodes"]], [str(s) for s in z["links"]], z["edges"], z["lengths"],
                     z["is_outfall"], z["is_storage"], z["hmax"], z["elevation"], z["ehmax"], z["area"])
@@ -43,8 +55,9 @@ def make_args(name, inp_path=None):
     netname = hp.pop("net")
     net, act_links = load_net(netname) if inp_path is None else (G.Network.from_inp(inp_path), None)
     length, order = hp.pop("length"), hp.pop("order")
-    ga = G.get_args(net, False, length, order, hp.get("graph_base", 0), act_links=act_links if hp.get("act") else None)
-    d = dict(vars(ga)); d.update(hp); d["model_dir"] = None
+    ga = G.get_args(net, False, length, order, hp.get("graph_base", 0), act_links=act_links if hp.get("act") else None,
+                    dense=net.n_node <= 4096)
+    d = dict(vars(ga)); d.update(hp); d["model_dir"] = None; d["env_name"] = netname
     return SimpleNamespace(**d)
 
 

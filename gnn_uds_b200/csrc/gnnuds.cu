@@ -86,7 +86,7 @@ struct gnnuds_handle {
   float* d_ws = nullptr;
   size_t ws_floats = 0;
   float *XA, *XB, *EA, *EB, *HB, *XE, *EX, *NX, *NE, *TX0, *TX1, *TE0, *TE1, *BEMB, *AEMB, *RES, *RESE,
-      *OUTN, *OUTE, *SS, *SN;
+      *OUTN, *OUTE, *SS, *SN, *HBJ = nullptr, *J0 = nullptr, *J1 = nullptr;
   float *in_x, *in_b, *in_a, *in_ex, *out_y, *out_ey;      // chunk staging on device
   // rollout state
   float *ro_x = nullptr, *ro_ex = nullptr, *ro_b = nullptr, *ro_a = nullptr;
@@ -377,12 +377,12 @@ int act_code(const gnnuds_config& c) { return c.activation; }
 
 // ---- temporal stack (emulator.py:154-163) ------------------------------------------------
 // in: (Bc,Ts,Nn,cin) at `src`; result (Bc,Td,Nn,H) in *dst (one of t0/t1).
-int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const float* src, int cin, long long Bc, int Nn,
+int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src, int cin, long long Bc, int Nn,
                  int Ts, int Td, float* t0, float* t1, float** dst) {
   const auto& c = h->c;
   const int H = c.hidden, P = c.n_tp_layer;
-  const float* cur = src;
-  int cw = cin;
+  const float* cur = src.p;
+  int cw = cin, cpitch = src.pitch, coff = src.off;
   float* bufs[2] = {t0, t1};
   for (int i = 0; i < P; ++i) {
     const bool last = (i == P - 1);
@@ -392,14 +392,14 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const float* sr
     if (c.recurrent == GNNUDS_REC_CONV1D) {
       std::vector<SegH> segs;
       const int k = c.kernel_size, d = 1 << i;
-      for (int j = 0; j < k; ++j) segs.push_back({cur, cw, cw, (k - 1 - j) * d, Nn, 0});
+      for (int j = 0; j < k; ++j) segs.push_back({cur, cw, cw, (k - 1 - j) * d, cpitch, coff});
       rc = launch_gemm(h, segs, W(h, L[i].t[0]), W(h, L[i].t[1]), o, H, H, act_code(c), Bc, Nn, Tdst, Ts, Nn, 0);
       if (rc) return rc;
     } else {
       const bool gru = c.recurrent == GNNUDS_REC_GRU;
       const int G = (gru ? 3 : 4) * H;
       // input projection for every time step
-      rc = launch_gemm(h, {{cur, cw, cw, 0, Nn, 0}}, W(h, L[i].t[0]), W(h, L[i].t[2]) /* b[0] or b */, h->HB, G, G,
+      rc = launch_gemm(h, {{cur, cw, cw, 0, cpitch, coff}}, W(h, L[i].t[0]), W(h, L[i].t[2]) /* b[0] or b */, h->HB, G, G,
                        ACT_LINEAR, Bc, Nn, Ts, Ts, Nn, 0);
       if (rc) return rc;
       const long long nseq = Bc * Nn;
@@ -418,7 +418,7 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const float* sr
       ++h->launches;
       CU(cudaGetLastError());
     }
-    cur = o; cw = H;
+    cur = o; cw = H; cpitch = Nn; coff = 0;
     // note: for non-final layers Tdst == Ts so the next layer reads a full-length sequence
   }
   *dst = const_cast<float*>(cur);
@@ -426,6 +426,7 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const float* sr
 }
 
 struct Stream2 { std::vector<SegH> x, e; };   // current node / edge stream as concatenated segments
+template <bool TC> int run_spatial_joint(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T);
 
 // ---- spatial block (emulator.py:219-235 / 272-288), graph_base == 0 -----------------------
 int run_spatial(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) {
@@ -462,8 +463,9 @@ int run_spatial(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) {
 }
 
 void set_dbg(gnnuds_handle* h, const Stream2& st, long long rows_x, long long rows_e) {
-  h->dbg_ptr[0] = st.x[0].p; h->dbg_width[0] = st.x[0].width; h->dbg_rows[0] = rows_x;
-  h->dbg_ptr[1] = st.e[0].p; h->dbg_width[1] = st.e[0].width; h->dbg_rows[1] = rows_e;
+  const bool joint = st.x[0].pitch != h->c.n_node;   // joint node+edge buffer: no compact view to fetch
+  h->dbg_ptr[0] = joint ? nullptr : st.x[0].p; h->dbg_width[0] = st.x[0].width; h->dbg_rows[0] = rows_x;
+  h->dbg_ptr[1] = joint ? nullptr : st.e[0].p; h->dbg_width[1] = st.e[0].width; h->dbg_rows[1] = rows_e;
 }
 
 int run_postproc(gnnuds_handle* h, const float* b, const float* a, long long Bc, float* y, float* ey, bool normalised_io) {
@@ -499,7 +501,6 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
   const int E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge, Ti = c.seq_in, To = c.seq_out;
   const int act = act_code(c);
   int rc;
-  if (c.graph_base) return fail(h, GNNUDS_E_INVALID, "graph_base != 0 forward not built in this revision");
   // ---- K1 embedding ----
   if ((rc = launch_embed(h, x, normalised_io ? nullptr : h->d_nx, h->cx_n, N, nullptr, 0, h->emb_x, h->XB, h->RES, Bc, Ti, N,
                          c.n_in, E, act, 0))) return rc;
@@ -518,15 +519,15 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
   if (h->debug_stop == 1) return 0;
   // the first spatial layer writes XA/EA (l even), so the embedding lives in XB/EB
   // ---- spatial block 1 ----
-  rc = run_spatial(h, 0, st, Bc, Ti);
+  rc = c.graph_base ? run_spatial_joint<false>(h, 0, st, Bc, Ti) : run_spatial(h, 0, st, Bc, Ti);
   set_dbg(h, st, Bc * Ti * N, Bc * Ti * M);
   if (rc == 1) return 0;
   if (rc) return rc;
   if (h->debug_stop == 2) return 0;
   // ---- temporal block 1 (keeps the last To steps, emulator.py:249,256) ----
   float *xt = nullptr, *et = nullptr;
-  if ((rc = run_temporal(h, h->tpx[0], st.x[0].p, E, Bc, N, Ti, To, h->TX0, h->TX1, &xt))) return rc;
-  if ((rc = run_temporal(h, h->tpe[0], st.e[0].p, E, Bc, M, Ti, To, h->TE0, h->TE1, &et))) return rc;
+  if ((rc = run_temporal(h, h->tpx[0], st.x[0], E, Bc, N, Ti, To, h->TX0, h->TX1, &xt))) return rc;
+  if ((rc = run_temporal(h, h->tpe[0], st.e[0], E, Bc, M, Ti, To, h->TE0, h->TE1, &et))) return rc;
   // ---- boundary / control concat (emulator.py:260-262) ----
   st.x = {{xt, H, H, 0, N, 0}, {h->BEMB, E2, E2, 0, N, 0}};
   st.e = {{et, H, H, 0, M, 0}};
@@ -534,14 +535,14 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
   set_dbg(h, st, Bc * To * N, Bc * To * M);
   if (h->debug_stop == 3) return 0;
   // ---- spatial block 2 ----
-  rc = run_spatial(h, 1, st, Bc, To);
+  rc = c.graph_base ? run_spatial_joint<false>(h, 1, st, Bc, To) : run_spatial(h, 1, st, Bc, To);
   set_dbg(h, st, Bc * To * N, Bc * To * M);
   if (rc == 1) return 0;
   if (rc) return rc;
   if (h->debug_stop == 4) return 0;
   // ---- temporal block 2 ----
-  if ((rc = run_temporal(h, h->tpx[1], st.x[0].p, E, Bc, N, To, To, h->TX0, h->TX1, &xt))) return rc;
-  if ((rc = run_temporal(h, h->tpe[1], st.e[0].p, E, Bc, M, To, To, h->TE0, h->TE1, &et))) return rc;
+  if ((rc = run_temporal(h, h->tpx[1], st.x[0], E, Bc, N, To, To, h->TX0, h->TX1, &xt))) return rc;
+  if ((rc = run_temporal(h, h->tpe[1], st.e[0], E, Bc, M, To, To, h->TE0, h->TE1, &et))) return rc;
   st.x = {{xt, H, H, 0, N, 0}};
   st.e = {{et, H, H, 0, M, 0}};
   set_dbg(h, st, Bc * To * N, Bc * To * M);
@@ -704,12 +705,12 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
   return 0;
 }
 
-int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const float* src, int cin, long long Bc, int Nn,
+int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src, int cin, long long Bc, int Nn,
                     int Ts, int Td, float* t0, float* t1, float** dst) {
   const auto& c = h->c;
   const int H = c.hidden, P = c.n_tp_layer;
-  const float* cur = src;
-  int cw = cin;
+  const float* cur = src.p;
+  int cw = cin, cpitch = src.pitch, coff = src.off;
   float* bufs[2] = {t0, t1};
   for (int i = 0; i < P; ++i) {
     const bool last = (i == P - 1);
@@ -719,12 +720,12 @@ int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const float*
     if (c.recurrent == GNNUDS_REC_CONV1D) {
       std::vector<SegH> segs;
       const int k = c.kernel_size, d = 1 << i;
-      for (int j = 0; j < k; ++j) segs.push_back({cur, cw, cw, (k - 1 - j) * d, Nn, 0});
+      for (int j = 0; j < k; ++j) segs.push_back({cur, cw, cw, (k - 1 - j) * d, cpitch, coff});
       if ((rc = launch_tc_gemm(h, segs, L[i].t[0], W(h, L[i].t[1]), o, H, H, act_code(c), Bc, Nn, Tdst, Ts, Nn, 0))) return rc;
     } else {
       const bool gru = c.recurrent == GNNUDS_REC_GRU;
       const int G = (gru ? 3 : 4) * H;
-      if ((rc = launch_tc_gemm(h, {{cur, cw, cw, 0, Nn, 0}}, L[i].t[0], W(h, L[i].t[2]), h->HB, G, G, ACT_LINEAR, Bc, Nn, Ts, Ts,
+      if ((rc = launch_tc_gemm(h, {{cur, cw, cw, 0, cpitch, coff}}, L[i].t[0], W(h, L[i].t[2]), h->HB, G, G, ACT_LINEAR, Bc, Nn, Ts, Ts,
                                Nn, 0))) return rc;
       const long long nseq = Bc * Nn;
       const int g = (int)((nseq + 31) / 32);
@@ -742,7 +743,7 @@ int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const float*
       ++h->launches;
       CU(cudaGetLastError());
     }
-    cur = o; cw = H;
+    cur = o; cw = H; cpitch = Nn; coff = 0;
   }
   *dst = const_cast<float*>(cur);
   return 0;
@@ -804,7 +805,6 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
   const int E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge, Ti = c.seq_in, To = c.seq_out;
   const int act = act_code(c);
   int rc;
-  if (c.graph_base) return fail(h, GNNUDS_E_INVALID, "graph_base != 0 forward not built in this revision");
   if ((rc = launch_embed<bf16>(h, x, normalised_io ? nullptr : h->d_nx, h->cx_n, N, nullptr, 0, h->emb_x, h->XB, h->RES, Bc, Ti, N,
                                c.n_in, E, act, 0))) return rc;
   if ((rc = launch_embed<bf16>(h, b, normalised_io ? nullptr : h->d_nb, h->cb_n, N, nullptr, 0, h->emb_b, h->BEMB, nullptr, Bc, To, N,
@@ -820,26 +820,26 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
   st.e = {{h->EB, E, E, 0, M, 0}};
   set_dbg(h, st, Bc * Ti * N, Bc * Ti * M);
   if (h->debug_stop == 1) return 0;
-  rc = run_spatial_tc(h, 0, st, Bc, Ti);
+  rc = c.graph_base ? run_spatial_joint<true>(h, 0, st, Bc, Ti) : run_spatial_tc(h, 0, st, Bc, Ti);
   set_dbg(h, st, Bc * Ti * N, Bc * Ti * M);
   if (rc == 1) return 0;
   if (rc) return rc;
   if (h->debug_stop == 2) return 0;
   float *xt = nullptr, *et = nullptr;
-  if ((rc = run_temporal_tc(h, h->tpx[0], st.x[0].p, E, Bc, N, Ti, To, h->TX0, h->TX1, &xt))) return rc;
-  if ((rc = run_temporal_tc(h, h->tpe[0], st.e[0].p, E, Bc, M, Ti, To, h->TE0, h->TE1, &et))) return rc;
+  if ((rc = run_temporal_tc(h, h->tpx[0], st.x[0], E, Bc, N, Ti, To, h->TX0, h->TX1, &xt))) return rc;
+  if ((rc = run_temporal_tc(h, h->tpe[0], st.e[0], E, Bc, M, Ti, To, h->TE0, h->TE1, &et))) return rc;
   st.x = {{xt, H, H, 0, N, 0}, {h->BEMB, E2, E2, 0, N, 0}};
   st.e = {{et, H, H, 0, M, 0}};
   if (c.act) st.e.push_back({h->AEMB, E2, E2, 0, M, 0});
   set_dbg(h, st, Bc * To * N, Bc * To * M);
   if (h->debug_stop == 3) return 0;
-  rc = run_spatial_tc(h, 1, st, Bc, To);
+  rc = c.graph_base ? run_spatial_joint<true>(h, 1, st, Bc, To) : run_spatial_tc(h, 1, st, Bc, To);
   set_dbg(h, st, Bc * To * N, Bc * To * M);
   if (rc == 1) return 0;
   if (rc) return rc;
   if (h->debug_stop == 4) return 0;
-  if ((rc = run_temporal_tc(h, h->tpx[1], st.x[0].p, E, Bc, N, To, To, h->TX0, h->TX1, &xt))) return rc;
-  if ((rc = run_temporal_tc(h, h->tpe[1], st.e[0].p, E, Bc, M, To, To, h->TE0, h->TE1, &et))) return rc;
+  if ((rc = run_temporal_tc(h, h->tpx[1], st.x[0], E, Bc, N, To, To, h->TX0, h->TX1, &xt))) return rc;
+  if ((rc = run_temporal_tc(h, h->tpe[1], st.e[0], E, Bc, M, To, To, h->TE0, h->TE1, &et))) return rc;
   st.x = {{xt, H, H, 0, N, 0}};
   st.e = {{et, H, H, 0, M, 0}};
   set_dbg(h, st, Bc * To * N, Bc * To * M);
@@ -874,6 +874,37 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
   return run_postproc(h, b, a, Bc, y, ey, normalised_io);
 }
 
+
+// ---- spatial block, graph_base != 0 (emulator.py:220-223 / 273-276): one conv over the joint
+// node+edge graph.  z = Conv([x ; e] rows, Adj (N+M,N+M)); x,e = split(z).  Node rows and edge rows of
+// a (b,t) sample sit next to each other in a joint buffer (pitch N+M, edge offset N), so the split is free.
+template <bool TC>
+int run_spatial_joint(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) {
+  const auto& c = h->c;
+  const int E = c.embed, N = c.n_node, M = c.n_edge, R = N + M;
+  const long long S = Bc * T;
+  const int act = act_code(c);
+  for (int l = 0; l < c.n_sp_layer; ++l) {
+    const SpatialW& w = h->sp[blk][l];
+    int rc;
+    float* jo = (l & 1) ? h->J1 : h->J0;
+    if (TC) {
+      if ((rc = launch_tc_gemm(h, st.x, w.joint.t[0], nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, N, T, T, R, 0))) return rc;
+      if ((rc = launch_tc_gemm(h, st.e, w.joint.t[0], nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, M, T, T, R, N))) return rc;
+      if ((rc = launch_agg<bf16>(h, h->HBJ, jo, h->d_rp, h->d_ci, h->d_val, w.joint, S, R, act))) return rc;
+    } else {
+      if ((rc = launch_gemm(h, st.x, W(h, w.joint.t[0]), nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, N, T, T, R, 0))) return rc;
+      if ((rc = launch_gemm(h, st.e, W(h, w.joint.t[0]), nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, M, T, T, R, N))) return rc;
+      if ((rc = launch_agg<float>(h, h->HBJ, jo, h->d_rp, h->d_ci, h->d_val, w.joint, S, R, act))) return rc;
+    }
+    st.x = {{jo, E, E, 0, R, 0}};
+    st.e = {{jo, E, E, 0, R, N}};
+    if (h->debug_stop == (blk ? 40 : 20) + l) return 1;
+  }
+  return 0;
+}
+
+
 int forward_any(gnnuds_handle* h, const float* x, const float* b, const float* a, const float* ex, long long Bc, float* y,
                 float* ey, bool normalised_io) {
   return h->tc() ? forward_chunk_tc(h, x, b, a, ex, Bc, y, ey, normalised_io) : forward_chunk(h, x, b, a, ex, Bc, y, ey, normalised_io);
@@ -892,6 +923,7 @@ int64_t floats_per_scenario(const gnnuds_config& c) {
   f += c.seq_out * (N + M) * 4;                          // OUTN OUTE
   f += c.seq_in * (N * c.n_in + M * c.e_in) + c.seq_out * (N * c.b_in + std::max(c.n_act, 1));
   f += c.seq_out * (N * 5 + M * 4);
+  if (c.graph_base) f += Tm * (N + M) * (3 * E + 2);
   return f + 64;
 }
 
@@ -916,6 +948,11 @@ int ensure_workspace(gnnuds_handle* h, int64_t Bc) {
       {&h->in_x, Bc * c.seq_in * N * c.n_in * 4}, {&h->in_b, Bc * c.seq_out * N * c.b_in * 4},
       {&h->in_a, Bc * c.seq_out * std::max(c.n_act, 1) * 4}, {&h->in_ex, Bc * c.seq_in * M * c.e_in * 4},
       {&h->out_y, Bc * c.seq_out * N * 5 * 4}, {&h->out_ey, Bc * c.seq_out * M * 4 * 4}};
+  if (c.graph_base) {
+    const int64_t RJ = Bc * Tm * (N + M);
+    plan.push_back({&h->HBJ, RJ * E * a}); plan.push_back({&h->J0, RJ * E * a}); plan.push_back({&h->J1, RJ * E * a});
+    plan[19].bytes = RJ * 4; plan[20].bytes = RJ * 4;   // SS, SN cover the joint rows
+  }
   size_t total = 0;
   for (auto& it : plan) total += (size_t)((it.bytes + 255) / 256 * 256);
   CU(cudaMalloc(&h->d_ws, total));

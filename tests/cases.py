@@ -41,9 +41,17 @@ CASES = {
     "ast_gcn_conv_eps0": dict(net="astlingen", conv="GCN", recurrent="Conv1D", resnet=True, seq_in=8, seq_out=4,
                               embed_size=128, hidden_dim=64, n_sp_layer=2, n_tp_layer=3, length=501, order=1,
                               edge_fusion=True, if_flood=2, epsilon=0.0, tide=True, B=2, seed=48),
+    # graph_base=1: one conv over the joint node+edge graph (emulator.py:220-223); needs act so that both
+    # streams enter block 2 with H+E/2 channels.  C5 is this architecture on a 100k-node tree.
+    "ast_joint_gcn_gru_act": dict(net="astlingen", conv="GCN", recurrent="GRU", resnet=True, seq_in=6, seq_out=6,
+                                  embed_size=128, hidden_dim=64, n_sp_layer=2, n_tp_layer=2, length=0, order=1,
+                                  graph_base=1, act="conti", if_flood=2, B=3, seed=49),
+    "ast_joint_gat_conv_act": dict(net="astlingen", conv="GAT", recurrent="Conv1D", resnet=False, seq_in=5, seq_out=5,
+                                   embed_size=64, hidden_dim=64, n_sp_layer=2, n_tp_layer=2, length=0, order=1,
+                                   graph_base=1, act="conti", edge_fusion=True, B=2, seed=50),
 }
 GOLDEN_CASES = ["c1_ast_gcn_gru", "c2_shq_gat_conv_10", "c3_ast_act_5", "ast_gat_gru_noflood",
-                "ast_gcn_lstm_act_nofusion", "ast_gcn_conv_eps0"]
+                "ast_gcn_lstm_act_nofusion", "ast_gcn_conv_eps0", "ast_joint_gcn_gru_act", "ast_joint_gat_conv_act"]
 
 
 def load_net(name):
