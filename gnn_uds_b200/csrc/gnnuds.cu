@@ -7,6 +7,7 @@
 #include "kernels.cuh"
 #include "tc_gemm.cuh"
 #include "tc_selftest.cuh"
+#include "fused_sp.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -67,6 +68,11 @@ struct gnnuds_handle {
   size_t es() const { return tc() ? 2 : 4; }   // bytes per stored activation element
   std::vector<float*> d_ne_matT[2];     // per spatial layer (block*S + l): N-side, M-side folded matrices
   int ldm_n = 0, ldm_m = 0, ti_n = 0, ti_m = 0;
+  // bf16 K-major images of the folded NodeEdge matrices for the fused spatial kernel (side 0: N x M, 1: M x N)
+  std::vector<uint8_t*> d_ne_img[2];
+  uint32_t ne_img_bytes[2] = {0, 0}, ne_pstride[2] = {0, 0};
+  int ne_kp[2] = {0, 0};
+  bool fused_on = true;                 // GNNUDS_FUSED=0 keeps the layer-by-layer tensor-core path
 
   // graph
   int *d_rp = nullptr, *d_ci = nullptr, *d_erp = nullptr, *d_eci = nullptr;
@@ -773,6 +779,69 @@ int run_conv_tc(gnnuds_handle* h, const std::vector<SegH>& segs, const LayerW& w
   return launch_agg<bf16>(h, h->HB, out, rp, ci, val, w, Bc * T, R, act);
 }
 
+// ---- fused spatial layer, one stream side (csrc/fused_sp.cuh) -----------------------------------
+// Returns 0 launched, -1 not applicable (caller falls back to the layer-by-layer kernels), > 0 error.
+int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* other_dense, int side, int li,
+                   const LayerW& w, void* out, const int* rp, const int* ci, const float* val, int nnz, long long S,
+                   int R, int Ro, int act) {
+  const auto& c = h->c;
+  const int E = c.embed, F = E / 2;
+  const bool gat = c.conv == GNNUDS_CONV_GAT;
+  if (!h->fused_on || segs.empty() || segs.size() > 2 || R > 256 || Ro > 256 || R < 1 || F % 32 || E % 64 || E > 128) return -1;
+  if (S <= 0 || S * (long long)std::max(R, Ro) >= (1ll << 31)) return -1;
+  SpConvP p{};
+  p.nseg = (int)segs.size();
+  p.Kself = 0;
+  for (int i = 0; i < p.nseg; ++i) {
+    const SegH& sg = segs[i];
+    if (sg.shift || sg.pitch != R || sg.off || sg.width % 16 || sg.ld % 8 || (reinterpret_cast<uintptr_t>(sg.p) & 15)) return -1;
+    p.segw[i] = sg.width; p.Kself += sg.width;
+  }
+  const int Ktot = p.Kself + F;
+  if ((long long)Ktot * E != h->tens[w.t[0]].numel || h->img_off[w.t[0]] < 0) return -1;
+  p.S = (int)S; p.R = R; p.Ro = Ro; p.F = F; p.Nout = E; p.act = act; p.gat = gat ? 1 : 0;
+  p.Rbox = (R + 7) / 8 * 8; p.Kp = h->ne_kp[side]; p.MT = (R + 127) / 128;
+  p.pstrideA = (uint32_t)p.Rbox * 16u; p.pstrideM = h->ne_pstride[side]; p.pstrideX = (uint32_t)p.Kp * 16u;
+  p.hsb = (uint32_t)E * 2u + 16u;
+  p.Wimg = h->d_wimg + h->img_off[w.t[0]]; p.w_bytes = (uint32_t)Ktot * E * 2u;
+  p.Mimg = h->d_ne_img[side][li]; p.m_bytes = h->ne_img_bytes[side];
+  p.bias = W(h, w.t[gat ? 3 : 1]);
+  p.a_self = gat ? W(h, w.t[1]) : nullptr; p.a_neigh = gat ? W(h, w.t[2]) : nullptr;
+  p.row_ptr = rp; p.col_idx = ci; p.val = val; p.nnz = nnz;
+  p.out = static_cast<bf16*>(out);
+  auto al = [](uint32_t v, uint32_t a) { return (v + a - 1) / a * a; };
+  p.off_w = 0;
+  p.off_m = al(p.w_bytes, 128);
+  p.off_in = al(p.off_m + p.m_bytes, 1024);
+  p.self_bytes = (uint32_t)(p.Kself / 8) * p.pstrideA;
+  p.xe_off = al(p.self_bytes, 128);
+  p.xe_bytes = (uint32_t)(F / 8) * p.pstrideX;
+  p.in_stride = al(std::max(p.xe_off + p.xe_bytes, (uint32_t)R * p.hsb), 1024);
+  p.off_nx = p.off_in + 2 * p.in_stride;
+  const uint32_t nx_bytes = (uint32_t)(F / 8) * p.pstrideA;
+  p.off_sc = al(p.off_nx + nx_bytes, 128);
+  const uint32_t RP = 128u * p.MT;
+  const uint32_t sc_bytes = (3u * E + 5u * RP + (uint32_t)nnz) * 4u + ((uint32_t)R + 1u + (uint32_t)nnz) * 4u;
+  p.off_bar = al(p.off_sc + sc_bytes, 16);
+  // operand views of M-tile mt read 128 rows from row mt*128 of every panel: keep those reads inside the allocation
+  const uint32_t reach = p.off_nx + (uint32_t)(F / 8 - 1) * p.pstrideA + RP * 16u;
+  const size_t smem = std::max<size_t>(p.off_bar + 11 * 8 + 16, reach);
+  if (smem > 227 * 1024) return -1;
+  for (int i = 0; i < p.nseg; ++i)
+    if (!make_rows_tmap(&p.tm_self[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox, segs[i].width)) return -1;
+  if (!make_rows_tmap(&p.tm_other, other_dense, S * Ro, F, F, p.Kp, F)) return -1;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CU(cudaFuncSetAttribute(sp_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  const unsigned grid = (unsigned)std::min<long long>(S, h->sm_count);
+  sp_conv_kernel<<<grid, SP_THREADS, smem, h->stream>>>(p);
+  ++h->launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+
 int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) {
   const auto& c = h->c;
   const int E = c.embed, E2 = E / 2, N = c.n_node, M = c.n_edge;
@@ -784,14 +853,23 @@ int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) 
     if ((rc = launch_tc_gemm(h, st.e, w.xe.t[0], W(h, w.xe.t[1]), h->XE, E2, E2, act, Bc, M, T, T, M, 0))) return rc;
     if ((rc = launch_tc_gemm(h, st.x, w.ex.t[0], W(h, w.ex.t[1]), h->EX, E2, E2, act, Bc, N, T, T, N, 0))) return rc;
     const int li = blk * c.n_sp_layer + l;
-    if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, h->XE, h->NX, S, M, N, E2))) return rc;
-    if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, h->EX, h->NE, S, N, M, E2))) return rc;
-    std::vector<SegH> sx = st.x; sx.push_back({h->NX, E2, E2, 0, N, 0});
-    std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
     float* xo = (l & 1) ? h->XB : h->XA;
     float* eo = (l & 1) ? h->EB : h->EA;
-    if ((rc = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return rc;
-    if ((rc = run_conv_tc(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, Bc, T, M, act))) return rc;
+    // fused NodeEdge + conv + aggregation per stream side; layer-by-layer kernels when it does not apply
+    rc = launch_sp_conv(h, st.x, h->XE, 0, li, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, M, act);
+    if (rc > 0) return rc;
+    if (rc < 0) {
+      if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, h->XE, h->NX, S, M, N, E2))) return rc;
+      std::vector<SegH> sx = st.x; sx.push_back({h->NX, E2, E2, 0, N, 0});
+      if ((rc = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return rc;
+    }
+    rc = launch_sp_conv(h, st.e, h->EX, 1, li, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, S, M, N, act);
+    if (rc > 0) return rc;
+    if (rc < 0) {
+      if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, h->EX, h->NE, S, N, M, E2))) return rc;
+      std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
+      if ((rc = run_conv_tc(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, Bc, T, M, act))) return rc;
+    }
     st.x = {{xo, E, E, 0, N, 0}};
     st.e = {{eo, E, E, 0, M, 0}};
     if (h->debug_stop == (blk ? 40 : 20) + l) return 1;
@@ -1046,6 +1124,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, c.device);
   cudaEventCreate(&h->ev_a); cudaEventCreate(&h->ev_b);
   h->tma_on = !(getenv("GNNUDS_NO_TMA") && getenv("GNNUDS_NO_TMA")[0] == '1');
+  h->fused_on = !(getenv("GNNUDS_FUSED") && getenv("GNNUDS_FUSED")[0] == '0');
   LayoutBuilder lb{h};
   lb.build();
   *out = h;
@@ -1061,6 +1140,7 @@ int gnnuds_destroy(gnnuds_handle* h) {
                   h->d_outfall, h->d_ehmax, h->d_nx, h->d_nb, h->d_ny, h->d_ne, h->d_ws, h->ro_x, h->ro_ex, h->ro_b, h->ro_a, h->d_wimg};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p);
+  for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_ne_img[s]) if (p) cudaFree(p);
   for (auto& e : h->gemm_ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (h->ev_a) cudaEventDestroy(h->ev_a);
   if (h->ev_b) cudaEventDestroy(h->ev_b);
@@ -1219,6 +1299,34 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
           h->d_ne_matT[1].push_back(d);
         }
       }
+    if (h->tc()) {
+      // the same folded matrices as bf16 K-major images (A operand of the NodeEdge MMA in sp_conv_kernel)
+      for (int s = 0; s < 2; ++s) { for (uint8_t* p : h->d_ne_img[s]) if (p) cudaFree(p); h->d_ne_img[s].clear(); }
+      const int Rs[2] = {N, M}, Ks[2] = {M, N};
+      for (int s = 0; s < 2; ++s) {
+        h->ne_kp[s] = (Ks[s] + 15) / 16 * 16;
+        h->ne_pstride[s] = (uint32_t)((Rs[s] + 7) / 8 * 8) * 16u;
+        h->ne_img_bytes[s] = (uint32_t)(h->ne_kp[s] / 8) * h->ne_pstride[s];
+      }
+      for (int blk = 0; blk < 2; ++blk)
+        for (int l = 0; l < c.n_sp_layer; ++l) {
+          const SpatialW& w = h->sp[blk][l];
+          for (int s = 0; s < 2; ++s) {
+            const LayerW& lw = s == 0 ? w.ne_n : w.ne_m;
+            const float* wt = blob + offsets[lw.t[0]]; const float* bs = blob + offsets[lw.t[1]];
+            std::vector<float> md((size_t)Rs[s] * Ks[s]);
+            for (int r = 0; r < Rs[s]; ++r)
+              for (int k = 0; k < Ks[s]; ++k) {
+                const float inc = s == 0 ? inci[(size_t)r * M + k] : inci[(size_t)k * M + r];
+                md[(size_t)r * Ks[s] + k] = wt[(size_t)r * Ks[s] + k] * inc + bs[(size_t)r * Ks[s] + k];
+              }
+            std::vector<uint16_t> img = pack_kmajor(md.data(), Rs[s], Ks[s], Ks[s], 1, 0, h->ne_kp[s], (int)h->ne_pstride[s]);
+            uint16_t* d = nullptr;
+            if ((rc = upload(h, &d, img.data(), img.size()))) return rc;
+            h->d_ne_img[s].push_back(reinterpret_cast<uint8_t*>(d));
+          }
+        }
+    }
   }
   h->has_weights = true;
   return 0;
