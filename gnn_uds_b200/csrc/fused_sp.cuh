@@ -12,10 +12,10 @@
 // Persistent, one CTA per SM, one sample per pass, inputs double-buffered by TMA:
 //   warps 0..3   "drain" group : TMEM -> smem.  NodeEdge result -> bf16 panels (A operand of the conv GEMM);
 //                                conv result h -> bf16 row tile + GAT scores from the fp32 accumulators
-//   warps 4..11  "graph" group : edge softmax + weighted neighbour sum over the h tile -> bias/act -> HBM
-//   warp  12     MMA issuer    : tcgen05.mma  NE: D[128 x F] = Mat(K-major) x other_dense(MN-major)
+//   warps 4..19  "graph" group : edge softmax + weighted neighbour sum over the h tile -> bias/act -> HBM
+//   warp  20     MMA issuer    : tcgen05.mma  NE: D[128 x F] = Mat(K-major) x other_dense(MN-major)
 //                                             conv: D[128 x Nout] = [self | NE](K-major) x Wconv(K-major)
-//   warp  13     TMA producer  : cp.async.bulk.tensor loads of sample i+2 once the graph group released the buffer
+//   warp  21     TMA producer  : cp.async.bulk.tensor loads of sample i+2 once the graph group released the buffer
 // The h tile of a sample aliases that sample's own input buffer (dead once the conv MMAs committed), so
 // the graph group works on sample i while MMA + drain already process sample i+1 in the other buffer.
 #pragma once
@@ -28,8 +28,8 @@
 namespace gu {
 
 constexpr int SP_DRAIN_WARPS = 4;
-constexpr int SP_GRAPH_WARPS = 8;
-constexpr int SP_THREADS = (SP_DRAIN_WARPS + SP_GRAPH_WARPS + 2) * 32;   // 448
+constexpr int SP_GRAPH_WARPS = 16;
+constexpr int SP_THREADS = (SP_DRAIN_WARPS + SP_GRAPH_WARPS + 2) * 32;   // 704
 
 struct SpConvP {
   CUtensorMap tm_self[2];     // {8, S*R rows, w/8 panels}, box {8, Rbox, w/8}
@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
   uint64_t* conv_done = bars + 8;    // conv MMAs committed
   uint64_t* wbar = bars + 9;         // resident weights landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
-  // scratch: bias[Nout] asf[Nout] anf[Nout] | ss[2][RP] sn[2][RP] | inv[RP] | alpha[nnz] | rp[R+1] ci[nnz]
+  // scratch: bias[Nout] asf[Nout] anf[Nout] | ss[2][RP] sn[2][RP] | inv[2][RP] | alpha[2][nnz] | rp[R+1] ci[nnz]
   const int RP = 128 * p.MT;
   float* bias_s = reinterpret_cast<float*>(smem + p.off_sc);
   float* asf = bias_s + p.Nout;
@@ -68,15 +68,15 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
   float* ss = anf + p.Nout;
   float* sn = ss + 2 * RP;
   float* inv_s = sn + 2 * RP;
-  float* alpha = inv_s + RP;
-  int* rp_s = reinterpret_cast<int*>(alpha + p.nnz);
+  float* alpha = inv_s + 2 * RP;
+  int* rp_s = reinterpret_cast<int*>(alpha + 2 * p.nnz);
   int* ci_s = rp_s + p.R + 1;
 
   if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
   if (tid == 32) {
     for (int i = 0; i < 2; ++i) {
       tc::mbar_init(&in_full[i], 1);
-      tc::mbar_init(&in_empty[i], 1);
+      tc::mbar_init(&in_empty[i], SP_GRAPH_WARPS * 32);
       tc::mbar_init(&h_full[i], SP_DRAIN_WARPS * 32);
     }
     tc::mbar_init(ne_done, 1);
@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
     anf[i] = p.gat ? p.a_neigh[i] : 0.f;
   }
   for (int i = tid; i <= p.R; i += SP_THREADS) rp_s[i] = p.row_ptr[i];
-  for (int i = tid; i < p.nnz; i += SP_THREADS) { ci_s[i] = p.col_idx[i]; if (!p.gat) alpha[i] = p.val[i]; }
+  for (int i = tid; i < p.nnz; i += SP_THREADS) { ci_s[i] = p.col_idx[i]; if (!p.gat) { alpha[i] = p.val[i]; alpha[p.nnz + i] = p.val[i]; } }
   {
     uint4* z = reinterpret_cast<uint4*>(smem + p.off_nx);
     const int n16 = (int)((p.F / 8) * p.pstrideA / 16);
@@ -138,38 +138,46 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
       const uint32_t w_addr = tc::smem_u32(smem + p.off_w), m_addr = tc::smem_u32(smem + p.off_m);
       const uint32_t nx_addr = tc::smem_u32(smem + p.off_nx);
       const uint32_t pstrideW = (uint32_t)p.Nout * 16u;
-      const int ks_self = p.Kself >> 4, ks_ne = p.F >> 4;
+      const int ks_self = p.Kself >> 4, ks_ne = p.F >> 4, ks_kp = p.Kp >> 4, F = p.F, Nout = p.Nout;
+      const bool MT2 = p.MT > 1;
+      const uint32_t pstrideA = p.pstrideA, pstrideX = p.pstrideX, xe_off = p.xe_off, off_in = p.off_in, in_stride = p.in_stride;
+      const uint64_t w_desc0 = tc::smem_desc(w_addr, pstrideW, 128u), m_desc0 = tc::smem_desc(m_addr, p.pstrideM, 128u);
+      const uint64_t nx_desc0 = tc::smem_desc(nx_addr, pstrideA, 128u);
+      const uint64_t a_step = (uint64_t)((2u * pstrideA) >> 4), w_step = (uint64_t)((2u * pstrideW) >> 4), m_step = (uint64_t)((2u * p.pstrideM) >> 4);
       for (int i = 0; i < n_it; ++i) {
         const int buf = i & 1;
-        const uint32_t in_addr = tc::smem_u32(smem + p.off_in + (size_t)buf * p.in_stride);
+        const uint32_t in_addr = tc::smem_u32(smem + off_in + (size_t)buf * in_stride);
         tc::mbar_wait(&in_full[buf], (i >> 1) & 1);
         tc::tc_fence_after();
         // NodeEdge: D[row, f] = sum_k Mat[row, k] * other_dense[k, f]
-        for (int ks = 0; ks < (p.Kp >> 4); ++ks) {
-          const uint64_t bd = tc::smem_desc(in_addr + p.xe_off + (uint32_t)ks * 256u, 128u, p.pstrideX);
-          for (int mt = 0; mt < p.MT; ++mt) {
-            const uint64_t ad = tc::smem_desc(m_addr + (uint32_t)mt * 2048u + 2u * ks * p.pstrideM, p.pstrideM, 128u);
-            tc::umma(acc_ne + (uint32_t)(mt * p.F), ad, bd, idesc_ne, ks != 0);
+        // descriptors advance linearly with the start address: one 64-bit add per MMA in the issue loops
+        {
+          uint64_t ad = m_desc0, bd = tc::smem_desc(in_addr + xe_off, 128u, pstrideX);
+          for (int ks = 0; ks < ks_kp; ++ks, ad += m_step, bd += 16u) {
+            tc::umma(acc_ne, ad, bd, idesc_ne, ks != 0);
+            if (MT2) tc::umma(acc_ne + (uint32_t)F, ad + 128u, bd, idesc_ne, ks != 0);
           }
         }
         tc::umma_commit(ne_done);
         // conv over the self columns first (they are ready), then over the NodeEdge columns.  The conv
         // accumulators of the previous sample must have been drained (h_full of sample i-1).
         if (i >= 1) { tc::mbar_wait(&h_full[(i - 1) & 1], ((i - 1) >> 1) & 1); tc::tc_fence_after(); }
-        for (int ks = 0; ks < ks_self; ++ks) {
-          const uint64_t bd = tc::smem_desc(w_addr + 2u * ks * pstrideW, pstrideW, 128u);
-          for (int mt = 0; mt < p.MT; ++mt) {
-            const uint64_t ad = tc::smem_desc(in_addr + (uint32_t)mt * 2048u + 2u * ks * p.pstrideA, p.pstrideA, 128u);
-            tc::umma(acc_conv + (uint32_t)(mt * p.Nout), ad, bd, idesc_cv, ks != 0);
+        uint64_t wd = w_desc0;
+        {
+          uint64_t ad = tc::smem_desc(in_addr, pstrideA, 128u);
+#pragma unroll 4
+          for (int ks = 0; ks < ks_self; ++ks, ad += a_step, wd += w_step) {
+            tc::umma(acc_conv, ad, wd, idesc_cv, ks != 0);
+            if (MT2) tc::umma(acc_conv + (uint32_t)Nout, ad + 128u, wd, idesc_cv, ks != 0);
           }
         }
         tc::mbar_wait(nx_ready, i & 1);
         tc::tc_fence_after();
-        for (int ks = 0; ks < ks_ne; ++ks) {
-          const uint64_t bd = tc::smem_desc(w_addr + 2u * (ks_self + ks) * pstrideW, pstrideW, 128u);
-          for (int mt = 0; mt < p.MT; ++mt) {
-            const uint64_t ad = tc::smem_desc(nx_addr + (uint32_t)mt * 2048u + 2u * ks * p.pstrideA, p.pstrideA, 128u);
-            tc::umma(acc_conv + (uint32_t)(mt * p.Nout), ad, bd, idesc_cv, 1u);
+        {
+          uint64_t ad = nx_desc0;
+          for (int ks = 0; ks < ks_ne; ++ks, ad += a_step, wd += w_step) {
+            tc::umma(acc_conv, ad, wd, idesc_cv, 1u);
+            if (MT2) tc::umma(acc_conv + (uint32_t)Nout, ad + 128u, wd, idesc_cv, 1u);
           }
         }
         tc::umma_commit(conv_done);
@@ -211,7 +219,9 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         const int row = mt * 128 + q * 32 + lane;
         const uint32_t ta = acc_conv + ((uint32_t)(q * 32) << 16) + (uint32_t)(mt * p.Nout);
         uint8_t* hrow = hbase + (size_t)row * p.hsb;
-        float ps = 0.f, pn = 0.f;
+        // scores from the fp32 accumulators: two independent chains per vector, 16-byte broadcast loads of the
+        // attention vectors (8 columns at a time keeps the 704-thread register budget)
+        float ps0 = 0.f, ps1 = 0.f, pn0 = 0.f, pn1 = 0.f;
         for (int c0 = 0; c0 < p.Nout; c0 += 32) {
           float v[32];
           tc::tmem_ld32(ta + (uint32_t)c0, v);
@@ -221,78 +231,106 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
             for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(hrow + c0 * 2 + j * 16) = tc::pack8_bf16(v + 8 * j);
             if (p.gat) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) { ps = fmaf(v[j], asf[c0 + j], ps); pn = fmaf(v[j], anf[c0 + j], pn); }
+              for (int j = 0; j < 8; ++j) {
+                const float4 a = *reinterpret_cast<const float4*>(asf + c0 + 4 * j);
+                const float4 b = *reinterpret_cast<const float4*>(anf + c0 + 4 * j);
+                ps0 = fmaf(v[4 * j], a.x, ps0); ps1 = fmaf(v[4 * j + 1], a.y, ps1);
+                ps0 = fmaf(v[4 * j + 2], a.z, ps0); ps1 = fmaf(v[4 * j + 3], a.w, ps1);
+                pn0 = fmaf(v[4 * j], b.x, pn0); pn1 = fmaf(v[4 * j + 1], b.y, pn1);
+                pn0 = fmaf(v[4 * j + 2], b.z, pn0); pn1 = fmaf(v[4 * j + 3], b.w, pn1);
+              }
             }
           }
         }
-        if (p.gat && row < p.R) { ss[buf * RP + row] = ps; sn[buf * RP + row] = pn; }
+        if (p.gat && row < p.R) { ss[buf * RP + row] = ps0 + ps1; sn[buf * RP + row] = pn0 + pn1; }
       }
       tc::tc_fence_before();
       mbar_arrive(&h_full[buf]);
     }
   } else {
     // ================================ graph group ================================
-    const int gt = tid - SP_DRAIN_WARPS * 32;         // 0..255
+    const int gt = tid - SP_DRAIN_WARPS * 32;         // 0..511
     const int gw = gt >> 5;
     const int lg = lane >> 3, gl = lane & 7;
     const int R = p.R;
+    const bool two = p.Nout > 64;                     // a lane owns 8 features of each 64-feature half
     for (int i = 0; i < n_it; ++i) {
       const int buf = i & 1;
       const int smp = (int)blockIdx.x + i * (int)gridDim.x;
       tc::mbar_wait(&h_full[buf], (i >> 1) & 1);
       const uint8_t* hbase = smem + p.off_in + (size_t)buf * p.in_stride;
+      float* al = alpha + buf * p.nnz;
+      float* inv = inv_s + buf * RP;
       if (p.gat) {
-        // edge softmax over the CSR pattern: one thread per row
+        // edge softmax over the CSR pattern: 4 lanes per row, neighbours strided over the lanes
         const float* ssb = ss + buf * RP;
         const float* snb = sn + buf * RP;
-        for (int r = gt; r < R; r += SP_GRAPH_WARPS * 32) {
-          const int beg = rp_s[r], end = rp_s[r + 1];
-          const float si = ssb[r];
+        const int sub = gt & 3;
+        for (int r0 = 0; r0 < R; r0 += SP_GRAPH_WARPS * 8) {
+          const int r = r0 + (gt >> 2);
+          const bool live = r < R;
+          const int beg = live ? rp_s[r] : 0, end = live ? rp_s[r + 1] : 0;
+          const float si = live ? ssb[r] : 0.f;
           float mx = -INFINITY;
-          for (int qq = beg; qq < end; ++qq) {
+          for (int qq = beg + sub; qq < end; qq += 4) {
             float sc = si + snb[ci_s[qq]];
             sc = sc > 0.f ? sc : 0.2f * sc;
+            al[qq] = sc;
             mx = fmaxf(mx, sc);
           }
+          mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+          mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
           float den = 0.f;
-          for (int qq = beg; qq < end; ++qq) {
-            float sc = si + snb[ci_s[qq]];
-            sc = sc > 0.f ? sc : 0.2f * sc;
-            const float w = __expf(sc - mx);
-            alpha[qq] = w;
+          for (int qq = beg + sub; qq < end; qq += 4) {
+            const float w = __expf(al[qq] - mx);
+            al[qq] = w;
             den += w;
           }
-          inv_s[r] = 1.f / den;
+          den += __shfl_xor_sync(0xffffffffu, den, 1);
+          den += __shfl_xor_sync(0xffffffffu, den, 2);
+          if (live && sub == 0) inv[r] = 1.f / den;
         }
         graph_bar_sync();
       }
-      // weighted neighbour sum: 8 lanes per output row (8 features each per 64-feature block), 4 rows per warp pass
+      // weighted neighbour sum: 8 lanes per output row, a lane owns features [8gl, 8gl+8) and [64+8gl, 64+8gl+8)
       for (int r = gw * 4 + lg; r < R; r += SP_GRAPH_WARPS * 4) {
         const int beg = rp_s[r], end = rp_s[r + 1];
-        const float scale = p.gat ? inv_s[r] : 1.f;
+        const float scale = p.gat ? inv[r] : 1.f;
         bf16* orow = p.out + ((size_t)smp * R + r) * p.Nout + gl * 8;
-        for (int e0 = 0; e0 < p.Nout; e0 += 64) {
-          float acc[8];
+        for (int e0 = 0; e0 < p.Nout; e0 += 128) {
+          float a0[8], a1[8];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+          for (int k = 0; k < 8; ++k) { a0[k] = 0.f; a1[k] = 0.f; }
           const uint8_t* hb = hbase + (e0 + gl * 8) * 2;
           for (int qq = beg; qq < end; ++qq) {
-            const float w = alpha[qq];
-            const uint4 u = *reinterpret_cast<const uint4*>(hb + (size_t)ci_s[qq] * p.hsb);
+            const float w = al[qq];
+            const uint8_t* hp = hb + (size_t)ci_s[qq] * p.hsb;
+            const uint4 u0 = *reinterpret_cast<const uint4*>(hp);
             float hv[8];
-            tc::unpack8_bf16(u, hv);
+            tc::unpack8_bf16(u0, hv);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) acc[k] = fmaf(w, hv[k], acc[k]);
+            for (int k = 0; k < 8; ++k) a0[k] = fmaf(w, hv[k], a0[k]);
+            if (two) {
+              const uint4 u1 = *reinterpret_cast<const uint4*>(hp + 128);
+              tc::unpack8_bf16(u1, hv);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) a1[k] = fmaf(w, hv[k], a1[k]);
+            }
           }
           const float* bp = bias_s + e0 + gl * 8;
 #pragma unroll
-          for (int k = 0; k < 8; ++k) acc[k] = fmaf(acc[k], scale, bp[k]);
-          act_tile<8>(acc, p.act);
-          *reinterpret_cast<uint4*>(orow + e0) = tc::pack8_bf16(acc);
+          for (int k = 0; k < 8; ++k) a0[k] = fmaf(a0[k], scale, bp[k]);
+          act_tile<8>(a0, p.act);
+          *reinterpret_cast<uint4*>(orow + e0) = tc::pack8_bf16(a0);
+          if (two) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a1[k] = fmaf(a1[k], scale, bp[64 + k]);
+            act_tile<8>(a1, p.act);
+            *reinterpret_cast<uint4*>(orow + e0 + 64) = tc::pack8_bf16(a1);
+          }
         }
       }
-      graph_bar_sync();                               // everyone done with h / alpha of this sample
-      if (gt == 0) mbar_arrive(&in_empty[buf]);
+      mbar_arrive(&in_empty[buf]);                    // this thread is done with the h tile of the sample
     }
   }
   tc::tc_fence_before();

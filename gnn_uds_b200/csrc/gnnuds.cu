@@ -8,6 +8,7 @@
 #include "tc_gemm.cuh"
 #include "tc_selftest.cuh"
 #include "fused_sp.cuh"
+#include "fused_conv.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -72,7 +73,7 @@ struct gnnuds_handle {
   std::vector<uint8_t*> d_ne_img[2];
   uint32_t ne_img_bytes[2] = {0, 0}, ne_pstride[2] = {0, 0};
   int ne_kp[2] = {0, 0};
-  bool fused_on = true;                 // GNNUDS_FUSED=0 keeps the layer-by-layer tensor-core path
+  int fused_mode = 1;                   // GNNUDS_FUSED: 0 layer-by-layer kernels, 1 sp_conv_kernel (default), 2 conv_agg_kernel (experimental)
 
   // graph
   int *d_rp = nullptr, *d_ci = nullptr, *d_erp = nullptr, *d_eci = nullptr;
@@ -787,7 +788,7 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   const auto& c = h->c;
   const int E = c.embed, F = E / 2;
   const bool gat = c.conv == GNNUDS_CONV_GAT;
-  if (!h->fused_on || segs.empty() || segs.size() > 2 || R > 256 || Ro > 256 || R < 1 || F % 32 || E % 64 || E > 128) return -1;
+  if (h->fused_mode != 1 || segs.empty() || segs.size() > 2 || R > 256 || Ro > 256 || R < 1 || F % 32 || E % 64 || E > 128) return -1;
   if (S <= 0 || S * (long long)std::max(R, Ro) >= (1ll << 31)) return -1;
   SpConvP p{};
   p.nseg = (int)segs.size();
@@ -821,7 +822,7 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   const uint32_t nx_bytes = (uint32_t)(F / 8) * p.pstrideA;
   p.off_sc = al(p.off_nx + nx_bytes, 128);
   const uint32_t RP = 128u * p.MT;
-  const uint32_t sc_bytes = (3u * E + 5u * RP + (uint32_t)nnz) * 4u + ((uint32_t)R + 1u + (uint32_t)nnz) * 4u;
+  const uint32_t sc_bytes = (3u * E + 6u * RP + 2u * (uint32_t)nnz) * 4u + ((uint32_t)R + 1u + (uint32_t)nnz) * 4u;
   p.off_bar = al(p.off_sc + sc_bytes, 16);
   // operand views of M-tile mt read 128 rows from row mt*128 of every panel: keep those reads inside the allocation
   const uint32_t reach = p.off_nx + (uint32_t)(F / 8 - 1) * p.pstrideA + RP * 16u;
@@ -839,6 +840,78 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   sp_conv_kernel<<<grid, SP_THREADS, smem, h->stream>>>(p);
   ++h->launches;
   CU(cudaGetLastError());
+  return 0;
+}
+
+// ---- fused conv + aggregation on tensor cores (csrc/fused_conv.cuh) -------------------------------
+// Returns 0 launched, -1 not applicable, > 0 error.
+int launch_conv_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const LayerW& w, void* out, const int* rp,
+                    const int* ci, const float* val, int nnz, long long S, int R, int act) {
+  const auto& c = h->c;
+  const int E = c.embed;
+  const bool gat = c.conv == GNNUDS_CONV_GAT;
+  if (h->fused_mode != 2 || segs.empty() || segs.size() > 3 || R > 256 || R < 1 || E % 32 || E > 128) return -1;
+  if (S <= 0 || S * (long long)R >= (1ll << 31)) return -1;
+  ConvAggP p{};
+  p.nseg = (int)segs.size();
+  p.Ktot = 0;
+  for (int i = 0; i < p.nseg; ++i) {
+    const SegH& sg = segs[i];
+    if (sg.shift || sg.pitch != R || sg.off || sg.width % 16 || sg.ld % 8 || (reinterpret_cast<uintptr_t>(sg.p) & 15)) return -1;
+    p.segw[i] = sg.width; p.Ktot += sg.width;
+  }
+  if ((long long)p.Ktot * E != h->tens[w.t[0]].numel || h->img_off[w.t[0]] < 0) return -1;
+  p.S = (int)S; p.R = R; p.Nout = E; p.act = act; p.gat = gat ? 1 : 0;
+  p.Rbox = (R + 7) / 8 * 8; p.KpJ = (R + 15) / 16 * 16; p.MT = (R + 127) / 128;
+  p.pstrideA = (uint32_t)p.Rbox * 16u; p.pstrideH = (uint32_t)p.KpJ * 16u;
+  p.Wimg = h->d_wimg + h->img_off[w.t[0]]; p.w_bytes = (uint32_t)p.Ktot * E * 2u;
+  p.bias = W(h, w.t[gat ? 3 : 1]);
+  p.a_self = gat ? W(h, w.t[1]) : nullptr; p.a_neigh = gat ? W(h, w.t[2]) : nullptr;
+  p.row_ptr = rp; p.col_idx = ci; p.val = val; p.nnz = nnz;
+  p.out = static_cast<bf16*>(out);
+  auto al = [](uint32_t v, uint32_t a) { return (v + a - 1) / a * a; };
+  p.off_w = 0;
+  p.off_in = al(p.w_bytes, 1024);
+  p.in_bytes = (uint32_t)(p.Ktot / 8) * p.pstrideA;
+  p.alpha_bytes = (uint32_t)(p.KpJ / 8) * p.pstrideA;
+  p.in_stride = al(std::max(p.in_bytes, p.alpha_bytes), 1024);
+  p.off_h = p.off_in + 2 * p.in_stride;
+  const uint32_t h_bytes = (uint32_t)(E / 8) * p.pstrideH;
+  p.off_sc = al(p.off_h + h_bytes, 128);
+  const uint32_t RP = 128u * p.MT;
+  const uint32_t sc_bytes = (3u * E + 2u * RP) * 4u + ((uint32_t)R + 1u + 2u * (uint32_t)nnz) * 4u;
+  p.off_bar = al(p.off_sc + sc_bytes, 16);
+  const uint32_t reach = p.off_in + p.in_stride + (uint32_t)(std::max(p.Ktot, p.KpJ) / 8 - 1) * p.pstrideA + RP * 16u;
+  const size_t smem = std::max<size_t>(p.off_bar + 11 * 8 + 16, reach);
+  if (smem > 227 * 1024) return -1;
+  for (int i = 0; i < p.nseg; ++i)
+    if (!make_rows_tmap(&p.tm[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox, segs[i].width)) return -1;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CU(cudaFuncSetAttribute(conv_agg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  const unsigned grid = (unsigned)std::min<long long>(S, h->sm_count);
+  static int traced = 0;
+  const char* tf = getenv("GNNUDS_TRACE_FILE");
+  const int want = getenv("GNNUDS_TRACE_LAUNCH") ? atoi(getenv("GNNUDS_TRACE_LAUNCH")) : 0;
+  const bool do_trace = tf && S >= 64 * (long long)h->sm_count && traced++ == want;
+  p.trace_mode = getenv("GNNUDS_TRACE_MODE") ? atoi(getenv("GNNUDS_TRACE_MODE")) : 0;
+  if (do_trace) { CU(cudaMalloc(&p.trace, 64 * 8 * sizeof(long long))); CU(cudaMemset(p.trace, 0, 64 * 8 * sizeof(long long))); }
+  conv_agg_kernel<<<grid, CA_THREADS, smem, h->stream>>>(p);
+  ++h->launches;
+  CU(cudaGetLastError());
+  if (do_trace) {
+    std::vector<long long> t(64 * 8);
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaMemcpy(t.data(), p.trace, t.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+    cudaFree(p.trace);
+    if (FILE* f = fopen(tf, "w")) {
+      fprintf(f, "# conv_agg R=%d Ktot=%d: sample, cycles since first stamp: conv_issue_begin conv_committed drain_conv_begin h_ready alpha_ready agg_committed drain_out_begin out_done\n", R, p.Ktot);
+      for (int i = 0; i < 64; ++i) { fprintf(f, "%d", i); for (int k = 0; k < 8; ++k) fprintf(f, " %lld", t[i * 8 + k] ? t[i * 8 + k] - t[0] : -1); fprintf(f, "\n"); }
+      fclose(f);
+    }
+  }
   return 0;
 }
 
@@ -861,14 +934,18 @@ int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) 
     if (rc < 0) {
       if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, h->XE, h->NX, S, M, N, E2))) return rc;
       std::vector<SegH> sx = st.x; sx.push_back({h->NX, E2, E2, 0, N, 0});
-      if ((rc = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return rc;
+      rc = launch_conv_agg(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, act);
+      if (rc > 0) return rc;
+      if (rc < 0 && (rc = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return rc;
     }
     rc = launch_sp_conv(h, st.e, h->EX, 1, li, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, S, M, N, act);
     if (rc > 0) return rc;
     if (rc < 0) {
       if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, h->EX, h->NE, S, N, M, E2))) return rc;
       std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
-      if ((rc = run_conv_tc(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, Bc, T, M, act))) return rc;
+      rc = launch_conv_agg(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, S, M, act);
+      if (rc > 0) return rc;
+      if (rc < 0 && (rc = run_conv_tc(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, Bc, T, M, act))) return rc;
     }
     st.x = {{xo, E, E, 0, N, 0}};
     st.e = {{eo, E, E, 0, M, 0}};
@@ -1124,7 +1201,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, c.device);
   cudaEventCreate(&h->ev_a); cudaEventCreate(&h->ev_b);
   h->tma_on = !(getenv("GNNUDS_NO_TMA") && getenv("GNNUDS_NO_TMA")[0] == '1');
-  h->fused_on = !(getenv("GNNUDS_FUSED") && getenv("GNNUDS_FUSED")[0] == '0');
+  if (getenv("GNNUDS_FUSED")) h->fused_mode = atoi(getenv("GNNUDS_FUSED"));
   LayoutBuilder lb{h};
   lb.build();
   *out = h;
