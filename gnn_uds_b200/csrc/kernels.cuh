@@ -89,6 +89,47 @@ __global__ void __launch_bounds__(256) embed_kernel(EmbedP p) {
   const int rows_per_blk = blockDim.x / g4;
   const int lr = threadIdx.x / g4, c4 = threadIdx.x % g4;
   if (lr >= rows_per_blk) return;
+  if (g4 <= 32 && g4 >= p.K && (g4 & (g4 - 1)) == 0 && p.rows < (1ll << 31)) {
+    // fast path: the g4 lanes of a row split the K input channels (one normalisation each) and exchange them
+    // by shuffle; 32-bit row arithmetic.  Same operation order per output as the generic path below.
+    const unsigned rows = (unsigned)p.rows, Nn = (unsigned)p.Nn, Tn = (unsigned)p.T;
+    const float4 bb = *reinterpret_cast<const float4*>(bs + c4 * 4);
+    float mx = 1.f, mn = 0.f;
+    const unsigned step = gridDim.x * (unsigned)rows_per_blk;
+    const unsigned r_first = blockIdx.x * (unsigned)rows_per_blk + (unsigned)lr;
+    const unsigned n_iter = (rows + step - 1) / step;          // uniform trip count: shuffles stay convergent
+    for (unsigned it = 0, r = r_first; it < n_iter; ++it, r += step) {
+      const bool live = r < rows;
+      const unsigned rr = live ? r : 0;
+      const unsigned n = rr % Nn, bt = rr / Nn;
+      float mine = 0.f;
+      if (p.mode == 2) {
+        if (c4 == 0) { const int k = p.gather[n]; mine = (k >= 0) ? p.in[(size_t)bt * p.n_act + k] : 1.f; }
+      } else if (c4 < p.K) {
+        mine = p.in[(size_t)rr * p.K + c4];
+        if (p.nmax) {
+          mx = p.nmax[n * p.cn + c4]; mn = p.nmin[n * p.cn + c4];
+          mine = (mine - mn) / (mx - mn);
+        }
+      }
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int c = 0; c < p.K; ++c) {
+        const float xc = __shfl_sync(0xffffffffu, mine, c, g4);
+        const float4 w = *reinterpret_cast<const float4*>(Ws + c * p.Eo + c4 * 4);
+        s.x = fmaf(xc, w.x, s.x); s.y = fmaf(xc, w.y, s.y); s.z = fmaf(xc, w.z, s.z); s.w = fmaf(xc, w.w, s.w);
+      }
+      float4 acc = make_float4(bb.x + s.x, bb.y + s.y, bb.z + s.z, bb.w + s.w);
+      if (!live) continue;
+      if (p.res) {
+        const unsigned t = bt % Tn;
+        if (t == Tn - 1) *reinterpret_cast<float4*>(p.res + ((size_t)(bt / Tn) * Nn + n) * p.Eo + c4 * 4) = acc;
+      }
+      acc.x = apply_act(acc.x, p.act); acc.y = apply_act(acc.y, p.act);
+      acc.z = apply_act(acc.z, p.act); acc.w = apply_act(acc.w, p.act);
+      st4(static_cast<T*>(p.out) + (size_t)rr * p.Eo + c4 * 4, acc);
+    }
+    return;
+  }
   for (long long r = (long long)blockIdx.x * rows_per_blk + lr; r < p.rows;
        r += (long long)gridDim.x * rows_per_blk) {
     const int n = (int)(r % p.Nn);
@@ -786,6 +827,51 @@ __global__ void __launch_bounds__(256) head_kernel(HeadP p) {
   const int lane = threadIdx.x & 31;
   const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  if (p.K % 128 == 0 && p.K <= 256 && p.ld % 4 == 0) {
+    // fast path: a lane owns 4 consecutive input columns per 128-column block (one 8/16-byte load per row),
+    // its weight rows live in registers, two rows per iteration; one butterfly reduction per output.
+    const int nb = p.K >> 7;
+    float wreg[2][4][4];
+#pragma unroll
+    for (int b = 0; b < 2; ++b)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int o = 0; o < 4; ++o) wreg[b][j][o] = (b < nb && o < p.Nout) ? Ws[(b * 128 + lane * 4 + j) * p.Nout + o] : 0.f;
+    float bo[4];
+#pragma unroll
+    for (int o = 0; o < 4; ++o) bo[o] = o < p.Nout ? p.bias[o] : 0.f;
+    for (long long r = w * 2; r < p.rows; r += nw * 2) {
+      float acc[2][4];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+#pragma unroll
+        for (int o = 0; o < 4; ++o) acc[u][o] = 0.f;
+        if (r + u < p.rows) {
+#pragma unroll
+          for (int b = 0; b < 2; ++b) {
+            if (b < nb) {
+              const float4 v = ld4(static_cast<const T*>(p.in) + (r + u) * p.ld + b * 128 + lane * 4);
+#pragma unroll
+              for (int o = 0; o < 4; ++o)
+                acc[u][o] = fmaf(v.x, wreg[b][0][o], fmaf(v.y, wreg[b][1][o], fmaf(v.z, wreg[b][2][o], fmaf(v.w, wreg[b][3][o], acc[u][o]))));
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+#pragma unroll
+        for (int o = 0; o < 4; ++o)
+          if (o < p.Nout) acc[u][o] = warp_sum(acc[u][o]);
+      if (lane < 2 && r + lane < p.rows) {
+#pragma unroll
+        for (int o = 0; o < 4; ++o)
+          if (o < p.Nout) p.out[(r + lane) * p.ldo + p.col0 + o] = apply_act((lane ? acc[1][o] : acc[0][o]) + bo[o], p.act);
+      }
+    }
+    return;
+  }
   for (long long r = w; r < p.rows; r += nw) {
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     for (int k = lane; k < p.K; k += 32) {

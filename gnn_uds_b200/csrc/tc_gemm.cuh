@@ -222,6 +222,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
       for (int s = 0; s < p.nseg; ++s) any_cp |= !p.use_tma[s];
       const uint32_t w_addr = tc::smem_u32(Wsm), st_addr = tc::smem_u32(stages);
       const uint32_t pstrideW = (uint32_t)p.Nout * 16u;
+      const uint32_t stage_bytes = p.stage_bytes;
+      const int kpc = p.kc / 16, Nout = p.Nout;
+      const bool MT2 = p.MT > 1;
+      const uint64_t a_desc0 = tc::smem_desc(st_addr, p.pstrideA, 128u), w_desc0 = tc::smem_desc(w_addr, pstrideW, 128u);
+      const uint64_t a_step = (uint64_t)((2u * p.pstrideA) >> 4), w_step = (uint64_t)((2u * pstrideW) >> 4);
       unsigned tile_it = 0;
       int stage = 0;
       uint32_t fphase = 0;
@@ -230,18 +235,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
         if (tile_it >= 2) tc::mbar_wait(&tempty[as], ((tile_it >> 1) & 1) ^ 1);
         tc::tc_fence_after();
         const uint32_t acc = tmem + (uint32_t)as * 256u;
+        uint64_t bd = w_desc0;
         for (int ch = 0; ch < nchunk; ++ch) {
           tc::mbar_wait(&full[stage], fphase);
           if (any_cp) tc::fence_async_smem();  // cp.async (generic proxy) writes -> tensor-core (async proxy) reads
           tc::tc_fence_after();
-          const uint32_t sa = st_addr + (uint32_t)stage * p.stage_bytes;
-          for (int ks = 0; ks < p.kc / 16; ++ks) {
-            const uint32_t kg = (uint32_t)(ch * (p.kc / 16) + ks);
-            const uint64_t bd = tc::smem_desc(w_addr + 2u * kg * pstrideW, pstrideW, 128u);
-            for (int mt = 0; mt < p.MT; ++mt) {
-              const uint64_t ad = tc::smem_desc(sa + (uint32_t)mt * 2048u + 2u * ks * p.pstrideA, p.pstrideA, 128u);
-              tc::umma(acc + (uint32_t)(mt * p.Nout), ad, bd, idesc, (ch | ks) != 0);
-            }
+          // descriptors advance linearly with the start address: one 64-bit add per MMA in the issue loop
+          uint64_t ad = a_desc0 + (uint64_t)(((uint32_t)stage * stage_bytes) >> 4);
+#pragma unroll 4
+          for (int ks = 0; ks < kpc; ++ks, ad += a_step, bd += w_step) {
+            tc::umma(acc, ad, bd, idesc, (ch | ks) != 0);
+            if (MT2) tc::umma(acc + (uint32_t)Nout, ad + 128u, bd, idesc, (ch | ks) != 0);
           }
           tc::umma_commit(&empty[stage]);
           if (++stage == NS) { stage = 0; fphase ^= 1; }
