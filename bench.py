@@ -37,15 +37,19 @@ def flops(em, B):
     E, H, S, P, k = em.embed_size, em.hidden_dim, em.n_sp_layer, em.n_tp_layer, em.kernel_size
     N, M, Ti, To, F = em.n_node, em.n_edge, em.seq_in, em.seq_out, em.if_flood
     act = 1 if em.act else 0
-    nnz_n, nnz_m = em.filter_csr.nnz, em.edge_filter_csr.nnz
+    nnz_n, nnz_m = em.filter_csr.nnz, (em.edge_filter_csr.nnz if em.edge_filter_csr is not None else 0)
     gat = em.conv_kind == "gat"
     tot = 2 * (B * Ti * (N * em.n_in + M * em.e_in) * E + B * To * (N * em.b_in + M * act) * E // 2)
     gemm = 0
     for blk, T in ((0, Ti), (1, To)):
         cx, ce = (E, E) if blk == 0 else (H + E // 2, H + (E // 2) * act)
         for l in range(S):
-            g = M * ce * (E // 2) + N * cx * (E // 2) + N * (cx + E // 2) * E + M * (ce + E // 2) * E
-            o = 2 * N * M * (E // 2) + (2 * (N + M) * E if gat else 0) + (nnz_n + nnz_m) * E
+            if em.graph_base:      # one conv over the joint node+edge graph (emulator.py:220-223)
+                g = (N * cx + M * ce) * E
+                o = (2 * (N + M) * E if gat else 0) + nnz_n * E
+            else:
+                g = M * ce * (E // 2) + N * cx * (E // 2) + N * (cx + E // 2) * E + M * (ce + E // 2) * E
+                o = 2 * N * M * (E // 2) + (2 * (N + M) * E if gat else 0) + (nnz_n + nnz_m) * E
             gemm += 2 * B * T * g
             tot += 2 * B * T * (g + o)
             cx = ce = E
@@ -60,6 +64,34 @@ def flops(em, B):
     tot += 2 * B * To * (heads_g + heads_o)
     gemm += 2 * B * To * heads_g
     return float(tot), float(gemm)
+
+
+def dominant_kernel(em, B, precision):
+    """Which kernel family dominates a step and its ALGORITHMIC bytes per step.
+    graph_base=0, tensor-core path: sp_conv_kernel (fused NodeEdge+conv+aggregation), HBM-bound by its
+    arithmetic intensity (~100 FLOP/B < 212 FLOP/B machine balance): per sample and side it must read
+    self (R x Kself) + other_dense (Ro x E/2) and write out (R x E), bf16.
+    graph_base=1: agg_large_kernel (CSR gather): nnz*E gathered + R*E written per sample and layer.
+    fp32 path: the rows-GEMM family (tensor roofline kept for reference)."""
+    E, H, S = em.embed_size, em.hidden_dim, em.n_sp_layer
+    N, M, Ti, To = em.n_node, em.n_edge, em.seq_in, em.seq_out
+    es = 2 if precision == "bf16" else 4
+    if em.graph_base:
+        R, nnz = N + M, em.filter_csr.nnz
+        per_sample = (nnz * E + R * E) * es
+        return dict(family=2, kernel="agg_large_kernel (CSR neighbour gather, joint node+edge graph)", bound="hbm",
+                    bytes=float(B * (Ti + To) * S * per_sample), unit_note="(nnz*E gathered + (N+M)*E written) * %d B per (b,t) sample and layer" % es)
+    if precision != "bf16":
+        return dict(family=0, kernel="rows_gemm_f32 (all Dense/conv-linear/Conv1D launches of a step)", bound="tensor", bytes=None, unit_note="")
+    act = 1 if em.act else 0
+    tot = 0
+    for blk, T in ((0, Ti), (1, To)):
+        cx, ce = (E, E) if blk == 0 else (H + E // 2, H + (E // 2) * act)
+        for l in range(S):
+            tot += B * T * ((N * cx + M * (E // 2) + N * E) + (M * ce + N * (E // 2) + M * E)) * 2
+            cx = ce = E
+    return dict(family=1, kernel="sp_conv_kernel (fused NodeEdge + conv + GAT/GCN aggregation, both stream sides)", bound="hbm",
+                bytes=float(tot), unit_note="per sample and side: (R*Kself + Ro*E/2 read + R*E written) * 2 B")
 
 
 class ClockSampler:
@@ -111,6 +143,19 @@ def peaks():
         d = json.load(open(p))
         return d.get("bf16_tflops_sustained", 1399.6), d.get("hbm_gbs", 6554.6), "measured"
     return 1400.0, 6650.0, "fallback"
+
+
+def traffic_per_launch(dom, workload, B, launches_per_step):
+    """dram__bytes_read + dram__bytes_write per launch of the dominant kernel from the committed ncu capture
+    (profiles/r01_traffic.json: bytes per scenario and step, measured at one batch size; the kernels stream
+    scenarios independently, so the figure scales linearly with B)."""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if not os.path.exists(p):
+        return None
+    d = json.load(open(p)).get(workload, {}).get(dom["kernel"].split(" ")[0])
+    if not d:
+        return None
+    return d["dram_bytes_per_scenario_step"] * B / launches_per_step
 
 
 def cpu_baseline(workload, seconds=20.0):
@@ -231,10 +276,17 @@ def main():
     l0 = em.launch_count()
     em.set_profiling(2)             # CUDA events on the library's own stream (torch events cannot see it); 2 = also per-GEMM pairs
     tot_ms, gemm_ms = 0.0, 0.0
+    dom = dominant_kernel(em, B, precision)
+    dom_ms, dom_launches = 0.0, 0
+    fam_ms = [0.0] * 4
     for _ in range(a.steps):
         step_dev()
         t, g = em.last_timing()
         tot_ms += t; gemm_ms += g
+        fm, fl = em.kernel_timing(dom["family"])
+        dom_ms += fm; dom_launches += fl
+        for f in range(4):
+            fam_ms[f] += em.kernel_timing(f)[0]
     barrier()
     launches = em.launch_count() - l0
     # the per-GEMM event pairs perturb the stream slightly; time the K steps again without them
@@ -295,7 +347,27 @@ def main():
         tot_f, gemm_f = flops(em, B)
         tf_peak, hbm_peak, src = peaks()
         gemm_ms_per_step = gemm_ms / a.steps
-        achieved = gemm_f / (gemm_ms_per_step * 1e-3) / 1e12 if gemm_ms_per_step > 0 else None
+        dom_ms_per_step = dom_ms / a.steps
+        launches_per_step = max(dom_launches // a.steps, 1)
+        extra = {"kernel": dom["kernel"], "launches_per_step": launches_per_step, "kernel_ms_per_step": dom_ms_per_step,
+                 "avg_launch_ms": dom_ms_per_step / launches_per_step, "share_of_step": dom_ms_per_step / ms_per_step,
+                 "algorithmic": dom["unit_note"], "total_flops_per_step": tot_f,
+                 "step_tflops": tot_f / (ms_per_step * 1e-3) / 1e12, "step_tflops_frac_of_bf16_peak": tot_f / (ms_per_step * 1e-3) / 1e12 / tf_peak,
+                 "family_ms_per_step": {"rows_gemm": fam_ms[0] / a.steps, "fused_spatial": fam_ms[1] / a.steps,
+                                        "csr_gather": fam_ms[2] / a.steps, "recurrent": fam_ms[3] / a.steps,
+                                        "note": "per-launch event pairs of a separate K-step pass; the rest of the step is embed/heads/post-processing"}}
+        if dom["bound"] == "hbm":
+            achieved = dom["bytes"] / (dom_ms_per_step * 1e-3) / 1e9 if dom_ms_per_step > 0 else None
+            roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": (achieved / hbm_peak) if achieved else None,
+                        "traffic": traffic_per_launch(dom, a.workload, B, launches_per_step),
+                        "algorithmic_bytes_per_launch": dom["bytes"] / launches_per_step, "peak_source": "%s hbm_gbs" % src}
+        else:
+            achieved = gemm_f / (gemm_ms_per_step * 1e-3) / 1e12 if gemm_ms_per_step > 0 else None
+            roofline = {"bound": "tensor", "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s",
+                        "frac": (achieved / tf_peak) if achieved else None, "traffic": None,
+                        "peak_source": "%s bf16_tflops_sustained" % src, "gemm_flops_per_step": gemm_f}
+        roofline.update(extra)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -308,12 +380,7 @@ def main():
                     "note": "Emulator.predict_ptrs with pinned host buffers, wall clock incl. copies"},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "tensor", "kernel": "rows_gemm (all Dense/conv-linear/Conv1D launches of a step)",
-                         "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s",
-                         "frac": (achieved / tf_peak) if achieved else None, "traffic": None,
-                         "peak_source": "%s bf16_tflops_sustained" % src,
-                         "gemm_ms_per_step": gemm_ms_per_step, "gemm_flops_per_step": gemm_f,
-                         "total_flops_per_step": tot_f, "step_tflops": tot_f / (ms_per_step * 1e-3) / 1e12},
+            "roofline": roofline,
             "wall_s_timed_region": wall,
         }
         if world == 1 and not a.no_cpu:

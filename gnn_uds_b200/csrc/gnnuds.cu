@@ -48,7 +48,10 @@ struct gnnuds_handle {
   int profiling = 0;            // 0 off, 1 whole-call event pair, 2 also one pair per GEMM launch
   float last_total_ms = 0.f, last_gemm_ms = 0.f;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> gemm_ev;
+  std::vector<int> ev_family;           // kernel family of each event pair (GNNUDS_FAM_*)
   size_t gemm_ev_used = 0;
+  float fam_ms[4] = {0.f, 0.f, 0.f, 0.f};
+  int64_t fam_launches[4] = {0, 0, 0, 0};
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;
 
   // layout
@@ -258,6 +261,28 @@ int grid_for(const gnnuds_handle* h, long long work_items, int per_block, int ma
 }
 
 // ---- launch helpers -------------------------------------------------------------------
+
+// per-launch CUDA event pairs (profiling level 2), tagged with a kernel family
+int prof_begin(gnnuds_handle* h, int family, cudaEvent_t* e1) {
+  *e1 = nullptr;
+  if (h->profiling < 2) return 0;
+  if (h->gemm_ev_used == h->gemm_ev.size()) {
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
+    h->gemm_ev.push_back({a, b});
+    h->ev_family.push_back(0);
+  }
+  h->ev_family[h->gemm_ev_used] = family;
+  *e1 = h->gemm_ev[h->gemm_ev_used].second;
+  CU(cudaEventRecord(h->gemm_ev[h->gemm_ev_used].first, h->stream));
+  ++h->gemm_ev_used;
+  return 0;
+}
+int prof_end(gnnuds_handle* h, cudaEvent_t e1) {
+  if (e1) CU(cudaEventRecord(e1, h->stream));
+  return 0;
+}
+
 struct SegH { const float* p; int ld; int width; int shift; int pitch; int off; };
 
 int launch_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, const float* Wp, const float* bias, float* out,
@@ -272,17 +297,8 @@ int launch_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, const float* Wp
   p.W = Wp; p.bias = bias; p.out = out; p.ldo = ldo; p.Nout = Nout; p.act = act;
   p.rows = Bc * Td * Nn; p.Nn = Nn; p.Td = Td; p.Ts = Ts; p.pitch_d = pitch_d; p.off_d = off_d;
   if (p.rows == 0) return 0;
-  cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (h->profiling >= 2) {
-    if (h->gemm_ev_used == h->gemm_ev.size()) {
-      cudaEvent_t a, b;
-      CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
-      h->gemm_ev.push_back({a, b});
-    }
-    e0 = h->gemm_ev[h->gemm_ev_used].first; e1 = h->gemm_ev[h->gemm_ev_used].second;
-    ++h->gemm_ev_used;
-    CU(cudaEventRecord(e0, h->stream));
-  }
+  cudaEvent_t e1 = nullptr;
+  { int prc = prof_begin(h, GNNUDS_FAM_GEMM, &e1); if (prc) return prc; }
   const unsigned gx = (unsigned)((p.rows + 127) / 128);
   if (Nout % 128 == 0) {
     rows_gemm_f32<128><<<dim3(gx, Nout / 128), 256, 0, h->stream>>>(p);
@@ -296,7 +312,7 @@ int launch_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, const float* Wp
     return fail(h, GNNUDS_E_INVALID, "rows_gemm: Nout %d not a multiple of 16", Nout);
   }
   ++h->launches;
-  if (h->profiling >= 2) CU(cudaEventRecord(e1, h->stream));
+  { int prc = prof_end(h, e1); if (prc) return prc; }
   CU(cudaGetLastError());
   return 0;
 }
@@ -361,8 +377,11 @@ int launch_agg(gnnuds_handle* h, const void* hin, void* out, const int* rp, cons
       ++h->launches;
     }
     AggLargeP p{hin, out, rp, ci, val, h->SS, h->SN, bias, S, R, E, act, gat ? 1 : 0};
+    cudaEvent_t e1 = nullptr;
+    { int prc = prof_begin(h, GNNUDS_FAM_GATHER, &e1); if (prc) return prc; }
     agg_large_kernel<T><<<grid_for(h, S * R, 8, 32), 256, 0, h->stream>>>(p);
     ++h->launches;
+    { int prc = prof_end(h, e1); if (prc) return prc; }
   }
   CU(cudaGetLastError());
   return 0;
@@ -415,12 +434,18 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src
         GruP p{h->HB, W(h, L[i].t[1]), W(h, L[i].t[2]) + G, o, nseq, Nn, Ts, Tdst, H};
         const size_t smem = ((size_t)H * G + 32 * H + 32 * G) * sizeof(float);
         CU(cudaFuncSetAttribute(gru_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaEvent_t e1 = nullptr;
+        { int prc = prof_begin(h, GNNUDS_FAM_RECURRENT, &e1); if (prc) return prc; }
         gru_kernel<float><<<g, 256, smem, h->stream>>>(p);
+        { int prc = prof_end(h, e1); if (prc) return prc; }
       } else {
         LstmP p{h->HB, W(h, L[i].t[1]), o, nseq, Nn, Ts, Tdst, H};
         const size_t smem = ((size_t)H * G + 64 * H + 32 * G) * sizeof(float);
         CU(cudaFuncSetAttribute(lstm_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaEvent_t e1 = nullptr;
+        { int prc = prof_begin(h, GNNUDS_FAM_RECURRENT, &e1); if (prc) return prc; }
         lstm_kernel<float><<<g, 256, smem, h->stream>>>(p);
+        { int prc = prof_end(h, e1); if (prc) return prc; }
       }
       ++h->launches;
       CU(cudaGetLastError());
@@ -494,7 +519,9 @@ int run_postproc(gnnuds_handle* h, const float* b, const float* a, long long Bc,
   p.if_flood = c.if_flood ? 1 : 0; p.edge_fusion = c.edge_fusion; p.act = c.act; p.tide = c.tide;
   p.normalised = normalised_io ? 1 : 0; p.epsilon = c.epsilon;
   if (normalised_io && c.tide) return fail(h, GNNUDS_E_INVALID, "ROLL_NORM with tide not supported");
-  postproc_kernel<<<grid_for(h, p.S, 1, 16), 128, (size_t)M * sizeof(float), h->stream>>>(p);
+  const bool big = (size_t)M * sizeof(float) > 40 * 1024;      // large graphs: edge flows staged in HBM scratch (SS covers Bc*T*max(N,M))
+  p.efl_g = big ? h->SS : nullptr;
+  postproc_kernel<<<grid_for(h, p.S, 1, 16), big ? 512 : 128, big ? 0 : (size_t)M * sizeof(float), h->stream>>>(p);
   ++h->launches;
   CU(cudaGetLastError());
   return 0;
@@ -688,17 +715,8 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
   p.sc_off = p.h_off + h_bytes;
   p.bar_off = (p.sc_off + sc_bytes + 15u) & ~15u;
   const size_t smem = p.bar_off + (size_t)(2 * p.NS + 6) * 8 + 16;
-  cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (h->profiling >= 2) {
-    if (h->gemm_ev_used == h->gemm_ev.size()) {
-      cudaEvent_t a, b;
-      CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
-      h->gemm_ev.push_back({a, b});
-    }
-    e0 = h->gemm_ev[h->gemm_ev_used].first; e1 = h->gemm_ev[h->gemm_ev_used].second;
-    ++h->gemm_ev_used;
-    CU(cudaEventRecord(e0, h->stream));
-  }
+  cudaEvent_t e1 = nullptr;
+  { int prc = prof_begin(h, GNNUDS_FAM_GEMM, &e1); if (prc) return prc; }
   static bool attr_set = false;
   if (!attr_set) {
     CU(cudaFuncSetAttribute(tc_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -707,7 +725,7 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
   const unsigned grid = std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count);
   tc_rows_kernel<<<grid, TC_THREADS, smem, h->stream>>>(p);
   ++h->launches;
-  if (h->profiling >= 2) CU(cudaEventRecord(e1, h->stream));
+  { int prc = prof_end(h, e1); if (prc) return prc; }
   CU(cudaGetLastError());
   return 0;
 }
@@ -740,12 +758,18 @@ int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& 
         GruP p{h->HB, W(h, L[i].t[1]), W(h, L[i].t[2]) + G, o, nseq, Nn, Ts, Tdst, H};
         const size_t smem = ((size_t)H * G + 32 * H + 32 * G) * sizeof(float);
         CU(cudaFuncSetAttribute(gru_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaEvent_t e1 = nullptr;
+        { int prc = prof_begin(h, GNNUDS_FAM_RECURRENT, &e1); if (prc) return prc; }
         gru_kernel<bf16><<<g, 256, smem, h->stream>>>(p);
+        { int prc = prof_end(h, e1); if (prc) return prc; }
       } else {
         LstmP p{h->HB, W(h, L[i].t[1]), o, nseq, Nn, Ts, Tdst, H};
         const size_t smem = ((size_t)H * G + 64 * H + 32 * G) * sizeof(float);
         CU(cudaFuncSetAttribute(lstm_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaEvent_t e1 = nullptr;
+        { int prc = prof_begin(h, GNNUDS_FAM_RECURRENT, &e1); if (prc) return prc; }
         lstm_kernel<bf16><<<g, 256, smem, h->stream>>>(p);
+        { int prc = prof_end(h, e1); if (prc) return prc; }
       }
       ++h->launches;
       CU(cudaGetLastError());
@@ -837,8 +861,11 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
     attr_set = true;
   }
   const unsigned grid = (unsigned)std::min<long long>(S, h->sm_count);
+  cudaEvent_t e1 = nullptr;
+  { int prc = prof_begin(h, GNNUDS_FAM_SPATIAL, &e1); if (prc) return prc; }
   sp_conv_kernel<<<grid, SP_THREADS, smem, h->stream>>>(p);
   ++h->launches;
+  { int prc = prof_end(h, e1); if (prc) return prc; }
   CU(cudaGetLastError());
   return 0;
 }
@@ -898,8 +925,11 @@ int launch_conv_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const Layer
   const bool do_trace = tf && S >= 64 * (long long)h->sm_count && traced++ == want;
   p.trace_mode = getenv("GNNUDS_TRACE_MODE") ? atoi(getenv("GNNUDS_TRACE_MODE")) : 0;
   if (do_trace) { CU(cudaMalloc(&p.trace, 64 * 8 * sizeof(long long))); CU(cudaMemset(p.trace, 0, 64 * 8 * sizeof(long long))); }
+  cudaEvent_t e1 = nullptr;
+  { int prc = prof_begin(h, GNNUDS_FAM_SPATIAL, &e1); if (prc) return prc; }
   conv_agg_kernel<<<grid, CA_THREADS, smem, h->stream>>>(p);
   ++h->launches;
+  { int prc = prof_end(h, e1); if (prc) return prc; }
   CU(cudaGetLastError());
   if (do_trace) {
     std::vector<long long> t(64 * 8);
@@ -1140,13 +1170,14 @@ void begin_timing(gnnuds_handle* h) { h->gemm_ev_used = 0; h->last_total_ms = 0.
 
 int finish_timing(gnnuds_handle* h) {
   if (!h->profiling) return 0;
-  float g = 0.f;
+  for (int f = 0; f < 4; ++f) { h->fam_ms[f] = 0.f; h->fam_launches[f] = 0; }
   for (size_t i = 0; i < h->gemm_ev_used; ++i) {
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, h->gemm_ev[i].first, h->gemm_ev[i].second));
-    g += ms;
+    h->fam_ms[h->ev_family[i] & 3] += ms;
+    ++h->fam_launches[h->ev_family[i] & 3];
   }
-  h->last_gemm_ms = g;
+  h->last_gemm_ms = h->fam_ms[GNNUDS_FAM_GEMM];
   return 0;
 }
 
@@ -1662,6 +1693,12 @@ int gnnuds_last_timing(const gnnuds_handle* h, float* total_ms, float* gemm_ms) 
   if (!h) return GNNUDS_E_INVALID;
   if (total_ms) *total_ms = h->last_total_ms;
   if (gemm_ms) *gemm_ms = h->last_gemm_ms;
+  return 0;
+}
+int gnnuds_kernel_timing(const gnnuds_handle* h, int32_t family, float* ms, int64_t* launches) {
+  if (!h || family < 0 || family > 3) return GNNUDS_E_INVALID;
+  if (ms) *ms = h->fam_ms[family];
+  if (launches) *launches = h->fam_launches[family];
   return 0;
 }
 int gnnuds_set_profiling(gnnuds_handle* h, int32_t on) {

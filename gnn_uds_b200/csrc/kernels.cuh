@@ -909,11 +909,13 @@ struct PostP {
   int N, M, b_in, n_out, e_out, ny;
   int if_flood, edge_fusion, act, tide, normalised;
   float epsilon;
+  float* efl_g;           // (S, M) scratch for the physical edge flows when M floats exceed shared memory, else null
 };
 
-__global__ void __launch_bounds__(128) postproc_kernel(PostP p) {
-  extern __shared__ float efl[];     // M physical edge flows
+__global__ void __launch_bounds__(512) postproc_kernel(PostP p) {
+  extern __shared__ float efl_s[];   // M physical edge flows
   for (long long s = blockIdx.x; s < p.S; s += gridDim.x) {
+    float* efl = p.efl_g ? p.efl_g + s * p.M : efl_s;
     __syncthreads();
     for (int m = threadIdx.x; m < p.M; m += blockDim.x) {
       const float* src = p.out_e + (s * p.M + m) * p.lde;

@@ -424,6 +424,12 @@ class Emulator:
         self._lib.gnnuds_last_timing(self._h, C.byref(t), C.byref(g))
         return t.value, g.value
 
+    def kernel_timing(self, family):
+        """(ms, launches) of one kernel family in the last call (profiling level 2): 0 rows GEMM, 1 fused spatial, 2 gather."""
+        t, n = C.c_float(), C.c_int64()
+        _lib.check(self._h, self._lib.gnnuds_kernel_timing(self._h, int(family), C.byref(t), C.byref(n)))
+        return t.value, n.value
+
     def debug_stage(self, stage, states, b, a=None, edge_state=None):
         """Test hook: run the forward up to `stage` and return the live (node, edge) streams."""
         x, b, a, ex = self._prep(states, b, a, edge_state)

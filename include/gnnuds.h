@@ -156,6 +156,13 @@ int64_t gnnuds_launch_count(const gnnuds_handle* h);
    compute (copies excluded) and of its dominant GEMM kernels. */
 int gnnuds_last_timing(const gnnuds_handle* h, float* total_ms, float* gemm_ms);
 int gnnuds_set_profiling(gnnuds_handle* h, int32_t on);
+/* With profiling level 2: summed device time and launch count of one kernel family in the last call.
+   No reference counterpart (the reference only prints wall-clock "Emulation time", main.py:362). */
+#define GNNUDS_FAM_GEMM 0     /* tc_rows_kernel / rows_gemm_f32: Dense, conv linear, Conv1D, GRU/LSTM projections */
+#define GNNUDS_FAM_SPATIAL 1  /* sp_conv_kernel / conv_agg_kernel: fused NodeEdge + conv + aggregation */
+#define GNNUDS_FAM_GATHER 2   /* agg_large_kernel: CSR neighbour gather of the large-graph path */
+#define GNNUDS_FAM_RECURRENT 3 /* gru_kernel / lstm_kernel: in-kernel time loop */
+int gnnuds_kernel_timing(const gnnuds_handle* h, int32_t family, float* ms, int64_t* launches);
 
 /* Test hook: stop the forward after `stage` (0 = off) and fetch the live node/edge
    streams of the first chunk.  which: 0 node stream, 1 edge stream. */
