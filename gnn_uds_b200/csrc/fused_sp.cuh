@@ -30,6 +30,7 @@ namespace gu {
 constexpr int SP_DRAIN_WARPS = 4;
 constexpr int SP_GRAPH_WARPS = 16;
 constexpr int SP_THREADS = (SP_DRAIN_WARPS + SP_GRAPH_WARPS + 2) * 32;   // 704
+constexpr int SP_BINS = SP_GRAPH_WARPS * 4;                               // 8-lane groups of the graph warps
 
 struct SpConvP {
   CUtensorMap tm_self[2];     // {8, S*R rows, w/8 panels}, box {8, Rbox, w/8}
@@ -39,6 +40,7 @@ struct SpConvP {
   const uint8_t* Mimg; uint32_t m_bytes;      // NodeEdge matrix image, panel stride pstrideM
   const float* bias; const float* a_self; const float* a_neigh;
   const int* row_ptr; const int* col_idx; const float* val; int nnz;
+  const int* bins;            // gather schedule: bin_ptr[SP_BINS+1] | bin_rows[R]  (gnnuds.cu::upload_bins)
   bf16* out;                  // (S*R, Nout)
   int S, R, Ro, Rbox, Kp, MT, Kself, F, Nout, act, gat;
   uint32_t pstrideA, pstrideM, pstrideX;      // bytes: self/NE panels (Rbox*16), Mat panels, other_dense panels (Kp*16)
@@ -71,6 +73,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
   float* alpha = inv_s + 2 * RP;
   int* rp_s = reinterpret_cast<int*>(alpha + 2 * p.nnz);
   int* ci_s = rp_s + p.R + 1;
+  int* bin_s = ci_s + p.nnz;         // bin_ptr[SP_BINS+1] | bin_rows[R]
 
   if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
   if (tid == 32) {
@@ -92,6 +95,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
     anf[i] = p.gat ? p.a_neigh[i] : 0.f;
   }
   for (int i = tid; i <= p.R; i += SP_THREADS) rp_s[i] = p.row_ptr[i];
+  for (int i = tid; i < SP_BINS + 1 + p.R; i += SP_THREADS) bin_s[i] = p.bins[i];
   for (int i = tid; i < p.nnz; i += SP_THREADS) { ci_s[i] = p.col_idx[i]; if (!p.gat) { alpha[i] = p.val[i]; alpha[p.nnz + i] = p.val[i]; } }
   {
     uint4* z = reinterpret_cast<uint4*>(smem + p.off_nx);
@@ -292,8 +296,12 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         }
         graph_bar_sync();
       }
-      // weighted neighbour sum: 8 lanes per output row, a lane owns features [8gl, 8gl+8) and [64+8gl, 64+8gl+8)
-      for (int r = gw * 4 + lg; r < R; r += SP_GRAPH_WARPS * 4) {
+      // weighted neighbour sum: 8 lanes per output row, a lane owns features [8gl, 8gl+8) and [64+8gl, 64+8gl+8).
+      // Each 8-lane group walks its own row list of the balanced schedule; two neighbours per step keep four
+      // 16-byte shared loads in flight.
+      const int bin = gw * 4 + lg;
+      for (int bi = bin_s[bin]; bi < bin_s[bin + 1]; ++bi) {
+        const int r = bin_s[SP_BINS + 1 + bi];
         const int beg = rp_s[r], end = rp_s[r + 1];
         const float scale = p.gat ? inv[r] : 1.f;
         bf16* orow = p.out + ((size_t)smp * R + r) * p.Nout + gl * 8;
@@ -302,7 +310,32 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
 #pragma unroll
           for (int k = 0; k < 8; ++k) { a0[k] = 0.f; a1[k] = 0.f; }
           const uint8_t* hb = hbase + (e0 + gl * 8) * 2;
-          for (int qq = beg; qq < end; ++qq) {
+          int qq = beg;
+          for (; qq + 1 < end; qq += 2) {
+            const float w0 = al[qq], w1 = al[qq + 1];
+            const uint8_t* hp0 = hb + (size_t)ci_s[qq] * p.hsb;
+            const uint8_t* hp1 = hb + (size_t)ci_s[qq + 1] * p.hsb;
+            const uint4 u00 = *reinterpret_cast<const uint4*>(hp0);
+            const uint4 u10 = *reinterpret_cast<const uint4*>(hp1);
+            uint4 u01 = u00, u11 = u10;
+            if (two) { u01 = *reinterpret_cast<const uint4*>(hp0 + 128); u11 = *reinterpret_cast<const uint4*>(hp1 + 128); }
+            float hv[8];
+            tc::unpack8_bf16(u00, hv);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a0[k] = fmaf(w0, hv[k], a0[k]);
+            tc::unpack8_bf16(u10, hv);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a0[k] = fmaf(w1, hv[k], a0[k]);
+            if (two) {
+              tc::unpack8_bf16(u01, hv);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) a1[k] = fmaf(w0, hv[k], a1[k]);
+              tc::unpack8_bf16(u11, hv);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) a1[k] = fmaf(w1, hv[k], a1[k]);
+            }
+          }
+          if (qq < end) {
             const float w = al[qq];
             const uint8_t* hp = hb + (size_t)ci_s[qq] * p.hsb;
             const uint4 u0 = *reinterpret_cast<const uint4*>(hp);

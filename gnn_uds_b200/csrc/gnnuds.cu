@@ -17,6 +17,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 using namespace gu;
@@ -76,10 +77,12 @@ struct gnnuds_handle {
   std::vector<uint8_t*> d_ne_img[2];
   uint32_t ne_img_bytes[2] = {0, 0}, ne_pstride[2] = {0, 0};
   int ne_kp[2] = {0, 0};
+  int fuse_heads = 1;                   // GNNUDS_FUSE_HEADS: 0 = separate cumsum / head kernels (debugging)
   int fused_mode = 1;                   // GNNUDS_FUSED: 0 layer-by-layer kernels, 1 sp_conv_kernel (default), 2 conv_agg_kernel (experimental)
 
   // graph
   int *d_rp = nullptr, *d_ci = nullptr, *d_erp = nullptr, *d_eci = nullptr;
+  int* d_bins[2] = {nullptr, nullptr};  // sp_conv gather schedule per stream side: bin_ptr[SP_BINS+1] | bin_rows[R]
   float *d_val = nullptr, *d_eval = nullptr;
   int nnz = 0, ennz = 0, n_adj = 0;
   int *d_edges = nullptr, *d_act_of_edge = nullptr, *d_act_out = nullptr, *d_act_in = nullptr;
@@ -98,6 +101,9 @@ struct gnnuds_handle {
   float *XA, *XB, *EA, *EB, *HB, *XE, *EX, *NX, *NE, *TX0, *TX1, *TE0, *TE1, *BEMB, *AEMB, *RES, *RESE,
       *OUTN, *OUTE, *SS, *SN, *HBJ = nullptr, *J0 = nullptr, *J1 = nullptr;
   float *in_x, *in_b, *in_a, *in_ex, *out_y, *out_ey;      // chunk staging on device
+  float *in2_x, *in2_b, *in2_a, *in2_ex, *out2_y, *out2_ey; // second staging set: copies of chunk i+1 / i-1 overlap compute of chunk i
+  cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+  cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
   // rollout state
   float *ro_x = nullptr, *ro_ex = nullptr, *ro_b = nullptr, *ro_a = nullptr;
   int64_t ro_B = 0;
@@ -326,6 +332,13 @@ int launch_embed(gnnuds_handle* h, const float* in, const float* nrm, int cn, in
   p.W = W(h, w.t[0]); p.bias = W(h, w.t[1]); p.out = out; p.res = res;
   p.rows = Bc * T * Nn; p.T = T; p.Nn = Nn; p.K = K; p.Eo = Eo; p.act = act; p.mode = mode;
   if (p.rows == 0) return 0;
+  if (std::is_same<ST, bf16>::value && mode == 0 && K <= 8 && (Eo == 128 || Eo == 64) && p.rows < (1ll << 31)) {
+    if (Eo == 128) embed_bf16_kernel<16><<<grid_for(h, p.rows, 16, 8), 256, 0, h->stream>>>(p);
+    else embed_bf16_kernel<8><<<grid_for(h, p.rows, 32, 8), 256, 0, h->stream>>>(p);
+    ++h->launches;
+    CU(cudaGetLastError());
+    return 0;
+  }
   const int rpb = 256 / (Eo / 4);
   embed_kernel<ST><<<grid_for(h, p.rows, rpb, 16), 256, (size_t)(K * Eo + Eo) * sizeof(float), h->stream>>>(p);
   ++h->launches;
@@ -653,9 +666,11 @@ uint32_t tc_agg_scratch_bytes(int MT, int Nout, int g, int R, int nnz, bool gat)
   return (uint32_t)(5 * 128 * MT + 3 * Nout + (gat ? g * nnz : nnz) + (R + 1) + nnz + 8) * 4u;
 }
 
+struct HeadArgs { const float* w; const float* b; float* out; int ldo, col, act; };
+
 int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor, const float* bias, void* out, int ldo,
                    int Nout, int act, long long Bc, int Nn, int Td, int Ts, int pitch_d, int off_d,
-                   const AggArgs* agg = nullptr) {
+                   const AggArgs* agg = nullptr, const HeadArgs* head = nullptr) {
   if (segs.empty() || segs.size() > 4) return fail(h, GNNUDS_E_INVALID, "tc_gemm: 1..4 segments");
   if (w_tensor < 0 || w_tensor >= (int)h->img_off.size() || h->img_off[w_tensor] < 0)
     return fail(h, GNNUDS_E_STATE, "tc_gemm: no bf16 image for weight tensor %d", w_tensor);
@@ -691,6 +706,10 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
     if (Nn != R || pitch_d != Nn || off_d != 0) return fail(h, GNNUDS_E_INVALID, "tc_gemm: aggregation needs sample-contiguous rows");
   } else {
     p.rpt = 128; p.MT = 1;
+    if (head) {
+      p.head_w = head->w; p.head_b = head->b; p.head_out = head->out; p.head_ldo = head->ldo; p.head_col = head->col;
+      p.head_act = head->act;
+    }
   }
   if (p.MT * Nout > 256) return fail(h, GNNUDS_E_INVALID, "tc_gemm: accumulator tile %d x %d exceeds TMEM stage", p.MT * 128, Nout);
   p.n_tiles = (unsigned)((rows + p.rpt - 1) / p.rpt);
@@ -706,7 +725,7 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
   }
   p.stage_off = (p.w_bytes + 127u) & ~127u;
   const uint32_t h_bytes = p.agg ? (((uint32_t)p.rpt * p.hsb + 127u) & ~127u) : 0u;
-  const uint32_t sc_bytes = p.agg ? tc_agg_scratch_bytes(p.MT, Nout, p.rpt / p.R, p.R, p.nnz, p.agg == 2) : (uint32_t)Nout * 4u;
+  const uint32_t sc_bytes = p.agg ? tc_agg_scratch_bytes(p.MT, Nout, p.rpt / p.R, p.R, p.nnz, p.agg == 2) : (uint32_t)Nout * 8u + 2048u;
   const uint32_t fixed = p.stage_off + h_bytes + sc_bytes + 256u + 4096u;
   const uint32_t cap = 227u * 1024u;
   if (fixed + 3u * p.stage_bytes > cap) return fail(h, GNNUDS_E_INVALID, "tc_gemm: tile does not fit shared memory");
@@ -832,7 +851,7 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   p.Mimg = h->d_ne_img[side][li]; p.m_bytes = h->ne_img_bytes[side];
   p.bias = W(h, w.t[gat ? 3 : 1]);
   p.a_self = gat ? W(h, w.t[1]) : nullptr; p.a_neigh = gat ? W(h, w.t[2]) : nullptr;
-  p.row_ptr = rp; p.col_idx = ci; p.val = val; p.nnz = nnz;
+  p.row_ptr = rp; p.col_idx = ci; p.val = val; p.nnz = nnz; p.bins = h->d_bins[side];
   p.out = static_cast<bf16*>(out);
   auto al = [](uint32_t v, uint32_t a) { return (v + a - 1) / a * a; };
   p.off_w = 0;
@@ -846,7 +865,8 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   const uint32_t nx_bytes = (uint32_t)(F / 8) * p.pstrideA;
   p.off_sc = al(p.off_nx + nx_bytes, 128);
   const uint32_t RP = 128u * p.MT;
-  const uint32_t sc_bytes = (3u * E + 6u * RP + 2u * (uint32_t)nnz) * 4u + ((uint32_t)R + 1u + (uint32_t)nnz) * 4u;
+  const uint32_t sc_bytes = (3u * E + 6u * RP + 2u * (uint32_t)nnz) * 4u + ((uint32_t)R + 1u + (uint32_t)nnz) * 4u +
+                            ((uint32_t)SP_BINS + 1u + (uint32_t)R) * 4u;
   p.off_bar = al(p.off_sc + sc_bytes, 16);
   // operand views of M-tile mt read 128 rows from row mt*128 of every panel: keep those reads inside the allocation
   const uint32_t reach = p.off_nx + (uint32_t)(F / 8 - 1) * p.pstrideA + RP * 16u;
@@ -1032,7 +1052,22 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
   const int ract = c.resnet ? ACT_LINEAR : act;
   if ((rc = launch_tc_gemm(h, st.x, h->resx.t[0], W(h, h->resx.t[1]), h->XA, E, E, ract, Bc, N, To, To, N, 0))) return rc;
   if ((rc = launch_tc_gemm(h, st.e, h->rese.t[0], W(h, h->rese.t[1]), h->EA, E, E, ract, Bc, M, To, To, M, 0))) return rc;
-  if (c.resnet) {
+  const long long RXo = Bc * To * N, REo = Bc * To * M;
+  const int ldn = h->ldn();
+  // resnet + narrow heads in one pass per stream (E == 128): x = act(cumsum_t(x_out) + res) feeds the hard_sigmoid /
+  // tanh head straight from registers; the edge stream's x is not written back at all (nothing else reads it),
+  // the node stream's only when the flood chain needs it
+  const bool fuse_ch = c.resnet && E == 128 && h->fuse_heads && !h->debug_stop && c.n_out <= 4 && c.e_out <= 4;
+  if (fuse_ch) {
+    CumHeadP px{reinterpret_cast<bf16*>(h->XA), h->RES, Bc, To, N, act, c.if_flood ? 1 : 0,
+                W(h, h->head_out.t[0]), W(h, h->head_out.t[1]), h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID};
+    cumsum_head_bf16_kernel<<<grid_for(h, Bc * N, 8, 8), 256, 0, h->stream>>>(px);
+    CumHeadP pe{reinterpret_cast<bf16*>(h->EA), h->RESE, Bc, To, M, act, 0,
+                W(h, h->head_e.t[0]), W(h, h->head_e.t[1]), h->OUTE, c.e_out, 0, c.e_out, ACT_TANH};
+    cumsum_head_bf16_kernel<<<grid_for(h, Bc * M, 8, 8), 256, 0, h->stream>>>(pe);
+    h->launches += 2;
+    CU(cudaGetLastError());
+  } else if (c.resnet) {
     cumsum_res_act_kernel<bf16><<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(reinterpret_cast<bf16*>(h->XA), h->RES, Bc, To, N, E, act);
     cumsum_res_act_kernel<bf16><<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(reinterpret_cast<bf16*>(h->EA), h->RESE, Bc, To, M, E, act);
     h->launches += 2;
@@ -1042,20 +1077,22 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
   st.e = {{h->EA, E, E, 0, M, 0}};
   set_dbg(h, st, Bc * To * N, Bc * To * M);
   if (h->debug_stop == 6) return 0;
-  const long long RXo = Bc * To * N, REo = Bc * To * M;
-  const int ldn = h->ldn();
-  if ((rc = launch_head<bf16>(h, h->XA, E, E, h->head_out, h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID, RXo))) return rc;
+  if (!fuse_ch && (rc = launch_head<bf16>(h, h->XA, E, E, h->head_out, h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID, RXo))) return rc;
   if (c.if_flood) {
     std::vector<SegH> cur = st.x;
     float* bufs[2] = {h->EX, h->NX};
+    // the last Dense of the chain carries the 1-column sigmoid head in its epilogue (its E/2-wide rows never reach HBM)
+    const HeadArgs fh{W(h, h->head_flood.t[0]), W(h, h->head_flood.t[1]), h->OUTN, ldn, c.n_out, ACT_SIGMOID};
+    const bool fuse_head = !h->debug_stop && h->fuse_heads;
     for (int i = 0; i < c.if_flood; ++i) {
+      const bool lastd = fuse_head && i == c.if_flood - 1;
       if ((rc = launch_tc_gemm(h, cur, h->flood_chain[i].t[0], W(h, h->flood_chain[i].t[1]), bufs[i & 1], E2, E2, act, Bc, N, To, To,
-                               N, 0))) return rc;
+                               N, 0, nullptr, lastd ? &fh : nullptr))) return rc;
       cur = {{bufs[i & 1], E2, E2, 0, N, 0}};
     }
-    if ((rc = launch_head<bf16>(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return rc;
+    if (!fuse_head && (rc = launch_head<bf16>(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return rc;
   }
-  if ((rc = launch_head<bf16>(h, h->EA, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
+  if (!fuse_ch && (rc = launch_head<bf16>(h, h->EA, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
   return run_postproc(h, b, a, Bc, y, ey, normalised_io);
 }
 
@@ -1106,8 +1143,8 @@ int64_t floats_per_scenario(const gnnuds_config& c) {
   f += c.seq_out * (N + M) * E2;                         // BEMB AEMB
   f += (N + M) * E;                                      // RES RESE
   f += c.seq_out * (N + M) * 4;                          // OUTN OUTE
-  f += c.seq_in * (N * c.n_in + M * c.e_in) + c.seq_out * (N * c.b_in + std::max(c.n_act, 1));
-  f += c.seq_out * (N * 5 + M * 4);
+  f += 2 * (c.seq_in * (N * c.n_in + M * c.e_in) + c.seq_out * (N * c.b_in + std::max(c.n_act, 1)));   // two staging sets
+  f += 2 * c.seq_out * (N * 5 + M * 4);
   if (c.graph_base) f += Tm * (N + M) * (3 * E + 2);
   return f + 64;
 }
@@ -1132,7 +1169,10 @@ int ensure_workspace(gnnuds_handle* h, int64_t Bc) {
       {&h->OUTN, Bc * c.seq_out * N * 4 * 4}, {&h->OUTE, Bc * c.seq_out * M * 4 * 4}, {&h->SS, RM * 4}, {&h->SN, RM * 4},
       {&h->in_x, Bc * c.seq_in * N * c.n_in * 4}, {&h->in_b, Bc * c.seq_out * N * c.b_in * 4},
       {&h->in_a, Bc * c.seq_out * std::max(c.n_act, 1) * 4}, {&h->in_ex, Bc * c.seq_in * M * c.e_in * 4},
-      {&h->out_y, Bc * c.seq_out * N * 5 * 4}, {&h->out_ey, Bc * c.seq_out * M * 4 * 4}};
+      {&h->out_y, Bc * c.seq_out * N * 5 * 4}, {&h->out_ey, Bc * c.seq_out * M * 4 * 4},
+      {&h->in2_x, Bc * c.seq_in * N * c.n_in * 4}, {&h->in2_b, Bc * c.seq_out * N * c.b_in * 4},
+      {&h->in2_a, Bc * c.seq_out * std::max(c.n_act, 1) * 4}, {&h->in2_ex, Bc * c.seq_in * M * c.e_in * 4},
+      {&h->out2_y, Bc * c.seq_out * N * 5 * 4}, {&h->out2_ey, Bc * c.seq_out * M * 4 * 4}};
   if (c.graph_base) {
     const int64_t RJ = Bc * Tm * (N + M);
     plan.push_back({&h->HBJ, RJ * E * a}); plan.push_back({&h->J0, RJ * E * a}); plan.push_back({&h->J1, RJ * E * a});
@@ -1231,12 +1271,41 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   }
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, c.device);
   cudaEventCreate(&h->ev_a); cudaEventCreate(&h->ev_b);
+  cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking);
+  cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking);
+  for (int i = 0; i < 2; ++i) {
+    cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->ev_comp[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->ev_out[i], cudaEventDisableTiming);
+  }
   h->tma_on = !(getenv("GNNUDS_NO_TMA") && getenv("GNNUDS_NO_TMA")[0] == '1');
   if (getenv("GNNUDS_FUSED")) h->fused_mode = atoi(getenv("GNNUDS_FUSED"));
+  if (getenv("GNNUDS_FUSE_HEADS")) h->fuse_heads = atoi(getenv("GNNUDS_FUSE_HEADS"));
   LayoutBuilder lb{h};
   lb.build();
   *out = h;
   return 0;
+}
+
+// Gather schedule of sp_conv_kernel: the R output rows are packed into SP_BINS row lists of nearly equal
+// neighbour count (longest-processing-time first), one list per 8-lane group of the graph warps, so that
+// a sample's aggregation takes ~nnz/SP_BINS neighbour steps instead of (passes x max row degree).
+int upload_bins(gnnuds_handle* h, int side, const int* rp, int R) {
+  std::vector<int> order(R), load(SP_BINS, 0), which(R);
+  for (int i = 0; i < R; ++i) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return rp[a + 1] - rp[a] > rp[b + 1] - rp[b]; });
+  for (int r : order) {
+    int best = 0;
+    for (int b = 1; b < SP_BINS; ++b) if (load[b] < load[best]) best = b;
+    which[r] = best; load[best] += rp[r + 1] - rp[r] + 1;     // +1: per-row epilogue (bias, act, store)
+  }
+  std::vector<int> bins(SP_BINS + 1 + R, 0);
+  for (int r = 0; r < R; ++r) ++bins[which[r] + 1];
+  for (int b = 0; b < SP_BINS; ++b) bins[b + 1] += bins[b];
+  std::vector<int> fill(bins.begin(), bins.begin() + SP_BINS);
+  for (int r = 0; r < R; ++r) bins[SP_BINS + 1 + fill[which[r]]++] = r;
+  if (h->d_bins[side]) { cudaFree(h->d_bins[side]); h->d_bins[side] = nullptr; }
+  return upload(h, &h->d_bins[side], bins.data(), bins.size());
 }
 
 int gnnuds_destroy(gnnuds_handle* h) {
@@ -1245,13 +1314,21 @@ int gnnuds_destroy(gnnuds_handle* h) {
   cudaStreamSynchronize(h->stream);
   void* ptrs[] = {h->d_blob, h->d_rp, h->d_ci, h->d_erp, h->d_eci, h->d_val, h->d_eval, h->d_edges, h->d_act_of_edge,
                   h->d_act_out, h->d_act_in, h->d_inc_ptr, h->d_inc_edge, h->d_inc_sign, h->d_hmin, h->d_hmax,
-                  h->d_outfall, h->d_ehmax, h->d_nx, h->d_nb, h->d_ny, h->d_ne, h->d_ws, h->ro_x, h->ro_ex, h->ro_b, h->ro_a, h->d_wimg};
+                  h->d_outfall, h->d_ehmax, h->d_nx, h->d_nb, h->d_ny, h->d_ne, h->d_ws, h->ro_x, h->ro_ex, h->ro_b, h->ro_a, h->d_wimg,
+                  h->d_bins[0], h->d_bins[1]};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_ne_img[s]) if (p) cudaFree(p);
   for (auto& e : h->gemm_ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (h->ev_a) cudaEventDestroy(h->ev_a);
   if (h->ev_b) cudaEventDestroy(h->ev_b);
+  for (int i = 0; i < 2; ++i) {
+    if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]);
+    if (h->ev_comp[i]) cudaEventDestroy(h->ev_comp[i]);
+    if (h->ev_out[i]) cudaEventDestroy(h->ev_out[i]);
+  }
+  if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
+  if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
   cudaStreamDestroy(h->stream);
   delete h;
   return 0;
@@ -1272,6 +1349,7 @@ int gnnuds_set_graph(gnnuds_handle* h, const gnnuds_graph* g) {
   if ((rc = upload(h, &h->d_ci, g->col_idx, (size_t)g->nnz))) return rc;
   if (g->val) { if ((rc = upload(h, &h->d_val, g->val, (size_t)g->nnz))) return rc; }
   h->nnz = g->nnz; h->n_adj = g->n;
+  if (!c.graph_base && (rc = upload_bins(h, 0, g->row_ptr, g->n))) return rc;
   if (!c.graph_base) {
     for (int i = 0; i < g->e_nnz; ++i) if (g->e_col_idx[i] < 0 || g->e_col_idx[i] >= g->m) return fail(h, GNNUDS_E_INVALID, "e_col_idx out of range");
     if (g->e_row_ptr[0] != 0 || g->e_row_ptr[g->m] != g->e_nnz) return fail(h, GNNUDS_E_INVALID, "e_row_ptr inconsistent with e_nnz");
@@ -1279,6 +1357,7 @@ int gnnuds_set_graph(gnnuds_handle* h, const gnnuds_graph* g) {
     if ((rc = upload(h, &h->d_eci, g->e_col_idx, (size_t)g->e_nnz))) return rc;
     if (g->e_val) { if ((rc = upload(h, &h->d_eval, g->e_val, (size_t)g->e_nnz))) return rc; }
     h->ennz = g->e_nnz;
+    if ((rc = upload_bins(h, 1, g->e_row_ptr, g->m))) return rc;
   }
   const int N = c.n_node, M = c.n_edge;
   h->h_edges.assign(g->edges, g->edges + 2 * (size_t)M);
@@ -1480,24 +1559,50 @@ int gnnuds_predict(gnnuds_handle* h, const float* x, const float* b, const float
                 se = (int64_t)Ti * M * c.e_in, sy = (int64_t)To * N * h->ny(), sey = (int64_t)To * M * c.e_out;
   begin_timing(h);
   if (h->profiling) CU(cudaEventRecord(h->ev_a, h->stream));
-  for (int64_t b0 = 0; b0 < B; b0 += Bc) {
-    const int64_t nb = std::min(Bc, B - b0);
-    const float *px = x + b0 * sx, *pb = b + b0 * sb, *pa = a ? a + b0 * sa : nullptr, *pe = ex + b0 * se;
-    float *py = y + b0 * sy, *pey = ey + b0 * sey;
-    if (where == GNNUDS_MEM_HOST) {
-      CU(cudaMemcpyAsync(h->in_x, px, nb * sx * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-      CU(cudaMemcpyAsync(h->in_b, pb, nb * sb * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-      CU(cudaMemcpyAsync(h->in_ex, pe, nb * se * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-      if (pa) CU(cudaMemcpyAsync(h->in_a, pa, nb * sa * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-      if ((rc = forward_any(h, h->in_x, h->in_b, pa ? h->in_a : nullptr, h->in_ex, nb, h->out_y, h->out_ey, false))) return rc;
-      if (!h->debug_stop) {
-        CU(cudaMemcpyAsync(py, h->out_y, nb * sy * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
-        CU(cudaMemcpyAsync(pey, h->out_ey, nb * sey * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
-      }
-    } else {
-      if ((rc = forward_any(h, px, pb, pa, pe, nb, py, pey, false))) return rc;
+  if (where == GNNUDS_MEM_HOST && !h->debug_stop) {
+    // Host buffers: three streams and two staging sets.  The H2D copy of chunk i+1 and the D2H copy of
+    // chunk i-1 run while chunk i computes; events order the reuse of a staging set (i and i+2 share one).
+    float* sin[2][4] = {{h->in_x, h->in_b, h->in_a, h->in_ex}, {h->in2_x, h->in2_b, h->in2_a, h->in2_ex}};
+    float* sout[2][2] = {{h->out_y, h->out_ey}, {h->out2_y, h->out2_ey}};
+    CU(cudaEventRecord(h->ev_comp[0], h->stream));     // earlier work on the handle's stream (workspace memset)
+    CU(cudaStreamWaitEvent(h->s_h2d, h->ev_comp[0], 0));
+    int64_t i = 0;
+    for (int64_t b0 = 0; b0 < B; b0 += Bc, ++i) {
+      const int64_t nb = std::min(Bc, B - b0);
+      const int k = (int)(i & 1);
+      const float *px = x + b0 * sx, *pb = b + b0 * sb, *pa = a ? a + b0 * sa : nullptr, *pe = ex + b0 * se;
+      if (i >= 2) CU(cudaStreamWaitEvent(h->s_h2d, h->ev_comp[k], 0));       // chunk i-2 has consumed this input set
+      CU(cudaMemcpyAsync(sin[k][0], px, nb * sx * sizeof(float), cudaMemcpyHostToDevice, h->s_h2d));
+      CU(cudaMemcpyAsync(sin[k][1], pb, nb * sb * sizeof(float), cudaMemcpyHostToDevice, h->s_h2d));
+      CU(cudaMemcpyAsync(sin[k][3], pe, nb * se * sizeof(float), cudaMemcpyHostToDevice, h->s_h2d));
+      if (pa) CU(cudaMemcpyAsync(sin[k][2], pa, nb * sa * sizeof(float), cudaMemcpyHostToDevice, h->s_h2d));
+      CU(cudaEventRecord(h->ev_in[k], h->s_h2d));
+      CU(cudaStreamWaitEvent(h->stream, h->ev_in[k], 0));
+      if (i >= 2) CU(cudaStreamWaitEvent(h->stream, h->ev_out[k], 0));       // chunk i-2's results have left this output set
+      if ((rc = forward_any(h, sin[k][0], sin[k][1], pa ? sin[k][2] : nullptr, sin[k][3], nb, sout[k][0], sout[k][1], false))) return rc;
+      CU(cudaEventRecord(h->ev_comp[k], h->stream));
+      CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[k], 0));
+      CU(cudaMemcpyAsync(y + b0 * sy, sout[k][0], nb * sy * sizeof(float), cudaMemcpyDeviceToHost, h->s_d2h));
+      CU(cudaMemcpyAsync(ey + b0 * sey, sout[k][1], nb * sey * sizeof(float), cudaMemcpyDeviceToHost, h->s_d2h));
+      CU(cudaEventRecord(h->ev_out[k], h->s_d2h));
     }
-    if (h->debug_stop) break;
+    for (int k = 0; k < 2 && k < i; ++k) CU(cudaStreamWaitEvent(h->stream, h->ev_out[k], 0));
+  } else {
+    for (int64_t b0 = 0; b0 < B; b0 += Bc) {
+      const int64_t nb = std::min(Bc, B - b0);
+      const float *px = x + b0 * sx, *pb = b + b0 * sb, *pa = a ? a + b0 * sa : nullptr, *pe = ex + b0 * se;
+      float *py = y + b0 * sy, *pey = ey + b0 * sey;
+      if (where == GNNUDS_MEM_HOST) {     // debug_stop: stage serially, nothing to copy back
+        CU(cudaMemcpyAsync(h->in_x, px, nb * sx * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        CU(cudaMemcpyAsync(h->in_b, pb, nb * sb * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        CU(cudaMemcpyAsync(h->in_ex, pe, nb * se * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        if (pa) CU(cudaMemcpyAsync(h->in_a, pa, nb * sa * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        if ((rc = forward_any(h, h->in_x, h->in_b, pa ? h->in_a : nullptr, h->in_ex, nb, h->out_y, h->out_ey, false))) return rc;
+      } else {
+        if ((rc = forward_any(h, px, pb, pa, pe, nb, py, pey, false))) return rc;
+      }
+      if (h->debug_stop) break;
+    }
   }
   if (h->profiling) CU(cudaEventRecord(h->ev_b, h->stream));
   CU(cudaStreamSynchronize(h->stream));

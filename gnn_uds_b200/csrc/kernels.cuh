@@ -46,6 +46,16 @@ __device__ __forceinline__ float apply_act(float v, int act) {
   }
 }
 
+__device__ __forceinline__ void act_tile4(float* v, int act) {
+  if (act == ACT_RELU) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = fmaxf(v[i], 0.f);
+  } else if (act != ACT_LINEAR) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = apply_act(v[i], act);
+  }
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -167,6 +177,73 @@ __global__ void __launch_bounds__(256) embed_kernel(EmbedP p) {
     acc.x = apply_act(acc.x, p.act); acc.y = apply_act(acc.y, p.act);
     acc.z = apply_act(acc.z, p.act); acc.w = apply_act(acc.w, p.act);
     st4(static_cast<T*>(p.out) + r * p.Eo + c4 * 4, acc);
+  }
+}
+
+// Tensor-core path variant of the embedding (bf16 rows out, mode 0, K <= 8, Eo = 8*LPR): a thread owns 8
+// output columns of a row (one 16-byte store), keeps its K x 8 weight slice in registers, and walks rows
+// with incremental (n, t) bookkeeping instead of a division per row.  The lanes c < K of a row's lane
+// group each load and normalise one input channel and broadcast it by shuffle.
+template <int LPR>
+__global__ void __launch_bounds__(256) embed_bf16_kernel(EmbedP p) {
+  constexpr int RPB = 256 / LPR;                   // rows per CTA pass
+  const int lr = threadIdx.x / LPR, c8 = threadIdx.x % LPR;
+  float w[8][8], bb[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) w[c][j] = c < p.K ? p.W[c * p.Eo + c8 * 8 + j] : 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) bb[j] = p.bias[c8 * 8 + j];
+  const unsigned rows = (unsigned)p.rows, Nn = (unsigned)p.Nn, Tn = (unsigned)p.T;
+  const unsigned step = gridDim.x * (unsigned)RPB;
+  const unsigned step_n = step % Nn, step_bt = step / Nn, step_t = step_bt % Tn;
+  unsigned r = blockIdx.x * (unsigned)RPB + (unsigned)lr;
+  unsigned n = r % Nn, bt = r / Nn, t = bt % Tn;
+  const unsigned n_iter = (rows + step - 1) / step;   // uniform trip count: shuffles stay convergent
+  const int K = p.K;
+  for (unsigned it = 0; it < n_iter; ++it) {
+    const bool live = r < rows;
+    float mine = 0.f;
+    if (live && c8 < K) {
+      mine = __ldg(p.in + (size_t)r * K + c8);
+      if (p.nmax) {
+        const float mx = __ldg(p.nmax + n * p.cn + c8), mn = __ldg(p.nmin + n * p.cn + c8);
+        mine = (mine - mn) / (mx - mn);
+      }
+    }
+    float s[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] = 0.f;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      if (c < K) {                                   // warp-uniform
+        const float xc = __shfl_sync(0xffffffffu, mine, c, LPR);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s[j] = fmaf(xc, w[c][j], s[j]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] += bb[j];
+    if (live) {
+      if (p.res && t == Tn - 1) {
+        float* rp = p.res + ((size_t)(bt / Tn) * Nn + n) * p.Eo + c8 * 8;
+        *reinterpret_cast<float4*>(rp) = make_float4(s[0], s[1], s[2], s[3]);
+        *reinterpret_cast<float4*>(rp + 4) = make_float4(s[4], s[5], s[6], s[7]);
+      }
+      if (p.act == ACT_RELU) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s[j] = fmaxf(s[j], 0.f);
+      } else if (p.act != ACT_LINEAR) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s[j] = apply_act(s[j], p.act);
+      }
+      *reinterpret_cast<uint4*>(static_cast<bf16*>(p.out) + (size_t)r * p.Eo + c8 * 8) =
+          make_uint4(pack2_bf16(s[0], s[1]), pack2_bf16(s[2], s[3]), pack2_bf16(s[4], s[5]), pack2_bf16(s[6], s[7]));
+    }
+    r += step; n += step_n; bt += step_bt; t += step_t;
+    if (n >= Nn) { n -= Nn; ++bt; ++t; }
+    if (t >= Tn) t -= Tn;
   }
 }
 
@@ -805,6 +882,78 @@ __global__ void __launch_bounds__(256) cumsum_res_act_kernel(T* __restrict__ x, 
       o.x = apply_act(acc.x + r.x, act); o.y = apply_act(acc.y + r.y, act);
       o.z = apply_act(acc.z + r.z, act); o.w = apply_act(acc.w + r.w, act);
       st4(ptr, o);
+    }
+  }
+}
+
+// K8 resnet + narrow head fused (tensor-core path, E == 128): one warp per (b,n) series, a lane owns 4 channels.
+//   x_t = act(cumsum_t(x_out) + res)          (written back as bf16 only when write_x)
+//   out[(b,t,n), col0 + o] = hact( x_t . W[:, o] + bias[o] ),  o < Nout <= 4
+// The head consumes the bf16-rounded x_t, i.e. the same values a separate head kernel would read back.
+struct CumHeadP {
+  bf16* x; const float* res; long long Bc; int Tn, Nn, act, write_x;
+  const float* W; const float* bias; float* out; int ldo, col0, Nout, hact;
+};
+
+__global__ void __launch_bounds__(256) cumsum_head_bf16_kernel(CumHeadP p) {
+  constexpr int E = 128, TB = 4;
+  const int lane = threadIdx.x & 31;
+  const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  float w[4][4], bo[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int o = 0; o < 4; ++o) w[j][o] = o < p.Nout ? p.W[(lane * 4 + j) * p.Nout + o] : 0.f;
+#pragma unroll
+  for (int o = 0; o < 4; ++o) bo[o] = o < p.Nout ? p.bias[o] : 0.f;
+  const size_t tstride = (size_t)p.Nn * E;
+  for (long long bn = gw; bn < p.Bc * p.Nn; bn += nw) {
+    const int n = (int)(bn % p.Nn);
+    const long long b = bn / p.Nn;
+    const float4 r = *reinterpret_cast<const float4*>(p.res + bn * E + lane * 4);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    bf16* base = p.x + ((size_t)b * p.Tn * p.Nn + n) * E + lane * 4;
+    float* obase = p.out + ((size_t)b * p.Tn * p.Nn + n) * p.ldo + p.col0;
+    for (int t0 = 0; t0 < p.Tn; t0 += TB) {
+      uint2 raw[TB];
+#pragma unroll
+      for (int u = 0; u < TB; ++u)
+        raw[u] = t0 + u < p.Tn ? *reinterpret_cast<const uint2*>(base + (size_t)(t0 + u) * tstride) : make_uint2(0u, 0u);
+      float d[TB][4];
+#pragma unroll
+      for (int u = 0; u < TB; ++u) {
+        acc.x += __uint_as_float(raw[u].x << 16); acc.y += __uint_as_float(raw[u].x & 0xFFFF0000u);
+        acc.z += __uint_as_float(raw[u].y << 16); acc.w += __uint_as_float(raw[u].y & 0xFFFF0000u);
+        float v[4] = {acc.x + r.x, acc.y + r.y, acc.z + r.z, acc.w + r.w};
+        act_tile4(v, p.act);
+        const uint2 pk = make_uint2(pack2_bf16(v[0], v[1]), pack2_bf16(v[2], v[3]));
+        if (p.write_x && t0 + u < p.Tn) *reinterpret_cast<uint2*>(base + (size_t)(t0 + u) * tstride) = pk;
+        const float q0 = __uint_as_float(pk.x << 16), q1 = __uint_as_float(pk.x & 0xFFFF0000u);
+        const float q2 = __uint_as_float(pk.y << 16), q3 = __uint_as_float(pk.y & 0xFFFF0000u);
+#pragma unroll
+        for (int o = 0; o < 4; ++o) d[u][o] = fmaf(q0, w[0][o], fmaf(q1, w[1][o], fmaf(q2, w[2][o], q3 * w[3][o])));
+      }
+      // TB x Nout butterfly reductions (independent chains)
+#pragma unroll
+      for (int s = 16; s > 0; s >>= 1)
+#pragma unroll
+        for (int u = 0; u < TB; ++u)
+#pragma unroll
+          for (int o = 0; o < 4; ++o)
+            if (o < p.Nout) d[u][o] += __shfl_xor_sync(0xffffffffu, d[u][o], s);
+      if (lane < TB && t0 + lane < p.Tn) {
+        float mine[4];
+#pragma unroll
+        for (int o = 0; o < 4; ++o) {
+          mine[o] = d[0][o];
+#pragma unroll
+          for (int u = 1; u < TB; ++u) if (lane == u) mine[o] = d[u][o];
+        }
+#pragma unroll
+        for (int o = 0; o < 4; ++o)
+          if (o < p.Nout) obase[(size_t)(t0 + lane) * p.Nn * p.ldo + o] = apply_act(mine[o] + bo[o], p.hact);
+      }
     }
   }
 }

@@ -53,6 +53,9 @@ struct TcGemmP {
   int agg, R, hsb, nnz;      // hsb = row stride in bytes of the bf16 h tile ((Nout + 8) * 2)
   const int* row_ptr; const int* col_idx; const float* val;
   const float* a_self; const float* a_neigh;
+  // narrow-head epilogue (agg == 0): out_head[row*head_ldo + head_col] = head_act( act(acc + bias) . head_w + head_b );
+  // the Nout-wide row itself is not written (K8 flood head, emulator.py:326-333)
+  const float* head_w; const float* head_b; float* head_out; int head_ldo, head_col, head_act;
 };
 
 __device__ __forceinline__ void cp_async16(void* dst_smem, const void* src, uint32_t src_bytes) {
@@ -108,6 +111,26 @@ __device__ __forceinline__ void epi_store_cols(uint32_t taddr, int c0, bool vali
       *reinterpret_cast<uint4*>(orow + c0 + i) = make_uint4(pack2_bf16(v[i], v[i + 1]), pack2_bf16(v[i + 2], v[i + 3]),
                                                             pack2_bf16(v[i + 4], v[i + 5]), pack2_bf16(v[i + 6], v[i + 7]));
   }
+}
+
+// narrow-head epilogue of NC columns: bias + activation, then the partial dot product with the head weights
+template <int NC>
+__device__ __forceinline__ float epi_head_cols(uint32_t taddr, int c0, const float* bias_s, const float* hw_s, int act) {
+  float v[NC];
+  tmem_load_cols<NC>(taddr + (uint32_t)c0, v);
+#pragma unroll
+  for (int i = 0; i < NC; i += 4) {
+    const float4 bb = *reinterpret_cast<const float4*>(bias_s + c0 + i);
+    v[i] += bb.x; v[i + 1] += bb.y; v[i + 2] += bb.z; v[i + 3] += bb.w;
+  }
+  act_tile<NC>(v, act);
+  float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+  for (int i = 0; i < NC; i += 4) {
+    const float4 w = *reinterpret_cast<const float4*>(hw_s + c0 + i);
+    d0 = fmaf(v[i], w.x, d0); d1 = fmaf(v[i + 1], w.y, d1); d0 = fmaf(v[i + 2], w.z, d0); d1 = fmaf(v[i + 3], w.w, d1);
+  }
+  return d0 + d1;
 }
 
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_constant__ TcGemmP p) {
@@ -270,6 +293,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
     int* rp_s = reinterpret_cast<int*>(alpha + (p.agg == 2 ? gsamp * p.nnz : p.nnz));
     int* ci_s = rp_s + p.R + 1;
     for (int i = tid; i < p.Nout; i += TC_EPI_WARPS * 32) bias_s[i] = p.bias ? p.bias[i] : 0.f;
+    float* hw_s = scbuf + p.Nout;       // narrow head (agg == 0 only): head_w[Nout], part[2][2][128]
+    float* part = hw_s + p.Nout;
+    if (p.head_w)
+      for (int i = tid; i < p.Nout; i += TC_EPI_WARPS * 32) hw_s[i] = p.head_w[i];
     if (p.agg) {
       for (int i = tid; i <= p.R; i += TC_EPI_WARPS * 32) rp_s[i] = p.row_ptr[i];
       for (int i = tid; i < p.nnz; i += TC_EPI_WARPS * 32) { ci_s[i] = p.col_idx[i]; if (p.agg == 1) alpha[i] = p.val[i]; }
@@ -289,7 +316,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
         const int rloc = mt * 128 + q * 32 + lane;
         const bool valid = rloc < nvalid;
         const uint32_t ta = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * 256 + mt * p.Nout);
-        if (p.agg == 0) {
+        if (p.agg == 0 && p.head_w) {
+          const int c0 = hf * half;
+          float d = 0.f;
+          switch (half) {                                          // warp-uniform
+            case 16: d = epi_head_cols<16>(ta, c0, bias_s, hw_s, p.act); break;
+            case 32: d = epi_head_cols<32>(ta, c0, bias_s, hw_s, p.act); break;
+            case 64: d = epi_head_cols<64>(ta, c0, bias_s, hw_s, p.act); break;
+            default:
+              for (int c = c0; c < c0 + half; c += 16) d += epi_head_cols<16>(ta, c, bias_s, hw_s, p.act);
+          }
+          part[(as * 2 + hf) * 128 + rloc] = d;
+        } else if (p.agg == 0) {
           const unsigned rl = row_base + rloc;
           const size_t rr = (size_t)(rl / p.Nn) * p.pitch_d + p.off_d + rl % p.Nn;
           bf16* orow = p.out + rr * p.ldo;
@@ -328,6 +366,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
       }
       tc::tc_fence_before();
       mbar_arrive(&tempty[as]);
+      if (p.head_w && !p.agg) {
+        epi_bar_sync();
+        if (tid < nvalid) {                                        // MT == 1: tid is the tile row
+          const unsigned rl = row_base + (unsigned)tid;
+          const size_t rr = (size_t)(rl / p.Nn) * p.pitch_d + p.off_d + rl % p.Nn;
+          p.head_out[rr * p.head_ldo + p.head_col] = apply_act(part[as * 256 + tid] + part[as * 256 + 128 + tid] + p.head_b[0], p.head_act);
+        }
+      }
       if (p.agg) {
         epi_bar_sync();
         const int R = p.R;
