@@ -1061,10 +1061,11 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
   if (fuse_ch) {
     CumHeadP px{reinterpret_cast<bf16*>(h->XA), h->RES, Bc, To, N, act, c.if_flood ? 1 : 0,
                 W(h, h->head_out.t[0]), W(h, h->head_out.t[1]), h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID};
-    cumsum_head_bf16_kernel<<<grid_for(h, Bc * N, 8, 8), 256, 0, h->stream>>>(px);
+    if (c.n_out == 1) cumsum_head_bf16_kernel<1, 8><<<grid_for(h, Bc * N, 8, 8), 256, 0, h->stream>>>(px);
+    else cumsum_head_bf16_kernel<4, 4><<<grid_for(h, Bc * N, 8, 8), 256, 0, h->stream>>>(px);
     CumHeadP pe{reinterpret_cast<bf16*>(h->EA), h->RESE, Bc, To, M, act, 0,
                 W(h, h->head_e.t[0]), W(h, h->head_e.t[1]), h->OUTE, c.e_out, 0, c.e_out, ACT_TANH};
-    cumsum_head_bf16_kernel<<<grid_for(h, Bc * M, 8, 8), 256, 0, h->stream>>>(pe);
+    cumsum_head_bf16_kernel<4, 4><<<grid_for(h, Bc * M, 8, 8), 256, 0, h->stream>>>(pe);
     h->launches += 2;
     CU(cudaGetLastError());
   } else if (c.resnet) {

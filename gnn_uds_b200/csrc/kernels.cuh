@@ -181,69 +181,79 @@ __global__ void __launch_bounds__(256) embed_kernel(EmbedP p) {
 }
 
 // Tensor-core path variant of the embedding (bf16 rows out, mode 0, K <= 8, Eo = 8*LPR): a thread owns 8
-// output columns of a row (one 16-byte store), keeps its K x 8 weight slice in registers, and walks rows
-// with incremental (n, t) bookkeeping instead of a division per row.  The lanes c < K of a row's lane
-// group each load and normalise one input channel and broadcast it by shuffle.
+// output columns of a row (one 16-byte store), reads its K x 8 weight slice from shared memory, and walks
+// rows with incremental (n, t) bookkeeping instead of a division per row.  The lanes c < K of a row's lane
+// group each load and normalise one input channel and broadcast it by shuffle.  Two rows per iteration keep
+// two independent global loads in flight per thread.
+struct EmbedRow { unsigned r, n, bt, t; };
+
 template <int LPR>
 __global__ void __launch_bounds__(256) embed_bf16_kernel(EmbedP p) {
   constexpr int RPB = 256 / LPR;                   // rows per CTA pass
+  __shared__ __align__(16) float Ws[8 * LPR * 8];
+  __shared__ __align__(16) float bs[LPR * 8];
+  for (int i = threadIdx.x; i < p.K * p.Eo; i += 256) Ws[i] = p.W[i];
+  for (int i = threadIdx.x; i < p.Eo; i += 256) bs[i] = p.bias[i];
+  __syncthreads();
   const int lr = threadIdx.x / LPR, c8 = threadIdx.x % LPR;
-  float w[8][8], bb[8];
-#pragma unroll
-  for (int c = 0; c < 8; ++c)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) w[c][j] = c < p.K ? p.W[c * p.Eo + c8 * 8 + j] : 0.f;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) bb[j] = p.bias[c8 * 8 + j];
   const unsigned rows = (unsigned)p.rows, Nn = (unsigned)p.Nn, Tn = (unsigned)p.T;
   const unsigned step = gridDim.x * (unsigned)RPB;
   const unsigned step_n = step % Nn, step_bt = step / Nn, step_t = step_bt % Tn;
-  unsigned r = blockIdx.x * (unsigned)RPB + (unsigned)lr;
-  unsigned n = r % Nn, bt = r / Nn, t = bt % Tn;
+  EmbedRow cur;
+  cur.r = blockIdx.x * (unsigned)RPB + (unsigned)lr;
+  cur.n = cur.r % Nn; cur.bt = cur.r / Nn; cur.t = cur.bt % Tn;
+  auto advance = [&](EmbedRow& q) {
+    q.r += step; q.n += step_n; q.bt += step_bt; q.t += step_t;
+    if (q.n >= Nn) { q.n -= Nn; ++q.bt; ++q.t; }
+    if (q.t >= Tn) q.t -= Tn;
+  };
   const unsigned n_iter = (rows + step - 1) / step;   // uniform trip count: shuffles stay convergent
   const int K = p.K;
-  for (unsigned it = 0; it < n_iter; ++it) {
-    const bool live = r < rows;
-    float mine = 0.f;
-    if (live && c8 < K) {
-      mine = __ldg(p.in + (size_t)r * K + c8);
-      if (p.nmax) {
-        const float mx = __ldg(p.nmax + n * p.cn + c8), mn = __ldg(p.nmin + n * p.cn + c8);
-        mine = (mine - mn) / (mx - mn);
-      }
-    }
-    float s[8];
+  const float* wcol = Ws + c8 * 8;
+  for (unsigned it = 0; it < n_iter; it += 2) {
+    EmbedRow q[2];
+    q[0] = cur; advance(cur); q[1] = cur; advance(cur);
+    float mine[2] = {0.f, 0.f};
 #pragma unroll
-    for (int j = 0; j < 8; ++j) s[j] = 0.f;
-#pragma unroll
-    for (int c = 0; c < 8; ++c) {
-      if (c < K) {                                   // warp-uniform
-        const float xc = __shfl_sync(0xffffffffu, mine, c, LPR);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) s[j] = fmaf(xc, w[c][j], s[j]);
+    for (int u = 0; u < 2; ++u) {
+      if (q[u].r < rows && c8 < K) {
+        mine[u] = __ldg(p.in + (size_t)q[u].r * K + c8);
+        if (p.nmax) {
+          const float mx = __ldg(p.nmax + q[u].n * p.cn + c8), mn = __ldg(p.nmin + q[u].n * p.cn + c8);
+          mine[u] = (mine[u] - mn) / (mx - mn);
+        }
       }
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) s[j] += bb[j];
-    if (live) {
-      if (p.res && t == Tn - 1) {
-        float* rp = p.res + ((size_t)(bt / Tn) * Nn + n) * p.Eo + c8 * 8;
-        *reinterpret_cast<float4*>(rp) = make_float4(s[0], s[1], s[2], s[3]);
-        *reinterpret_cast<float4*>(rp + 4) = make_float4(s[4], s[5], s[6], s[7]);
-      }
-      if (p.act == ACT_RELU) {
+    for (int u = 0; u < 2; ++u) {
+      float s[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) s[j] = fmaxf(s[j], 0.f);
-      } else if (p.act != ACT_LINEAR) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) s[j] = apply_act(s[j], p.act);
+      for (int j = 0; j < 8; ++j) s[j] = 0.f;
+      for (int c = 0; c < K; ++c) {                  // warp-uniform trip count
+        const float xc = __shfl_sync(0xffffffffu, mine[u], c, LPR);
+        const float4 w0 = *reinterpret_cast<const float4*>(wcol + c * p.Eo), w1 = *reinterpret_cast<const float4*>(wcol + c * p.Eo + 4);
+        s[0] = fmaf(xc, w0.x, s[0]); s[1] = fmaf(xc, w0.y, s[1]); s[2] = fmaf(xc, w0.z, s[2]); s[3] = fmaf(xc, w0.w, s[3]);
+        s[4] = fmaf(xc, w1.x, s[4]); s[5] = fmaf(xc, w1.y, s[5]); s[6] = fmaf(xc, w1.z, s[6]); s[7] = fmaf(xc, w1.w, s[7]);
       }
-      *reinterpret_cast<uint4*>(static_cast<bf16*>(p.out) + (size_t)r * p.Eo + c8 * 8) =
-          make_uint4(pack2_bf16(s[0], s[1]), pack2_bf16(s[2], s[3]), pack2_bf16(s[4], s[5]), pack2_bf16(s[6], s[7]));
+      const float4 b0 = *reinterpret_cast<const float4*>(bs + c8 * 8), b1 = *reinterpret_cast<const float4*>(bs + c8 * 8 + 4);
+      s[0] += b0.x; s[1] += b0.y; s[2] += b0.z; s[3] += b0.w; s[4] += b1.x; s[5] += b1.y; s[6] += b1.z; s[7] += b1.w;
+      if (q[u].r < rows) {
+        if (p.res && q[u].t == Tn - 1) {
+          float* rp = p.res + ((size_t)(q[u].bt / Tn) * Nn + q[u].n) * p.Eo + c8 * 8;
+          *reinterpret_cast<float4*>(rp) = make_float4(s[0], s[1], s[2], s[3]);
+          *reinterpret_cast<float4*>(rp + 4) = make_float4(s[4], s[5], s[6], s[7]);
+        }
+        if (p.act == ACT_RELU) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) s[j] = fmaxf(s[j], 0.f);
+        } else if (p.act != ACT_LINEAR) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) s[j] = apply_act(s[j], p.act);
+        }
+        *reinterpret_cast<uint4*>(static_cast<bf16*>(p.out) + (size_t)q[u].r * p.Eo + c8 * 8) =
+            make_uint4(pack2_bf16(s[0], s[1]), pack2_bf16(s[2], s[3]), pack2_bf16(s[4], s[5]), pack2_bf16(s[6], s[7]));
+      }
     }
-    r += step; n += step_n; bt += step_bt; t += step_t;
-    if (n >= Nn) { n -= Nn; ++bt; ++t; }
-    if (t >= Tn) t -= Tn;
   }
 }
 
@@ -888,25 +898,53 @@ __global__ void __launch_bounds__(256) cumsum_res_act_kernel(T* __restrict__ x, 
 
 // K8 resnet + narrow head fused (tensor-core path, E == 128): one warp per (b,n) series, a lane owns 4 channels.
 //   x_t = act(cumsum_t(x_out) + res)          (written back as bf16 only when write_x)
-//   out[(b,t,n), col0 + o] = hact( x_t . W[:, o] + bias[o] ),  o < Nout <= 4
+//   out[(b,t,n), col0 + o] = hact( x_t . W[:, o] + bias[o] ),  o < Nout <= NOUT
 // The head consumes the bf16-rounded x_t, i.e. the same values a separate head kernel would read back.
+// TB time steps are loaded ahead; their TB*NOUT partial dot products are reduced across the warp by
+// recursive halving (NV-1+log terms instead of 5 shuffles per value).
 struct CumHeadP {
   bf16* x; const float* res; long long Bc; int Tn, Nn, act, write_x;
   const float* W; const float* bias; float* out; int ldo, col0, Nout, hact;
 };
 
+// NV (power of two, <= 32) per-lane values -> lane l holds the warp total of value l / (32 / NV) in v[0]
+template <int NV>
+__device__ __forceinline__ void warp_reduce_spread(float* v, int lane) {
+  int n = NV;
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    if (n > 1) {
+      n >>= 1;
+      const bool up = (lane & s) != 0;
+#pragma unroll
+      for (int i = 0; i < NV / 2; ++i) {
+        if (i < n) {
+          const float keep = up ? v[i + n] : v[i];
+          const float send = up ? v[i] : v[i + n];
+          v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+        }
+      }
+    } else {
+      v[0] += __shfl_xor_sync(0xffffffffu, v[0], s);
+    }
+  }
+}
+
+template <int NOUT, int TB>
 __global__ void __launch_bounds__(256) cumsum_head_bf16_kernel(CumHeadP p) {
-  constexpr int E = 128, TB = 4;
+  constexpr int E = 128, NV = NOUT * TB, DUP = 32 / NV;
+  static_assert(NV <= 32 && (NV & (NV - 1)) == 0, "NOUT*TB must be a power of two <= 32");
   const int lane = threadIdx.x & 31;
   const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
-  float w[4][4], bo[4];
+  float w[4][NOUT];
 #pragma unroll
   for (int j = 0; j < 4; ++j)
 #pragma unroll
-    for (int o = 0; o < 4; ++o) w[j][o] = o < p.Nout ? p.W[(lane * 4 + j) * p.Nout + o] : 0.f;
-#pragma unroll
-  for (int o = 0; o < 4; ++o) bo[o] = o < p.Nout ? p.bias[o] : 0.f;
+    for (int o = 0; o < NOUT; ++o) w[j][o] = o < p.Nout ? p.W[(lane * 4 + j) * p.Nout + o] : 0.f;
+  const int my = lane / DUP, my_u = my / NOUT, my_o = my % NOUT;      // the (time step, column) this lane finalises
+  const bool writer = (lane % DUP) == 0 && my_o < p.Nout;
+  const float my_b = my_o < p.Nout ? p.bias[my_o] : 0.f;
   const size_t tstride = (size_t)p.Nn * E;
   for (long long bn = gw; bn < p.Bc * p.Nn; bn += nw) {
     const int n = (int)(bn % p.Nn);
@@ -920,7 +958,7 @@ __global__ void __launch_bounds__(256) cumsum_head_bf16_kernel(CumHeadP p) {
 #pragma unroll
       for (int u = 0; u < TB; ++u)
         raw[u] = t0 + u < p.Tn ? *reinterpret_cast<const uint2*>(base + (size_t)(t0 + u) * tstride) : make_uint2(0u, 0u);
-      float d[TB][4];
+      float d[NV];
 #pragma unroll
       for (int u = 0; u < TB; ++u) {
         acc.x += __uint_as_float(raw[u].x << 16); acc.y += __uint_as_float(raw[u].x & 0xFFFF0000u);
@@ -932,28 +970,10 @@ __global__ void __launch_bounds__(256) cumsum_head_bf16_kernel(CumHeadP p) {
         const float q0 = __uint_as_float(pk.x << 16), q1 = __uint_as_float(pk.x & 0xFFFF0000u);
         const float q2 = __uint_as_float(pk.y << 16), q3 = __uint_as_float(pk.y & 0xFFFF0000u);
 #pragma unroll
-        for (int o = 0; o < 4; ++o) d[u][o] = fmaf(q0, w[0][o], fmaf(q1, w[1][o], fmaf(q2, w[2][o], q3 * w[3][o])));
+        for (int o = 0; o < NOUT; ++o) d[u * NOUT + o] = fmaf(q0, w[0][o], fmaf(q1, w[1][o], fmaf(q2, w[2][o], q3 * w[3][o])));
       }
-      // TB x Nout butterfly reductions (independent chains)
-#pragma unroll
-      for (int s = 16; s > 0; s >>= 1)
-#pragma unroll
-        for (int u = 0; u < TB; ++u)
-#pragma unroll
-          for (int o = 0; o < 4; ++o)
-            if (o < p.Nout) d[u][o] += __shfl_xor_sync(0xffffffffu, d[u][o], s);
-      if (lane < TB && t0 + lane < p.Tn) {
-        float mine[4];
-#pragma unroll
-        for (int o = 0; o < 4; ++o) {
-          mine[o] = d[0][o];
-#pragma unroll
-          for (int u = 1; u < TB; ++u) if (lane == u) mine[o] = d[u][o];
-        }
-#pragma unroll
-        for (int o = 0; o < 4; ++o)
-          if (o < p.Nout) obase[(size_t)(t0 + lane) * p.Nn * p.ldo + o] = apply_act(mine[o] + bo[o], p.hact);
-      }
+      warp_reduce_spread<NV>(d, lane);
+      if (writer && t0 + my_u < p.Tn) obase[(size_t)(t0 + my_u) * p.Nn * p.ldo + my_o] = apply_act(d[0] + my_b, p.hact);
     }
   }
 }

@@ -106,10 +106,14 @@ __device__ __forceinline__ void epi_store_cols(uint32_t taddr, int c0, bool vali
       v[i] += bb.x; v[i + 1] += bb.y; v[i + 2] += bb.z; v[i + 3] += bb.w;
     }
     act_tile<NC>(v, act);
+    // 32-byte stores (st.global.v8.b32): a lane's row slice goes out in whole sectors
 #pragma unroll
-    for (int i = 0; i < NC; i += 8)
-      *reinterpret_cast<uint4*>(orow + c0 + i) = make_uint4(pack2_bf16(v[i], v[i + 1]), pack2_bf16(v[i + 2], v[i + 3]),
-                                                            pack2_bf16(v[i + 4], v[i + 5]), pack2_bf16(v[i + 6], v[i + 7]));
+    for (int i = 0; i < NC; i += 16)
+      asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(orow + c0 + i), "r"(pack2_bf16(v[i], v[i + 1])),
+                   "r"(pack2_bf16(v[i + 2], v[i + 3])), "r"(pack2_bf16(v[i + 4], v[i + 5])), "r"(pack2_bf16(v[i + 6], v[i + 7])),
+                   "r"(pack2_bf16(v[i + 8], v[i + 9])), "r"(pack2_bf16(v[i + 10], v[i + 11])), "r"(pack2_bf16(v[i + 12], v[i + 13])),
+                   "r"(pack2_bf16(v[i + 14], v[i + 15]))
+                   : "memory");
   }
 }
 
