@@ -77,6 +77,7 @@ struct gnnuds_handle {
   std::vector<uint8_t*> d_ne_img[2];
   uint32_t ne_img_bytes[2] = {0, 0}, ne_pstride[2] = {0, 0};
   int ne_kp[2] = {0, 0};
+  int conv1d_tma = 1;                   // GNNUDS_CONV1D_TMA: 0 = cp.async gathers for time-shifted segments
   int fuse_heads = 1;                   // GNNUDS_FUSE_HEADS: 0 = separate cumsum / head kernels (debugging)
   int fused_mode = 1;                   // GNNUDS_FUSED: 0 layer-by-layer kernels, 1 sp_conv_kernel (default), 2 conv_agg_kernel (experimental)
 
@@ -662,6 +663,18 @@ bool make_rows_tmap(CUtensorMap* m, const void* base, long long rows, int ld, in
              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// rank-4 map over (Bc, Ts, Nn, C) activations: {8, Ts*Nn rows of a scenario, Bc, C/8}, box {8, 128, 1, kc/8}
+bool make_rows_tmap4(CUtensorMap* m, const void* base, long long Bc, long long rows_per_b, int ld, int width, int kc) {
+  tmap_encode_fn enc = tmap_encoder();
+  if (!enc) return false;
+  cuuint64_t dims[4] = {8, (cuuint64_t)rows_per_b, (cuuint64_t)Bc, (cuuint64_t)(width / 8)};
+  cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)rows_per_b * ld * 2, 16};
+  cuuint32_t box[4] = {8, 128, 1, (cuuint32_t)(kc / 8)};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 uint32_t tc_agg_scratch_bytes(int MT, int Nout, int g, int R, int nnz, bool gat) {
   return (uint32_t)(5 * 128 * MT + 3 * Nout + (gat ? g * nnz : nnz) + (R + 1) + nnz + 8) * 4u;
 }
@@ -717,7 +730,23 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
   p.boxrows = std::min(128 * p.MT, (p.rpt + 7) / 8 * 8);
   p.pstrideA = (uint32_t)p.boxrows * 16u;
   p.stage_bytes = 8u * p.pstrideA;
+  // time-shifted segments (causal Conv1D): scenario-aligned tiles, every tap a rank-4 TMA box (tc_gemm.cuh)
+  bool shifted = false, tma4_ok = h->tma_on && h->conv1d_tma && !(agg && agg->kind) && pitch_d == Nn && off_d == 0 && Ts >= Td;
   for (int i = 0; i < p.nseg; ++i) {
+    const SegH& sg = segs[i];
+    shifted |= sg.shift != 0;
+    tma4_ok &= sg.pitch == Nn && sg.off == 0 && (reinterpret_cast<uintptr_t>(sg.p) & 15) == 0 && sg.shift <= Ts;
+  }
+  if (shifted && tma4_ok) {
+    const long long rows_src = (long long)Ts * Nn, rows_dst = (long long)Td * Nn;
+    for (int i = 0; i < p.nseg && tma4_ok; ++i) tma4_ok = make_rows_tmap4(&p.tmap[i], segs[i].p, Bc, rows_src, segs[i].ld, segs[i].width, kc);
+    if (tma4_ok) {
+      p.tpb = (int)((rows_dst + 127) / 128); p.rows_per_b = (unsigned)rows_dst;
+      p.n_tiles = (unsigned)(Bc * p.tpb);
+      for (int i = 0; i < p.nseg; ++i) p.use_tma[i] = 1;
+    }
+  }
+  for (int i = 0; i < p.nseg && !p.tpb; ++i) {
     const SegH& sg = segs[i];
     p.use_tma[i] = 0;
     if (h->tma_on && sg.shift == 0 && Ts == Td && sg.pitch == Nn && sg.off == 0 && (reinterpret_cast<uintptr_t>(sg.p) & 15) == 0)
@@ -1281,6 +1310,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   }
   h->tma_on = !(getenv("GNNUDS_NO_TMA") && getenv("GNNUDS_NO_TMA")[0] == '1');
   if (getenv("GNNUDS_FUSED")) h->fused_mode = atoi(getenv("GNNUDS_FUSED"));
+  if (getenv("GNNUDS_CONV1D_TMA")) h->conv1d_tma = atoi(getenv("GNNUDS_CONV1D_TMA"));
   if (getenv("GNNUDS_FUSE_HEADS")) h->fuse_heads = atoi(getenv("GNNUDS_FUSE_HEADS"));
   LayoutBuilder lb{h};
   lb.build();

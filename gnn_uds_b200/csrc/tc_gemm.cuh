@@ -48,6 +48,11 @@ struct TcGemmP {
   int Nout, Ktot, kc, act;
   unsigned rows; int Nn, Td, Ts, pitch_d, off_d;
   int rpt, MT; unsigned n_tiles; int NS;
+  // scenario-aligned tiling (tpb > 0; time-shifted segments, i.e. the causal Conv1D): a tile is 128 rows of ONE
+  // scenario b (tpb tiles per scenario, the last one partial), every segment is a rank-4 tensor map
+  // {8, Ts*Nn rows of a scenario, Bc, C/8}, and tap `shift` is the same box moved up by shift*Nn rows - rows before
+  // t = 0 fall outside the scenario's extent and arrive as zeros (the causal padding), no gather needed.
+  int tpb; unsigned rows_per_b;
   uint32_t w_bytes, stage_bytes, pstrideA, stage_off, h_off, sc_off, bar_off;
   // aggregation epilogue (agg: 0 none, 1 GCN, 2 GAT) over samples of R rows
   int agg, R, hsb, nnz;      // hsb = row stride in bytes of the bf16 h tile ((Nout + 8) * 2)
@@ -137,6 +142,19 @@ __device__ __forceinline__ float epi_head_cols(uint32_t taddr, int c0, const flo
   return d0 + d1;
 }
 
+__device__ __forceinline__ void tile_rows(const TcGemmP& p, unsigned tile, unsigned& row_base, int& nvalid, unsigned& b, unsigned& rb) {
+  if (p.tpb) {
+    b = tile / (unsigned)p.tpb;
+    rb = (tile - b * (unsigned)p.tpb) * 128u;
+    row_base = b * p.rows_per_b + rb;
+    nvalid = (int)min(128u, p.rows_per_b - rb);
+  } else {
+    b = 0; rb = 0;
+    row_base = tile * (unsigned)p.rpt;
+    nvalid = (int)min((unsigned)p.rpt, p.rows - row_base);
+  }
+}
+
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_constant__ TcGemmP p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -179,7 +197,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
     uint32_t ephase = 1;                       // parity to wait for on empty[]: passes at once on the first lap
     uint32_t tq[2], tn[2];                     // per owned row: b*Ts + t + (Ts-Td) (~0 = no such row), (t << 20) | n
     for (unsigned tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-      const unsigned row_base = tile * (unsigned)p.rpt;
+      unsigned row_base, tb_b, tb_rb; int nv_unused;
+      tile_rows(p, tile, row_base, nv_unused, tb_b, tb_rb);
+      if (p.tpb) {
+        // every segment is a rank-4 TMA box; one elected thread issues, the others only arrive
+        for (int s = 0; s < p.nseg; ++s) {
+          const int row0 = (int)tb_rb + (p.Ts - p.Td - p.seg[s].shift) * p.Nn;
+          for (int k0 = 0; k0 < p.seg[s].width; k0 += p.kc) {
+            tc::mbar_wait(&empty[stage], ephase);
+            if (ptid == 0) {
+              tc::mbar_expect_tx(&full[stage], (uint32_t)p.boxrows * 16u * (uint32_t)cpr);
+              tc::tma_load_4d(stages + (size_t)stage * p.stage_bytes, &p.tmap[s], 0, row0, (int)tb_b, k0 >> 3, &full[stage]);
+            } else {
+              mbar_arrive(&full[stage]);
+            }
+            if (++stage == NS) { stage = 0; ephase ^= 1; }
+          }
+        }
+        continue;
+      }
 #pragma unroll
       for (int m = 0; m < 2; ++m) {
         const int rloc = ptid + 128 * m;
@@ -311,8 +347,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
     unsigned tile_it = 0;
     for (unsigned tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++tile_it) {
       const int as = tile_it & 1;
-      const unsigned row_base = tile * (unsigned)p.rpt;
-      const int nvalid = (int)min((unsigned)p.rpt, p.rows - row_base);
+      unsigned row_base, tb_b, tb_rb; int nvalid;
+      tile_rows(p, tile, row_base, nvalid, tb_b, tb_rb);
       tc::mbar_wait(&tfull[as], (tile_it >> 1) & 1);
       tc::tc_fence_after();
       for (int mt = 0; mt < p.MT; ++mt) {
