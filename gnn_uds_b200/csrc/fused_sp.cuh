@@ -46,7 +46,11 @@ struct SpConvP {
   uint32_t pstrideA, pstrideM, pstrideX;      // bytes: self/NE panels (Rbox*16), Mat panels, other_dense panels (Kp*16)
   uint32_t off_w, off_m, off_in, in_stride, xe_off, off_nx, off_sc, off_bar, hsb;
   uint32_t self_bytes, xe_bytes;
+  int pf;                     // L2 prefetch distance in samples beyond the two shared-memory buffers (0 = off)
+  long long* trace;           // debug: clock64 stamps of CTA 0, SP_NSTAMP per sample (GNNUDS_TRACE_FILE), else null
 };
+constexpr int SP_NSTAMP = 10;
+#define SP_STAMP(i, k) do { if (p.trace && blockIdx.x == 0 && (i) < 64) p.trace[(i) * SP_NSTAMP + (k)] = clock64(); } while (0)
 
 __device__ __forceinline__ void graph_bar_sync() { asm volatile("bar.sync 2, %0;" ::"n"(SP_GRAPH_WARPS * 32) : "memory"); }
 
@@ -116,10 +120,21 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
     if (lane == 0) {
       for (int s = 0; s < p.nseg; ++s) tc::tma_prefetch_desc(&p.tm_self[s]);
       tc::tma_prefetch_desc(&p.tm_other);
+      // the HBM latency of a sample's 50-80 KB is hidden by an L2 prefetch issued SP_PF samples ahead: the
+      // shared-memory fill (issued when the buffer is released) then streams from L2
+      auto prefetch = [&](int i) {
+        if (i >= n_it) return;
+        const int smp = (int)blockIdx.x + i * (int)gridDim.x;
+        for (int s = 0; s < p.nseg; ++s) tc::tma_prefetch_3d(&p.tm_self[s], 0, smp * p.R, 0);
+        tc::tma_prefetch_3d(&p.tm_other, 0, smp * p.Ro, 0);
+      };
+      for (int i = 2; i < 2 + p.pf; ++i) prefetch(i);
       for (int i = 0; i < n_it; ++i) {
         const int buf = i & 1;
         const int smp = (int)blockIdx.x + i * (int)gridDim.x;
+        if (p.pf) prefetch(i + 2 + p.pf);
         if (i >= 2) tc::mbar_wait(&in_empty[buf], ((i >> 1) & 1) ^ 1);
+        SP_STAMP(i, 0);
         uint8_t* dst = smem + p.off_in + (size_t)buf * p.in_stride;
         tc::mbar_expect_tx(&in_full[buf], p.self_bytes + p.xe_bytes);
         uint32_t o = 0;
@@ -153,6 +168,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         const uint32_t in_addr = tc::smem_u32(smem + off_in + (size_t)buf * in_stride);
         tc::mbar_wait(&in_full[buf], (i >> 1) & 1);
         tc::tc_fence_after();
+        SP_STAMP(i, 1);
         // NodeEdge: D[row, f] = sum_k Mat[row, k] * other_dense[k, f]
         // descriptors advance linearly with the start address: one 64-bit add per MMA in the issue loops
         {
@@ -163,6 +179,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
           }
         }
         tc::umma_commit(ne_done);
+        SP_STAMP(i, 2);
         // conv over the self columns first (they are ready), then over the NodeEdge columns.  The conv
         // accumulators of the previous sample must have been drained (h_full of sample i-1).
         if (i >= 1) { tc::mbar_wait(&h_full[(i - 1) & 1], ((i - 1) >> 1) & 1); tc::tc_fence_after(); }
@@ -195,6 +212,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
       // ---- NodeEdge accumulators -> bf16 panels (A operand of the conv GEMM) ----
       tc::mbar_wait(ne_done, i & 1);
       tc::tc_fence_after();
+      if (tid == 0) SP_STAMP(i, 3);
       for (int mt = 0; mt < p.MT; ++mt) {
         if (mt * 128 + q * 32 >= p.R) continue;       // warp-uniform
         const int row = mt * 128 + q * 32 + lane;
@@ -214,9 +232,11 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
       tc::fence_async_smem();                         // generic-proxy panel writes -> tensor-core reads
       tc::tc_fence_before();
       mbar_arrive(nx_ready);
+      if (tid == 0) SP_STAMP(i, 4);
       // ---- conv accumulators -> h tile (bf16 rows) + GAT scores from the fp32 values ----
       tc::mbar_wait(conv_done, i & 1);
       tc::tc_fence_after();
+      if (tid == 0) SP_STAMP(i, 5);
       uint8_t* hbase = smem + p.off_in + (size_t)buf * p.in_stride;
       for (int mt = 0; mt < p.MT; ++mt) {
         if (mt * 128 + q * 32 >= p.R) continue;
@@ -250,6 +270,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
       }
       tc::tc_fence_before();
       mbar_arrive(&h_full[buf]);
+      if (tid == 0) SP_STAMP(i, 6);
     }
   } else {
     // ================================ graph group ================================
@@ -262,6 +283,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
       const int buf = i & 1;
       const int smp = (int)blockIdx.x + i * (int)gridDim.x;
       tc::mbar_wait(&h_full[buf], (i >> 1) & 1);
+      if (gt == 0) SP_STAMP(i, 7);
       const uint8_t* hbase = smem + p.off_in + (size_t)buf * p.in_stride;
       float* al = alpha + buf * p.nnz;
       float* inv = inv_s + buf * RP;
@@ -296,6 +318,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         }
         graph_bar_sync();
       }
+      if (gt == 0) SP_STAMP(i, 8);
       // weighted neighbour sum: 8 lanes per output row, a lane owns features [8gl, 8gl+8) and [64+8gl, 64+8gl+8).
       // Each 8-lane group walks its own row list of the balanced schedule; two neighbours per step keep four
       // 16-byte shared loads in flight.
@@ -363,6 +386,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
           }
         }
       }
+      if (gt == 0) SP_STAMP(i, 9);
       mbar_arrive(&in_empty[buf]);                    // this thread is done with the h tile of the sample
     }
   }

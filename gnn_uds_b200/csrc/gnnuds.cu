@@ -77,6 +77,7 @@ struct gnnuds_handle {
   std::vector<uint8_t*> d_ne_img[2];
   uint32_t ne_img_bytes[2] = {0, 0}, ne_pstride[2] = {0, 0};
   int ne_kp[2] = {0, 0};
+  int sw128 = 1;                        // GNNUDS_SW128: 0 = 16-byte panel boxes for every TMA-fed operand tile
   int conv1d_tma = 1;                   // GNNUDS_CONV1D_TMA: 0 = cp.async gathers for time-shifted segments
   int fuse_heads = 1;                   // GNNUDS_FUSE_HEADS: 0 = separate cumsum / head kernels (debugging)
   int fused_mode = 1;                   // GNNUDS_FUSED: 0 layer-by-layer kernels, 1 sp_conv_kernel (default), 2 conv_agg_kernel (experimental)
@@ -663,6 +664,19 @@ bool make_rows_tmap(CUtensorMap* m, const void* base, long long rows, int ld, in
              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// SWIZZLE_128B maps for K-major operand tiles: {C, rows} box {64, boxrows}, or {C, rows of a scenario, Bc} box {64, boxrows, 1}
+bool make_rows_tmap_sw(CUtensorMap* m, const void* base, long long rows, int ld, int width, int boxrows, long long Bc = 0) {
+  tmap_encode_fn enc = tmap_encoder();
+  if (!enc) return false;
+  cuuint64_t dims[3] = {(cuuint64_t)width, (cuuint64_t)rows, (cuuint64_t)std::max<long long>(Bc, 1)};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)rows * ld * 2};
+  cuuint32_t box[3] = {64, (cuuint32_t)boxrows, 1};
+  cuuint32_t es[3] = {1, 1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, Bc > 0 ? 3 : 2, const_cast<void*>(base), dims, strides, box, es,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 // rank-4 map over (Bc, Ts, Nn, C) activations: {8, Ts*Nn rows of a scenario, Bc, C/8}, box {8, 128, 1, kc/8}
 bool make_rows_tmap4(CUtensorMap* m, const void* base, long long Bc, long long rows_per_b, int ld, int width, int kc) {
   tmap_encode_fn enc = tmap_encoder();
@@ -737,22 +751,37 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
     shifted |= sg.shift != 0;
     tma4_ok &= sg.pitch == Nn && sg.off == 0 && (reinterpret_cast<uintptr_t>(sg.p) & 15) == 0 && sg.shift <= Ts;
   }
+  const bool sw_ok = h->sw128 && kc == 64 && p.boxrows % 8 == 0;
   if (shifted && tma4_ok) {
     const long long rows_src = (long long)Ts * Nn, rows_dst = (long long)Td * Nn;
-    for (int i = 0; i < p.nseg && tma4_ok; ++i) tma4_ok = make_rows_tmap4(&p.tmap[i], segs[i].p, Bc, rows_src, segs[i].ld, segs[i].width, kc);
+    for (int i = 0; i < p.nseg && tma4_ok; ++i)
+      tma4_ok = sw_ok ? make_rows_tmap_sw(&p.tmap[i], segs[i].p, rows_src, segs[i].ld, segs[i].width, 128, Bc)
+                      : make_rows_tmap4(&p.tmap[i], segs[i].p, Bc, rows_src, segs[i].ld, segs[i].width, kc);
     if (tma4_ok) {
       p.tpb = (int)((rows_dst + 127) / 128); p.rows_per_b = (unsigned)rows_dst;
       p.n_tiles = (unsigned)(Bc * p.tpb);
+      p.sw128 = sw_ok ? 1 : 0;
       for (int i = 0; i < p.nseg; ++i) p.use_tma[i] = 1;
     }
   }
-  for (int i = 0; i < p.nseg && !p.tpb; ++i) {
+  if (!p.tpb) {
+    bool all = h->tma_on && Ts == Td;
+    for (int i = 0; i < p.nseg; ++i) {
+      const SegH& sg = segs[i];
+      all &= sg.shift == 0 && sg.pitch == Nn && sg.off == 0 && (reinterpret_cast<uintptr_t>(sg.p) & 15) == 0;
+    }
+    if (all && sw_ok) {
+      for (int i = 0; i < p.nseg && all; ++i) all = make_rows_tmap_sw(&p.tmap[i], segs[i].p, rows, segs[i].ld, segs[i].width, p.boxrows);
+      if (all) { p.sw128 = 1; for (int i = 0; i < p.nseg; ++i) p.use_tma[i] = 1; }
+    }
+  }
+  for (int i = 0; i < p.nseg && !p.tpb && !p.sw128; ++i) {
     const SegH& sg = segs[i];
     p.use_tma[i] = 0;
     if (h->tma_on && sg.shift == 0 && Ts == Td && sg.pitch == Nn && sg.off == 0 && (reinterpret_cast<uintptr_t>(sg.p) & 15) == 0)
       p.use_tma[i] = make_rows_tmap(&p.tmap[i], sg.p, rows, sg.ld, sg.width, p.boxrows, kc) ? 1 : 0;
   }
-  p.stage_off = (p.w_bytes + 127u) & ~127u;
+  p.stage_off = (p.w_bytes + 1023u) & ~1023u;       // SWIZZLE_128B tiles need 1024-byte alignment
   const uint32_t h_bytes = p.agg ? (((uint32_t)p.rpt * p.hsb + 127u) & ~127u) : 0u;
   const uint32_t sc_bytes = p.agg ? tc_agg_scratch_bytes(p.MT, Nout, p.rpt / p.R, p.R, p.nnz, p.agg == 2) : (uint32_t)Nout * 8u + 2048u;
   const uint32_t fixed = p.stage_off + h_bytes + sc_bytes + 256u + 4096u;
@@ -909,13 +938,32 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
     CU(cudaFuncSetAttribute(sp_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
+  p.pf = getenv("GNNUDS_SP_PF") ? atoi(getenv("GNNUDS_SP_PF")) : 2;
   const unsigned grid = (unsigned)std::min<long long>(S, h->sm_count);
+  // GNNUDS_TRACE_FILE=<path> [GNNUDS_TRACE_LAUNCH=k]: clock64 stamps of CTA 0 of the k-th sp_conv launch
+  static int traced = 0;
+  const char* tf = getenv("GNNUDS_TRACE_FILE");
+  const int want = getenv("GNNUDS_TRACE_LAUNCH") ? atoi(getenv("GNNUDS_TRACE_LAUNCH")) : 0;
+  const bool do_trace = tf && S >= 64 * (long long)h->sm_count && traced++ == want;
+  const size_t tn = 64 * SP_NSTAMP;
+  if (do_trace) { CU(cudaMalloc(&p.trace, tn * sizeof(long long))); CU(cudaMemset(p.trace, 0, tn * sizeof(long long))); }
   cudaEvent_t e1 = nullptr;
   { int prc = prof_begin(h, GNNUDS_FAM_SPATIAL, &e1); if (prc) return prc; }
   sp_conv_kernel<<<grid, SP_THREADS, smem, h->stream>>>(p);
   ++h->launches;
   { int prc = prof_end(h, e1); if (prc) return prc; }
   CU(cudaGetLastError());
+  if (do_trace) {
+    std::vector<long long> t(tn);
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaMemcpy(t.data(), p.trace, tn * sizeof(long long), cudaMemcpyDeviceToHost));
+    cudaFree(p.trace);
+    if (FILE* f = fopen(tf, "w")) {
+      fprintf(f, "# sp_conv R=%d Ro=%d Kself=%d MT=%d: sample, cycles since first stamp: tma_issue in_full ne_issued ne_done nx_ready conv_done h_full graph_start softmax_done gather_done\n", R, Ro, p.Kself, p.MT);
+      for (int i = 0; i < 64; ++i) { fprintf(f, "%d", i); for (int k = 0; k < SP_NSTAMP; ++k) fprintf(f, " %lld", t[i * SP_NSTAMP + k] ? t[i * SP_NSTAMP + k] - t[0] : -1); fprintf(f, "\n"); }
+      fclose(f);
+    }
+  }
   return 0;
 }
 
@@ -1310,6 +1358,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   }
   h->tma_on = !(getenv("GNNUDS_NO_TMA") && getenv("GNNUDS_NO_TMA")[0] == '1');
   if (getenv("GNNUDS_FUSED")) h->fused_mode = atoi(getenv("GNNUDS_FUSED"));
+  if (getenv("GNNUDS_SW128")) h->sw128 = atoi(getenv("GNNUDS_SW128"));
   if (getenv("GNNUDS_CONV1D_TMA")) h->conv1d_tma = atoi(getenv("GNNUDS_CONV1D_TMA"));
   if (getenv("GNNUDS_FUSE_HEADS")) h->fuse_heads = atoi(getenv("GNNUDS_FUSE_HEADS"));
   LayoutBuilder lb{h};

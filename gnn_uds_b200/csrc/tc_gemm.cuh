@@ -53,6 +53,9 @@ struct TcGemmP {
   // {8, Ts*Nn rows of a scenario, Bc, C/8}, and tap `shift` is the same box moved up by shift*Nn rows - rows before
   // t = 0 fall outside the scenario's extent and arrive as zeros (the causal padding), no gather needed.
   int tpb; unsigned rows_per_b;
+  // sw128 (all segments by TMA, kc == 64): a stage is one SWIZZLE_128B K-major tile [boxrows x 64] written by a TMA box
+  // with a 128-byte inner extent (8x fewer TMA requests than the 16-byte panel boxes); maps are {C, rows} or {C, rows, Bc}
+  int sw128;
   uint32_t w_bytes, stage_bytes, pstrideA, stage_off, h_off, sc_off, bar_off;
   // aggregation epilogue (agg: 0 none, 1 GCN, 2 GAT) over samples of R rows
   int agg, R, hsb, nnz;      // hsb = row stride in bytes of the bf16 h tile ((Nout + 8) * 2)
@@ -156,7 +159,7 @@ __device__ __forceinline__ void tile_rows(const TcGemmP& p, unsigned tile, unsig
 }
 
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_constant__ TcGemmP p) {
-  extern __shared__ __align__(128) uint8_t smem[];
+  extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   uint8_t* Wsm = smem;
   uint8_t* stages = smem + p.stage_off;
@@ -207,7 +210,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
             tc::mbar_wait(&empty[stage], ephase);
             if (ptid == 0) {
               tc::mbar_expect_tx(&full[stage], (uint32_t)p.boxrows * 16u * (uint32_t)cpr);
-              tc::tma_load_4d(stages + (size_t)stage * p.stage_bytes, &p.tmap[s], 0, row0, (int)tb_b, k0 >> 3, &full[stage]);
+              if (p.sw128) tc::tma_load_3d(stages + (size_t)stage * p.stage_bytes, &p.tmap[s], k0, row0, (int)tb_b, &full[stage]);
+              else tc::tma_load_4d(stages + (size_t)stage * p.stage_bytes, &p.tmap[s], 0, row0, (int)tb_b, k0 >> 3, &full[stage]);
             } else {
               mbar_arrive(&full[stage]);
             }
@@ -243,7 +247,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
           if (p.use_tma[s]) {
             if (ptid == 0) {
               tc::mbar_expect_tx(&full[stage], (uint32_t)p.boxrows * 16u * (uint32_t)cpr);
-              tc::tma_load_3d(stages + (size_t)stage * p.stage_bytes, &p.tmap[s], 0, (int)row_base, k0 >> 3, &full[stage]);
+              if (p.sw128) tc::tma_load_2d(stages + (size_t)stage * p.stage_bytes, &p.tmap[s], k0, (int)row_base, &full[stage]);
+              else tc::tma_load_3d(stages + (size_t)stage * p.stage_bytes, &p.tmap[s], 0, (int)row_base, k0 >> 3, &full[stage]);
             } else {
               mbar_arrive(&full[stage]);
             }
@@ -288,8 +293,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
       const uint32_t stage_bytes = p.stage_bytes;
       const int kpc = p.kc / 16, Nout = p.Nout;
       const bool MT2 = p.MT > 1;
-      const uint64_t a_desc0 = tc::smem_desc(st_addr, p.pstrideA, 128u), w_desc0 = tc::smem_desc(w_addr, pstrideW, 128u);
-      const uint64_t a_step = (uint64_t)((2u * p.pstrideA) >> 4), w_step = (uint64_t)((2u * pstrideW) >> 4);
+      const uint64_t a_desc0 = p.sw128 ? tc::smem_desc_sw128(st_addr) : tc::smem_desc(st_addr, p.pstrideA, 128u);
+      const uint64_t w_desc0 = tc::smem_desc(w_addr, pstrideW, 128u);
+      const uint64_t a_step = p.sw128 ? 2u : (uint64_t)((2u * p.pstrideA) >> 4), w_step = (uint64_t)((2u * pstrideW) >> 4);
+      const uint64_t a_mt2 = p.sw128 ? 1024u : 128u;        // second M-tile: +128 rows
       unsigned tile_it = 0;
       int stage = 0;
       uint32_t fphase = 0;
@@ -308,7 +315,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
 #pragma unroll 4
           for (int ks = 0; ks < kpc; ++ks, ad += a_step, bd += w_step) {
             tc::umma(acc, ad, bd, idesc, (ch | ks) != 0);
-            if (MT2) tc::umma(acc + (uint32_t)Nout, ad + 128u, bd, idesc, (ch | ks) != 0);
+            if (MT2) tc::umma(acc + (uint32_t)Nout, ad + a_mt2, bd, idesc, (ch | ks) != 0);
           }
           tc::umma_commit(&empty[stage]);
           if (++stage == NS) { stage = 0; fphase ^= 1; }

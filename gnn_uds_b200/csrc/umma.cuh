@@ -63,6 +63,17 @@ __device__ __forceinline__ void tma_load_3d(void* dst_smem, const void* tmap, in
       "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
       : "memory");
 }
+// L2 prefetch of a rank-3 TMA box (no shared-memory destination, no completion to wait for)
+__device__ __forceinline__ void tma_prefetch_3d(const void* tmap, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(tmap), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst_smem, const void* tmap, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+          smem_u32(dst_smem)),
+      "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_4d(void* dst_smem, const void* tmap, int c0, int c1, int c2, int c3, uint64_t* bar) {
   asm volatile(
       "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];" ::"r"(
@@ -123,6 +134,18 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes,
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;
+  return d;
+}
+// K-major operand tile in the SWIZZLE_128B canonical layout (rows of 64 bf16 = 128 bytes, 8-row groups of 1024 bytes,
+// 16-byte chunks XOR-swizzled by row%8; written by a TMA box {64, rows} with CU_TENSOR_MAP_SWIZZLE_128B).  The tile base
+// must be 1024-byte aligned; one K=16 step advances the start address by 32 bytes, 128 rows by 16384 bytes.
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;                        // LBO: unused for swizzled K-major
+  d |= (uint64_t)(1024u >> 4) << 32;             // SBO: 8-row group stride
+  d |= (uint64_t)1 << 46;                        // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
   return d;
 }
 // rows of a panel buffer as the M/N index, columns as K (K-major): one K=16 step spans two panels
