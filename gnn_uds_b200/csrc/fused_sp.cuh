@@ -33,7 +33,8 @@ constexpr int SP_THREADS = (SP_DRAIN_WARPS + SP_GRAPH_WARPS + 2) * 32;   // 704
 constexpr int SP_BINS = SP_GRAPH_WARPS * 4;                               // 8-lane groups of the graph warps
 
 struct SpConvP {
-  CUtensorMap tm_self[2];     // {8, S*R rows, w/8 panels}, box {8, Rbox, w/8}
+  CUtensorMap tm_self[2];     // {8, S*R rows, w/8 panels}, box {8, Rbox, w/8};  sw128: {w, S*R rows}, box {64, Rbox}, SWIZZLE_128B
+  int sw128; uint32_t chunk_bytes;   // self operand as SWIZZLE_128B K-major tiles of Rbox*128 bytes per 64 columns
   CUtensorMap tm_other;       // {8, S*Ro rows, F/8 panels}, box {8, Kp, F/8}
   int nseg, segw[2];
   const uint8_t* Wimg; uint32_t w_bytes;      // conv weight image, panel stride Nout*16
@@ -46,7 +47,6 @@ struct SpConvP {
   uint32_t pstrideA, pstrideM, pstrideX;      // bytes: self/NE panels (Rbox*16), Mat panels, other_dense panels (Kp*16)
   uint32_t off_w, off_m, off_in, in_stride, xe_off, off_nx, off_sc, off_bar, hsb;
   uint32_t self_bytes, xe_bytes;
-  int pf;                     // L2 prefetch distance in samples beyond the two shared-memory buffers (0 = off)
   long long* trace;           // debug: clock64 stamps of CTA 0, SP_NSTAMP per sample (GNNUDS_TRACE_FILE), else null
 };
 constexpr int SP_NSTAMP = 10;
@@ -55,7 +55,7 @@ constexpr int SP_NSTAMP = 10;
 __device__ __forceinline__ void graph_bar_sync() { asm volatile("bar.sync 2, %0;" ::"n"(SP_GRAPH_WARPS * 32) : "memory"); }
 
 __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_constant__ SpConvP p) {
-  extern __shared__ __align__(128) uint8_t smem[];
+  extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.off_bar);
   uint64_t* in_full = bars;          // [2] TMA complete_tx
@@ -120,27 +120,21 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
     if (lane == 0) {
       for (int s = 0; s < p.nseg; ++s) tc::tma_prefetch_desc(&p.tm_self[s]);
       tc::tma_prefetch_desc(&p.tm_other);
-      // the HBM latency of a sample's 50-80 KB is hidden by an L2 prefetch issued SP_PF samples ahead: the
-      // shared-memory fill (issued when the buffer is released) then streams from L2
-      auto prefetch = [&](int i) {
-        if (i >= n_it) return;
-        const int smp = (int)blockIdx.x + i * (int)gridDim.x;
-        for (int s = 0; s < p.nseg; ++s) tc::tma_prefetch_3d(&p.tm_self[s], 0, smp * p.R, 0);
-        tc::tma_prefetch_3d(&p.tm_other, 0, smp * p.Ro, 0);
-      };
-      for (int i = 2; i < 2 + p.pf; ++i) prefetch(i);
       for (int i = 0; i < n_it; ++i) {
         const int buf = i & 1;
         const int smp = (int)blockIdx.x + i * (int)gridDim.x;
-        if (p.pf) prefetch(i + 2 + p.pf);
         if (i >= 2) tc::mbar_wait(&in_empty[buf], ((i >> 1) & 1) ^ 1);
         SP_STAMP(i, 0);
         uint8_t* dst = smem + p.off_in + (size_t)buf * p.in_stride;
         tc::mbar_expect_tx(&in_full[buf], p.self_bytes + p.xe_bytes);
         uint32_t o = 0;
         for (int s = 0; s < p.nseg; ++s) {
-          tc::tma_load_3d(dst + o, &p.tm_self[s], 0, smp * p.R, 0, &in_full[buf]);
-          o += (uint32_t)(p.segw[s] >> 3) * p.pstrideA;
+          if (p.sw128) {        // one SWIZZLE_128B tile [Rbox x 64] per 64 columns (128-byte TMA requests)
+            for (int k0 = 0; k0 < p.segw[s]; k0 += 64, o += p.chunk_bytes) tc::tma_load_2d(dst + o, &p.tm_self[s], k0, smp * p.R, &in_full[buf]);
+          } else {
+            tc::tma_load_3d(dst + o, &p.tm_self[s], 0, smp * p.R, 0, &in_full[buf]);
+            o += (uint32_t)(p.segw[s] >> 3) * p.pstrideA;
+          }
         }
         tc::tma_load_3d(dst + p.xe_off, &p.tm_other, 0, smp * p.Ro, 0, &in_full[buf]);
       }
@@ -185,11 +179,22 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         if (i >= 1) { tc::mbar_wait(&h_full[(i - 1) & 1], ((i - 1) >> 1) & 1); tc::tc_fence_after(); }
         uint64_t wd = w_desc0;
         {
-          uint64_t ad = tc::smem_desc(in_addr, pstrideA, 128u);
+          if (p.sw128) {
+            for (int c = 0; c < (ks_self >> 2); ++c) {
+              uint64_t ad = tc::smem_desc_sw128(in_addr + (uint32_t)c * p.chunk_bytes);
+#pragma unroll
+              for (int j = 0; j < 4; ++j, ad += 2u, wd += w_step) {
+                tc::umma(acc_conv, ad, wd, idesc_cv, (c | j) != 0);
+                if (MT2) tc::umma(acc_conv + (uint32_t)Nout, ad + 1024u, wd, idesc_cv, (c | j) != 0);
+              }
+            }
+          } else {
+            uint64_t ad = tc::smem_desc(in_addr, pstrideA, 128u);
 #pragma unroll 4
-          for (int ks = 0; ks < ks_self; ++ks, ad += a_step, wd += w_step) {
-            tc::umma(acc_conv, ad, wd, idesc_cv, ks != 0);
-            if (MT2) tc::umma(acc_conv + (uint32_t)Nout, ad + 128u, wd, idesc_cv, ks != 0);
+            for (int ks = 0; ks < ks_self; ++ks, ad += a_step, wd += w_step) {
+              tc::umma(acc_conv, ad, wd, idesc_cv, ks != 0);
+              if (MT2) tc::umma(acc_conv + (uint32_t)Nout, ad + 128u, wd, idesc_cv, ks != 0);
+            }
           }
         }
         tc::mbar_wait(nx_ready, i & 1);

@@ -927,18 +927,24 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
                             ((uint32_t)SP_BINS + 1u + (uint32_t)R) * 4u;
   p.off_bar = al(p.off_sc + sc_bytes, 16);
   // operand views of M-tile mt read 128 rows from row mt*128 of every panel: keep those reads inside the allocation
-  const uint32_t reach = p.off_nx + (uint32_t)(F / 8 - 1) * p.pstrideA + RP * 16u;
+  uint32_t reach = p.off_nx + (uint32_t)(F / 8 - 1) * p.pstrideA + RP * 16u;
+  p.sw128 = h->sw128 ? 1 : 0;
+  for (int i = 0; i < p.nseg; ++i) if (segs[i].width % 64) p.sw128 = 0;
+  p.chunk_bytes = (uint32_t)p.Rbox * 128u;
+  // the last SWIZZLE_128B tile of the second buffer is read for 128*MT rows: keep that inside the allocation
+  if (p.sw128) reach = std::max(reach, p.off_in + p.in_stride + (uint32_t)(p.Kself / 64 - 1) * p.chunk_bytes + RP * 128u);
   const size_t smem = std::max<size_t>(p.off_bar + 11 * 8 + 16, reach);
   if (smem > 227 * 1024) return -1;
-  for (int i = 0; i < p.nseg; ++i)
-    if (!make_rows_tmap(&p.tm_self[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox, segs[i].width)) return -1;
+  for (int i = 0; i < p.nseg; ++i) {
+    if (p.sw128 ? !make_rows_tmap_sw(&p.tm_self[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox)
+                : !make_rows_tmap(&p.tm_self[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox, segs[i].width)) return -1;
+  }
   if (!make_rows_tmap(&p.tm_other, other_dense, S * Ro, F, F, p.Kp, F)) return -1;
   static bool attr_set = false;
   if (!attr_set) {
     CU(cudaFuncSetAttribute(sp_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
-  p.pf = getenv("GNNUDS_SP_PF") ? atoi(getenv("GNNUDS_SP_PF")) : 2;
   const unsigned grid = (unsigned)std::min<long long>(S, h->sm_count);
   // GNNUDS_TRACE_FILE=<path> [GNNUDS_TRACE_LAUNCH=k]: clock64 stamps of CTA 0 of the k-th sp_conv launch
   static int traced = 0;
