@@ -34,6 +34,7 @@ constexpr int SP_BINS = SP_GRAPH_WARPS * 4;                               // 8-l
 
 struct SpConvP {
   CUtensorMap tm_self[2];     // {8, S*R rows, w/8 panels}, box {8, Rbox, w/8};  sw128: {w, S*R rows}, box {64, Rbox}, SWIZZLE_128B
+  int sw_x;                   // other_dense as one SWIZZLE_128B MN-major tile [Kp x 64] (F == 64): map {F, S*Ro rows}, box {64, Kp}
   int sw128; uint32_t chunk_bytes;   // self operand as SWIZZLE_128B K-major tiles of Rbox*128 bytes per 64 columns
   CUtensorMap tm_other;       // {8, S*Ro rows, F/8 panels}, box {8, Kp, F/8}
   int nseg, segw[2];
@@ -136,7 +137,8 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
             o += (uint32_t)(p.segw[s] >> 3) * p.pstrideA;
           }
         }
-        tc::tma_load_3d(dst + p.xe_off, &p.tm_other, 0, smp * p.Ro, 0, &in_full[buf]);
+        if (p.sw_x) tc::tma_load_2d(dst + p.xe_off, &p.tm_other, 0, smp * p.Ro, &in_full[buf]);
+        else tc::tma_load_3d(dst + p.xe_off, &p.tm_other, 0, smp * p.Ro, 0, &in_full[buf]);
       }
     }
   } else if (warp == SP_DRAIN_WARPS + SP_GRAPH_WARPS) {
@@ -166,8 +168,10 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         // NodeEdge: D[row, f] = sum_k Mat[row, k] * other_dense[k, f]
         // descriptors advance linearly with the start address: one 64-bit add per MMA in the issue loops
         {
-          uint64_t ad = m_desc0, bd = tc::smem_desc(in_addr + xe_off, 128u, pstrideX);
-          for (int ks = 0; ks < ks_kp; ++ks, ad += m_step, bd += 16u) {
+          // B = other_dense[s], MN-major: 16 k-rows per step = 256 bytes of a panel, or two 1024-byte swizzle atoms
+          uint64_t ad = m_desc0, bd = p.sw_x ? tc::smem_desc_sw128(in_addr + xe_off) : tc::smem_desc(in_addr + xe_off, 128u, pstrideX);
+          const uint64_t b_step = p.sw_x ? 128u : 16u;
+          for (int ks = 0; ks < ks_kp; ++ks, ad += m_step, bd += b_step) {
             tc::umma(acc_ne, ad, bd, idesc_ne, ks != 0);
             if (MT2) tc::umma(acc_ne + (uint32_t)F, ad + 128u, bd, idesc_ne, ks != 0);
           }

@@ -916,7 +916,8 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   p.off_m = al(p.w_bytes, 128);
   p.off_in = al(p.off_m + p.m_bytes, 1024);
   p.self_bytes = (uint32_t)(p.Kself / 8) * p.pstrideA;
-  p.xe_off = al(p.self_bytes, 128);
+  p.sw_x = (h->sw128 && F == 64 && p.Kp % 8 == 0) ? 1 : 0;
+  p.xe_off = al(p.self_bytes, p.sw_x ? 1024 : 128);
   p.xe_bytes = (uint32_t)(F / 8) * p.pstrideX;
   p.in_stride = al(std::max(p.xe_off + p.xe_bytes, (uint32_t)R * p.hsb), 1024);
   p.off_nx = p.off_in + 2 * p.in_stride;
@@ -939,7 +940,8 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
     if (p.sw128 ? !make_rows_tmap_sw(&p.tm_self[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox)
                 : !make_rows_tmap(&p.tm_self[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox, segs[i].width)) return -1;
   }
-  if (!make_rows_tmap(&p.tm_other, other_dense, S * Ro, F, F, p.Kp, F)) return -1;
+  if (p.sw_x ? !make_rows_tmap_sw(&p.tm_other, other_dense, S * Ro, F, F, p.Kp)
+             : !make_rows_tmap(&p.tm_other, other_dense, S * Ro, F, F, p.Kp, F)) return -1;
   static bool attr_set = false;
   if (!attr_set) {
     CU(cudaFuncSetAttribute(sp_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
