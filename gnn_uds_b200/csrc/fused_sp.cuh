@@ -50,7 +50,7 @@ struct SpConvP {
   uint32_t self_bytes, xe_bytes;
   long long* trace;           // debug: clock64 stamps of CTA 0, SP_NSTAMP per sample (GNNUDS_TRACE_FILE), else null
 };
-constexpr int SP_NSTAMP = 10;
+constexpr int SP_NSTAMP = 12;
 #define SP_STAMP(i, k) do { if (p.trace && blockIdx.x == 0 && (i) < 64) p.trace[(i) * SP_NSTAMP + (k)] = clock64(); } while (0)
 
 __device__ __forceinline__ void graph_bar_sync() { asm volatile("bar.sync 2, %0;" ::"n"(SP_GRAPH_WARPS * 32) : "memory"); }
@@ -59,14 +59,16 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.off_bar);
-  uint64_t* in_full = bars;          // [2] TMA complete_tx
-  uint64_t* in_empty = bars + 2;     // [2] graph group released the buffer (h tile consumed)
-  uint64_t* h_full = bars + 4;       // [2] drain group wrote the h tile
-  uint64_t* ne_done = bars + 6;      // NodeEdge MMAs committed
-  uint64_t* nx_ready = bars + 7;     // NE panels written (drain group)
-  uint64_t* conv_done = bars + 8;    // conv MMAs committed
-  uint64_t* wbar = bars + 9;         // resident weights landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  uint64_t* xe_full = bars;          // [2] TMA complete_tx, other_dense tile
+  uint64_t* self_full = bars + 2;    // [2] TMA complete_tx, self tiles
+  uint64_t* xe_empty = bars + 4;     // [2] NodeEdge MMAs that read the other_dense tile completed (tcgen05.commit)
+  uint64_t* self_empty = bars + 6;   // [2] graph group released the self region (h tile consumed)
+  uint64_t* h_full = bars + 8;       // [2] drain group wrote the h tile
+  uint64_t* ne_done = bars + 10;     // NodeEdge MMAs committed
+  uint64_t* nx_ready = bars + 11;    // NE panels written (drain group)
+  uint64_t* conv_done = bars + 12;   // conv MMAs committed
+  uint64_t* wbar = bars + 13;        // resident weights landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
   // scratch: bias[Nout] asf[Nout] anf[Nout] | ss[2][RP] sn[2][RP] | inv[2][RP] | alpha[2][nnz] | rp[R+1] ci[nnz]
   const int RP = 128 * p.MT;
   float* bias_s = reinterpret_cast<float*>(smem + p.off_sc);
@@ -83,8 +85,10 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
   if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
   if (tid == 32) {
     for (int i = 0; i < 2; ++i) {
-      tc::mbar_init(&in_full[i], 1);
-      tc::mbar_init(&in_empty[i], SP_GRAPH_WARPS * 32);
+      tc::mbar_init(&xe_full[i], 1);
+      tc::mbar_init(&self_full[i], 1);
+      tc::mbar_init(&xe_empty[i], 1);
+      tc::mbar_init(&self_empty[i], SP_GRAPH_WARPS * 32);
       tc::mbar_init(&h_full[i], SP_DRAIN_WARPS * 32);
     }
     tc::mbar_init(ne_done, 1);
@@ -121,24 +125,37 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
     if (lane == 0) {
       for (int s = 0; s < p.nseg; ++s) tc::tma_prefetch_desc(&p.tm_self[s]);
       tc::tma_prefetch_desc(&p.tm_other);
+      // The two halves of an input buffer are released at different times: the other_dense tile as soon as the
+      // NodeEdge MMAs have read it, the self tiles (whose bytes then hold the h tile) only when the graph group is
+      // done with the sample.  So NodeEdge + its drain of sample i+2 run while the graph group still works on
+      // sample i, and only [self load -> conv -> drain] remains between two samples of the graph group.
+      auto issue_xe = [&](int i) {
+        const int buf = i & 1;
+        const int smp = (int)blockIdx.x + i * (int)gridDim.x;
+        if (i >= 2) tc::mbar_wait(&xe_empty[buf], ((i >> 1) & 1) ^ 1);
+        uint8_t* dst = smem + p.off_in + (size_t)buf * p.in_stride + p.xe_off;
+        tc::mbar_expect_tx(&xe_full[buf], p.xe_bytes);
+        if (p.sw_x) tc::tma_load_2d(dst, &p.tm_other, 0, smp * p.Ro, &xe_full[buf]);
+        else tc::tma_load_3d(dst, &p.tm_other, 0, smp * p.Ro, 0, &xe_full[buf]);
+      };
+      if (n_it > 0) issue_xe(0);
       for (int i = 0; i < n_it; ++i) {
         const int buf = i & 1;
         const int smp = (int)blockIdx.x + i * (int)gridDim.x;
-        if (i >= 2) tc::mbar_wait(&in_empty[buf], ((i >> 1) & 1) ^ 1);
+        if (i >= 2) tc::mbar_wait_sleep(&self_empty[buf], ((i >> 1) & 1) ^ 1, 64);
         SP_STAMP(i, 0);
         uint8_t* dst = smem + p.off_in + (size_t)buf * p.in_stride;
-        tc::mbar_expect_tx(&in_full[buf], p.self_bytes + p.xe_bytes);
+        tc::mbar_expect_tx(&self_full[buf], p.self_bytes);
         uint32_t o = 0;
         for (int s = 0; s < p.nseg; ++s) {
           if (p.sw128) {        // one SWIZZLE_128B tile [Rbox x 64] per 64 columns (128-byte TMA requests)
-            for (int k0 = 0; k0 < p.segw[s]; k0 += 64, o += p.chunk_bytes) tc::tma_load_2d(dst + o, &p.tm_self[s], k0, smp * p.R, &in_full[buf]);
+            for (int k0 = 0; k0 < p.segw[s]; k0 += 64, o += p.chunk_bytes) tc::tma_load_2d(dst + o, &p.tm_self[s], k0, smp * p.R, &self_full[buf]);
           } else {
-            tc::tma_load_3d(dst + o, &p.tm_self[s], 0, smp * p.R, 0, &in_full[buf]);
+            tc::tma_load_3d(dst + o, &p.tm_self[s], 0, smp * p.R, 0, &self_full[buf]);
             o += (uint32_t)(p.segw[s] >> 3) * p.pstrideA;
           }
         }
-        if (p.sw_x) tc::tma_load_2d(dst + p.xe_off, &p.tm_other, 0, smp * p.Ro, &in_full[buf]);
-        else tc::tma_load_3d(dst + p.xe_off, &p.tm_other, 0, smp * p.Ro, 0, &in_full[buf]);
+        if (i + 1 < n_it) issue_xe(i + 1);
       }
     }
   } else if (warp == SP_DRAIN_WARPS + SP_GRAPH_WARPS) {
@@ -162,7 +179,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
       for (int i = 0; i < n_it; ++i) {
         const int buf = i & 1;
         const uint32_t in_addr = tc::smem_u32(smem + off_in + (size_t)buf * in_stride);
-        tc::mbar_wait(&in_full[buf], (i >> 1) & 1);
+        tc::mbar_wait(&xe_full[buf], (i >> 1) & 1);
         tc::tc_fence_after();
         SP_STAMP(i, 1);
         // NodeEdge: D[row, f] = sum_k Mat[row, k] * other_dense[k, f]
@@ -177,10 +194,13 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
           }
         }
         tc::umma_commit(ne_done);
+        tc::umma_commit(&xe_empty[buf]);
         SP_STAMP(i, 2);
         // conv over the self columns first (they are ready), then over the NodeEdge columns.  The conv
         // accumulators of the previous sample must have been drained (h_full of sample i-1).
         if (i >= 1) { tc::mbar_wait(&h_full[(i - 1) & 1], ((i - 1) >> 1) & 1); tc::tc_fence_after(); }
+        tc::mbar_wait(&self_full[buf], (i >> 1) & 1);
+        tc::tc_fence_after();
         uint64_t wd = w_desc0;
         {
           if (p.sw128) {
@@ -251,7 +271,8 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         if (mt * 128 + q * 32 >= p.R) continue;
         const int row = mt * 128 + q * 32 + lane;
         const uint32_t ta = acc_conv + ((uint32_t)(q * 32) << 16) + (uint32_t)(mt * p.Nout);
-        uint8_t* hrow = hbase + (size_t)row * p.hsb;
+        uint8_t* hrow = hbase + (size_t)row * p.hsb;       // 16-byte chunk c of a row lives at chunk c ^ (row & 7)
+        const int hsw = row & 7;
         // scores from the fp32 accumulators: two independent chains per vector, 16-byte broadcast loads of the
         // attention vectors (8 columns at a time keeps the 704-thread register budget)
         float ps0 = 0.f, ps1 = 0.f, pn0 = 0.f, pn1 = 0.f;
@@ -261,7 +282,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
           tc::tmem_ld_wait();
           if (row < p.R) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(hrow + c0 * 2 + j * 16) = tc::pack8_bf16(v + 8 * j);
+            for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(hrow + ((((c0 >> 3) + j) ^ hsw) << 4)) = tc::pack8_bf16(v + 8 * j);
             if (p.gat) {
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
@@ -291,7 +312,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
     for (int i = 0; i < n_it; ++i) {
       const int buf = i & 1;
       const int smp = (int)blockIdx.x + i * (int)gridDim.x;
-      tc::mbar_wait(&h_full[buf], (i >> 1) & 1);
+      tc::mbar_wait_sleep(&h_full[buf], (i >> 1) & 1, 64);
       if (gt == 0) SP_STAMP(i, 7);
       const uint8_t* hbase = smem + p.off_in + (size_t)buf * p.in_stride;
       float* al = alpha + buf * p.nnz;
@@ -341,12 +362,13 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
           float a0[8], a1[8];
 #pragma unroll
           for (int k = 0; k < 8; ++k) { a0[k] = 0.f; a1[k] = 0.f; }
-          const uint8_t* hb = hbase + (e0 + gl * 8) * 2;
+          const uint8_t* hb = hbase + e0 * 2;
           int qq = beg;
           for (; qq + 1 < end; qq += 2) {
             const float w0 = al[qq], w1 = al[qq + 1];
-            const uint8_t* hp0 = hb + (size_t)ci_s[qq] * p.hsb;
-            const uint8_t* hp1 = hb + (size_t)ci_s[qq + 1] * p.hsb;
+            const int j0 = ci_s[qq], j1 = ci_s[qq + 1];
+            const uint8_t* hp0 = hb + (size_t)j0 * p.hsb + ((gl ^ (j0 & 7)) << 4);
+            const uint8_t* hp1 = hb + (size_t)j1 * p.hsb + ((gl ^ (j1 & 7)) << 4);
             const uint4 u00 = *reinterpret_cast<const uint4*>(hp0);
             const uint4 u10 = *reinterpret_cast<const uint4*>(hp1);
             uint4 u01 = u00, u11 = u10;
@@ -369,7 +391,8 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
           }
           if (qq < end) {
             const float w = al[qq];
-            const uint8_t* hp = hb + (size_t)ci_s[qq] * p.hsb;
+            const int j0 = ci_s[qq];
+            const uint8_t* hp = hb + (size_t)j0 * p.hsb + ((gl ^ (j0 & 7)) << 4);
             const uint4 u0 = *reinterpret_cast<const uint4*>(hp);
             float hv[8];
             tc::unpack8_bf16(u0, hv);
@@ -396,7 +419,11 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         }
       }
       if (gt == 0) SP_STAMP(i, 9);
-      mbar_arrive(&in_empty[buf]);                    // this thread is done with the h tile of the sample
+      if (p.trace && blockIdx.x == 0 && i < 64 && lane == 0) {     // slowest / per-warp-0..3 spread of the gather
+        atomicMax(reinterpret_cast<unsigned long long*>(p.trace + i * SP_NSTAMP + 10), (unsigned long long)clock64());
+        if (gw == 15) p.trace[i * SP_NSTAMP + 11] = clock64();
+      }
+      mbar_arrive(&self_empty[buf]);                  // this thread is done with the h tile of the sample
     }
   }
   tc::tc_fence_before();

@@ -904,7 +904,7 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   p.S = (int)S; p.R = R; p.Ro = Ro; p.F = F; p.Nout = E; p.act = act; p.gat = gat ? 1 : 0;
   p.Rbox = (R + 7) / 8 * 8; p.Kp = h->ne_kp[side]; p.MT = (R + 127) / 128;
   p.pstrideA = (uint32_t)p.Rbox * 16u; p.pstrideM = h->ne_pstride[side]; p.pstrideX = (uint32_t)p.Kp * 16u;
-  p.hsb = (uint32_t)E * 2u + 16u;
+  p.hsb = (uint32_t)E * 2u;           // swizzled rows, no padding: the h tile fits the bytes of the self tiles
   p.Wimg = h->d_wimg + h->img_off[w.t[0]]; p.w_bytes = (uint32_t)Ktot * E * 2u;
   p.Mimg = h->d_ne_img[side][li]; p.m_bytes = h->ne_img_bytes[side];
   p.bias = W(h, w.t[gat ? 3 : 1]);
@@ -917,7 +917,7 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   p.off_in = al(p.off_m + p.m_bytes, 1024);
   p.self_bytes = (uint32_t)(p.Kself / 8) * p.pstrideA;
   p.sw_x = (h->sw128 && F == 64 && p.Kp % 8 == 0) ? 1 : 0;
-  p.xe_off = al(p.self_bytes, p.sw_x ? 1024 : 128);
+  p.xe_off = al(std::max(p.self_bytes, (uint32_t)R * p.hsb), p.sw_x ? 1024 : 128);   // h tile stays clear of the other_dense tile
   p.xe_bytes = (uint32_t)(F / 8) * p.pstrideX;
   p.in_stride = al(std::max(p.xe_off + p.xe_bytes, (uint32_t)R * p.hsb), 1024);
   p.off_nx = p.off_in + 2 * p.in_stride;
@@ -934,7 +934,7 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   p.chunk_bytes = (uint32_t)p.Rbox * 128u;
   // the last SWIZZLE_128B tile of the second buffer is read for 128*MT rows: keep that inside the allocation
   if (p.sw128) reach = std::max(reach, p.off_in + p.in_stride + (uint32_t)(p.Kself / 64 - 1) * p.chunk_bytes + RP * 128u);
-  const size_t smem = std::max<size_t>(p.off_bar + 11 * 8 + 16, reach);
+  const size_t smem = std::max<size_t>(p.off_bar + 15 * 8 + 16, reach);
   if (smem > 227 * 1024) return -1;
   for (int i = 0; i < p.nseg; ++i) {
     if (p.sw128 ? !make_rows_tmap_sw(&p.tm_self[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox)

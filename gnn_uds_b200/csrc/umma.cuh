@@ -46,6 +46,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
 }
 
+// same, for waiters that are not on the critical path: back off with nanosleep between polls so that spinning
+// warps do not take issue slots from working ones
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns) {
+  uint32_t done;
+  for (;;) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    if (done) break;
+    __nanosleep(ns);
+  }
+}
+
 // ---- bulk copy global -> shared (TMA engine, 1-D; SASS UBLKCP) ------------------------------
 // bytes % 16 == 0, both addresses 16-byte aligned; completion is signalled on `bar` (complete_tx).
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
