@@ -10,7 +10,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgnnuds.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 CONV_GCN, CONV_GAT = 1, 2
 REC_CONV1D, REC_GRU, REC_LSTM = 1, 2, 3
 ACT = {"linear": 0, None: 0, "relu": 1, "tanh": 2, "sigmoid": 3}
@@ -35,7 +35,8 @@ class Graph(C.Structure):
     _fields_ = [("row_ptr", _pi), ("col_idx", _pi), ("val", _pf), ("n", C.c_int32), ("nnz", C.c_int32),
                 ("e_row_ptr", _pi), ("e_col_idx", _pi), ("e_val", _pf), ("m", C.c_int32), ("e_nnz", C.c_int32),
                 ("edges", _pi), ("act_of_edge", _pi), ("act_out_of_node", _pi), ("act_in_of_node", _pi),
-                ("hmin", _pf), ("hmax", _pf), ("is_outfall", _pf), ("ehmax", _pf)]
+                ("hmin", _pf), ("hmax", _pf), ("is_outfall", _pf), ("ehmax", _pf),
+                ("pump", _pf), ("offset", _pf), ("pump_in", _pf), ("pump_out", _pf), ("area", _pf)]
 
 
 class GnnUdsError(RuntimeError):

@@ -90,6 +90,11 @@ struct gnnuds_handle {
   int *d_edges = nullptr, *d_act_of_edge = nullptr, *d_act_out = nullptr, *d_act_in = nullptr;
   int *d_inc_ptr = nullptr, *d_inc_edge = nullptr, *d_inc_sign = nullptr;
   float *d_hmin = nullptr, *d_hmax = nullptr, *d_outfall = nullptr, *d_ehmax = nullptr;
+  // pumped / offset networks (null on the others)
+  float *d_pump = nullptr, *d_offset = nullptr, *d_pump_in = nullptr, *d_pump_out = nullptr, *d_area = nullptr;
+  int *d_edge_from = nullptr, *d_ps = nullptr;
+  int n_ps = 0;                         // pumped-storage nodes (emulator.py:591)
+  bool has_pump = false, has_offset = false;
   std::vector<int> h_edges;
 
   // norms (max,min) per item
@@ -515,7 +520,8 @@ void set_dbg(gnnuds_handle* h, const Stream2& st, long long rows_x, long long ro
   h->dbg_ptr[1] = joint ? nullptr : st.e[0].p; h->dbg_width[1] = st.e[0].width; h->dbg_rows[1] = rows_e;
 }
 
-int run_postproc(gnnuds_handle* h, const float* b, const float* a, long long Bc, float* y, float* ey, bool normalised_io) {
+int run_postproc(gnnuds_handle* h, const float* x, const float* b, const float* a, long long Bc, float* y, float* ey,
+                 bool normalised_io) {
   const auto& c = h->c;
   const int N = c.n_node, M = c.n_edge, To = c.seq_out;
   const int ldn = h->ldn();
@@ -536,9 +542,25 @@ int run_postproc(gnnuds_handle* h, const float* b, const float* a, long long Bc,
   if (normalised_io && c.tide) return fail(h, GNNUDS_E_INVALID, "ROLL_NORM with tide not supported");
   const bool big = (size_t)M * sizeof(float) > 40 * 1024;      // large graphs: edge flows staged in HBM scratch (SS covers Bc*T*max(N,M))
   p.efl_g = big ? h->SS : nullptr;
-  postproc_kernel<<<grid_for(h, p.S, 1, 16), big ? 512 : 128, big ? 0 : (size_t)M * sizeof(float), h->stream>>>(p);
+  const bool need_h = h->has_pump || h->has_offset;
+  if (need_h) {
+    p.edge_from = h->d_edge_from; p.pump = h->has_pump ? h->d_pump : nullptr; p.offset = h->has_offset ? h->d_offset : nullptr;
+    p.pump_in = h->has_pump ? h->d_pump_in : nullptr; p.pump_out = h->has_pump ? h->d_pump_out : nullptr;
+    p.hn_g = big ? h->SN : nullptr;
+  }
+  const size_t psm = big ? 0 : (size_t)(M + (need_h ? N : 0)) * sizeof(float);
+  postproc_kernel<<<grid_for(h, p.S, 1, 16), big ? 512 : 128, psm, h->stream>>>(p);
   ++h->launches;
   CU(cudaGetLastError());
+  if (h->n_ps && !normalised_io) {
+    // P3: pumped-storage depth integrated over the horizon (emulator.py:590-598), then the h-dependent part of constrain
+    PumpStoreP q{y, h->ny(), x, c.n_in, b, c.b_in, h->d_ps, h->n_ps, h->d_area, h->d_hmin, h->d_hmax, h->d_outfall,
+                 Bc, c.seq_in, To, N, c.if_flood ? 1 : 0, c.epsilon};
+    const long long work = Bc * h->n_ps;
+    pump_storage_kernel<<<(unsigned)((work + 127) / 128), 128, 0, h->stream>>>(q);
+    ++h->launches;
+    CU(cudaGetLastError());
+  }
   return 0;
 }
 
@@ -624,7 +646,7 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
     if ((rc = launch_head(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return rc;
   }
   if ((rc = launch_head(h, h->EA, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
-  return run_postproc(h, b, a, Bc, y, ey, normalised_io);
+  return run_postproc(h, x, b, a, Bc, y, ey, normalised_io);
 }
 
 // =========================================================================================
@@ -1179,7 +1201,7 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
     if (!fuse_head && (rc = launch_head<bf16>(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return rc;
   }
   if (!fuse_ch && (rc = launch_head<bf16>(h, h->EA, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
-  return run_postproc(h, b, a, Bc, y, ey, normalised_io);
+  return run_postproc(h, x, b, a, Bc, y, ey, normalised_io);
 }
 
 
@@ -1403,7 +1425,7 @@ int gnnuds_destroy(gnnuds_handle* h) {
   void* ptrs[] = {h->d_blob, h->d_rp, h->d_ci, h->d_erp, h->d_eci, h->d_val, h->d_eval, h->d_edges, h->d_act_of_edge,
                   h->d_act_out, h->d_act_in, h->d_inc_ptr, h->d_inc_edge, h->d_inc_sign, h->d_hmin, h->d_hmax,
                   h->d_outfall, h->d_ehmax, h->d_nx, h->d_nb, h->d_ny, h->d_ne, h->d_ws, h->ro_x, h->ro_ex, h->ro_b, h->ro_a, h->d_wimg,
-                  h->d_bins[0], h->d_bins[1]};
+                  h->d_bins[0], h->d_bins[1], h->d_pump, h->d_offset, h->d_pump_in, h->d_pump_out, h->d_area, h->d_edge_from, h->d_ps};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_ne_img[s]) if (p) cudaFree(p);
@@ -1480,6 +1502,37 @@ int gnnuds_set_graph(gnnuds_handle* h, const gnnuds_graph* g) {
   if ((rc = upload(h, &h->d_hmax, g->hmax, (size_t)N))) return rc;
   if ((rc = upload(h, &h->d_outfall, g->is_outfall, (size_t)N))) return rc;
   if ((rc = upload(h, &h->d_ehmax, g->ehmax, (size_t)M))) return rc;
+  // pumps, inlet offsets, pumped storage (emulator.py:590-598, 649-667)
+  {
+    void* old[] = {h->d_pump, h->d_offset, h->d_pump_in, h->d_pump_out, h->d_area, h->d_edge_from, h->d_ps};
+    for (void* q : old) if (q) cudaFree(q);
+    h->d_pump = h->d_offset = h->d_pump_in = h->d_pump_out = h->d_area = nullptr; h->d_edge_from = h->d_ps = nullptr;
+    h->n_ps = 0; h->has_pump = h->has_offset = false;
+    auto any = [](const float* v, int n) { if (!v) return false; for (int i = 0; i < n; ++i) if (v[i] != 0.f) return true; return false; };
+    const bool pm = any(g->pump, M) || any(g->pump_in, N) || any(g->pump_out, N), of = any(g->offset, M);
+    if ((pm || of) && c.graph_base) return fail(h, GNNUDS_E_INVALID, "pumps / inlet offsets with graph_base != 0 are not supported");
+    if (pm || of) {
+      std::vector<int> from(M);
+      for (int m = 0; m < M; ++m) from[m] = g->edges[2 * m];
+      if ((rc = upload(h, &h->d_edge_from, from.data(), (size_t)M))) return rc;
+    }
+    if (of) { if ((rc = upload(h, &h->d_offset, g->offset, (size_t)M))) return rc; h->has_offset = true; }
+    if (pm) {
+      std::vector<float> zm(M, 0.f), zn(N, 0.f);
+      if ((rc = upload(h, &h->d_pump, g->pump ? g->pump : zm.data(), (size_t)M))) return rc;
+      if ((rc = upload(h, &h->d_pump_in, g->pump_in ? g->pump_in : zn.data(), (size_t)N))) return rc;
+      if ((rc = upload(h, &h->d_pump_out, g->pump_out ? g->pump_out : zn.data(), (size_t)N))) return rc;
+      if ((rc = upload(h, &h->d_area, g->area ? g->area : zn.data(), (size_t)N))) return rc;
+      // ps = (area * (clip(node_edge,0,1) @ pump)) > 0: storage nodes that are the inlet of a pump
+      std::vector<double> acc(N, 0.0);
+      if (g->pump) for (int m = 0; m < M; ++m) if (g->edges[2 * m] != g->edges[2 * m + 1]) acc[g->edges[2 * m]] += g->pump[m];
+      std::vector<int> ps;
+      for (int n = 0; n < N; ++n) if (g->area && g->area[n] * acc[n] > 0) ps.push_back(n);
+      h->n_ps = (int)ps.size();
+      if (h->n_ps && (rc = upload(h, &h->d_ps, ps.data(), ps.size()))) return rc;
+      h->has_pump = true;
+    }
+  }
   h->has_graph = true;
   h->has_weights = false;   // folded NodeEdge matrices depend on the incidence
   return 0;

@@ -1079,18 +1079,49 @@ struct PostP {
   int if_flood, edge_fusion, act, tide, normalised;
   float epsilon;
   float* efl_g;           // (S, M) scratch for the physical edge flows when M floats exceed shared memory, else null
+  // pumped / offset networks (all null on pump-free, offset-free ones)
+  const int* edge_from;   // (M) FromNode of a link: np.matmul(v, clip(node_edge,0,1))[m] = v[from(m)]
+  const float* pump; const float* offset;        // (M)
+  const float* pump_in; const float* pump_out;   // (N)
+  float* hn_g;            // (S, N) scratch for the normalised node depth when the edge pass needs it and N floats exceed smem
 };
 
 __global__ void __launch_bounds__(512) postproc_kernel(PostP p) {
-  extern __shared__ float efl_s[];   // M physical edge flows
+  extern __shared__ float efl_s[];   // M physical edge flows [+ N normalised node depths on pumped/offset networks]
+  const bool need_h = p.pump || p.offset;
   for (long long s = blockIdx.x; s < p.S; s += gridDim.x) {
     float* efl = p.efl_g ? p.efl_g + s * p.M : efl_s;
+    float* hn = p.hn_g ? p.hn_g + s * p.N : efl_s + p.M;
     __syncthreads();
+    if (need_h) {                                                // node depth (tide applied) read by the edge pass
+      for (int n = threadIdx.x; n < p.N; n += blockDim.x) {
+        float hN = p.out_n[(s * p.N + n) * p.ldn];
+        if (p.tide) {
+          const float braw = p.b_raw[(s * p.N + n) * p.b_in + p.b_in - 1];
+          const float mx = p.bmax[n * p.cb + p.b_in - 1], mn = p.bmin[n * p.cb + p.b_in - 1];
+          hN = hN * (1.f - p.is_outfall[n]) + (braw - mn) / (mx - mn);
+        }
+        hn[n] = hN;
+      }
+      __syncthreads();
+    }
     for (int m = threadIdx.x; m < p.M; m += blockDim.x) {
       const float* src = p.out_e + (s * p.M + m) * p.lde;
       float v[4];
       for (int c = 0; c < p.e_out; ++c) v[c] = src[c];
+      if (p.offset && p.offset[m] > 0.f) {                       // emulator.py:649-653: inlet offset gate on positive flow
+        const int fn = p.edge_from[m];
+        const float mx = p.ymax[fn * p.cy], mn = p.ymin[fn * p.cy];
+        const float inoff = (hn[fn] * (mx - mn) + mn) - p.hmin[fn];
+        float& f = v[p.e_out - 1];
+        if (f > 0.f && !(inoff > p.offset[m])) f = 0.f;
+      }
       if (p.act) {
+        if (p.pump && p.pump[m] != 0.f) {                        // emulator.py:656-659: rated flow while the inlet tank holds water
+          const float mx = p.emax[m * p.ce + p.e_out - 1];
+          const float fl = p.pump[m] * (hn[p.edge_from[m]] > 0.01f ? 1.f : 0.f) * (mx > 1e-3f ? 1.f / mx : 0.f);
+          if (fl != 0.f) v[p.e_out - 1] = fl;
+        }
         const int k = p.act_of_edge[m];
         const float ae = (k >= 0) ? p.a[s * p.n_act + k] : 1.f;
         v[p.e_out - 1] *= ae;                                    // emulator.py:660
@@ -1133,6 +1164,12 @@ __global__ void __launch_bounds__(512) postproc_kernel(PostP p) {
       } else {
         yn[1] = src[1]; yn[2] = src[2];
         if (p.act) {                                             // emulator.py:661-670
+          if (p.pump_in) {
+            const float on = hN > 0.01f ? 1.f : 0.f;
+            const float fli = p.pump_in[n] * on / p.ymax[n * p.cy + 1], flo = p.pump_out[n] * on / p.ymax[n * p.cy + 2];
+            if (fli != 0.f) yn[1] = fli;
+            if (flo != 0.f) yn[2] = flo;
+          }
           const int ko = p.act_out_of_node[n], ki = p.act_in_of_node[n];
           if (ko >= 0) yn[2] *= p.a[s * p.n_act + ko];
           if (ki >= 0) yn[1] *= p.a[s * p.n_act + ki];
@@ -1169,6 +1206,42 @@ __global__ void __launch_bounds__(512) postproc_kernel(PostP p) {
       else if (p.if_flood) qw *= f ? 1.f : 0.f;
       dst[0] = h; dst[1] = yp[1]; dst[2] = yp[2];
       if (p.if_flood) { dst[3] = pr; dst[4] = qw; } else dst[3] = qw;
+    }
+  }
+}
+
+// P3 pumped-storage depth (emulator.py:590-598) for the nodes `ps` (storage nodes that feed a pump): the depth is
+// integrated from the predicted flows, de_0 = clip(h_in[last]), de_t = clip(de_{t-1} + (q_us - q_ds)_t / (area + 1e-6)),
+// and replaces h BEFORE constrain, so the h-dependent parts of constrain (emulator.py:727-748) are redone here.
+struct PumpStoreP {
+  float* y; int ny;             // (Bc, To, N, ny) physical, already constrained by postproc_kernel
+  const float* x; int n_in;     // (Bc, Ti, N, n_in) physical input states
+  const float* b_raw; int b_in;
+  const int* ps; int n_ps;      // node indices
+  const float* area; const float* hmin; const float* hmax; const float* is_outfall;
+  long long Bc; int Ti, To, N, if_flood; float epsilon;
+};
+
+__global__ void __launch_bounds__(128) pump_storage_kernel(PumpStoreP p) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.Bc * p.n_ps) return;
+  const long long b = i / p.n_ps;
+  const int n = p.ps[i % p.n_ps];
+  const float lo = p.hmin[n], hi = p.hmax[n], ar = p.area[n] + 1e-6f;
+  float de = 0.f;
+  for (int t = 0; t < p.To; ++t) {
+    float* yy = p.y + ((b * p.To + t) * p.N + n) * p.ny;
+    const float v = t == 0 ? p.x[((b * p.Ti + p.Ti - 1) * p.N + n) * p.n_in] : de + (yy[1] - yy[2]) / ar;
+    de = fminf(fmaxf(v, lo), hi);
+    float h = de;                                               // clip(h, hmin, hmax) of constrain is the identity on de
+    bool f = false;
+    if (p.if_flood) { f = yy[3] > 0.5f; h = f ? hi : h; }
+    yy[0] = h;
+    if (p.epsilon > 0.f) {                                      // q_w gate depends on h: recompute
+      const float r = p.b_raw[((b * p.To + t) * p.N + n) * p.b_in];
+      float qw = fmaxf(yy[1] + r - yy[2], 0.f) * (1.f - p.is_outfall[n]);
+      qw *= ((hi - h) < p.epsilon) ? 1.f : 0.f;
+      yy[p.ny - 1] = qw;
     }
   }
 }

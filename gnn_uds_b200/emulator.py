@@ -106,10 +106,10 @@ class Emulator:
         self.hmax = np.asarray(g("hmax", np.full(self.n_node, 1.5)), dtype=np.float64)
         self.hmin = np.asarray(g("hmin", np.zeros(self.n_node)), dtype=np.float64)
         self.nwei = np.asarray(g("nwei", np.ones(self.n_node)))
-        if float(self.pump.sum() + self.pump_in.sum() + self.pump_out.sum()) > 0:
-            raise NotImplementedError("pumped networks (emulator.py:590-598,656-667) are a 'next' row; not on the CUDA path yet")
-        if float(np.max(self.offset)) > 0:
-            raise NotImplementedError("inlet offsets (emulator.py:649-653) are a 'next' row; not on the CUDA path yet")
+        # pumps / inlet offsets / pumped storage (emulator.py:590-598, 649-667) run on the CUDA path for graph_base == 0
+        self.has_pumps = float(self.pump.sum() + self.pump_in.sum() + self.pump_out.sum()) > 0
+        if (self.has_pumps or float(np.max(self.offset)) > 0) and self.graph_base:
+            raise NotImplementedError("pumps / inlet offsets with graph_base != 0 are not on the CUDA path")
         self.conv = False if conv in ["None", "False", "NoneType", None, False] else conv
         if not self.conv:
             raise NotImplementedError("NN-cat (conv=False, emulator.py:231-233) is a 'next' row; not on the CUDA path yet")
@@ -244,6 +244,10 @@ class Emulator:
             keep.update(aoe=aoe, aout=aout, ain=ain)
             g.act_of_edge, g.act_out_of_node, g.act_in_of_node = cast_i(aoe), cast_i(aout), cast_i(ain)
         g.hmin, g.hmax, g.is_outfall, g.ehmax = cast_f(keep["hmin"]), cast_f(keep["hmax"]), cast_f(keep["outf"]), cast_f(keep["ehmax"])
+        if self.has_pumps or float(np.max(self.offset)) > 0:
+            keep.update(pump=_f32(self.pump), offset=_f32(self.offset), pump_in=_f32(self.pump_in),
+                        pump_out=_f32(self.pump_out), area=_f32(self.area))
+            g.pump, g.offset, g.pump_in, g.pump_out, g.area = (cast_f(keep[k]) for k in ("pump", "offset", "pump_in", "pump_out", "area"))
         _lib.check(self._h, self._lib.gnnuds_set_graph(self._h, C.byref(g)))
 
     # ------------------------------------------------------------------ weights / norms

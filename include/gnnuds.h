@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define GNNUDS_ABI_VERSION 1
+#define GNNUDS_ABI_VERSION 2
 
 enum {
   GNNUDS_OK = 0,
@@ -78,6 +78,13 @@ typedef struct gnnuds_graph {
   const int32_t* act_in_of_node;  /* (n_node) column of `a` or -1 (a_in) */
   const float* hmin; const float* hmax; const float* is_outfall;   /* (n_node) */
   const float* ehmax;                                               /* (n_edge) */
+  /* pumped / offset networks (chaohu, hague): NULL = all zero.  emulator.py:590-598 (pumped-storage depth),
+     649-653 (inlet offset gate), 656-667 (rated pump flow); envs/scenario/chaohu.py:203-226 */
+  const float* pump;      /* (n_edge) rated pump flow of the link, 0 = not a pump */
+  const float* offset;    /* (n_edge) inlet offset of the link */
+  const float* pump_in;   /* (n_node) rated inflow by pumps (non-edge-fusion models) */
+  const float* pump_out;  /* (n_node) rated outflow by pumps */
+  const float* area;      /* (n_node) storage area (emulator.py:591,596) */
 } gnnuds_graph;
 
 typedef struct gnnuds_handle gnnuds_handle;

@@ -49,9 +49,19 @@ CASES = {
     "ast_joint_gat_conv_act": dict(net="astlingen", conv="GAT", recurrent="Conv1D", resnet=False, seq_in=5, seq_out=5,
                                    embed_size=64, hidden_dim=64, n_sp_layer=2, n_tp_layer=2, length=0, order=1,
                                    graph_base=1, act="conti", edge_fusion=True, B=2, seed=50),
+    # pumped / offset networks (chaohu/hague features, emulator.py:590-598, 649-667) on the astlingen table: the four
+    # controlled links become rated pumps fed by the tanks T2,T3,T4,T6 (storage area > 0 -> pumped-storage depth scan),
+    # a few conduits get inlet offsets
+    "ast_pump_act_fusion": dict(net="astlingen", conv="GAT", recurrent="Conv1D", resnet=True, seq_in=6, seq_out=6,
+                                embed_size=128, hidden_dim=64, n_sp_layer=2, n_tp_layer=2, length=1.0, order=1,
+                                edge_fusion=True, if_flood=2, act="conti", epsilon=0.1, pumps=True, B=4, seed=51),
+    "ast_pump_act_nofusion": dict(net="astlingen", conv="GCN", recurrent="GRU", resnet=False, seq_in=5, seq_out=5,
+                                  embed_size=128, hidden_dim=64, n_sp_layer=1, n_tp_layer=1, length=0, order=1,
+                                  act="conti", pumps=True, B=3, seed=52),
 }
 GOLDEN_CASES = ["c1_ast_gcn_gru", "c2_shq_gat_conv_10", "c3_ast_act_5", "ast_gat_gru_noflood",
-                "ast_gcn_lstm_act_nofusion", "ast_gcn_conv_eps0", "ast_joint_gcn_gru_act", "ast_joint_gat_conv_act"]
+                "ast_gcn_lstm_act_nofusion", "ast_gcn_conv_eps0", "ast_joint_gcn_gru_act", "ast_joint_gat_conv_act",
+                "ast_pump_act_fusion", "ast_pump_act_nofusion"]
 
 
 def load_net(name):
@@ -70,6 +80,19 @@ def build_args(case):
     B, seed = hp.pop("B"), hp.pop("seed")
     ga = G.get_args(net, False, length, order, hp.get("graph_base", 0), act_links=act_links if hp.get("act") else None)
     d = dict(vars(ga))
+    if hp.pop("pumps", False):
+        # synthetic pump table in the format of chaohu.get_args (chaohu.py:203-226): rated flows on the controlled
+        # links, their in/out-flow seen from the end nodes, inlet offsets on every 7th conduit
+        rng = np.random.default_rng(1000 + seed)
+        M, N = len(net.links), len(net.nodes)
+        pump, offset, pump_in, pump_out = np.zeros(M), np.zeros(M), np.zeros(N), np.zeros(N)
+        for (u, v) in np.asarray(ga.act_edges):
+            m = int(np.where((np.asarray(ga.edges) == (u, v)).all(1))[0][0])
+            pump[m] = rng.uniform(0.05, 0.5)
+            pump_out[u] += pump[m]
+            pump_in[v] += pump[m]
+        offset[::7] = rng.uniform(0.2, 1.0, size=len(offset[::7])) * (pump[::7] == 0)
+        d.update(pump=pump, offset=offset, pump_in=pump_in, pump_out=pump_out)
     d.update(hp)
     d["model_dir"] = "/nonexistent"
     args = SimpleNamespace(**d)
