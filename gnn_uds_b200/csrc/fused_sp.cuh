@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
   }
   for (int i = tid; i <= p.R; i += SP_THREADS) rp_s[i] = p.row_ptr[i];
   for (int i = tid; i < SP_BINS + 1 + p.R; i += SP_THREADS) bin_s[i] = p.bins[i];
-  for (int i = tid; i < p.nnz; i += SP_THREADS) { ci_s[i] = p.col_idx[i]; if (!p.gat) { alpha[i] = p.val[i]; alpha[p.nnz + i] = p.val[i]; } }
+  for (int i = tid; i < p.nnz; i += SP_THREADS) { ci_s[i] = p.col_idx[i]; if (!p.gat) { const float v = __uint_as_float(tc::pack_f16(p.val[i], p.val[i])); alpha[i] = v; alpha[p.nnz + i] = v; } }
   {
     uint4* z = reinterpret_cast<uint4*>(smem + p.off_nx);
     const int n16 = (int)((p.F / 8) * p.pstrideA / 16);
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
           tc::tmem_ld_wait();
           if (row < p.R) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(hrow + ((((c0 >> 3) + j) ^ hsw) << 4)) = tc::pack8_bf16(v + 8 * j);
+            for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(hrow + ((((c0 >> 3) + j) ^ hsw) << 4)) = tc::pack8_f16(v + 8 * j);
             if (p.gat) {
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
@@ -338,9 +338,11 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
           mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
           float den = 0.f;
           for (int qq = beg + sub; qq < end; qq += 4) {
-            const float w = __expf(al[qq] - mx);
-            al[qq] = w;
-            den += w;
+            // the weight is stored as an fp16 pair; the denominator sums the rounded weights so that the
+            // attention stays a convex combination
+            const __half wh = __float2half_rn(__expf(al[qq] - mx));
+            al[qq] = __uint_as_float(tc::pack_f16(0.f, 0.f) | ((uint32_t)__half_as_ushort(wh) * 0x10001u));
+            den += __half2float(wh);
           }
           den += __shfl_xor_sync(0xffffffffu, den, 1);
           den += __shfl_xor_sync(0xffffffffu, den, 2);
@@ -359,13 +361,16 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         const float scale = p.gat ? inv[r] : 1.f;
         bf16* orow = p.out + ((size_t)smp * R + r) * p.Nout + gl * 8;
         for (int e0 = 0; e0 < p.Nout; e0 += 128) {
-          float a0[8], a1[8];
+          // fp16 h tile, fp16 weights, HFMA2 accumulation (two features per instruction, no unpacking); the few
+          // (<= ~20) terms per row keep the fp16 partial sums within ~1e-3 relative, below the bf16 output rounding
+          __half2 h0[4], h1[4];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) { a0[k] = 0.f; a1[k] = 0.f; }
+          for (int k = 0; k < 4; ++k) { h0[k] = __float2half2_rn(0.f); h1[k] = h0[k]; }
           const uint8_t* hb = hbase + e0 * 2;
+          const uint32_t* alw = reinterpret_cast<const uint32_t*>(al);
           int qq = beg;
           for (; qq + 1 < end; qq += 2) {
-            const float w0 = al[qq], w1 = al[qq + 1];
+            const __half2 w0 = tc::as_half2(alw[qq]), w1 = tc::as_half2(alw[qq + 1]);
             const int j0 = ci_s[qq], j1 = ci_s[qq + 1];
             const uint8_t* hp0 = hb + (size_t)j0 * p.hsb + ((gl ^ (j0 & 7)) << 4);
             const uint8_t* hp1 = hb + (size_t)j1 * p.hsb + ((gl ^ (j1 & 7)) << 4);
@@ -373,37 +378,22 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
             const uint4 u10 = *reinterpret_cast<const uint4*>(hp1);
             uint4 u01 = u00, u11 = u10;
             if (two) { u01 = *reinterpret_cast<const uint4*>(hp0 + 128); u11 = *reinterpret_cast<const uint4*>(hp1 + 128); }
-            float hv[8];
-            tc::unpack8_bf16(u00, hv);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) a0[k] = fmaf(w0, hv[k], a0[k]);
-            tc::unpack8_bf16(u10, hv);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) a0[k] = fmaf(w1, hv[k], a0[k]);
-            if (two) {
-              tc::unpack8_bf16(u01, hv);
-#pragma unroll
-              for (int k = 0; k < 8; ++k) a1[k] = fmaf(w0, hv[k], a1[k]);
-              tc::unpack8_bf16(u11, hv);
-#pragma unroll
-              for (int k = 0; k < 8; ++k) a1[k] = fmaf(w1, hv[k], a1[k]);
-            }
+            tc::hfma8(h0, u00, w0);
+            tc::hfma8(h0, u10, w1);
+            if (two) { tc::hfma8(h1, u01, w0); tc::hfma8(h1, u11, w1); }
           }
           if (qq < end) {
-            const float w = al[qq];
+            const __half2 w = tc::as_half2(alw[qq]);
             const int j0 = ci_s[qq];
             const uint8_t* hp = hb + (size_t)j0 * p.hsb + ((gl ^ (j0 & 7)) << 4);
-            const uint4 u0 = *reinterpret_cast<const uint4*>(hp);
-            float hv[8];
-            tc::unpack8_bf16(u0, hv);
+            tc::hfma8(h0, *reinterpret_cast<const uint4*>(hp), w);
+            if (two) tc::hfma8(h1, *reinterpret_cast<const uint4*>(hp + 128), w);
+          }
+          float a0[8], a1[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) a0[k] = fmaf(w, hv[k], a0[k]);
-            if (two) {
-              const uint4 u1 = *reinterpret_cast<const uint4*>(hp + 128);
-              tc::unpack8_bf16(u1, hv);
-#pragma unroll
-              for (int k = 0; k < 8; ++k) a1[k] = fmaf(w, hv[k], a1[k]);
-            }
+          for (int k = 0; k < 4; ++k) {
+            const float2 f0 = __half22float2(h0[k]), f1 = __half22float2(h1[k]);
+            a0[2 * k] = f0.x; a0[2 * k + 1] = f0.y; a1[2 * k] = f1.x; a1[2 * k + 1] = f1.y;
           }
           const float* bp = bias_s + e0 + gl * 8;
 #pragma unroll

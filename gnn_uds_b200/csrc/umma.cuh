@@ -15,6 +15,7 @@
 // back by shift*16 bytes.  pstride = (R+1)*16 keeps both row-parallel and panel-parallel
 // 16-byte accesses from SIMT code bank-conflict free.
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -199,6 +200,19 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 }
 __device__ __forceinline__ uint4 pack8_bf16(const float* v) {
   return make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+}
+__device__ __forceinline__ uint32_t pack_f16(float lo, float hi) {
+  __half2 v = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ uint4 pack8_f16(const float* v) {
+  return make_uint4(pack_f16(v[0], v[1]), pack_f16(v[2], v[3]), pack_f16(v[4], v[5]), pack_f16(v[6], v[7]));
+}
+__device__ __forceinline__ __half2 as_half2(uint32_t u) { return *reinterpret_cast<__half2*>(&u); }
+// acc[0..3] (8 fp16 lanes) += w * u (8 fp16 values): four HFMA2, no unpacking
+__device__ __forceinline__ void hfma8(__half2* acc, const uint4& u, __half2 w) {
+  acc[0] = __hfma2(w, as_half2(u.x), acc[0]); acc[1] = __hfma2(w, as_half2(u.y), acc[1]);
+  acc[2] = __hfma2(w, as_half2(u.z), acc[2]); acc[3] = __hfma2(w, as_half2(u.w), acc[3]);
 }
 __device__ __forceinline__ void unpack8_bf16(const uint4& u, float* v) {
   const uint32_t w[4] = {u.x, u.y, u.z, u.w};
