@@ -69,7 +69,8 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
   uint64_t* conv_done = bars + 12;   // conv MMAs committed
   uint64_t* wbar = bars + 13;        // resident weights landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
-  // scratch: bias[Nout] asf[Nout] anf[Nout] | ss[2][RP] sn[2][RP] | inv[2][RP] | alpha[2][nnz] | rp[R+1] ci[nnz]
+  // scratch: bias[Nout] asf[Nout] anf[Nout] | ss[2][RP] sn[2][RP] | inv[2][RP] | alpha[2][nnz] | ci[nnz] | rp[R+1] | bins
+  // (nnz counts the PADDED CSR: rows start on multiples of 4 entries, so alpha / ci blocks are 16-byte aligned)
   const int RP = 128 * p.MT;
   float* bias_s = reinterpret_cast<float*>(smem + p.off_sc);
   float* asf = bias_s + p.Nout;
@@ -78,9 +79,10 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
   float* sn = ss + 2 * RP;
   float* inv_s = sn + 2 * RP;
   float* alpha = inv_s + 2 * RP;
-  int* rp_s = reinterpret_cast<int*>(alpha + 2 * p.nnz);
-  int* ci_s = rp_s + p.R + 1;
-  int* bin_s = ci_s + p.nnz;         // bin_ptr[SP_BINS+1] | bin_rows[R]
+  int* ci_s = reinterpret_cast<int*>(alpha + 2 * p.nnz);
+  int* rp_s = ci_s + p.nnz;
+  int* bin_s = rp_s + p.R + 1;       // bin_ptr[SP_BINS+1] | bin_rows[R] | row_len[R]
+  const int* rlen_s = bin_s + SP_BINS + 1 + p.R;
 
   if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
   if (tid == 32) {
@@ -104,7 +106,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
     anf[i] = p.gat ? p.a_neigh[i] : 0.f;
   }
   for (int i = tid; i <= p.R; i += SP_THREADS) rp_s[i] = p.row_ptr[i];
-  for (int i = tid; i < SP_BINS + 1 + p.R; i += SP_THREADS) bin_s[i] = p.bins[i];
+  for (int i = tid; i < SP_BINS + 1 + 2 * p.R; i += SP_THREADS) bin_s[i] = p.bins[i];
   for (int i = tid; i < p.nnz; i += SP_THREADS) { ci_s[i] = p.col_idx[i]; if (!p.gat) { const float v = __uint_as_float(tc::pack_f16(p.val[i], p.val[i])); alpha[i] = v; alpha[p.nnz + i] = v; } }
   {
     uint4* z = reinterpret_cast<uint4*>(smem + p.off_nx);
@@ -325,9 +327,10 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         for (int r0 = 0; r0 < R; r0 += SP_GRAPH_WARPS * 8) {
           const int r = r0 + (gt >> 2);
           const bool live = r < R;
-          const int beg = live ? rp_s[r] : 0, end = live ? rp_s[r + 1] : 0;
+          const int beg = live ? rp_s[r] : 0, pend = live ? rp_s[r + 1] : 0, end = live ? beg + rlen_s[r] : 0;
           const float si = live ? ssb[r] : 0.f;
           float mx = -INFINITY;
+          for (int qq = end + ((sub - end) & 3); qq < pend; qq += 4) al[qq] = 0.f;     // pads of the last block: weight 0
           for (int qq = beg + sub; qq < end; qq += 4) {
             float sc = si + snb[ci_s[qq]];
             sc = sc > 0.f ? sc : 0.2f * sc;
@@ -367,27 +370,25 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
 #pragma unroll
           for (int k = 0; k < 4; ++k) { h0[k] = __float2half2_rn(0.f); h1[k] = h0[k]; }
           const uint8_t* hb = hbase + e0 * 2;
-          const uint32_t* alw = reinterpret_cast<const uint32_t*>(al);
-          int qq = beg;
-          for (; qq + 1 < end; qq += 2) {
-            const __half2 w0 = tc::as_half2(alw[qq]), w1 = tc::as_half2(alw[qq + 1]);
-            const int j0 = ci_s[qq], j1 = ci_s[qq + 1];
-            const uint8_t* hp0 = hb + (size_t)j0 * p.hsb + ((gl ^ (j0 & 7)) << 4);
-            const uint8_t* hp1 = hb + (size_t)j1 * p.hsb + ((gl ^ (j1 & 7)) << 4);
-            const uint4 u00 = *reinterpret_cast<const uint4*>(hp0);
-            const uint4 u10 = *reinterpret_cast<const uint4*>(hp1);
-            uint4 u01 = u00, u11 = u10;
-            if (two) { u01 = *reinterpret_cast<const uint4*>(hp0 + 128); u11 = *reinterpret_cast<const uint4*>(hp1 + 128); }
-            tc::hfma8(h0, u00, w0);
-            tc::hfma8(h0, u10, w1);
-            if (two) { tc::hfma8(h1, u01, w0); tc::hfma8(h1, u11, w1); }
-          }
-          if (qq < end) {
-            const __half2 w = tc::as_half2(alw[qq]);
-            const int j0 = ci_s[qq];
-            const uint8_t* hp = hb + (size_t)j0 * p.hsb + ((gl ^ (j0 & 7)) << 4);
-            tc::hfma8(h0, *reinterpret_cast<const uint4*>(hp), w);
-            if (two) tc::hfma8(h1, *reinterpret_cast<const uint4*>(hp + 128), w);
+          // one block = 4 neighbours: their indices and weights arrive as two 16-byte loads, then eight 16-byte
+          // h loads are in flight before the first HFMA2 (pads carry weight 0)
+          for (int qq = beg; qq < end; qq += 4) {
+            const int4 jj = *reinterpret_cast<const int4*>(ci_s + qq);
+            const uint4 ww = *reinterpret_cast<const uint4*>(al + qq);
+            const uint8_t* hp0 = hb + (size_t)jj.x * p.hsb + ((gl ^ (jj.x & 7)) << 4);
+            const uint8_t* hp1 = hb + (size_t)jj.y * p.hsb + ((gl ^ (jj.y & 7)) << 4);
+            const uint8_t* hp2 = hb + (size_t)jj.z * p.hsb + ((gl ^ (jj.z & 7)) << 4);
+            const uint8_t* hp3 = hb + (size_t)jj.w * p.hsb + ((gl ^ (jj.w & 7)) << 4);
+            const uint4 u0 = *reinterpret_cast<const uint4*>(hp0), u1 = *reinterpret_cast<const uint4*>(hp1);
+            const uint4 u2 = *reinterpret_cast<const uint4*>(hp2), u3 = *reinterpret_cast<const uint4*>(hp3);
+            if (two) {
+              const uint4 v0 = *reinterpret_cast<const uint4*>(hp0 + 128), v1 = *reinterpret_cast<const uint4*>(hp1 + 128);
+              const uint4 v2 = *reinterpret_cast<const uint4*>(hp2 + 128), v3 = *reinterpret_cast<const uint4*>(hp3 + 128);
+              tc::hfma8(h1, v0, tc::as_half2(ww.x)); tc::hfma8(h1, v1, tc::as_half2(ww.y));
+              tc::hfma8(h1, v2, tc::as_half2(ww.z)); tc::hfma8(h1, v3, tc::as_half2(ww.w));
+            }
+            tc::hfma8(h0, u0, tc::as_half2(ww.x)); tc::hfma8(h0, u1, tc::as_half2(ww.y));
+            tc::hfma8(h0, u2, tc::as_half2(ww.z)); tc::hfma8(h0, u3, tc::as_half2(ww.w));
           }
           float a0[8], a1[8];
 #pragma unroll

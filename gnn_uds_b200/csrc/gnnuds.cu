@@ -84,7 +84,10 @@ struct gnnuds_handle {
 
   // graph
   int *d_rp = nullptr, *d_ci = nullptr, *d_erp = nullptr, *d_eci = nullptr;
-  int* d_bins[2] = {nullptr, nullptr};  // sp_conv gather schedule per stream side: bin_ptr[SP_BINS+1] | bin_rows[R]
+  int* d_bins[2] = {nullptr, nullptr};  // sp_conv gather schedule per stream side: bin_ptr[SP_BINS+1] | bin_rows[R] | row_len[R]
+  // CSR padded to 4 entries per block (zero-weight pads) for the 16-byte index / weight loads of sp_conv_kernel
+  int* d_prp[2] = {nullptr, nullptr}; int* d_pci[2] = {nullptr, nullptr}; float* d_pval[2] = {nullptr, nullptr};
+  int pnnz[2] = {0, 0};
   float *d_val = nullptr, *d_eval = nullptr;
   int nnz = 0, ennz = 0, n_adj = 0;
   int *d_edges = nullptr, *d_act_of_edge = nullptr, *d_act_out = nullptr, *d_act_in = nullptr;
@@ -931,7 +934,9 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   p.Mimg = h->d_ne_img[side][li]; p.m_bytes = h->ne_img_bytes[side];
   p.bias = W(h, w.t[gat ? 3 : 1]);
   p.a_self = gat ? W(h, w.t[1]) : nullptr; p.a_neigh = gat ? W(h, w.t[2]) : nullptr;
-  p.row_ptr = rp; p.col_idx = ci; p.val = val; p.nnz = nnz; p.bins = h->d_bins[side];
+  // the kernel walks the padded CSR (16-byte index / weight loads); `val` non-null only says "GCN"
+  p.row_ptr = h->d_prp[side]; p.col_idx = h->d_pci[side]; p.val = val ? h->d_pval[side] : nullptr; p.nnz = nnz = h->pnnz[side];
+  p.bins = h->d_bins[side];
   p.out = static_cast<bf16*>(out);
   auto al = [](uint32_t v, uint32_t a) { return (v + a - 1) / a * a; };
   p.off_w = 0;
@@ -947,7 +952,7 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   p.off_sc = al(p.off_nx + nx_bytes, 128);
   const uint32_t RP = 128u * p.MT;
   const uint32_t sc_bytes = (3u * E + 6u * RP + 2u * (uint32_t)nnz) * 4u + ((uint32_t)R + 1u + (uint32_t)nnz) * 4u +
-                            ((uint32_t)SP_BINS + 1u + (uint32_t)R) * 4u;
+                            ((uint32_t)SP_BINS + 1u + 2u * (uint32_t)R) * 4u + 64u;
   p.off_bar = al(p.off_sc + sc_bytes, 16);
   // operand views of M-tile mt read 128 rows from row mt*128 of every panel: keep those reads inside the allocation
   uint32_t reach = p.off_nx + (uint32_t)(F / 8 - 1) * p.pstrideA + RP * 16u;
@@ -1400,16 +1405,39 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
 // Gather schedule of sp_conv_kernel: the R output rows are packed into SP_BINS row lists of nearly equal
 // neighbour count (longest-processing-time first), one list per 8-lane group of the graph warps, so that
 // a sample's aggregation takes ~nnz/SP_BINS neighbour steps instead of (passes x max row degree).
-int upload_bins(gnnuds_handle* h, int side, const int* rp, int R) {
+int upload_bins(gnnuds_handle* h, int side, const int* rp, const int* ci, const float* val, int R) {
+  // padded CSR: every row starts on a multiple of 4 entries; pads repeat the row's first neighbour with weight 0
+  {
+    std::vector<int> prp(R + 1, 0), pci;
+    std::vector<float> pval;
+    for (int r = 0; r < R; ++r) {
+      const int len = rp[r + 1] - rp[r], plen = (len + 3) / 4 * 4;
+      for (int k = 0; k < plen; ++k) {
+        pci.push_back(k < len ? ci[rp[r] + k] : (len ? ci[rp[r]] : r));
+        pval.push_back(k < len && val ? val[rp[r] + k] : 0.f);
+      }
+      prp[r + 1] = (int)pci.size();
+    }
+    if (pci.empty()) { pci.assign(4, 0); pval.assign(4, 0.f); }
+    void* old[] = {h->d_prp[side], h->d_pci[side], h->d_pval[side]};
+    for (void* q : old) if (q) cudaFree(q);
+    h->d_prp[side] = h->d_pci[side] = nullptr; h->d_pval[side] = nullptr;
+    int rc;
+    if ((rc = upload(h, &h->d_prp[side], prp.data(), prp.size()))) return rc;
+    if ((rc = upload(h, &h->d_pci[side], pci.data(), pci.size()))) return rc;
+    if ((rc = upload(h, &h->d_pval[side], pval.data(), pval.size()))) return rc;
+    h->pnnz[side] = prp[R];
+  }
   std::vector<int> order(R), load(SP_BINS, 0), which(R);
   for (int i = 0; i < R; ++i) order[i] = i;
   std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return rp[a + 1] - rp[a] > rp[b + 1] - rp[b]; });
   for (int r : order) {
     int best = 0;
     for (int b = 1; b < SP_BINS; ++b) if (load[b] < load[best]) best = b;
-    which[r] = best; load[best] += rp[r + 1] - rp[r] + 1;     // +1: per-row epilogue (bias, act, store)
+    which[r] = best; load[best] += (rp[r + 1] - rp[r] + 3) / 4 * 4 + 2;     // blocks of 4 neighbours + per-row epilogue
   }
-  std::vector<int> bins(SP_BINS + 1 + R, 0);
+  std::vector<int> bins(SP_BINS + 1 + 2 * R, 0);
+  for (int r = 0; r < R; ++r) bins[SP_BINS + 1 + R + r] = rp[r + 1] - rp[r];
   for (int r = 0; r < R; ++r) ++bins[which[r] + 1];
   for (int b = 0; b < SP_BINS; ++b) bins[b + 1] += bins[b];
   std::vector<int> fill(bins.begin(), bins.begin() + SP_BINS);
@@ -1425,7 +1453,7 @@ int gnnuds_destroy(gnnuds_handle* h) {
   void* ptrs[] = {h->d_blob, h->d_rp, h->d_ci, h->d_erp, h->d_eci, h->d_val, h->d_eval, h->d_edges, h->d_act_of_edge,
                   h->d_act_out, h->d_act_in, h->d_inc_ptr, h->d_inc_edge, h->d_inc_sign, h->d_hmin, h->d_hmax,
                   h->d_outfall, h->d_ehmax, h->d_nx, h->d_nb, h->d_ny, h->d_ne, h->d_ws, h->ro_x, h->ro_ex, h->ro_b, h->ro_a, h->d_wimg,
-                  h->d_bins[0], h->d_bins[1], h->d_pump, h->d_offset, h->d_pump_in, h->d_pump_out, h->d_area, h->d_edge_from, h->d_ps};
+                  h->d_bins[0], h->d_bins[1], h->d_prp[0], h->d_prp[1], h->d_pci[0], h->d_pci[1], h->d_pval[0], h->d_pval[1], h->d_pump, h->d_offset, h->d_pump_in, h->d_pump_out, h->d_area, h->d_edge_from, h->d_ps};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_ne_img[s]) if (p) cudaFree(p);
@@ -1459,7 +1487,7 @@ int gnnuds_set_graph(gnnuds_handle* h, const gnnuds_graph* g) {
   if ((rc = upload(h, &h->d_ci, g->col_idx, (size_t)g->nnz))) return rc;
   if (g->val) { if ((rc = upload(h, &h->d_val, g->val, (size_t)g->nnz))) return rc; }
   h->nnz = g->nnz; h->n_adj = g->n;
-  if (!c.graph_base && (rc = upload_bins(h, 0, g->row_ptr, g->n))) return rc;
+  if (!c.graph_base && (rc = upload_bins(h, 0, g->row_ptr, g->col_idx, g->val, g->n))) return rc;
   if (!c.graph_base) {
     for (int i = 0; i < g->e_nnz; ++i) if (g->e_col_idx[i] < 0 || g->e_col_idx[i] >= g->m) return fail(h, GNNUDS_E_INVALID, "e_col_idx out of range");
     if (g->e_row_ptr[0] != 0 || g->e_row_ptr[g->m] != g->e_nnz) return fail(h, GNNUDS_E_INVALID, "e_row_ptr inconsistent with e_nnz");
@@ -1467,7 +1495,7 @@ int gnnuds_set_graph(gnnuds_handle* h, const gnnuds_graph* g) {
     if ((rc = upload(h, &h->d_eci, g->e_col_idx, (size_t)g->e_nnz))) return rc;
     if (g->e_val) { if ((rc = upload(h, &h->d_eval, g->e_val, (size_t)g->e_nnz))) return rc; }
     h->ennz = g->e_nnz;
-    if ((rc = upload_bins(h, 1, g->e_row_ptr, g->m))) return rc;
+    if ((rc = upload_bins(h, 1, g->e_row_ptr, g->e_col_idx, g->e_val, g->m))) return rc;
   }
   const int N = c.n_node, M = c.n_edge;
   h->h_edges.assign(g->edges, g->edges + 2 * (size_t)M);
