@@ -343,8 +343,12 @@ int launch_embed(gnnuds_handle* h, const float* in, const float* nrm, int cn, in
   p.rows = Bc * T * Nn; p.T = T; p.Nn = Nn; p.K = K; p.Eo = Eo; p.act = act; p.mode = mode;
   if (p.rows == 0) return 0;
   if (std::is_same<ST, bf16>::value && mode == 0 && K <= 8 && (Eo == 128 || Eo == 64) && p.rows < (1ll << 31)) {
-    if (Eo == 128) embed_bf16_kernel<16><<<grid_for(h, p.rows, 16, 8), 256, 0, h->stream>>>(p);
-    else embed_bf16_kernel<8><<<grid_for(h, p.rows, 32, 8), 256, 0, h->stream>>>(p);
+    const int g16 = grid_for(h, p.rows, 16, 8), g8 = grid_for(h, p.rows, 32, 8);
+#define GU_EMBED(KT) do { if (Eo == 128) embed_bf16_kernel<16, KT><<<g16, 256, 0, h->stream>>>(p); \
+                          else embed_bf16_kernel<8, KT><<<g8, 256, 0, h->stream>>>(p); } while (0)
+    switch (K) { case 1: GU_EMBED(1); break; case 2: GU_EMBED(2); break; case 4: GU_EMBED(4); break; case 5: GU_EMBED(5); break;
+                 default: GU_EMBED(0); }
+#undef GU_EMBED
     ++h->launches;
     CU(cudaGetLastError());
     return 0;

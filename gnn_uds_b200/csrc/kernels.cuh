@@ -187,9 +187,10 @@ __global__ void __launch_bounds__(256) embed_kernel(EmbedP p) {
 // two independent global loads in flight per thread.
 struct EmbedRow { unsigned r, n, bt, t; };
 
-template <int LPR>
+template <int LPR, int KT>                          // KT: compile-time channel count (full unrolling), 0 = runtime p.K
 __global__ void __launch_bounds__(256) embed_bf16_kernel(EmbedP p) {
   constexpr int RPB = 256 / LPR;                   // rows per CTA pass
+  constexpr int Eo = LPR * 8;
   __shared__ __align__(16) float Ws[8 * LPR * 8];
   __shared__ __align__(16) float bs[LPR * 8];
   for (int i = threadIdx.x; i < p.K * p.Eo; i += 256) Ws[i] = p.W[i];
@@ -208,7 +209,7 @@ __global__ void __launch_bounds__(256) embed_bf16_kernel(EmbedP p) {
     if (q.t >= Tn) q.t -= Tn;
   };
   const unsigned n_iter = (rows + step - 1) / step;   // uniform trip count: shuffles stay convergent
-  const int K = p.K;
+  const int K = KT ? KT : p.K;
   const float* wcol = Ws + c8 * 8;
   for (unsigned it = 0; it < n_iter; it += 2) {
     EmbedRow q[2];
@@ -229,9 +230,11 @@ __global__ void __launch_bounds__(256) embed_bf16_kernel(EmbedP p) {
       float s[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) s[j] = 0.f;
-      for (int c = 0; c < K; ++c) {                  // warp-uniform trip count
+#pragma unroll
+      for (int c = 0; c < (KT ? KT : 8); ++c) {      // warp-uniform trip count
+        if (!KT && c >= K) break;
         const float xc = __shfl_sync(0xffffffffu, mine[u], c, LPR);
-        const float4 w0 = *reinterpret_cast<const float4*>(wcol + c * p.Eo), w1 = *reinterpret_cast<const float4*>(wcol + c * p.Eo + 4);
+        const float4 w0 = *reinterpret_cast<const float4*>(wcol + c * Eo), w1 = *reinterpret_cast<const float4*>(wcol + c * Eo + 4);
         s[0] = fmaf(xc, w0.x, s[0]); s[1] = fmaf(xc, w0.y, s[1]); s[2] = fmaf(xc, w0.z, s[2]); s[3] = fmaf(xc, w0.w, s[3]);
         s[4] = fmaf(xc, w1.x, s[4]); s[5] = fmaf(xc, w1.y, s[5]); s[6] = fmaf(xc, w1.z, s[6]); s[7] = fmaf(xc, w1.w, s[7]);
       }
@@ -239,7 +242,7 @@ __global__ void __launch_bounds__(256) embed_bf16_kernel(EmbedP p) {
       s[0] += b0.x; s[1] += b0.y; s[2] += b0.z; s[3] += b0.w; s[4] += b1.x; s[5] += b1.y; s[6] += b1.z; s[7] += b1.w;
       if (q[u].r < rows) {
         if (p.res && q[u].t == Tn - 1) {
-          float* rp = p.res + ((size_t)(q[u].bt / Tn) * Nn + q[u].n) * p.Eo + c8 * 8;
+          float* rp = p.res + ((size_t)(q[u].bt / Tn) * Nn + q[u].n) * Eo + c8 * 8;
           *reinterpret_cast<float4*>(rp) = make_float4(s[0], s[1], s[2], s[3]);
           *reinterpret_cast<float4*>(rp + 4) = make_float4(s[4], s[5], s[6], s[7]);
         }
@@ -250,7 +253,7 @@ __global__ void __launch_bounds__(256) embed_bf16_kernel(EmbedP p) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) s[j] = apply_act(s[j], p.act);
         }
-        *reinterpret_cast<uint4*>(static_cast<bf16*>(p.out) + (size_t)q[u].r * p.Eo + c8 * 8) =
+        *reinterpret_cast<uint4*>(static_cast<bf16*>(p.out) + (size_t)q[u].r * Eo + c8 * 8) =
             make_uint4(pack2_bf16(s[0], s[1]), pack2_bf16(s[2], s[3]), pack2_bf16(s[4], s[5]), pack2_bf16(s[6], s[7]));
       }
     }
