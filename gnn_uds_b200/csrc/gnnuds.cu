@@ -9,6 +9,7 @@
 #include "tc_selftest.cuh"
 #include "fused_sp.cuh"
 #include "fused_conv.cuh"
+#include "gru_tc.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -16,6 +17,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <set>
 #include <string>
 #include <type_traits>
 #include <vector>
@@ -77,6 +79,7 @@ struct gnnuds_handle {
   std::vector<uint8_t*> d_ne_img[2];
   uint32_t ne_img_bytes[2] = {0, 0}, ne_pstride[2] = {0, 0};
   int ne_kp[2] = {0, 0};
+  int gru_tc = 1;                       // GNNUDS_GRU_TC: 0 = fp32 SIMT recurrence (gru_kernel) on the tensor-core path
   int sw128 = 1;                        // GNNUDS_SW128: 0 = 16-byte panel boxes for every TMA-fed operand tile
   int conv1d_tma = 1;                   // GNNUDS_CONV1D_TMA: 0 = cp.async gathers for time-shifted segments
   int fuse_heads = 1;                   // GNNUDS_FUSE_HEADS: 0 = separate cumsum / head kernels (debugging)
@@ -860,7 +863,18 @@ int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& 
                                Nn, 0))) return rc;
       const long long nseq = Bc * Nn;
       const int g = (int)((nseq + 31) / 32);
-      if (gru) {
+      if (gru && h->gru_tc && H == 64 && h->img_off[L[i].t[1]] >= 0 && nseq < (1ll << 31) * 64) {
+        // recurrence on tensor cores (csrc/gru_tc.cuh): 128 sequences per CTA tile, state in registers
+        GruTcP p{reinterpret_cast<const bf16*>(h->HB), h->d_wimg + h->img_off[L[i].t[1]], W(h, L[i].t[2]) + G,
+                 reinterpret_cast<bf16*>(o), nseq, Nn, Ts, Tdst, H, (unsigned)((nseq + 127) / 128)};
+        const size_t smem = 2 * (size_t)H * G * 2 + 2 * 128 * H * 2 + G * 4 + 64;
+        static bool attr_set = false;
+        if (!attr_set) { CU(cudaFuncSetAttribute(gru_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
+        cudaEvent_t e1 = nullptr;
+        { int prc = prof_begin(h, GNNUDS_FAM_RECURRENT, &e1); if (prc) return prc; }
+        gru_tc_kernel<64><<<std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count), GRU_THREADS, smem, h->stream>>>(p);
+        { int prc = prof_end(h, e1); if (prc) return prc; }
+      } else if (gru) {
         GruP p{h->HB, W(h, L[i].t[1]), W(h, L[i].t[2]) + G, o, nseq, Nn, Ts, Tdst, H};
         const size_t smem = ((size_t)H * G + 32 * H + 32 * G) * sizeof(float);
         CU(cudaFuncSetAttribute(gru_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -1397,6 +1411,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   }
   h->tma_on = !(getenv("GNNUDS_NO_TMA") && getenv("GNNUDS_NO_TMA")[0] == '1');
   if (getenv("GNNUDS_FUSED")) h->fused_mode = atoi(getenv("GNNUDS_FUSED"));
+  if (getenv("GNNUDS_GRU_TC")) h->gru_tc = atoi(getenv("GNNUDS_GRU_TC"));
   if (getenv("GNNUDS_SW128")) h->sw128 = atoi(getenv("GNNUDS_SW128"));
   if (getenv("GNNUDS_CONV1D_TMA")) h->conv1d_tma = atoi(getenv("GNNUDS_CONV1D_TMA"));
   if (getenv("GNNUDS_FUSE_HEADS")) h->fuse_heads = atoi(getenv("GNNUDS_FUSE_HEADS"));
@@ -1597,13 +1612,14 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
   if (h->tc()) {
     // bf16 K-major images (B operand = W^T) of every GEMM layer, one blob
     std::vector<int> ids;
+    std::set<int> rec_ids;
     auto add = [&](const LayerW& l) { ids.push_back(l.t[0]); };
     for (int blk = 0; blk < 2; ++blk) {
       for (const SpatialW& w : h->sp[blk]) {
         if (c.graph_base) add(w.joint); else { add(w.xe); add(w.ex); add(w.conv_x); add(w.conv_e); }
       }
-      for (const LayerW& l : h->tpx[blk]) add(l);
-      for (const LayerW& l : h->tpe[blk]) add(l);
+      for (const LayerW& l : h->tpx[blk]) { add(l); if (c.recurrent == GNNUDS_REC_GRU) { ids.push_back(l.t[1]); rec_ids.insert(l.t[1]); } }   // + recurrent kernel R
+      for (const LayerW& l : h->tpe[blk]) { add(l); if (c.recurrent == GNNUDS_REC_GRU) { ids.push_back(l.t[1]); rec_ids.insert(l.t[1]); } }
     }
     add(h->resx); add(h->rese);
     for (const LayerW& l : h->flood_chain) add(l);
@@ -1617,6 +1633,18 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
       while (all.size() % 64) all.push_back(0);
       h->img_off[t] = (long long)all.size() * 2;
       all.insert(all.end(), img.begin(), img.end());
+      if (c.recurrent == GNNUDS_REC_GRU && rec_ids.count(t)) {
+        // recurrent kernel R: a second image of the bf16 residual R - bf16(R) right behind the first (csrc/gru_tc.cuh)
+        std::vector<float> lo((size_t)Nout * Ktot);
+        for (size_t i = 0; i < lo.size(); ++i) {
+          const float v = blob[offsets[t] + i];
+          const uint32_t hb = (uint32_t)f2bf(v) << 16;
+          float hv; std::memcpy(&hv, &hb, 4);
+          lo[i] = v - hv;
+        }
+        std::vector<uint16_t> img2 = pack_kmajor(lo.data(), Nout, Ktot, 1, Nout, Nout, Ktot, Nout * 16);
+        all.insert(all.end(), img2.begin(), img2.end());
+      }
     }
     if (h->d_wimg) { cudaFree(h->d_wimg); h->d_wimg = nullptr; }
     uint16_t* d = nullptr;
