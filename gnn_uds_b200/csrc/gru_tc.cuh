@@ -145,11 +145,11 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) gru_tc_kernel(const __grid_con
 #pragma unroll
           for (int k = 0; k < 16; ++k) {
             const int u = u0 + c0 + k;
-            const float z = 1.f / (1.f + __expf(-(xz[k] + az[k] + b1s[u])));
-            const float r = 1.f / (1.f + __expf(-(xr[k] + ar[k] + b1s[H + u])));
+            const float z = __fdividef(1.f, 1.f + __expf(-(xz[k] + az[k] + b1s[u])));
+            const float r = __fdividef(1.f, 1.f + __expf(-(xr[k] + ar[k] + b1s[H + u])));
             const float pre = xc[k] + r * (ac[k] + b1s[2 * H + u]);
             const float e2 = __expf(-2.f * fabsf(pre));          // tanh(pre) = sign(pre) * (1 - e2) / (1 + e2)
-            const float hh = copysignf((1.f - e2) / (1.f + e2), pre);
+            const float hh = copysignf(__fdividef(1.f - e2, 1.f + e2), pre);
             hn[k] = z * h[c0 + k] + (1.f - z) * hh;
             h[c0 + k] = hn[k];
           }
