@@ -43,7 +43,8 @@ struct SpConvP {
   const float* bias; const float* a_self; const float* a_neigh;
   const int* row_ptr; const int* col_idx; const float* val; int nnz;
   const int* bins;            // gather schedule: bin_ptr[SP_BINS+1] | bin_rows[R]  (gnnuds.cu::upload_bins)
-  bf16* out;                  // (S*R, Nout)
+  bf16* out;                  // (rows_total, Nout)
+  long long rows_total;       // true row count of `out` (a partial last sample group stores fewer than R rows)
   int S, R, Ro, Rbox, Kp, MT, Kself, F, Nout, act, gat;
   uint32_t pstrideA, pstrideM, pstrideX;      // bytes: self/NE panels (Rbox*16), Mat panels, other_dense panels (Kp*16)
   uint32_t off_w, off_m, off_in, in_stride, xe_off, off_nx, off_sc, off_bar, hsb;
@@ -362,6 +363,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         const int r = bin_s[SP_BINS + 1 + bi];
         const int beg = rp_s[r], end = rp_s[r + 1];
         const float scale = p.gat ? inv[r] : 1.f;
+        const bool store = (long long)smp * R + r < p.rows_total;
         bf16* orow = p.out + ((size_t)smp * R + r) * p.Nout + gl * 8;
         for (int e0 = 0; e0 < p.Nout; e0 += 128) {
           // fp16 h tile, fp16 weights, HFMA2 accumulation (two features per instruction, no unpacking); the few
@@ -400,12 +402,12 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
 #pragma unroll
           for (int k = 0; k < 8; ++k) a0[k] = fmaf(a0[k], scale, bp[k]);
           act_tile<8>(a0, p.act);
-          *reinterpret_cast<uint4*>(orow + e0) = tc::pack8_bf16(a0);
+          if (store) *reinterpret_cast<uint4*>(orow + e0) = tc::pack8_bf16(a0);
           if (two) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) a1[k] = fmaf(a1[k], scale, bp[64 + k]);
             act_tile<8>(a1, p.act);
-            *reinterpret_cast<uint4*>(orow + e0 + 64) = tc::pack8_bf16(a1);
+            if (store) *reinterpret_cast<uint4*>(orow + e0 + 64) = tc::pack8_bf16(a1);
           }
         }
       }

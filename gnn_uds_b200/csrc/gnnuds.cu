@@ -79,6 +79,9 @@ struct gnnuds_handle {
   std::vector<uint8_t*> d_ne_img[2];
   uint32_t ne_img_bytes[2] = {0, 0}, ne_pstride[2] = {0, 0};
   int ne_kp[2] = {0, 0};
+  // small graphs: sp_conv_kernel processes sp_g consecutive (b,t) samples as ONE block-diagonal super-sample
+  // (sp_g*R rows fill the 128-row MMA tile: NodeEdge matrix and CSR are replicated on the diagonal)
+  int sp_g = 1;
   int gru_tc = 1;                       // GNNUDS_GRU_TC: 0 = fp32 SIMT recurrence (gru_kernel) on the tensor-core path
   int sw128 = 1;                        // GNNUDS_SW128: 0 = 16-byte panel boxes for every TMA-fed operand tile
   int conv1d_tma = 1;                   // GNNUDS_CONV1D_TMA: 0 = cp.async gathers for time-shifted segments
@@ -932,6 +935,10 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   const auto& c = h->c;
   const int E = c.embed, F = E / 2;
   const bool gat = c.conv == GNNUDS_CONV_GAT;
+  // sample groups: sp_g consecutive samples form one block-diagonal super-sample; the tensor maps keep the true row
+  // counts, so the rows of a partial last group read as zeros and are not stored (rows_total)
+  const long long rows_total = S * R, rows_other = S * Ro;
+  { const int g = h->sp_g; S = (S + g - 1) / g; R *= g; Ro *= g; }
   if (h->fused_mode != 1 || segs.empty() || segs.size() > 2 || R > 256 || Ro > 256 || R < 1 || F % 32 || E % 64 || E > 128) return -1;
   if (S <= 0 || S * (long long)std::max(R, Ro) >= (1ll << 31)) return -1;
   SpConvP p{};
@@ -939,7 +946,7 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   p.Kself = 0;
   for (int i = 0; i < p.nseg; ++i) {
     const SegH& sg = segs[i];
-    if (sg.shift || sg.pitch != R || sg.off || sg.width % 16 || sg.ld % 8 || (reinterpret_cast<uintptr_t>(sg.p) & 15)) return -1;
+    if (sg.shift || sg.pitch * h->sp_g != R || sg.off || sg.width % 16 || sg.ld % 8 || (reinterpret_cast<uintptr_t>(sg.p) & 15)) return -1;
     p.segw[i] = sg.width; p.Kself += sg.width;
   }
   const int Ktot = p.Kself + F;
@@ -982,11 +989,12 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   const size_t smem = std::max<size_t>(p.off_bar + 15 * 8 + 16, reach);
   if (smem > 227 * 1024) return -1;
   for (int i = 0; i < p.nseg; ++i) {
-    if (p.sw128 ? !make_rows_tmap_sw(&p.tm_self[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox)
-                : !make_rows_tmap(&p.tm_self[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox, segs[i].width)) return -1;
+    if (p.sw128 ? !make_rows_tmap_sw(&p.tm_self[i], segs[i].p, rows_total, segs[i].ld, segs[i].width, p.Rbox)
+                : !make_rows_tmap(&p.tm_self[i], segs[i].p, rows_total, segs[i].ld, segs[i].width, p.Rbox, segs[i].width)) return -1;
   }
-  if (p.sw_x ? !make_rows_tmap_sw(&p.tm_other, other_dense, S * Ro, F, F, p.Kp)
-             : !make_rows_tmap(&p.tm_other, other_dense, S * Ro, F, F, p.Kp, F)) return -1;
+  if (p.sw_x ? !make_rows_tmap_sw(&p.tm_other, other_dense, rows_other, F, F, p.Kp)
+             : !make_rows_tmap(&p.tm_other, other_dense, rows_other, F, F, p.Kp, F)) return -1;
+  p.rows_total = rows_total;
   static bool attr_set = false;
   if (!attr_set) {
     CU(cudaFuncSetAttribute(sp_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -1412,6 +1420,8 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   h->tma_on = !(getenv("GNNUDS_NO_TMA") && getenv("GNNUDS_NO_TMA")[0] == '1');
   if (getenv("GNNUDS_FUSED")) h->fused_mode = atoi(getenv("GNNUDS_FUSED"));
   if (getenv("GNNUDS_GRU_TC")) h->gru_tc = atoi(getenv("GNNUDS_GRU_TC"));
+  h->sp_g = std::max(1, std::min(8, 128 / std::max(1, std::max(c.n_node, c.n_edge))));
+  if (getenv("GNNUDS_SP_GROUP")) h->sp_g = std::max(1, std::min(h->sp_g, atoi(getenv("GNNUDS_SP_GROUP"))));
   if (getenv("GNNUDS_SW128")) h->sw128 = atoi(getenv("GNNUDS_SW128"));
   if (getenv("GNNUDS_CONV1D_TMA")) h->conv1d_tma = atoi(getenv("GNNUDS_CONV1D_TMA"));
   if (getenv("GNNUDS_FUSE_HEADS")) h->fuse_heads = atoi(getenv("GNNUDS_FUSE_HEADS"));
@@ -1424,7 +1434,17 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
 // Gather schedule of sp_conv_kernel: the R output rows are packed into SP_BINS row lists of nearly equal
 // neighbour count (longest-processing-time first), one list per 8-lane group of the graph warps, so that
 // a sample's aggregation takes ~nnz/SP_BINS neighbour steps instead of (passes x max row degree).
-int upload_bins(gnnuds_handle* h, int side, const int* rp, const int* ci, const float* val, int R) {
+int upload_bins(gnnuds_handle* h, int side, const int* rp0, const int* ci0, const float* val0, int R0) {
+  // block-diagonal replication for the sample groups of small graphs (h->sp_g)
+  const int g = h->sp_g, R = g * R0;
+  std::vector<int> rpv(R + 1, 0), civ;
+  std::vector<float> valv;
+  for (int q = 0; q < g; ++q)
+    for (int r = 0; r < R0; ++r) {
+      for (int k = rp0[r]; k < rp0[r + 1]; ++k) { civ.push_back(ci0[k] + q * R0); if (val0) valv.push_back(val0[k]); }
+      rpv[q * R0 + r + 1] = (int)civ.size();
+    }
+  const int* rp = rpv.data(); const int* ci = civ.data(); const float* val = val0 ? valv.data() : nullptr;
   // padded CSR: every row starts on a multiple of 4 entries; pads repeat the row's first neighbour with weight 0
   {
     std::vector<int> prp(R + 1, 0), pci;
@@ -1691,9 +1711,10 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
       // the same folded matrices as bf16 K-major images (A operand of the NodeEdge MMA in sp_conv_kernel)
       for (int s = 0; s < 2; ++s) { for (uint8_t* p : h->d_ne_img[s]) if (p) cudaFree(p); h->d_ne_img[s].clear(); }
       const int Rs[2] = {N, M}, Ks[2] = {M, N};
+      const int g = h->sp_g;
       for (int s = 0; s < 2; ++s) {
-        h->ne_kp[s] = (Ks[s] + 15) / 16 * 16;
-        h->ne_pstride[s] = (uint32_t)((Rs[s] + 7) / 8 * 8) * 16u;
+        h->ne_kp[s] = (g * Ks[s] + 15) / 16 * 16;
+        h->ne_pstride[s] = (uint32_t)((g * Rs[s] + 7) / 8 * 8) * 16u;
         h->ne_img_bytes[s] = (uint32_t)(h->ne_kp[s] / 8) * h->ne_pstride[s];
       }
       for (int blk = 0; blk < 2; ++blk)
@@ -1702,13 +1723,15 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
           for (int s = 0; s < 2; ++s) {
             const LayerW& lw = s == 0 ? w.ne_n : w.ne_m;
             const float* wt = blob + offsets[lw.t[0]]; const float* bs = blob + offsets[lw.t[1]];
-            std::vector<float> md((size_t)Rs[s] * Ks[s]);
-            for (int r = 0; r < Rs[s]; ++r)
-              for (int k = 0; k < Ks[s]; ++k) {
-                const float inc = s == 0 ? inci[(size_t)r * M + k] : inci[(size_t)k * M + r];
-                md[(size_t)r * Ks[s] + k] = wt[(size_t)r * Ks[s] + k] * inc + bs[(size_t)r * Ks[s] + k];
-              }
-            std::vector<uint16_t> img = pack_kmajor(md.data(), Rs[s], Ks[s], Ks[s], 1, 0, h->ne_kp[s], (int)h->ne_pstride[s]);
+            const int Rg = g * Rs[s], Kg = g * Ks[s];
+            std::vector<float> md((size_t)Rg * Kg, 0.f);       // block diagonal: one copy per sample of the group
+            for (int q = 0; q < g; ++q)
+              for (int r = 0; r < Rs[s]; ++r)
+                for (int k = 0; k < Ks[s]; ++k) {
+                  const float inc = s == 0 ? inci[(size_t)r * M + k] : inci[(size_t)k * M + r];
+                  md[(size_t)(q * Rs[s] + r) * Kg + q * Ks[s] + k] = wt[(size_t)r * Ks[s] + k] * inc + bs[(size_t)r * Ks[s] + k];
+                }
+            std::vector<uint16_t> img = pack_kmajor(md.data(), Rg, Kg, Kg, 1, 0, h->ne_kp[s], (int)h->ne_pstride[s]);
             uint16_t* d = nullptr;
             if ((rc = upload(h, &d, img.data(), img.size()))) return rc;
             h->d_ne_img[s].push_back(reinterpret_cast<uint8_t*>(d));
