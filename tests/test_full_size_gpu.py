@@ -1,0 +1,99 @@
+"""Full-size checks at BASELINE.json's headline configuration (C2: shunqing GAT+Conv1D edge_fusion/resnet/flood,
+60 -> 60, B = 4096, tensor-core path), where the NumPy oracle would need hours: size-independent properties of the
+path instead of element-wise comparison, plus an oracle comparison of a handful of scenarios picked out of the batch.
+
+  * replication: the batch is 64 distinct scenarios tiled 64 times; scenarios are independent, so every replica must
+    be BITWISE equal to the first copy, whatever internal chunk / CTA / sample slot it landed in;
+  * constrain (emulator.py:727-748): h in [hmin, hmax], h == hmax where the flood probability > 0.5, q_w >= 0 and
+    q_w == 0 at outfalls, edge depth in [0, ehmax] (emulator.py:588);
+  * edge-fusion mass balance (emulator.py:671-677): summed over the nodes, inflow and outflow derived from the edge
+    flows are the same edge flows seen from the two ends, so sum_n q_in*norm == sum_n q_out*norm per (b,t).
+"""
+import numpy as np
+import pytest
+
+from gnn_uds_b200 import configs, synthetic
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def c2_full():
+    em, args, rng = configs.make_emulator("C2", precision="bf16")
+    base = synthetic.make_inputs(em, 64, rng)
+    B = 4096
+    inp = [None if t is None else np.ascontiguousarray(np.concatenate([t] * (B // 64), 0)) for t in base]
+    y, ey = em.predict(*inp)
+    return em, args, base, inp, y, ey
+
+
+def test_replicas_are_bitwise_equal(c2_full):
+    em, args, base, inp, y, ey = c2_full
+    assert y.shape == (4096, 60, 113, 5) and ey.shape == (4096, 60, 131, 3)
+    assert np.isfinite(y).all() and np.isfinite(ey).all()
+    y0, ey0 = y[:64], ey[:64]
+    for k in range(1, 64):
+        assert np.array_equal(y[64 * k:64 * (k + 1)], y0), "replica %d differs" % k
+        assert np.array_equal(ey[64 * k:64 * (k + 1)], ey0), "replica %d differs (edges)" % k
+
+
+def test_constrain_and_clip_invariants(c2_full):
+    em, args, base, inp, y, ey = c2_full
+    y, ey = y[:64], ey[:64]
+    hmax, hmin = em.hmax.astype(np.float32), em.hmin.astype(np.float32)
+    h, prob, qw = y[..., 0], y[..., 3], y[..., 4]
+    assert (h >= hmin - 1e-6).all() and (h <= hmax + 1e-6).all()
+    flooded = prob > 0.5
+    assert np.array_equal(h[flooded], np.broadcast_to(hmax, h.shape)[flooded])
+    assert (qw >= 0).all()
+    assert (qw[..., np.asarray(em.is_outfall) > 0] == 0).all()
+    assert (qw[~flooded] == 0).all()                         # epsilon < 0 and if_flood: q_w gated by the flag
+    assert (ey[..., 0] >= 0).all() and (ey[..., 0] <= em.ehmax.astype(np.float32) + 1e-6).all()
+
+
+def test_edge_fusion_mass_balance(c2_full):
+    em, args, base, inp, y, ey = c2_full
+    y, ey = y[:64].astype(np.float64), ey[:64].astype(np.float64)
+    # q_us / q_ds (physical) are the scaled sums of the physical edge flows at the nodes' ends; undo the
+    # (norm > 1e-3)/norm * (max-min)+min scaling only where it is the identity (min = 0, max > 1e-3)
+    ymax, ymin = em.norm_y[0], em.norm_y[1]
+    ok = (ymax[:, 1] > 1e-3) & (ymax[:, 2] > 1e-3) & (ymin[:, 1] == 0) & (ymin[:, 2] == 0)
+    assert ok.all()
+    flow = np.abs(ey[..., 2])                                # every edge contributes |flow| once as inflow, once as outflow
+    edges = np.asarray(em.edges)
+    loops = edges[:, 0] == edges[:, 1]
+    total = flow[..., ~loops].sum(-1)
+    q_in, q_out = y[..., 1].sum(-1), y[..., 2].sum(-1)
+    scale = np.maximum(total, 1.0)
+    assert (np.abs(q_in - total) / scale).max() < 1e-4
+    assert (np.abs(q_out - total) / scale).max() < 1e-4
+
+
+def test_picked_scenarios_match_oracle(c2_full):
+    """Two scenarios out of the 4096 against the float64 oracle (60 -> 60 takes the oracle ~10 s each)."""
+    import cases
+    from oracle.emulator_oracle import OracleEmulator
+    em, args, base, inp, y, ey = c2_full
+    o = OracleEmulator(args.conv, args.resnet, args.recurrent, args, dtype=np.float64)
+    o.set_weights(em.weights)
+    o.set_norm(em.norm_x, em.norm_b, em.norm_y, em.norm_r, em.norm_e)
+    pick = [3, 41]
+    sub = [None if t is None else t[pick] for t in base]
+    y64, ey64 = o.predict(*sub)
+    sc = lambda t: np.maximum(np.abs(t).reshape(-1, t.shape[-1]).max(0), 1.0)
+    for k, i in enumerate(pick):
+        for rep in (0, 37):                                   # the same scenario in two different replicas
+            d = np.abs(y[64 * rep + i][..., :3] - y64[k][..., :3]) / sc(y64[..., :3])
+            de = np.abs(ey[64 * rep + i] - ey64[k]) / sc(ey64)
+            # bf16 operands / fp32 accumulation: same bounds as tests/test_tc_parity_gpu.py; elements of nodes whose
+            # flood flag differs are excluded (threshold flips)
+            same = (y[64 * rep + i][..., 3] > 0.5) == (y64[k][..., 3] > 0.5)
+            decided = np.abs(y64[k][..., 3] - 0.5) > 5e-3     # a probability inside the tolerance band may land either side
+            assert (~same & decided).mean() <= 1e-3 and (~same).mean() <= 1e-2
+            # Node outputs: the bounds of tests/test_tc_parity_gpu.py.  Edge outputs at the full 60-step horizon: the
+            # resnet cumsum (emulator.py:318-320) adds the bf16 noise of the 60 increments coherently, and on these
+            # random-init scenarios the increments partly cancel, so late-horizon edge volumes deviate by up to ~4 % of
+            # the channel scale (RMSE 3e-3 over all channels, 5e-3 on the volume channel; the fp32 path is at 5e-6 on
+            # the same scenarios, tools/diag_full.py).  The bound below is what the bf16 path delivers, not a target.
+            assert d[same].max() < 1e-2 and np.sqrt((d[same] ** 2).mean()) < 3e-3
+            assert de.max() < 6e-2 and np.sqrt((de ** 2).mean()) < 5e-3
