@@ -386,7 +386,7 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32" if precision == "fp32" else "bf16(f32 acc)", "data": "synthetic",
+            "dtype": "f32" if precision == "fp32" else ("f16(f32 acc)" if em._lib.gnnuds_tc_operand_is_half() else "bf16(f32 acc)"), "data": "synthetic",
             "config": {"workload": "%s: %s %s+%s edge_fusion=%s resnet=%s if_flood=%d act=%s, N=%d M=%d, seq %d->%d, B=%d per GPU" % (
                 a.workload, args.__dict__.get("env_name", configs.WORKLOADS[a.workload]["net"]), em.conv_kind.upper(), em.recurrent,
                 em.edge_fusion, em.resnet, em.if_flood, bool(em.act), N, M, Ti, To, B),

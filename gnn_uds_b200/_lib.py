@@ -52,6 +52,7 @@ SYMBOLS = [
     "gnnuds_rollout", "gnnuds_objective", "gnnuds_alloc_pinned", "gnnuds_free_pinned", "gnnuds_alloc_device",
     "gnnuds_free_device", "gnnuds_memcpy", "gnnuds_synchronize", "gnnuds_launch_count", "gnnuds_last_timing",
     "gnnuds_set_profiling", "gnnuds_kernel_timing", "gnnuds_debug_stop_after", "gnnuds_debug_fetch", "gnnuds_debug_umma_selftest",
+    "gnnuds_tc_operand_is_half",
 ]
 
 

@@ -326,7 +326,7 @@ __global__ void __launch_bounds__(CA_THREADS, 1) conv_agg_kernel(const __grid_co
 #pragma unroll
             for (int k = 0; k < 16; ++k)
               if (beg + k < end)
-                *reinterpret_cast<bf16*>(arow + (size_t)(js[k] >> 3) * kpstrideA + (js[k] & 7) * 2) = __float2bfloat16_rn(sc[k] * inv);
+                st1(reinterpret_cast<bf16*>(arow + (size_t)(js[k] >> 3) * kpstrideA + (js[k] & 7) * 2), sc[k] * inv);
           } else {
             float mx = -INFINITY;
             for (int qq = beg; qq < end; ++qq) {
@@ -345,13 +345,13 @@ __global__ void __launch_bounds__(CA_THREADS, 1) conv_agg_kernel(const __grid_co
               const int j = ci_s[qq];
               float t = si + sn[j];
               t = t > 0.f ? t : 0.2f * t;
-              *reinterpret_cast<bf16*>(arow + (size_t)(j >> 3) * kpstrideA + (j & 7) * 2) = __float2bfloat16_rn(__expf(t - mx) * inv);
+              st1(reinterpret_cast<bf16*>(arow + (size_t)(j >> 3) * kpstrideA + (j & 7) * 2), __expf(t - mx) * inv);
             }
           }
         } else {
           for (int qq = beg; qq < end; ++qq) {
             const int j = ci_s[qq];
-            *reinterpret_cast<bf16*>(arow + (size_t)(j >> 3) * kpstrideA + (j & 7) * 2) = __float2bfloat16_rn(val_s[qq]);
+            st1(reinterpret_cast<bf16*>(arow + (size_t)(j >> 3) * kpstrideA + (j & 7) * 2), val_s[qq]);
           }
         }
       }

@@ -153,12 +153,30 @@ int fail(gnnuds_handle* h, int code, const char* fmt, ...) {
   } while (0)
 
 // ---- bf16 operand images for the tensor-core kernels (layout: csrc/umma.cuh) -------------
-inline uint16_t f2bf(float f) {
+#if GU_F16
+#define GU_TMAP_16 CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+#else
+#define GU_TMAP_16 CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+#endif
+inline uint16_t f2bf(float f) {          // float -> the build's 16-bit storage type (round to nearest even)
+#if GU_F16
+  return __half_as_ushort(__float2half_rn(f));
+#else
   uint32_t u;
   std::memcpy(&u, &f, 4);
   if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;
   u += 0x7fffu + ((u >> 16) & 1u);
   return (uint16_t)(u >> 16);
+#endif
+}
+inline float bf2f(uint16_t b) {          // and back
+#if GU_F16
+  return __half2float(__ushort_as_half(b));
+#else
+  const uint32_t u = (uint32_t)b << 16;
+  float f; std::memcpy(&f, &u, 4);
+  return f;
+#endif
 }
 // K-major panel image of mat[rows][cols] (element (r,k) = mat[r*ldr + k*ldk]); rows/cols beyond the
 // matrix are zero.  Byte offset of (r,k): (k/8)*pstride + r*16 + (k%8)*2.
@@ -695,7 +713,7 @@ bool make_rows_tmap(CUtensorMap* m, const void* base, long long rows, int ld, in
   cuuint64_t strides[2] = {(cuuint64_t)ld * 2, 16};
   cuuint32_t box[3] = {8, (cuuint32_t)boxrows, (cuuint32_t)(kc / 8)};
   cuuint32_t es[3] = {1, 1, 1};
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  return enc(m, GU_TMAP_16, 3, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
@@ -707,7 +725,7 @@ bool make_rows_tmap_sw(CUtensorMap* m, const void* base, long long rows, int ld,
   cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)rows * ld * 2};
   cuuint32_t box[3] = {64, (cuuint32_t)boxrows, 1};
   cuuint32_t es[3] = {1, 1, 1};
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, Bc > 0 ? 3 : 2, const_cast<void*>(base), dims, strides, box, es,
+  return enc(m, GU_TMAP_16, Bc > 0 ? 3 : 2, const_cast<void*>(base), dims, strides, box, es,
              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
@@ -720,7 +738,7 @@ bool make_rows_tmap4(CUtensorMap* m, const void* base, long long Bc, long long r
   cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)rows_per_b * ld * 2, 16};
   cuuint32_t box[4] = {8, 128, 1, (cuuint32_t)(kc / 8)};
   cuuint32_t es[4] = {1, 1, 1, 1};
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  return enc(m, GU_TMAP_16, 4, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
@@ -1658,9 +1676,7 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
         std::vector<float> lo((size_t)Nout * Ktot);
         for (size_t i = 0; i < lo.size(); ++i) {
           const float v = blob[offsets[t] + i];
-          const uint32_t hb = (uint32_t)f2bf(v) << 16;
-          float hv; std::memcpy(&hv, &hb, 4);
-          lo[i] = v - hv;
+          lo[i] = v - bf2f(f2bf(v));
         }
         std::vector<uint16_t> img2 = pack_kmajor(lo.data(), Nout, Ktot, 1, Nout, Nout, Ktot, Nout * 16);
         all.insert(all.end(), img2.begin(), img2.end());
@@ -1759,6 +1775,8 @@ int gnnuds_set_norm(gnnuds_handle* h, const float* norm_x, int32_t c_x, const fl
   h->has_norm = true;
   return 0;
 }
+
+int gnnuds_tc_operand_is_half(void) { return GU_F16 ? 16 : 0; }
 
 int gnnuds_output_dims(const gnnuds_handle* h, int32_t* y_channels, int32_t* ey_channels) {
   if (!h) return GNNUDS_E_INVALID;
@@ -2083,7 +2101,7 @@ int gnnuds_debug_fetch(gnnuds_handle* h, int32_t which, float* out, int64_t max_
     if (h->tc()) {
       std::vector<uint16_t> tmp((size_t)n);
       CU(cudaMemcpy(tmp.data(), h->dbg_ptr[which], n * 2, cudaMemcpyDeviceToHost));
-      for (int64_t i = 0; i < n; ++i) { const uint32_t u = (uint32_t)tmp[i] << 16; std::memcpy(out + i, &u, 4); }
+      for (int64_t i = 0; i < n; ++i) out[i] = bf2f(tmp[i]);
     } else {
       CU(cudaMemcpy(out, h->dbg_ptr[which], n * sizeof(float), cudaMemcpyDeviceToHost));
     }

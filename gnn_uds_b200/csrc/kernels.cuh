@@ -7,22 +7,45 @@
 // by shift*Nn, and the GRU walks rows with stride Nn.
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 namespace gu {
 
-// Activation storage: float (fp32 parity path) or bf16 (tensor-core path).  Every kernel below
+// Activation storage: float (fp32 parity path) or a 16-bit type (tensor-core path).  Every kernel below
 // that touches an activation tensor is a template over the storage type and computes in fp32.
+// The 16-bit type - historically named `bf16` throughout - is IEEE fp16 by default (GU_F16 = 1: 11 significand bits,
+// operands of tcgen05 kind::f16 as F16 x F16 -> F32) and bfloat16 when built with -DGNNUDS_TC_BF16 (8 bits, wider range).
+// fp16 cuts the tensor-core path's deviation from the fp32 path by ~8x; the model's activations are O(1..100), far
+// from fp16's 65504.
+#ifdef GNNUDS_TC_BF16
+#define GU_F16 0
 typedef __nv_bfloat16 bf16;
+#else
+#define GU_F16 1
+typedef __half bf16;
+#endif
+// two packed 16-bit storage values <-> fp32
+__device__ __forceinline__ float2 unpack2_16(uint32_t u) {
+#if GU_F16
+  return __half22float2(*reinterpret_cast<const __half2*>(&u));
+#else
+  return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xFFFF0000u));
+#endif
+}
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 __device__ __forceinline__ float4 ld4(const bf16* p) {
   const uint2 u = *reinterpret_cast<const uint2*>(p);
-  return make_float4(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xFFFF0000u), __uint_as_float(u.y << 16),
-                     __uint_as_float(u.y & 0xFFFF0000u));
+  const float2 a = unpack2_16(u.x), b = unpack2_16(u.y);
+  return make_float4(a.x, a.y, b.x, b.y);
 }
 __device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
+#if GU_F16
+  __half2 v = __floats2half2_rn(lo, hi);
+#else
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+#endif
   return *reinterpret_cast<uint32_t*>(&v);
 }
 __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
@@ -30,9 +53,17 @@ __device__ __forceinline__ void st4(bf16* p, float4 v) {
   *reinterpret_cast<uint2*>(p) = make_uint2(pack2_bf16(v.x, v.y), pack2_bf16(v.z, v.w));
 }
 __device__ __forceinline__ float ld1(const float* p) { return *p; }
+#if GU_F16
+__device__ __forceinline__ float ld1(const bf16* p) { return __half2float(*p); }
+#else
 __device__ __forceinline__ float ld1(const bf16* p) { return __bfloat162float(*p); }
+#endif
 __device__ __forceinline__ void st1(float* p, float v) { *p = v; }
+#if GU_F16
+__device__ __forceinline__ void st1(bf16* p, float v) { *p = __float2half_rn(v); }
+#else
 __device__ __forceinline__ void st1(bf16* p, float v) { *p = __float2bfloat16_rn(v); }
+#endif
 
 enum { ACT_LINEAR = 0, ACT_RELU = 1, ACT_TANH = 2, ACT_SIGMOID = 3, ACT_HARD_SIGMOID = 4 };
 
@@ -964,14 +995,13 @@ __global__ void __launch_bounds__(256) cumsum_head_bf16_kernel(CumHeadP p) {
       float d[NV];
 #pragma unroll
       for (int u = 0; u < TB; ++u) {
-        acc.x += __uint_as_float(raw[u].x << 16); acc.y += __uint_as_float(raw[u].x & 0xFFFF0000u);
-        acc.z += __uint_as_float(raw[u].y << 16); acc.w += __uint_as_float(raw[u].y & 0xFFFF0000u);
+        { const float2 f0 = unpack2_16(raw[u].x), f1 = unpack2_16(raw[u].y); acc.x += f0.x; acc.y += f0.y; acc.z += f1.x; acc.w += f1.y; }
         float v[4] = {acc.x + r.x, acc.y + r.y, acc.z + r.z, acc.w + r.w};
         act_tile4(v, p.act);
         const uint2 pk = make_uint2(pack2_bf16(v[0], v[1]), pack2_bf16(v[2], v[3]));
         if (p.write_x && t0 + u < p.Tn) *reinterpret_cast<uint2*>(base + (size_t)(t0 + u) * tstride) = pk;
-        const float q0 = __uint_as_float(pk.x << 16), q1 = __uint_as_float(pk.x & 0xFFFF0000u);
-        const float q2 = __uint_as_float(pk.y << 16), q3 = __uint_as_float(pk.y & 0xFFFF0000u);
+        const float2 qa = unpack2_16(pk.x), qb = unpack2_16(pk.y);
+        const float q0 = qa.x, q1 = qa.y, q2 = qb.x, q3 = qb.y;
 #pragma unroll
         for (int o = 0; o < NOUT; ++o) d[u * NOUT + o] = fmaf(q0, w[0][o], fmaf(q1, w[1][o], fmaf(q2, w[2][o], q3 * w[3][o])));
       }

@@ -172,9 +172,15 @@ __device__ __forceinline__ uint64_t desc_kmajor(uint32_t base, uint32_t pstride,
 __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, uint32_t pstride, int col0, int kstep) {
   return smem_desc(base + (uint32_t)(col0 >> 3) * pstride + (uint32_t)kstep * 256u, 128u, pstride);
 }
-// instruction descriptor: kind::f16, bf16 x bf16 -> fp32 (cute::UMMA::InstrDescriptor)
+// instruction descriptor: kind::f16, 16-bit x 16-bit -> fp32 (cute::UMMA::InstrDescriptor): c_format F32 (bit 4),
+// a_format / b_format (bits 7..9 / 10..12) 0 = F16, 1 = BF16 - set by the build's 16-bit storage type (kernels.cuh)
+#ifdef GNNUDS_TC_BF16
+#define GU_IDESC_AB ((1u << 7) | (1u << 10))
+#else
+#define GU_IDESC_AB 0u
+#endif
 __host__ __device__ constexpr uint32_t idesc_bf16(int M, int N, int a_mn_major, int b_mn_major) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+  return (1u << 4) | GU_IDESC_AB | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 // D[tmem] (+)= A[smem] * B[smem], one K=16 step; issued by ONE thread
@@ -194,8 +200,12 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
 }
 
 // ---- bf16 packing ---------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {    // the build's 16-bit storage type (kernels.cuh)
+#ifdef GNNUDS_TC_BF16
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+#else
+  __half2 v = __floats2half2_rn(lo, hi);
+#endif
   return *reinterpret_cast<uint32_t*>(&v);
 }
 __device__ __forceinline__ uint4 pack8_bf16(const float* v) {
@@ -218,8 +228,13 @@ __device__ __forceinline__ void unpack8_bf16(const uint4& u, float* v) {
   const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
+#ifdef GNNUDS_TC_BF16
     v[2 * i] = __uint_as_float(w[i] << 16);
     v[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+#else
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+    v[2 * i] = f.x; v[2 * i + 1] = f.y;
+#endif
   }
 }
 

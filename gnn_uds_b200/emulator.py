@@ -164,7 +164,7 @@ class Emulator:
         cfg.resnet, cfg.if_flood, cfg.edge_fusion = int(self.resnet), self.if_flood, int(self.edge_fusion)
         cfg.act, cfg.graph_base, cfg.tide, cfg.n_act = int(bool(self.act)), self.graph_base, int(self.tide), self.n_act
         cfg.epsilon = self.epsilon
-        cfg.precision = {"fp32": _lib.PREC_FP32, "bf16": _lib.PREC_BF16_TC}[precision]
+        cfg.precision = {"fp32": _lib.PREC_FP32, "bf16": _lib.PREC_BF16_TC, "fp16": _lib.PREC_BF16_TC, "tc": _lib.PREC_BF16_TC}[precision]   # "bf16" = historical name of the 16-bit tensor-core path (fp16 operands in the default build)
         cfg.device, cfg.max_chunk, cfg.workspace_mb = self.device, int(max_chunk), int(workspace_mb)
         self._cfg = cfg
         self._h = C.c_void_p()

@@ -36,7 +36,8 @@ enum { GNNUDS_CONV_GCN = 1, GNNUDS_CONV_GAT = 2 };                 /* emulator.p
 enum { GNNUDS_REC_CONV1D = 1, GNNUDS_REC_GRU = 2, GNNUDS_REC_LSTM = 3 }; /* emulator.py:154-163 */
 enum { GNNUDS_ACT_LINEAR = 0, GNNUDS_ACT_RELU = 1, GNNUDS_ACT_TANH = 2, GNNUDS_ACT_SIGMOID = 3 };
 enum { GNNUDS_PREC_FP32 = 0,    /* fp32 SIMT, parity mode (<=1e-5 rel per step) */
-       GNNUDS_PREC_BF16_TC = 1  /* bf16 operands on tcgen05, fp32 accumulate */ };
+       GNNUDS_PREC_BF16_TC = 1  /* 16-bit operands on tcgen05 (fp16 by default, bf16 with -DGNNUDS_TC_BF16; see
+                               gnnuds_tc_operand_is_half), fp32 accumulate */ };
 enum { GNNUDS_MEM_HOST = 0, GNNUDS_MEM_DEVICE = 1 };
 /* feedback rule of the autoregressive chunk loop */
 enum { GNNUDS_ROLL_MPC = 1,     /* mpc.py:565-582 */
@@ -113,6 +114,10 @@ int gnnuds_set_norm(gnnuds_handle* h, const float* norm_x, int32_t c_x,
                     const float* norm_b, int32_t c_b,
                     const float* norm_y, int32_t c_y,
                     const float* norm_e, int32_t c_e);
+
+/* 16-bit operand type of this build's tensor-core path: 16 = IEEE fp16 (default), 0 = bfloat16 (-DGNNUDS_TC_BF16).
+   No handle needed. */
+int gnnuds_tc_operand_is_half(void);
 
 /* Channels of the node output y ([h,q_us,q_ds,(flood_prob),q_w]) and edge output. */
 int gnnuds_output_dims(const gnnuds_handle* h, int32_t* y_channels, int32_t* ey_channels);

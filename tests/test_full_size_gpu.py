@@ -90,10 +90,8 @@ def test_picked_scenarios_match_oracle(c2_full):
             same = (y[64 * rep + i][..., 3] > 0.5) == (y64[k][..., 3] > 0.5)
             decided = np.abs(y64[k][..., 3] - 0.5) > 5e-3     # a probability inside the tolerance band may land either side
             assert (~same & decided).mean() <= 1e-3 and (~same).mean() <= 1e-2
-            # Node outputs: the bounds of tests/test_tc_parity_gpu.py.  Edge outputs at the full 60-step horizon: the
-            # resnet cumsum (emulator.py:318-320) adds the bf16 noise of the 60 increments coherently, and on these
-            # random-init scenarios the increments partly cancel, so late-horizon edge volumes deviate by up to ~4 % of
-            # the channel scale (RMSE 3e-3 over all channels, 5e-3 on the volume channel; the fp32 path is at 5e-6 on
-            # the same scenarios, tools/diag_full.py).  The bound below is what the bf16 path delivers, not a target.
-            assert d[same].max() < 1e-2 and np.sqrt((d[same] ** 2).mean()) < 3e-3
-            assert de.max() < 6e-2 and np.sqrt((de ** 2).mean()) < 5e-3
+            # The resnet cumsum (emulator.py:318-320) adds the rounding noise of the 60 increments coherently, so the
+            # full horizon is the hardest case: measured with fp16 operands max 5.7e-3 / RMSE 8e-4 on the edge volume
+            # channel (bf16 operands: 4.1e-2 / 5.1e-3; fp32 path 5e-6 on the same scenarios, tools/diag_full.py).
+            assert d[same].max() < 5e-3 and np.sqrt((d[same] ** 2).mean()) < 1e-3
+            assert de.max() < 1e-2 and np.sqrt((de ** 2).mean()) < 1e-3

@@ -1,10 +1,12 @@
-"""GPU parity of the tensor-core (bf16 operands, fp32 accumulate) path against the float64 oracle.
+"""GPU parity of the tensor-core path (16-bit operands - fp16 in the default build -, fp32 accumulate) against
+the float64 oracle.  `precision="bf16"` is the historical name of the 16-bit path in the API.
 
 Tolerance (north_star: "tensor-core path within a stated tolerance on per-step depth/flow and on
-full-rollout RMSE/NSE deltas (<= 1e-3)"): per step, max error <= 1e-2 and RMSE <= 3e-3 of the
-per-channel output scale (max |truth|, floor 1); NSE delta <= 1e-3 (the oracle against itself has
-NSE 1, so the delta is 1 - NSE(product, truth)); flood-flag flip rate <= 1e-3.  bf16 keeps 8
-mantissa bits, so these are ~40x the measured errors of a 14-layer network, not a loose bound.
+full-rollout RMSE/NSE deltas (<= 1e-3)"): per step, max error <= 5e-3 and RMSE <= 1e-3 of the
+per-channel output scale (max |truth|, floor 1); NSE delta <= 1e-4 (the oracle against itself has
+NSE 1, so the delta is 1 - NSE(product, truth)); flood-flag flip rate <= 1e-3.  Measured with fp16
+operands: max <= 1.4e-3, RMSE <= 2.6e-4, NSE delta <= 1.3e-5 over all cases (bf16 operands, build flag
+-DGNNUDS_TC_BF16, are ~8x worse and need 1e-2 / 3e-3 / 1e-3).
 """
 import numpy as np
 import pytest
@@ -12,7 +14,16 @@ import pytest
 import cases
 
 pytestmark = pytest.mark.gpu
-MAX_TOL, RMSE_TOL, NSE_TOL, FLIP_TOL = 1e-2, 3e-3, 1e-3, 1e-3
+MAX_TOL, RMSE_TOL, NSE_TOL, FLIP_TOL = 5e-3, 1e-3, 1e-4, 1e-3
+
+
+def _is_bf16_build():
+    from gnn_uds_b200 import _lib
+    return not _lib.load().gnnuds_tc_operand_is_half()
+
+
+if _is_bf16_build():
+    MAX_TOL, RMSE_TOL, NSE_TOL = 1e-2, 3e-3, 1e-3
 
 
 def _scale(t):

@@ -1,4 +1,4 @@
-"""tcgen05 building blocks (csrc/umma.cuh) against NumPy: bf16 operands, fp32 accumulate.
+"""tcgen05 building blocks (csrc/umma.cuh) against NumPy: 16-bit operands (fp16 by default, bf16 builds), fp32 accumulate.
 Covers the operand views every tensor-core kernel of the library relies on."""
 import ctypes as C
 
@@ -11,6 +11,10 @@ pytestmark = pytest.mark.gpu
 
 
 def bf16_round(a):
+    """Round to the library's 16-bit operand type."""
+    from gnn_uds_b200 import _lib
+    if _lib.load().gnnuds_tc_operand_is_half():
+        return np.asarray(a, np.float32).astype(np.float16).astype(np.float32)
     u = np.ascontiguousarray(a, np.float32).view(np.uint32).astype(np.uint64)
     u = (u + 0x7FFF + ((u >> 16) & 1)) & 0xFFFF0000
     return u.astype(np.uint32).view(np.float32)
