@@ -41,6 +41,18 @@ def flops(em, B):
     gat = em.conv_kind == "gat"
     tot = 2 * (B * Ti * (N * em.n_in + M * em.e_in) * E + B * To * (N * em.b_in + M * act) * E // 2)
     gemm = 0
+    if em.conv_kind == "nn":       # NN-cat: one flattened row per (b,t) (emulator.py:231-233), everything is a row GEMM
+        for blk, T in ((0, Ti), (1, To)):
+            c = 2 * E if blk == 0 else 2 * H + E // 2 + (E // 2) * act
+            for l in range(S):
+                tot += 2 * B * T * c * 2 * E
+                c = 2 * E
+            for l in range(P):
+                c = E if l == 0 else H
+                tot += 2 * 2 * B * T * {"Conv1D": k * c * H, "GRU": 3 * H * (c + H), "LSTM": 4 * H * (c + H)}[em.recurrent]
+        tot += 2 * B * To * (2 * H * E + (E * E // 2 + (F - 1) * (E // 2) ** 2 + (E // 2) * N if F else 0)
+                             + E * em.n_out * N + E * em.e_out * M)
+        return float(tot), float(tot)
     for blk, T in ((0, Ti), (1, To)):
         cx, ce = (E, E) if blk == 0 else (H + E // 2, H + (E // 2) * act)
         for l in range(S):
@@ -81,7 +93,7 @@ def dominant_kernel(em, B, precision):
         per_sample = (nnz * E + R * E) * es
         return dict(family=2, kernel="agg_large_kernel (CSR neighbour gather, joint node+edge graph)", bound="hbm",
                     bytes=float(B * (Ti + To) * S * per_sample), unit_note="(nnz*E gathered + (N+M)*E written) * %d B per (b,t) sample and layer" % es)
-    if precision != "bf16":
+    if precision != "bf16" or em.conv_kind == "nn":
         return dict(family=0, kernel="rows_gemm_f32 (all Dense/conv-linear/Conv1D launches of a step)", bound="tensor", bytes=None, unit_note="")
     act = 1 if em.act else 0
     tot = 0
@@ -386,7 +398,7 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32" if precision == "fp32" else ("f16(f32 acc)" if em._lib.gnnuds_tc_operand_is_half() else "bf16(f32 acc)"), "data": "synthetic",
+            "dtype": "f32" if (precision == "fp32" or em.conv_kind == "nn") else ("f16(f32 acc)" if em._lib.gnnuds_tc_operand_is_half() else "bf16(f32 acc)"), "data": "synthetic",
             "config": {"workload": "%s: %s %s+%s edge_fusion=%s resnet=%s if_flood=%d act=%s, N=%d M=%d, seq %d->%d, B=%d per GPU" % (
                 a.workload, args.__dict__.get("env_name", configs.WORKLOADS[a.workload]["net"]), em.conv_kind.upper(), em.recurrent,
                 em.edge_fusion, em.resnet, em.if_flood, bool(em.act), N, M, Ti, To, B),

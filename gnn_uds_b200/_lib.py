@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgnnuds.so")
 
 ABI_VERSION = 2
-CONV_GCN, CONV_GAT = 1, 2
+CONV_NONE, CONV_GCN, CONV_GAT = 0, 1, 2
 REC_CONV1D, REC_GRU, REC_LSTM = 1, 2, 3
 ACT = {"linear": 0, None: 0, "relu": 1, "tanh": 2, "sigmoid": 3}
 PREC_FP32, PREC_BF16_TC = 0, 1

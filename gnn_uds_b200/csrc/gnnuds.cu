@@ -10,6 +10,7 @@
 #include "fused_sp.cuh"
 #include "fused_conv.cuh"
 #include "gru_tc.cuh"
+#include "nn_cat.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -64,6 +65,13 @@ struct gnnuds_handle {
   std::vector<LayerW> tpx[2], tpe[2];
   LayerW resx, rese, head_out, head_flood, head_e;
   std::vector<LayerW> flood_chain;
+  // NN-cat (conv == GNNUDS_CONV_NONE): Dense(2E) spatial layers and zero-padded copies of the layers whose flattened
+  // widths (N*C) are not multiples of 16 (csrc/nn_cat.cuh)
+  std::vector<LayerW> nn_sp[2];
+  bool nn() const { return c.conv == GNNUDS_CONV_NONE; }
+  float* d_nnpad = nullptr;
+  struct NnPad { long long w = 0, b = 0; int K = 0, Kp = 0, No = 0, Nop = 0; };
+  NnPad nnp_x, nnp_b, nnp_e, nnp_a, nnp_out, nnp_flood, nnp_eout;
 
   // device parameters
   float* d_blob = nullptr;
@@ -265,9 +273,35 @@ struct LayoutBuilder {
       cx = ce = E;
     }
   }
+  // NN-cat creation order (emulator.py:195-336 with conv falsy)
+  void build_nn() {
+    const auto& c = h->c;
+    const int E = c.embed, H = c.hidden, N = c.n_node, M = c.n_edge;
+    h->emb_x = dense(N * c.n_in, E);               // :197-198
+    h->emb_b = dense(N * c.b_in, E / 2);           // :202-203
+    h->emb_e = dense(M * c.e_in, E);               // :205-206
+    if (c.act) h->emb_a = dense(M, E / 2);         // :211-212
+    for (int l = 0; l < c.n_sp_layer; ++l) h->nn_sp[0].push_back(dense(2 * E, 2 * E));   // :232
+    temporal(h->tpx[0], E);
+    temporal(h->tpe[0], E);
+    int ci = 2 * H + E / 2 + (c.act ? E / 2 : 0);
+    for (int l = 0; l < c.n_sp_layer; ++l) { h->nn_sp[1].push_back(dense(ci, 2 * E)); ci = 2 * E; }   // :285
+    temporal(h->tpx[1], E);
+    temporal(h->tpe[1], E);
+    h->resx = dense(H, E);
+    h->rese = dense(H, E);
+    h->head_out = dense(E, c.n_out * N);           // :322-324
+    if (c.if_flood) {
+      int cf = E;
+      for (int i = 0; i < c.if_flood; ++i) { h->flood_chain.push_back(dense(cf, E / 2)); cf = E / 2; }
+      h->head_flood = dense(cf, N);                // :327,330
+    }
+    h->head_e = dense(E, c.e_out * M);             // :335-336
+  }
   void build() {
     const auto& c = h->c;
     const int E = c.embed, H = c.hidden;
+    if (h->nn()) { build_nn(); return; }
     h->emb_x = dense(c.n_in, E);                   // :198
     h->emb_b = dense(c.b_in, E / 2);               // :203
     h->emb_e = dense(c.e_in, E);                   // :206
@@ -459,7 +493,7 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src
   const auto& c = h->c;
   const int H = c.hidden, P = c.n_tp_layer;
   const float* cur = src.p;
-  int cw = cin, cpitch = src.pitch, coff = src.off;
+  int cw = cin, cld = src.ld, cpitch = src.pitch, coff = src.off;
   float* bufs[2] = {t0, t1};
   for (int i = 0; i < P; ++i) {
     const bool last = (i == P - 1);
@@ -469,14 +503,14 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src
     if (c.recurrent == GNNUDS_REC_CONV1D) {
       std::vector<SegH> segs;
       const int k = c.kernel_size, d = 1 << i;
-      for (int j = 0; j < k; ++j) segs.push_back({cur, cw, cw, (k - 1 - j) * d, cpitch, coff});
+      for (int j = 0; j < k; ++j) segs.push_back({cur, cld, cw, (k - 1 - j) * d, cpitch, coff});
       rc = launch_gemm(h, segs, W(h, L[i].t[0]), W(h, L[i].t[1]), o, H, H, act_code(c), Bc, Nn, Tdst, Ts, Nn, 0);
       if (rc) return rc;
     } else {
       const bool gru = c.recurrent == GNNUDS_REC_GRU;
       const int G = (gru ? 3 : 4) * H;
       // input projection for every time step
-      rc = launch_gemm(h, {{cur, cw, cw, 0, cpitch, coff}}, W(h, L[i].t[0]), W(h, L[i].t[2]) /* b[0] or b */, h->HB, G, G,
+      rc = launch_gemm(h, {{cur, cld, cw, 0, cpitch, coff}}, W(h, L[i].t[0]), W(h, L[i].t[2]) /* b[0] or b */, h->HB, G, G,
                        ACT_LINEAR, Bc, Nn, Ts, Ts, Nn, 0);
       if (rc) return rc;
       const long long nseq = Bc * Nn;
@@ -501,7 +535,7 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src
       ++h->launches;
       CU(cudaGetLastError());
     }
-    cur = o; cw = H; cpitch = Nn; coff = 0;
+    cur = o; cw = H; cld = H; cpitch = Nn; coff = 0;
     // note: for non-final layers Tdst == Ts so the next layer reads a full-length sequence
   }
   *dst = const_cast<float*>(cur);
@@ -677,6 +711,112 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
     if ((rc = launch_head(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return rc;
   }
   if ((rc = launch_head(h, h->EA, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
+  return run_postproc(h, x, b, a, Bc, y, ey, normalised_io);
+}
+
+// ---- NN-cat forward (conv falsy): flattened rows through Dense / temporal stacks, csrc/nn_cat.cuh ----
+int forward_chunk_nn(gnnuds_handle* h, const float* x, const float* b, const float* a, const float* ex, long long Bc,
+                     float* y, float* ey, bool normalised_io) {
+  const auto& c = h->c;
+  const int E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge, Ti = c.seq_in, To = c.seq_out;
+  const int act = act_code(c);
+  const float* P = h->d_nnpad;
+  int rc;
+  auto prep = [&](const float* in, const float* nrm, int cn, int Nn, int K, int Kp, int mode, long long rows) -> int {
+    NnPrepP p{in, nrm, nrm ? nrm + (size_t)Nn * cn : nullptr, cn, h->d_act_of_edge, c.n_act, h->HB, rows, Nn, K, Kp, mode};
+    nn_prep_kernel<<<grid_for(h, rows * Kp, 256, 16), 256, 0, h->stream>>>(p);
+    ++h->launches;
+    CU(cudaGetLastError());
+    return 0;
+  };
+  auto unflat = [&](const float* in, int ldi, float* out, int ldo, int col0, long long rows, int Nn, int nc) -> int {
+    NnUnflatP p{in, ldi, out, ldo, col0, rows, Nn, nc};
+    nn_unflatten_kernel<<<grid_for(h, rows * Nn * nc, 256, 16), 256, 0, h->stream>>>(p);
+    ++h->launches;
+    CU(cudaGetLastError());
+    return 0;
+  };
+  // ---- embeddings (emulator.py:195-213): x and e keep the pre-activation of the last input step for the resnet ----
+  const float* nx = normalised_io ? nullptr : h->d_nx;
+  const float* nb = normalised_io ? nullptr : h->d_nb;
+  const float* ne = normalised_io ? nullptr : h->d_ne;
+  if ((rc = prep(x, nx, h->cx_n, N, c.n_in, h->nnp_x.Kp, 0, Bc * Ti))) return rc;
+  {
+    const std::vector<SegH> s = {{h->HB, h->nnp_x.Kp, h->nnp_x.Kp, 0, 1, 0}};
+    if ((rc = launch_gemm(h, s, P + h->nnp_x.w, W(h, h->emb_x.t[1]), h->XB, E, E, act, Bc, 1, Ti, Ti, 1, 0))) return rc;
+    if ((rc = launch_gemm(h, s, P + h->nnp_x.w, W(h, h->emb_x.t[1]), h->RES, E, E, ACT_LINEAR, Bc, 1, 1, Ti, 1, 0))) return rc;
+  }
+  if ((rc = prep(b, nb, h->cb_n, N, c.b_in, h->nnp_b.Kp, 0, Bc * To))) return rc;
+  if ((rc = launch_gemm(h, {{h->HB, h->nnp_b.Kp, h->nnp_b.Kp, 0, 1, 0}}, P + h->nnp_b.w, W(h, h->emb_b.t[1]), h->BEMB, E2, E2, act,
+                        Bc, 1, To, To, 1, 0))) return rc;
+  if ((rc = prep(ex, ne, h->ce_n, M, c.e_in, h->nnp_e.Kp, 0, Bc * Ti))) return rc;
+  {
+    const std::vector<SegH> s = {{h->HB, h->nnp_e.Kp, h->nnp_e.Kp, 0, 1, 0}};
+    if ((rc = launch_gemm(h, s, P + h->nnp_e.w, W(h, h->emb_e.t[1]), h->EB, E, E, act, Bc, 1, Ti, Ti, 1, 0))) return rc;
+    if ((rc = launch_gemm(h, s, P + h->nnp_e.w, W(h, h->emb_e.t[1]), h->RESE, E, E, ACT_LINEAR, Bc, 1, 1, Ti, 1, 0))) return rc;
+  }
+  if (c.act) {
+    if ((rc = prep(a, nullptr, 0, M, 1, h->nnp_a.Kp, 2, Bc * To))) return rc;
+    if ((rc = launch_gemm(h, {{h->HB, h->nnp_a.Kp, h->nnp_a.Kp, 0, 1, 0}}, P + h->nnp_a.w, W(h, h->emb_a.t[1]), h->AEMB, E2, E2, act,
+                          Bc, 1, To, To, 1, 0))) return rc;
+  }
+  Stream2 st;
+  st.x = {{h->XB, E, E, 0, 1, 0}};
+  st.e = {{h->EB, E, E, 0, 1, 0}};
+  // spatial block: x,e = split(Dense(2E)(concat[x,e])) (emulator.py:231-233); the halves stay views of one 2E-wide row
+  auto spatial = [&](int blk, int T) -> int {
+    for (int l = 0; l < c.n_sp_layer; ++l) {
+      const LayerW& w = h->nn_sp[blk][l];
+      std::vector<SegH> segs = st.x;
+      segs.insert(segs.end(), st.e.begin(), st.e.end());
+      float* z = (l & 1) ? h->EA : h->XA;
+      int r = launch_gemm(h, segs, W(h, w.t[0]), W(h, w.t[1]), z, 2 * E, 2 * E, act, Bc, 1, T, T, 1, 0);
+      if (r) return r;
+      st.x = {{z, 2 * E, E, 0, 1, 0}};
+      st.e = {{z + E, 2 * E, E, 0, 1, 0}};
+    }
+    return 0;
+  };
+  if ((rc = spatial(0, Ti))) return rc;
+  float *xt = nullptr, *et = nullptr;
+  if ((rc = run_temporal(h, h->tpx[0], st.x[0], E, Bc, 1, Ti, To, h->TX0, h->TX1, &xt))) return rc;
+  if ((rc = run_temporal(h, h->tpe[0], st.e[0], E, Bc, 1, Ti, To, h->TE0, h->TE1, &et))) return rc;
+  st.x = {{xt, H, H, 0, 1, 0}, {h->BEMB, E2, E2, 0, 1, 0}};
+  st.e = {{et, H, H, 0, 1, 0}};
+  if (c.act) st.e.push_back({h->AEMB, E2, E2, 0, 1, 0});
+  if ((rc = spatial(1, To))) return rc;
+  if ((rc = run_temporal(h, h->tpx[1], st.x[0], E, Bc, 1, To, To, h->TX0, h->TX1, &xt))) return rc;
+  if ((rc = run_temporal(h, h->tpe[1], st.e[0], E, Bc, 1, To, To, h->TE0, h->TE1, &et))) return rc;
+  // ---- resnet + heads (emulator.py:312-338) ----
+  const int ract = c.resnet ? ACT_LINEAR : act;
+  if ((rc = launch_gemm(h, {{xt, H, H, 0, 1, 0}}, W(h, h->resx.t[0]), W(h, h->resx.t[1]), h->XB, E, E, ract, Bc, 1, To, To, 1, 0))) return rc;
+  if ((rc = launch_gemm(h, {{et, H, H, 0, 1, 0}}, W(h, h->rese.t[0]), W(h, h->rese.t[1]), h->EB, E, E, ract, Bc, 1, To, To, 1, 0))) return rc;
+  if (c.resnet) {
+    cumsum_res_act_kernel<float><<<grid_for(h, Bc * (E / 4), 256, 16), 256, 0, h->stream>>>(h->XB, h->RES, Bc, To, 1, E, act);
+    cumsum_res_act_kernel<float><<<grid_for(h, Bc * (E / 4), 256, 16), 256, 0, h->stream>>>(h->EB, h->RESE, Bc, To, 1, E, act);
+    h->launches += 2;
+    CU(cudaGetLastError());
+  }
+  const long long So = Bc * To;
+  const int ldn = h->ldn();
+  if ((rc = launch_gemm(h, {{h->XB, E, E, 0, 1, 0}}, P + h->nnp_out.w, P + h->nnp_out.b, h->XA, h->nnp_out.Nop, h->nnp_out.Nop,
+                        ACT_HARD_SIGMOID, Bc, 1, To, To, 1, 0))) return rc;
+  if ((rc = unflat(h->XA, h->nnp_out.Nop, h->OUTN, ldn, 0, So, N, c.n_out))) return rc;
+  if (c.if_flood) {
+    std::vector<SegH> cur = {{h->XB, E, E, 0, 1, 0}};
+    float* bufs[2] = {h->EX, h->NX};
+    for (int i = 0; i < c.if_flood; ++i) {
+      if ((rc = launch_gemm(h, cur, W(h, h->flood_chain[i].t[0]), W(h, h->flood_chain[i].t[1]), bufs[i & 1], E2, E2, act, Bc, 1,
+                            To, To, 1, 0))) return rc;
+      cur = {{bufs[i & 1], E2, E2, 0, 1, 0}};
+    }
+    if ((rc = launch_gemm(h, cur, P + h->nnp_flood.w, P + h->nnp_flood.b, h->XA, h->nnp_flood.Nop, h->nnp_flood.Nop, ACT_SIGMOID,
+                          Bc, 1, To, To, 1, 0))) return rc;
+    if ((rc = unflat(h->XA, h->nnp_flood.Nop, h->OUTN, ldn, c.n_out, So, N, 1))) return rc;
+  }
+  if ((rc = launch_gemm(h, {{h->EB, E, E, 0, 1, 0}}, P + h->nnp_eout.w, P + h->nnp_eout.b, h->EA, h->nnp_eout.Nop, h->nnp_eout.Nop,
+                        ACT_TANH, Bc, 1, To, To, 1, 0))) return rc;
+  if ((rc = unflat(h->EA, h->nnp_eout.Nop, h->OUTE, c.e_out, 0, So, M, c.e_out))) return rc;
   return run_postproc(h, x, b, a, Bc, y, ey, normalised_io);
 }
 
@@ -1286,19 +1426,33 @@ int run_spatial_joint(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int 
 
 int forward_any(gnnuds_handle* h, const float* x, const float* b, const float* a, const float* ex, long long Bc, float* y,
                 float* ey, bool normalised_io) {
+  if (h->nn()) return forward_chunk_nn(h, x, b, a, ex, Bc, y, ey, normalised_io);
   return h->tc() ? forward_chunk_tc(h, x, b, a, ex, Bc, y, ey, normalised_io) : forward_chunk(h, x, b, a, ex, Bc, y, ey, normalised_io);
 }
 
+// NN-cat keeps ONE row per (b,t): the activation buffers are sized for nn_rows_equiv() "nodes" of width E, enough for
+// the widest flattened row (inputs N*C, 2E spatial rows, flattened heads)
+int64_t nn_rows_equiv(const gnnuds_config& c) {
+  auto r16 = [](int64_t v) { return (v + 15) / 16 * 16; };
+  const int64_t N = c.n_node, M = c.n_edge;
+  int64_t w = 2 * c.embed;
+  for (int64_t v : {N * c.n_in, N * c.b_in, M * c.e_in, M, N * c.n_out, M * c.e_out, N}) w = std::max(w, r16(v));
+  return std::max<int64_t>(2, (w + c.embed - 1) / c.embed);
+}
+
 int64_t floats_per_scenario(const gnnuds_config& c) {
-  const int64_t E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge;
+  const int64_t E = c.embed, E2 = E / 2, H = c.hidden;
+  const bool nn = c.conv == GNNUDS_CONV_NONE;
+  int64_t N = nn ? nn_rows_equiv(c) : c.n_node, M = nn ? nn_rows_equiv(c) : c.n_edge;
   const int64_t Tm = std::max(c.seq_in, c.seq_out);
   const int64_t G = c.recurrent == GNNUDS_REC_GRU ? 3 * H : c.recurrent == GNNUDS_REC_LSTM ? 4 * H : 0;
   const int64_t W2 = std::max(E2, H);
   int64_t f = 0;
   f += Tm * (N + M) * (2 * E + 2 * W2 + 2 * H);          // XA XB EA EB | XE EX NX NE | TX* TE*
-  f += Tm * std::max(N, M) * std::max(E, G) + Tm * std::max(N, M) * 2;   // HB, SS, SN
+  f += Tm * std::max(N, M) * std::max(E, G) + Tm * std::max<int64_t>(c.n_node, c.n_edge) * 2;   // HB, SS, SN
   f += c.seq_out * (N + M) * E2;                         // BEMB AEMB
   f += (N + M) * E;                                      // RES RESE
+  if (nn) { N = c.n_node; M = c.n_edge; }
   f += c.seq_out * (N + M) * 4;                          // OUTN OUTE
   f += 2 * (c.seq_in * (N * c.n_in + M * c.e_in) + c.seq_out * (N * c.b_in + std::max(c.n_act, 1)));   // two staging sets
   f += 2 * c.seq_out * (N * 5 + M * 4);
@@ -1311,19 +1465,21 @@ int ensure_workspace(gnnuds_handle* h, int64_t Bc) {
   const auto& c = h->c;
   if (h->d_ws) { cudaFree(h->d_ws); h->d_ws = nullptr; }
   const int64_t E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge;
+  const int64_t Nw = h->nn() ? nn_rows_equiv(c) : N, Mw = h->nn() ? nn_rows_equiv(c) : M;   // activation rows per (b,t)
   const int64_t Tm = std::max(c.seq_in, c.seq_out);
   const int64_t G = c.recurrent == GNNUDS_REC_GRU ? 3 * H : c.recurrent == GNNUDS_REC_LSTM ? 4 * H : 0;
   const int64_t W2 = std::max(E2, H);
-  const int64_t RX = Bc * Tm * N, RE = Bc * Tm * M, RM = Bc * Tm * std::max(N, M);
+  const int64_t RX = Bc * Tm * Nw, RE = Bc * Tm * Mw, RM = Bc * Tm * std::max(Nw, Mw);
+  const int64_t RS = Bc * Tm * std::max(N, M);   // post-processing scratch rows
   const int64_t a = (int64_t)h->es();      // activation element size (fp32 path 4, tensor-core path 2)
   struct Item { float** p; int64_t bytes; };
   std::vector<Item> plan = {
       {&h->XA, RX * E * a}, {&h->XB, RX * E * a}, {&h->EA, RE * E * a}, {&h->EB, RE * E * a}, {&h->HB, RM * std::max(E, G) * a},
       {&h->XE, RE * W2 * a}, {&h->EX, RX * W2 * a}, {&h->NX, RX * W2 * a}, {&h->NE, RE * W2 * a},
       {&h->TX0, RX * H * a}, {&h->TX1, RX * H * a}, {&h->TE0, RE * H * a}, {&h->TE1, RE * H * a},
-      {&h->BEMB, Bc * c.seq_out * N * E2 * a}, {&h->AEMB, Bc * c.seq_out * M * E2 * a},
-      {&h->RES, Bc * N * E * 4}, {&h->RESE, Bc * M * E * 4},
-      {&h->OUTN, Bc * c.seq_out * N * 4 * 4}, {&h->OUTE, Bc * c.seq_out * M * 4 * 4}, {&h->SS, RM * 4}, {&h->SN, RM * 4},
+      {&h->BEMB, Bc * c.seq_out * Nw * E2 * a}, {&h->AEMB, Bc * c.seq_out * Mw * E2 * a},
+      {&h->RES, Bc * Nw * E * 4}, {&h->RESE, Bc * Mw * E * 4},
+      {&h->OUTN, Bc * c.seq_out * N * 4 * 4}, {&h->OUTE, Bc * c.seq_out * M * 4 * 4}, {&h->SS, RS * 4}, {&h->SN, RS * 4},
       {&h->in_x, Bc * c.seq_in * N * c.n_in * 4}, {&h->in_b, Bc * c.seq_out * N * c.b_in * 4},
       {&h->in_a, Bc * c.seq_out * std::max(c.n_act, 1) * 4}, {&h->in_ex, Bc * c.seq_in * M * c.e_in * 4},
       {&h->out_y, Bc * c.seq_out * N * 5 * 4}, {&h->out_ey, Bc * c.seq_out * M * 4 * 4},
@@ -1401,8 +1557,10 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   if (!cfg || !out) return fail(nullptr, GNNUDS_E_INVALID, "null argument");
   if (cfg->abi_version != GNNUDS_ABI_VERSION) return fail(nullptr, GNNUDS_E_INVALID, "ABI version mismatch (%d vs %d)", cfg->abi_version, GNNUDS_ABI_VERSION);
   const gnnuds_config& c = *cfg;
-  if (c.conv != GNNUDS_CONV_GCN && c.conv != GNNUDS_CONV_GAT)
-    return fail(nullptr, GNNUDS_E_INVALID, "conv kind %d unsupported (GCN/GAT only; NN-cat/Diffusion/General are not on the CUDA path)", c.conv);
+  if (c.conv != GNNUDS_CONV_GCN && c.conv != GNNUDS_CONV_GAT && c.conv != GNNUDS_CONV_NONE)
+    return fail(nullptr, GNNUDS_E_INVALID, "conv kind %d unsupported (NN-cat/GCN/GAT only; Diffusion/General are not on the CUDA path)", c.conv);
+  if (c.conv == GNNUDS_CONV_NONE && (c.n_node < 2 || c.n_edge < 2 || c.graph_base))
+    return fail(nullptr, GNNUDS_E_INVALID, "NN-cat needs n_node, n_edge >= 2 and graph_base == 0 (graph_base is ignored without conv, emulator.py:221)");
   if (c.recurrent < GNNUDS_REC_CONV1D || c.recurrent > GNNUDS_REC_LSTM) return fail(nullptr, GNNUDS_E_INVALID, "recurrent kind %d unsupported", c.recurrent);
   if (c.embed % 32 || c.embed < 32 || c.embed > 256) return fail(nullptr, GNNUDS_E_INVALID, "embed_size %d must be a multiple of 32 in [32,256]", c.embed);
   if (c.hidden % 16 || c.hidden > 128 || (c.recurrent != GNNUDS_REC_CONV1D && (c.hidden * 3) % 64)) return fail(nullptr, GNNUDS_E_INVALID, "hidden_dim %d unsupported", c.hidden);
@@ -1421,6 +1579,9 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   if (c.device < 0 || c.device >= ndev) return fail(nullptr, GNNUDS_E_INVALID, "device %d out of range (%d devices)", c.device, ndev);
   h = new gnnuds_handle();
   h->c = c;
+  // NN-cat is a chain of small row GEMMs over Bc*T rows (no per-node rows): it runs on the fp32 SIMT kernels whatever
+  // precision was asked for
+  if (c.conv == GNNUDS_CONV_NONE) h->c.precision = GNNUDS_PREC_FP32;
   if (cudaSetDevice(c.device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) {
     g_create_error = "cudaSetDevice/cudaStreamCreate failed";
     delete h;
@@ -1687,8 +1848,37 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
     if ((rc = upload(h, &d, all.data(), all.size()))) return rc;
     h->d_wimg = reinterpret_cast<uint8_t*>(d);
   }
+  if (h->nn()) {
+    // zero-padded copies: flattened input widths (K) and flattened head widths (Nout) rounded up to 16
+    std::vector<float> pad;
+    const int N = c.n_node, M = c.n_edge, E = c.embed;
+    auto r16 = [](int v) { return (v + 15) / 16 * 16; };
+    auto padK = [&](const LayerW& l, int K, int Nout, gnnuds_handle::NnPad& q) {
+      q.K = K; q.Kp = r16(K); q.No = q.Nop = Nout; q.w = (long long)pad.size(); q.b = -1;
+      pad.insert(pad.end(), blob + offsets[l.t[0]], blob + offsets[l.t[0]] + (size_t)K * Nout);
+      pad.resize(pad.size() + (size_t)(q.Kp - K) * Nout, 0.f);
+    };
+    auto padN = [&](const LayerW& l, int K, int Nout, gnnuds_handle::NnPad& q) {
+      q.K = q.Kp = K; q.No = Nout; q.Nop = r16(Nout); q.w = (long long)pad.size();
+      for (int k = 0; k < K; ++k) {
+        pad.insert(pad.end(), blob + offsets[l.t[0]] + (size_t)k * Nout, blob + offsets[l.t[0]] + (size_t)(k + 1) * Nout);
+        pad.resize(pad.size() + (size_t)(q.Nop - Nout), 0.f);
+      }
+      q.b = (long long)pad.size();
+      pad.insert(pad.end(), blob + offsets[l.t[1]], blob + offsets[l.t[1]] + Nout);
+      pad.resize(pad.size() + (size_t)(q.Nop - Nout), 0.f);
+    };
+    padK(h->emb_x, N * c.n_in, E, h->nnp_x);
+    padK(h->emb_b, N * c.b_in, E / 2, h->nnp_b);
+    padK(h->emb_e, M * c.e_in, E, h->nnp_e);
+    if (c.act) padK(h->emb_a, M, E / 2, h->nnp_a);
+    padN(h->head_out, E, c.n_out * N, h->nnp_out);
+    if (c.if_flood) padN(h->head_flood, E / 2, N, h->nnp_flood);
+    padN(h->head_e, E, c.e_out * M, h->nnp_eout);
+    if ((rc = upload(h, &h->d_nnpad, pad.data(), pad.size()))) return rc;
+  }
   // fold NodeEdge: mat = w * |inci| + b  (emulator.py:43), stored transposed + zero padded
-  if (!c.graph_base) {
+  if (!c.graph_base && !h->nn()) {
     const int N = c.n_node, M = c.n_edge, F = c.embed / 2;
     const int IG = 256 / (F / 4);
     auto ti_for = [&](int r_out) { int t = (r_out + IG - 1) / IG; t = (t + 3) / 4 * 4; return t; };
@@ -1794,7 +1984,15 @@ int gnnuds_predict(gnnuds_handle* h, const float* x, const float* b, const float
   if (c.act && !a) return fail(h, GNNUDS_E_INVALID, "act model needs settings `a`");
   CU(cudaSetDevice(c.device));
   if (B == 0) return 0;
-  const int64_t Bc = pick_chunk(h, B);
+  int64_t Bc = pick_chunk(h, B);
+  if (where == GNNUDS_MEM_HOST && c.max_chunk <= 0 && h->nn()) {
+    // host buffers, NN-cat: the copies take longer than the compute and only overlap it across chunks, so prefer ~8
+    // chunks as long as one chunk still fills the machine (>= 4 waves of 128-row tiles).  The conv models are
+    // compute-dominated and lose more to short launches than the overlap returns (C3b: 118 -> 101 M/s when split).
+    const int64_t rows_per_sc = (int64_t)std::max(c.seq_in, c.seq_out);
+    const int64_t fill = ((int64_t)h->sm_count * 128 * 4 + rows_per_sc - 1) / rows_per_sc;
+    Bc = std::min(Bc, std::max((B + 7) / 8, fill));
+  }
   if ((rc = ensure_workspace(h, Bc))) return rc;
   const int N = c.n_node, M = c.n_edge, Ti = c.seq_in, To = c.seq_out;
   const int64_t sx = (int64_t)Ti * N * c.n_in, sb = (int64_t)To * N * c.b_in, sa = (int64_t)To * c.n_act,

@@ -112,8 +112,9 @@ class Emulator:
             raise NotImplementedError("pumps / inlet offsets with graph_base != 0 are not on the CUDA path")
         self.conv = False if conv in ["None", "False", "NoneType", None, False] else conv
         if not self.conv:
-            raise NotImplementedError("NN-cat (conv=False, emulator.py:231-233) is a 'next' row; not on the CUDA path yet")
-        if "GCN" in self.conv:
+            self.conv_kind = "nn"          # NN-cat: flattened Dense stacks (emulator.py:180,231-233); graph_base unused
+            self.graph_base = 0
+        elif "GCN" in self.conv:
             self.conv_kind = "gcn"
         elif "GAT" in self.conv:
             self.conv_kind = "gat"
@@ -158,7 +159,7 @@ class Emulator:
         cfg.seq_in, cfg.seq_out = self.seq_in, self.seq_out
         cfg.embed, cfg.hidden, cfg.kernel_size = self.embed_size, self.hidden_dim, self.kernel_size
         cfg.n_sp_layer, cfg.n_tp_layer = self.n_sp_layer, self.n_tp_layer
-        cfg.conv = _lib.CONV_GCN if self.conv_kind == "gcn" else _lib.CONV_GAT
+        cfg.conv = {"nn": _lib.CONV_NONE, "gcn": _lib.CONV_GCN, "gat": _lib.CONV_GAT}[self.conv_kind]
         cfg.recurrent = {"Conv1D": _lib.REC_CONV1D, "GRU": _lib.REC_GRU, "LSTM": _lib.REC_LSTM}[recurrent]
         cfg.activation = _lib.ACT[self.activation]
         cfg.resnet, cfg.if_flood, cfg.edge_fusion = int(self.resnet), self.if_flood, int(self.edge_fusion)

@@ -62,6 +62,34 @@ def layer_specs(cfg):
                 conv(ce + E // 2, tag + "conv_e")
             cx = ce = E
 
+    if getattr(cfg, "conv_kind", None) == "nn":
+        # NN-cat (emulator.py:180,197-211,231-233,284-286,322-337): node / edge features flattened per time step
+        dense(N * cfg.n_in, E, "embed_x")
+        dense(N * cfg.b_in, E // 2, "embed_b")
+        dense(M * cfg.e_in, E, "embed_e")
+        if cfg.act:
+            dense(M, E // 2, "embed_a")
+        for l in range(S):
+            dense(2 * E, 2 * E, "sp1.%d.cat" % l)
+        temporal(E, "tp1.x")
+        temporal(E, "tp1.e")
+        c = 2 * H + E // 2 + (E // 2 if cfg.act else 0)
+        for l in range(S):
+            dense(c, 2 * E, "sp2.%d.cat" % l)
+            c = 2 * E
+        temporal(E, "tp2.x")
+        temporal(E, "tp2.e")
+        dense(H, E, "res_x", fixed="dense_resx")
+        dense(H, E, "res_e")
+        dense(E, cfg.n_out * N, "out")
+        if cfg.if_flood:
+            c = E
+            for i in range(cfg.if_flood):
+                dense(c, E // 2, "flood%d" % i)
+                c = E // 2
+            dense(c, N, "flood_out")
+        dense(E, cfg.e_out * M, "e_out")
+        return out
     dense(cfg.n_in, E, "embed_x")
     dense(cfg.b_in, E // 2, "embed_b")
     dense(cfg.e_in, E, "embed_e")

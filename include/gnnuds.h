@@ -32,7 +32,7 @@ enum {
   GNNUDS_E_NOMEM = -4
 };
 
-enum { GNNUDS_CONV_GCN = 1, GNNUDS_CONV_GAT = 2 };                 /* emulator.py:129-152 */
+enum { GNNUDS_CONV_NONE = 0 /* NN-cat: conv falsy, emulator.py:180,231-233 */, GNNUDS_CONV_GCN = 1, GNNUDS_CONV_GAT = 2 };  /* emulator.py:129-152 */
 enum { GNNUDS_REC_CONV1D = 1, GNNUDS_REC_GRU = 2, GNNUDS_REC_LSTM = 3 }; /* emulator.py:154-163 */
 enum { GNNUDS_ACT_LINEAR = 0, GNNUDS_ACT_RELU = 1, GNNUDS_ACT_TANH = 2, GNNUDS_ACT_SIGMOID = 3 };
 enum { GNNUDS_PREC_FP32 = 0,    /* fp32 SIMT, parity mode (<=1e-5 rel per step) */

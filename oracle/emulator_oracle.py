@@ -127,7 +127,7 @@ def lstm(x, K, R, b):
 # the Emulator
 # ----------------------------------------------------------------------------
 class OracleEmulator:
-    """Forward-only restatement of emulator.py:47-852 (conv variants)."""
+    """Forward-only restatement of emulator.py:47-852 (GCN / GAT and the no-conv NN-cat variant)."""
 
     def __init__(self, conv=None, resnet=False, recurrent=None, args=None, dtype=np.float32):
         g = lambda k, d=None: getattr(args, k, d)
@@ -174,9 +174,10 @@ class OracleEmulator:
         self.resnet = resnet
         self.recurrent = recurrent
         self.roll = g("roll", 0)
-        if not self.conv:
-            raise NotImplementedError("oracle: NN-cat (conv=False) variant is a 'next' row (SURVEY 8f.1)")
-        self._set_filters()
+        if self.conv:
+            self._set_filters()
+        else:
+            self.kind = "nn"       # NN-cat: flattened (N*C) Dense stacks, emulator.py:180,197-211,231-233
         self.spec = self.build_spec()
         self.weights = None
         self.trace = None          # set to {} to record per-stage activations of the next model() call
@@ -220,6 +221,8 @@ class OracleEmulator:
         """Creation order of weighted layers in build_network (emulator.py:195-336)."""
         E, H, S = self.embed_size, self.hidden_dim, self.n_sp_layer
         N, M = self.n_node, self.n_edge
+        if not self.conv:
+            return self._build_spec_nn()
         sp = [("dense", [(self.n_in, E), (E,)]),             # :198
               ("dense", [(self.b_in, E // 2), (E // 2,)]),   # :203
               ("dense", [(self.e_in, E), (E,)])]             # :206
@@ -257,6 +260,37 @@ class OracleEmulator:
         sp.append(("dense", [(E, self.e_out), (self.e_out,)]))   # :336
         return sp
 
+    def _build_spec_nn(self):
+        """NN-cat creation order (emulator.py:195-336 with conv falsy): node / edge features flattened per time step."""
+        E, H, S = self.embed_size, self.hidden_dim, self.n_sp_layer
+        N, M = self.n_node, self.n_edge
+        sp = [("dense", [(N * self.n_in, E), (E,)]),         # :197-198
+              ("dense", [(N * self.b_in, E // 2), (E // 2,)]),   # :202-203
+              ("dense", [(M * self.e_in, E), (E,)])]         # :205-206
+        if self.act:
+            sp.append(("dense", [(M, E // 2), (E // 2,)]))   # :211-212
+        for _ in range(S):
+            sp.append(("dense", [(2 * E, 2 * E), (2 * E,)]))     # :232
+        sp += self._tem_shapes(E)                            # :247
+        sp += self._tem_shapes(E)                            # :254
+        c = 2 * H + E // 2 + (E // 2 if self.act else 0)
+        for _ in range(S):
+            sp.append(("dense", [(c, 2 * E), (2 * E,)]))     # :285
+            c = 2 * E
+        sp += self._tem_shapes(E)                            # :302
+        sp += self._tem_shapes(E)                            # :308
+        sp.append(("dense_resx", [(H, E), (E,)]))            # :313
+        sp.append(("dense", [(H, E), (E,)]))                 # :317
+        sp.append(("dense", [(E, self.n_out * N), (self.n_out * N,)]))   # :322-324
+        if self.if_flood:
+            c = E
+            for _ in range(self.if_flood):
+                sp.append(("dense", [(c, E // 2), (E // 2,)]))   # :329
+                c = E // 2
+            sp.append(("dense", [(c, N), (N,)]))             # :327,330
+        sp.append(("dense", [(E, self.e_out * M), (self.e_out * M,)]))   # :335-336
+        return sp
+
     def set_weights(self, weights):
         assert len(weights) == len(self.spec), (len(weights), len(self.spec))
         out = []
@@ -288,6 +322,8 @@ class OracleEmulator:
         """The Keras graph of build_network (emulator.py:195-340), normalised inputs."""
         dt = self.dtype
         X, Bn, E_in = [np.asarray(v, dtype=dt) for v in (X, Bn, E_in)]
+        if not self.conv:
+            return self._model_nn(X, Bn, E_in, AE)
         it = iter(self.weights)
         actv = act_fn(self.activation)
         N, M, Ti, To, H = self.n_node, self.n_edge, self.seq_in, self.seq_out, self.hidden_dim
@@ -360,6 +396,58 @@ class OracleEmulator:
             w = next(it); flood = dense(x, w[0], w[1], "sigmoid")
             out = np.concatenate([out, flood], axis=-1)
         w = next(it); e_o = dense(e, w[0], w[1], "tanh")
+        assert next(it, None) is None
+        return out, e_o
+
+    def _model_nn(self, X, Bn, E_in, AE=None):
+        """NN-cat graph (emulator.py:195-340 with conv falsy): (B,T,N*C) rows through Dense / temporal stacks."""
+        dt = self.dtype
+        it = iter(self.weights)
+        actv = act_fn(self.activation)
+        N, M, To = self.n_node, self.n_edge, self.seq_out
+        B = X.shape[0]
+        flat = lambda v: v.reshape(v.shape[0], v.shape[1], -1)
+        w = next(it); x = dense(flat(X), w[0], w[1], "linear")
+        res = x[:, -1:, :]
+        x = actv(x)
+        w = next(it); b = dense(flat(Bn), w[0], w[1], self.activation)
+        w = next(it); e = dense(flat(E_in), w[0], w[1], "linear")
+        res_e = e[:, -1:, :]
+        e = actv(e)
+        if self.act:
+            w = next(it); ae = dense(flat(np.asarray(AE, dtype=dt)), w[0], w[1], self.activation)
+        tr = self.trace if self.trace is not None else {}
+
+        def spatial(x, e):
+            for _ in range(self.n_sp_layer):
+                w = next(it); z = dense(np.concatenate([x, e], axis=-1), w[0], w[1], self.activation)   # :232
+                x, e = np.split(z, 2, axis=-1)                                                         # :233
+            return x, e
+
+        x, e = spatial(x, e)
+        tr["sp1"] = (x.copy(), e.copy())
+        x = self._temporal(x, it)[:, -To:, :]
+        e = self._temporal(e, it)[:, -To:, :]
+        x = np.concatenate([x, b], axis=-1)
+        if self.act:
+            e = np.concatenate([e, ae], axis=-1)
+        x, e = spatial(x, e)
+        tr["sp2"] = (x.copy(), e.copy())
+        x = self._temporal(x, it)
+        e = self._temporal(e, it)
+        tr["tp2"] = (x.copy(), e.copy())
+        w = next(it); x_out = dense(x, w[0], w[1], "linear")
+        x = actv(np.cumsum(x_out, axis=1, dtype=dt) + res) if self.resnet else actv(x_out)
+        w = next(it); e_out = dense(e, w[0], w[1], "linear")
+        e = actv(np.cumsum(e_out, axis=1, dtype=dt) + res_e) if self.resnet else actv(e_out)
+        tr["res"] = (x.copy(), e.copy())
+        w = next(it); out = dense(x, w[0], w[1], "hard_sigmoid").reshape(B, To, N, self.n_out)   # :324-325
+        if self.if_flood:
+            for _ in range(self.if_flood):
+                w = next(it); x = dense(x, w[0], w[1], self.activation)
+            w = next(it); flood = dense(x, w[0], w[1], "sigmoid").reshape(B, To, N, 1)
+            out = np.concatenate([out, flood], axis=-1)
+        w = next(it); e_o = dense(e, w[0], w[1], "tanh").reshape(B, To, M, self.e_out)          # :336-337
         assert next(it, None) is None
         return out, e_o
 

@@ -58,10 +58,16 @@ CASES = {
     "ast_pump_act_nofusion": dict(net="astlingen", conv="GCN", recurrent="GRU", resnet=False, seq_in=5, seq_out=5,
                                   embed_size=128, hidden_dim=64, n_sp_layer=1, n_tp_layer=1, length=0, order=1,
                                   act="conti", pumps=True, B=3, seed=52),
+    # NN-cat (conv falsy, emulator.py:180,231-233: flattened Dense stacks; 25 of the 86 saved model configs)
+    "ast_nn_conv_act_fusion": dict(net="astlingen", conv="False", recurrent="Conv1D", resnet=True, seq_in=6, seq_out=6,
+                                   embed_size=128, hidden_dim=64, n_sp_layer=3, n_tp_layer=3, length=0, order=1,
+                                   edge_fusion=True, if_flood=2, act="conti", B=5, seed=53),
+    "shq_nn_gru": dict(net="shunqing", conv=None, recurrent="GRU", resnet=False, seq_in=8, seq_out=4,
+                       embed_size=64, hidden_dim=64, n_sp_layer=2, n_tp_layer=2, length=0, order=1, B=3, seed=54),
 }
 GOLDEN_CASES = ["c1_ast_gcn_gru", "c2_shq_gat_conv_10", "c3_ast_act_5", "ast_gat_gru_noflood",
                 "ast_gcn_lstm_act_nofusion", "ast_gcn_conv_eps0", "ast_joint_gcn_gru_act", "ast_joint_gat_conv_act",
-                "ast_pump_act_fusion", "ast_pump_act_nofusion"]
+                "ast_pump_act_fusion", "ast_pump_act_nofusion", "ast_nn_conv_act_fusion", "shq_nn_gru"]
 
 
 def load_net(name):
