@@ -290,6 +290,41 @@ def joint_adjacency(net, directed=False, length=0, order=1):
     return CSR(n, _traverse(G, n, length, order, l_std, symmetric=(not directed) and not length))
 
 
+def edge_based_adjacency(net, directed=False, length=0, order=1):
+    """base.py:500-532 get_edge_based_adj (graph_base=2): line graph of the links (ids n_node+i) plus a tie from every
+    link to its end nodes; one-way fill (the reference does not mirror these rows)."""
+    n_node, n_edge = int(net.edges.max()) + 1, net.n_edge
+    l_std = np.std(net.lengths) if length else 0.0
+    X = _AdjList(directed)
+    for i, (u, v) in enumerate(net.edges):
+        X.add_edge(int(u), int(v), edge=n_node + i, length=float(net.lengths[i]) if length else 0)
+    EX = _AdjList(directed)
+
+    def tie(a, b, l):
+        if length:
+            EX.add_edge(a, b, length=l)
+        else:
+            EX.add_edge(a, b)
+    for n in list(X.adj):
+        if directed:
+            for a in X.pred[n]:
+                for d in X.adj[n]:
+                    u, v = X.adj[a][n], X.adj[n][d]
+                    tie(u["edge"], v["edge"], (u["length"] + v["length"]) / 2)
+            for a in X.pred[n]:
+                tie(X.adj[a][n]["edge"], n, X.adj[a][n]["length"] / 2)
+            for d in X.adj[n]:
+                tie(n, X.adj[n][d]["edge"], X.adj[n][d]["length"] / 2)
+        else:
+            for b, d in combinations(list(X.adj[n]), 2):
+                u, v = X.adj[n][b], X.adj[n][d]
+                tie(u["edge"], v["edge"], (u["length"] + v["length"]) / 2)
+            for b in list(X.adj[n]):
+                tie(X.adj[n][b]["edge"], n, X.adj[n][b]["length"] / 2)
+    n = n_node + n_edge
+    return CSR(n, _traverse(EX, n, length, order, l_std, symmetric=False))
+
+
 def gcn_normalise(csr):
     """spektral.utils.gcn_filter on CSR: D^-1/2 (A + I) D^-1/2, D = rowsum(A + I).
     The reference's A already carries 1 on the diagonal, so the diagonal becomes 2."""
@@ -351,7 +386,7 @@ def get_args(inp_path, directed=False, length=0, order=1, graph_base=0,
     if graph_base == 1:
         a.adj_csr = joint_adjacency(net, directed, length, order)
     elif graph_base == 2:
-        raise NotImplementedError("graph_base=2 (base.py:500-) is not on the hot path yet")
+        a.adj_csr = edge_based_adjacency(net, directed, length, order)
     else:
         a.adj_csr = node_adjacency(net, directed, length, order)
     a.edge_adj_csr = edge_adjacency(net, directed, length, order)

@@ -206,6 +206,42 @@ def get_node_based_adj(edges, lengths=None, directed=False, length=0, order=1):
     return adj
 
 
+def get_edge_based_adj(edges, lengths=None, directed=False, length=0, order=1):
+    """base.py:500-532 (graph_base=2): the line graph of the links (ids n_node+i), every link also tied to its end
+    nodes; rows are filled one way only (no symmetric mirror, unlike get_node_based_adj)."""
+    n_node, n_edge = int(edges.max()) + 1, edges.shape[0]
+    l_std = np.std(lengths) if length else 0.0
+    X = nx.DiGraph() if directed else nx.Graph()
+    for i, (u, v) in enumerate(edges):
+        X.add_edge(int(u), int(v), edge=n_node + i, length=lengths[i] if length else 0)
+    EX = nx.DiGraph() if directed else nx.Graph()
+    half = lambda d: d["length"] / 2 if length else 0
+    for n in X.nodes():
+        if directed:
+            pairs = [(X[a][b], X[c][d]) for (a, b) in X.in_edges(n) for (c, d) in X.out_edges(n)]
+        else:
+            pairs = [(X[a][b], X[c][d]) for (a, b), (c, d) in combinations(X.edges(n), 2)]
+        for u, v in pairs:
+            EX.add_edge(u["edge"], v["edge"], length=(u["length"] + v["length"]) / 2 if length else 0)
+        if directed:
+            for a, b in X.in_edges(n):
+                EX.add_edge(X[a][b]["edge"], n, length=half(X[a][b]))
+            for c, d in X.out_edges(n):
+                EX.add_edge(n, X[c][d]["edge"], length=half(X[c][d]))
+        else:
+            for a, b in X.edges(n):
+                EX.add_edge(X[a][b]["edge"], n, length=half(X[a][b]))
+    adj = np.zeros((n_node + n_edge, n_node + n_edge))
+    for n in range(n_node + n_edge):
+        if length:
+            for a, l in nx.single_source_dijkstra_path_length(EX, n, weight="length", cutoff=length).items():
+                adj[n, a] = np.exp(-(l / (l_std + 1e-5)) ** 2)
+        else:
+            for a in (list(nx.dfs_preorder_nodes(EX, n, order)) if order > 0 else [n]):
+                adj[n, a] = 1
+    return adj
+
+
 def get_args(path, directed=False, length=0, order=1, graph_base=0, act_links=None, head=False):
     """Restates base.py:277-332 (+ astlingen.py:136-150 for area/act_edges)."""
     net = parse_network(path)
@@ -220,7 +256,7 @@ def get_args(path, directed=False, length=0, order=1, graph_base=0, act_links=No
     if graph_base == 1:
         args["adj"] = get_node_based_adj(net["edges"], L, directed, length, order)
     elif graph_base == 2:
-        raise NotImplementedError("graph_base=2 (base.py:500-) is outside the hot-path scope")
+        args["adj"] = get_edge_based_adj(net["edges"], L, directed, length, order)
     else:
         args["adj"] = get_adj(net["edges"], L, directed, length, order)
     args["edge_adj"] = get_edge_adj(net["edges"], L, directed, length, order)

@@ -58,6 +58,10 @@ CASES = {
     "ast_pump_act_nofusion": dict(net="astlingen", conv="GCN", recurrent="GRU", resnet=False, seq_in=5, seq_out=5,
                                   embed_size=128, hidden_dim=64, n_sp_layer=1, n_tp_layer=1, length=0, order=1,
                                   act="conti", pumps=True, B=3, seed=52),
+    # graph_base=2: the same joint conv over the link-based graph of base.py:500-532 (asymmetric rows, order 2)
+    "ast_edgebased_gcn_lstm_act": dict(net="astlingen", conv="GCN", recurrent="LSTM", resnet=True, seq_in=4, seq_out=4,
+                                       embed_size=64, hidden_dim=64, n_sp_layer=2, n_tp_layer=1, length=0, order=2,
+                                       graph_base=2, act="conti", edge_fusion=True, if_flood=1, B=2, seed=55),
     # NN-cat (conv falsy, emulator.py:180,231-233: flattened Dense stacks; 25 of the 86 saved model configs)
     "ast_nn_conv_act_fusion": dict(net="astlingen", conv="False", recurrent="Conv1D", resnet=True, seq_in=6, seq_out=6,
                                    embed_size=128, hidden_dim=64, n_sp_layer=3, n_tp_layer=3, length=0, order=1,
@@ -67,7 +71,8 @@ CASES = {
 }
 GOLDEN_CASES = ["c1_ast_gcn_gru", "c2_shq_gat_conv_10", "c3_ast_act_5", "ast_gat_gru_noflood",
                 "ast_gcn_lstm_act_nofusion", "ast_gcn_conv_eps0", "ast_joint_gcn_gru_act", "ast_joint_gat_conv_act",
-                "ast_pump_act_fusion", "ast_pump_act_nofusion", "ast_nn_conv_act_fusion", "shq_nn_gru"]
+                "ast_pump_act_fusion", "ast_pump_act_nofusion", "ast_nn_conv_act_fusion", "shq_nn_gru",
+                "ast_edgebased_gcn_lstm_act"]
 
 
 def load_net(name):

@@ -48,7 +48,29 @@ def test_live_oracle_dense_equals_csr():
         assert np.array_equal(G.node_adjacency(net, directed, length, order).to_dense(), go.get_adj(net.edges, L, directed, length, order))
         assert np.array_equal(G.edge_adjacency(net, directed, length, order).to_dense(), go.get_edge_adj(net.edges, L, directed, length, order))
         assert np.array_equal(G.joint_adjacency(net, directed, length, order).to_dense(), go.get_node_based_adj(net.edges, L, directed, length, order))
+        assert np.array_equal(G.edge_based_adjacency(net, directed, length, order).to_dense(), go.get_edge_based_adj(net.edges, L, directed, length, order))
     assert np.array_equal(G.incidence(net), go.get_node_edge(net.n_node, net.edges))
+
+
+def test_edge_based_adjacency_known_answer():
+    """graph_base=2 (base.py:500-532) on the path 0-1-2: links get the ids 3 and 4, are tied to each other through
+    node 1 and to their end nodes; order=1 rows are {self} + neighbours."""
+    from oracle import graph_oracle as go
+    edges = np.array([[0, 1], [1, 2]])
+    want = np.zeros((5, 5))
+    for r, cols in {0: [0, 3], 1: [1, 3, 4], 2: [2, 4], 3: [3, 0, 1, 4], 4: [4, 1, 2, 3]}.items():
+        want[r, cols] = 1
+    assert np.array_equal(go.get_edge_based_adj(edges), want)
+    net = G.Network(["a", "b", "c"], ["l0", "l1"], edges, np.array([10.0, 30.0]), np.zeros(3), np.zeros(3), np.ones(3),
+                    np.zeros(3), np.ones(2), np.zeros(3))
+    assert np.array_equal(G.edge_based_adjacency(net).to_dense(), want)
+    # order=0: identity; length mode: exp(-(l/std)^2) of half-length ties (l0-a: 5, l0-l1: 20, l1-b: 15)
+    assert np.array_equal(G.edge_based_adjacency(net, order=0).to_dense(), np.eye(5))
+    d = G.edge_based_adjacency(net, length=16.0).to_dense()
+    std = np.std([10.0, 30.0])
+    assert np.isclose(d[3, 0], np.exp(-(5.0 / (std + 1e-5)) ** 2)) and np.isclose(d[4, 1], np.exp(-(15.0 / (std + 1e-5)) ** 2))
+    assert d[3, 4] == 0 and d[0, 1] == np.exp(-(10.0 / (std + 1e-5)) ** 2)      # l0-l1 is 20 > cutoff; a-l0-b is 5+5
+    assert np.array_equal(d, go.get_edge_based_adj(edges, np.array([10.0, 30.0]), False, 16.0, 1))
 
 
 def test_gcn_filter_and_gat_pattern():
