@@ -24,6 +24,10 @@ WORKLOADS = {
     "C2nn": dict(net="shunqing", conv="False", recurrent="Conv1D", resnet=True, seq_in=60, seq_out=60, embed_size=128,
                  hidden_dim=64, n_sp_layer=3, n_tp_layer=3, length=1200.0, order=1, edge_fusion=True, if_flood=3,
                  B=4096, seed=43),
+    # LSTM twin of C2 (6 of the saved model configs use recurrent: LSTM)
+    "C2lstm": dict(net="shunqing", conv="GAT", recurrent="LSTM", resnet=True, seq_in=60, seq_out=60, embed_size=128,
+                   hidden_dim=64, n_sp_layer=3, n_tp_layer=3, length=1200.0, order=1, edge_fusion=True, if_flood=3,
+                   B=1024, seed=43),
     # configs[2]: astlingen act+edge_fusion+flood MPC evaluator; (a) 60->60 5 layers, (b) 12 AR chunks of 5->5
     "C3a": dict(net="astlingen", conv="GAT", recurrent="Conv1D", resnet=True, seq_in=60, seq_out=60, embed_size=128,
                 hidden_dim=64, n_sp_layer=5, n_tp_layer=5, length=1.0, order=1, edge_fusion=True, if_flood=5,

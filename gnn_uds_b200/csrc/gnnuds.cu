@@ -1043,6 +1043,17 @@ int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& 
         { int prc = prof_begin(h, GNNUDS_FAM_RECURRENT, &e1); if (prc) return prc; }
         gru_kernel<bf16><<<g, 256, smem, h->stream>>>(p);
         { int prc = prof_end(h, e1); if (prc) return prc; }
+      } else if (h->gru_tc && H == 64 && h->img_off[L[i].t[1]] >= 0) {
+        // LSTM recurrence on tensor cores (csrc/gru_tc.cuh, lstm_tc_kernel): N = 4H accumulator columns
+        LstmTcP p{reinterpret_cast<const bf16*>(h->HB), h->d_wimg + h->img_off[L[i].t[1]], reinterpret_cast<bf16*>(o), nseq, Nn, Ts,
+                  Tdst, H, (unsigned)((nseq + 127) / 128)};
+        const size_t smem = 2 * (size_t)H * G * 2 + 2 * 128 * H * 2 + 64;
+        static bool attr_set = false;
+        if (!attr_set) { CU(cudaFuncSetAttribute(lstm_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
+        cudaEvent_t e1 = nullptr;
+        { int prc = prof_begin(h, GNNUDS_FAM_RECURRENT, &e1); if (prc) return prc; }
+        lstm_tc_kernel<64><<<std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count), GRU_THREADS, smem, h->stream>>>(p);
+        { int prc = prof_end(h, e1); if (prc) return prc; }
       } else {
         LstmP p{h->HB, W(h, L[i].t[1]), o, nseq, Nn, Ts, Tdst, H};
         const size_t smem = ((size_t)H * G + 64 * H + 32 * G) * sizeof(float);
@@ -1817,8 +1828,8 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
       for (const SpatialW& w : h->sp[blk]) {
         if (c.graph_base) add(w.joint); else { add(w.xe); add(w.ex); add(w.conv_x); add(w.conv_e); }
       }
-      for (const LayerW& l : h->tpx[blk]) { add(l); if (c.recurrent == GNNUDS_REC_GRU) { ids.push_back(l.t[1]); rec_ids.insert(l.t[1]); } }   // + recurrent kernel R
-      for (const LayerW& l : h->tpe[blk]) { add(l); if (c.recurrent == GNNUDS_REC_GRU) { ids.push_back(l.t[1]); rec_ids.insert(l.t[1]); } }
+      for (const LayerW& l : h->tpx[blk]) { add(l); if (c.recurrent != GNNUDS_REC_CONV1D) { ids.push_back(l.t[1]); rec_ids.insert(l.t[1]); } }   // + recurrent kernel R
+      for (const LayerW& l : h->tpe[blk]) { add(l); if (c.recurrent != GNNUDS_REC_CONV1D) { ids.push_back(l.t[1]); rec_ids.insert(l.t[1]); } }
     }
     add(h->resx); add(h->rese);
     for (const LayerW& l : h->flood_chain) add(l);
@@ -1832,7 +1843,7 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
       while (all.size() % 64) all.push_back(0);
       h->img_off[t] = (long long)all.size() * 2;
       all.insert(all.end(), img.begin(), img.end());
-      if (c.recurrent == GNNUDS_REC_GRU && rec_ids.count(t)) {
+      if (rec_ids.count(t)) {
         // recurrent kernel R: a second image of the bf16 residual R - bf16(R) right behind the first (csrc/gru_tc.cuh)
         std::vector<float> lo((size_t)Nout * Ktot);
         for (size_t i = 0; i < lo.size(); ++i) {

@@ -180,4 +180,157 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) gru_tc_kernel(const __grid_con
   if (warp == 0) tc::tmem_free(tmem, 256);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// LSTM recurrence on tensor cores: keras LSTM v2, gate order i,f,c,o (emulator.py:160-161)
+//   z_t = mx_t + h_{t-1} @ R     (mx = x_t @ K + b from tc_rows_kernel, 4H wide; R^T resident as hi + residual images)
+//   i,f,o = sigmoid(z_i,z_f,z_o)   c_t = f*c_{t-1} + i*tanh(z_c)   h_t = o*tanh(c_t)
+// Same roles and barriers as gru_tc_kernel; N = 4H = 256 accumulator columns, fp32 cell and hidden state in
+// registers, the hidden state enters the MMA as hi + lo 16-bit operands.  8 units per accumulator read to stay
+// inside the register budget (4 gates x 8 columns live).
+struct LstmTcP {
+  const bf16* mx;        // (Bc, Ts, Nn, 4H)
+  const uint8_t* Rimg;   // two K-major images of R^T (high part, residual), as GruTcP::Rimg with G = 4H
+  bf16* out;             // (Bc, Td, Nn, H)
+  long long nseq;
+  int Nn, Ts, Td, H;
+  unsigned n_tiles;
+};
+
+__device__ __forceinline__ float fast_sigmoid(float v) { return __fdividef(1.f, 1.f + __expf(-v)); }
+__device__ __forceinline__ float fast_tanh(float v) {
+  const float e2 = __expf(-2.f * fabsf(v));
+  return copysignf(__fdividef(1.f - e2, 1.f + e2), v);
+}
+
+template <int H>
+__global__ void __launch_bounds__(GRU_THREADS, 1) lstm_tc_kernel(const __grid_constant__ LstmTcP p) {
+  constexpr int G = 4 * H, HH = H / 4;
+  constexpr uint32_t R_BYTES = (uint32_t)H * G * 2u;
+  constexpr uint32_t A_BYTES = 128u * H * 2u;
+  constexpr uint32_t PSTRIDE_A = 128u * 16u, PSTRIDE_W = (uint32_t)G * 16u;
+  static_assert(H % 64 == 0 && G <= 256, "hidden size must be a multiple of 64 with 4H <= 256");
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* Rs = smem;
+  uint8_t* As = smem + 2 * R_BYTES;
+  uint8_t* Al = As + A_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(Al + A_BYTES);
+  uint64_t* h_ready = bars;
+  uint64_t* mma_done = bars + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
+  if (tid == 32) {
+    tc::mbar_init(h_ready, GRU_GATE_WARPS * 32);
+    tc::mbar_init(mma_done, 1);
+    tc::mbar_fence_init();
+  }
+  for (uint32_t i = tid * 16u; i < 2 * R_BYTES; i += GRU_THREADS * 16u)
+    *reinterpret_cast<uint4*>(Rs + i) = *reinterpret_cast<const uint4*>(p.Rimg + i);
+  tc::fence_async_smem();
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  uint32_t ph_h = 0, ph_m = 0;
+
+  if (warp == GRU_GATE_WARPS) {
+    if (lane == 0) {
+      const uint32_t idesc = tc::idesc_bf16(128, G, 0, 0);
+      const uint64_t a0 = tc::smem_desc(tc::smem_u32(As), PSTRIDE_A, 128u), w0 = tc::smem_desc(tc::smem_u32(Rs), PSTRIDE_W, 128u);
+      const uint64_t l0 = tc::smem_desc(tc::smem_u32(Al), PSTRIDE_A, 128u), w1 = tc::smem_desc(tc::smem_u32(Rs + R_BYTES), PSTRIDE_W, 128u);
+      const uint64_t a_step = (uint64_t)((2u * PSTRIDE_A) >> 4), w_step = (uint64_t)((2u * PSTRIDE_W) >> 4);
+      for (unsigned tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        for (int t = 0; t < p.Ts; ++t) {
+          tc::mbar_wait(h_ready, ph_h); ph_h ^= 1u;
+          tc::tc_fence_after();
+          uint64_t ad = a0, wd = w0;
+#pragma unroll
+          for (int ks = 0; ks < H / 16; ++ks, ad += a_step, wd += w_step) tc::umma(tmem, ad, wd, idesc, ks != 0);
+          ad = l0; wd = w0;
+#pragma unroll
+          for (int ks = 0; ks < H / 16; ++ks, ad += a_step, wd += w_step) tc::umma(tmem, ad, wd, idesc, 1u);
+          ad = a0; wd = w1;
+#pragma unroll
+          for (int ks = 0; ks < H / 16; ++ks, ad += a_step, wd += w_step) tc::umma(tmem, ad, wd, idesc, 1u);
+          tc::umma_commit(mma_done);
+        }
+      }
+    }
+  } else {
+    const int q4 = warp & 3, part = warp >> 2;
+    const int row = q4 * 32 + lane;
+    const int u0 = part * HH;
+    const uint32_t ta = tmem + ((uint32_t)(q4 * 32) << 16);
+    uint8_t* arow = As + (size_t)row * 16;
+    uint8_t* lrow = Al + (size_t)row * 16;
+    for (unsigned tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      const long long q = (long long)tile * 128 + row;
+      const bool live = q < p.nseq;
+      const long long b = live ? q / p.Nn : 0;
+      const int n = live ? (int)(q % p.Nn) : 0;
+      float cst[HH];
+#pragma unroll
+      for (int k = 0; k < HH; ++k) cst[k] = 0.f;
+#pragma unroll
+      for (int c = 0; c < HH / 8; ++c) {
+        *reinterpret_cast<uint4*>(arow + (size_t)(u0 / 8 + c) * PSTRIDE_A) = make_uint4(0u, 0u, 0u, 0u);
+        *reinterpret_cast<uint4*>(lrow + (size_t)(u0 / 8 + c) * PSTRIDE_A) = make_uint4(0u, 0u, 0u, 0u);
+      }
+      tc::fence_async_smem();
+      mbar_arrive(h_ready);
+      for (int t = 0; t < p.Ts; ++t) {
+        uint4 mg[4][HH / 8];                         // this step's mx slices of the 4 gates, loaded before the wait
+        const bf16* mxr = p.mx + ((size_t)(b * p.Ts + t) * p.Nn + n) * G + u0;
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+#pragma unroll
+          for (int c = 0; c < HH / 8; ++c)
+            mg[g][c] = live ? *reinterpret_cast<const uint4*>(mxr + g * H + c * 8) : make_uint4(0u, 0u, 0u, 0u);
+        tc::mbar_wait(mma_done, ph_m); ph_m ^= 1u;
+        tc::tc_fence_after();
+        const int td = t - (p.Ts - p.Td);
+        bf16* orow = p.out + ((size_t)(b * p.Td + (td > 0 ? td : 0)) * p.Nn + n) * H + u0;
+#pragma unroll
+        for (int c0 = 0; c0 < HH; c0 += 8) {
+          float ai[8], af[8], ac[8], ao[8];
+          tc::tmem_ld8(ta + (uint32_t)(u0 + c0), ai);
+          tc::tmem_ld8(ta + (uint32_t)(H + u0 + c0), af);
+          tc::tmem_ld8(ta + (uint32_t)(2 * H + u0 + c0), ac);
+          tc::tmem_ld8(ta + (uint32_t)(3 * H + u0 + c0), ao);
+          tc::tmem_ld_wait();
+          float xi[8], xf[8], xc[8], xo[8];
+          tc::unpack8_bf16(mg[0][c0 / 8], xi); tc::unpack8_bf16(mg[1][c0 / 8], xf);
+          tc::unpack8_bf16(mg[2][c0 / 8], xc); tc::unpack8_bf16(mg[3][c0 / 8], xo);
+          float hn[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float ig = fast_sigmoid(xi[k] + ai[k]);
+            const float fg = fast_sigmoid(xf[k] + af[k]);
+            const float cg = fast_tanh(xc[k] + ac[k]);
+            const float og = fast_sigmoid(xo[k] + ao[k]);
+            const float cn = fg * cst[c0 + k] + ig * cg;
+            cst[c0 + k] = cn;
+            hn[k] = og * fast_tanh(cn);
+          }
+          const uint4 p0 = tc::pack8_bf16(hn);
+          *reinterpret_cast<uint4*>(arow + (size_t)((u0 + c0) / 8) * PSTRIDE_A) = p0;
+          float hi[8];
+          tc::unpack8_bf16(p0, hi);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) hi[k] = hn[k] - hi[k];
+          *reinterpret_cast<uint4*>(lrow + (size_t)((u0 + c0) / 8) * PSTRIDE_A) = tc::pack8_bf16(hi);
+          if (live && td >= 0) *reinterpret_cast<uint4*>(orow + c0) = p0;
+        }
+        tc::tc_fence_before();
+        tc::fence_async_smem();
+        if (t + 1 < p.Ts) mbar_arrive(h_ready);
+      }
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc::tmem_free(tmem, 256);
+}
+
 }  // namespace gu
