@@ -49,6 +49,8 @@ struct SpConvP {
   uint32_t pstrideA, pstrideM, pstrideX;      // bytes: self/NE panels (Rbox*16), Mat panels, other_dense panels (Kp*16)
   uint32_t off_w, off_m, off_in, in_stride, xe_off, off_nx, off_sc, off_bar, hsb;
   uint32_t self_bytes, xe_bytes;
+  int max_len;                // longest CSR row (true entries): <= 20 selects the register softmax
+  int dbg;                    // GNNUDS_SP_DBG timing experiments (results are wrong when set): 1 no h loads, 2 no neighbour blocks, 4 no softmax
   long long* trace;           // debug: clock64 stamps of CTA 0, SP_NSTAMP per sample (GNNUDS_TRACE_FILE), else null
 };
 constexpr int SP_NSTAMP = 12;
@@ -101,8 +103,12 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
     tc::mbar_fence_init();
   }
   // constants into scratch (all threads), zero the NE panels once (rows >= R stay zero/finite)
+  // fp16 build, relu / linear activation: the aggregation epilogue stays in half2 (scale, bias, relu, store) and reads
+  // the bias as fp16 from the same scratch slot
+  const bool fast_epi = GU_F16 && (p.act == ACT_RELU || p.act == ACT_LINEAR);
   for (int i = tid; i < p.Nout; i += SP_THREADS) {
-    bias_s[i] = p.bias ? p.bias[i] : 0.f;
+    if (fast_epi) reinterpret_cast<__half*>(bias_s)[i] = __float2half_rn(p.bias ? p.bias[i] : 0.f);
+    else bias_s[i] = p.bias ? p.bias[i] : 0.f;
     asf[i] = p.gat ? p.a_self[i] : 0.f;
     anf[i] = p.gat ? p.a_neigh[i] : 0.f;
   }
@@ -320,7 +326,61 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
       const uint8_t* hbase = smem + p.off_in + (size_t)buf * p.in_stride;
       float* al = alpha + buf * p.nnz;
       float* inv = inv_s + buf * RP;
-      if (p.gat) {
+      if (p.gat && !(p.dbg & 4) && p.max_len <= 20) {
+        // edge softmax over the CSR pattern, 4 lanes per row, two rows per quad and pass.  A lane keeps its (<= 5)
+        // scores in registers: the index / score loads of both rows are independent, so a pass costs two shared-memory
+        // round trips instead of a store -> load chain per neighbour.
+        const float* ssb = ss + buf * RP;
+        const float* snb = sn + buf * RP;
+        const int sub = gt & 3;
+        constexpr int KM = 5;
+        for (int r0 = 0; r0 < R; r0 += SP_GRAPH_WARPS * 16) {
+          int beg[2], end[2], pend[2], rr[2];
+          float sc[2][KM], si[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            rr[u] = r0 + (gt >> 2) + u * SP_GRAPH_WARPS * 8;
+            const bool live = rr[u] < R;
+            beg[u] = live ? rp_s[rr[u]] : 0; pend[u] = live ? rp_s[rr[u] + 1] : 0; end[u] = live ? beg[u] + rlen_s[rr[u]] : 0;
+            si[u] = live ? ssb[rr[u]] : 0.f;
+          }
+          int jj[2][KM];
+#pragma unroll
+          for (int u = 0; u < 2; ++u)
+#pragma unroll
+            for (int k = 0; k < KM; ++k) { const int qq = beg[u] + sub + 4 * k; jj[u][k] = qq < end[u] ? ci_s[qq] : 0; }
+#pragma unroll
+          for (int u = 0; u < 2; ++u)
+#pragma unroll
+            for (int k = 0; k < KM; ++k) {
+              float v = si[u] + snb[jj[u][k]];
+              v = v > 0.f ? v : 0.2f * v;
+              sc[u][k] = beg[u] + sub + 4 * k < end[u] ? v : -INFINITY;
+            }
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            float mx = sc[u][0];
+#pragma unroll
+            for (int k = 1; k < KM; ++k) mx = fmaxf(mx, sc[u][k]);
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+            float den = 0.f;
+#pragma unroll
+            for (int k = 0; k < KM; ++k) {
+              const int qq = beg[u] + sub + 4 * k;
+              // the weight is stored as an fp16 pair; the denominator sums the rounded weights so that the
+              // attention stays a convex combination; pads of the last block carry weight 0
+              const __half wh = qq < end[u] ? __float2half_rn(__expf(sc[u][k] - mx)) : __float2half_rn(0.f);
+              den += __half2float(wh);
+              if (qq < pend[u]) al[qq] = __uint_as_float((uint32_t)__half_as_ushort(wh) * 0x10001u);
+            }
+            den += __shfl_xor_sync(0xffffffffu, den, 1);
+            den += __shfl_xor_sync(0xffffffffu, den, 2);
+            if (rr[u] < R && sub == 0) inv[rr[u]] = 1.f / den;
+          }
+        }
+        graph_bar_sync();
+      } else if (p.gat && !(p.dbg & 4)) {
         // edge softmax over the CSR pattern: 4 lanes per row, neighbours strided over the lanes
         const float* ssb = ss + buf * RP;
         const float* snb = sn + buf * RP;
@@ -361,7 +421,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
       const int bin = gw * 4 + lg;
       for (int bi = bin_s[bin]; bi < bin_s[bin + 1]; ++bi) {
         const int r = bin_s[SP_BINS + 1 + bi];
-        const int beg = rp_s[r], end = rp_s[r + 1];
+        const int beg = rp_s[r], end = (p.dbg & 2) ? beg : rp_s[r + 1];
         const float scale = p.gat ? inv[r] : 1.f;
         const bool store = (long long)smp * R + r < p.rows_total;
         bf16* orow = p.out + ((size_t)smp * R + r) * p.Nout + gl * 8;
@@ -381,17 +441,45 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
             const uint8_t* hp1 = hb + (size_t)jj.y * p.hsb + ((gl ^ (jj.y & 7)) << 4);
             const uint8_t* hp2 = hb + (size_t)jj.z * p.hsb + ((gl ^ (jj.z & 7)) << 4);
             const uint8_t* hp3 = hb + (size_t)jj.w * p.hsb + ((gl ^ (jj.w & 7)) << 4);
-            const uint4 u0 = *reinterpret_cast<const uint4*>(hp0), u1 = *reinterpret_cast<const uint4*>(hp1);
-            const uint4 u2 = *reinterpret_cast<const uint4*>(hp2), u3 = *reinterpret_cast<const uint4*>(hp3);
+            const bool nl = p.dbg & 1;
+            const uint4 cu = make_uint4((uint32_t)(size_t)hp0, (uint32_t)(size_t)hp1, (uint32_t)(size_t)hp2, (uint32_t)(size_t)hp3);
+            const uint4 u0 = nl ? cu : *reinterpret_cast<const uint4*>(hp0), u1 = nl ? cu : *reinterpret_cast<const uint4*>(hp1);
+            const uint4 u2 = nl ? cu : *reinterpret_cast<const uint4*>(hp2), u3 = nl ? cu : *reinterpret_cast<const uint4*>(hp3);
             if (two) {
-              const uint4 v0 = *reinterpret_cast<const uint4*>(hp0 + 128), v1 = *reinterpret_cast<const uint4*>(hp1 + 128);
-              const uint4 v2 = *reinterpret_cast<const uint4*>(hp2 + 128), v3 = *reinterpret_cast<const uint4*>(hp3 + 128);
+              const uint4 v0 = nl ? cu : *reinterpret_cast<const uint4*>(hp0 + 128), v1 = nl ? cu : *reinterpret_cast<const uint4*>(hp1 + 128);
+              const uint4 v2 = nl ? cu : *reinterpret_cast<const uint4*>(hp2 + 128), v3 = nl ? cu : *reinterpret_cast<const uint4*>(hp3 + 128);
               tc::hfma8(h1, v0, tc::as_half2(ww.x)); tc::hfma8(h1, v1, tc::as_half2(ww.y));
               tc::hfma8(h1, v2, tc::as_half2(ww.z)); tc::hfma8(h1, v3, tc::as_half2(ww.w));
             }
             tc::hfma8(h0, u0, tc::as_half2(ww.x)); tc::hfma8(h0, u1, tc::as_half2(ww.y));
             tc::hfma8(h0, u2, tc::as_half2(ww.z)); tc::hfma8(h0, u3, tc::as_half2(ww.w));
           }
+#if GU_F16
+          if (fast_epi) {
+            const __half2 sc2 = __float2half2_rn(scale), z2 = __float2half2_rn(0.f);
+            const bool relu = p.act == ACT_RELU;
+            const __half* bh = reinterpret_cast<const __half*>(bias_s) + e0 + gl * 8;
+            {
+              const uint4 bq = *reinterpret_cast<const uint4*>(bh);
+              const __half2* b2 = reinterpret_cast<const __half2*>(&bq);
+              uint4 o;
+              __half2* o2 = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) { const __half2 v = __hfma2(h0[k], sc2, b2[k]); o2[k] = relu ? __hmax2(v, z2) : v; }
+              if (store) *reinterpret_cast<uint4*>(orow + e0) = o;
+            }
+            if (two) {
+              const uint4 bq = *reinterpret_cast<const uint4*>(bh + 64);
+              const __half2* b2 = reinterpret_cast<const __half2*>(&bq);
+              uint4 o;
+              __half2* o2 = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) { const __half2 v = __hfma2(h1[k], sc2, b2[k]); o2[k] = relu ? __hmax2(v, z2) : v; }
+              if (store) *reinterpret_cast<uint4*>(orow + e0 + 64) = o;
+            }
+            continue;
+          }
+#endif
           float a0[8], a1[8];
 #pragma unroll
           for (int k = 0; k < 4; ++k) {

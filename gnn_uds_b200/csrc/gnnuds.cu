@@ -102,6 +102,7 @@ struct gnnuds_handle {
   // CSR padded to 4 entries per block (zero-weight pads) for the 16-byte index / weight loads of sp_conv_kernel
   int* d_prp[2] = {nullptr, nullptr}; int* d_pci[2] = {nullptr, nullptr}; float* d_pval[2] = {nullptr, nullptr};
   int pnnz[2] = {0, 0};
+  int sp_max_len[2] = {0, 0};           // longest true CSR row per side (selects sp_conv's register softmax)
   float *d_val = nullptr, *d_eval = nullptr;
   int nnz = 0, ennz = 0, n_adj = 0;
   int *d_edges = nullptr, *d_act_of_edge = nullptr, *d_act_out = nullptr, *d_act_in = nullptr;
@@ -1175,6 +1176,8 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   const char* tf = getenv("GNNUDS_TRACE_FILE");
   const int want = getenv("GNNUDS_TRACE_LAUNCH") ? atoi(getenv("GNNUDS_TRACE_LAUNCH")) : 0;
   const bool do_trace = tf && S >= 64 * (long long)h->sm_count && traced++ == want;
+  p.dbg = getenv("GNNUDS_SP_DBG") ? atoi(getenv("GNNUDS_SP_DBG")) : 0;
+  p.max_len = h->sp_max_len[side];
   const size_t tn = 64 * SP_NSTAMP;
   if (do_trace) { CU(cudaMalloc(&p.trace, tn * sizeof(long long))); CU(cudaMemset(p.trace, 0, tn * sizeof(long long))); }
   cudaEvent_t e1 = nullptr;
@@ -1657,20 +1660,31 @@ int upload_bins(gnnuds_handle* h, int side, const int* rp0, const int* ci0, cons
     if ((rc = upload(h, &h->d_pval[side], pval.data(), pval.size()))) return rc;
     h->pnnz[side] = prp[R];
   }
-  std::vector<int> order(R), load(SP_BINS, 0), which(R);
+  // The four 8-lane groups of a warp run in lockstep: a warp's time is the sum over its row slots of the LONGEST row
+  // of the slot.  So rows are sorted by length, cut into quads of similar length (one quad = one slot of one warp),
+  // and the quads are spread over the warps longest-processing-time first.
+  std::vector<int> order(R), which(R);
   for (int i = 0; i < R; ++i) order[i] = i;
   std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return rp[a + 1] - rp[a] > rp[b + 1] - rp[b]; });
-  for (int r : order) {
-    int best = 0;
-    for (int b = 1; b < SP_BINS; ++b) if (load[b] < load[best]) best = b;
-    which[r] = best; load[best] += (rp[r + 1] - rp[r] + 3) / 4 * 4 + 2;     // blocks of 4 neighbours + per-row epilogue
+  {
+    constexpr int NW = SP_BINS / 4;
+    std::vector<int> wload(NW, 0);
+    for (int q0 = 0; q0 < R; q0 += 4) {
+      const int len0 = rp[order[q0] + 1] - rp[order[q0]];
+      int best = 0;
+      for (int w = 1; w < NW; ++w) if (wload[w] < wload[best]) best = w;
+      wload[best] += (len0 + 3) / 4 * 4 + 2;                 // blocks of 4 neighbours + per-row epilogue
+      for (int j = 0; j < 4 && q0 + j < R; ++j) which[order[q0 + j]] = best * 4 + j;
+    }
   }
   std::vector<int> bins(SP_BINS + 1 + 2 * R, 0);
   for (int r = 0; r < R; ++r) bins[SP_BINS + 1 + R + r] = rp[r + 1] - rp[r];
+  h->sp_max_len[side] = 0;
+  for (int r = 0; r < R; ++r) h->sp_max_len[side] = std::max(h->sp_max_len[side], rp[r + 1] - rp[r]);
   for (int r = 0; r < R; ++r) ++bins[which[r] + 1];
   for (int b = 0; b < SP_BINS; ++b) bins[b + 1] += bins[b];
   std::vector<int> fill(bins.begin(), bins.begin() + SP_BINS);
-  for (int r = 0; r < R; ++r) bins[SP_BINS + 1 + fill[which[r]]++] = r;
+  for (int r : order) bins[SP_BINS + 1 + fill[which[r]]++] = r;          // slot order = quad order within a warp
   if (h->d_bins[side]) { cudaFree(h->d_bins[side]); h->d_bins[side] = nullptr; }
   return upload(h, &h->d_bins[side], bins.data(), bins.size());
 }
