@@ -56,6 +56,57 @@ struct SpConvP {
 constexpr int SP_NSTAMP = 12;
 #define SP_STAMP(i, k) do { if (p.trace && blockIdx.x == 0 && (i) < 64) p.trace[(i) * SP_NSTAMP + (k)] = clock64(); } while (0)
 
+// 16-byte shared load that is not issued when `on` is false (zeros instead): the pads of a neighbour block carry
+// weight 0, and a quarter-warp whose lanes are all predicated off costs no shared-memory wavefront
+template <int OFS>
+__device__ __forceinline__ uint4 lds128_if(uint32_t saddr, bool on) {
+  uint4 v = make_uint4(0u, 0u, 0u, 0u);
+  asm("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %5, 0;\n\t@q ld.shared.v4.u32 {%0, %1, %2, %3}, [%4+%6];\n\t}"
+      : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w)
+      : "r"(saddr), "r"((uint32_t)on), "n"(OFS));
+  return v;
+}
+
+// Edge softmax of one CSR row by a quad of lanes (lane `sub` takes the neighbours sub, sub+4, ...), at most 4*KM
+// neighbours: scores stay in registers, so the row costs two rounds of independent shared loads.  The weight is stored
+// as an fp16 pair and the denominator sums the ROUNDED weights, so the attention stays a convex combination; the pads
+// of the last block of 4 get weight 0.  ci holds byte offsets into the h tile (index << hshift | swizzle bits).
+template <int KM>
+__device__ __forceinline__ void softmax_row(int r, int R, int sub, int hshift, const int* rp_s, const int* rlen_s, const int* ci_s,
+                                            const float* ssb, const float* snb, float* al, float* inv) {
+  const bool live = r < R;
+  const int beg = live ? rp_s[r] : 0, pend = live ? rp_s[r + 1] : 0, end = live ? beg + rlen_s[r] : 0;
+  const float si = live ? ssb[r] : 0.f;
+  int jj[KM];
+#pragma unroll
+  for (int k = 0; k < KM; ++k) { const int qq = beg + sub + 4 * k; jj[k] = qq < end ? (ci_s[qq] >> hshift) : 0; }
+  float sc[KM];
+#pragma unroll
+  for (int k = 0; k < KM; ++k) {
+    float v = si + snb[jj[k]];
+    v = v > 0.f ? v : 0.2f * v;
+    sc[k] = beg + sub + 4 * k < end ? v : -INFINITY;
+  }
+  float mx = sc[0];
+#pragma unroll
+  for (int k = 1; k < KM; ++k) mx = fmaxf(mx, sc[k]);
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+  float den = 0.f;
+#pragma unroll
+  for (int k = 0; k < KM; ++k) {
+    const int qq = beg + sub + 4 * k;
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"((sc[k] - mx) * 1.4426950408889634f));
+    const __half wh = __float2half_rn(qq < end ? e : 0.f);
+    den += __half2float(wh);
+    if (qq < pend) al[qq] = __uint_as_float((uint32_t)__half_as_ushort(wh) * 0x10001u);
+  }
+  den += __shfl_xor_sync(0xffffffffu, den, 1);
+  den += __shfl_xor_sync(0xffffffffu, den, 2);
+  if (live && sub == 0) inv[r] = 1.f / den;
+}
+
 __device__ __forceinline__ void graph_bar_sync() { asm volatile("bar.sync 2, %0;" ::"n"(SP_GRAPH_WARPS * 32) : "memory"); }
 
 __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_constant__ SpConvP p) {
@@ -114,7 +165,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
   }
   for (int i = tid; i <= p.R; i += SP_THREADS) rp_s[i] = p.row_ptr[i];
   for (int i = tid; i < SP_BINS + 1 + 2 * p.R; i += SP_THREADS) bin_s[i] = p.bins[i];
-  for (int i = tid; i < p.nnz; i += SP_THREADS) { ci_s[i] = p.col_idx[i]; if (!p.gat) { const float v = __uint_as_float(tc::pack_f16(p.val[i], p.val[i])); alpha[i] = v; alpha[p.nnz + i] = v; } }
+  for (int i = tid; i < p.nnz; i += SP_THREADS) { const int j = p.col_idx[i]; ci_s[i] = j * (int)p.hsb + ((j & 7) << 4); if (!p.gat) { const float v = __uint_as_float(tc::pack_f16(p.val[i], p.val[i])); alpha[i] = v; alpha[p.nnz + i] = v; } }
   {
     uint4* z = reinterpret_cast<uint4*>(smem + p.off_nx);
     const int n16 = (int)((p.F / 8) * p.pstrideA / 16);
@@ -318,6 +369,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
     const int lg = lane >> 3, gl = lane & 7;
     const int R = p.R;
     const bool two = p.Nout > 64;                     // a lane owns 8 features of each 64-feature half
+    const uint32_t glsh = (uint32_t)gl << 4;
     for (int i = 0; i < n_it; ++i) {
       const int buf = i & 1;
       const int smp = (int)blockIdx.x + i * (int)gridDim.x;
@@ -326,58 +378,19 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
       const uint8_t* hbase = smem + p.off_in + (size_t)buf * p.in_stride;
       float* al = alpha + buf * p.nnz;
       float* inv = inv_s + buf * RP;
+      const int hshift = 31 - __clz((int)p.hsb);         // h rows are 128 or 256 bytes
       if (p.gat && !(p.dbg & 4) && p.max_len <= 20) {
-        // edge softmax over the CSR pattern, 4 lanes per row, two rows per quad and pass.  A lane keeps its (<= 5)
-        // scores in registers: the index / score loads of both rows are independent, so a pass costs two shared-memory
-        // round trips instead of a store -> load chain per neighbour.
+        // one row per quad and pass; a warp whose 8 rows are all beyond R skips the pass (R = 131: only warp 0 runs the
+        // second one).  KM is sized to the longest row of the graph.
         const float* ssb = ss + buf * RP;
         const float* snb = sn + buf * RP;
-        const int sub = gt & 3;
-        constexpr int KM = 5;
-        for (int r0 = 0; r0 < R; r0 += SP_GRAPH_WARPS * 16) {
-          int beg[2], end[2], pend[2], rr[2];
-          float sc[2][KM], si[2];
-#pragma unroll
-          for (int u = 0; u < 2; ++u) {
-            rr[u] = r0 + (gt >> 2) + u * SP_GRAPH_WARPS * 8;
-            const bool live = rr[u] < R;
-            beg[u] = live ? rp_s[rr[u]] : 0; pend[u] = live ? rp_s[rr[u] + 1] : 0; end[u] = live ? beg[u] + rlen_s[rr[u]] : 0;
-            si[u] = live ? ssb[rr[u]] : 0.f;
-          }
-          int jj[2][KM];
-#pragma unroll
-          for (int u = 0; u < 2; ++u)
-#pragma unroll
-            for (int k = 0; k < KM; ++k) { const int qq = beg[u] + sub + 4 * k; jj[u][k] = qq < end[u] ? ci_s[qq] : 0; }
-#pragma unroll
-          for (int u = 0; u < 2; ++u)
-#pragma unroll
-            for (int k = 0; k < KM; ++k) {
-              float v = si[u] + snb[jj[u][k]];
-              v = v > 0.f ? v : 0.2f * v;
-              sc[u][k] = beg[u] + sub + 4 * k < end[u] ? v : -INFINITY;
-            }
-#pragma unroll
-          for (int u = 0; u < 2; ++u) {
-            float mx = sc[u][0];
-#pragma unroll
-            for (int k = 1; k < KM; ++k) mx = fmaxf(mx, sc[u][k]);
-            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
-            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-            float den = 0.f;
-#pragma unroll
-            for (int k = 0; k < KM; ++k) {
-              const int qq = beg[u] + sub + 4 * k;
-              // the weight is stored as an fp16 pair; the denominator sums the rounded weights so that the
-              // attention stays a convex combination; pads of the last block carry weight 0
-              const __half wh = qq < end[u] ? __float2half_rn(__expf(sc[u][k] - mx)) : __float2half_rn(0.f);
-              den += __half2float(wh);
-              if (qq < pend[u]) al[qq] = __uint_as_float((uint32_t)__half_as_ushort(wh) * 0x10001u);
-            }
-            den += __shfl_xor_sync(0xffffffffu, den, 1);
-            den += __shfl_xor_sync(0xffffffffu, den, 2);
-            if (rr[u] < R && sub == 0) inv[rr[u]] = 1.f / den;
-          }
+        const int km = (p.max_len + 3) >> 2;
+        for (int r0 = 0; r0 < R; r0 += SP_GRAPH_WARPS * 8) {
+          if (r0 + gw * 8 >= R) continue;
+          const int r = r0 + (gt >> 2);
+          if (km <= 3) softmax_row<3>(r, R, gt & 3, hshift, rp_s, rlen_s, ci_s, ssb, snb, al, inv);
+          else if (km == 4) softmax_row<4>(r, R, gt & 3, hshift, rp_s, rlen_s, ci_s, ssb, snb, al, inv);
+          else softmax_row<5>(r, R, gt & 3, hshift, rp_s, rlen_s, ci_s, ssb, snb, al, inv);
         }
         graph_bar_sync();
       } else if (p.gat && !(p.dbg & 4)) {
@@ -393,7 +406,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
           float mx = -INFINITY;
           for (int qq = end + ((sub - end) & 3); qq < pend; qq += 4) al[qq] = 0.f;     // pads of the last block: weight 0
           for (int qq = beg + sub; qq < end; qq += 4) {
-            float sc = si + snb[ci_s[qq]];
+            float sc = si + snb[ci_s[qq] >> hshift];
             sc = sc > 0.f ? sc : 0.2f * sc;
             al[qq] = sc;
             mx = fmaxf(mx, sc);
@@ -421,7 +434,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
       const int bin = gw * 4 + lg;
       for (int bi = bin_s[bin]; bi < bin_s[bin + 1]; ++bi) {
         const int r = bin_s[SP_BINS + 1 + bi];
-        const int beg = rp_s[r], end = (p.dbg & 2) ? beg : rp_s[r + 1];
+        const int beg = rp_s[r], end = (p.dbg & 2) ? beg : rp_s[r + 1], tend = beg + rlen_s[r];
         const float scale = p.gat ? inv[r] : 1.f;
         const bool store = (long long)smp * R + r < p.rows_total;
         bf16* orow = p.out + ((size_t)smp * R + r) * p.Nout + gl * 8;
@@ -431,23 +444,21 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
           __half2 h0[4], h1[4];
 #pragma unroll
           for (int k = 0; k < 4; ++k) { h0[k] = __float2half2_rn(0.f); h1[k] = h0[k]; }
-          const uint8_t* hb = hbase + e0 * 2;
+          const uint32_t hb32 = tc::smem_u32(hbase) + (uint32_t)e0 * 2u;
           // one block = 4 neighbours: their indices and weights arrive as two 16-byte loads, then eight 16-byte
           // h loads are in flight before the first HFMA2 (pads carry weight 0)
           for (int qq = beg; qq < end; qq += 4) {
             const int4 jj = *reinterpret_cast<const int4*>(ci_s + qq);
             const uint4 ww = *reinterpret_cast<const uint4*>(al + qq);
-            const uint8_t* hp0 = hb + (size_t)jj.x * p.hsb + ((gl ^ (jj.x & 7)) << 4);
-            const uint8_t* hp1 = hb + (size_t)jj.y * p.hsb + ((gl ^ (jj.y & 7)) << 4);
-            const uint8_t* hp2 = hb + (size_t)jj.z * p.hsb + ((gl ^ (jj.z & 7)) << 4);
-            const uint8_t* hp3 = hb + (size_t)jj.w * p.hsb + ((gl ^ (jj.w & 7)) << 4);
+            const uint32_t a0 = hb32 + ((uint32_t)jj.x ^ glsh), a1 = hb32 + ((uint32_t)jj.y ^ glsh);
+            const uint32_t a2 = hb32 + ((uint32_t)jj.z ^ glsh), a3 = hb32 + ((uint32_t)jj.w ^ glsh);
             const bool nl = p.dbg & 1;
-            const uint4 cu = make_uint4((uint32_t)(size_t)hp0, (uint32_t)(size_t)hp1, (uint32_t)(size_t)hp2, (uint32_t)(size_t)hp3);
-            const uint4 u0 = nl ? cu : *reinterpret_cast<const uint4*>(hp0), u1 = nl ? cu : *reinterpret_cast<const uint4*>(hp1);
-            const uint4 u2 = nl ? cu : *reinterpret_cast<const uint4*>(hp2), u3 = nl ? cu : *reinterpret_cast<const uint4*>(hp3);
+            const bool k1 = !nl && qq + 1 < tend, k2 = !nl && qq + 2 < tend, k3 = !nl && qq + 3 < tend;
+            const uint4 u0 = lds128_if<0>(a0, !nl), u1 = lds128_if<0>(a1, k1);
+            const uint4 u2 = lds128_if<0>(a2, k2), u3 = lds128_if<0>(a3, k3);
             if (two) {
-              const uint4 v0 = nl ? cu : *reinterpret_cast<const uint4*>(hp0 + 128), v1 = nl ? cu : *reinterpret_cast<const uint4*>(hp1 + 128);
-              const uint4 v2 = nl ? cu : *reinterpret_cast<const uint4*>(hp2 + 128), v3 = nl ? cu : *reinterpret_cast<const uint4*>(hp3 + 128);
+              const uint4 v0 = lds128_if<128>(a0, !nl), v1 = lds128_if<128>(a1, k1);
+              const uint4 v2 = lds128_if<128>(a2, k2), v3 = lds128_if<128>(a3, k3);
               tc::hfma8(h1, v0, tc::as_half2(ww.x)); tc::hfma8(h1, v1, tc::as_half2(ww.y));
               tc::hfma8(h1, v2, tc::as_half2(ww.z)); tc::hfma8(h1, v3, tc::as_half2(ww.w));
             }
