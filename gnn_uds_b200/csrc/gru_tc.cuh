@@ -131,19 +131,19 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) gru_tc_kernel(const __grid_con
         const int td = t - (p.Ts - p.Td);
         bf16* orow = p.out + ((size_t)(b * p.Td + (td > 0 ? td : 0)) * p.Nn + n) * H + u0;
 #pragma unroll
-        for (int c0 = 0; c0 < HH; c0 += 16) {        // 16 units at a time: 3 x 16 accumulator columns
-          float az[16], ar[16], ac[16];
-          tc::tmem_ld16(ta + (uint32_t)(u0 + c0), az);
-          tc::tmem_ld16(ta + (uint32_t)(H + u0 + c0), ar);
-          tc::tmem_ld16(ta + (uint32_t)(2 * H + u0 + c0), ac);
+        for (int c0 = 0; c0 < HH; c0 += 8) {         // 8 units at a time: 3 x 8 accumulator columns (register budget)
+          float az[8], ar[8], ac[8];
+          tc::tmem_ld8(ta + (uint32_t)(u0 + c0), az);
+          tc::tmem_ld8(ta + (uint32_t)(H + u0 + c0), ar);
+          tc::tmem_ld8(ta + (uint32_t)(2 * H + u0 + c0), ac);
           tc::tmem_ld_wait();
-          float xz[16], xr[16], xc[16];
-          tc::unpack8_bf16(mz[c0 / 8], xz); tc::unpack8_bf16(mz[c0 / 8 + 1], xz + 8);
-          tc::unpack8_bf16(mr[c0 / 8], xr); tc::unpack8_bf16(mr[c0 / 8 + 1], xr + 8);
-          tc::unpack8_bf16(mc[c0 / 8], xc); tc::unpack8_bf16(mc[c0 / 8 + 1], xc + 8);
-          float hn[16];
+          float xz[8], xr[8], xc[8];
+          tc::unpack8_bf16(mz[c0 / 8], xz);
+          tc::unpack8_bf16(mr[c0 / 8], xr);
+          tc::unpack8_bf16(mc[c0 / 8], xc);
+          float hn[8];
 #pragma unroll
-          for (int k = 0; k < 16; ++k) {
+          for (int k = 0; k < 8; ++k) {
             const int u = u0 + c0 + k;
             const float z = __fdividef(1.f, 1.f + __expf(-(xz[k] + az[k] + b1s[u])));
             const float r = __fdividef(1.f, 1.f + __expf(-(xr[k] + ar[k] + b1s[H + u])));
@@ -153,21 +153,14 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) gru_tc_kernel(const __grid_con
             hn[k] = z * h[c0 + k] + (1.f - z) * hh;
             h[c0 + k] = hn[k];
           }
-          const uint4 p0 = tc::pack8_bf16(hn), p1 = tc::pack8_bf16(hn + 8);
+          const uint4 p0 = tc::pack8_bf16(hn);
           *reinterpret_cast<uint4*>(arow + (size_t)((u0 + c0) / 8) * PSTRIDE_A) = p0;
-          *reinterpret_cast<uint4*>(arow + (size_t)((u0 + c0) / 8 + 1) * PSTRIDE_A) = p1;
-          {
-            float hi[16];
-            tc::unpack8_bf16(p0, hi); tc::unpack8_bf16(p1, hi + 8);
+          float hi[8];
+          tc::unpack8_bf16(p0, hi);
 #pragma unroll
-            for (int k = 0; k < 16; ++k) hi[k] = hn[k] - hi[k];
-            *reinterpret_cast<uint4*>(lrow + (size_t)((u0 + c0) / 8) * PSTRIDE_A) = tc::pack8_bf16(hi);
-            *reinterpret_cast<uint4*>(lrow + (size_t)((u0 + c0) / 8 + 1) * PSTRIDE_A) = tc::pack8_bf16(hi + 8);
-          }
-          if (live && td >= 0) {
-            *reinterpret_cast<uint4*>(orow + c0) = p0;
-            *reinterpret_cast<uint4*>(orow + c0 + 8) = p1;
-          }
+          for (int k = 0; k < 8; ++k) hi[k] = hn[k] - hi[k];
+          *reinterpret_cast<uint4*>(lrow + (size_t)((u0 + c0) / 8) * PSTRIDE_A) = tc::pack8_bf16(hi);
+          if (live && td >= 0) *reinterpret_cast<uint4*>(orow + c0) = p0;
         }
         tc::tc_fence_before();
         tc::fence_async_smem();
