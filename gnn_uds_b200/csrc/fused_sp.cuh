@@ -386,8 +386,10 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
         const float* snb = sn + buf * RP;
         const int km = (p.max_len + 3) >> 2;
         for (int r0 = 0; r0 < R; r0 += SP_GRAPH_WARPS * 8) {
-          if (r0 + gw * 8 >= R) continue;
-          const int r = r0 + (gt >> 2);
+          // the short tail pass goes to the LAST warps, which carry the lightest gather lists
+          const int gwp = r0 ? SP_GRAPH_WARPS - 1 - gw : gw;
+          if (r0 + gwp * 8 >= R) continue;
+          const int r = r0 + gwp * 8 + (lane >> 2);
           if (km <= 3) softmax_row<3>(r, R, gt & 3, hshift, rp_s, rlen_s, ci_s, ssb, snb, al, inv);
           else if (km == 4) softmax_row<4>(r, R, gt & 3, hshift, rp_s, rlen_s, ci_s, ssb, snb, al, inv);
           else softmax_row<5>(r, R, gt & 3, hshift, rp_s, rlen_s, ci_s, ssb, snb, al, inv);
