@@ -47,8 +47,11 @@ struct gnnuds_handle {
   cudaStream_t stream = nullptr;
   int sm_count = 148;
   int64_t launches = 0;
+  bool attr_done[8] = {false, false, false, false, false, false, false, false};   // per handle (= per device): opt-in to > 48 KB dynamic smem
   bool has_graph = false, has_weights = false, has_norm = false;
   int debug_stop = 0;
+  int pp_variant = 0;           // 0 post_proc (numpy rules), 1 post_proc_tf (gnnuds_set_post_proc_variant); rollouts always use 1
+  bool pump_all = false;        // every link is a pump (emulator.py:698 pump.min() > 0)
   int profiling = 0;            // 0 off, 1 whole-call event pair, 2 also one pair per GEMM launch
   float last_total_ms = 0.f, last_gemm_ms = 0.f;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> gemm_ev;
@@ -604,13 +607,13 @@ int run_postproc(gnnuds_handle* h, const float* x, const float* b, const float* 
   p.y = y; p.ey = ey; p.S = Bc * To; p.N = N; p.M = M; p.b_in = c.b_in; p.n_out = c.n_out; p.e_out = c.e_out;
   p.ny = normalised_io ? 3 + (c.if_flood ? 1 : 0) : h->ny();
   p.if_flood = c.if_flood ? 1 : 0; p.edge_fusion = c.edge_fusion; p.act = c.act; p.tide = c.tide;
-  p.normalised = normalised_io ? 1 : 0; p.epsilon = c.epsilon;
+  p.normalised = normalised_io ? 1 : 0; p.epsilon = c.epsilon; p.tf_rules = h->pp_variant;
   if (normalised_io && c.tide) return fail(h, GNNUDS_E_INVALID, "ROLL_NORM with tide not supported");
-  const bool big = (size_t)M * sizeof(float) > 40 * 1024;      // large graphs: edge flows staged in HBM scratch (SS covers Bc*T*max(N,M))
+  const bool big = (size_t)(M + ((h->has_pump || h->has_offset) ? N : 0)) * sizeof(float) > 40 * 1024;      // large graphs: edge flows staged in HBM scratch (SS covers Bc*T*max(N,M))
   p.efl_g = big ? h->SS : nullptr;
   const bool need_h = h->has_pump || h->has_offset;
   if (need_h) {
-    p.edge_from = h->d_edge_from; p.pump = h->has_pump ? h->d_pump : nullptr; p.offset = h->has_offset ? h->d_offset : nullptr;
+    p.edge_from = h->d_edge_from; p.pump = (h->has_pump && (!h->pp_variant || h->pump_all)) ? h->d_pump : nullptr; p.offset = h->has_offset ? h->d_offset : nullptr;
     p.pump_in = h->has_pump ? h->d_pump_in : nullptr; p.pump_out = h->has_pump ? h->d_pump_out : nullptr;
     p.hn_g = big ? h->SN : nullptr;
   }
@@ -988,10 +991,9 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
   const size_t smem = p.bar_off + (size_t)(2 * p.NS + 6) * 8 + 16;
   cudaEvent_t e1 = nullptr;
   { int prc = prof_begin(h, GNNUDS_FAM_GEMM, &e1); if (prc) return prc; }
-  static bool attr_set = false;
-  if (!attr_set) {
+  if (!h->attr_done[0]) {
     CU(cudaFuncSetAttribute(tc_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
+    h->attr_done[0] = true;
   }
   const unsigned grid = std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count);
   tc_rows_kernel<<<grid, TC_THREADS, smem, h->stream>>>(p);
@@ -1030,8 +1032,7 @@ int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& 
         GruTcP p{reinterpret_cast<const bf16*>(h->HB), h->d_wimg + h->img_off[L[i].t[1]], W(h, L[i].t[2]) + G,
                  reinterpret_cast<bf16*>(o), nseq, Nn, Ts, Tdst, H, (unsigned)((nseq + 127) / 128)};
         const size_t smem = 2 * (size_t)H * G * 2 + 2 * 128 * H * 2 + G * 4 + 64;
-        static bool attr_set = false;
-        if (!attr_set) { CU(cudaFuncSetAttribute(gru_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
+        if (!h->attr_done[1]) { CU(cudaFuncSetAttribute(gru_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); h->attr_done[1] = true; }
         cudaEvent_t e1 = nullptr;
         { int prc = prof_begin(h, GNNUDS_FAM_RECURRENT, &e1); if (prc) return prc; }
         gru_tc_kernel<64><<<std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count), GRU_THREADS, smem, h->stream>>>(p);
@@ -1049,8 +1050,7 @@ int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& 
         LstmTcP p{reinterpret_cast<const bf16*>(h->HB), h->d_wimg + h->img_off[L[i].t[1]], reinterpret_cast<bf16*>(o), nseq, Nn, Ts,
                   Tdst, H, (unsigned)((nseq + 127) / 128)};
         const size_t smem = 2 * (size_t)H * G * 2 + 2 * 128 * H * 2 + 64;
-        static bool attr_set = false;
-        if (!attr_set) { CU(cudaFuncSetAttribute(lstm_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set = true; }
+        if (!h->attr_done[2]) { CU(cudaFuncSetAttribute(lstm_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); h->attr_done[2] = true; }
         cudaEvent_t e1 = nullptr;
         { int prc = prof_begin(h, GNNUDS_FAM_RECURRENT, &e1); if (prc) return prc; }
         lstm_tc_kernel<64><<<std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count), GRU_THREADS, smem, h->stream>>>(p);
@@ -1165,10 +1165,9 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   if (p.sw_x ? !make_rows_tmap_sw(&p.tm_other, other_dense, rows_other, F, F, p.Kp)
              : !make_rows_tmap(&p.tm_other, other_dense, rows_other, F, F, p.Kp, F)) return -1;
   p.rows_total = rows_total;
-  static bool attr_set = false;
-  if (!attr_set) {
+  if (!h->attr_done[3]) {
     CU(cudaFuncSetAttribute(sp_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
+    h->attr_done[3] = true;
   }
   const unsigned grid = (unsigned)std::min<long long>(S, h->sm_count);
   // GNNUDS_TRACE_FILE=<path> [GNNUDS_TRACE_LAUNCH=k]: clock64 stamps of CTA 0 of the k-th sp_conv launch
@@ -1243,10 +1242,9 @@ int launch_conv_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const Layer
   if (smem > 227 * 1024) return -1;
   for (int i = 0; i < p.nseg; ++i)
     if (!make_rows_tmap(&p.tm[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox, segs[i].width)) return -1;
-  static bool attr_set = false;
-  if (!attr_set) {
+  if (!h->attr_done[4]) {
     CU(cudaFuncSetAttribute(conv_agg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
+    h->attr_done[4] = true;
   }
   const unsigned grid = (unsigned)std::min<long long>(S, h->sm_count);
   static int traced = 0;
@@ -1507,7 +1505,12 @@ int ensure_workspace(gnnuds_handle* h, int64_t Bc) {
   }
   size_t total = 0;
   for (auto& it : plan) total += (size_t)((it.bytes + 255) / 256 * 256);
-  CU(cudaMalloc(&h->d_ws, total));
+  if (cudaMalloc(&h->d_ws, total) != cudaSuccess) {
+    (void)cudaGetLastError();
+    h->d_ws = nullptr; h->ws_chunk = 0;
+    return fail(h, GNNUDS_E_NOMEM, "workspace of %zu MB for %lld scenarios per pass does not fit the device (lower max_chunk / workspace_mb)",
+                total >> 20, (long long)Bc);
+  }
   CU(cudaMemsetAsync(h->d_ws, 0, total, h->stream));
   size_t off = 0;
   for (auto& it : plan) { *it.p = reinterpret_cast<float*>(reinterpret_cast<char*>(h->d_ws) + off); off += (size_t)((it.bytes + 255) / 256 * 256); }
@@ -1519,7 +1522,7 @@ int ensure_workspace(gnnuds_handle* h, int64_t Bc) {
 int64_t pick_chunk(const gnnuds_handle* h, int64_t B) {
   const auto& c = h->c;
   if (c.max_chunk > 0) return std::min<int64_t>(B, c.max_chunk);
-  const int64_t budget = (int64_t)(c.workspace_mb > 0 ? c.workspace_mb : 8192) * 1024 * 1024 / 4;
+  const int64_t budget = (int64_t)(c.workspace_mb > 0 ? c.workspace_mb : 8192 /* include/gnnuds.h: 0 = 8192 MB */) * 1024 * 1024 / 4;
   int64_t bc = budget / floats_per_scenario(c) * (h->tc() ? 2 : 1);
   if (bc < 1) bc = 1;
   return std::min(B, bc);
@@ -1778,7 +1781,7 @@ int gnnuds_set_graph(gnnuds_handle* h, const gnnuds_graph* g) {
     void* old[] = {h->d_pump, h->d_offset, h->d_pump_in, h->d_pump_out, h->d_area, h->d_edge_from, h->d_ps};
     for (void* q : old) if (q) cudaFree(q);
     h->d_pump = h->d_offset = h->d_pump_in = h->d_pump_out = h->d_area = nullptr; h->d_edge_from = h->d_ps = nullptr;
-    h->n_ps = 0; h->has_pump = h->has_offset = false;
+    h->n_ps = 0; h->has_pump = h->has_offset = false; h->pump_all = false;
     auto any = [](const float* v, int n) { if (!v) return false; for (int i = 0; i < n; ++i) if (v[i] != 0.f) return true; return false; };
     const bool pm = any(g->pump, M) || any(g->pump_in, N) || any(g->pump_out, N), of = any(g->offset, M);
     if ((pm || of) && c.graph_base) return fail(h, GNNUDS_E_INVALID, "pumps / inlet offsets with graph_base != 0 are not supported");
@@ -1802,6 +1805,8 @@ int gnnuds_set_graph(gnnuds_handle* h, const gnnuds_graph* g) {
       h->n_ps = (int)ps.size();
       if (h->n_ps && (rc = upload(h, &h->d_ps, ps.data(), ps.size()))) return rc;
       h->has_pump = true;
+      h->pump_all = g->pump != nullptr;
+      for (int m = 0; m < M && h->pump_all; ++m) h->pump_all = g->pump[m] > 0.f;
     }
   }
   h->has_graph = true;
@@ -1991,6 +1996,13 @@ int gnnuds_set_norm(gnnuds_handle* h, const float* norm_x, int32_t c_x, const fl
   return 0;
 }
 
+int gnnuds_set_post_proc_variant(gnnuds_handle* h, int32_t variant) {
+  if (!h) return GNNUDS_E_INVALID;
+  if (variant != 0 && variant != 1) return fail(h, GNNUDS_E_INVALID, "post-processing variant %d unknown (0 numpy, 1 tf)", variant);
+  h->pp_variant = variant;
+  return 0;
+}
+
 int gnnuds_tc_operand_is_half(void) { return GU_F16 ? 16 : 0; }
 
 int gnnuds_output_dims(const gnnuds_handle* h, int32_t* y_channels, int32_t* ey_channels) {
@@ -2139,6 +2151,11 @@ int gnnuds_rollout(gnnuds_handle* h, int32_t rule, const float* x0, const float*
   begin_timing(h);
   if (h->profiling) cudaEventRecord(h->ev_a, h->stream);
   rc = 0;
+  // every autoregressive loop of the reference runs the TF variant of the post-processing (mpc.py:575 and mbrl.py:337
+  // call predict_tf, emulator.py:413 calls post_proc_tf)
+  const int saved_variant = h->pp_variant;
+  h->pp_variant = 1;
+  struct Restore { gnnuds_handle* h; int v; ~Restore() { h->pp_variant = v; } } restore{h, saved_variant};
   for (int64_t b0 = 0; b0 < B && !rc; b0 += Bc) {
     const int64_t nb = std::min(Bc, B - b0);
     const float *hb = b + b0 * sbh, *ha = a ? a + b0 * sah : nullptr;

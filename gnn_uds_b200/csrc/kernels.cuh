@@ -40,13 +40,20 @@ __device__ __forceinline__ float4 ld4(const bf16* p) {
   const float2 a = unpack2_16(u.x), b = unpack2_16(u.y);
   return make_float4(a.x, a.y, b.x, b.y);
 }
+// fp16 storage saturates at +-65504 instead of overflowing to inf (a trained model with large activations must not
+// turn into inf -> NaN behind the bounded heads); NaN stays NaN
+__device__ __forceinline__ uint32_t cvt_f16x2_sat(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
 __device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
 #if GU_F16
-  __half2 v = __floats2half2_rn(lo, hi);
+  return cvt_f16x2_sat(lo, hi);
 #else
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
-#endif
   return *reinterpret_cast<uint32_t*>(&v);
+#endif
 }
 __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 __device__ __forceinline__ void st4(bf16* p, float4 v) {
@@ -60,7 +67,7 @@ __device__ __forceinline__ float ld1(const bf16* p) { return __bfloat162float(*p
 #endif
 __device__ __forceinline__ void st1(float* p, float v) { *p = v; }
 #if GU_F16
-__device__ __forceinline__ void st1(bf16* p, float v) { *p = __float2half_rn(v); }
+__device__ __forceinline__ void st1(bf16* p, float v) { *reinterpret_cast<unsigned short*>(p) = (unsigned short)(cvt_f16x2_sat(v, 0.f) & 0xFFFFu); }
 #else
 __device__ __forceinline__ void st1(bf16* p, float v) { *p = __float2bfloat16_rn(v); }
 #endif
@@ -1116,6 +1123,8 @@ struct PostP {
   const int* edge_from;   // (M) FromNode of a link: np.matmul(v, clip(node_edge,0,1))[m] = v[from(m)]
   const float* pump; const float* offset;        // (M)
   const float* pump_in; const float* pump_out;   // (N)
+  int tf_rules;           // post_proc_tf (emulator.py:680-725): node-side pump gates use h > 0 instead of h > 0.01; the host
+                          // passes pump == null unless every link is a pump (emulator.py:698)
   float* hn_g;            // (S, N) scratch for the normalised node depth when the edge pass needs it and N floats exceed smem
 };
 
@@ -1198,7 +1207,7 @@ __global__ void __launch_bounds__(512) postproc_kernel(PostP p) {
         yn[1] = src[1]; yn[2] = src[2];
         if (p.act) {                                             // emulator.py:661-670
           if (p.pump_in) {
-            const float on = hN > 0.01f ? 1.f : 0.f;
+            const float on = hN > (p.tf_rules ? 0.f : 0.01f) ? 1.f : 0.f;
             const float fli = p.pump_in[n] * on / p.ymax[n * p.cy + 1], flo = p.pump_out[n] * on / p.ymax[n * p.cy + 2];
             if (fli != 0.f) yn[1] = fli;
             if (flo != 0.f) yn[2] = flo;

@@ -210,17 +210,20 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {    // the build's 16-bit storage type (kernels.cuh)
 #ifdef GNNUDS_TC_BF16
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
-#else
-  __half2 v = __floats2half2_rn(lo, hi);
-#endif
   return *reinterpret_cast<uint32_t*>(&v);
+#else
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));   // saturating: no inf from overflow
+  return r;
+#endif
 }
 __device__ __forceinline__ uint4 pack8_bf16(const float* v) {
   return make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
 }
 __device__ __forceinline__ uint32_t pack_f16(float lo, float hi) {
-  __half2 v = __floats2half2_rn(lo, hi);
-  return *reinterpret_cast<uint32_t*>(&v);
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
 }
 __device__ __forceinline__ uint4 pack8_f16(const float* v) {
   return make_uint4(pack_f16(v[0], v[1]), pack_f16(v[2], v[3]), pack_f16(v[4], v[5]), pack_f16(v[6], v[7]));

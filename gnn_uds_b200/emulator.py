@@ -376,7 +376,14 @@ class Emulator:
         return self._run_predict(x, b, a, ex)
 
     def predict_tf(self, states, b, a=None, edge_state=None):           # emulator.py:604-641 (forward only)
-        return self.predict(states, b, a, edge_state)
+        """Same pipeline with the reference's TF post-processing rules (post_proc_tf, emulator.py:680-725): on pumped
+        networks the rated pump flow is applied to the links only when every link is a pump and the node-side pump
+        gates use h > 0 - the variant the MPC / MBRL callers run (mpc.py:250,575; mbrl.py:337)."""
+        _lib.check(self._h, self._lib.gnnuds_set_post_proc_variant(self._h, 1))
+        try:
+            return self.predict(states, b, a, edge_state)
+        finally:
+            self._lib.gnnuds_set_post_proc_variant(self._h, 0)
 
     def simulate(self, states, runoff, a=None, edge_states=None):       # emulator.py:521-564
         """All T' teacher-forced windows as one batch (the reference loops batch-1 per index).

@@ -13,7 +13,10 @@ import numpy as np
 from . import graph as _graph
 
 
-def make_norms(n_node, n_edge, if_flood, rng, tide=False):
+def make_norms(n_node, n_edge, if_flood, rng, tide=False, head_min=None, is_outfall=None, head_max=None):
+    """head_min (scalar): head-based network (dataloader.py:231-232,246-253): the h channel is normalised between the
+    global minimum head and the global maximum head, so norm_x/norm_y carry a NON-ZERO minimum in channel 0 and
+    norm_b (tide) one at the outfalls."""
     q = rng.uniform(0.5, 5.0, size=(n_node, 4)).astype(np.float32)       # h, q_us, q_ds, r maxima
     one = np.ones((n_node, 1), np.float32)
     qw = np.full((n_node, 1), np.float32(q[:, 1].max()))
@@ -29,6 +32,18 @@ def make_norms(n_node, n_edge, if_flood, rng, tide=False):
     ne = rng.uniform(0.5, 5.0, size=(n_edge, 4)).astype(np.float32)
     ne[:, 3] = 1.0
     st = lambda a: np.stack([a, np.zeros_like(a)]).astype(np.float32)
+    if head_min is not None:
+        hm = np.float32(head_max + 1e-6)
+        nx[:, 0] = hm; ny[:, 0] = hm
+        out = dict(norm_x=st(nx), norm_y=st(ny), norm_r=st(q[:, 3:4]), norm_e=st(ne))
+        out["norm_x"][1, :, 0] = np.float32(head_min)
+        out["norm_y"][1, :, 0] = np.float32(head_min)
+        if tide:
+            nb[:, 1] = hm * np.asarray(is_outfall, np.float32) + 1e-6
+        out["norm_b"] = st(nb)
+        if tide:
+            out["norm_b"][1, :, 1] = np.float32(head_min) * np.asarray(is_outfall, np.float32)
+        return out
     return dict(norm_x=st(nx), norm_b=st(nb), norm_y=st(ny), norm_r=st(q[:, 3:4]), norm_e=st(ne))
 
 
@@ -48,6 +63,9 @@ def make_inputs(emul, B, rng, horizon=None, shared_state=False):
     Bs = 1 if shared_state else B
     hmax = np.where(emul.hmax > 0, emul.hmax, 1.0)
     h = rng.uniform(0, 1, (Bs, Ti, N)) * hmax
+    hmin = np.asarray(getattr(emul, "hmin", 0.0), np.float64)
+    if np.max(hmin) > 0:                                   # head-based: h between the invert elevation and the rim
+        h = hmin + rng.uniform(0, 1, (Bs, Ti, N)) * np.where(emul.hmax - hmin > 0, emul.hmax - hmin, 1.0)
     q_us = rng.uniform(0, 1, (Bs, Ti, N)) * nx[:, 1]
     q_ds = rng.uniform(0, 1, (Bs, Ti, N)) * nx[:, 2]
     pulse = chicago_pulse(Ti + Th, rng, (B, 1)) * rng.uniform(0, 1, (B, 1, 1))       # (B,1,Ti+Th)
@@ -61,6 +79,9 @@ def make_inputs(emul, B, rng, horizon=None, shared_state=False):
     b = rain[:, Ti:, :, None]
     if emul.tide:
         tide = rng.uniform(0, 1, (B, Th, N)) * nb[:, 1] * emul.is_outfall
+        if np.max(hmin) > 0:                               # tide level as a head above the global minimum
+            lo = float(emul.norm_b[1][:, 1].max())
+            tide = (lo + rng.uniform(0, 1, (B, Th, N)) * (nb[:, 1] - lo)) * emul.is_outfall
         b = np.concatenate([b, tide[..., None]], -1)
     ehmax = np.where(emul.ehmax > 0, emul.ehmax, 1.0)
     depth = rng.uniform(0, 1, (Bs, Ti, M)) * ehmax

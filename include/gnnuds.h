@@ -62,7 +62,7 @@ typedef struct gnnuds_config {
   int32_t precision;       /* GNNUDS_PREC_* */
   int32_t device;          /* CUDA ordinal */
   int32_t max_chunk;       /* scenarios per internal pass; 0 = auto from workspace_mb */
-  int32_t workspace_mb;    /* activation workspace budget; 0 = 4096 */
+  int32_t workspace_mb;    /* activation workspace budget in MB; 0 = 8192 (the tensor-core path fits twice the scenarios in it) */
 } gnnuds_config;
 
 /* per-network vectors, get_args (envs/scenario/base.py:277-332) + emulator.py:71-98 */
@@ -114,6 +114,14 @@ int gnnuds_set_norm(gnnuds_handle* h, const float* norm_x, int32_t c_x,
                     const float* norm_b, int32_t c_b,
                     const float* norm_y, int32_t c_y,
                     const float* norm_e, int32_t c_e);
+
+/* Which of the reference's two post-processing variants gnnuds_predict / gnnuds_simulate follow:
+   0 = post_proc (NumPy, emulator.py:643-678; what Emulator.predict and simulate run),
+   1 = post_proc_tf (emulator.py:680-725; what predict_tf runs).  They differ on pumped networks only: the TF
+   variant applies the rated pump flow to the link flows only when every link is a pump (pump.min()>0, :698) and
+   gates pump_in / pump_out on h > 0 instead of h > 0.01 (:710-711).  gnnuds_rollout always uses variant 1
+   (mpc.py:575, mbrl.py:337, emulator.py:413 call the TF variant). */
+int gnnuds_set_post_proc_variant(gnnuds_handle* h, int32_t variant);
 
 /* 16-bit operand type of this build's tensor-core path: 16 = IEEE fp16 (default), 0 = bfloat16 (-DGNNUDS_TC_BF16).
    No handle needed. */

@@ -481,7 +481,10 @@ class OracleEmulator:
         a_in[..., self.act_edges[:, 1]] = a
         return a_out, a_in
 
-    def post_proc(self, y, ey, a, b):                                # emulator.py:643-678
+    def post_proc(self, y, ey, a, b, tf=False):                      # emulator.py:643-678 (numpy) / 680-725 (tf=True)
+        """tf=True follows post_proc_tf, which differs on pumped networks: the rated pump flow overrides the edge
+        flow only when EVERY link is a pump (``self.pump.min()>0``, :698) and the node-side pump gates use ``>0``
+        instead of ``>0.01`` (:710-711).  The inlet-offset gate (:688) is the same arithmetic in both."""
         ne = self.node_edge.astype(np.float64 if self.dtype == np.float64 else np.float32)
         if self.tide:
             h = y[..., 0] * (1 - self.is_outfall) + b[..., -1]
@@ -493,15 +496,17 @@ class OracleEmulator:
         ey = np.concatenate([ey[..., :-1], flow], axis=-1)
         if self.act:
             ae = self.get_edge_action(a)
-            fl = self.pump * np.matmul(y[..., 0] > 0.01, np.clip(ne, 0, 1))
-            fl = fl * ((self.norm_e[0, :, 2] > 1e-3) / self.norm_e[0, :, 2])
             ey = ey.copy()
-            ey[..., -1] = ey[..., -1] * (fl == 0) + fl
+            if not tf or np.min(self.pump) > 0:
+                fl = self.pump * np.matmul(y[..., 0] > 0.01, np.clip(ne, 0, 1))
+                fl = fl * ((self.norm_e[0, :, 2] > 1e-3) / self.norm_e[0, :, 2])
+                ey[..., -1] = ey[..., -1] * (fl == 0) + fl
             ey[..., -1:] *= ae
             if not self.edge_fusion:
                 a_out, a_in = self.get_action(a[:, :self.seq_out, ...])
-                fli = self.pump_in * (y[..., 0] > 0.01) / self.norm_y[0, :, 1]
-                flo = self.pump_out * (y[..., 0] > 0.01) / self.norm_y[0, :, 2]
+                thr = 0.0 if tf else 0.01
+                fli = self.pump_in * (y[..., 0] > thr) / self.norm_y[0, :, 1]
+                flo = self.pump_out * (y[..., 0] > thr) / self.norm_y[0, :, 2]
                 y = y.copy()
                 y[..., 1] = y[..., 1] * (fli == 0) + fli
                 y[..., 2] = y[..., 2] * (flo == 0) + flo
@@ -539,7 +544,7 @@ class OracleEmulator:
     def has_pumps(self):
         return float(np.sum(self.pump_in) + np.sum(self.pump_out) + np.sum(self.pump)) > 0
 
-    def predict(self, states, b, a=None, edge_state=None):           # emulator.py:566-602
+    def predict(self, states, b, a=None, edge_state=None, tf=False):  # emulator.py:566-602 (tf=True: 604-641)
         dt = self.dtype
         x = np.asarray(states)[:, -self.seq_in:, ...].astype(dt)
         ex = np.asarray(edge_state)[:, -self.seq_in:, ...].astype(dt)
@@ -548,7 +553,7 @@ class OracleEmulator:
         ae = self.get_edge_action(np.asarray(a).astype(dt)) if self.act else None
         nb = self.normalize(b, "b").astype(dt)
         y, ey = self.model(self.normalize(x, "x"), nb, self.normalize(ex, "e"), ae)
-        y, ey = self.post_proc(y, ey, None if a is None else np.asarray(a).astype(dt), nb)
+        y, ey = self.post_proc(y, ey, None if a is None else np.asarray(a).astype(dt), nb, tf=tf)
         y = self.normalize(y, "y", True)
         ey = self.normalize(ey, "e", True)
         ey = np.concatenate([np.clip(ey[..., 0], 0, self.ehmax)[..., None], ey[..., 1:]], axis=-1)
@@ -566,7 +571,8 @@ class OracleEmulator:
         y = np.concatenate([y, q_w[..., None]], axis=-1)
         return y.astype(dt), ey.astype(dt)
 
-    predict_tf = predict   # same pipeline for pump-free, offset-free networks (emulator.py:604-641)
+    def predict_tf(self, states, b, a=None, edge_state=None):        # emulator.py:604-641
+        return self.predict(states, b, a, edge_state, tf=True)
 
     def simulate(self, states, runoff, a=None, edge_states=None):    # emulator.py:521-564
         """Per-index batch-1 loop in the reference; every window is independent, so the
@@ -585,7 +591,7 @@ class OracleEmulator:
             if self.if_flood and idx > 0:
                 f = (perf > 0).astype(state.dtype)
                 state = np.concatenate([state[..., :-1], f, state[..., -1:]], axis=-1)
-            y, ey = self.predict(state, ri, sett, edge_state)
+            y, ey = self.predict_tf(state, ri, sett, edge_state)          # mpc.py:575
             state, perf = np.concatenate([y[..., :-2], ri], axis=-1), y[..., -1:]
             ae = self.get_edge_action(sett) if self.act else np.ones(ey.shape[:-1] + (1,), ey.dtype)
             edge_state = np.concatenate([ey, ae.astype(ey.dtype)], axis=-1)
@@ -598,7 +604,7 @@ class OracleEmulator:
         for i in range(b.shape[1] // To):
             bi = b[:, i * To:(i + 1) * To, ...]
             sett = settings[:, i * To:(i + 1) * To, :] if settings is not None else None
-            y, ey = self.predict(x, bi, sett, ex)
+            y, ey = self.predict_tf(x, bi, sett, ex)                     # mbrl.py:337
             if self.if_flood:
                 x = np.concatenate([y[..., :-2], (y[..., -2:-1] > 0.5).astype(y.dtype), bi], axis=-1)
             else:
@@ -619,7 +625,7 @@ class OracleEmulator:
             ai = a[:, i * To:(i + 1) * To, ...] if a is not None else None
             aei = self.get_edge_action(np.asarray(ai, dtype=dt)) if self.act else None
             y, ey = self.model(x[:, -Ti:], bi, ex[:, -Ti:], aei)
-            y, ey = self.post_proc(y, ey, ai, bi)
+            y, ey = self.post_proc(y, ey, ai, bi, tf=True)               # emulator.py:413 post_proc_tf
             P.append(y); EP.append(ey)
             if self.if_flood:
                 x_new = np.concatenate([y[..., :-1], (y[..., -1:] > 0.5).astype(dt), bi], axis=-1)

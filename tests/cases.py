@@ -58,6 +58,15 @@ CASES = {
     "ast_pump_act_nofusion": dict(net="astlingen", conv="GCN", recurrent="GRU", resnet=False, seq_in=5, seq_out=5,
                                   embed_size=128, hidden_dim=64, n_sp_layer=1, n_tp_layer=1, length=0, order=1,
                                   act="conti", pumps=True, B=3, seed=52),
+    # hague-style head-based network (base.py:289-292, dataloader.py:231-253, hague.py:115-136): h is a head, hmin =
+    # invert elevation > 0, norm_x / norm_y / norm_b carry NON-ZERO minima, tide boundary, inlet offsets
+    "ast_head_tide_offset": dict(net="astlingen", conv="GAT", recurrent="Conv1D", resnet=True, seq_in=6, seq_out=6,
+                                 embed_size=128, hidden_dim=64, n_sp_layer=2, n_tp_layer=2, length=1.0, order=1,
+                                 edge_fusion=True, if_flood=2, act="conti", epsilon=0.1, tide=True, head=True,
+                                 offsets=True, B=4, seed=56),
+    "ast_head_gcn_gru_nofusion": dict(net="astlingen", conv="GCN", recurrent="GRU", resnet=False, seq_in=5, seq_out=5,
+                                      embed_size=128, hidden_dim=64, n_sp_layer=1, n_tp_layer=1, length=0, order=1,
+                                      head=True, B=3, seed=57),
     # graph_base=2: the same joint conv over the link-based graph of base.py:500-532 (asymmetric rows, order 2)
     "ast_edgebased_gcn_lstm_act": dict(net="astlingen", conv="GCN", recurrent="LSTM", resnet=True, seq_in=4, seq_out=4,
                                        embed_size=64, hidden_dim=64, n_sp_layer=2, n_tp_layer=1, length=0, order=2,
@@ -72,7 +81,7 @@ CASES = {
 GOLDEN_CASES = ["c1_ast_gcn_gru", "c2_shq_gat_conv_10", "c3_ast_act_5", "ast_gat_gru_noflood",
                 "ast_gcn_lstm_act_nofusion", "ast_gcn_conv_eps0", "ast_joint_gcn_gru_act", "ast_joint_gat_conv_act",
                 "ast_pump_act_fusion", "ast_pump_act_nofusion", "ast_nn_conv_act_fusion", "shq_nn_gru",
-                "ast_edgebased_gcn_lstm_act"]
+                "ast_edgebased_gcn_lstm_act", "ast_head_tide_offset", "ast_head_gcn_gru_nofusion"]
 
 
 def load_net(name):
@@ -89,8 +98,15 @@ def build_args(case):
     net, act_links = load_net(hp.pop("net"))
     length, order = hp.pop("length"), hp.pop("order")
     B, seed = hp.pop("B"), hp.pop("seed")
-    ga = G.get_args(net, False, length, order, hp.get("graph_base", 0), act_links=act_links if hp.get("act") else None)
+    head = hp.pop("head", False)
+    ga = G.get_args(net, False, length, order, hp.get("graph_base", 0), act_links=act_links if hp.get("act") else None,
+                    head=head)
     d = dict(vars(ga))
+    if hp.pop("offsets", False):
+        rng = np.random.default_rng(2000 + seed)
+        off = np.zeros(len(net.links))
+        off[::5] = rng.uniform(0.2, 1.0, size=len(off[::5]))
+        d["offset"] = off
     if hp.pop("pumps", False):
         # synthetic pump table in the format of chaohu.get_args (chaohu.py:203-226): rated flows on the controlled
         # links, their in/out-flow seen from the end nodes, inlet offsets on every 7th conduit
@@ -124,8 +140,12 @@ def model_data(case, specs_from):
     specs = Wt.layer_specs(specs_from)
     ws = Wt.init_weights(specs, seed, node_edge_bias_std=0.05, bias_std=0.05)
     rng = np.random.default_rng(seed)
+    hmin = np.asarray(getattr(args, "hmin", 0.0), np.float64)
+    head_kw = {}
+    if np.max(hmin) > 0:
+        head_kw = dict(head_min=float(hmin.min()) - 0.5, head_max=float(np.max(args.hmax)), is_outfall=args.is_outfall)
     norms = synthetic.make_norms(specs_from.n_node, specs_from.n_edge, specs_from.if_flood, rng,
-                                 tide=getattr(specs_from, "tide", False))
+                                 tide=getattr(specs_from, "tide", False), **head_kw)
     return ws, norms, rng, B
 
 
@@ -140,6 +160,7 @@ class SpecShim:
         self.act, self.if_flood, self.tide = o.act, o.if_flood, o.tide
         self.seq_in, self.seq_out = o.seq_in, o.seq_out
         self.hmax, self.ehmax, self.is_outfall = o.hmax, o.ehmax, o.is_outfall
+        self.hmin = o.hmin
         self.n_act = len(o.act_edges) if o.act else 0
 
 

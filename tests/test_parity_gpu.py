@@ -78,6 +78,35 @@ def test_predict_matches_oracle(case):
         assert flips <= 1e-3
 
 
+@pytest.mark.parametrize("case", ["ast_pump_act_fusion", "ast_pump_act_nofusion", "c3_ast_act_5"])
+@pytest.mark.parametrize("all_pumps", [False, True])
+def test_predict_tf_follows_post_proc_tf(case, all_pumps, monkeypatch):
+    """predict_tf runs post_proc_tf (emulator.py:680-725), which differs from post_proc on pumped networks: rated pump
+    flows override link flows only if EVERY link is a pump (:698), node-side gates use h > 0 (:710-711)."""
+    if all_pumps:
+        if "pump" not in case:
+            pytest.skip("pump-free case")
+        orig = cases.build_args
+
+        def patched(c):
+            args, B, seed = orig(c)
+            args.pump = np.where(args.pump > 0, args.pump, 0.07)      # every link a pump -> pump.min() > 0
+            return args, B, seed
+        monkeypatch.setattr(cases, "build_args", patched)
+    em, inp = cases.setup_product(case)
+    o, inp_o = cases.make_oracle(case, np.float64)
+    y, ey = em.predict_tf(*inp)
+    y64, ey64 = o.predict_tf(*inp_o)
+    _check(case + " tf y", y, y64, mask=_flag_mask(em, y64))
+    _check(case + " tf ey", ey, ey64)
+    yn, eyn = em.predict(*inp)                                        # the handle is back on the numpy rules
+    y64n, ey64n = o.predict(*inp_o)
+    _check(case + " np y", yn, y64n, mask=_flag_mask(em, y64n))
+    _check(case + " np ey", eyn, ey64n)
+    if "pump" in case and not all_pumps:
+        assert np.abs(ey64 - ey64n).max() > 1e-3                       # the two variants really differ here
+
+
 @pytest.mark.parametrize("case", cases.GOLDEN_CASES)
 def test_predict_matches_committed_golden(case):
     z = np.load(os.path.join(cases.GOLD, "fwd_%s.npz" % case))
@@ -157,9 +186,44 @@ def test_rollout_norm_rule():
     xn, bn, exn = em.normalize(states, "x").astype(np.float32), em.normalize(b, "b").astype(np.float32), em.normalize(ex, "e").astype(np.float32)
     y, ey = em.rollout(xn, bn, a, exn, rule="norm")
     y64, ey64 = o.rollout_norm(xn.astype(np.float64), a.astype(np.float64), bn.astype(np.float64), exn.astype(np.float64))
-    sl = slice(0, em.seq_out)
-    _check("norm chunk0 y", y[:, sl], y64[:, sl])
-    _check("norm chunk0 ey", ey[:, sl], ey64[:, sl])
+    # every chunk of the roll loop (emulator.py:416-423 feeds post_proc'ed, UNclipped predictions + the 0.5-thresholded
+    # flood flag back): a scenario stays comparable until its flag (prob > 0.5) could flip on rounding
+    T = em.seq_out
+    ok = np.ones(y.shape[0], bool)
+    good = 0
+    for k in range(3):
+        sl = slice(k * T, (k + 1) * T)
+        assert ok.any()
+        _check("norm chunk %d y" % k, y[ok, sl], y64[ok, sl], rtol=2e-5 * (k + 1))
+        _check("norm chunk %d ey" % k, ey[ok, sl], ey64[ok, sl], rtol=2e-5 * (k + 1))
+        good += int(ok.sum())
+        near = (np.abs(y64[:, sl, :, -1] - 0.5) < 1e-4).any(axis=(1, 2))
+        ok &= ((y[:, sl, :, -1] > 0.5) == (y64[:, sl, :, -1] > 0.5)).all(axis=(1, 2)) & ~near
+    assert good >= 4 * 2 + 2, good      # the feedback step itself is verified on (nearly) every scenario
+
+
+def test_simulate_c_abi_window_repack_and_error_path():
+    """gnnuds_simulate straight through ctypes: runoff windows longer than seq_out (the C side repacks the first
+    seq_out steps, emulator.py:532) equal predict on the cut windows; device pointers with seq_r > seq_out are refused."""
+    import ctypes as C
+    from gnn_uds_b200 import _lib
+    em, (states, b, a, ex) = cases.setup_product("c2_shq_gat_conv_10")
+    B, To = states.shape[0], em.seq_out
+    seq_r = To + 3
+    rng = np.random.default_rng(11)
+    runoff = np.concatenate([b, rng.uniform(0, 1, (B, 3) + b.shape[2:]).astype(np.float32)], axis=1)
+    y = np.empty((B, To, em.n_node, em.y_channels), np.float32)
+    ey = np.empty((B, To, em.n_edge, em.ey_channels), np.float32)
+    vp = lambda t: t.ctypes.data_as(C.c_void_p)
+    rc = em._lib.gnnuds_simulate(em._h, vp(states), vp(runoff), seq_r, None, vp(ex), B, vp(y), vp(ey), _lib.MEM_HOST)
+    assert rc == 0, em._lib.gnnuds_last_error(em._h)
+    y2, ey2 = em.predict(states, b, None, ex)
+    assert np.array_equal(y, y2) and np.array_equal(ey, ey2)
+    rc = em._lib.gnnuds_simulate(em._h, vp(states), vp(runoff), seq_r, None, vp(ex), B, vp(y), vp(ey), _lib.MEM_DEVICE)
+    assert rc == _lib.E_INVALID if hasattr(_lib, "E_INVALID") else rc == -1
+    assert b"host buffers" in em._lib.gnnuds_last_error(em._h)
+    rc = em._lib.gnnuds_simulate(em._h, vp(states), vp(runoff), To - 1, None, vp(ex), B, vp(y), vp(ey), _lib.MEM_HOST)
+    assert rc == -1
 
 
 def test_objective_matches_oracle():
