@@ -9,9 +9,17 @@ A step = one Emulator.predict over one batch of synthetic scenarios.  At N=1 the
 BASELINE.json configs[1] (C2: shunqing GAT+Conv1D edge_fusion/resnet/flood, 60->60, B=4096).
 `value`   : inputs already resident in HBM, device-side timing (CUDA events), max over ranks.
 `e2e`     : the same through Emulator.predict with pinned HOST buffers (H2D + D2H inside).
-`roofline`: the dominant kernel family (the rows-GEMM) timed live with CUDA events.
+`e2e`     : the same through Emulator.predict with pinned HOST buffers (H2D + D2H inside); `e2e.numpy_api` is the
+            caller's real entry, Emulator.predict(states, b, a, edge_state) on ordinary (pageable) NumPy arrays.
+`roofline`: the dominant kernel family timed live with CUDA events on the library's stream.  Small-graph models
+            (graph_base 0, C1-C4) are dense contractions -> bound "tensor" (SURVEY 8d): achieved = the FLOPs the fused
+            spatial kernel executes per launch / its average launch time, peak = bf16_tflops_sustained.  The
+            layer-by-layer HBM view of the same kernel is kept as `design_hbm_frac`; `io_bytes_per_step` is 8(d)'s
+            algorithmic I/O (inputs + outputs), `traffic` the ncu dram bytes per launch.  graph_base 1 (C5): the CSR
+            gather, bound "hbm".
 `cpu_baseline`: the NumPy oracle (a port - the reference needs TF/spektral, absent here) on a
-                bounded sample of the same workload, rank 0, N=1 only.
+                bounded sample of the same workload, rank 0, N=1 only; `cpu_baseline_c1` is C1 exactly as
+                BASELINE.json words it (astlingen GCN+GRU 10->10, B=64), median of 5.
 """
 import argparse
 import json
@@ -94,16 +102,25 @@ def dominant_kernel(em, B, precision):
         return dict(family=2, kernel="agg_large_kernel (CSR neighbour gather, joint node+edge graph)", bound="hbm",
                     bytes=float(B * (Ti + To) * S * per_sample), unit_note="(nnz*E gathered + (N+M)*E written) * %d B per (b,t) sample and layer" % es)
     if precision != "bf16" or em.conv_kind == "nn":
-        return dict(family=0, kernel="rows_gemm_f32 (all Dense/conv-linear/Conv1D launches of a step)", bound="tensor", bytes=None, unit_note="")
+        return dict(family=0, kernel="rows_gemm_f32 (all Dense/conv-linear/Conv1D launches of a step)", bound="fp32", bytes=None, unit_note="")
     act = 1 if em.act else 0
-    tot = 0
+    gat = em.conv_kind == "gat"
+    nnz_n, nnz_m = em.filter_csr.nnz, em.edge_filter_csr.nnz
+    tot, fl = 0, 0
     for blk, T in ((0, Ti), (1, To)):
         cx, ce = (E, E) if blk == 0 else (H + E // 2, H + (E // 2) * act)
         for l in range(S):
             tot += B * T * ((N * cx + M * (E // 2) + N * E) + (M * ce + N * (E // 2) + M * E)) * 2
+            # what the fused kernel executes (2*MAC): NodeEdge both sides, conv linear part, GAT scores, CSR aggregation
+            fl += 2 * B * T * (2 * N * M * (E // 2) + N * (cx + E // 2) * E + M * (ce + E // 2) * E
+                               + (2 * (N + M) * E if gat else 0) + (nnz_n + nnz_m) * E)
             cx = ce = E
-    return dict(family=1, kernel="sp_conv_kernel (fused NodeEdge + conv + GAT/GCN aggregation, both stream sides)", bound="hbm",
-                bytes=float(tot), unit_note="per sample and side: (R*Kself + Ro*E/2 read + R*E written) * 2 B")
+    io = 4 * B * (Ti * (N * em.n_in + M * em.e_in) + To * (N * em.b_in + (em.n_act if em.act else 0))
+                  + To * (N * em.y_channels + M * em.ey_channels))
+    return dict(family=1, kernel="sp_agg_kernel / sp_conv_kernel (fused NodeEdge + conv + GAT/GCN aggregation, both stream sides)",
+                bound="tensor", bytes=float(tot), flops=float(fl), io_bytes=float(io),
+                unit_note="FLOPs per sample and side: 2*(R*Ro*E/2 + R*(Kself+E/2)*E [+ 2*R*E GAT scores] + nnz*E); "
+                          "design_hbm bytes: (R*Kself + Ro*E/2 read + R*E written) * 2 B")
 
 
 class ClockSampler:
@@ -383,7 +400,28 @@ def main():
                  "family_ms_per_step": {"rows_gemm": fam_ms[0] / a.steps, "fused_spatial": fam_ms[1] / a.steps,
                                         "csr_gather": fam_ms[2] / a.steps, "recurrent": fam_ms[3] / a.steps,
                                         "note": "per-launch event pairs of a separate K-step pass; the rest of the step is embed/heads/post-processing"}}
-        if dom["bound"] == "hbm":
+        if dom["bound"] == "tensor" and dom.get("flops"):
+            # C1-C4 are tensor-bound; achieved = FLOPs the fused spatial kernel executes per launch / launch time
+            fpl = dom["flops"] / launches_per_step
+            avg_ms = dom_ms_per_step / launches_per_step
+            achieved = fpl / (avg_ms * 1e-3) / 1e12 if avg_ms > 0 else None
+            hbm_ach = dom["bytes"] / (dom_ms_per_step * 1e-3) / 1e9 if dom_ms_per_step > 0 else None
+            tr = traffic_per_launch(dom, a.workload, B, launches_per_step)
+            roofline = {"bound": "tensor", "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s",
+                        "frac": (achieved / tf_peak) if achieved else None, "traffic": tr,
+                        "algorithmic_flops_per_launch": fpl, "peak_source": "%s bf16_tflops_sustained" % src,
+                        "design_hbm_frac": (hbm_ach / hbm_peak) if hbm_ach else None,
+                        "design_hbm_bytes_per_launch": dom["bytes"] / launches_per_step,
+                        "io_bytes_per_step": dom["io_bytes"],
+                        "traffic_over_io": (tr * launches_per_step / dom["io_bytes"]) if tr else None}
+        elif dom["bound"] == "fp32":
+            achieved = gemm_f / (gemm_ms_per_step * 1e-3) / 1e12 if gemm_ms_per_step > 0 else None
+            f32_peak = em.measure_fp32_tflops()
+            roofline = {"bound": "tensor", "achieved": achieved, "peak": f32_peak, "unit": "TFLOP/s",
+                        "frac": (achieved / f32_peak) if achieved and f32_peak else None, "traffic": None,
+                        "peak_source": "fp32 FFMA peak measured in this run (gnnuds_measure_fp32_tflops); the fp32 parity path runs on SIMT FMA, not tensor cores",
+                        "gemm_flops_per_step": gemm_f}
+        elif dom["bound"] == "hbm":
             achieved = dom["bytes"] / (dom_ms_per_step * 1e-3) / 1e9 if dom_ms_per_step > 0 else None
             roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                         "frac": (achieved / hbm_peak) if achieved else None,
@@ -402,7 +440,7 @@ def main():
             "config": {"workload": "%s: %s %s+%s edge_fusion=%s resnet=%s if_flood=%d act=%s, N=%d M=%d, seq %d->%d, B=%d per GPU" % (
                 a.workload, args.__dict__.get("env_name", configs.WORKLOADS[a.workload]["net"]), em.conv_kind.upper(), em.recurrent,
                 em.edge_fusion, em.resnet, em.if_flood, bool(em.act), N, M, Ti, To, B),
-                "l2": l2_note, "precision": precision, "sharding": "scenarios over ranks, no data-path collective"},
+                "l2": l2_note, "precision": ("f16" if em._lib.gnnuds_tc_operand_is_half() else "bf16") if precision == "bf16" else precision, "sharding": "scenarios over ranks, no data-path collective"},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "note": "Emulator.predict_ptrs with pinned host buffers, wall clock incl. copies"},
             "gpu_launches": int(launches),

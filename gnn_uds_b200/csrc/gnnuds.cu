@@ -9,6 +9,7 @@
 #include "tc_selftest.cuh"
 #include "fused_sp.cuh"
 #include "fused_conv.cuh"
+#include "fused_agg.cuh"
 #include "gru_tc.cuh"
 #include "nn_cat.cuh"
 
@@ -106,6 +107,12 @@ struct gnnuds_handle {
   int* d_prp[2] = {nullptr, nullptr}; int* d_pci[2] = {nullptr, nullptr}; float* d_pval[2] = {nullptr, nullptr};
   int pnnz[2] = {0, 0};
   int sp_max_len[2] = {0, 0};           // longest true CSR row per side (selects sp_conv's register softmax)
+  // sp_agg_kernel (csrc/fused_agg.cuh): unpadded block-diagonal CSR with per-entry alpha offsets, GCN values
+  int* d_arp[2] = {nullptr, nullptr}; uint32_t* d_acj[2] = {nullptr, nullptr}; float* d_aval[2] = {nullptr, nullptr};
+  int annz[2] = {0, 0};
+  std::vector<uint8_t*> d_cv_img[2];    // GAT conv weight images with the score columns (NW = E + 16 rows per panel)
+  std::vector<uint32_t> cv_img_bytes[2];
+  int sp_agg = 1;                       // GNNUDS_SP_AGG: 0 = sp_conv_kernel (SIMT gather) instead of sp_agg_kernel
   float *d_val = nullptr, *d_eval = nullptr;
   int nnz = 0, ennz = 0, n_adj = 0;
   int *d_edges = nullptr, *d_act_of_edge = nullptr, *d_act_out = nullptr, *d_act_in = nullptr;
@@ -1199,6 +1206,103 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   return 0;
 }
 
+// ---- fused spatial layer, aggregation on tensor cores (csrc/fused_agg.cuh) ----------------------
+// Returns 0 launched, -1 not applicable (caller tries sp_conv_kernel next), > 0 error.
+int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* other_dense, int side, int li,
+                  const LayerW& w, void* out, long long S, int R, int Ro, int act) {
+  const auto& c = h->c;
+  const int E = c.embed, F = E / 2;
+  const bool gat = c.conv == GNNUDS_CONV_GAT;
+  const long long rows_total = S * R, rows_other = S * Ro;
+  { const int g = h->sp_g; S = (S + g - 1) / g; R *= g; Ro *= g; }
+  if (h->fused_mode != 1 || !h->sp_agg || !h->sw128 || segs.empty() || segs.size() > 2 || R > 256 || Ro > 256 || R < 1 || E != 128) return -1;
+  if (S <= 0 || S * (long long)std::max(R, Ro) >= (1ll << 31) || !h->annz[side] || h->sp_max_len[side] > 20) return -1;
+  if (gat ? (int)h->d_cv_img[side].size() <= li : !h->d_aval[side]) return -1;
+  SpAggP p{};
+  p.nseg = (int)segs.size();
+  p.Kself = 0;
+  for (int i = 0; i < p.nseg; ++i) {
+    const SegH& sg = segs[i];
+    if (sg.shift || sg.pitch * h->sp_g != R || sg.off || sg.width % 64 || sg.ld % 8 || (reinterpret_cast<uintptr_t>(sg.p) & 15)) return -1;
+    p.segw[i] = sg.width; p.Kself += sg.width;
+  }
+  const int Ktot = p.Kself + F;
+  if ((long long)Ktot * E != h->tens[w.t[0]].numel || h->img_off[w.t[0]] < 0) return -1;
+  p.S = (int)S; p.R = R; p.Ro = Ro; p.F = F; p.Nout = E; p.act = act; p.gat = gat ? 1 : 0;
+  p.NW = gat ? E + 16 : E;
+  p.Rbox = (R + 7) / 8 * 8; p.Kp = h->ne_kp[side]; p.KpJ = (R + 15) / 16 * 16; p.MT = (R + 127) / 128;
+  if (p.Kp % 8) return -1;
+  p.nb_self = p.MT > 1 ? 1 : 2; p.alias_acc = p.MT > 1 ? 1 : 0;
+  p.max_len = h->sp_max_len[side];
+  p.pstrideP = (uint32_t)p.Rbox * 16u; p.pstrideM = h->ne_pstride[side]; p.pstrideH = (uint32_t)p.KpJ * 16u; p.pstrideAl = (uint32_t)p.Rbox * 16u;
+  if (gat) { p.Wimg = h->d_cv_img[side][li]; p.w_bytes = h->cv_img_bytes[side][li]; }
+  else { p.Wimg = h->d_wimg + h->img_off[w.t[0]]; p.w_bytes = (uint32_t)Ktot * E * 2u; }
+  if (p.w_bytes != (uint32_t)(Ktot / 8) * (uint32_t)p.NW * 16u) return -1;
+  p.Mimg = h->d_ne_img[side][li]; p.m_bytes = h->ne_img_bytes[side];
+  p.bias = W(h, w.t[gat ? 3 : 1]);
+  p.rp = h->d_arp[side]; p.cj = h->d_acj[side]; p.val = gat ? nullptr : h->d_aval[side]; p.nnz = h->annz[side];
+  p.out = static_cast<bf16*>(out); p.rows_total = rows_total;
+  auto al = [](uint32_t v, uint32_t a) { return (v + a - 1) / a * a; };
+  const uint32_t RP = 128u * p.MT;
+  p.chunk_bytes = (uint32_t)p.Rbox * 128u;
+  p.self_bytes = (uint32_t)(p.Kself / 64) * p.chunk_bytes;
+  p.xe_bytes = (uint32_t)p.Kp * 128u;
+  p.nx_bytes = (uint32_t)(F / 8) * p.pstrideP;
+  p.al_bytes = (uint32_t)(p.KpJ / 8) * p.pstrideAl;
+  const uint32_t h_bytes = (uint32_t)(E / 8) * p.pstrideH;
+  p.off_w = 0;
+  p.off_m = al(p.w_bytes, 128);
+  p.off_self = al(p.off_m + p.m_bytes, 1024);
+  p.self_stride = al(std::max(p.self_bytes, h_bytes), 1024);
+  p.off_xe = p.off_self + (uint32_t)p.nb_self * p.self_stride;
+  p.off_nx = al(p.off_xe + p.xe_bytes, 128);
+  p.off_al = al(p.off_nx + p.nx_bytes, 128);
+  p.off_sc = al(p.off_al + p.al_bytes, 128);
+  const uint32_t sc_bytes = ((uint32_t)E + 3u * RP) * 4u + ((uint32_t)R + 1u + (uint32_t)p.nnz) * 4u;
+  p.off_bar = al(p.off_sc + sc_bytes, 16);
+  // operand views of an M tile read 128 rows from the tile's first row of every panel / swizzle chunk: keep those
+  // reads inside the allocation
+  uint32_t reach = p.off_bar + 15u * 8u + 16u;
+  reach = std::max(reach, p.off_self + (uint32_t)(p.nb_self - 1) * p.self_stride + (uint32_t)(p.Kself / 64 - 1) * p.chunk_bytes + RP * 128u);
+  reach = std::max(reach, p.off_nx + (uint32_t)(F / 8 - 1) * p.pstrideP + RP * 16u);
+  reach = std::max(reach, p.off_al + (uint32_t)(p.KpJ / 8 - 1) * p.pstrideAl + RP * 16u);
+  reach = std::max(reach, p.off_m + (uint32_t)(p.Kp / 8 - 1) * p.pstrideM + RP * 16u);
+  const size_t smem = reach;
+  if (smem > 227 * 1024) return -1;
+  for (int i = 0; i < p.nseg; ++i)
+    if (!make_rows_tmap_sw(&p.tm_self[i], segs[i].p, rows_total, segs[i].ld, segs[i].width, p.Rbox)) return -1;
+  if (!make_rows_tmap_sw(&p.tm_other, other_dense, rows_other, F, F, p.Kp)) return -1;
+  if (!h->attr_done[5]) {
+    CU(cudaFuncSetAttribute(sp_agg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    h->attr_done[5] = true;
+  }
+  const unsigned grid = (unsigned)std::min<long long>(S, h->sm_count);
+  static int traced = 0;
+  const char* tf = getenv("GNNUDS_TRACE_FILE");
+  const int want = getenv("GNNUDS_TRACE_LAUNCH") ? atoi(getenv("GNNUDS_TRACE_LAUNCH")) : 0;
+  const bool do_trace = tf && S >= 64 * (long long)h->sm_count && traced++ == want;
+  const size_t tn = 64 * SA_NSTAMP;
+  if (do_trace) { CU(cudaMalloc(&p.trace, tn * sizeof(long long))); CU(cudaMemset(p.trace, 0, tn * sizeof(long long))); }
+  cudaEvent_t e1 = nullptr;
+  { int prc = prof_begin(h, GNNUDS_FAM_SPATIAL, &e1); if (prc) return prc; }
+  sp_agg_kernel<<<grid, SA_THREADS, smem, h->stream>>>(p);
+  ++h->launches;
+  { int prc = prof_end(h, e1); if (prc) return prc; }
+  CU(cudaGetLastError());
+  if (do_trace) {
+    std::vector<long long> t(tn);
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaMemcpy(t.data(), p.trace, tn * sizeof(long long), cudaMemcpyDeviceToHost));
+    cudaFree(p.trace);
+    if (FILE* f = fopen(tf, "w")) {
+      fprintf(f, "# sp_agg R=%d Ro=%d Kself=%d MT=%d smem=%zu: sample, cycles since first stamp: conv_done_seen h_ready alpha_ready ne_drained agg_done_seen out_done\n", R, Ro, p.Kself, p.MT, smem);
+      for (int i = 0; i < 64; ++i) { fprintf(f, "%d", i); for (int k = 0; k < 6; ++k) fprintf(f, " %lld", t[i * SA_NSTAMP + k] ? t[i * SA_NSTAMP + k] - t[0] : -1); fprintf(f, "\n"); }
+      fclose(f);
+    }
+  }
+  return 0;
+}
+
 // ---- fused conv + aggregation on tensor cores (csrc/fused_conv.cuh) -------------------------------
 // Returns 0 launched, -1 not applicable, > 0 error.
 int launch_conv_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const LayerW& w, void* out, const int* rp,
@@ -1287,7 +1391,8 @@ int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) 
     float* xo = (l & 1) ? h->XB : h->XA;
     float* eo = (l & 1) ? h->EB : h->EA;
     // fused NodeEdge + conv + aggregation per stream side; layer-by-layer kernels when it does not apply
-    rc = launch_sp_conv(h, st.x, h->XE, 0, li, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, M, act);
+    rc = launch_sp_agg(h, st.x, h->XE, 0, li, w.conv_x, xo, S, N, M, act);
+    if (rc < 0) rc = launch_sp_conv(h, st.x, h->XE, 0, li, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, M, act);
     if (rc > 0) return rc;
     if (rc < 0) {
       if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, h->XE, h->NX, S, M, N, E2))) return rc;
@@ -1296,7 +1401,8 @@ int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) 
       if (rc > 0) return rc;
       if (rc < 0 && (rc = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return rc;
     }
-    rc = launch_sp_conv(h, st.e, h->EX, 1, li, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, S, M, N, act);
+    rc = launch_sp_agg(h, st.e, h->EX, 1, li, w.conv_e, eo, S, M, N, act);
+    if (rc < 0) rc = launch_sp_conv(h, st.e, h->EX, 1, li, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, S, M, N, act);
     if (rc > 0) return rc;
     if (rc < 0) {
       if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, h->EX, h->NE, S, N, M, E2))) return rc;
@@ -1616,6 +1722,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   h->tma_on = !(getenv("GNNUDS_NO_TMA") && getenv("GNNUDS_NO_TMA")[0] == '1');
   if (getenv("GNNUDS_FUSED")) h->fused_mode = atoi(getenv("GNNUDS_FUSED"));
   if (getenv("GNNUDS_GRU_TC")) h->gru_tc = atoi(getenv("GNNUDS_GRU_TC"));
+  if (getenv("GNNUDS_SP_AGG")) h->sp_agg = atoi(getenv("GNNUDS_SP_AGG"));
   h->sp_g = std::max(1, std::min(8, 128 / std::max(1, std::max(c.n_node, c.n_edge))));
   if (getenv("GNNUDS_SP_GROUP")) h->sp_g = std::max(1, std::min(h->sp_g, atoi(getenv("GNNUDS_SP_GROUP"))));
   if (getenv("GNNUDS_SW128")) h->sw128 = atoi(getenv("GNNUDS_SW128"));
@@ -1663,6 +1770,27 @@ int upload_bins(gnnuds_handle* h, int side, const int* rp0, const int* ci0, cons
     if ((rc = upload(h, &h->d_pval[side], pval.data(), pval.size()))) return rc;
     h->pnnz[side] = prp[R];
   }
+  {  // sp_agg_kernel tables: alpha[i][j] of the dense K-major operand sits at (j/8)*pstrideAl + i*16 + (j%8)*2
+    const uint32_t pstrideAl = (uint32_t)((R + 7) / 8 * 8) * 16u;
+    std::vector<uint32_t> cj(std::max<size_t>(civ.size(), 1), 0u);
+    bool ok = R <= 256;
+    for (int r = 0; r < R && ok; ++r)
+      for (int k = rp[r]; k < rp[r + 1]; ++k) {
+        const uint32_t j = (uint32_t)ci[k], off = (j >> 3) * pstrideAl + (uint32_t)r * 16u + (j & 7u) * 2u;
+        if (off >= (1u << 24)) { ok = false; break; }
+        cj[k] = (off << 8) | j;
+      }
+    void* old[] = {h->d_arp[side], h->d_acj[side], h->d_aval[side]};
+    for (void* q : old) if (q) cudaFree(q);
+    h->d_arp[side] = nullptr; h->d_acj[side] = nullptr; h->d_aval[side] = nullptr; h->annz[side] = 0;
+    if (ok) {
+      int rc;
+      if ((rc = upload(h, &h->d_arp[side], rpv.data(), rpv.size()))) return rc;
+      if ((rc = upload(h, &h->d_acj[side], cj.data(), cj.size()))) return rc;
+      if (val && !valv.empty()) { if ((rc = upload(h, &h->d_aval[side], valv.data(), valv.size()))) return rc; }
+      h->annz[side] = (int)civ.size();
+    }
+  }
   // The four 8-lane groups of a warp run in lockstep: a warp's time is the sum over its row slots of the LONGEST row
   // of the slot.  So rows are sorted by length, cut into quads of similar length (one quad = one slot of one warp),
   // and the quads are spread over the warps longest-processing-time first.
@@ -1699,10 +1827,11 @@ int gnnuds_destroy(gnnuds_handle* h) {
   void* ptrs[] = {h->d_blob, h->d_rp, h->d_ci, h->d_erp, h->d_eci, h->d_val, h->d_eval, h->d_edges, h->d_act_of_edge,
                   h->d_act_out, h->d_act_in, h->d_inc_ptr, h->d_inc_edge, h->d_inc_sign, h->d_hmin, h->d_hmax,
                   h->d_outfall, h->d_ehmax, h->d_nx, h->d_nb, h->d_ny, h->d_ne, h->d_ws, h->ro_x, h->ro_ex, h->ro_b, h->ro_a, h->d_wimg,
-                  h->d_bins[0], h->d_bins[1], h->d_prp[0], h->d_prp[1], h->d_pci[0], h->d_pci[1], h->d_pval[0], h->d_pval[1], h->d_pump, h->d_offset, h->d_pump_in, h->d_pump_out, h->d_area, h->d_edge_from, h->d_ps};
+                  h->d_bins[0], h->d_bins[1], h->d_prp[0], h->d_prp[1], h->d_pci[0], h->d_pci[1], h->d_pval[0], h->d_pval[1], h->d_arp[0], h->d_arp[1], h->d_acj[0], h->d_acj[1], h->d_aval[0], h->d_aval[1], h->d_pump, h->d_offset, h->d_pump_in, h->d_pump_out, h->d_area, h->d_edge_from, h->d_ps};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_ne_img[s]) if (p) cudaFree(p);
+  for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_cv_img[s]) if (p) cudaFree(p);
   for (auto& e : h->gemm_ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (h->ev_a) cudaEventDestroy(h->ev_a);
   if (h->ev_b) cudaEventDestroy(h->ev_b);
@@ -1973,6 +2102,32 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
             h->d_ne_img[s].push_back(reinterpret_cast<uint8_t*>(d));
           }
         }
+      // GAT: conv weight images with 16 extra output columns [hi(W a_self) lo(W a_self) hi(W a_neigh) lo(W a_neigh) 0..]
+      // (hi/lo = 16-bit split of the fp32 product), so sp_agg_kernel reads the attention scores as accumulator columns
+      for (int s = 0; s < 2; ++s) { for (uint8_t* p : h->d_cv_img[s]) if (p) cudaFree(p); h->d_cv_img[s].clear(); h->cv_img_bytes[s].clear(); }
+      if (c.conv == GNNUDS_CONV_GAT && c.embed % 16 == 0)
+        for (int blk = 0; blk < 2; ++blk)
+          for (int l = 0; l < c.n_sp_layer; ++l) {
+            const SpatialW& w = h->sp[blk][l];
+            for (int s = 0; s < 2; ++s) {
+              const LayerW& lw = s == 0 ? w.conv_x : w.conv_e;
+              const int E = c.embed, NW = E + 16, Ktot = (int)(h->tens[lw.t[0]].numel / E);
+              const float* Wk = blob + offsets[lw.t[0]]; const float* as = blob + offsets[lw.t[1]]; const float* an = blob + offsets[lw.t[2]];
+              std::vector<float> wx((size_t)Ktot * NW, 0.f);
+              for (int k = 0; k < Ktot; ++k) {
+                double ds = 0.0, dn = 0.0;
+                for (int n = 0; n < E; ++n) { wx[(size_t)k * NW + n] = Wk[(size_t)k * E + n]; ds += (double)Wk[(size_t)k * E + n] * as[n]; dn += (double)Wk[(size_t)k * E + n] * an[n]; }
+                const float fs = (float)ds, fn = (float)dn, fsh = bf2f(f2bf(fs)), fnh = bf2f(f2bf(fn));
+                wx[(size_t)k * NW + E] = fsh; wx[(size_t)k * NW + E + 1] = fs - fsh;
+                wx[(size_t)k * NW + E + 2] = fnh; wx[(size_t)k * NW + E + 3] = fn - fnh;
+              }
+              std::vector<uint16_t> img = pack_kmajor(wx.data(), NW, Ktot, 1, NW, NW, Ktot, NW * 16);
+              uint16_t* d = nullptr;
+              if ((rc = upload(h, &d, img.data(), img.size()))) return rc;
+              h->d_cv_img[s].push_back(reinterpret_cast<uint8_t*>(d));
+              h->cv_img_bytes[s].push_back((uint32_t)(img.size() * 2));
+            }
+          }
     }
   }
   h->has_weights = true;
