@@ -187,8 +187,8 @@ def traffic_per_launch(dom, workload, B, launches_per_step):
     return d["dram_bytes_per_scenario_step"] * B / launches_per_step
 
 
-def cpu_baseline(workload, seconds=20.0):
-    """NumPy oracle (port) fp32 on a bounded sample of the workload; all BLAS threads."""
+def cpu_baseline(workload, seconds=20.0, fixed_B=None, runs=3):
+    """NumPy oracle (port) fp32 on a bounded sample of the workload (or exactly fixed_B scenarios); all BLAS threads."""
     import cases   # noqa: F401  (tests/cases.py helpers are not needed; keep path set up)
     from gnn_uds_b200 import configs, synthetic, weights as Wt
     from oracle.emulator_oracle import OracleEmulator
@@ -203,14 +203,14 @@ def cpu_baseline(workload, seconds=20.0):
     Bs = 1
     inp = synthetic.make_inputs(shim, Bs, rng)
     t0 = time.perf_counter(); o.predict(*inp); t1 = time.perf_counter() - t0      # warm-up + calibration
-    Bs = int(max(1, min(64, seconds / 3.0 / max(t1, 1e-3))))
+    Bs = int(fixed_B) if fixed_B else int(max(1, min(64, seconds / 3.0 / max(t1, 1e-3))))
     inp = synthetic.make_inputs(shim, Bs, rng)
     ts = []
-    for _ in range(3):
+    for _ in range(runs):
         t0 = time.perf_counter(); o.predict(*inp); ts.append(time.perf_counter() - t0)
     t = float(np.median(ts))
     return {"value": Bs * o.seq_out * o.n_node / t, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
-            "sample": "%s model, B=%d scenarios x %d steps, NumPy fp32 dense formulation, median of 3" % (workload, Bs, o.seq_out),
+            "sample": "%s model, B=%d scenarios x %d steps, NumPy fp32 dense formulation, median of %d" % (workload, Bs, o.seq_out, runs),
             "ms_per_sample_call": t * 1e3}
 
 
@@ -232,6 +232,100 @@ def run_reference(a):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": {"workload": a.workload},
             "cpu_baseline": res, "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
+
+
+def run_mpc(a):
+    """--workload C3mpc: BASELINE.json configs[2] as north_star words it - an 8192-candidate population (TOTAL, strong
+    scaling) x 60-step horizon = 12 autoregressive chunks of the astlingen act+edge_fusion+flood 5->5 model, candidates
+    sharded over the ranks, evaluated by MpcEvaluator.pred_emu_device: only the decision matrix goes in, the rollout,
+    the feedback rule and the objective stay on the device, and every step ends with the ONE collective of the path,
+    the NCCL all-gather of the per-candidate objectives."""
+    import torch
+    import torch.distributed as dist
+    from gnn_uds_b200 import configs, synthetic, mpc, sharding
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    precision = "bf16" if a.precision == "auto" else a.precision
+    em, args, rng = configs.make_emulator("C3b", device=local, precision=precision)
+    net, _ = configs.load_net("astlingen")
+    pop = a.batch or 8192
+    chunks = configs.WORKLOADS["C3b"]["chunks"]
+    T = em.seq_out * chunks
+    ev = mpc.MpcEvaluator(em, net.nodes, interval=1, eval_horizon=T, control_horizon=T, setting_duration=5,
+                          gamma=0.99 ** np.arange(T))
+    rng = np.random.default_rng(args.seed)          # same state and population on every rank
+    states, b, _, ex = synthetic.make_inputs(em, 1, rng, horizon=T)
+    ev.load_state(states[0], b[0], ex[0])
+    x = mpc.latin_hypercube(pop, np.full(ev.n_var, 0.05), np.ones(ev.n_var), rng)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(a.warmup, 3)):
+        F = ev.pred_emu_device(x)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    em.set_profiling(1)
+    l0 = em.launch_count()
+    dev_ms = 0.0
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        F = ev.pred_emu_device(x)
+        dev_ms += em.last_timing()[0]
+    barrier()
+    wall = time.perf_counter() - t0
+    launches = em.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    # the collective alone (CUDA events on torch's stream): per-candidate objectives of every shard
+    gather_us = None
+    if world > 1:
+        per = (pop + world - 1) // world
+        buf = torch.zeros(per, dtype=torch.float32, device=dev)
+        out = torch.empty(per * world, dtype=torch.float32, device=dev)
+        for _ in range(5):
+            dist.all_gather_into_tensor(out, buf)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(20):
+            dist.all_gather_into_tensor(out, buf)
+        e1.record()
+        torch.cuda.synchronize()
+        gather_us = e0.elapsed_time(e1) / 20 * 1e3
+    t_all = torch.tensor([dev_ms, wall], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_all, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t_all[0].item()) / a.steps
+    units = pop * T * em.n_node
+    if rank == 0:
+        lo, hi = sharding.shard_range(pop, 0, world)
+        line = {"metric": METRIC.replace("shunqing GAT rollout", "astlingen MPC population evaluation"), "value": units / (ms_per_step * 1e-3),
+                "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_per_step,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32" if precision == "fp32" else ("f16(f32 acc)" if em._lib.gnnuds_tc_operand_is_half() else "bf16(f32 acc)"),
+                "data": "synthetic",
+                "config": {"workload": "C3mpc: astlingen GAT+Conv1D act+edge_fusion+resnet+flood 5->5, %d candidates TOTAL x %d-step horizon "
+                                       "(%d AR chunks, MPC feedback rule) + astlingen objective, %d candidates per GPU" % (pop, T, chunks, hi - lo),
+                           "l2": "the chunk loop's activations per pass exceed the 126 MB L2 at %d candidates per GPU" % (hi - lo) if (hi - lo) * T * 59 * 128 * 2 > 126e6 else "small shard: activations of a pass fit the L2 (strong scaling at 8 GPUs)",
+                           "precision": precision, "sharding": "candidates over ranks; ONE NCCL all-gather of the objectives per step"},
+                "e2e": {"value": units * a.steps / float(t_all[1].item()), "unit": UNIT, "h2d_bytes_per_step": int(x[lo:hi].nbytes + states[0].nbytes + b[0].nbytes + ex[0].nbytes),
+                        "d2h_bytes_per_step": int(4 * ((pop + world - 1) // world) * world),
+                        "note": "MpcEvaluator.pred_emu_device(x) wall clock: decision matrix in, all-gathered objectives out"},
+                "gpu_launches": int(launches), "clocks": clocks, "allgather_us": gather_us,
+                "objective_checksum": float(np.sum(F)), "wall_s_timed_region": wall}
+        emit(line)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 _JSON_OUT = None
@@ -262,6 +356,8 @@ def main():
     a = ap.parse_args()
     if a.impl == "reference":
         return run_reference(a)
+    if a.workload == "C3mpc":
+        return run_mpc(a)
 
     import torch
     import torch.distributed as dist
@@ -386,6 +482,24 @@ def main():
     e2e_val = world * B * To * N * a.steps / float(e_all.item())
     h2d = int(in_bytes)
     d2h = int((dy.numel() + dey.numel()) * 4)
+    # the caller's real entry: Emulator.predict on ordinary (pageable) NumPy arrays, results as NumPy arrays
+    res = None
+    for _ in range(2):
+        res = em.predict(states, b, act, ex)
+    del res
+    barrier()
+    t0 = time.perf_counter()
+    chk = 0.0
+    for _ in range(a.steps):
+        res = em.predict(states, b, act, ex)
+        chk += float(res[0][0, 0, 0, 0])
+        del res
+    barrier()
+    np_s = time.perf_counter() - t0
+    n_all = torch.tensor([np_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(n_all, op=dist.ReduceOp.MAX)
+    np_val = world * B * To * N * a.steps / float(n_all.item())
 
     if rank == 0:
         tot_f, gemm_f = flops(em, B)
@@ -419,7 +533,7 @@ def main():
             f32_peak = em.measure_fp32_tflops()
             roofline = {"bound": "tensor", "achieved": achieved, "peak": f32_peak, "unit": "TFLOP/s",
                         "frac": (achieved / f32_peak) if achieved and f32_peak else None, "traffic": None,
-                        "peak_source": "fp32 FFMA peak measured in this run (gnnuds_measure_fp32_tflops); the fp32 parity path runs on SIMT FMA, not tensor cores",
+                        "peak_source": "fp32 FFMA peak measured in this run (gnnuds_measure_simt_tflops); the fp32 parity path runs on SIMT FMA, not tensor cores",
                         "gemm_flops_per_step": gemm_f}
         elif dom["bound"] == "hbm":
             achieved = dom["bytes"] / (dom_ms_per_step * 1e-3) / 1e9 if dom_ms_per_step > 0 else None
@@ -442,7 +556,10 @@ def main():
                 em.edge_fusion, em.resnet, em.if_flood, bool(em.act), N, M, Ti, To, B),
                 "l2": l2_note, "precision": ("f16" if em._lib.gnnuds_tc_operand_is_half() else "bf16") if precision == "bf16" else precision, "sharding": "scenarios over ranks, no data-path collective"},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "note": "Emulator.predict_ptrs with pinned host buffers, wall clock incl. copies"},
+                    "note": "Emulator.predict_ptrs with pinned host buffers, wall clock incl. copies",
+                    "numpy_api": {"value": np_val, "unit": UNIT, "frac_of_device_resident": np_val / value,
+                                  "note": "Emulator.predict(states, b, a, edge_state) on pageable NumPy arrays, NumPy results; "
+                                          "the library stages chunks through a pinned ring with copy threads"}},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roofline,
@@ -450,6 +567,8 @@ def main():
         }
         if world == 1 and not a.no_cpu:
             line["cpu_baseline"] = cpu_baseline(a.workload)
+            # "C1 exactly as BASELINE.json words it" (astlingen GCN+GRU 10->10, B=64), median of 5
+            line["cpu_baseline_c1"] = cpu_baseline("C1", fixed_B=64, runs=5)
         emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -49,9 +49,9 @@ _lib = None
 SYMBOLS = [
     "gnnuds_create", "gnnuds_destroy", "gnnuds_last_error", "gnnuds_set_graph", "gnnuds_weight_layout",
     "gnnuds_set_weights", "gnnuds_set_norm", "gnnuds_output_dims", "gnnuds_predict", "gnnuds_simulate",
-    "gnnuds_rollout", "gnnuds_objective", "gnnuds_alloc_pinned", "gnnuds_free_pinned", "gnnuds_alloc_device",
+    "gnnuds_rollout", "gnnuds_objective", "gnnuds_evaluate", "gnnuds_replay", "gnnuds_build_windows", "gnnuds_alloc_pinned", "gnnuds_free_pinned", "gnnuds_alloc_device",
     "gnnuds_free_device", "gnnuds_memcpy", "gnnuds_synchronize", "gnnuds_launch_count", "gnnuds_last_timing",
-    "gnnuds_set_profiling", "gnnuds_kernel_timing", "gnnuds_debug_stop_after", "gnnuds_debug_fetch", "gnnuds_debug_umma_selftest",
+    "gnnuds_set_profiling", "gnnuds_measure_simt_tflops", "gnnuds_kernel_timing", "gnnuds_debug_stop_after", "gnnuds_debug_fetch", "gnnuds_debug_umma_selftest",
     "gnnuds_tc_operand_is_half", "gnnuds_set_post_proc_variant",
 ]
 
@@ -90,6 +90,10 @@ def load():
     lib.gnnuds_launch_count.restype = i64
     lib.gnnuds_last_timing.argtypes = [vp, P(C.c_float), P(C.c_float)]
     lib.gnnuds_set_profiling.argtypes = [vp, i32]
+    lib.gnnuds_evaluate.argtypes = [vp, i32, vp, vp, vp, i32, vp, i32, i32, i64, i32, vp, vp, vp, vp, vp, i32, i32]
+    lib.gnnuds_replay.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, i32]
+    lib.gnnuds_build_windows.argtypes = [vp, vp, vp, vp, vp, i64, i64, i64, vp, vp, vp, vp, i32]
+    lib.gnnuds_measure_simt_tflops.argtypes = [vp, P(C.c_float)]
     lib.gnnuds_kernel_timing.argtypes = [vp, i32, P(C.c_float), P(i64)]
     lib.gnnuds_debug_stop_after.argtypes = [vp, i32]
     lib.gnnuds_set_post_proc_variant.argtypes = [vp, i32]

@@ -14,6 +14,8 @@
 #include "nn_cat.cuh"
 
 #include <algorithm>
+#include <array>
+#include <thread>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -139,9 +141,17 @@ struct gnnuds_handle {
   float *in2_x, *in2_b, *in2_a, *in2_ex, *out2_y, *out2_ey; // second staging set: copies of chunk i+1 / i-1 overlap compute of chunk i
   cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
   cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+  // pageable caller buffers (plain NumPy arrays): a ring of two pinned input / output sets; worker threads copy
+  // between caller memory and the ring while the GPU computes (gnnuds_predict)
+  float* pin_in[2] = {nullptr, nullptr}; float* pin_out[2] = {nullptr, nullptr};
+  size_t pin_in_floats = 0, pin_out_floats = 0;
   // rollout state
   float *ro_x = nullptr, *ro_ex = nullptr, *ro_b = nullptr, *ro_a = nullptr;
   int64_t ro_B = 0;
+  // grow-only device buffers of the autoregressive / MPC entry points (no cudaMalloc on the hot path once warm):
+  // 0..3 rollout horizon b / a / y / ey, 4..10 objective (weights x3, gamma, y, q0, obj), 11..17 evaluate
+  // (x0, ex0, b, dec, partial sums, prev_q, obj)
+  float* gb[24] = {nullptr}; size_t gb_cap[24] = {0};   // 18..21 replay (raw states, perfs, edge states, settings)
 
   // live streams for debug_fetch
   const float* dbg_ptr[2] = {nullptr, nullptr};
@@ -1249,16 +1259,19 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
   p.xe_bytes = (uint32_t)p.Kp * 128u;
   p.nx_bytes = (uint32_t)(F / 8) * p.pstrideP;
   p.al_bytes = (uint32_t)(p.KpJ / 8) * p.pstrideAl;
-  const uint32_t h_bytes = (uint32_t)(E / 8) * p.pstrideH;
+  const uint32_t h_bytes = (uint32_t)((p.KpJ + 63) / 64) * (uint32_t)E * 128u;   // h^T tiles [E x 64 neighbours]
   p.off_w = 0;
   p.off_m = al(p.w_bytes, 128);
   p.off_self = al(p.off_m + p.m_bytes, 1024);
   p.self_stride = al(std::max(p.self_bytes, h_bytes), 1024);
   p.off_xe = p.off_self + (uint32_t)p.nb_self * p.self_stride;
   p.off_nx = al(p.off_xe + p.xe_bytes, 128);
-  p.off_al = al(p.off_nx + p.nx_bytes, 128);
-  p.off_sc = al(p.off_al + p.al_bytes, 128);
-  const uint32_t sc_bytes = ((uint32_t)E + 3u * RP) * 4u + ((uint32_t)R + 1u + (uint32_t)p.nnz) * 4u;
+  p.off_al = al(p.off_nx + p.nx_bytes, 1024);      // doubles as the SWIZZLE_128B staging tile of the TMA store
+  p.stage_half = al((uint32_t)R * 128u, 1024);
+  p.al_zero = al(std::max(p.al_bytes, 2u * p.stage_half), 16);
+  p.off_sc = al(p.off_al + p.al_zero, 128);
+  p.agg_n128 = getenv("GNNUDS_AGG_N128") ? atoi(getenv("GNNUDS_AGG_N128")) : 1;
+  const uint32_t sc_bytes = ((uint32_t)E + 3u * RP) * 4u + ((uint32_t)R + 1u + (uint32_t)p.nnz * (gat ? 1u : 2u)) * 4u;
   p.off_bar = al(p.off_sc + sc_bytes, 16);
   // operand views of an M tile read 128 rows from the tile's first row of every panel / swizzle chunk: keep those
   // reads inside the allocation
@@ -1272,6 +1285,7 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
   for (int i = 0; i < p.nseg; ++i)
     if (!make_rows_tmap_sw(&p.tm_self[i], segs[i].p, rows_total, segs[i].ld, segs[i].width, p.Rbox)) return -1;
   if (!make_rows_tmap_sw(&p.tm_other, other_dense, rows_other, F, F, p.Kp)) return -1;
+  if (!make_rows_tmap_sw(&p.tm_out, out, rows_total, E, E, R)) return -1;
   if (!h->attr_done[5]) {
     CU(cudaFuncSetAttribute(sp_agg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     h->attr_done[5] = true;
@@ -1295,8 +1309,8 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
     CU(cudaMemcpy(t.data(), p.trace, tn * sizeof(long long), cudaMemcpyDeviceToHost));
     cudaFree(p.trace);
     if (FILE* f = fopen(tf, "w")) {
-      fprintf(f, "# sp_agg R=%d Ro=%d Kself=%d MT=%d smem=%zu: sample, cycles since first stamp: conv_done_seen h_ready alpha_ready ne_drained agg_done_seen out_done\n", R, Ro, p.Kself, p.MT, smem);
-      for (int i = 0; i < 64; ++i) { fprintf(f, "%d", i); for (int k = 0; k < 6; ++k) fprintf(f, " %lld", t[i * SA_NSTAMP + k] ? t[i * SA_NSTAMP + k] - t[0] : -1); fprintf(f, "\n"); }
+      fprintf(f, "# sp_agg R=%d Ro=%d Kself=%d MT=%d smem=%zu: sample, cycles since first stamp: 0 conv_done_seen 1 h_ready 2 alpha_ready 3 ne_drained 4 agg_done_seen 5 out_done | 6 A:tmem 7 A:stored 8 B:bar1 9 B:zeroed 10 D:tmem 11 D:staged 12 D:bar | MMA thread: 13 conv issued 14 agg issue 15 agg issued 16 NE issue 17 NE issued 18 conv issue\n", R, Ro, p.Kself, p.MT, smem);
+      for (int i = 0; i < 64; ++i) { fprintf(f, "%d", i); for (int k = 0; k < SA_NSTAMP; ++k) fprintf(f, " %lld", t[i * SA_NSTAMP + k] ? t[i * SA_NSTAMP + k] - t[0] : -1); fprintf(f, "\n"); }
       fclose(f);
     }
   }
@@ -1666,6 +1680,85 @@ int upload(gnnuds_handle* h, T** dst, const T* src, size_t n) {
   return 0;
 }
 
+
+// ---- pageable host buffers ---------------------------------------------------------------------
+bool is_pageable(const void* p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { (void)cudaGetLastError(); return true; }
+  return at.type == cudaMemoryTypeUnregistered;
+}
+
+struct CopyJob { void* dst; const void* src; size_t bytes; };
+// memcpy split over a few threads (one core moves ~10 GB/s, less than a step's copies need to hide behind the compute)
+void parallel_copy(const std::vector<CopyJob>& jobs) {
+  size_t total = 0;
+  for (const CopyJob& j : jobs) total += j.bytes;
+  const unsigned hw = std::thread::hardware_concurrency();
+  int T = (int)std::max(1u, std::min(8u, hw ? hw / 2 : 4u));
+  if (total < (8u << 20)) T = 1;
+  if (T == 1) {
+    for (const CopyJob& j : jobs) if (j.bytes) std::memcpy(j.dst, j.src, j.bytes);
+    return;
+  }
+  std::vector<std::thread> th;
+  for (int t = 0; t < T; ++t)
+    th.emplace_back([&jobs, t, T]() {
+      for (const CopyJob& j : jobs) {
+        const size_t n = j.bytes, lo = n * t / T / 64 * 64, hi = t == T - 1 ? n : n * (t + 1) / T / 64 * 64;
+        if (hi > lo) std::memcpy(static_cast<char*>(j.dst) + lo, static_cast<const char*>(j.src) + lo, hi - lo);
+      }
+    });
+  for (auto& x : th) x.join();
+}
+
+int ensure_pinned(gnnuds_handle* h, size_t in_floats, size_t out_floats) {
+  if (in_floats > h->pin_in_floats) {
+    for (int k = 0; k < 2; ++k) { if (h->pin_in[k]) cudaFreeHost(h->pin_in[k]); h->pin_in[k] = nullptr; }
+    h->pin_in_floats = 0;
+    for (int k = 0; k < 2; ++k)
+      if (cudaMallocHost(&h->pin_in[k], in_floats * sizeof(float)) != cudaSuccess) { (void)cudaGetLastError(); return fail(h, GNNUDS_E_NOMEM, "pinned staging ring: %zu MB not available", (in_floats * 4) >> 20); }
+    h->pin_in_floats = in_floats;
+  }
+  if (out_floats > h->pin_out_floats) {
+    for (int k = 0; k < 2; ++k) { if (h->pin_out[k]) cudaFreeHost(h->pin_out[k]); h->pin_out[k] = nullptr; }
+    h->pin_out_floats = 0;
+    for (int k = 0; k < 2; ++k)
+      if (cudaMallocHost(&h->pin_out[k], out_floats * sizeof(float)) != cudaSuccess) { (void)cudaGetLastError(); return fail(h, GNNUDS_E_NOMEM, "pinned staging ring: %zu MB not available", (out_floats * 4) >> 20); }
+    h->pin_out_floats = out_floats;
+  }
+  return 0;
+}
+
+
+// grow-only device buffer `slot` of the handle with room for n floats
+int grow(gnnuds_handle* h, int slot, size_t n, float** out) {
+  n = std::max<size_t>(n, 1);
+  if (h->gb_cap[slot] < n) {
+    if (h->gb[slot]) { cudaStreamSynchronize(h->stream); cudaFree(h->gb[slot]); h->gb[slot] = nullptr; h->gb_cap[slot] = 0; }
+    if (cudaMalloc(&h->gb[slot], n * sizeof(float)) != cudaSuccess) { (void)cudaGetLastError(); return fail(h, GNNUDS_E_NOMEM, "device buffer of %zu MB", (n * 4) >> 20); }
+    h->gb_cap[slot] = n;
+  }
+  *out = h->gb[slot];
+  return 0;
+}
+
+int ensure_rollout_state(gnnuds_handle* h, int64_t Bc) {
+  const auto& c = h->c;
+  if (h->ro_B >= Bc && h->ro_x) return 0;
+  for (float** p : {&h->ro_x, &h->ro_ex, &h->ro_b, &h->ro_a}) if (*p) { cudaFree(*p); *p = nullptr; }
+  h->ro_B = 0;
+  const int64_t T = c.seq_out;
+  if (cudaMalloc(&h->ro_x, Bc * c.seq_in * c.n_node * c.n_in * sizeof(float)) != cudaSuccess ||
+      cudaMalloc(&h->ro_ex, Bc * c.seq_in * c.n_edge * c.e_in * sizeof(float)) != cudaSuccess ||
+      cudaMalloc(&h->ro_b, Bc * T * c.n_node * c.b_in * sizeof(float)) != cudaSuccess ||
+      cudaMalloc(&h->ro_a, std::max<int64_t>(Bc * T * c.n_act, 1) * sizeof(float)) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return fail(h, GNNUDS_E_NOMEM, "rollout state buffers");
+  }
+  h->ro_B = Bc;
+  return 0;
+}
+
 }  // namespace
 
 // =========================================================================================
@@ -1832,6 +1925,8 @@ int gnnuds_destroy(gnnuds_handle* h) {
   for (int s = 0; s < 2; ++s) for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_ne_img[s]) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_cv_img[s]) if (p) cudaFree(p);
+  for (int k = 0; k < 2; ++k) { if (h->pin_in[k]) cudaFreeHost(h->pin_in[k]); if (h->pin_out[k]) cudaFreeHost(h->pin_out[k]); }
+  for (float* q : h->gb) if (q) cudaFree(q);
   for (auto& e : h->gemm_ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (h->ev_a) cudaEventDestroy(h->ev_a);
   if (h->ev_b) cudaEventDestroy(h->ev_b);
@@ -2160,6 +2255,29 @@ int gnnuds_set_post_proc_variant(gnnuds_handle* h, int32_t variant) {
 
 int gnnuds_tc_operand_is_half(void) { return GU_F16 ? 16 : 0; }
 
+int gnnuds_measure_simt_tflops(gnnuds_handle* h, float* tflops) {
+  if (!h || !tflops) return GNNUDS_E_INVALID;
+  CU(cudaSetDevice(h->c.device));
+  const int blocks = h->sm_count * 8, threads = 256, iters = 1 << 14;
+  float* d = nullptr;
+  CU(cudaMalloc(&d, (size_t)blocks * threads * sizeof(float)));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+  float best = 0.f;
+  for (int rep = 0; rep < 4; ++rep) {
+    CU(cudaEventRecord(e0, h->stream));
+    fp32_peak_kernel<<<blocks, threads, 0, h->stream>>>(d, iters);
+    CU(cudaEventRecord(e1, h->stream));
+    CU(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    if (rep && ms > 0.f) best = std::max(best, (float)(2.0 * 16.0 * iters * blocks * threads / (ms * 1e-3) / 1e12));
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+  *tflops = best;
+  return 0;
+}
+
 int gnnuds_output_dims(const gnnuds_handle* h, int32_t* y_channels, int32_t* ey_channels) {
   if (!h) return GNNUDS_E_INVALID;
   if (y_channels) *y_channels = h->ny();
@@ -2191,7 +2309,50 @@ int gnnuds_predict(gnnuds_handle* h, const float* x, const float* b, const float
                 se = (int64_t)Ti * M * c.e_in, sy = (int64_t)To * N * h->ny(), sey = (int64_t)To * M * c.e_out;
   begin_timing(h);
   if (h->profiling) CU(cudaEventRecord(h->ev_a, h->stream));
-  if (where == GNNUDS_MEM_HOST && !h->debug_stop) {
+  const bool staged = where == GNNUDS_MEM_HOST && !h->debug_stop && !(getenv("GNNUDS_NO_PIN_RING") && getenv("GNNUDS_NO_PIN_RING")[0] == '1') &&
+                      (is_pageable(x) || is_pageable(b) || is_pageable(ex) || (a && is_pageable(a)) || is_pageable(y) || is_pageable(ey));
+  if (staged) {
+    // Pageable caller buffers (plain NumPy arrays): cudaMemcpyAsync from pageable memory blocks the host and runs at a
+    // fraction of the pinned rate, so chunks go through a ring of two pinned input / output sets.  Worker threads copy
+    // caller memory <-> ring while the GPU computes: stage-in of chunk i+1 and drain of chunk i-1 overlap chunk i.
+    if ((rc = ensure_pinned(h, (size_t)(Bc * (sx + sb + sa + se)), (size_t)(Bc * (sy + sey))))) return rc;
+    float* sin[2][4] = {{h->in_x, h->in_b, h->in_a, h->in_ex}, {h->in2_x, h->in2_b, h->in2_a, h->in2_ex}};
+    float* sout[2][2] = {{h->out_y, h->out_ey}, {h->out2_y, h->out2_ey}};
+    CU(cudaEventRecord(h->ev_comp[0], h->stream));
+    CU(cudaStreamWaitEvent(h->s_h2d, h->ev_comp[0], 0));
+    int64_t i = 0, prev_b0 = 0, prev_nb = 0;
+    auto drain = [&](int k, int64_t b0, int64_t nb) -> int {
+      CU(cudaEventSynchronize(h->ev_out[k]));
+      parallel_copy({{y + b0 * sy, h->pin_out[k], (size_t)(nb * sy) * sizeof(float)},
+                     {ey + b0 * sey, h->pin_out[k] + nb * sy, (size_t)(nb * sey) * sizeof(float)}});
+      return 0;
+    };
+    for (int64_t b0 = 0; b0 < B; b0 += Bc, ++i) {
+      const int64_t nb = std::min(Bc, B - b0);
+      const int k = (int)(i & 1);
+      if (i >= 2) CU(cudaEventSynchronize(h->ev_in[k]));                    // the H2D copy of chunk i-2 has left this ring slot
+      float *qx = h->pin_in[k], *qb = qx + nb * sx, *qe = qb + nb * sb, *qa = qe + nb * se;
+      parallel_copy({{qx, x + b0 * sx, (size_t)(nb * sx) * sizeof(float)}, {qb, b + b0 * sb, (size_t)(nb * sb) * sizeof(float)},
+                     {qe, ex + b0 * se, (size_t)(nb * se) * sizeof(float)}, {qa, a ? a + b0 * sa : nullptr, a ? (size_t)(nb * sa) * sizeof(float) : 0}});
+      if (i >= 2) CU(cudaStreamWaitEvent(h->s_h2d, h->ev_comp[k], 0));
+      CU(cudaMemcpyAsync(sin[k][0], qx, nb * sx * sizeof(float), cudaMemcpyHostToDevice, h->s_h2d));
+      CU(cudaMemcpyAsync(sin[k][1], qb, nb * sb * sizeof(float), cudaMemcpyHostToDevice, h->s_h2d));
+      CU(cudaMemcpyAsync(sin[k][3], qe, nb * se * sizeof(float), cudaMemcpyHostToDevice, h->s_h2d));
+      if (a) CU(cudaMemcpyAsync(sin[k][2], qa, nb * sa * sizeof(float), cudaMemcpyHostToDevice, h->s_h2d));
+      CU(cudaEventRecord(h->ev_in[k], h->s_h2d));
+      CU(cudaStreamWaitEvent(h->stream, h->ev_in[k], 0));
+      if (i >= 2) CU(cudaStreamWaitEvent(h->stream, h->ev_out[k], 0));
+      if ((rc = forward_any(h, sin[k][0], sin[k][1], a ? sin[k][2] : nullptr, sin[k][3], nb, sout[k][0], sout[k][1], false))) return rc;
+      CU(cudaEventRecord(h->ev_comp[k], h->stream));
+      CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[k], 0));
+      CU(cudaMemcpyAsync(h->pin_out[k], sout[k][0], nb * sy * sizeof(float), cudaMemcpyDeviceToHost, h->s_d2h));
+      CU(cudaMemcpyAsync(h->pin_out[k] + nb * sy, sout[k][1], nb * sey * sizeof(float), cudaMemcpyDeviceToHost, h->s_d2h));
+      CU(cudaEventRecord(h->ev_out[k], h->s_d2h));
+      if (i >= 1 && (rc = drain(k ^ 1, prev_b0, prev_nb))) return rc;
+      prev_b0 = b0; prev_nb = nb;
+    }
+    if (i >= 1 && (rc = drain((int)((i - 1) & 1), prev_b0, prev_nb))) return rc;
+  } else if (where == GNNUDS_MEM_HOST && !h->debug_stop) {
     // Host buffers: three streams and two staging sets.  The H2D copy of chunk i+1 and the D2H copy of
     // chunk i-1 run while chunk i computes; events order the reuse of a staging set (i and i+2 share one).
     float* sin[2][4] = {{h->in_x, h->in_b, h->in_a, h->in_ex}, {h->in2_x, h->in2_b, h->in2_a, h->in2_ex}};
@@ -2279,30 +2440,13 @@ int gnnuds_rollout(gnnuds_handle* h, int32_t rule, const float* x0, const float*
   const int64_t Th = (int64_t)n_chunks * T;
   const int64_t sx = (int64_t)T * N * c.n_in, se = (int64_t)T * M * c.e_in;
   const int64_t sbh = Th * N * c.b_in, sah = Th * c.n_act, syh = Th * N * nyc, seyh = Th * M * c.e_out;
-  if (h->ro_B < Bc) {
-    for (float** p : {&h->ro_x, &h->ro_ex, &h->ro_b, &h->ro_a}) if (*p) { cudaFree(*p); *p = nullptr; }
-    h->ro_B = 0;
-  }
-  // (re)allocate horizon buffers every call: horizon may change
+  // horizon staging (host callers) and per-chunk state: grow-only buffers of the handle
   float *d_b = nullptr, *d_a = nullptr, *d_y = nullptr, *d_ey = nullptr;
-  auto cleanup = [&]() { for (float* p : {d_b, d_a, d_y, d_ey}) if (p) cudaFree(p); };
   if (where == GNNUDS_MEM_HOST) {
-    if (cudaMalloc(&d_b, Bc * sbh * sizeof(float)) != cudaSuccess || cudaMalloc(&d_y, Bc * syh * sizeof(float)) != cudaSuccess ||
-        cudaMalloc(&d_ey, Bc * seyh * sizeof(float)) != cudaSuccess ||
-        (a && cudaMalloc(&d_a, std::max<int64_t>(Bc * sah, 1) * sizeof(float)) != cudaSuccess)) {
-      cleanup();
-      return fail(h, GNNUDS_E_NOMEM, "rollout horizon buffers");
-    }
+    if ((rc = grow(h, 0, (size_t)(Bc * sbh), &d_b)) || (rc = grow(h, 2, (size_t)(Bc * syh), &d_y)) || (rc = grow(h, 3, (size_t)(Bc * seyh), &d_ey))) return rc;
+    if (a && (rc = grow(h, 1, (size_t)(Bc * sah), &d_a))) return rc;
   }
-  if (!h->ro_x) {
-    if (cudaMalloc(&h->ro_x, Bc * sx * sizeof(float)) != cudaSuccess || cudaMalloc(&h->ro_ex, Bc * se * sizeof(float)) != cudaSuccess ||
-        cudaMalloc(&h->ro_b, Bc * T * N * c.b_in * sizeof(float)) != cudaSuccess ||
-        cudaMalloc(&h->ro_a, std::max<int64_t>(Bc * T * c.n_act, 1) * sizeof(float)) != cudaSuccess) {
-      cleanup();
-      return fail(h, GNNUDS_E_NOMEM, "rollout state buffers");
-    }
-    h->ro_B = Bc;
-  }
+  if ((rc = ensure_rollout_state(h, Bc))) return rc;
   begin_timing(h);
   if (h->profiling) cudaEventRecord(h->ev_a, h->stream);
   rc = 0;
@@ -2360,7 +2504,6 @@ int gnnuds_rollout(gnnuds_handle* h, int32_t rule, const float* x0, const float*
   }
   if (h->profiling) cudaEventRecord(h->ev_b, h->stream);
   cudaError_t e = cudaStreamSynchronize(h->stream);
-  cleanup();
   if (rc) return rc;
   if (e != cudaSuccess) return fail(h, GNNUDS_E_CUDA, "rollout: %s", cudaGetErrorString(e));
   if (h->profiling) cudaEventElapsedTime(&h->last_total_ms, h->ev_a, h->ev_b);
@@ -2375,31 +2518,227 @@ int gnnuds_objective(gnnuds_handle* h, const float* y, const float* q_in0, int64
   if (B == 0) return 0;
   const int N = c.n_node, nyc = h->ny();
   float *dfw = nullptr, *dww = nullptr, *drw = nullptr, *dg = nullptr, *dy = nullptr, *dq = nullptr, *dobj = nullptr;
-  auto cleanup = [&]() { for (float* p : {dfw, dww, drw, dg, dy, dq, dobj}) if (p) cudaFree(p); };
   int rc = 0;
-  auto up = [&](float** d, const float* s, size_t n) {
-    if (cudaMalloc(d, n * sizeof(float)) != cudaSuccess) return 1;
-    return cudaMemcpyAsync(*d, s, n * sizeof(float), cudaMemcpyHostToDevice, h->stream) != cudaSuccess ? 1 : 0;
+  auto up = [&](int slot, float** d, const float* src, size_t n) {
+    int r = grow(h, slot, n, d);
+    if (r) return r;
+    return cudaMemcpyAsync(*d, src, n * sizeof(float), cudaMemcpyHostToDevice, h->stream) != cudaSuccess ? fail(h, GNNUDS_E_CUDA, "objective: copy failed") : 0;
   };
-  rc |= up(&dfw, flood_w, N); rc |= up(&dww, wwtp_w, N);
-  if (rough_w) rc |= up(&drw, rough_w, N);
-  if (gamma) rc |= up(&dg, gamma, T);
+  if ((rc = up(4, &dfw, flood_w, N)) || (rc = up(5, &dww, wwtp_w, N))) return rc;
+  if (rough_w && (rc = up(6, &drw, rough_w, N))) return rc;
+  if (gamma && (rc = up(7, &dg, gamma, T))) return rc;
   const float *py = y, *pq = q_in0;
   float* po = obj;
   if (where == GNNUDS_MEM_HOST) {
-    rc |= up(&dy, y, (size_t)B * T * N * nyc); rc |= up(&dq, q_in0, (size_t)B * N);
-    if (cudaMalloc(&dobj, B * sizeof(float)) != cudaSuccess) rc = 1;
+    if ((rc = up(8, &dy, y, (size_t)B * T * N * nyc)) || (rc = up(9, &dq, q_in0, (size_t)B * N)) || (rc = grow(h, 10, (size_t)B, &dobj))) return rc;
     py = dy; pq = dq; po = dobj;
   }
-  if (rc) { cleanup(); return fail(h, GNNUDS_E_NOMEM, "objective buffers"); }
   ObjP p{py, nyc, pq, dfw, dww, drw, dg, po, B, T, N};
   objective_kernel<<<grid_for(h, B, 1, 16), 128, 0, h->stream>>>(p);
   ++h->launches;
   if (where == GNNUDS_MEM_HOST) cudaMemcpyAsync(obj, dobj, B * sizeof(float), cudaMemcpyDeviceToHost, h->stream);
   cudaError_t e = cudaStreamSynchronize(h->stream);
-  cleanup();
   if (e != cudaSuccess) return fail(h, GNNUDS_E_CUDA, "objective: %s", cudaGetErrorString(e));
   return 0;
+}
+
+int gnnuds_evaluate(gnnuds_handle* h, int32_t rule, const float* x0, const float* ex0, const float* b, int32_t n_b,
+                    const float* dec, int32_t n_step, int32_t r_step, int64_t B, int32_t n_chunks, const float* flood_w,
+                    const float* wwtp_w, const float* rough_w, const float* gamma, float* obj, int32_t where, int32_t obj_where) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const auto& c = h->c;
+  if (rule < GNNUDS_ROLL_MPC || rule > GNNUDS_ROLL_MBRL) return fail(h, GNNUDS_E_INVALID, "evaluate: feedback rule %d (MPC or MBRL)", rule);
+  if (!x0 || !ex0 || !b || !dec || !flood_w || !wwtp_w || !obj || n_chunks < 1 || n_b < 1 || n_step < 1 || r_step < 1 || B < 0)
+    return fail(h, GNNUDS_E_INVALID, "evaluate: bad argument");
+  if (!c.act || !c.if_flood) return fail(h, GNNUDS_E_INVALID, "evaluate needs an act + if_flood model (mpc.py:575, astlingen.py:75-99)");
+  if (n_chunks > 1 && c.seq_in != c.seq_out) return fail(h, GNNUDS_E_INVALID, "chunked evaluation needs seq_in == seq_out (mpc.py:573-579)");
+  CU(cudaSetDevice(c.device));
+  if (B == 0) return 0;
+  const int N = c.n_node, M = c.n_edge, T = c.seq_out, Ti = c.seq_in, nyc = h->ny();
+  const int64_t Th = (int64_t)n_chunks * T;
+  const int64_t Bc = pick_chunk(h, B);
+  if ((rc = ensure_workspace(h, Bc)) || (rc = ensure_rollout_state(h, Bc))) return rc;
+  const size_t nx0 = (size_t)Ti * N * c.n_in, nex0 = (size_t)Ti * M * c.e_in, nbb = (size_t)n_b * Th * N * c.b_in,
+               ndec = (size_t)B * n_step * c.n_act;
+  const float *dx0 = x0, *dex0 = ex0, *db = b, *ddec = dec, *dfw = flood_w, *dww = wwtp_w, *drw = rough_w, *dg = gamma;
+  float *part = nullptr, *prevq = nullptr, *dobj = obj;
+  if (where == GNNUDS_MEM_HOST) {
+    auto up = [&](int slot, const float** d, const float* src, size_t n) {
+      float* q = nullptr;
+      int r = grow(h, slot, n, &q);
+      if (r) return r;
+      *d = q;
+      return cudaMemcpyAsync(q, src, n * sizeof(float), cudaMemcpyHostToDevice, h->stream) != cudaSuccess ? fail(h, GNNUDS_E_CUDA, "evaluate: copy failed") : 0;
+    };
+    if ((rc = up(11, &dx0, x0, nx0)) || (rc = up(12, &dex0, ex0, nex0)) || (rc = up(13, &db, b, nbb)) || (rc = up(14, &ddec, dec, ndec)) ||
+        (rc = up(4, &dfw, flood_w, N)) || (rc = up(5, &dww, wwtp_w, N))) return rc;
+    if (rough_w && (rc = up(6, &drw, rough_w, N))) return rc;
+    if (gamma && (rc = up(7, &dg, gamma, (size_t)Th))) return rc;
+  }
+  if ((rc = grow(h, 15, (size_t)Bc * 128, &part)) || (rc = grow(h, 16, (size_t)Bc * N, &prevq))) return rc;
+  if (obj_where == GNNUDS_MEM_HOST && (rc = grow(h, 17, (size_t)B, &dobj))) return rc;
+  begin_timing(h);
+  if (h->profiling) CU(cudaEventRecord(h->ev_a, h->stream));
+  // the MPC / MBRL loops of the reference run predict_tf (mpc.py:250,575; mbrl.py:337)
+  const int saved_variant = h->pp_variant;
+  h->pp_variant = 1;
+  struct Restore { gnnuds_handle* h; int v; ~Restore() { h->pp_variant = v; } } restore{h, saved_variant};
+  for (int64_t b0 = 0; b0 < B; b0 += Bc) {
+    const int64_t nb = std::min(Bc, B - b0);
+    // one state broadcast over the candidates of the chunk (mpc.py:237-240); q_in of the last observed step
+    bcast_time_kernel<<<grid_for(h, nb * (long long)nx0, 256, 16), 256, 0, h->stream>>>(dx0, h->ro_x, nb, 0, 1, Ti, 0, Ti, (long long)N * c.n_in);
+    bcast_time_kernel<<<grid_for(h, nb * (long long)nex0, 256, 16), 256, 0, h->stream>>>(dex0, h->ro_ex, nb, 0, 1, Ti, 0, Ti, (long long)M * c.e_in);
+    init_prevq_kernel<<<grid_for(h, nb * N, 256, 16), 256, 0, h->stream>>>(dx0 + (size_t)(Ti - 1) * N * c.n_in, prevq, nb, N, c.n_in);
+    h->launches += 3;
+    for (int k = 0; k < n_chunks; ++k) {
+      bcast_time_kernel<<<grid_for(h, nb * T * (long long)N * c.b_in, 256, 16), 256, 0, h->stream>>>(db, h->ro_b, nb, b0, n_b, (int)Th, k * T, T, (long long)N * c.b_in);
+      dec_slice_kernel<<<grid_for(h, nb * T * c.n_act, 256, 16), 256, 0, h->stream>>>(ddec, h->ro_a, nb, b0, n_step, r_step, k * T, T, c.n_act);
+      h->launches += 2;
+      if ((rc = forward_any(h, h->ro_x, h->ro_b, h->ro_a, h->ro_ex, nb, h->out_y, h->out_ey, false))) return rc;
+      ObjAccP op{h->out_y, nyc, prevq, dfw, dww, drw, dg, part, nb, T, N, k * T, k == 0 ? 1 : 0};
+      obj_acc_kernel<<<grid_for(h, nb, 1, 16), 128, 0, h->stream>>>(op);
+      ++h->launches;
+      if (k + 1 < n_chunks) {
+        FeedP p{};
+        p.y = h->out_y; p.ny = nyc; p.ey = h->out_ey; p.e_out = c.e_out; p.b = h->ro_b; p.b_in = c.b_in;
+        p.a = h->ro_a; p.n_act = c.n_act; p.act_of_edge = h->d_act_of_edge;
+        p.x = h->ro_x; p.n_in = c.n_in; p.ex = h->ro_ex; p.e_in = c.e_in;
+        p.S = nb * T; p.N = N; p.M = M; p.if_flood = 1; p.rule = rule;
+        feedback_kernel<<<grid_for(h, p.S * (N + M), 256, 16), 256, 0, h->stream>>>(p);
+        ++h->launches;
+      }
+      CU(cudaGetLastError());
+    }
+    obj_final_kernel<<<grid_for(h, nb, 1, 16), 128, 0, h->stream>>>(part, dobj + b0, nb);
+    ++h->launches;
+  }
+  if (obj_where == GNNUDS_MEM_HOST) CU(cudaMemcpyAsync(obj, dobj, B * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+  if (h->profiling) CU(cudaEventRecord(h->ev_b, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (h->profiling) CU(cudaEventElapsedTime(&h->last_total_ms, h->ev_a, h->ev_b));
+  return finish_timing(h);
+}
+
+// upload one raw event (replay / build_windows): device pointers of the four series
+static int replay_upload(gnnuds_handle* h, const float* states, const float* perfs, const float* edge_states, const float* settings,
+                         int64_t T, int32_t where, const float** ds, const float** dp, const float** de, const float** dse) {
+  const auto& c = h->c;
+  *ds = states; *dp = perfs; *de = edge_states; *dse = settings;
+  if (where != GNNUDS_MEM_HOST) return 0;
+  int rc;
+  auto up = [&](int slot, const float** d, const float* src, size_t n) {
+    float* q = nullptr;
+    int r = grow(h, slot, n, &q);
+    if (r) return r;
+    *d = q;
+    return cudaMemcpyAsync(q, src, n * sizeof(float), cudaMemcpyHostToDevice, h->stream) != cudaSuccess ? fail(h, GNNUDS_E_CUDA, "replay: copy failed") : 0;
+  };
+  if ((rc = up(18, ds, states, (size_t)T * c.n_node * 4)) || (rc = up(20, de, edge_states, (size_t)T * c.n_edge * c.e_in))) return rc;
+  if (perfs && (rc = up(19, dp, perfs, (size_t)T * c.n_node))) return rc;
+  if (settings && (rc = up(21, dse, settings, (size_t)T * c.n_act))) return rc;
+  return 0;
+}
+
+static int replay_check(gnnuds_handle* h, const float* states, const float* perfs, const float* edge_states, const float* settings, int64_t T) {
+  const auto& c = h->c;
+  if (!states || !edge_states || T < 0) return fail(h, GNNUDS_E_INVALID, "replay: null series");
+  if (c.if_flood && !perfs) return fail(h, GNNUDS_E_INVALID, "replay: an if_flood model needs the cumflooding series (main.py:339)");
+  if (c.act && !settings) return fail(h, GNNUDS_E_INVALID, "replay: an act model needs the settings series (main.py:350)");
+  if (c.n_in != 4 + (c.if_flood ? 1 : 0) || c.e_in != 4) return fail(h, GNNUDS_E_INVALID, "replay: node state [h,cuminflow,outflow,lateral] and 4 edge channels expected");
+  if (c.b_in > 2) return fail(h, GNNUDS_E_INVALID, "replay: b_in %d", c.b_in);
+  return 0;
+}
+
+static void replay_launch(gnnuds_handle* h, const float* ds, const float* dp, const float* de, const float* dse, int64_t T, int64_t w0,
+                          int64_t nw, float* x, float* b, float* a, float* ex) {
+  const auto& c = h->c;
+  ReplayP p{ds, dp, de, dse, h->d_outfall, x, b, c.act ? a : nullptr, ex, w0, nw, (int)T, c.n_node, c.n_edge, c.seq_in, c.seq_out,
+            std::max(c.seq_in, c.seq_out), c.n_in, c.b_in, c.e_in, c.n_act, c.if_flood ? 1 : 0};
+  const long long work = nw * ((long long)c.seq_in * (c.n_node * c.n_in + c.n_edge * c.e_in) + (long long)c.seq_out * c.n_node * c.b_in);
+  replay_windows_kernel<<<grid_for(h, work, 256, 16), 256, 0, h->stream>>>(p);
+  ++h->launches;
+}
+
+int gnnuds_build_windows(gnnuds_handle* h, const float* states, const float* perfs, const float* edge_states, const float* settings,
+                         int64_t T, int64_t w0, int64_t nw, float* x, float* b, float* a, float* ex, int32_t where) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const auto& c = h->c;
+  if ((rc = replay_check(h, states, perfs, edge_states, settings, T))) return rc;
+  if (!x || !b || !ex || (c.act && !a) || w0 < 0 || nw < 0 || w0 + nw > std::max<int64_t>(T - c.seq_out, 0)) return fail(h, GNNUDS_E_INVALID, "build_windows: bad window range");
+  CU(cudaSetDevice(c.device));
+  if (nw == 0) return 0;
+  const float *ds, *dp, *de, *dse;
+  if ((rc = replay_upload(h, states, perfs, edge_states, settings, T, where, &ds, &dp, &de, &dse))) return rc;
+  const size_t nx = (size_t)nw * c.seq_in * c.n_node * c.n_in, nbb = (size_t)nw * c.seq_out * c.n_node * c.b_in,
+               na = (size_t)nw * c.seq_out * std::max(c.n_act, 1), ne = (size_t)nw * c.seq_in * c.n_edge * c.e_in;
+  if (where == GNNUDS_MEM_HOST) {
+    float* tmp = nullptr;
+    if ((rc = grow(h, 22, nx + nbb + na + ne, &tmp))) return rc;
+    replay_launch(h, ds, dp, de, dse, T, w0, nw, tmp, tmp + nx, tmp + nx + nbb, tmp + nx + nbb + na);
+    CU(cudaMemcpyAsync(x, tmp, nx * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(b, tmp + nx, nbb * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (c.act) CU(cudaMemcpyAsync(a, tmp + nx + nbb, (size_t)nw * c.seq_out * c.n_act * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(ex, tmp + nx + nbb + na, ne * 4, cudaMemcpyDeviceToHost, h->stream));
+  } else {
+    replay_launch(h, ds, dp, de, dse, T, w0, nw, x, b, a, ex);
+  }
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int gnnuds_replay(gnnuds_handle* h, const float* states, const float* perfs, const float* edge_states, const float* settings,
+                  int64_t T, float* y, float* ey, int32_t where) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const auto& c = h->c;
+  if ((rc = replay_check(h, states, perfs, edge_states, settings, T))) return rc;
+  if (!y || !ey) return fail(h, GNNUDS_E_INVALID, "replay: null output");
+  CU(cudaSetDevice(c.device));
+  const int64_t W = T - c.seq_out;
+  if (W <= 0) return 0;
+  const float *ds, *dp, *de, *dse;
+  if ((rc = replay_upload(h, states, perfs, edge_states, settings, T, where, &ds, &dp, &de, &dse))) return rc;
+  const int64_t Bc = pick_chunk(h, W);
+  if ((rc = ensure_workspace(h, Bc))) return rc;
+  const int N = c.n_node, M = c.n_edge, To = c.seq_out;
+  const int64_t sy = (int64_t)To * N * h->ny(), sey = (int64_t)To * M * c.e_out;
+  const bool host = where == GNNUDS_MEM_HOST;
+  if (host && (rc = ensure_pinned(h, 0, (size_t)(Bc * (sy + sey))))) return rc;
+  begin_timing(h);
+  if (h->profiling) CU(cudaEventRecord(h->ev_a, h->stream));
+  float* sout[2][2] = {{h->out_y, h->out_ey}, {h->out2_y, h->out2_ey}};
+  int64_t i = 0, prev_w0 = 0, prev_nw = 0;
+  auto drain = [&](int k, int64_t w0, int64_t nw) -> int {
+    CU(cudaEventSynchronize(h->ev_out[k]));
+    parallel_copy({{y + w0 * sy, h->pin_out[k], (size_t)(nw * sy) * sizeof(float)},
+                   {ey + w0 * sey, h->pin_out[k] + nw * sy, (size_t)(nw * sey) * sizeof(float)}});
+    return 0;
+  };
+  for (int64_t w0 = 0; w0 < W; w0 += Bc, ++i) {
+    const int64_t nw = std::min(Bc, W - w0);
+    const int k = (int)(i & 1);
+    replay_launch(h, ds, dp, de, dse, T, w0, nw, h->in_x, h->in_b, h->in_a, h->in_ex);
+    float *oy = host ? sout[k][0] : y + w0 * sy, *oey = host ? sout[k][1] : ey + w0 * sey;
+    if (host && i >= 2) CU(cudaStreamWaitEvent(h->stream, h->ev_out[k], 0));   // chunk i-2's results have left this output set
+    if ((rc = forward_any(h, h->in_x, h->in_b, c.act ? h->in_a : nullptr, h->in_ex, nw, oy, oey, false))) return rc;
+    if (host) {
+      CU(cudaEventRecord(h->ev_comp[k], h->stream));
+      CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[k], 0));
+      CU(cudaMemcpyAsync(h->pin_out[k], sout[k][0], nw * sy * sizeof(float), cudaMemcpyDeviceToHost, h->s_d2h));
+      CU(cudaMemcpyAsync(h->pin_out[k] + nw * sy, sout[k][1], nw * sey * sizeof(float), cudaMemcpyDeviceToHost, h->s_d2h));
+      CU(cudaEventRecord(h->ev_out[k], h->s_d2h));
+      if (i >= 1 && (rc = drain(k ^ 1, prev_w0, prev_nw))) return rc;
+      prev_w0 = w0; prev_nw = nw;
+    }
+  }
+  if (host && i >= 1 && (rc = drain((int)((i - 1) & 1), prev_w0, prev_nw))) return rc;
+  if (h->profiling) CU(cudaEventRecord(h->ev_b, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (h->profiling) CU(cudaEventElapsedTime(&h->last_total_ms, h->ev_a, h->ev_b));
+  return finish_timing(h);
 }
 
 int gnnuds_alloc_pinned(void** p, int64_t bytes) {

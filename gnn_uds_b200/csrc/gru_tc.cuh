@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) gru_tc_kernel(const __grid_con
   uint64_t* h_ready = bars;        // gate group wrote the A panels (and drained the accumulators)
   uint64_t* mma_done = bars + 1;   // the step's MMAs completed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;   // warp-uniform to the compiler
 
   if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
   if (tid == 32) {
@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) gru_tc_kernel(const __grid_con
 
   if (warp == GRU_GATE_WARPS) {
     // ================================ MMA issuer ================================
-    if (lane == 0) {
+    {
       const uint32_t idesc = tc::idesc_bf16(128, G, 0, 0);
       const uint64_t a0 = tc::smem_desc(tc::smem_u32(As), PSTRIDE_A, 128u), w0 = tc::smem_desc(tc::smem_u32(Rs), PSTRIDE_W, 128u);
       const uint64_t l0 = tc::smem_desc(tc::smem_u32(Al), PSTRIDE_A, 128u), w1 = tc::smem_desc(tc::smem_u32(Rs + R_BYTES), PSTRIDE_W, 128u);
@@ -79,16 +79,16 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) gru_tc_kernel(const __grid_con
         for (int t = 0; t < p.Ts; ++t) {
           tc::mbar_wait(h_ready, ph_h); ph_h ^= 1u;
           tc::tc_fence_after();
-          uint64_t ad = a0, wd = w0;
+          if (tc::elect_one()) {      // warp-uniform issue code, one elected lane (tc::elect_one)
 #pragma unroll
-          for (int ks = 0; ks < H / 16; ++ks, ad += a_step, wd += w_step) tc::umma(tmem, ad, wd, idesc, ks != 0);
-          ad = l0; wd = w0;
+            for (int ks = 0; ks < H / 16; ++ks) tc::umma(tmem, a0 + (uint64_t)ks * a_step, w0 + (uint64_t)ks * w_step, idesc, ks != 0);
 #pragma unroll
-          for (int ks = 0; ks < H / 16; ++ks, ad += a_step, wd += w_step) tc::umma(tmem, ad, wd, idesc, 1u);
-          ad = a0; wd = w1;
+            for (int ks = 0; ks < H / 16; ++ks) tc::umma(tmem, l0 + (uint64_t)ks * a_step, w0 + (uint64_t)ks * w_step, idesc, 1u);
 #pragma unroll
-          for (int ks = 0; ks < H / 16; ++ks, ad += a_step, wd += w_step) tc::umma(tmem, ad, wd, idesc, 1u);
-          tc::umma_commit(mma_done);
+            for (int ks = 0; ks < H / 16; ++ks) tc::umma(tmem, a0 + (uint64_t)ks * a_step, w1 + (uint64_t)ks * w_step, idesc, 1u);
+            tc::umma_commit(mma_done);
+          }
+          __syncwarp();
         }
       }
     }
@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) lstm_tc_kernel(const __grid_co
   uint64_t* h_ready = bars;
   uint64_t* mma_done = bars + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;   // warp-uniform to the compiler
 
   if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
   if (tid == 32) {
@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) lstm_tc_kernel(const __grid_co
   uint32_t ph_h = 0, ph_m = 0;
 
   if (warp == GRU_GATE_WARPS) {
-    if (lane == 0) {
+    {
       const uint32_t idesc = tc::idesc_bf16(128, G, 0, 0);
       const uint64_t a0 = tc::smem_desc(tc::smem_u32(As), PSTRIDE_A, 128u), w0 = tc::smem_desc(tc::smem_u32(Rs), PSTRIDE_W, 128u);
       const uint64_t l0 = tc::smem_desc(tc::smem_u32(Al), PSTRIDE_A, 128u), w1 = tc::smem_desc(tc::smem_u32(Rs + R_BYTES), PSTRIDE_W, 128u);
@@ -237,16 +237,16 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) lstm_tc_kernel(const __grid_co
         for (int t = 0; t < p.Ts; ++t) {
           tc::mbar_wait(h_ready, ph_h); ph_h ^= 1u;
           tc::tc_fence_after();
-          uint64_t ad = a0, wd = w0;
+          if (tc::elect_one()) {      // warp-uniform issue code, one elected lane (tc::elect_one)
 #pragma unroll
-          for (int ks = 0; ks < H / 16; ++ks, ad += a_step, wd += w_step) tc::umma(tmem, ad, wd, idesc, ks != 0);
-          ad = l0; wd = w0;
+            for (int ks = 0; ks < H / 16; ++ks) tc::umma(tmem, a0 + (uint64_t)ks * a_step, w0 + (uint64_t)ks * w_step, idesc, ks != 0);
 #pragma unroll
-          for (int ks = 0; ks < H / 16; ++ks, ad += a_step, wd += w_step) tc::umma(tmem, ad, wd, idesc, 1u);
-          ad = a0; wd = w1;
+            for (int ks = 0; ks < H / 16; ++ks) tc::umma(tmem, l0 + (uint64_t)ks * a_step, w0 + (uint64_t)ks * w_step, idesc, 1u);
 #pragma unroll
-          for (int ks = 0; ks < H / 16; ++ks, ad += a_step, wd += w_step) tc::umma(tmem, ad, wd, idesc, 1u);
-          tc::umma_commit(mma_done);
+            for (int ks = 0; ks < H / 16; ++ks) tc::umma(tmem, a0 + (uint64_t)ks * a_step, w1 + (uint64_t)ks * w_step, idesc, 1u);
+            tc::umma_commit(mma_done);
+          }
+          __syncwarp();
         }
       }
     }

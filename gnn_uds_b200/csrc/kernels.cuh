@@ -1384,4 +1384,166 @@ __global__ void __launch_bounds__(128) objective_kernel(ObjP p) {
   }
 }
 
+// ---- device-resident MPC evaluation (gnnuds_evaluate; mpc.py:210-259, 565-582) -------------------
+// dst[i, t, :] = src[((b0 + i) % n_src), t0 + t, :]: one shared state / runoff broadcast over the candidates of a chunk
+// (mpc.py:237-240 tiles them on the host)
+__global__ void __launch_bounds__(256) bcast_time_kernel(const float* __restrict__ src, float* __restrict__ dst, long long nb,
+                                                         long long b0, int n_src, int Tsrc, int t0, int Tdst, long long L) {
+  const long long total = nb * Tdst * L;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
+    const long long l = g % L, it = g / L;
+    const int t = (int)(it % Tdst);
+    const long long i = it / Tdst;
+    dst[g] = src[(((b0 + i) % n_src) * Tsrc + t0 + t) * L + l];
+  }
+}
+// settings of chunk steps t0..t0+T-1 from the decision matrix (mpc.py:211-218: every setting held r_step steps, the last
+// one repeated to the end of the horizon): dst[i, t, j] = dec[b0 + i, min((t0 + t) / r_step, n_step - 1), j]
+__global__ void __launch_bounds__(256) dec_slice_kernel(const float* __restrict__ dec, float* __restrict__ dst, long long nb,
+                                                        long long b0, int n_step, int r_step, int t0, int T, int n_act) {
+  const long long total = nb * T * n_act;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
+    const int j = (int)(g % n_act);
+    const long long it = g / n_act;
+    const int t = (int)(it % T);
+    const long long i = it / T;
+    const int st = min((t0 + t) / r_step, n_step - 1);
+    dst[g] = dec[((b0 + i) * n_step + st) * n_act + j];
+  }
+}
+// prev_q[i, n] = q_in of the last observed step (state[-1, n, 1], astlingen.py:83), the same for every candidate
+__global__ void __launch_bounds__(256) init_prevq_kernel(const float* __restrict__ x_last, float* __restrict__ prev_q, long long nb,
+                                                         int N, int n_in) {
+  const long long total = nb * N;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x)
+    prev_q[g] = x_last[(g % N) * n_in + 1];
+}
+// astlingen objective accumulated chunk by chunk: thread `tid` of candidate i owns the terms g = t*N + n with
+// g % 128 == tid over the WHOLE horizon, in increasing g - the same partial sums objective_kernel forms in one pass,
+// so obj_final_kernel returns bitwise the same value.  prev_q carries q_in of the last step into the next chunk.
+struct ObjAccP {
+  const float* y; int ny;     // (nb,T,N,ny) predictions of this chunk
+  float* prev_q;              // (nb,N) q_in of the step before this chunk (state[:, -1, :, 1] for the first)
+  const float* flood_w; const float* wwtp_w; const float* rough_w; const float* gamma;
+  float* part;                // (nb,128) running per-thread partial sums
+  long long nb; int T, N, t0, first;
+};
+__global__ void __launch_bounds__(128) obj_acc_kernel(ObjAccP p) {
+  for (long long i = blockIdx.x; i < p.nb; i += gridDim.x) {
+    const int tid = threadIdx.x;
+    float acc = p.first ? 0.f : p.part[i * 128 + tid];
+    const long long g0 = (long long)p.t0 * p.N;
+    const int start = (int)(((tid - g0) % 128 + 128) % 128);
+    for (int g = start; g < p.T * p.N; g += 128) {
+      const int t = g / p.N, n = g % p.N;
+      const float* ys = p.y + ((i * p.T + t) * p.N + n) * p.ny;
+      const float gm = p.gamma ? p.gamma[p.t0 + t] : 1.f;
+      float v = ys[p.ny - 1] * p.flood_w[n] + ys[1] * p.wwtp_w[n];
+      if (p.rough_w) {
+        const float prev = (t == 0) ? p.prev_q[i * p.N + n] : (ys - (long long)p.N * p.ny)[1];
+        v += fabsf(ys[1] - prev) * p.rough_w[n];
+      }
+      acc += v * gm;
+    }
+    p.part[i * 128 + tid] = acc;
+    __syncthreads();
+    for (int n = tid; n < p.N; n += 128) p.prev_q[i * p.N + n] = p.y[((i * p.T + p.T - 1) * p.N + n) * p.ny + 1];
+    __syncthreads();
+  }
+}
+__global__ void __launch_bounds__(128) obj_final_kernel(const float* __restrict__ part, float* __restrict__ obj, long long nb) {
+  __shared__ float red[4];
+  for (long long i = blockIdx.x; i < nb; i += gridDim.x) {
+    float acc = warp_sum(part[i * 128 + threadIdx.x]);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) obj[i] = red[0] + red[1] + red[2] + red[3];
+  }
+}
+
+// ---- event replay: teacher-forced windows built on the device (main.py:327-354, dataloader.py:93-95) -------------
+// The reference expands an event of T steps into T windows of `seq` steps on the host (expand_seq: window idx holds the
+// steps idx-seq .. idx-1, zero-padded on the left; ones for settings) - a seq-fold blow-up of the data before it reaches
+// the model.  Here the raw series is uploaded once and every window element is gathered by index arithmetic:
+//   x [w, s, n, :]  = [h, cuminflow - lateral, outflow, (cumflooding > 0), lateral] at step w - Ti + s      (0 when < 0)
+//   b [w, s, n, 0]  = lateral at step w + To - seq + s  (seq = max(Ti, To); the reference's r = states[seq_out:, ..., -1:]
+//                     keeps the FIRST To steps of a seq-step window, emulator.py:532);  b[..., 1] = h * is_outfall (tide)
+//   a [w, s, :]     = settings at step w + s;            ex[w, s, m, :] = edge state at step w - Ti + s     (0 when < 0)
+struct ReplayP {
+  const float* st; const float* pf; const float* es; const float* se; const float* outfall;
+  float* x; float* b; float* a; float* ex;
+  long long w0, nw; int T, N, M, Ti, To, seq, n_in, b_in, e_in, n_act, if_flood;
+};
+__global__ void __launch_bounds__(256) replay_windows_kernel(ReplayP p) {
+  const long long stride = (long long)gridDim.x * blockDim.x, g0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  {
+    const long long total = p.nw * p.Ti * p.N * p.n_in;
+    for (long long g = g0; g < total; g += stride) {
+      const int c = (int)(g % p.n_in);
+      long long q = g / p.n_in;
+      const int n = (int)(q % p.N); q /= p.N;
+      const int s = (int)(q % p.Ti);
+      const long long t = p.w0 + q / p.Ti - p.Ti + s;
+      float v = 0.f;
+      if (t >= 0) {
+        const float* r = p.st + (t * p.N + n) * 4;
+        if (c == 0) v = r[0];
+        else if (c == 1) v = r[1] - r[3];
+        else if (c == 2) v = r[2];
+        else if (c == p.n_in - 1) v = r[3];
+        else v = p.pf[t * p.N + n] > 0.f ? 1.f : 0.f;
+      }
+      p.x[g] = v;
+    }
+  }
+  {
+    const long long total = p.nw * p.To * p.N * p.b_in;
+    for (long long g = g0; g < total; g += stride) {
+      const int c = (int)(g % p.b_in);
+      long long q = g / p.b_in;
+      const int n = (int)(q % p.N); q /= p.N;
+      const int s = (int)(q % p.To);
+      const long long t = p.w0 + q / p.To + p.To - p.seq + s;
+      float v = 0.f;
+      if (t >= 0) v = c == 0 ? p.st[(t * p.N + n) * 4 + 3] : p.st[(t * p.N + n) * 4] * p.outfall[n];
+      p.b[g] = v;
+    }
+  }
+  if (p.a) {
+    const long long total = p.nw * p.To * p.n_act;
+    for (long long g = g0; g < total; g += stride) {
+      const int j = (int)(g % p.n_act);
+      const long long q = g / p.n_act;
+      const int s = (int)(q % p.To);
+      p.a[g] = p.se[(p.w0 + q / p.To + s) * p.n_act + j];
+    }
+  }
+  {
+    const long long total = p.nw * p.Ti * p.M * p.e_in;
+    for (long long g = g0; g < total; g += stride) {
+      const long long L = (long long)p.M * p.e_in, l = g % L, q = g / L;
+      const int s = (int)(q % p.Ti);
+      const long long t = p.w0 + q / p.Ti - p.Ti + s;
+      p.ex[g] = t >= 0 ? p.es[t * L + l] : 0.f;
+    }
+  }
+}
+
+// fp32 FFMA peak of the device (bench.py's roofline denominator of the fp32 parity path): 16 independent chains per thread
+__global__ void fp32_peak_kernel(float* out, int iters) {
+  float a[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) a[k] = (float)(threadIdx.x + k) * 1e-3f;
+  const float b = 0.999f, c = 1e-3f;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) a[k] = fmaf(a[k], b, c);
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) s += a[k];
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 }  // namespace gu

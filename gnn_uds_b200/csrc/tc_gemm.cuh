@@ -160,7 +160,8 @@ __device__ __forceinline__ void tile_rows(const TcGemmP& p, unsigned tile, unsig
 
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_constant__ TcGemmP p) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // warp index through a shuffle: known warp-uniform to the compiler, so the role code stays on the uniform datapath
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   uint8_t* Wsm = smem;
   uint8_t* stages = smem + p.stage_off;
   float* hbuf = reinterpret_cast<float*>(smem + p.h_off);
@@ -278,12 +279,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
     }
   } else if (warp == TC_EPI_WARPS + TC_PROD_WARPS) {
     // ================================ MMA issuer ================================
-    if (lane == 0) {
-      tc::mbar_expect_tx(wbar, p.w_bytes);
-      for (uint32_t o = 0; o < p.w_bytes; o += 16384) {
-        const uint32_t n = p.w_bytes - o < 16384u ? p.w_bytes - o : 16384u;
-        tc::bulk_g2s(Wsm + o, p.Wimg + o, n, wbar);
+    // warp-uniform code, one elected lane issues (tc::elect_one): no ELECT / R2UR waterfall around the tcgen05 instructions
+    {
+      if (tc::elect_one()) {
+        tc::mbar_expect_tx(wbar, p.w_bytes);
+        for (uint32_t o = 0; o < p.w_bytes; o += 16384) {
+          const uint32_t n = p.w_bytes - o < 16384u ? p.w_bytes - o : 16384u;
+          tc::bulk_g2s(Wsm + o, p.Wimg + o, n, wbar);
+        }
       }
+      __syncwarp();
       tc::mbar_wait(wbar, 0);
       const uint32_t idesc = tc::idesc_bf16(128, p.Nout, 0, 0);
       bool any_cp = false;
@@ -314,13 +319,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
           uint64_t ad = a_desc0 + (uint64_t)(((uint32_t)stage * stage_bytes) >> 4);
 #pragma unroll 4
           for (int ks = 0; ks < kpc; ++ks, ad += a_step, bd += w_step) {
-            tc::umma(acc, ad, bd, idesc, (ch | ks) != 0);
-            if (MT2) tc::umma(acc + (uint32_t)Nout, ad + a_mt2, bd, idesc, (ch | ks) != 0);
+            if (tc::elect_one()) {
+              tc::umma(acc, ad, bd, idesc, (ch | ks) != 0);
+              if (MT2) tc::umma(acc + (uint32_t)Nout, ad + a_mt2, bd, idesc, (ch | ks) != 0);
+            }
           }
-          tc::umma_commit(&empty[stage]);
+          if (tc::elect_one()) tc::umma_commit(&empty[stage]);
+          __syncwarp();
           if (++stage == NS) { stage = 0; fphase ^= 1; }
         }
-        tc::umma_commit(&tfull[as]);
+        if (tc::elect_one()) tc::umma_commit(&tfull[as]);
+        __syncwarp();
       }
     }
   } else {

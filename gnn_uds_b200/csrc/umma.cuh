@@ -33,17 +33,21 @@ __device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+// try_wait with a suspend-time hint (as CUTLASS' ClusterBarrier::wait): the hardware parks the thread until the phase
+// completes or the hint expires instead of returning after a short system-dependent limit.  Without the hint, 16 waiting
+// warps re-poll the barrier word in shared memory continuously and take shared-memory bandwidth from the tensor core's
+// operand fetch (SS-mode MMAs need all 128 B/clk: measured 2x slower MMAs next to spinning warps).
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n\t"
       ".reg .pred p;\n\t"
       "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
       "@p bra DONE_%=;\n\t"
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t"
       "}\n" ::"r"(smem_u32(bar)),
-      "r"(parity)
+      "r"(parity), "r"(0x989680u)
       : "memory");
 }
 
@@ -200,6 +204,15 @@ __device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t b
       "}\n" ::"r"(tmem_d),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
+}
+// One lane of a fully converged warp.  tcgen05.mma / commit take their operands from uniform registers: issued under
+// `if (lane == 0)` the compiler treats descriptors and addresses as thread-variant and wraps EVERY instruction in an
+// ELECT / R2UR / BRA.U.ANY waterfall loop (~12 extra instructions, 100-160 cycles per MMA under load).  Warp-uniform issue
+// code with only the instruction itself behind elect_one() keeps the whole descriptor arithmetic on the uniform datapath.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 // all previously issued MMAs of this thread complete -> one arrival on `bar`
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {

@@ -14,6 +14,7 @@ or without a CUDA device construction fails.
 """
 import ctypes as C
 import os
+import sys
 from types import SimpleNamespace
 
 import numpy as np
@@ -334,10 +335,23 @@ class Emulator:
 
     def _run_predict(self, x, b, a, ex):
         B = x.shape[0]
-        y = np.empty((B, self.seq_out, self.n_node, self.y_channels), np.float32)
-        ey = np.empty((B, self.seq_out, self.n_edge, self.ey_channels), np.float32)
+        y, ey = self._out_arrays(B)
         _lib.check(self._h, self._lib.gnnuds_predict(self._h, _ptr(x), _ptr(b), _ptr(a), _ptr(ex), B,
                                                      _ptr(y), _ptr(ey), _lib.MEM_HOST))
+        return y, ey
+
+    def _out_arrays(self, B):
+        """Result arrays of a predict call.  Fresh arrays as in the reference, except that a large pair handed out by the
+        previous call is recycled once the caller has dropped every reference to it (views included): first-touch
+        page faults of a fresh 0.9 GB result cost more than the copy that fills it."""
+        shp = ((B, self.seq_out, self.n_node, self.y_channels), (B, self.seq_out, self.n_edge, self.ey_channels))
+        c = getattr(self, "_out_cache", None)
+        if c is not None and c[0].shape == shp[0] and c[1].shape == shp[1]:
+            y, ey = c
+            if sys.getrefcount(y) == 3 and sys.getrefcount(ey) == 3:   # the cache tuple, these locals, the call's argument
+                return y, ey
+        y, ey = np.empty(shp[0], np.float32), np.empty(shp[1], np.float32)
+        self._out_cache = (y, ey) if y.nbytes + ey.nbytes >= (16 << 20) else None
         return y, ey
 
     def predict_ptrs(self, x, b, a, ex, B, y, ey, device=True):
@@ -423,6 +437,39 @@ class Emulator:
                                                        _ptr(gm), _ptr(obj), _lib.MEM_HOST))
         return obj
 
+    def evaluate(self, state, runoff, edge_state, dec, r_step, horizon, flood_w, wwtp_w, rough_w=None, gamma=None,
+                 rule="mpc", obj_ptr=None):
+        """MPC population evaluation in one device-resident call (gnnuds_evaluate): ONE observed state
+        (seq_in,N,n_in) / edge_state (seq_in,M,e_in) shared by the candidates, runoff (horizon,N,b_in) or
+        (n_b,horizon,N,b_in), dec (pop,n_step,n_act) held r_step steps each (mpc.py:211-218), objective weights as in
+        `objective`.  Returns the per-candidate objectives (pop,) as NumPy, or writes them to the device pointer
+        `obj_ptr` (an int, e.g. a torch CUDA tensor's data_ptr()) and returns None."""
+        code = {"mpc": _lib.ROLL_MPC, "mbrl": _lib.ROLL_MBRL}[rule]
+        x0 = _f32(np.asarray(state)[-self.seq_in:])
+        ex0 = _f32(np.asarray(edge_state)[-self.seq_in:])
+        b = _f32(runoff)
+        if b.ndim == 3:
+            b = b[None]
+        dec = _f32(dec)
+        if x0.shape != (self.seq_in, self.n_node, self.n_in) or ex0.shape != (self.seq_in, self.n_edge, self.e_in):
+            raise ValueError("state %s / edge_state %s: one observed window expected" % (x0.shape, ex0.shape))
+        if horizon % self.seq_out or b.shape[1:] != (horizon, self.n_node, self.b_in):
+            raise ValueError("runoff shape %s does not cover a horizon of %d steps" % (b.shape, horizon))
+        if dec.ndim != 3 or dec.shape[2] != self.n_act:
+            raise ValueError("dec shape %s, expected (pop, n_step, %d)" % (dec.shape, self.n_act))
+        B = dec.shape[0]
+        fw, ww = _f32(flood_w), _f32(wwtp_w)
+        rw = None if rough_w is None else _f32(rough_w)
+        gm = None if gamma is None else _f32(gamma)
+        if gm is not None and gm.shape[0] < horizon:
+            raise ValueError("gamma needs one weight per horizon step")
+        obj = None if obj_ptr is not None else np.empty(B, np.float32)
+        _lib.check(self._h, self._lib.gnnuds_evaluate(
+            self._h, code, _ptr(x0), _ptr(ex0), _ptr(b), b.shape[0], _ptr(dec), dec.shape[1], int(r_step), B,
+            horizon // self.seq_out, _ptr(fw), _ptr(ww), _ptr(rw), _ptr(gm), obj_ptr if obj_ptr is not None else _ptr(obj),
+            _lib.MEM_HOST, _lib.MEM_DEVICE if obj_ptr is not None else _lib.MEM_HOST))
+        return obj
+
     # ------------------------------------------------------------------ instrumentation
     def launch_count(self):
         return int(self._lib.gnnuds_launch_count(self._h))
@@ -435,6 +482,12 @@ class Emulator:
         t, g = C.c_float(), C.c_float()
         self._lib.gnnuds_last_timing(self._h, C.byref(t), C.byref(g))
         return t.value, g.value
+
+    def measure_fp32_tflops(self):
+        """fp32 FFMA peak of this device, measured now (TFLOP/s)."""
+        t = C.c_float()
+        _lib.check(self._h, self._lib.gnnuds_measure_simt_tflops(self._h, C.byref(t)))
+        return float(t.value)
 
     def kernel_timing(self, family):
         """(ms, launches) of one kernel family in the last call (profiling level 2): 0 rows GEMM, 1 fused spatial, 2 gather."""

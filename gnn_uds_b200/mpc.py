@@ -96,11 +96,42 @@ class MpcEvaluator:
                 objs = objs.reshape(hi - lo, self.stochastic).mean(axis=1)
         return sharding.gather_objectives(objs, pop, device=em.device)
 
+    def pred_emu_device(self, y):
+        """pred_emu with nothing but the decision matrix and the objectives crossing PCIe: the shared state / runoff are
+        broadcast on the device, the chunk loop and the objective reduction run in gnnuds_evaluate, and (NCCL) the
+        per-candidate objectives go from the kernel's output buffer straight into the all-gather; ONE device->host
+        copy of the gathered vector at the end.  Bitwise equal to pred_emu on the fp32 path."""
+        dec = np.asarray(y, np.float32).reshape((-1, self.n_step, self.n_act))
+        pop = dec.shape[0]
+        rank, ws = sharding.world()
+        lo, hi = sharding.shard_range(pop, rank, ws)
+        k = max(self.stochastic, 1)
+        mine = np.repeat(dec[lo:hi], k, axis=0) if self.stochastic else dec[lo:hi]
+        T = self.eval_hrz // self.step
+        em = self.emul
+        runoff = np.asarray(self.runoff, np.float32)                # (T,N,b_in) or (stochastic,T,N,b_in)
+        gamma = None if self.gamma is None else np.asarray(self.gamma, np.float32)
+        rw = self.rw if self.rough else None
+        if ws > 1 and sharding.backend() == "nccl" and not self.stochastic:
+            import torch
+            per = (pop + ws - 1) // ws
+            buf = torch.zeros(per, dtype=torch.float32, device=torch.device("cuda", em.device))
+            if hi > lo:
+                em.evaluate(self.state, runoff, self.edge_state, mine, self.r_step, T, self.fw, self.ww, rw, gamma,
+                            obj_ptr=buf.data_ptr())
+            return sharding.gather_objectives_device(buf, pop)
+        objs = np.zeros(0, np.float32)
+        if hi > lo:
+            objs = em.evaluate(self.state, runoff, self.edge_state, mine, self.r_step, T, self.fw, self.ww, rw, gamma)
+            if self.stochastic:
+                objs = objs.reshape(hi - lo, self.stochastic).mean(axis=1)
+        return sharding.gather_objectives(objs, pop, device=em.device)
+
     def _evaluate(self, x, out, *args, **kwargs):                   # mpc.py:261-264
-        out["F"] = self.pred_emu(x) + 1e-6
+        out["F"] = self.pred_emu_device(x) + 1e-6
 
     def pred(self, x):                                              # mpc.py:273-276
-        return self.pred_emu(x) + 1e-6
+        return self.pred_emu_device(x) + 1e-6
 
 
 def latin_hypercube(pop, lo, hi, rng):

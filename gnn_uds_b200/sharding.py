@@ -20,6 +20,17 @@ def world():
     return 0, 1
 
 
+def backend():
+    """Backend name of the default process group ('nccl', 'gloo'), None when not initialised."""
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_backend()
+    except Exception:
+        pass
+    return None
+
+
 def shard_range(n, rank, world_size):
     """Contiguous slice [lo, hi) of n items for `rank`: ceil(n/G) per rank."""
     per = (n + world_size - 1) // world_size
@@ -63,3 +74,17 @@ def gather_objectives(local_obj, n_total, device=None):
         lo, hi = shard_range(n_total, r, ws)
         parts.append(out[r, : hi - lo])
     return np.concatenate(parts)
+
+
+def gather_objectives_device(local_buf, n_total):
+    """Same all-gather for objectives that already sit in a padded device tensor of ceil(n_total/ws) floats (written by
+    gnnuds_evaluate): the shards stay on the device through the collective, ONE device->host copy at the end."""
+    import torch
+    import torch.distributed as dist
+    rank, ws = world()
+    per = (n_total + ws - 1) // ws
+    assert local_buf.numel() == per
+    out = torch.empty(per * ws, dtype=torch.float32, device=local_buf.device)
+    dist.all_gather_into_tensor(out, local_buf)
+    out = out.cpu().numpy().reshape(ws, per)
+    return np.concatenate([out[r, : shard_range(n_total, r, ws)[1] - shard_range(n_total, r, ws)[0]] for r in range(ws)])

@@ -126,6 +126,9 @@ int gnnuds_set_post_proc_variant(gnnuds_handle* h, int32_t variant);
 /* 16-bit operand type of this build's tensor-core path: 16 = IEEE fp16 (default), 0 = bfloat16 (-DGNNUDS_TC_BF16).
    No handle needed. */
 int gnnuds_tc_operand_is_half(void);
+/* fp32 FFMA peak of the handle's device in TFLOP/s, measured now with a register-only FMA kernel (the roofline
+ * denominator of the fp32 parity path; SURVEY.md 8(d) asks for a measured figure instead of the nominal 74). */
+int gnnuds_measure_simt_tflops(gnnuds_handle* h, float* tflops);
 
 /* Channels of the node output y ([h,q_us,q_ds,(flood_prob),q_w]) and edge output. */
 int gnnuds_output_dims(const gnnuds_handle* h, int32_t* y_channels, int32_t* ey_channels);
@@ -160,6 +163,36 @@ int gnnuds_rollout(gnnuds_handle* h, int32_t rule, const float* x0, const float*
 int gnnuds_objective(gnnuds_handle* h, const float* y, const float* q_in0, int64_t B, int32_t T,
                      const float* flood_w, const float* wwtp_w, const float* rough_w,
                      const float* gamma, float* obj, int32_t where);
+
+/* MPC population evaluation as ONE device-resident call (mpc.py:210-259 pred_emu/pred_emu_tf, :565-582 chunked loop,
+ * envs/scenario/astlingen.py:75-99 objective): B candidates share one observed state x0 (seq_in,N,n_in) / ex0
+ * (seq_in,M,e_in) - the reference tiles them on the host (mpc.py:237-240) - and n_b runoff scenarios b
+ * (n_b, n_chunks*seq_out, N, b_in); candidate i runs scenario i % n_b (n_b = `stochastic`, else 1).  dec is the
+ * decision matrix (B, n_step, n_act); every setting is held r_step steps and the last one to the end of the horizon
+ * (mpc.py:211-218).  n_chunks == 1 is one forward, n_chunks > 1 the autoregressive chunk loop with feedback `rule`
+ * (GNNUDS_ROLL_MPC / GNNUDS_ROLL_MBRL).  Predictions never leave the device: the objective (weights per node as in
+ * gnnuds_objective, gamma per horizon step or NULL) is accumulated chunk by chunk and only obj (B) is written, to host
+ * (obj_where GNNUDS_MEM_HOST) or device memory.  `where` says where x0, ex0, b, dec and the weight vectors live.
+ * Bitwise equal to gnnuds_predict / gnnuds_rollout followed by gnnuds_objective on the fp32 path. */
+int gnnuds_evaluate(gnnuds_handle* h, int32_t rule, const float* x0, const float* ex0, const float* b, int32_t n_b,
+                    const float* dec, int32_t n_step, int32_t r_step, int64_t B, int32_t n_chunks, const float* flood_w,
+                    const float* wwtp_w, const float* rough_w, const float* gamma, float* obj, int32_t where,
+                    int32_t obj_where);
+
+/* Event replay (main.py:306-382 test loop, dataloader.py:93-95 expand_seq): one rainfall event of T recorded steps -
+ * states (T,N,4) = [h, cuminflow, outflow, lateral inflow], perfs (T,N) cumflooding (if_flood models, else NULL),
+ * edge_states (T,M,4), settings (T,n_act) (act models, else NULL) - is uploaded ONCE and its T - seq_out teacher-forced
+ * windows are built on the device by index arithmetic (the reference expands every series seq-fold on the host):
+ * window w = states of steps w-seq_in..w-1 (zero-padded before the event start, q_us = cuminflow - lateral, flood flag =
+ * cumflooding > 0), runoff of steps w+seq_out-seq.. (seq = max(seq_in,seq_out), first seq_out of them), settings of steps
+ * w..w+seq_out-1.  gnnuds_replay runs Emulator.simulate over all windows: y (T-seq_out, seq_out, N, y_channels),
+ * ey (T-seq_out, seq_out, M, ey_channels).  gnnuds_build_windows returns windows w0..w0+nw-1 themselves
+ * (x (nw,seq_in,N,n_in), b (nw,seq_out,N,b_in), a (nw,seq_out,n_act) or NULL, ex (nw,seq_in,M,4)). */
+int gnnuds_replay(gnnuds_handle* h, const float* states, const float* perfs, const float* edge_states, const float* settings,
+                  int64_t T, float* y, float* ey, int32_t where);
+int gnnuds_build_windows(gnnuds_handle* h, const float* states, const float* perfs, const float* edge_states,
+                         const float* settings, int64_t T, int64_t w0, int64_t nw, float* x, float* b, float* a, float* ex,
+                         int32_t where);
 
 /* Pinned host buffers for callers that want truly asynchronous copies. */
 int gnnuds_alloc_pinned(void** p, int64_t bytes);

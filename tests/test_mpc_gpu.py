@@ -41,3 +41,42 @@ def test_mpc_evaluator_matches_oracle(horizon_chunks):
     close = np.isclose(F, ref, rtol=2e-4, atol=2e-4)
     print("mpc objective: %d of %d candidates within tolerance, max |d| %.3g" % (close.sum(), pop, np.abs(F - ref).max()))
     assert close.mean() >= (1.0 if horizon_chunks == 1 else 0.8)
+
+
+@pytest.mark.parametrize("horizon_chunks,stochastic", [(1, 0), (3, 0), (2, 3)])
+def test_evaluate_bitwise_equals_host_bounce(horizon_chunks, stochastic):
+    """gnnuds_evaluate (state broadcast, chunk loop and objective on the device, only dec in / obj out) returns bitwise
+    the objectives of the old path: predictions copied to the host (predict / rollout) and back into gnnuds_objective."""
+    from gnn_uds_b200 import mpc, synthetic
+    case = "c3_ast_act_5"
+    em, _ = cases.setup_product(case)
+    net, _ = cases.load_net("astlingen")
+    T = em.seq_out * horizon_chunks
+    ev = mpc.MpcEvaluator(em, net.nodes, interval=1, eval_horizon=T, control_horizon=T, setting_duration=5,
+                          stochastic=stochastic, gamma=0.9 ** np.arange(T))
+    rng = np.random.default_rng(5)
+    states, b, _, ex = synthetic.make_inputs(em, max(stochastic, 1), rng, horizon=T)
+    ev.load_state(states[0], b if stochastic else b[0], ex[0])
+    pop = 37
+    x = mpc.latin_hypercube(pop, np.full(ev.n_var, 0.1), np.ones(ev.n_var), rng)
+    old = ev.pred_emu(x)
+    new = ev.pred_emu_device(x)
+    assert old.shape == new.shape == (pop,)
+    assert np.array_equal(old, new), "max |d| %.3g" % np.abs(old - new).max()
+
+
+def test_evaluate_argument_errors():
+    from gnn_uds_b200 import synthetic
+    em, _ = cases.setup_product("c3_ast_act_5")
+    rng = np.random.default_rng(1)
+    states, b, a, ex = synthetic.make_inputs(em, 1, rng)
+    w = np.ones(em.n_node, np.float32)
+    with pytest.raises(ValueError):
+        em.evaluate(states[0], b[0][:-1], ex[0], a[:, :1], 5, em.seq_out, w, w)           # runoff shorter than the horizon
+    with pytest.raises(ValueError):
+        em.evaluate(states[0], b[0], ex[0], a[:, :1, :-1], 5, em.seq_out, w, w)           # wrong number of controls
+    em2, _ = cases.setup_product("c1_ast_gcn_gru")                                         # no act / no flood head
+    s2, b2, _, e2 = synthetic.make_inputs(em2, 1, rng)
+    with pytest.raises(Exception):
+        em2.evaluate(s2[0], b2[0], e2[0], np.ones((3, 1, 1), np.float32), 5, em2.seq_out, np.ones(em2.n_node, np.float32),
+                     np.ones(em2.n_node, np.float32))
