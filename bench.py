@@ -328,6 +328,102 @@ def run_mpc(a):
         dist.destroy_process_group()
 
 
+def run_c4(a):
+    """--workload C4: BASELINE.json configs[3] - the C2 model replayed over all 148 shunqing events (lengths from
+    events.csv, synthetic recorded series), whole events balanced over the ranks (strong scaling).  Mode A = the reference's
+    test loop (main.py:306-382): every event's T - seq_out teacher-forced windows, built on the device from the raw series
+    (Emulator.replay), predictions returned as NumPy arrays.  Mode B (secondary figure) = a true autoregressive roll of
+    every event from its first full window (MPC feedback rule)."""
+    import torch
+    import torch.distributed as dist
+    from gnn_uds_b200 import configs, replay, sharding
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    precision = "bf16" if a.precision == "auto" else a.precision
+    em, args, _ = configs.make_emulator("C2", device=local, precision=precision)
+    names, sets, steps = replay.shunqing_events()
+    if a.batch:                                   # --batch K: only the first K events (quick runs)
+        names, sets, steps = names[:a.batch], sets[:a.batch], steps[:a.batch]
+    mine = sharding.balance_events(steps, world)[rank]
+    events = {i: replay.synthetic_event(em, int(steps[i]), np.random.default_rng(1000 + i)) for i in mine}
+    To, N = em.seq_out, em.n_node
+    units_all = int(sum((int(t) - To) * To * N for t in steps))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_pass():
+        chk, dev_ms = 0.0, 0.0
+        for i in mine:
+            e = events[i]
+            p, ep = em.replay(e["states"], e["perfs"], e["edge_states"], e["settings"])
+            dev_ms += em.last_timing()[0]
+            chk += float(p[-1, -1, 0, 0]) + float(ep[-1, -1, 0, 0])
+            del p, ep
+        return chk, dev_ms
+
+    em.set_profiling(1)
+    for _ in range(max(1, min(a.warmup, 1))):     # one warm-up pass = 148 events, every shape seen
+        one_pass()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = em.launch_count()
+    t0 = time.perf_counter()
+    dev_ms = 0.0
+    for _ in range(a.steps):
+        chk, d = one_pass()
+        dev_ms += d
+    barrier()
+    wall = time.perf_counter() - t0
+    launches = em.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    # mode B: autoregressive roll of every event of this rank
+    tb = time.perf_counter()
+    units_b = 0
+    for i in mine:
+        e = events[i]
+        y, _, _ = replay.replay_event_ar(em, e["states"], e["perfs"], e["edge_states"], e["settings"])
+        units_b += y.shape[1] * N
+    barrier()
+    wall_b = time.perf_counter() - tb
+    t_all = torch.tensor([dev_ms, wall, wall_b, float(units_b)], dtype=torch.float64, device=dev)
+    u_all = torch.tensor([float(units_b)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_all, op=dist.ReduceOp.MAX)
+        dist.all_reduce(u_all, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        ms = float(t_all[0].item()) / a.steps
+        line = {"metric": METRIC.replace("rollout", "full-event replay"), "value": units_all / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
+                "steps": a.steps, "warmup": 1, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32" if precision == "fp32" else ("f16(f32 acc)" if em._lib.gnnuds_tc_operand_is_half() else "bf16(f32 acc)"),
+                "data": "synthetic",
+                "config": {"workload": "C4: shunqing GAT+Conv1D edge_fusion resnet flood 60->60 replayed over %d events (%d recorded steps, "
+                                       "%d teacher-forced windows, reference accounting sum (T-seq_out)*seq_out*N), one step = all events"
+                                       % (len(steps), int(steps.sum()), int(sum(int(t) - To for t in steps))),
+                           "l2": "every event's window batch (360..1440 windows x 60 steps) exceeds the 126 MB L2", "precision": precision,
+                           "sharding": "whole events balanced over ranks by length, no data-path collective"},
+                "e2e": {"value": units_all * a.steps / float(t_all[1].item()), "unit": UNIT,
+                        "h2d_bytes_per_step": int(sum(sum(v.nbytes for v in e.values() if v is not None) for e in events.values())),
+                        "d2h_bytes_per_step": int(sum((int(steps[i]) - To) * To * (N * em.y_channels + em.n_edge * em.ey_channels) * 4 for i in mine)),
+                        "note": "Emulator.replay(raw series) per event, wall clock: raw series in, all window predictions out as NumPy (rank 0's bytes)"},
+                "mode_b": {"value": float(u_all.item()) / float(t_all[2].item()), "unit": UNIT,
+                           "note": "true autoregressive roll of every event from its first full window (B=1 per event, MPC rule), wall clock"},
+                "gpu_launches": int(launches), "clocks": clocks, "checksum": chk, "wall_s_timed_region": wall}
+        emit(line)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 _JSON_OUT = None
 
 
@@ -358,6 +454,8 @@ def main():
         return run_reference(a)
     if a.workload == "C3mpc":
         return run_mpc(a)
+    if a.workload == "C4":
+        return run_c4(a)
 
     import torch
     import torch.distributed as dist

@@ -405,6 +405,51 @@ class Emulator:
         runoff = np.asarray(runoff)[:, :self.seq_out]
         return self.predict(states, runoff, a, edge_states)
 
+    def _replay_args(self, states, perfs, edge_states, settings):
+        st = _f32(states)
+        es = _f32(edge_states)
+        T = st.shape[0]
+        if st.shape[1:] != (self.n_node, 4) or es.shape != (T, self.n_edge, 4):
+            raise ValueError("replay: states (T,%d,4) [h, cuminflow, outflow, lateral] and edge_states (T,%d,4) expected, got %s / %s"
+                             % (self.n_node, self.n_edge, st.shape, es.shape))
+        pf = None
+        if self.if_flood:
+            if perfs is None:
+                raise ValueError("replay: an if_flood model needs the cumflooding series `perfs` (main.py:339)")
+            pf = _f32(np.asarray(perfs).reshape(T, self.n_node))
+        se = None
+        if self.act:
+            if settings is None:
+                raise ValueError("replay: an act model needs the settings series (main.py:350)")
+            se = _f32(np.asarray(settings).reshape(T, self.n_act))
+        return st, pf, es, se, T
+
+    def replay(self, states, perfs, edge_states, settings=None):           # main.py:327-361 + emulator.py:521-564
+        """Teacher-forced replay of ONE recorded event: the T - seq_out windows of main.py:327-354 are built on the device
+        from the raw series (states (T,N,4) [h, cuminflow, outflow, lateral], perfs (T,N) cumflooding, edge_states (T,M,4),
+        settings (T,n_act)) and run as one batch.  Returns what ``emul.simulate(states_w, r, a, edge_states_w)`` returns:
+        (T-seq_out, seq_out, N, y_channels), (T-seq_out, seq_out, M, ey_channels)."""
+        st, pf, es, se, T = self._replay_args(states, perfs, edge_states, settings)
+        W = max(T - self.seq_out, 0)
+        y = np.empty((W, self.seq_out, self.n_node, self.y_channels), np.float32)
+        ey = np.empty((W, self.seq_out, self.n_edge, self.ey_channels), np.float32)
+        _lib.check(self._h, self._lib.gnnuds_replay(self._h, _ptr(st), _ptr(pf), _ptr(es), _ptr(se), T, _ptr(y), _ptr(ey), _lib.MEM_HOST))
+        return y, ey
+
+    def build_windows(self, states, perfs, edge_states, settings=None, first=0, count=None):
+        """The replay windows themselves (device window builder, expand_seq semantics): x, b, a, ex of windows
+        first..first+count-1, laid out as ``predict`` takes them."""
+        st, pf, es, se, T = self._replay_args(states, perfs, edge_states, settings)
+        W = max(T - self.seq_out, 0)
+        count = W - first if count is None else count
+        x = np.empty((count, self.seq_in, self.n_node, self.n_in), np.float32)
+        b = np.empty((count, self.seq_out, self.n_node, self.b_in), np.float32)
+        a = np.empty((count, self.seq_out, self.n_act), np.float32) if self.act else None
+        ex = np.empty((count, self.seq_in, self.n_edge, self.e_in), np.float32)
+        _lib.check(self._h, self._lib.gnnuds_build_windows(self._h, _ptr(st), _ptr(pf), _ptr(es), _ptr(se), T, int(first), int(count),
+                                                           _ptr(x), _ptr(b), _ptr(a), _ptr(ex), _lib.MEM_HOST))
+        return x, b, a, ex
+
     # ------------------------------------------------------------------ autoregressive loops
     def rollout(self, states, b, a=None, edge_state=None, rule="mpc"):
         """Chunked autoregressive rollout on the device.  rule: 'mpc' (mpc.py:565-582),

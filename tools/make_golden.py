@@ -25,6 +25,17 @@ OUT = os.path.join(ROOT, "tests", "golden")
 AST_ACT_LINKS = ["V2", "V3", "V4", "V6"]       # envs/config/astlingen.yaml:114-163 action_space keys
 
 
+def events_table():
+    """envs/network/shunqing/events.csv -> gnn_uds_b200/data/shunqing_events.npz (name, Train/Test, duration in hours):
+    the event list of BASELINE.json configs[3] (replay of all 148 synthetic rainfalls)."""
+    import csv
+    rows = list(csv.reader(open(os.path.join(REF, "shunqing", "events.csv"))))[1:]
+    out = os.path.join(ROOT, "gnn_uds_b200", "data", "shunqing_events.npz")
+    np.savez_compressed(out, name=np.array([r[0] for r in rows]), set=np.array([r[1] for r in rows]),
+                        duration_h=np.array([float(r[2]) for r in rows]))
+    print("wrote", out, len(rows), "events")
+
+
 def dense_to_csr(a):
     rp, ci, vv = [0], [], []
     for i in range(a.shape[0]):
@@ -74,6 +85,10 @@ def forward_vectors():
         np.savez_compressed(os.path.join(OUT, "fwd_%s.npz" % case), **d)
         print(case, {k: v.shape for k, v in d.items()})
 
+
+if __name__ == "__main__" and "--events" in sys.argv:
+    events_table()
+    sys.exit(0)
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
