@@ -176,9 +176,9 @@ def peaks():
 
 def traffic_per_launch(dom, workload, B, launches_per_step):
     """dram__bytes_read + dram__bytes_write per launch of the dominant kernel from the committed ncu capture
-    (profiles/r01_traffic.json: bytes per scenario and step, measured at one batch size; the kernels stream
+    (profiles/r02_traffic.json: bytes per scenario and step, measured at one batch size; the kernels stream
     scenarios independently, so the figure scales linearly with B)."""
-    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    p = os.path.join(ROOT, "profiles", "r02_traffic.json")
     if not os.path.exists(p):
         return None
     d = json.load(open(p)).get(workload, {}).get(dom["kernel"].split(" ")[0])

@@ -52,7 +52,7 @@ SYMBOLS = [
     "gnnuds_rollout", "gnnuds_objective", "gnnuds_evaluate", "gnnuds_replay", "gnnuds_build_windows", "gnnuds_alloc_pinned", "gnnuds_free_pinned", "gnnuds_alloc_device",
     "gnnuds_free_device", "gnnuds_memcpy", "gnnuds_synchronize", "gnnuds_launch_count", "gnnuds_last_timing",
     "gnnuds_set_profiling", "gnnuds_measure_simt_tflops", "gnnuds_kernel_timing", "gnnuds_debug_stop_after", "gnnuds_debug_fetch", "gnnuds_debug_umma_selftest",
-    "gnnuds_tc_operand_is_half", "gnnuds_set_post_proc_variant",
+    "gnnuds_tc_operand_is_half", "gnnuds_set_post_proc_variant", "gnnuds_set_adj_action",
 ]
 
 
@@ -97,6 +97,7 @@ def load():
     lib.gnnuds_kernel_timing.argtypes = [vp, i32, P(C.c_float), P(i64)]
     lib.gnnuds_debug_stop_after.argtypes = [vp, i32]
     lib.gnnuds_set_post_proc_variant.argtypes = [vp, i32]
+    lib.gnnuds_set_adj_action.argtypes = [vp, vp, vp]
     lib.gnnuds_debug_fetch.argtypes = [vp, i32, vp, i64, P(i64), P(i32)]
     lib.gnnuds_debug_umma_selftest.argtypes = [vp, i32, vp, i32, i32, vp, i32, i32, i32, i32, vp]
     for s in SYMBOLS:

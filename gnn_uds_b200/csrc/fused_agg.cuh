@@ -238,9 +238,12 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
         for (int s = 0; s < p.nseg; ++s)
           for (int k0 = 0; k0 < p.segw[s]; k0 += 64, o += p.chunk_bytes) tc::tma_load_2d(dst + o, &p.tm_self[s], k0, smp * p.R, &self_full[buf]);
       };
+      // the other_dense tile of sample k+2 is free to load (NodeEdge[k+1] committed) long before the self buffer of sample
+      // k+1 (aggregation of sample k-1 / k committed): keep that order, or the NodeEdge MMAs wait for a late tile
       issue_xe(0);
       issue_self(0);
-      for (int i = 0; i + 1 < n_it; ++i) { issue_xe(i + 1); issue_self(i + 1); }
+      if (n_it > 1) issue_xe(1);
+      for (int k = 0; k + 1 < n_it; ++k) { if (k + 2 < n_it) issue_xe(k + 2); issue_self(k + 1); }
     }
   } else if (warp == SA_WORKERS) {
     // ================================ MMA issuer ================================
@@ -272,6 +275,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
       const uint32_t chunk_bytes = p.chunk_bytes;
       auto issue_ne = [&](int i) {
         tc::mbar_wait(xe_full, i & 1);
+        if (i >= 1) tc::mbar_wait(nx_ready, (i - 1) & 1);                 // NodeEdge accumulators of sample i-1 drained
         tc::tc_fence_after();
         if (lane == 0) SA_STAMPM(i, 16);
         // groups of 4 K steps behind ONE election, every descriptor computed from the base (no dependent add chain on the
@@ -338,13 +342,15 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
       // pipe order: conv[i+1] goes in BEFORE agg[i] when the accumulators are separate (MT == 1): it runs while the workers
       // do the softmax of sample i.  With aliased accumulators conv[i+1] has to wait for the aggregation
       // drain of sample i.
-      issue_ne(0);
-      issue_conv(0);
-      if (n_it > 1) issue_ne(1);
+      // Separate accumulators (MT == 1): NodeEdge runs TWO samples ahead - per sample the pipe sees NE[i+2], conv[i+1],
+      // agg[i]; the workers drain NE[i+2] while they would otherwise wait for agg[i], and conv[i+1] has its NodeEdge panels
+      // from the previous sample's wait window, so it starts as soon as the conv accumulators of sample i are drained.
+      if (!alias) { issue_ne(0); if (n_it > 1) issue_ne(1); issue_conv(0); }
+      else { issue_ne(0); issue_conv(0); if (n_it > 1) issue_ne(1); }
       for (int i = 0; i < n_it; ++i) {
         const int buf = i % NB;
         const uint32_t in_addr = tc::smem_u32(smem + p.off_self + (size_t)buf * p.self_stride);
-        if (!alias && i + 1 < n_it) issue_conv(i + 1);
+        if (!alias) { if (i + 2 < n_it) issue_ne(i + 2); if (i + 1 < n_it) issue_conv(i + 1); }
         // ---- agg[i] ----
         tc::mbar_wait(alpha_ready, i & 1);
         if (!alias && i >= 1) tc::mbar_wait(out_done, (i - 1) & 1);       // aggregation accumulators of sample i-1 drained
@@ -374,8 +380,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
         if (lane == 0) SA_STAMPM(i, 15);
         // NodeEdge[i+2] goes in behind agg[i] (its MN-major B operand makes it slow, ~100 cycles per K step, and the
         // aggregation drain is waiting for agg[i]); its result is not needed before the conv drain of sample i+1 is over
-        if (alias && i + 1 < n_it) issue_conv(i + 1);
-        if (i + 2 < n_it) issue_ne(i + 2);
+        if (alias) { if (i + 1 < n_it) issue_conv(i + 1); if (i + 2 < n_it) issue_ne(i + 2); }
       }
     }
   } else {
@@ -404,7 +409,9 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
       tc::tc_fence_before();
       mbar_arrive(nx_ready);
     };
+    const bool alias_w = p.alias_acc != 0;
     if (n_it > 0) drain_ne(0);
+    if (!alias_w && n_it > 1) { tc::mbar_wait(conv_done, 0); drain_ne(1); }   // panels[1] once conv[0] has read panels[0]
     for (int i = 0; i < n_it; ++i) {
       const int buf = i % NB;
       const int smp = (int)blockIdx.x + i * (int)gridDim.x;
@@ -453,8 +460,8 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
       SA_STAMP(i, 1);
       // ---- C: NodeEdge accumulators of the next sample -> fp16 panels (back to back with the conv drain: the softmax
       //         then runs with no TMEM reads in flight, which slow concurrent MMAs ~2x) ----
-      if (i + 1 < n_it) drain_ne(i + 1);
-      SA_STAMP(i, 3);
+      if (alias_w && i + 1 < n_it) drain_ne(i + 1);
+      if (alias_w) SA_STAMP(i, 3);
       // ---- B: edge softmax over the CSR pattern -> alpha entries ----
       // the alpha region doubled as the output staging tile of the previous sample: once the TMA store has read it,
       // zero it again and rewrite the pattern's entries
@@ -490,6 +497,12 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
       }
       mbar_arrive(alpha_ready);
       SA_STAMP(i, 2);
+      // ---- C' (separate accumulators): NodeEdge accumulators of sample i+2 -> fp16 panels while agg[i] runs; conv[i+1]
+      //         must have read the panels of sample i+1 ----
+      if (!alias_w) {
+        if (i + 2 < n_it) { tc::mbar_wait(conv_done, (i + 1) & 1); drain_ne(i + 2); }
+        SA_STAMP(i, 3);
+      }
       // ---- D: aggregation accumulators -> 1/den, bias, act -> fp16 -> HBM ----
       tc::mbar_wait(agg_done, i & 1);
       tc::tc_fence_after();

@@ -114,6 +114,8 @@ struct gnnuds_handle {
   int annz[2] = {0, 0};
   std::vector<uint8_t*> d_cv_img[2];    // GAT conv weight images with the score columns (NW = E + 16 rows per panel)
   std::vector<uint32_t> cv_img_bytes[2];
+  // use_adj (GAT): per-entry controlled-link index / static keep flags of the node filter, the chunk's settings
+  int* d_adj_act = nullptr; unsigned char* d_adj_keep = nullptr; bool use_adj = false; const float* cur_a = nullptr;
   int sp_agg = 1;                       // GNNUDS_SP_AGG: 0 = sp_conv_kernel (SIMT gather) instead of sp_agg_kernel
   float *d_val = nullptr, *d_eval = nullptr;
   int nnz = 0, ennz = 0, n_adj = 0;
@@ -466,18 +468,21 @@ int launch_nodeedge(gnnuds_handle* h, const float* matT, int ldm, int TI, const 
 
 template <typename T = float>
 int launch_agg(gnnuds_handle* h, const void* hin, void* out, const int* rp, const int* ci, const float* val,
-               const LayerW& w, long long S, int R, int act) {
+               const LayerW& w, long long S, int R, int act, bool dyn = false) {
   const auto& c = h->c;
   const int E = c.embed;
   const bool gat = c.conv == GNNUDS_CONV_GAT;
   const float* bias = W(h, w.t[gat ? 3 : 1]);
   const size_t smem = ((size_t)R * E + 2 * (size_t)R) * sizeof(float);
   if (smem <= 200 * 1024) {
-    AggP p{hin, out, rp, ci, val, gat ? W(h, w.t[1]) : nullptr, gat ? W(h, w.t[2]) : nullptr, bias, S, R, E, act, gat ? 1 : 0};
+    AggP p{hin, out, rp, ci, val, gat ? W(h, w.t[1]) : nullptr, gat ? W(h, w.t[2]) : nullptr, bias, S, R, E, act, gat ? 1 : 0,
+           nullptr, nullptr, nullptr, 0};
+    if (dyn && h->use_adj && h->cur_a) { p.act_entry = h->d_adj_act; p.keep = h->d_adj_keep; p.a_dyn = h->cur_a; p.n_act = c.n_act; }
     CU(cudaFuncSetAttribute(agg_small_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     agg_small_kernel<T><<<grid_for(h, S, 1, 16), 256, smem, h->stream>>>(p);
     ++h->launches;
   } else {
+    if (dyn && h->use_adj) return fail(h, GNNUDS_E_INVALID, "use_adj: graph of %d rows does not fit the per-sample aggregation kernel", R);
     if (gat) {
       row_scores_kernel<T><<<grid_for(h, S * R, 8, 16), 256, 0, h->stream>>>(static_cast<const T*>(hin), W(h, w.t[1]), W(h, w.t[2]), h->SS, h->SN, S * R, E);
       ++h->launches;
@@ -590,7 +595,7 @@ int run_spatial(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) {
     float* xo = (l & 1) ? h->XB : h->XA;
     float* eo = (l & 1) ? h->EB : h->EA;
     if ((rc = launch_gemm(h, sx, W(h, w.conv_x.t[0]), nullptr, h->HB, E, E, ACT_LINEAR, Bc, N, T, T, N, 0))) return rc;
-    if ((rc = launch_agg(h, h->HB, xo, h->d_rp, h->d_ci, h->d_val, w.conv_x, S, N, act))) return rc;
+    if ((rc = launch_agg(h, h->HB, xo, h->d_rp, h->d_ci, h->d_val, w.conv_x, S, N, act, blk == 1))) return rc;
     if ((rc = launch_gemm(h, se, W(h, w.conv_e.t[0]), nullptr, h->HB, E, E, ACT_LINEAR, Bc, M, T, T, M, 0))) return rc;
     if ((rc = launch_agg(h, h->HB, eo, h->d_erp, h->d_eci, h->d_eval, w.conv_e, S, M, act))) return rc;
     st.x = {{xo, E, E, 0, N, 0}};
@@ -1405,15 +1410,21 @@ int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) 
     float* xo = (l & 1) ? h->XB : h->XA;
     float* eo = (l & 1) ? h->EB : h->EA;
     // fused NodeEdge + conv + aggregation per stream side; layer-by-layer kernels when it does not apply
-    rc = launch_sp_agg(h, st.x, h->XE, 0, li, w.conv_x, xo, S, N, M, act);
-    if (rc < 0) rc = launch_sp_conv(h, st.x, h->XE, 0, li, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, M, act);
+    const bool dyn_x = blk == 1 && h->use_adj;   // per-sample attention mask: layer-by-layer kernels on the node side
+    rc = dyn_x ? -1 : launch_sp_agg(h, st.x, h->XE, 0, li, w.conv_x, xo, S, N, M, act);
+    if (rc < 0 && !dyn_x) rc = launch_sp_conv(h, st.x, h->XE, 0, li, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, M, act);
     if (rc > 0) return rc;
     if (rc < 0) {
       if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, h->XE, h->NX, S, M, N, E2))) return rc;
       std::vector<SegH> sx = st.x; sx.push_back({h->NX, E2, E2, 0, N, 0});
-      rc = launch_conv_agg(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, act);
-      if (rc > 0) return rc;
-      if (rc < 0 && (rc = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return rc;
+      if (dyn_x) {
+        if ((rc = launch_tc_gemm(h, sx, w.conv_x.t[0], nullptr, h->HB, E, E, ACT_LINEAR, Bc, N, T, T, N, 0))) return rc;
+        if ((rc = launch_agg<bf16>(h, h->HB, xo, h->d_rp, h->d_ci, h->d_val, w.conv_x, S, N, act, true))) return rc;
+      } else {
+        rc = launch_conv_agg(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, act);
+        if (rc > 0) return rc;
+        if (rc < 0 && (rc = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return rc;
+      }
     }
     rc = launch_sp_agg(h, st.e, h->EX, 1, li, w.conv_e, eo, S, M, N, act);
     if (rc < 0) rc = launch_sp_conv(h, st.e, h->EX, 1, li, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, S, M, N, act);
@@ -1542,11 +1553,11 @@ int run_spatial_joint(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int 
     if (TC) {
       if ((rc = launch_tc_gemm(h, st.x, w.joint.t[0], nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, N, T, T, R, 0))) return rc;
       if ((rc = launch_tc_gemm(h, st.e, w.joint.t[0], nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, M, T, T, R, N))) return rc;
-      if ((rc = launch_agg<bf16>(h, h->HBJ, jo, h->d_rp, h->d_ci, h->d_val, w.joint, S, R, act))) return rc;
+      if ((rc = launch_agg<bf16>(h, h->HBJ, jo, h->d_rp, h->d_ci, h->d_val, w.joint, S, R, act, blk == 1))) return rc;
     } else {
       if ((rc = launch_gemm(h, st.x, W(h, w.joint.t[0]), nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, N, T, T, R, 0))) return rc;
       if ((rc = launch_gemm(h, st.e, W(h, w.joint.t[0]), nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, M, T, T, R, N))) return rc;
-      if ((rc = launch_agg<float>(h, h->HBJ, jo, h->d_rp, h->d_ci, h->d_val, w.joint, S, R, act))) return rc;
+      if ((rc = launch_agg<float>(h, h->HBJ, jo, h->d_rp, h->d_ci, h->d_val, w.joint, S, R, act, blk == 1))) return rc;
     }
     st.x = {{jo, E, E, 0, R, 0}};
     st.e = {{jo, E, E, 0, R, N}};
@@ -1558,6 +1569,7 @@ int run_spatial_joint(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int 
 
 int forward_any(gnnuds_handle* h, const float* x, const float* b, const float* a, const float* ex, long long Bc, float* y,
                 float* ey, bool normalised_io) {
+  h->cur_a = a;                 // use_adj: the settings of this chunk drive the block-2 attention mask
   if (h->nn()) return forward_chunk_nn(h, x, b, a, ex, Bc, y, ey, normalised_io);
   return h->tc() ? forward_chunk_tc(h, x, b, a, ex, Bc, y, ey, normalised_io) : forward_chunk(h, x, b, a, ex, Bc, y, ey, normalised_io);
 }
@@ -1920,7 +1932,7 @@ int gnnuds_destroy(gnnuds_handle* h) {
   void* ptrs[] = {h->d_blob, h->d_rp, h->d_ci, h->d_erp, h->d_eci, h->d_val, h->d_eval, h->d_edges, h->d_act_of_edge,
                   h->d_act_out, h->d_act_in, h->d_inc_ptr, h->d_inc_edge, h->d_inc_sign, h->d_hmin, h->d_hmax,
                   h->d_outfall, h->d_ehmax, h->d_nx, h->d_nb, h->d_ny, h->d_ne, h->d_ws, h->ro_x, h->ro_ex, h->ro_b, h->ro_a, h->d_wimg,
-                  h->d_bins[0], h->d_bins[1], h->d_prp[0], h->d_prp[1], h->d_pci[0], h->d_pci[1], h->d_pval[0], h->d_pval[1], h->d_arp[0], h->d_arp[1], h->d_acj[0], h->d_acj[1], h->d_aval[0], h->d_aval[1], h->d_pump, h->d_offset, h->d_pump_in, h->d_pump_out, h->d_area, h->d_edge_from, h->d_ps};
+                  h->d_bins[0], h->d_bins[1], h->d_prp[0], h->d_prp[1], h->d_pci[0], h->d_pci[1], h->d_pval[0], h->d_pval[1], h->d_adj_act, h->d_adj_keep, h->d_arp[0], h->d_arp[1], h->d_acj[0], h->d_acj[1], h->d_aval[0], h->d_aval[1], h->d_pump, h->d_offset, h->d_pump_in, h->d_pump_out, h->d_area, h->d_edge_from, h->d_ps};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_ne_img[s]) if (p) cudaFree(p);
@@ -2250,6 +2262,24 @@ int gnnuds_set_post_proc_variant(gnnuds_handle* h, int32_t variant) {
   if (!h) return GNNUDS_E_INVALID;
   if (variant != 0 && variant != 1) return fail(h, GNNUDS_E_INVALID, "post-processing variant %d unknown (0 numpy, 1 tf)", variant);
   h->pp_variant = variant;
+  return 0;
+}
+
+int gnnuds_set_adj_action(gnnuds_handle* h, const int32_t* act_entry, const uint8_t* base_keep) {
+  if (!h || !act_entry || !base_keep) return GNNUDS_E_INVALID;
+  const auto& c = h->c;
+  if (!h->has_graph) return fail(h, GNNUDS_E_STATE, "set_adj_action: set the graph first");
+  if (!c.act) return fail(h, GNNUDS_E_INVALID, "use_adj needs an act model (emulator.py:178)");
+  if (c.conv != GNNUDS_CONV_GAT)
+    return fail(h, GNNUDS_E_INVALID, "use_adj is supported for GAT only: with GCN the reference hands a 4-D adjacency to spektral's "
+                                     "gcn_filter, which raises (np.diag_indices_from needs equal dimensions)");
+  CU(cudaSetDevice(c.device));
+  int rc;
+  std::vector<int> ae(act_entry, act_entry + h->nnz);
+  for (int v : ae) if (v < 0 || v > c.n_act) return fail(h, GNNUDS_E_INVALID, "set_adj_action: controlled-link index %d out of range", v);
+  if ((rc = upload(h, &h->d_adj_act, ae.data(), ae.size()))) return rc;
+  if ((rc = upload(h, &h->d_adj_keep, base_keep, (size_t)h->nnz))) return rc;
+  h->use_adj = true;
   return 0;
 }
 

@@ -603,7 +603,17 @@ struct AggP {
   const float* a_self; const float* a_neigh;                  // (E) GAT only
   const float* bias;     // (E)
   long long S; int R, E, act, gat;
+  // use_adj (emulator.py:268-271, 343-362), GAT: per-sample attention mask.  Entry q of the pattern belongs to controlled
+  // link act_entry[q]-1 (0 = none): it is kept iff trunc(setting) != 0 (`adj.astype(int)` of the adjacency with the
+  // setting written into it); other entries are kept iff trunc(adjacency value) != 0 (keep[q]); the diagonal always.
+  const int* act_entry; const unsigned char* keep; const float* a_dyn; int n_act;   // a_dyn (S, n_act) or null
 };
+
+__device__ __forceinline__ bool agg_kept(const AggP& p, long long s, int q, int i, int j) {
+  if (!p.a_dyn || i == j) return true;
+  const int k = p.act_entry[q];
+  return k ? truncf(p.a_dyn[s * p.n_act + k - 1]) != 0.f : p.keep[q] != 0;
+}
 
 template <typename T>
 __global__ void __launch_bounds__(256) agg_small_kernel(AggP p) {
@@ -641,9 +651,10 @@ __global__ void __launch_bounds__(256) agg_small_kernel(AggP p) {
       if (p.gat) {
         const float si = ss[i];
         for (int q = beg + lane; q < end; q += 32) {
-          float sc = si + sn[p.col_idx[q]];
+          const int cj = p.col_idx[q];
+          float sc = si + sn[cj];
           sc = sc > 0.f ? sc : 0.2f * sc;
-          mx = fmaxf(mx, sc);
+          if (agg_kept(p, s, q, i, cj)) mx = fmaxf(mx, sc);
         }
         mx = warp_max(mx);
       }
@@ -659,7 +670,7 @@ __global__ void __launch_bounds__(256) agg_small_kernel(AggP p) {
             if (p.gat) {
               float sc = ss[i] + sn[cj];
               sc = sc > 0.f ? sc : 0.2f * sc;
-              wj = expf(sc - mx);
+              wj = agg_kept(p, s, q, i, cj) ? expf(sc - mx) : 0.f;
             } else {
               wj = p.val[q];
             }

@@ -98,8 +98,9 @@ class Emulator:
         if self.act:
             self.act_edges = np.asarray(args.act_edges)
             self.use_adj = bool(g("use_adj", False))
-            if self.use_adj:
-                raise NotImplementedError("use_adj (dynamic adjacency, emulator.py:343-362) is not on the CUDA path")
+            if self.use_adj and "GCN" in str(conv):
+                raise NotImplementedError("use_adj with GCN: the reference hands the (B,T,N,N) adjacency of get_adj_action to "
+                                          "spektral's gcn_filter, which raises for 4-D input (emulator.py:357-358)")
         self.area = np.asarray(g("area", np.zeros(self.n_node)), dtype=np.float64)
         self.pump_in = np.asarray(g("pump_in", np.zeros(self.n_node)), dtype=np.float64)
         self.pump_out = np.asarray(g("pump_out", np.zeros(self.n_node)), dtype=np.float64)
@@ -174,6 +175,8 @@ class Emulator:
         if rc != 0:
             raise _lib.GnnUdsError("gnnuds_create failed (%d): %s" % (rc, self._lib.gnnuds_last_error(None).decode()))
         self._set_graph()
+        if self.act and getattr(self, "use_adj", False) and self.conv_kind == "gat":
+            self._set_adj_action()
         self.specs = _weights.layer_specs(self)
         nt = C.c_int32()
         _lib.check(self._h, self._lib.gnnuds_weight_layout(self._h, C.byref(nt), None))
@@ -196,6 +199,30 @@ class Emulator:
             except Exception:
                 pass
             self._h = None
+
+    def _set_adj_action(self):
+        """use_adj (emulator.py:268-271, 343-362): tell the library which entries of the node filter belong to controlled
+        links and which of the others survive `adj.astype(int)` (get_adj_action casts the WEIGHTED adjacency)."""
+        f, adj = self.filter_csr, self.adj_csr
+        raw = {}
+        for i in range(adj.n):
+            for q in range(adj.row_ptr[i], adj.row_ptr[i + 1]):
+                raw[(i, int(adj.col_idx[q]))] = float(adj.val[q])
+        act_entry = np.zeros(f.nnz, np.int32)
+        keep = np.zeros(f.nnz, np.uint8)
+        pos = {}
+        for i in range(f.n):
+            for q in range(f.row_ptr[i], f.row_ptr[i + 1]):
+                j = int(f.col_idx[q])
+                pos[(i, j)] = q
+                keep[q] = 1 if int(raw.get((i, j), 0.0)) != 0 else 0
+        for k, (u, v) in enumerate(np.asarray(self.act_edges).reshape(-1, 2)):
+            q = pos.get((int(u), int(v)))
+            if q is None:
+                raise ValueError("use_adj: controlled link (%d,%d) is not an entry of the adjacency pattern" % (u, v))
+            act_entry[q] = k + 1                                   # the last controlled link writing an entry wins, as in get_act
+        self._adj_act_entry, self._adj_keep = act_entry, keep
+        _lib.check(self._h, self._lib.gnnuds_set_adj_action(self._h, _ptr(act_entry), _ptr(keep)))
 
     @staticmethod
     def _csr_from_dense(a):

@@ -103,11 +103,32 @@ class Network:
                 vals = vals[1:]
             if t[0] not in first_pt and len(vals) >= 2:
                 first_pt[t[0]] = _num(vals[1])
-        return cls(nodes, links, edges, lengths,
-                   [1 if k == "OUTFALLS" else 0 for k in kind],
-                   [1 if k == "STORAGE" else 0 for k in kind],
-                   hmax, elev, [geom1.get(l, 0.0) for l in links],
-                   [first_pt.get(c, 0.0) if c else 0.0 for c in curve_of])
+        net = cls(nodes, links, edges, lengths,
+                  [1 if k == "OUTFALLS" else 0 for k in kind],
+                  [1 if k == "STORAGE" else 0 for k in kind],
+                  hmax, elev, [geom1.get(l, 0.0) for l in links],
+                  [first_pt.get(c, 0.0) if c else 0.0 for c in curve_of])
+        # pumped / tidal scenarios (chaohu.py:203-208, hague.py:127-132): rated pump flow = first point of the pump curve
+        # * 60/1000, inlet offset = Orifice/Outlet Offset or Conduit InOffset, FUNCTIONAL storage area = first coefficient
+        pump, offset, kept = [], [], set(links)
+        col = {"CONDUITS": 5, "ORIFICES": 4, "OUTLETS": 3}
+        for sec in LINK_SECTIONS:
+            for t in s.get(sec, ()):
+                if t[0] in kept and t[1] in pos and t[2] in pos:
+                    pump.append(first_pt.get(t[3], 0.0) * 60 / 1000 if sec == "PUMPS" else 0.0)
+                    offset.append(_num(t[col[sec]]) if sec in col and len(t) > col[sec] else 0.0)
+        net.pump, net.offset = np.asarray(pump), np.asarray(offset)
+        net.area_functional = np.asarray([_num(t[5]) if len(t) > 5 and t[4].upper() == "FUNCTIONAL" else 0.0
+                                          for t in s.get("STORAGE", ())])
+        return net
+
+    def area_functional_nodes(self):
+        """hague.py:127: area per node = first coefficient of the FUNCTIONAL storage curve (0 for non-storage nodes)."""
+        out, k = np.zeros(self.n_node), 0
+        for i, st in enumerate(self.is_storage):
+            if st:
+                out[i] = self.area_functional[k]; k += 1
+        return out
 
     def edge_list(self, link_names):
         """base.py:349-365 with ``links=...``: (from,to) rows for the named links."""
@@ -249,8 +270,46 @@ def node_adjacency(net, directed=False, length=0, order=1):
     return CSR(n_node, _traverse(G, n_node, length, order, l_std, symmetric=(not directed) and not length))
 
 
-def edge_adjacency(net, directed=False, length=0, order=1):
-    """base.py:393-429 get_edge_adj (line graph) -> CSR."""
+def _multi_edge_adjacency(net, directed, length, order):
+    """chaohu.py:248-282: get_edge_adj over a MULTIgraph - parallel links between the same two nodes (chaohu's twin pumps)
+    stay distinct line-graph vertices.  Incident edges of a node are enumerated as nx.MultiGraph.edges(n, data=True) does:
+    neighbours in first-insertion order, parallel edges in key order; a self loop once."""
+    l_std = np.std(net.lengths) if length else 0.0
+    adj, pred = {}, {}                     # node -> {nbr: [edge ids]}
+
+    def touch(n):
+        if n not in adj:
+            adj[n] = {}; pred[n] = {}
+    for i, (u, v) in enumerate(net.edges):
+        u, v = int(u), int(v)
+        touch(u); touch(v)
+        adj[u].setdefault(v, []).append(i)
+        if directed:
+            pred[v].setdefault(u, []).append(i)
+        elif u != v:
+            adj[v].setdefault(u, []).append(i)
+    EX = _AdjList(directed)
+
+    def link(a, b):
+        if length:
+            EX.add_edge(a, b, length=(float(net.lengths[a]) + float(net.lengths[b])) / 2)
+        else:
+            EX.add_edge(a, b)
+    for n in list(adj):
+        if directed:
+            for a in [e for es in pred[n].values() for e in es]:
+                for b in [e for es in adj[n].values() for e in es]:
+                    link(a, b)
+        else:
+            for a, b in combinations([e for es in adj[n].values() for e in es], 2):
+                link(a, b)
+    return CSR(net.n_edge, _traverse(EX, net.n_edge, length, order, l_std, symmetric=False))
+
+
+def edge_adjacency(net, directed=False, length=0, order=1, multigraph=False):
+    """base.py:393-429 get_edge_adj (line graph) -> CSR; multigraph=True follows the chaohu override."""
+    if multigraph:
+        return _multi_edge_adjacency(net, directed, length, order)
     X = _AdjList(directed)
     l_std = np.std(net.lengths) if length else 0.0
     for i, (u, v) in enumerate(net.edges):
@@ -365,7 +424,7 @@ def incidence(net):
 
 
 def get_args(inp_path, directed=False, length=0, order=1, graph_base=0,
-             act_links=None, head=False, dense=True, **extra):
+             act_links=None, head=False, dense=True, scenario=None, **extra):
     """Drop-in for ``env.get_args(directed,length,order,graph_base)`` restricted to the
     keys ``Emulator`` reads (emulator.py:49-127).  Returns a namespace; ``adj_csr`` /
     ``edge_adj_csr`` are what this package's Emulator consumes, the dense ``adj`` /
@@ -389,7 +448,19 @@ def get_args(inp_path, directed=False, length=0, order=1, graph_base=0,
         a.adj_csr = edge_based_adjacency(net, directed, length, order)
     else:
         a.adj_csr = node_adjacency(net, directed, length, order)
-    a.edge_adj_csr = edge_adjacency(net, directed, length, order)
+    a.edge_adj_csr = edge_adjacency(net, directed, length, order, multigraph=(scenario == "chaohu"))
+    if scenario in ("chaohu", "hague"):
+        # chaohu.py:199-208 / hague.py:115-132: storage areas, rated pump flows, inlet offsets and the node-side pump tables
+        a.area = net.area_functional_nodes() if scenario == "hague" else net.area
+        a.pump = net.pump
+        if scenario == "hague":
+            a.offset = net.offset
+        a.pump_out = np.zeros(net.n_node); a.pump_in = np.zeros(net.n_node)
+        for m, (u, v) in enumerate(net.edges):
+            if u != v:                       # a self loop cancels in node_edge (+1 - 1)
+                a.pump_out[u] += net.pump[m]; a.pump_in[v] += net.pump[m]
+        if scenario == "hague":
+            a.tide, a.head = True, head
     if dense:
         a.adj = a.adj_csr.to_dense()
         a.edge_adj = a.edge_adj_csr.to_dense()

@@ -115,6 +115,14 @@ int gnnuds_set_norm(gnnuds_handle* h, const float* norm_x, int32_t c_x,
                     const float* norm_y, int32_t c_y,
                     const float* norm_e, int32_t c_e);
 
+/* use_adj (emulator.py:92,178-180,268-271,343-362; act models, GAT): the block-2 node convolution attends over a
+   per-sample adjacency - the static one with the setting of every controlled link written into its (from,to) entry
+   and cast to int (get_adj_action: `adj.astype(int)`), so an entry survives iff trunc(value) != 0.  act_entry (nnz of
+   the node filter set by gnnuds_set_graph): 1 + column of `a` for the entry of a controlled link, 0 otherwise;
+   base_keep (nnz): trunc(adjacency value) != 0 for the other entries.  The diagonal is always kept (spektral
+   add_self_loops).  GCN + use_adj is rejected: the reference's call raises inside spektral (4-D gcn_filter). */
+int gnnuds_set_adj_action(gnnuds_handle* h, const int32_t* act_entry, const uint8_t* base_keep);
+
 /* Which of the reference's two post-processing variants gnnuds_predict / gnnuds_simulate follow:
    0 = post_proc (NumPy, emulator.py:643-678; what Emulator.predict and simulate run),
    1 = post_proc_tf (emulator.py:680-725; what predict_tf runs).  They differ on pumped networks only: the TF

@@ -59,7 +59,11 @@ def gat_conv(x, filt, W, a_self, a_neigh, b, act):
     """spektral GATConv._call_dense, heads=1, concat, add_self_loops=True, no dropout.
     W (C,1,E); a_self/a_neigh (E,1,1); filt (N,N)."""
     a = np.array(filt, dtype=x.dtype, copy=True)
-    a[np.diag_indices_from(a)] = 1
+    if a.ndim == 2:
+        a[np.diag_indices_from(a)] = 1
+    else:                                                      # per-sample adjacency (use_adj): tf.linalg.set_diag on every sample
+        idx = np.arange(a.shape[-1])
+        a[..., idx, idx] = 1
     h = np.matmul(x, W[:, 0, :])                              # (...,N,E)
     s_self = np.matmul(h, a_self[:, 0, :])                    # (...,N,1)
     s_neigh = np.matmul(h, a_neigh[:, 0, :])                  # (...,N,1)
@@ -318,7 +322,19 @@ class OracleEmulator:
                 x = lstm(x, w[0], w[1], w[2])
         return x
 
-    def model(self, X, Bn, E_in, AE=None):
+    def get_adj_action(self, a):                                     # emulator.py:343-362 (numpy branch)
+        """(B,T,n_act) -> (B,T,n,n): the adjacency with every controlled link's setting written into its (from,to) entry,
+        then `adj.astype(int)` for GAT.  (GCN: GCNConv.preprocess on this 4-D array raises inside spektral's gcn_filter -
+        np.diag_indices_from needs equal dimensions - so the reference's GCN + use_adj cannot run; not restated.)"""
+        assert self.kind == "gat", "use_adj is only functional with GAT in the reference"
+        def get_act(s):
+            adj = self.adj.copy()
+            adj[tuple(self.act_edges.T)] = s
+            return adj
+        adj = np.apply_along_axis(get_act, -1, np.asarray(a, dtype=np.float64))
+        return adj.astype(int)
+
+    def model(self, X, Bn, E_in, AE=None, A_dyn=None):
         """The Keras graph of build_network (emulator.py:195-340), normalised inputs."""
         dt = self.dtype
         X, Bn, E_in = [np.asarray(v, dtype=dt) for v in (X, Bn, E_in)]
@@ -341,7 +357,7 @@ class OracleEmulator:
         if self.act:
             w = next(it); ae = dense(np.asarray(AE, dtype=dt), w[0], w[1], self.activation)
 
-        def spatial(x, e):
+        def spatial(x, e, filt=filt):
             for _ in range(self.n_sp_layer):
                 if self.graph_base:
                     z = self._conv(np.concatenate([x, e], axis=-2), filt, next(it))
@@ -373,7 +389,10 @@ class OracleEmulator:
         if self.act:
             e = np.concatenate([e, ae], axis=-1)
         x = x.reshape((-1,) + x.shape[2:]); e = e.reshape((-1,) + e.shape[2:])
-        x, e = spatial(x, e)
+        if A_dyn is not None:                                        # emulator.py:268-269: A = reshape(A_in, (-1, n, n))
+            x, e = spatial(x, e, np.asarray(A_dyn, dtype=dt).reshape((-1,) + A_dyn.shape[-2:]))
+        else:
+            x, e = spatial(x, e)
         x = x.reshape((B, To, N, -1)); e = e.reshape((B, To, M, -1))
         tr["sp2"] = (x.copy(), e.copy())
         x = np.transpose(x, (0, 2, 1, 3)).reshape((B * N, To, -1))
@@ -552,7 +571,8 @@ class OracleEmulator:
         assert b.shape[1] == self.seq_out
         ae = self.get_edge_action(np.asarray(a).astype(dt)) if self.act else None
         nb = self.normalize(b, "b").astype(dt)
-        y, ey = self.model(self.normalize(x, "x"), nb, self.normalize(ex, "e"), ae)
+        adj = self.get_adj_action(np.asarray(a)[:, :self.seq_out]) if self.act and getattr(self, "use_adj", False) else None   # emulator.py:573-574
+        y, ey = self.model(self.normalize(x, "x"), nb, self.normalize(ex, "e"), ae, adj)
         y, ey = self.post_proc(y, ey, None if a is None else np.asarray(a).astype(dt), nb, tf=tf)
         y = self.normalize(y, "y", True)
         ey = self.normalize(ey, "e", True)

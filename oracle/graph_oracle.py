@@ -269,3 +269,74 @@ def get_args(path, directed=False, length=0, order=1, graph_base=0, act_links=No
             frm_to.append(tuple(net["edges"][i]))
         args["act_edges"] = np.array(frm_to)
     return args
+
+
+def get_edge_adj_multigraph(edges, lengths=None, directed=False, length=0, order=1):
+    """envs/scenario/chaohu.py:248-282: the line graph of a MULTIgraph (chaohu has parallel pumps between the same two
+    nodes, which nx.Graph would merge), then the same traversal."""
+    X = nx.MultiDiGraph() if directed else nx.MultiGraph()
+    if length:
+        l_std = np.std(lengths)
+    for i, (u, v) in enumerate(edges):
+        if length:
+            X.add_edge(int(u), int(v), edge=i, length=lengths[i])
+        else:
+            X.add_edge(int(u), int(v), edge=i)
+    EX = nx.DiGraph() if directed else nx.Graph()
+    for n in X.nodes():
+        if directed:
+            for _, _, u in X.in_edges(n, data=True):
+                for _, _, v in X.out_edges(n, data=True):
+                    EX.add_edge(u["edge"], v["edge"])
+                    if length:
+                        EX[u["edge"]][v["edge"]].update(length=(u["length"] + v["length"]) / 2)
+        else:
+            for (_, _, u), (_, _, v) in combinations(X.edges(n, data=True), 2):
+                EX.add_edge(u["edge"], v["edge"])
+                if length:
+                    EX[u["edge"]][v["edge"]].update(length=(u["length"] + v["length"]) / 2)
+    n_edge = edges.shape[0]
+    adj = np.zeros((n_edge, n_edge))
+    for n in range(n_edge):
+        if length:
+            p_l = nx.single_source_dijkstra_path_length(EX, n, weight="length", cutoff=length)
+            for a, l in p_l.items():
+                adj[n, a] = np.exp(-(l / (l_std + 1e-5)) ** 2)
+        else:
+            for a in list(nx.dfs_preorder_nodes(EX, n, order)):
+                adj[n, a] = 1
+    return adj
+
+
+def scenario_tables(path, scenario):
+    """The extra get_args vectors of the pumped / tidal scenarios (restated on the raw .inp sections; swmm-api attribute
+    names in brackets): chaohu.py:203-208 - area = first point of the storage curve [CURVES[node.Curve].points[0][1]],
+    pump = rated flow of the pump curve's first point * 60/1000 [CURVES[link.Curve].points[0][1]], pump_in / pump_out
+    = rows of |clip(node_edge)| * pump; hague.py:127-132 - area = first coefficient of the FUNCTIONAL storage curve
+    [node.Curve[0]], pump as above, offset = Orifice/Outlet.Offset + Conduit.InOffset."""
+    s = read_sections(path)
+    net = parse_network(path)
+    curves = {}
+    for t in s.get("CURVES", []):
+        vals = t[1:]
+        if vals and _f(vals[0], None) is None:
+            vals = vals[1:]
+        curves.setdefault(t[0], []).extend([(_f(vals[i]), _f(vals[i + 1])) for i in range(0, len(vals) - 1, 2)])
+    area, pump, offset = [], [], []
+    for sec in NODE_SECTIONS:
+        for t in s.get(sec, []):
+            if sec != "STORAGE":
+                area.append(0.0)
+            elif scenario == "hague":
+                area.append(_f(t[5]))                                  # FUNCTIONAL A B C: Curve = [A, B, C]
+            else:
+                area.append(curves[t[5]][0][1])                        # TABULAR curve name
+    for sec in LINK_SECTIONS:
+        for t in s.get(sec, []):
+            pump.append(curves[t[3]][0][1] * 60 / 1000 if sec == "PUMPS" else 0.0)
+            offset.append({"CONDUITS": lambda: _f(t[5]) if len(t) > 5 else 0.0, "ORIFICES": lambda: _f(t[4]) if len(t) > 4 else 0.0,
+                           "OUTLETS": lambda: _f(t[3]) if len(t) > 3 else 0.0}.get(sec, lambda: 0.0)())
+    area, pump, offset = np.array(area), np.array(pump), np.array(offset)
+    ne = get_node_edge(len(net["nodes"]), net["edges"])
+    return dict(area=area, pump=pump, offset=offset, pump_in=(-np.clip(ne, -1, 0) * pump).sum(axis=1),
+                pump_out=(np.clip(ne, 0, 1) * pump).sum(axis=1))

@@ -67,6 +67,14 @@ CASES = {
     "ast_head_gcn_gru_nofusion": dict(net="astlingen", conv="GCN", recurrent="GRU", resnet=False, seq_in=5, seq_out=5,
                                       embed_size=128, hidden_dim=64, n_sp_layer=1, n_tp_layer=1, length=0, order=1,
                                       head=True, B=3, seed=57),
+    # use_adj (emulator.py:268-271, 343-362): per-sample attention mask from the settings; unit adjacency (length 0) and
+    # Gaussian-weighted adjacency (length 1.0, where `adj.astype(int)` drops every off-diagonal entry)
+    "ast_gat_use_adj": dict(net="astlingen", conv="GAT", recurrent="Conv1D", resnet=True, seq_in=5, seq_out=5, embed_size=128,
+                            hidden_dim=64, n_sp_layer=2, n_tp_layer=2, length=0, order=1, edge_fusion=True, if_flood=2,
+                            act="conti", use_adj=True, B=5, seed=58),
+    "ast_gat_use_adj_weighted": dict(net="astlingen", conv="GAT", recurrent="GRU", resnet=False, seq_in=4, seq_out=4, embed_size=64,
+                                     hidden_dim=64, n_sp_layer=2, n_tp_layer=1, length=501, order=1, act="conti", use_adj=True,
+                                     B=3, seed=59),
     # graph_base=2: the same joint conv over the link-based graph of base.py:500-532 (asymmetric rows, order 2)
     "ast_edgebased_gcn_lstm_act": dict(net="astlingen", conv="GCN", recurrent="LSTM", resnet=True, seq_in=4, seq_out=4,
                                        embed_size=64, hidden_dim=64, n_sp_layer=2, n_tp_layer=1, length=0, order=2,
@@ -81,7 +89,8 @@ CASES = {
 GOLDEN_CASES = ["c1_ast_gcn_gru", "c2_shq_gat_conv_10", "c3_ast_act_5", "ast_gat_gru_noflood",
                 "ast_gcn_lstm_act_nofusion", "ast_gcn_conv_eps0", "ast_joint_gcn_gru_act", "ast_joint_gat_conv_act",
                 "ast_pump_act_fusion", "ast_pump_act_nofusion", "ast_nn_conv_act_fusion", "shq_nn_gru",
-                "ast_edgebased_gcn_lstm_act", "ast_head_tide_offset", "ast_head_gcn_gru_nofusion"]
+                "ast_edgebased_gcn_lstm_act", "ast_head_tide_offset", "ast_head_gcn_gru_nofusion",
+                "ast_gat_use_adj", "ast_gat_use_adj_weighted"]
 
 
 def load_net(name):
@@ -164,6 +173,18 @@ class SpecShim:
         self.n_act = len(o.act_edges) if o.act else 0
 
 
+def _tweak_inputs(case, inputs):
+    """use_adj cases: half of the settings are exactly 1 (fully open: the link stays in the attention mask), the others
+    stay fractional (trunc -> 0: the link is masked out), so both branches of `adj.astype(int)` are exercised."""
+    if not CASES[case].get("use_adj"):
+        return inputs
+    states, b, a, ex = inputs
+    a = np.array(a, copy=True)
+    idx = np.indices(a.shape).sum(0) % 2 == 0
+    a[idx] = 1.0
+    return states, b, a, ex
+
+
 def make_oracle(case, dtype=np.float64):
     from oracle.emulator_oracle import OracleEmulator
     args, B, seed = build_args(case)
@@ -173,7 +194,7 @@ def make_oracle(case, dtype=np.float64):
     o.set_weights(ws)
     o.set_norm(norms["norm_x"], norms["norm_b"], norms["norm_y"], norms["norm_r"], norms["norm_e"])
     shim.norm_x, shim.norm_b, shim.norm_e = norms["norm_x"], norms["norm_b"], norms["norm_e"]
-    inputs = synthetic.make_inputs(shim, B, rng)
+    inputs = _tweak_inputs(case, synthetic.make_inputs(shim, B, rng))
     return o, inputs
 
 
@@ -197,5 +218,5 @@ def setup_product(case, device=0, precision="fp32", **kw):
     ws, norms, rng, B = model_data(case, em)
     em.set_weights(ws)
     em.set_norm(norms["norm_x"], norms["norm_b"], norms["norm_y"], norms["norm_r"], norms["norm_e"])
-    inputs = synthetic.make_inputs(em, B, rng)
+    inputs = _tweak_inputs(case, synthetic.make_inputs(em, B, rng))
     return em, inputs

@@ -108,3 +108,49 @@ def test_random_tree_is_a_tree():
     assert (net.edges[:, 1] < net.edges[:, 0]).all()
     j = G.joint_adjacency(net)
     assert j.n == 2 * net.n_node - 1 and j.nnz == 6 * net.n_edge + j.n
+
+
+# ---- pumped / tidal scenarios: chaohu (multigraph line graph, pump tables), hague (offsets, functional storage) ----
+def _scenario(name):
+    return np.load(os.path.join(GOLD, "scenario_%s.npz" % name))
+
+
+@pytest.mark.parametrize("key,length,order", [("eadj_l0_o1", 0, 1), ("eadj_l0_o2", 0, 2), ("eadj_l200_o1", 200.0, 1)])
+def test_chaohu_multigraph_edge_adjacency(key, length, order):
+    """chaohu.py:248-282: parallel pumps between the same two nodes stay distinct line-graph vertices (bit-exact CSR
+    against the networkx MultiGraph restatement run on the reference's chaohu.inp)."""
+    z = _scenario("chaohu")
+    M = len(z["links"])
+    net = G.Network([str(s) for s in z["nodes"]], [str(s) for s in z["links"]], z["edges"], z["lengths"], np.zeros(len(z["nodes"])),
+                    np.zeros(len(z["nodes"])), np.zeros(len(z["nodes"])), np.zeros(len(z["nodes"])), np.zeros(M), np.zeros(len(z["nodes"])))
+    pairs = [tuple(e) for e in z["edges"].tolist()]
+    assert len(set(pairs)) < len(pairs), "chaohu has parallel links"
+    csr = G.edge_adjacency(net, False, length, order, multigraph=True)
+    assert np.array_equal(csr.row_ptr, z[key + "_rp"]) and np.array_equal(csr.col_idx, z[key + "_ci"])
+    assert np.array_equal(csr.val, z[key + "_val"])
+    try:                                                                  # the base-class version merges the twins: the merged
+        simple = G.edge_adjacency(net, False, length, order)              # link is no line-graph vertex (networkx raises too)
+        assert simple.nnz != csr.nnz
+    except KeyError:
+        pass
+
+
+@pytest.mark.parametrize("name", ["chaohu", "hague"])
+def test_scenario_tables_from_inp(name):
+    """get_args(scenario=...) derives area / pump / pump_in / pump_out / offset from the .inp as chaohu.py:203-208 and
+    hague.py:127-132 do (goldens made by tools/make_golden.py --scenarios through the oracle's restatement)."""
+    path = os.path.join("/root/reference/surrogate/envs/network", name, name + ".inp")
+    if not os.path.exists(path):
+        pytest.skip("reference networks not present on this machine")
+    z = _scenario(name)
+    a = G.get_args(path, False, 0, 1, 0, scenario=name)
+    assert [str(s) for s in z["nodes"]] == a.nodes and [str(s) for s in z["links"]] == a.links
+    for k in ("area", "pump", "pump_in", "pump_out"):
+        assert np.array_equal(np.asarray(getattr(a, k), np.float64), z["tab_" + k]), k
+    if name == "hague":
+        assert np.array_equal(np.asarray(a.offset, np.float64), z["tab_offset"]) and a.offset.max() > 0
+        assert a.tide is True
+    else:
+        assert (a.pump > 0).sum() == 7 and a.area.max() > 0                # chaohu: 7 pumps, two storage tanks
+    key = "eadj_l0_o1"
+    assert np.array_equal(a.edge_adj_csr.row_ptr, z[key + "_rp"]) and np.array_equal(a.edge_adj_csr.col_idx, z[key + "_ci"])

@@ -270,3 +270,37 @@ def test_large_batch_properties():
     assert (y[..., 0] >= -1e-6).all() and (y[..., 0] <= em.hmax + 1e-5).all() and (y[..., -1] >= 0).all()
     assert (y[..., em.is_outfall.astype(bool), -1] == 0).all()
     assert (ey[..., 0] >= 0).all() and (ey[..., 0] <= em.ehmax + 1e-6).all()
+
+
+@pytest.mark.parametrize("case", ["ast_gat_use_adj", "ast_gat_use_adj_weighted"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_use_adj_dynamic_mask(case, precision):
+    """use_adj (emulator.py:268-271, 343-362): the block-2 node attention runs over the per-sample `adj.astype(int)` mask.
+    Besides the oracle comparison, switching the dynamic mask off must change the result by what it changes in the
+    oracle (the settings of this case alternate between 1.0 = link kept and fractions = link masked)."""
+    em, inp = cases.setup_product(case, precision=precision)
+    y, ey = em.predict(*inp)
+    o, inp_o = cases.make_oracle(case, np.float64)
+    y64, ey64 = o.predict(*inp_o)
+    o.use_adj = False
+    y64s, _ = o.predict(*inp_o)
+    sc = lambda t: np.maximum(np.abs(t).reshape(-1, t.shape[-1]).max(0), 1.0)
+    tol = 1e-5 if precision == "fp32" else 5e-3
+    d = np.abs(y - y64) / sc(y64)
+    if em.if_flood:
+        d[np.abs(y64[..., 3] - 0.5) < (1e-4 if precision == "fp32" else 5e-3)] = 0
+    assert d.max() < tol and (np.abs(ey - ey64) / sc(ey64)).max() < tol
+    if precision == "fp32":
+        effect = np.abs(y64 - y64s).max()
+        assert effect > 20 * np.abs(y - y64).max(), "the dynamic mask must matter more than the fp32 error (%.3g vs %.3g)" % (effect, np.abs(y - y64).max())
+        assert np.abs((y - y64s)).max() > 0.5 * effect
+
+
+def test_use_adj_gcn_rejected():
+    import copy
+    args, B, seed = cases.build_args("ast_gcn_lstm_act_nofusion")
+    args = copy.copy(args)
+    args.use_adj = True
+    from gnn_uds_b200.emulator import Emulator
+    with pytest.raises(NotImplementedError):
+        Emulator(args.conv, args.resnet, args.recurrent, args)

@@ -36,6 +36,24 @@ def events_table():
     print("wrote", out, len(rows), "events")
 
 
+def scenario_goldens():
+    """chaohu (multigraph line graph + pump tables) and hague (offsets, functional storage areas) from the reference .inp
+    files through the networkx restatements of oracle/graph_oracle.py."""
+    for name, variants in (("chaohu", [(0, 1), (0, 2), (200.0, 1)]), ("hague", [(0, 1)])):
+        path = os.path.join(REF, name, name + ".inp")
+        net = go.parse_network(path)
+        d = dict(nodes=np.array(net["nodes"]), links=np.array(net["links"]), edges=net["edges"], lengths=net["lengths"])
+        d.update({"tab_" + k: v for k, v in go.scenario_tables(path, name).items()})
+        for length, order in variants:
+            L = net["lengths"] if length else None
+            m = go.get_edge_adj_multigraph(net["edges"], L, False, length, order) if name == "chaohu" else go.get_edge_adj(net["edges"], L, False, length, order)
+            rp, ci, vv = dense_to_csr(m)
+            key = "eadj_l%g_o%d" % (length, order)
+            d[key + "_rp"], d[key + "_ci"], d[key + "_val"] = rp, ci, vv
+        np.savez_compressed(os.path.join(OUT, "scenario_%s.npz" % name), **d)
+        print("wrote scenario_%s.npz" % name, len(net["nodes"]), "nodes", len(net["links"]), "links")
+
+
 def dense_to_csr(a):
     rp, ci, vv = [0], [], []
     for i in range(a.shape[0]):
@@ -85,6 +103,10 @@ def forward_vectors():
         np.savez_compressed(os.path.join(OUT, "fwd_%s.npz" % case), **d)
         print(case, {k: v.shape for k, v in d.items()})
 
+
+if __name__ == "__main__" and "--scenarios" in sys.argv:
+    scenario_goldens()
+    sys.exit(0)
 
 if __name__ == "__main__" and "--events" in sys.argv:
     events_table()
