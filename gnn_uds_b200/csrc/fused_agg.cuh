@@ -38,7 +38,7 @@
 namespace gu {
 
 constexpr int SA_WORKERS = 16;
-constexpr int SA_THREADS = (SA_WORKERS + 2) * 32;   // 576
+constexpr int SA_THREADS = (SA_WORKERS + 3) * 32;   // 608: workers, MMA issuer, TMA producer, store warp
 
 struct SpAggP {
   CUtensorMap tm_self[2];     // {w, S*R rows}, box {64, Rbox}, SWIZZLE_128B (K-major tiles of 64 columns)
@@ -51,6 +51,7 @@ struct SpAggP {
   const int* rp;              // CSR row pointers (R+1), block-diagonal replica for sample groups
   const uint32_t* cj;         // per CSR entry: (byte offset of alpha[i][j] in the alpha operand) << 8 | j
   const float* val;           // GCN filter values per CSR entry (null for GAT)
+  const uint8_t* zeros;       // >= al_zero zero bytes in global memory: the alpha region is re-zeroed by a bulk copy
   int nnz;
   bf16* out; long long rows_total;
   int S, R, Ro, Rbox, Kp, KpJ, MT, Kself, F, Nout, NW, act, gat, nb_self, alias_acc, max_len;
@@ -170,7 +171,9 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
   uint64_t* agg_done = bars + 11;    // aggregation MMAs committed
   uint64_t* out_done = bars + 12;    // aggregation accumulators drained (workers)
   uint64_t* wbar = bars + 13;        // resident weights landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+  uint64_t* zbar = bars + 14;        // alpha region zeroed again (bulk copy complete_tx) after it served as the output staging tile
+  uint64_t* staged = bars + 15;      // output tile staged in shared memory (workers)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
   // scratch: bias[Nout] | ss[RP] sn[RP] inv[RP] | rp[R+1] | cj[nnz] | val[nnz] (GCN)
   const int RP = 128 * p.MT;
   float* bias_s = reinterpret_cast<float*>(smem + p.off_sc);
@@ -194,6 +197,8 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
     tc::mbar_init(agg_done, 1);
     tc::mbar_init(out_done, SA_WORKERS * 32);
     tc::mbar_init(wbar, 1);
+    tc::mbar_init(zbar, 1);
+    tc::mbar_init(staged, SA_WORKERS * 32);
     tc::mbar_fence_init();
   }
   for (int i = tid; i < p.Nout; i += SA_THREADS) bias_s[i] = p.bias ? p.bias[i] : 0.f;
@@ -244,6 +249,24 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
       issue_self(0);
       if (n_it > 1) issue_xe(1);
       for (int k = 0; k + 1 < n_it; ++k) { if (k + 2 < n_it) issue_xe(k + 2); issue_self(k + 1); }
+    }
+  } else if (warp == SA_WORKERS + 2) {
+    // ================================ store warp ================================
+    // The staged output tile of sample i leaves through two TMA stores; once they have read shared memory, the alpha
+    // region the tile occupied is zeroed again by a bulk copy from a zero buffer - all asynchronous to the workers, who
+    // only wait for `zbar` before the next softmax writes the pattern's entries.
+    if (lane == 0) {
+      for (int i = 0; i < n_it; ++i) {
+        const int smp = (int)blockIdx.x + i * (int)gridDim.x;
+        tc::mbar_wait(staged, i & 1);
+        tma_store_2d(&p.tm_out, 0, smp * p.R, smem + p.off_al);
+        tma_store_2d(&p.tm_out, 64, smp * p.R, smem + p.off_al + p.stage_half);
+        bulk_commit();
+        bulk_wait_read();
+        tc::mbar_expect_tx(zbar, p.al_zero);
+        for (uint32_t o = 0; o < p.al_zero; o += 16384) tc::bulk_g2s(smem + p.off_al + o, p.zeros + o, min(p.al_zero - o, 16384u), zbar);
+      }
+      bulk_wait_all();
     }
   } else if (warp == SA_WORKERS) {
     // ================================ MMA issuer ================================
@@ -382,6 +405,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
         // aggregation drain is waiting for agg[i]); its result is not needed before the conv drain of sample i+1 is over
         if (alias) { if (i + 1 < n_it) issue_conv(i + 1); if (i + 2 < n_it) issue_ne(i + 2); }
       }
+
     }
   } else {
     // ================================ workers ================================
@@ -463,16 +487,11 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
       if (alias_w && i + 1 < n_it) drain_ne(i + 1);
       if (alias_w) SA_STAMP(i, 3);
       // ---- B: edge softmax over the CSR pattern -> alpha entries ----
-      // the alpha region doubled as the output staging tile of the previous sample: once the TMA store has read it,
-      // zero it again and rewrite the pattern's entries
-      if (tid == 0) bulk_wait_read();
-      workers_bar_sync();                              // staging consumed; scores of every row visible
+      // the alpha region doubled as the output staging tile of the previous sample; the MMA warp stored it and had it
+      // zeroed again (handle_store): rewrite the pattern's entries
+      if (i >= 1) tc::mbar_wait(zbar, (i - 1) & 1);    // the bulk copy that zeroed the region after sample i-1's store
       SA_STAMP(i, 8);
-      {
-        uint4* z = reinterpret_cast<uint4*>(al);
-        for (int k = tid; k < (int)(p.al_zero >> 4); k += SA_WORKERS * 32) z[k] = make_uint4(0u, 0u, 0u, 0u);
-      }
-      workers_bar_sync();
+      workers_bar_sync();                              // scores of every row visible
       SA_STAMP(i, 9);
       if (!gat) {
         for (int k = tid; k < p.nnz; k += SA_WORKERS * 32) *reinterpret_cast<__half*>(al + (cj_s[k] >> 8)) = __float2half_rn(val_s[k]);
@@ -537,17 +556,11 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
       tc::tc_fence_before();
       mbar_arrive(out_done);
       tc::fence_async_smem();                          // staged tile -> TMA store reads
-      workers_bar_sync();
+      mbar_arrive(staged);
       SA_STAMP(i, 12);
-      if (tid == 0) {
-        tma_store_2d(&p.tm_out, 0, smp * R, al);
-        tma_store_2d(&p.tm_out, 64, smp * R, al + p.stage_half);
-        bulk_commit();
-      }
       SA_STAMP(i, 5);
     }
   }
-  if (tid == 0) bulk_wait_all();
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 0) tc::tmem_free(tmem, 512);

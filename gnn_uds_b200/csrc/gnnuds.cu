@@ -10,6 +10,7 @@
 #include "fused_sp.cuh"
 #include "fused_conv.cuh"
 #include "fused_agg.cuh"
+#include "fused_tp.cuh"
 #include "gru_tc.cuh"
 #include "nn_cat.cuh"
 
@@ -115,7 +116,9 @@ struct gnnuds_handle {
   std::vector<uint8_t*> d_cv_img[2];    // GAT conv weight images with the score columns (NW = E + 16 rows per panel)
   std::vector<uint32_t> cv_img_bytes[2];
   // use_adj (GAT): per-entry controlled-link index / static keep flags of the node filter, the chunk's settings
+  uint8_t* d_zeros = nullptr;           // 64 KB of zeros: source of sp_agg_kernel's bulk re-zeroing of its alpha region
   int* d_adj_act = nullptr; unsigned char* d_adj_keep = nullptr; bool use_adj = false; const float* cur_a = nullptr;
+  int tp_fused = 1;                     // GNNUDS_TP_FUSED: 0 = one tc_rows_kernel launch per Conv1D layer instead of tp_conv_kernel
   int sp_agg = 1;                       // GNNUDS_SP_AGG: 0 = sp_conv_kernel (SIMT gather) instead of sp_agg_kernel
   float *d_val = nullptr, *d_eval = nullptr;
   int nnz = 0, ennz = 0, n_adj = 0;
@@ -1025,10 +1028,90 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
   return 0;
 }
 
+// {C, Nn, Ts, Bc} view of a (Bc, Ts, Nn, C) activation buffer, box {64 columns, G nodes, Ts steps, 1}: the rows of G whole
+// sequences arrive interleaved (row = t*G + g) as one SWIZZLE_128B K-major stage (csrc/fused_tp.cuh)
+bool make_seq_tmap(CUtensorMap* m, const void* base, long long Bc, int Ts, int Nn, int ld, int width, int G) {
+  tmap_encode_fn enc = tmap_encoder();
+  if (!enc) return false;
+  cuuint64_t dims[4] = {(cuuint64_t)width, (cuuint64_t)Nn, (cuuint64_t)Ts, (cuuint64_t)Bc};
+  cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)Nn * ld * 2, (cuuint64_t)Ts * Nn * ld * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)G, (cuuint32_t)Ts, 1};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  return enc(m, GU_TMAP_16, 4, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// ---- fused Conv1D stack (csrc/fused_tp.cuh).  Returns 0 launched, -1 not applicable, > 0 error. ----
+int launch_tp_conv(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src, int cin, long long Bc, int Nn, int Ts,
+                   int Td, float* out, const LayerW* tail = nullptr, int tail_n = 0, int tail_act = 0) {
+  const auto& c = h->c;
+  const int H = c.hidden, Pc = c.n_tp_layer, k = c.kernel_size, P = Pc + (tail ? 1 : 0);
+  if (!h->tp_fused || !h->tma_on || !h->sw128 || c.recurrent != GNNUDS_REC_CONV1D || H != 64 || cin % 64 || cin > 256 || k < 1 || k > 4 ||
+      Pc < 2 || P > TP_MAXP || (tail && tail_n != 128) || Ts > 128 || Ts < 1 || Td > Ts || src.shift || src.pitch != Nn || src.off || src.ld % 8 || src.width != cin ||
+      (reinterpret_cast<uintptr_t>(src.p) & 15) || Bc <= 0 || Bc * (long long)Nn >= (1ll << 31))
+    return -1;
+  TpConvP p{};
+  p.P = P; p.Pc = Pc; p.k = k; p.cin = cin; p.H = H; p.Ts = Ts; p.Td = Td; p.Nn = Nn; p.act = act_code(c);
+  p.Nlast = tail ? tail_n : H; p.act_last = tail ? tail_act : act_code(c);
+  p.G = std::max(1, std::min(std::min(128 / Ts, Nn), 256));
+  p.tpb = (Nn + p.G - 1) / p.G;
+  p.n_tiles = (unsigned)(Bc * p.tpb);
+  p.interleave = P <= 4 ? 1 : 0;        // every layer's output in its own panel buffer: layer 1 of tile i+1 runs ahead
+  // zero rows in front of the panels: the largest shift a later layer really uses (shifts >= Ts are skipped)
+  int maxshift = 0;
+  for (int l = 1; l < Pc; ++l) for (int j = 0; j < k; ++j) { const int sft = (k - 1 - j) << l; if (sft < Ts) maxshift = std::max(maxshift, sft); }
+  p.pad_rows = (uint32_t)(maxshift * p.G);
+  p.pstrideP = (p.pad_rows + 128u) * 16u;
+  auto al = [](uint32_t v, uint32_t a) { return (v + a - 1) / a * a; };
+  uint32_t off = 0;
+  for (int l = 0; l < P; ++l) {
+    const LayerW& lw = l < Pc ? L[l] : *tail;
+    const int t = lw.t[0];
+    const int K = l < Pc ? (l == 0 ? cin : H) * k : H, Nl = l < Pc ? H : tail_n;
+    if (t < 0 || t >= (int)h->img_off.size() || h->img_off[t] < 0 || h->tens[t].numel != (int64_t)K * Nl) return -1;
+    p.Wimg[l] = h->d_wimg + h->img_off[t]; p.w_bytes[l] = (uint32_t)K * Nl * 2u; p.w_off[l] = off;
+    p.bias[l] = W(h, lw.t[1]);
+    off = al(off + p.w_bytes[l], 128);
+  }
+  const uint32_t pan_bytes = (uint32_t)(H / 8) * p.pstrideP;
+  const int npan = p.interleave ? P - 1 : std::min(P - 1, 2);
+  off = al(off, 128);
+  for (int b = 0; b < TP_MAXP; ++b) p.off_pan[b] = off;
+  for (int b = 0; b < npan; ++b) { p.off_pan[b] = off; off = al(off + pan_bytes, 128); }
+  p.off_bias = off;
+  p.off_bar = al(p.off_bias + (uint32_t)P * 128u * 4u, 16);
+  const uint32_t bar_bytes = (uint32_t)(2 * 8 + 2 * TP_MAXP + 2) * 8u + 16u;
+  p.off_stage = al(p.off_bar + bar_bytes, 1024);
+  const uint32_t cap = 227u * 1024u;
+  if (p.off_stage + 2u * 16384u > cap) return -1;
+  p.NS = (int)std::min<uint32_t>(8u, (cap - p.off_stage) / 16384u);
+  // barrier block was sized for 8 stages; the barrier pointers are laid out from NS
+  const size_t smem = p.off_stage + (size_t)p.NS * 16384u;
+  if ((P - 1) * H + p.Nlast > 512) return -1;
+  if (!make_seq_tmap(&p.tm_in, src.p, Bc, Ts, Nn, src.ld, cin, p.G)) return -1;
+  p.out = reinterpret_cast<bf16*>(out);
+  if (!h->attr_done[6]) {
+    CU(cudaFuncSetAttribute(tp_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    h->attr_done[6] = true;
+  }
+  cudaEvent_t e1 = nullptr;
+  { int prc = prof_begin(h, GNNUDS_FAM_GEMM, &e1); if (prc) return prc; }
+  tp_conv_kernel<<<std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count), TP_THREADS, smem, h->stream>>>(p);
+  ++h->launches;
+  { int prc = prof_end(h, e1); if (prc) return prc; }
+  CU(cudaGetLastError());
+  return 0;
+}
+
 int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src, int cin, long long Bc, int Nn,
                     int Ts, int Td, float* t0, float* t1, float** dst) {
   const auto& c = h->c;
   const int H = c.hidden, P = c.n_tp_layer;
+  if (c.recurrent == GNNUDS_REC_CONV1D) {      // the whole Conv1D stack in one kernel when it applies
+    const int frc = launch_tp_conv(h, L, src, cin, Bc, Nn, Ts, Td, t0);
+    if (frc > 0) return frc;
+    if (frc == 0) { *dst = t0; return 0; }
+  }
   const float* cur = src.p;
   int cw = cin, cpitch = src.pitch, coff = src.off;
   float* bufs[2] = {t0, t1};
@@ -1257,6 +1340,8 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
   p.bias = W(h, w.t[gat ? 3 : 1]);
   p.rp = h->d_arp[side]; p.cj = h->d_acj[side]; p.val = gat ? nullptr : h->d_aval[side]; p.nnz = h->annz[side];
   p.out = static_cast<bf16*>(out); p.rows_total = rows_total;
+  if (!h->d_zeros) { CU(cudaMalloc(&h->d_zeros, 65536)); CU(cudaMemset(h->d_zeros, 0, 65536)); }
+  p.zeros = h->d_zeros;
   auto al = [](uint32_t v, uint32_t a) { return (v + a - 1) / a * a; };
   const uint32_t RP = 128u * p.MT;
   p.chunk_bytes = (uint32_t)p.Rbox * 128u;
@@ -1280,7 +1365,7 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
   p.off_bar = al(p.off_sc + sc_bytes, 16);
   // operand views of an M tile read 128 rows from the tile's first row of every panel / swizzle chunk: keep those
   // reads inside the allocation
-  uint32_t reach = p.off_bar + 15u * 8u + 16u;
+  uint32_t reach = p.off_bar + 17u * 8u + 16u;
   reach = std::max(reach, p.off_self + (uint32_t)(p.nb_self - 1) * p.self_stride + (uint32_t)(p.Kself / 64 - 1) * p.chunk_bytes + RP * 128u);
   reach = std::max(reach, p.off_nx + (uint32_t)(F / 8 - 1) * p.pstrideP + RP * 16u);
   reach = std::max(reach, p.off_al + (uint32_t)(p.KpJ / 8 - 1) * p.pstrideAl + RP * 16u);
@@ -1482,15 +1567,31 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
   if (rc == 1) return 0;
   if (rc) return rc;
   if (h->debug_stop == 4) return 0;
-  if ((rc = run_temporal_tc(h, h->tpx[1], st.x[0], E, Bc, N, To, To, h->TX0, h->TX1, &xt))) return rc;
-  if ((rc = run_temporal_tc(h, h->tpe[1], st.e[0], E, Bc, M, To, To, h->TE0, h->TE1, &et))) return rc;
-  st.x = {{xt, H, H, 0, N, 0}};
-  st.e = {{et, H, H, 0, M, 0}};
-  set_dbg(h, st, Bc * To * N, Bc * To * M);
-  if (h->debug_stop == 5) return 0;
   const int ract = c.resnet ? ACT_LINEAR : act;
-  if ((rc = launch_tc_gemm(h, st.x, h->resx.t[0], W(h, h->resx.t[1]), h->XA, E, E, ract, Bc, N, To, To, N, 0))) return rc;
-  if ((rc = launch_tc_gemm(h, st.e, h->rese.t[0], W(h, h->rese.t[1]), h->EA, E, E, ract, Bc, M, To, To, M, 0))) return rc;
+  // Conv1D: the block-2 temporal net AND the Dense that follows it (dense_resx, emulator.py:313 / :317) in one kernel per
+  // stream - the (B,To,Nn,H) tensor between them never reaches HBM (not under a debug stop, which wants to see it)
+  bool tail_x = false, tail_e = false;
+  // x_out / e_out (B,To,Nn,E): the buffer of the pair that the block-2 spatial output does NOT occupy
+  float* XO = st.x[0].p == h->XA ? h->XB : h->XA;
+  float* EO = st.e[0].p == h->EA ? h->EB : h->EA;
+  // (measured at C2: 159.4 against 157.1 ms per step without it - the extra weights leave 3 instead of 5 layer-1 stages
+  //  in shared memory - so it is opt-in: GNNUDS_TP_FUSED=2)
+  if (h->tp_fused == 2 && c.recurrent == GNNUDS_REC_CONV1D && !h->debug_stop && E == 128 && !c.graph_base) {
+    int frc = launch_tp_conv(h, h->tpx[1], st.x[0], E, Bc, N, To, To, XO, &h->resx, E, ract);
+    if (frc > 0) return frc;
+    tail_x = frc == 0;
+    frc = launch_tp_conv(h, h->tpe[1], st.e[0], E, Bc, M, To, To, EO, &h->rese, E, ract);
+    if (frc > 0) return frc;
+    tail_e = frc == 0;
+  }
+  if (!tail_x && (rc = run_temporal_tc(h, h->tpx[1], st.x[0], E, Bc, N, To, To, h->TX0, h->TX1, &xt))) return rc;
+  if (!tail_e && (rc = run_temporal_tc(h, h->tpe[1], st.e[0], E, Bc, M, To, To, h->TE0, h->TE1, &et))) return rc;
+  if (!tail_x) st.x = {{xt, H, H, 0, N, 0}};
+  if (!tail_e) st.e = {{et, H, H, 0, M, 0}};
+  if (!tail_x && !tail_e) set_dbg(h, st, Bc * To * N, Bc * To * M);
+  if (h->debug_stop == 5) return 0;
+  if (!tail_x && (rc = launch_tc_gemm(h, st.x, h->resx.t[0], W(h, h->resx.t[1]), XO, E, E, ract, Bc, N, To, To, N, 0))) return rc;
+  if (!tail_e && (rc = launch_tc_gemm(h, st.e, h->rese.t[0], W(h, h->rese.t[1]), EO, E, E, ract, Bc, M, To, To, M, 0))) return rc;
   const long long RXo = Bc * To * N, REo = Bc * To * M;
   const int ldn = h->ldn();
   // resnet + narrow heads in one pass per stream (E == 128): x = act(cumsum_t(x_out) + res) feeds the hard_sigmoid /
@@ -1498,26 +1599,26 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
   // the node stream's only when the flood chain needs it
   const bool fuse_ch = c.resnet && E == 128 && h->fuse_heads && !h->debug_stop && c.n_out <= 4 && c.e_out <= 4;
   if (fuse_ch) {
-    CumHeadP px{reinterpret_cast<bf16*>(h->XA), h->RES, Bc, To, N, act, c.if_flood ? 1 : 0,
+    CumHeadP px{reinterpret_cast<bf16*>(XO), h->RES, Bc, To, N, act, c.if_flood ? 1 : 0,
                 W(h, h->head_out.t[0]), W(h, h->head_out.t[1]), h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID};
     if (c.n_out == 1) cumsum_head_bf16_kernel<1, 8><<<grid_for(h, Bc * N, 8, 8), 256, 0, h->stream>>>(px);
     else cumsum_head_bf16_kernel<4, 4><<<grid_for(h, Bc * N, 8, 8), 256, 0, h->stream>>>(px);
-    CumHeadP pe{reinterpret_cast<bf16*>(h->EA), h->RESE, Bc, To, M, act, 0,
+    CumHeadP pe{reinterpret_cast<bf16*>(EO), h->RESE, Bc, To, M, act, 0,
                 W(h, h->head_e.t[0]), W(h, h->head_e.t[1]), h->OUTE, c.e_out, 0, c.e_out, ACT_TANH};
     cumsum_head_bf16_kernel<4, 4><<<grid_for(h, Bc * M, 8, 8), 256, 0, h->stream>>>(pe);
     h->launches += 2;
     CU(cudaGetLastError());
   } else if (c.resnet) {
-    cumsum_res_act_kernel<bf16><<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(reinterpret_cast<bf16*>(h->XA), h->RES, Bc, To, N, E, act);
-    cumsum_res_act_kernel<bf16><<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(reinterpret_cast<bf16*>(h->EA), h->RESE, Bc, To, M, E, act);
+    cumsum_res_act_kernel<bf16><<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(reinterpret_cast<bf16*>(XO), h->RES, Bc, To, N, E, act);
+    cumsum_res_act_kernel<bf16><<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(reinterpret_cast<bf16*>(EO), h->RESE, Bc, To, M, E, act);
     h->launches += 2;
     CU(cudaGetLastError());
   }
-  st.x = {{h->XA, E, E, 0, N, 0}};
-  st.e = {{h->EA, E, E, 0, M, 0}};
+  st.x = {{XO, E, E, 0, N, 0}};
+  st.e = {{EO, E, E, 0, M, 0}};
   set_dbg(h, st, Bc * To * N, Bc * To * M);
   if (h->debug_stop == 6) return 0;
-  if (!fuse_ch && (rc = launch_head<bf16>(h, h->XA, E, E, h->head_out, h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID, RXo))) return rc;
+  if (!fuse_ch && (rc = launch_head<bf16>(h, XO, E, E, h->head_out, h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID, RXo))) return rc;
   if (c.if_flood) {
     std::vector<SegH> cur = st.x;
     float* bufs[2] = {h->EX, h->NX};
@@ -1532,7 +1633,7 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
     }
     if (!fuse_head && (rc = launch_head<bf16>(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return rc;
   }
-  if (!fuse_ch && (rc = launch_head<bf16>(h, h->EA, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
+  if (!fuse_ch && (rc = launch_head<bf16>(h, EO, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
   return run_postproc(h, x, b, a, Bc, y, ey, normalised_io);
 }
 
@@ -1828,6 +1929,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   if (getenv("GNNUDS_FUSED")) h->fused_mode = atoi(getenv("GNNUDS_FUSED"));
   if (getenv("GNNUDS_GRU_TC")) h->gru_tc = atoi(getenv("GNNUDS_GRU_TC"));
   if (getenv("GNNUDS_SP_AGG")) h->sp_agg = atoi(getenv("GNNUDS_SP_AGG"));
+  if (getenv("GNNUDS_TP_FUSED")) h->tp_fused = atoi(getenv("GNNUDS_TP_FUSED"));
   h->sp_g = std::max(1, std::min(8, 128 / std::max(1, std::max(c.n_node, c.n_edge))));
   if (getenv("GNNUDS_SP_GROUP")) h->sp_g = std::max(1, std::min(h->sp_g, atoi(getenv("GNNUDS_SP_GROUP"))));
   if (getenv("GNNUDS_SW128")) h->sw128 = atoi(getenv("GNNUDS_SW128"));
@@ -1932,7 +2034,7 @@ int gnnuds_destroy(gnnuds_handle* h) {
   void* ptrs[] = {h->d_blob, h->d_rp, h->d_ci, h->d_erp, h->d_eci, h->d_val, h->d_eval, h->d_edges, h->d_act_of_edge,
                   h->d_act_out, h->d_act_in, h->d_inc_ptr, h->d_inc_edge, h->d_inc_sign, h->d_hmin, h->d_hmax,
                   h->d_outfall, h->d_ehmax, h->d_nx, h->d_nb, h->d_ny, h->d_ne, h->d_ws, h->ro_x, h->ro_ex, h->ro_b, h->ro_a, h->d_wimg,
-                  h->d_bins[0], h->d_bins[1], h->d_prp[0], h->d_prp[1], h->d_pci[0], h->d_pci[1], h->d_pval[0], h->d_pval[1], h->d_adj_act, h->d_adj_keep, h->d_arp[0], h->d_arp[1], h->d_acj[0], h->d_acj[1], h->d_aval[0], h->d_aval[1], h->d_pump, h->d_offset, h->d_pump_in, h->d_pump_out, h->d_area, h->d_edge_from, h->d_ps};
+                  h->d_bins[0], h->d_bins[1], h->d_prp[0], h->d_prp[1], h->d_pci[0], h->d_pci[1], h->d_pval[0], h->d_pval[1], h->d_zeros, h->d_adj_act, h->d_adj_keep, h->d_arp[0], h->d_arp[1], h->d_acj[0], h->d_acj[1], h->d_aval[0], h->d_aval[1], h->d_pump, h->d_offset, h->d_pump_in, h->d_pump_out, h->d_area, h->d_edge_from, h->d_ps};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_ne_img[s]) if (p) cudaFree(p);
