@@ -214,6 +214,20 @@ def cpu_baseline(workload, seconds=20.0, fixed_B=None, runs=3):
             "ms_per_sample_call": t * 1e3}
 
 
+def reference_config(a):
+    """The b200 arm's `config` for the same workload (same wording), plus what the CPU arm actually ran per step."""
+    from gnn_uds_b200 import configs
+    args = configs.make_args(a.workload)
+    conv = "NN" if str(args.conv) in ("False", "None") else ("GAT" if "GAT" in str(args.conv) else "GCN")
+    N, M = len(args.nodes), len(args.links)
+    B = a.batch or args.B
+    return {"workload": "%s: %s %s+%s edge_fusion=%s resnet=%s if_flood=%d act=%s, N=%d M=%d, seq %d->%d, B=%d per GPU" % (
+                a.workload, configs.WORKLOADS[a.workload]["net"], conv, args.recurrent, bool(getattr(args, "edge_fusion", False)),
+                bool(args.resnet), int(getattr(args, "if_flood", 0)), bool(getattr(args, "act", False)), N, M, args.seq_in, args.seq_out, B),
+            "precision": "fp32", "sharding": "rank 0 only: host cores",
+            "sample": "each step = a bounded sample of the workload (B of a few scenarios, see cpu_baseline.sample); the rate is per node-timestep, so it compares with the full batch"}
+
+
 def run_reference(a):
     """--impl reference: the reference's math on host cores (oracle port; TF/spektral are absent)."""
     rank = int(os.environ.get("RANK", "0"))
@@ -229,7 +243,7 @@ def run_reference(a):
     res["value"] = v
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": res["ms_per_sample_call"], "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": {"workload": a.workload},
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": reference_config(a),
             "cpu_baseline": res, "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
 

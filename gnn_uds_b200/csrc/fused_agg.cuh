@@ -6,9 +6,8 @@
 // aggregation (K4/K5) of one (b,t) sample with no intermediate leaving the SM - but EVERY contraction runs on tcgen05,
 // the neighbour sum included: the attention (GAT) / filter (GCN) matrix of a 30..256-row drainage graph is tiny, so it
 // is kept as a dense fp16 K-major A operand in shared memory (zeros off the CSR pattern, the pattern's entries
-// rewritten per sample by the edge softmax) and `alpha @ h` is one more MMA series with the h tile as MN-major B
-// operand.  The SIMT gather of sp_conv_kernel (550 instructions per warp and sample, 6.4 k of its 8.4 k cycle period)
-// becomes <= 18 MMAs + one TMEM drain.
+// rewritten per sample by the edge softmax) and `alpha @ h` is one more MMA series.  The SIMT gather of sp_conv_kernel
+// (550 instructions per warp and sample, 6.4 k of its 8.4 k cycle period) becomes <= 18 MMAs + one TMEM drain.
 //
 // GAT scores also come from the tensor core: the conv weight image carries 16 extra output columns,
 // [hi(W a_self) lo(W a_self) hi(W a_neigh) lo(W a_neigh) 0...], so h.a_self and h.a_neigh arrive as accumulator
@@ -17,14 +16,19 @@
 //
 // Persistent, one CTA per SM, one sample per pass:
 //   warps 0..15  workers: every TMEM drain and the softmax, in phases (a warp owns TMEM lanes 32*(w%4).. and the
-//                column slice w/4):  A conv drain -> h tile (fp16, MN-major panels) + scores
-//                                     B edge softmax -> alpha entries (GAT only)
-//                                     C NodeEdge drain of the NEXT sample -> fp16 panels (A operand of its conv GEMM)
-//                                     D aggregation drain -> 1/den, bias, act -> fp16 -> HBM
-//   warp  16     MMA issuer (one thread): conv[i], NodeEdge[i+1], agg[i] in that order, so the tensor pipe works on
-//                conv/NodeEdge while the workers run the softmax, and on agg while they drain NodeEdge
+//                column slice w/4):
+//                  A  conv drain -> h^T (fp16 K-major SWIZZLE_128B tiles [features x 64 neighbours], written transposed
+//                     through tcgen05.ld.16x256b fragments + stmatrix.trans) + scores
+//                  C  NodeEdge drain -> fp16 panels (A operand of a later conv GEMM)
+//                  B  edge softmax -> alpha entries (GAT) / filter values (GCN)
+//                  D  aggregation drain -> 1/den, bias, act -> fp16, staged in the alpha region as SWIZZLE_128B tiles
+//                Order A C B D with NodeEdge one sample ahead (MT == 2), A B C D with NodeEdge TWO samples ahead and C in
+//                the window where the workers would wait for the aggregation MMAs (MT == 1).
+//   warp  16     MMA issuer (warp-uniform code, one elected lane): per sample NE[i+2], conv[i+1], agg[i] (MT == 1) or
+//                agg[i], conv[i+1], NE[i+2] (MT == 2)
 //   warp  17     TMA producer: other_dense tile (single buffer, free again once the NodeEdge MMAs read it) and the
-//                self tiles (nb_self buffers; the h tile of a sample aliases its own self tiles)
+//                self tiles (nb_self buffers; h^T of a sample aliases its own self tiles)
+//   warp  18     store warp: TMA store of the staged output tile, then a bulk copy of zeros re-arms the alpha region
 // MT == 2 (R > 128, the 131-link side of shunqing): one self/h buffer and the aggregation accumulators alias the conv
 // accumulators (shared memory and TMEM are both full), so conv[i+1] waits for the aggregation drain of sample i.
 #pragma once
