@@ -66,7 +66,7 @@ struct SpAggP {
   int agg_n128;               // 1: one N=128 aggregation MMA per K step (LBO = distance of the two h tiles), 0: two N=64 MMAs
   long long* trace;           // debug: clock64 stamps of CTA 0, SA_NSTAMP per sample (GNNUDS_TRACE_FILE), else null
 };
-constexpr int SA_NSTAMP = 20;
+constexpr int SA_NSTAMP = 24;
 #define SA_STAMP(i, k) do { if (p.trace && blockIdx.x == 0 && tid == 0 && (i) < 64) p.trace[(i) * SA_NSTAMP + (k)] = clock64(); } while (0)
 #define SA_STAMPM(i, k) do { if (p.trace && blockIdx.x == 0 && (i) < 64) p.trace[(i) * SA_NSTAMP + (k)] = clock64(); } while (0)
 

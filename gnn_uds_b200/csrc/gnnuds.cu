@@ -10,6 +10,7 @@
 #include "fused_sp.cuh"
 #include "fused_conv.cuh"
 #include "fused_agg.cuh"
+#include "fused_aggt.cuh"
 #include "fused_tp.cuh"
 #include "gru_tc.cuh"
 #include "nn_cat.cuh"
@@ -118,6 +119,8 @@ struct gnnuds_handle {
   // use_adj (GAT): per-entry controlled-link index / static keep flags of the node filter, the chunk's settings
   uint8_t* d_zeros = nullptr;           // 64 KB of zeros: source of sp_agg_kernel's bulk re-zeroing of its alpha region
   int* d_adj_act = nullptr; unsigned char* d_adj_keep = nullptr; bool use_adj = false; const float* cur_a = nullptr;
+  int sp_aggt = 1;                      // GNNUDS_SP_AGGT: 0 = sp_agg_kernel (rows on M, two tiles) for 128 < R <= 144 instead of sp_aggt_kernel
+  std::vector<uint8_t*> d_wa[2];        // GAT: score operand images per conv layer and side (sp_aggt_kernel, fused_aggt.cuh)
   int tp_fused = 1;                     // GNNUDS_TP_FUSED: 0 = one tc_rows_kernel launch per Conv1D layer instead of tp_conv_kernel
   int sp_agg = 1;                       // GNNUDS_SP_AGG: 0 = sp_conv_kernel (SIMT gather) instead of sp_agg_kernel
   float *d_val = nullptr, *d_eval = nullptr;
@@ -1327,13 +1330,15 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
   const int Ktot = p.Kself + F;
   if ((long long)Ktot * E != h->tens[w.t[0]].numel || h->img_off[w.t[0]] < 0) return -1;
   p.S = (int)S; p.R = R; p.Ro = Ro; p.F = F; p.Nout = E; p.act = act; p.gat = gat ? 1 : 0;
-  p.NW = gat ? E + 16 : E;
   p.Rbox = (R + 7) / 8 * 8; p.Kp = h->ne_kp[side]; p.KpJ = (R + 15) / 16 * 16; p.MT = (R + 127) / 128;
   if (p.Kp % 8) return -1;
+  // 128 < R <= 144: transposed kernel (features on M, rows on N), csrc/fused_aggt.cuh
+  const bool T = h->sp_aggt && p.MT == 2 && p.KpJ <= 144 && p.Kself <= 128 && (!gat || (int)h->d_wa[side].size() > li);
+  p.NW = gat && !T ? E + 16 : E;
   p.nb_self = p.MT > 1 ? 1 : 2; p.alias_acc = p.MT > 1 ? 1 : 0;
   p.max_len = h->sp_max_len[side];
   p.pstrideP = (uint32_t)p.Rbox * 16u; p.pstrideM = h->ne_pstride[side]; p.pstrideH = (uint32_t)p.KpJ * 16u; p.pstrideAl = (uint32_t)p.Rbox * 16u;
-  if (gat) { p.Wimg = h->d_cv_img[side][li]; p.w_bytes = h->cv_img_bytes[side][li]; }
+  if (gat && !T) { p.Wimg = h->d_cv_img[side][li]; p.w_bytes = h->cv_img_bytes[side][li]; }
   else { p.Wimg = h->d_wimg + h->img_off[w.t[0]]; p.w_bytes = (uint32_t)Ktot * E * 2u; }
   if (p.w_bytes != (uint32_t)(Ktot / 8) * (uint32_t)p.NW * 16u) return -1;
   p.Mimg = h->d_ne_img[side][li]; p.m_bytes = h->ne_img_bytes[side];
@@ -1362,7 +1367,10 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
   p.off_sc = al(p.off_al + p.al_zero, 128);
   p.agg_n128 = getenv("GNNUDS_AGG_N128") ? atoi(getenv("GNNUDS_AGG_N128")) : 1;
   const uint32_t sc_bytes = ((uint32_t)E + 3u * RP) * 4u + ((uint32_t)R + 1u + (uint32_t)p.nnz * (gat ? 1u : 2u)) * 4u;
-  p.off_bar = al(p.off_sc + sc_bytes, 16);
+  SpAggTP pt{};
+  pt.off_wa = al(p.off_sc + sc_bytes, 128);                                  // T: the two score operand images
+  pt.off_dump = pt.off_wa + (T && gat ? (uint32_t)(Ktot / 8) * 128u : 0u);
+  p.off_bar = T ? al(pt.off_dump + 256u, 16) : al(p.off_sc + sc_bytes, 16);
   // operand views of an M tile read 128 rows from the tile's first row of every panel / swizzle chunk: keep those
   // reads inside the allocation
   uint32_t reach = p.off_bar + 17u * 8u + 16u;
@@ -1378,6 +1386,7 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
   if (!make_rows_tmap_sw(&p.tm_out, out, rows_total, E, E, R)) return -1;
   if (!h->attr_done[5]) {
     CU(cudaFuncSetAttribute(sp_agg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    CU(cudaFuncSetAttribute(sp_aggt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     h->attr_done[5] = true;
   }
   const unsigned grid = (unsigned)std::min<long long>(S, h->sm_count);
@@ -1389,7 +1398,12 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
   if (do_trace) { CU(cudaMalloc(&p.trace, tn * sizeof(long long))); CU(cudaMemset(p.trace, 0, tn * sizeof(long long))); }
   cudaEvent_t e1 = nullptr;
   { int prc = prof_begin(h, GNNUDS_FAM_SPATIAL, &e1); if (prc) return prc; }
-  sp_agg_kernel<<<grid, SA_THREADS, smem, h->stream>>>(p);
+  if (T) {
+    pt.b = p; pt.wa = gat ? h->d_wa[side][li] : nullptr; pt.Nr = p.KpJ;
+    sp_aggt_kernel<<<grid, SA_THREADS, smem, h->stream>>>(pt);
+  } else {
+    sp_agg_kernel<<<grid, SA_THREADS, smem, h->stream>>>(p);
+  }
   ++h->launches;
   { int prc = prof_end(h, e1); if (prc) return prc; }
   CU(cudaGetLastError());
@@ -1399,7 +1413,7 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
     CU(cudaMemcpy(t.data(), p.trace, tn * sizeof(long long), cudaMemcpyDeviceToHost));
     cudaFree(p.trace);
     if (FILE* f = fopen(tf, "w")) {
-      fprintf(f, "# sp_agg R=%d Ro=%d Kself=%d MT=%d smem=%zu: sample, cycles since first stamp: 0 conv_done_seen 1 h_ready 2 alpha_ready 3 ne_drained 4 agg_done_seen 5 out_done | 6 A:tmem 7 A:stored 8 B:bar1 9 B:zeroed 10 D:tmem 11 D:staged 12 D:bar | MMA thread: 13 conv issued 14 agg issue 15 agg issued 16 NE issue 17 NE issued 18 conv issue\n", R, Ro, p.Kself, p.MT, smem);
+      fprintf(f, "# sp_agg%s R=%d Ro=%d Kself=%d MT=%d smem=%zu: sample, cycles since first stamp: 0 conv_done_seen 1 h_ready 2 alpha_ready 3 ne_drained 4 agg_done_seen 5 out_done | 6 A:tmem 7 A:stored 8 B:bar1 9 B:zeroed 10 D:tmem 11 D:staged 12 D:bar | MMA thread: 13 conv issued 14 agg issue 15 agg issued 16 NE issue 17 NE issued 18 conv issue\n", T ? "t" : "", R, Ro, p.Kself, p.MT, smem);
       for (int i = 0; i < 64; ++i) { fprintf(f, "%d", i); for (int k = 0; k < SA_NSTAMP; ++k) fprintf(f, " %lld", t[i * SA_NSTAMP + k] ? t[i * SA_NSTAMP + k] - t[0] : -1); fprintf(f, "\n"); }
       fclose(f);
     }
@@ -1930,6 +1944,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   if (getenv("GNNUDS_GRU_TC")) h->gru_tc = atoi(getenv("GNNUDS_GRU_TC"));
   if (getenv("GNNUDS_SP_AGG")) h->sp_agg = atoi(getenv("GNNUDS_SP_AGG"));
   if (getenv("GNNUDS_TP_FUSED")) h->tp_fused = atoi(getenv("GNNUDS_TP_FUSED"));
+  if (getenv("GNNUDS_SP_AGGT")) h->sp_aggt = atoi(getenv("GNNUDS_SP_AGGT"));
   h->sp_g = std::max(1, std::min(8, 128 / std::max(1, std::max(c.n_node, c.n_edge))));
   if (getenv("GNNUDS_SP_GROUP")) h->sp_g = std::max(1, std::min(h->sp_g, atoi(getenv("GNNUDS_SP_GROUP"))));
   if (getenv("GNNUDS_SW128")) h->sw128 = atoi(getenv("GNNUDS_SW128"));
@@ -2039,6 +2054,7 @@ int gnnuds_destroy(gnnuds_handle* h) {
   for (int s = 0; s < 2; ++s) for (float* p : h->d_ne_matT[s]) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_ne_img[s]) if (p) cudaFree(p);
   for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_cv_img[s]) if (p) cudaFree(p);
+  for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_wa[s]) if (p) cudaFree(p);
   for (int k = 0; k < 2; ++k) { if (h->pin_in[k]) cudaFreeHost(h->pin_in[k]); if (h->pin_out[k]) cudaFreeHost(h->pin_out[k]); }
   for (float* q : h->gb) if (q) cudaFree(q);
   for (auto& e : h->gemm_ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
@@ -2314,6 +2330,7 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
       // GAT: conv weight images with 16 extra output columns [hi(W a_self) lo(W a_self) hi(W a_neigh) lo(W a_neigh) 0..]
       // (hi/lo = 16-bit split of the fp32 product), so sp_agg_kernel reads the attention scores as accumulator columns
       for (int s = 0; s < 2; ++s) { for (uint8_t* p : h->d_cv_img[s]) if (p) cudaFree(p); h->d_cv_img[s].clear(); h->cv_img_bytes[s].clear(); }
+      for (int s = 0; s < 2; ++s) { for (uint8_t* p : h->d_wa[s]) if (p) cudaFree(p); h->d_wa[s].clear(); }
       if (c.conv == GNNUDS_CONV_GAT && c.embed % 16 == 0)
         for (int blk = 0; blk < 2; ++blk)
           for (int l = 0; l < c.n_sp_layer; ++l) {
@@ -2322,14 +2339,19 @@ int gnnuds_set_weights(gnnuds_handle* h, const float* blob, int64_t n_floats, co
               const LayerW& lw = s == 0 ? w.conv_x : w.conv_e;
               const int E = c.embed, NW = E + 16, Ktot = (int)(h->tens[lw.t[0]].numel / E);
               const float* Wk = blob + offsets[lw.t[0]]; const float* as = blob + offsets[lw.t[1]]; const float* an = blob + offsets[lw.t[2]];
+              // sp_aggt_kernel: the same four vectors as 8-row A operand panels [K/8][8 rows][8 K], rows 0..3
               std::vector<float> wx((size_t)Ktot * NW, 0.f);
+              std::vector<uint16_t> wav((size_t)Ktot * 8, 0);
               for (int k = 0; k < Ktot; ++k) {
                 double ds = 0.0, dn = 0.0;
                 for (int n = 0; n < E; ++n) { wx[(size_t)k * NW + n] = Wk[(size_t)k * E + n]; ds += (double)Wk[(size_t)k * E + n] * as[n]; dn += (double)Wk[(size_t)k * E + n] * an[n]; }
                 const float fs = (float)ds, fn = (float)dn, fsh = bf2f(f2bf(fs)), fnh = bf2f(f2bf(fn));
                 wx[(size_t)k * NW + E] = fsh; wx[(size_t)k * NW + E + 1] = fs - fsh;
                 wx[(size_t)k * NW + E + 2] = fnh; wx[(size_t)k * NW + E + 3] = fn - fnh;
+                const float four[4] = {fsh, fs - fsh, fnh, fn - fnh};
+                for (int r = 0; r < 4; ++r) wav[(size_t)(k >> 3) * 64 + (size_t)r * 8 + (k & 7)] = f2bf(four[r]);
               }
+              { uint16_t* dw = nullptr; if ((rc = upload(h, &dw, wav.data(), wav.size()))) return rc; h->d_wa[s].push_back(reinterpret_cast<uint8_t*>(dw)); }
               std::vector<uint16_t> img = pack_kmajor(wx.data(), NW, Ktot, 1, NW, NW, Ktot, NW * 16);
               uint16_t* d = nullptr;
               if ((rc = upload(h, &d, img.data(), img.size()))) return rc;
