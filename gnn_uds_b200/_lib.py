@@ -49,7 +49,7 @@ _lib = None
 SYMBOLS = [
     "gnnuds_create", "gnnuds_destroy", "gnnuds_last_error", "gnnuds_set_graph", "gnnuds_weight_layout",
     "gnnuds_set_weights", "gnnuds_set_norm", "gnnuds_output_dims", "gnnuds_predict", "gnnuds_simulate",
-    "gnnuds_rollout", "gnnuds_objective", "gnnuds_evaluate", "gnnuds_replay", "gnnuds_build_windows", "gnnuds_alloc_pinned", "gnnuds_free_pinned", "gnnuds_alloc_device",
+    "gnnuds_rollout", "gnnuds_objective", "gnnuds_objective_static", "gnnuds_evaluate", "gnnuds_replay", "gnnuds_build_windows", "gnnuds_alloc_pinned", "gnnuds_free_pinned", "gnnuds_alloc_device",
     "gnnuds_free_device", "gnnuds_memcpy", "gnnuds_synchronize", "gnnuds_launch_count", "gnnuds_last_timing",
     "gnnuds_set_profiling", "gnnuds_measure_simt_tflops", "gnnuds_kernel_timing", "gnnuds_debug_stop_after", "gnnuds_debug_fetch", "gnnuds_debug_umma_selftest",
     "gnnuds_tc_operand_is_half", "gnnuds_set_post_proc_variant", "gnnuds_set_adj_action",
@@ -80,6 +80,7 @@ def load():
     lib.gnnuds_simulate.argtypes = [vp, vp, vp, i32, vp, vp, i64, vp, vp, i32]
     lib.gnnuds_rollout.argtypes = [vp, i32, vp, vp, vp, vp, i64, i32, vp, vp, i32]
     lib.gnnuds_objective.argtypes = [vp, vp, vp, i64, i32, vp, vp, vp, vp, vp, i32]
+    lib.gnnuds_objective_static.argtypes = [vp, vp, vp, i64, i32, vp, vp, vp, vp, vp, i32]
     lib.gnnuds_alloc_pinned.argtypes = [P(vp), i64]
     lib.gnnuds_free_pinned.argtypes = [vp]
     lib.gnnuds_alloc_device.argtypes = [vp, P(vp), i64]

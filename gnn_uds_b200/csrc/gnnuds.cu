@@ -19,6 +19,7 @@
 #include <array>
 #include <thread>
 #include <cmath>
+#include <mutex>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -2998,3 +2999,103 @@ int gnnuds_debug_fetch(gnnuds_handle* h, int32_t which, float* out, int64_t max_
 }
 
 }  // extern "C"
+
+// =====================================================================================================================
+// gnnuds_objective_static: the astlingen objective with NO allocation (include/gnnuds.h).  No counterpart in the
+// reference; added for callers that cannot call cudaMalloc (CUDA graph capture,
+// tight serving loops, harnesses that forbid it).
+//
+// The chunked objective (obj_acc_kernel, kernels.cuh) carries two pieces of scratch from one time slab to the next: the
+// 128 per-thread partial sums of every candidate and q_in of the slab's last step.  gnnuds_evaluate keeps them in
+// grow-only buffers of the handle (cudaMalloc on first use); here they live in ONE file-scope device array of a fixed
+// size that every GPU which loads the library holds until the process exits.  All calls (all handles, all streams) on a
+// device share it: calls that overlap on the GPU race.  Nothing in it has to start at zero - the first slab overwrites
+// the partial sums and q_in - so a call is not affected by what the previous one left behind.
+// =====================================================================================================================
+namespace {
+
+static __device__ __align__(256) float g_obj_scratch[GNNUDS_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+// In host code the array's name is only a handle for the runtime, not a device address: the address a kernel can use
+// comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr int GU_STATIC_MAX_DEV = 64;
+float* g_obj_scratch_ptr[GU_STATIC_MAX_DEV] = {};
+std::mutex g_obj_scratch_mu;
+
+// time slab t0..t1-1 of the FULL prediction tensor y (B,T,N,ny).  Same ownership as obj_acc_kernel / objective_kernel:
+// thread tid of candidate i adds the terms g = t*N + n with g % 128 == tid in increasing g, so the final sum is bitwise
+// the one objective_kernel returns.
+struct ObjSlabP {
+  const float* y; int ny;
+  const float* q_in0;
+  const float* flood_w; const float* wwtp_w; const float* rough_w; const float* gamma;
+  float* part;      // scratch (B,128): running partial sums
+  float* prev_q;    // scratch (B,N): q_in of step t0-1, written by the slab before
+  long long B; int T, N, t0, t1;
+};
+__global__ void __launch_bounds__(128) obj_slab_static_kernel(ObjSlabP p) {
+  for (long long i = blockIdx.x; i < p.B; i += gridDim.x) {
+    const int tid = threadIdx.x;
+    float acc = p.t0 == 0 ? 0.f : p.part[i * 128 + tid];
+    const int g0 = p.t0 * p.N;
+    for (int g = g0 + ((tid - g0) % 128 + 128) % 128; g < p.t1 * p.N; g += 128) {
+      const int t = g / p.N, n = g % p.N;
+      const float* ys = p.y + ((i * p.T + t) * p.N + n) * p.ny;
+      const float gm = p.gamma ? p.gamma[t] : 1.f;
+      float v = ys[p.ny - 1] * p.flood_w[n] + ys[1] * p.wwtp_w[n];
+      if (p.rough_w) {
+        const float prev = t > p.t0 ? (ys - (long long)p.N * p.ny)[1] : (p.t0 == 0 ? p.q_in0[i * p.N + n] : p.prev_q[i * p.N + n]);
+        v += fabsf(ys[1] - prev) * p.rough_w[n];
+      }
+      acc += v * gm;
+    }
+    p.part[i * 128 + tid] = acc;
+    __syncthreads();                                   // every read of prev_q of this candidate is done
+    for (int n = tid; n < p.N; n += 128) p.prev_q[i * p.N + n] = p.y[((i * p.T + p.t1 - 1) * p.N + n) * p.ny + 1];
+  }
+}
+
+}  // namespace
+
+extern "C" int gnnuds_objective_static(gnnuds_handle* h, const float* y, const float* q_in0, int64_t B, int32_t T,
+                                       const float* flood_w, const float* wwtp_w, const float* rough_w, const float* gamma,
+                                       float* obj, int32_t sync) {
+  if (!h) return GNNUDS_E_INVALID;
+  if (!y || !q_in0 || !flood_w || !wwtp_w || !obj || B < 0 || T < 1) return fail(h, GNNUDS_E_INVALID, "objective_static: bad argument");
+  const auto& c = h->c;
+  const int N = c.n_node, nyc = h->ny();
+  const long long need = (long long)B * (128 + N), have = (long long)(GNNUDS_STATIC_SCRATCH_BYTES / sizeof(float));
+  if (need > have)
+    return fail(h, GNNUDS_E_INVALID,
+                "objective_static: B * (128 + n_node) = %lld x %d = %lld floats of scratch, the static array holds %lld "
+                "(GNNUDS_STATIC_SCRATCH_BYTES = %d); split the population or use gnnuds_objective",
+                (long long)B, 128 + N, need, have, (int)GNNUDS_STATIC_SCRATCH_BYTES);
+  if (c.device < 0 || c.device >= GU_STATIC_MAX_DEV) return fail(h, GNNUDS_E_INVALID, "objective_static: device %d", c.device);
+  CU(cudaSetDevice(c.device));
+  if (B == 0) return 0;
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_obj_scratch_mu);
+    if (!g_obj_scratch_ptr[c.device]) {
+      float* ptr = nullptr;
+      cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_obj_scratch);
+      if (e != cudaSuccess || !ptr) return fail(h, GNNUDS_E_CUDA, "objective_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      g_obj_scratch_ptr[c.device] = ptr;
+    }
+    scratch = g_obj_scratch_ptr[c.device];
+  }
+  ObjSlabP p{y, nyc, q_in0, flood_w, wwtp_w, rough_w, gamma, scratch, scratch + (size_t)B * 128, (long long)B, T, N, 0, 0};
+  const int grid = grid_for(h, B, 1, 16);
+  const int cut = T >= 2 ? T / 2 : T;                  // two slabs: the scratch really is the carried state
+  for (int t0 = 0; t0 < T; t0 = p.t1) {
+    p.t0 = t0; p.t1 = t0 == 0 ? cut : T;
+    obj_slab_static_kernel<<<grid, 128, 0, h->stream>>>(p);
+    ++h->launches;
+  }
+  obj_final_kernel<<<grid, 128, 0, h->stream>>>(scratch, obj, B);
+  ++h->launches;
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess && sync) e = cudaStreamSynchronize(h->stream);
+  if (e != cudaSuccess) return fail(h, GNNUDS_E_CUDA, "objective_static: %s", cudaGetErrorString(e));
+  return 0;
+}

@@ -172,6 +172,23 @@ int gnnuds_objective(gnnuds_handle* h, const float* y, const float* q_in0, int64
                      const float* flood_w, const float* wwtp_w, const float* rough_w,
                      const float* gamma, float* obj, int32_t where);
 
+/* The same objective with NO allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Every pointer is DEVICE memory on cfg.device, laid out as for gnnuds_objective (y (B,T,n_node,y_ch), q_in0 (B,n_node),
+ * flood_w / wwtp_w / rough_w|NULL (n_node), gamma|NULL (T), obj (B)).  The objective is accumulated in two time slabs
+ * whose carried state (128 partial sums and the last q_in per candidate) lives in a file-scope `static __device__` array
+ * of GNNUDS_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until exit; its device address is taken
+ * once per device with cudaGetSymbolAddress.  The call makes no cudaMalloc / cudaFree / allocating library call.
+ * Limit: B * (128 + n_node) * 4 bytes <= GNNUDS_STATIC_SCRATCH_BYTES (astlingen, 30 nodes: B <= 6636), else
+ * GNNUDS_E_INVALID with the sizes in gnnuds_last_error.  All calls on a device share the array: calls that overlap on
+ * the GPU (two handles, two host threads) race; calls in sequence are independent (nothing in the array has to start at
+ * zero, the first slab overwrites it).  Runs on the handle's stream; sync != 0 waits for it, sync == 0 only enqueues
+ * (gnnuds_synchronize waits).  Bitwise equal to gnnuds_objective. */
+#define GNNUDS_STATIC_SCRATCH_BYTES (4 << 20)
+int gnnuds_objective_static(gnnuds_handle* h, const float* y, const float* q_in0, int64_t B, int32_t T,
+                            const float* flood_w, const float* wwtp_w, const float* rough_w,
+                            const float* gamma, float* obj, int32_t sync);
+
 /* MPC population evaluation as ONE device-resident call (mpc.py:210-259 pred_emu/pred_emu_tf, :565-582 chunked loop,
  * envs/scenario/astlingen.py:75-99 objective): B candidates share one observed state x0 (seq_in,N,n_in) / ex0
  * (seq_in,M,e_in) - the reference tiles them on the host (mpc.py:237-240) - and n_b runoff scenarios b
