@@ -21,8 +21,17 @@
 // every lane group hold the scores, each worker warp reads some columns from its own quadrant.  Any SIMT version of this product (plain FMAs, mma.sync + ldmatrix) took 2.5-4 k cycles next to the running MMAs:
 // shared-memory loads issue every ~250 cycles while the tensor pipe streams operands.
 //
-// Roles and barriers as in sp_agg_kernel: 16 workers (S scores, A conv drain, C NodeEdge drain of the next sample,
-// B softmax, D aggregation drain), MMA issuer (agg[i], conv[i+1], NE[i+2]; one self / h^T buffer), TMA producer, store warp.
+// Shared memory is what bounds the pipeline (W^T image 48 KB + NodeEdge image 34 KB + self tiles 34 KB + h^T 36..48 KB + x_e
+// 16 KB + NodeEdge panels 17 KB + alpha / staging 38 KB > 227 KB): with h^T written over the self tiles the load of the next
+// sample could only start when agg[i] had completed, and TMA latency + conv[i+1] sat on the critical path behind the
+// aggregation drain.  So the persistent A operand of conv^T lives in TENSOR MEMORY (96 columns, written once per CTA with
+// tcgen05.st; tcgen05.mma takes A from TMEM - which also removes the 4 KB/MMA shared-memory read of A), h^T gets its own
+// region (two SWIZZLE_128B tiles + plain panels for the rows 128..143), and so does the staging tile of the TMA store: the
+// alpha operand is zeroed once per CTA, every sample's softmax rewrites the same CSR positions.
+// TMEM: conv 144 | aggregation + scores 144 | W^T 96 | NodeEdge 128 = 512 columns.
+//
+// Roles: 16 workers (A conv drain -> h^T, score read, B softmax, C NodeEdge drain of the next sample while agg[i] runs,
+// D aggregation drain), MMA issuer (agg[i], conv[i+1], scores[i+1], NE[i+2]), TMA producer, store warp.
 #pragma once
 #include <cuda.h>
 
@@ -44,6 +53,8 @@ struct SpAggTP {
   const uint8_t* wa;          // GAT score operand: 2 images x K/8 panels x [8 rows x 8 K] 16-bit (set_weights), K = Kself + F
   int Nr;                     // rows of a sample rounded up to 16: N of the transposed MMAs
   uint32_t off_wa, off_dump;  // smem: the score operand images; 256 bytes that swallow stmatrix rows beyond R
+  uint32_t off_h;             // smem: h^T, two SWIZZLE_128B tiles [Nout x 64 rows] + (Nr - 128) / 8 plain panels [Nout x 8 rows]
+  uint32_t off_stage;         // smem: SWIZZLE_128B staging tile of the TMA store (two 64-column halves, stage_half apart)
 };
 
 __global__ void __launch_bounds__(SA_THREADS, 1) sp_aggt_kernel(const __grid_constant__ SpAggTP pp) {
@@ -61,11 +72,12 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_aggt_kernel(const __grid_con
   uint64_t* h_ready = bars + 9;
   uint64_t* alpha_ready = bars + 10;
   uint64_t* agg_done = bars + 11;
-  uint64_t* out_done = bars + 12;
+  uint64_t* agg_read = bars + 12;    // aggregation accumulators of this sample are in registers (workers)
   uint64_t* wbar = bars + 13;
-  uint64_t* zbar = bars + 14;
+  uint64_t* st_free = bars + 14;     // TMA store of this sample has read the staging tile (store warp)
   uint64_t* staged = bars + 15;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+  uint64_t* sc_done = bars + 16;     // score MMAs of this sample completed (tcgen05.commit)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
   const int RP = 256;
   float* bias_s = reinterpret_cast<float*>(smem + p.off_sc);
   float* ss = bias_s + p.Nout;       // [h.a_self 256 | h.a_neigh 256]
@@ -80,14 +92,16 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_aggt_kernel(const __grid_con
   if (tid == 32) {
     for (int i = 0; i < 2; ++i) { tc::mbar_init(&self_full[i], 1); tc::mbar_init(&self_empty[i], 1); }
     tc::mbar_init(xe_full, 1); tc::mbar_init(xe_empty, 1); tc::mbar_init(ne_done, 1);
-    tc::mbar_init(nx_ready, SA_WORKERS * 32);
+    // worker barriers: one arrival per warp (mbar_arrive_warp)
+    tc::mbar_init(nx_ready, SA_WORKERS);
     tc::mbar_init(conv_done, 1);
-    tc::mbar_init(h_ready, SA_WORKERS * 32);
-    tc::mbar_init(alpha_ready, SA_WORKERS * 32);
+    tc::mbar_init(h_ready, SA_WORKERS);
+    tc::mbar_init(alpha_ready, SA_WORKERS);
     tc::mbar_init(agg_done, 1);
-    tc::mbar_init(out_done, SA_WORKERS * 32);
-    tc::mbar_init(wbar, 1); tc::mbar_init(zbar, 1);
-    tc::mbar_init(staged, SA_WORKERS * 32);
+    tc::mbar_init(agg_read, SA_WORKERS);
+    tc::mbar_init(wbar, 1); tc::mbar_init(st_free, 1);
+    tc::mbar_init(staged, SA_WORKERS);
+    tc::mbar_init(sc_done, 1);
     tc::mbar_fence_init();
   }
   for (int i = tid; i < p.Nout; i += SA_THREADS) bias_s[i] = p.bias ? p.bias[i] : 0.f;
@@ -110,7 +124,20 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_aggt_kernel(const __grid_con
   const uint32_t acc_conv = tmem;               // Nr columns (<= 144)
   const uint32_t acc_agg = tmem + 144u;         // Nr columns
   const uint32_t acc_sc = acc_agg;              // GAT scores of the next sample, lanes 8g+0..3, between the aggregations
+  const uint32_t a_w = tmem + 288u;             // W^T as A operand: lane = feature, K/2 columns (<= 96)
   const uint32_t acc_ne = tmem + 384u;          // 2 x F columns
+  if (warp < SA_WORKERS) {
+    // W^T image (global, K-major panels [K/8][Nout][8]) -> tensor memory: 16 bytes of a panel row = 4 columns of lane f
+    const int q = warp & 3, cs = warp >> 2, f = q * 32 + lane;
+    for (int pn = cs; pn < (K >> 3); pn += 4) {
+      const uint4 w = f < p.Nout ? *reinterpret_cast<const uint4*>(p.Wimg + ((size_t)pn * p.Nout + f) * 16) : make_uint4(0u, 0u, 0u, 0u);
+      tc::tmem_st4(a_w + ((uint32_t)(q * 32) << 16) + (uint32_t)(4 * pn), w);
+    }
+    tc::tmem_st_wait();
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
   const int n_it = p.S > (int)blockIdx.x ? (p.S - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
   const int Nr = pp.Nr;
   const uint32_t h_tile = (uint32_t)p.Nout * 128u;            // one h^T tile [Nout features x 64 rows]
@@ -133,8 +160,8 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_aggt_kernel(const __grid_con
         uint32_t o = 0;
         for (int s = 0; s < p.nseg; ++s)
           for (int k0 = 0; k0 < p.segw[s]; k0 += 64, o += p.chunk_bytes) tc::tma_load_2d(smem + p.off_self + o, &p.tm_self[s], k0, smp * p.R, &self_full[0]);
-        // ONE self buffer (h^T overwrites it): the load of sample i+1 starts when agg[i] completes and sits on the critical
-        // path - bring its lines into L2 a whole sample early, so that it is an L2 hit (~2 k -> ~0.7 k cycles)
+        // ONE self buffer: the load of sample i+1 starts when conv[i] and scores[i] have read it - bring its lines into L2 a
+        // whole sample early, so that it is an L2 hit
         if (i + 1 < n_it)
           for (int s = 0; s < p.nseg; ++s)
             for (int k0 = 0; k0 < p.segw[s]; k0 += 64) tc::tma_prefetch_2d(&p.tm_self[s], k0, (smp + (int)gridDim.x) * p.R);
@@ -142,7 +169,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_aggt_kernel(const __grid_con
       issue_xe(0);
       issue_self(0);
       if (n_it > 1) issue_xe(1);
-      for (int k = 0; k + 1 < n_it; ++k) { if (k + 2 < n_it) issue_xe(k + 2); issue_self(k + 1); }
+      for (int k = 0; k + 1 < n_it; ++k) { issue_self(k + 1); if (k + 2 < n_it) issue_xe(k + 2); }   // NE[k+2] is issued late in sample k: its x_e slot must not hold up the self tiles
     }
   } else if (warp == SA_WORKERS + 2) {
     // ================================ store warp ================================
@@ -150,12 +177,11 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_aggt_kernel(const __grid_con
       for (int i = 0; i < n_it; ++i) {
         const int smp = (int)blockIdx.x + i * (int)gridDim.x;
         tc::mbar_wait(staged, i & 1);
-        tma_store_2d(&p.tm_out, 0, smp * p.R, smem + p.off_al);
-        tma_store_2d(&p.tm_out, 64, smp * p.R, smem + p.off_al + p.stage_half);
+        tma_store_2d(&p.tm_out, 0, smp * p.R, smem + pp.off_stage);
+        tma_store_2d(&p.tm_out, 64, smp * p.R, smem + pp.off_stage + p.stage_half);
         bulk_commit();
         bulk_wait_read();
-        tc::mbar_expect_tx(zbar, p.al_zero);
-        for (uint32_t o = 0; o < p.al_zero; o += 16384) tc::bulk_g2s(smem + p.off_al + o, p.zeros + o, min(p.al_zero - o, 16384u), zbar);
+        mbar_arrive(st_free);
       }
       bulk_wait_all();
     }

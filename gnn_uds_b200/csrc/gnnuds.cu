@@ -1356,26 +1356,36 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
   p.nx_bytes = (uint32_t)(F / 8) * p.pstrideP;
   p.al_bytes = (uint32_t)(p.KpJ / 8) * p.pstrideAl;
   const uint32_t h_bytes = (uint32_t)((p.KpJ + 63) / 64) * (uint32_t)E * 128u;   // h^T tiles [E x 64 neighbours]
+  SpAggTP pt{};
   p.off_w = 0;
-  p.off_m = al(p.w_bytes, 128);
-  p.off_self = al(p.off_m + p.m_bytes, 1024);
-  p.self_stride = al(std::max(p.self_bytes, h_bytes), 1024);
-  p.off_xe = p.off_self + (uint32_t)p.nb_self * p.self_stride;
+  if (T) {
+    // W^T lives in tensor memory; h^T and the staging tile of the TMA store have their own regions (fused_aggt.cuh)
+    p.off_m = 0;
+    p.off_self = al(p.m_bytes, 1024);
+    p.self_stride = al(p.self_bytes, 1024);
+    pt.off_h = p.off_self + p.self_stride;
+    pt.off_stage = pt.off_h + al(2u * (uint32_t)E * 128u + (uint32_t)((p.KpJ - 128) / 8) * (uint32_t)E * 16u, 1024);
+    p.off_xe = pt.off_stage + 2u * al((uint32_t)R * 128u, 1024);
+  } else {
+    p.off_m = al(p.w_bytes, 128);
+    p.off_self = al(p.off_m + p.m_bytes, 1024);
+    p.self_stride = al(std::max(p.self_bytes, h_bytes), 1024);
+    p.off_xe = p.off_self + (uint32_t)p.nb_self * p.self_stride;
+  }
   p.off_nx = al(p.off_xe + p.xe_bytes, 128);
-  p.off_al = al(p.off_nx + p.nx_bytes, 1024);      // doubles as the SWIZZLE_128B staging tile of the TMA store
+  p.off_al = al(p.off_nx + p.nx_bytes, 1024);      // doubles as the SWIZZLE_128B staging tile of the TMA store (not T)
   p.stage_half = al((uint32_t)R * 128u, 1024);
-  p.al_zero = al(std::max(p.al_bytes, 2u * p.stage_half), 16);
+  p.al_zero = T ? al(p.al_bytes, 16) : al(std::max(p.al_bytes, 2u * p.stage_half), 16);   // T: own staging tile
   p.off_sc = al(p.off_al + p.al_zero, 128);
   p.agg_n128 = getenv("GNNUDS_AGG_N128") ? atoi(getenv("GNNUDS_AGG_N128")) : 1;
   const uint32_t sc_bytes = ((uint32_t)E + 3u * RP) * 4u + ((uint32_t)R + 1u + (uint32_t)p.nnz * (gat ? 1u : 2u)) * 4u;
-  SpAggTP pt{};
   pt.off_wa = al(p.off_sc + sc_bytes, 128);                                  // T: the two score operand images
   pt.off_dump = pt.off_wa + (T && gat ? (uint32_t)(Ktot / 8) * 128u : 0u);
   p.off_bar = T ? al(pt.off_dump + 256u, 16) : al(p.off_sc + sc_bytes, 16);
   // operand views of an M tile read 128 rows from the tile's first row of every panel / swizzle chunk: keep those
   // reads inside the allocation
-  uint32_t reach = p.off_bar + 17u * 8u + 16u;
-  reach = std::max(reach, p.off_self + (uint32_t)(p.nb_self - 1) * p.self_stride + (uint32_t)(p.Kself / 64 - 1) * p.chunk_bytes + RP * 128u);
+  uint32_t reach = p.off_bar + 18u * 8u + 16u;
+  reach = std::max(reach, p.off_self + (uint32_t)(T ? 0 : p.nb_self - 1) * p.self_stride + (uint32_t)(p.Kself / 64 - 1) * p.chunk_bytes + RP * 128u);
   reach = std::max(reach, p.off_nx + (uint32_t)(F / 8 - 1) * p.pstrideP + RP * 16u);
   reach = std::max(reach, p.off_al + (uint32_t)(p.KpJ / 8 - 1) * p.pstrideAl + RP * 16u);
   reach = std::max(reach, p.off_m + (uint32_t)(p.Kp / 8 - 1) * p.pstrideM + RP * 16u);

@@ -80,6 +80,12 @@ __device__ __forceinline__ void cp_async_arrive(uint64_t* bar) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc::smem_u32(bar)) : "memory");
 }
+// One arrival per WARP instead of 32 arrivals on the same barrier word.  The lanes' own fences (tcgen05 / async proxy)
+// come before; __syncwarp orders their writes before lane 0's release.
+__device__ __forceinline__ void mbar_arrive_warp(uint64_t* bar, int lane) {
+  __syncwarp();
+  if (lane == 0) mbar_arrive(bar);
+}
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_WARPS * 32) : "memory"); }
 
 // activation over a register tile; the branch is warp-uniform and sits outside the element loop
