@@ -14,6 +14,7 @@
 #include "fused_tp.cuh"
 #include "gru_tc.cuh"
 #include "nn_cat.cuh"
+#include "backward.cuh"
 
 #include <algorithm>
 #include <array>
@@ -44,6 +45,24 @@ struct SpatialW {
 };
 
 struct TensorDesc { int64_t numel; int d0, d1, d2; int last() const { return d2 ? d2 : (d1 ? d1 : d0); } };
+
+// Activation tape of one fp32 forward chunk, kept for the reverse pass (csrc/backward.cuh, backward_host.inc): with the
+// tape on, every layer whose output the backward needs (post-activation values for act', h = x@W of the GAT / GCN
+// aggregations) writes into its own slice of a bump-allocated arena instead of the ping-pong workspace buffers.
+struct SpTape { float *XE, *EX, *HBx, *HBe, *xo, *eo; };
+struct Tape {
+  bool on = false;
+  float* base = nullptr; size_t cap = 0, used = 0;     // floats
+  SpTape sp[2][16];
+  float* tp[2][2][8];                                  // [block][0 node / 1 edge][layer] Conv1D outputs
+  float *resx = nullptr, *rese = nullptr;              // activated resnet outputs (the heads' input)
+  float* flood[8];
+  float* alloc(size_t n) {
+    n = (n + 63) / 64 * 64;
+    if (!on || used + n > cap) return nullptr;
+    float* p = base + used; used += n; return p;
+  }
+};
 
 }  // namespace
 
@@ -160,7 +179,10 @@ struct gnnuds_handle {
   // grow-only device buffers of the autoregressive / MPC entry points (no cudaMalloc on the hot path once warm):
   // 0..3 rollout horizon b / a / y / ey, 4..10 objective (weights x3, gamma, y, q0, obj), 11..17 evaluate
   // (x0, ex0, b, dec, partial sums, prev_q, obj)
-  float* gb[24] = {nullptr}; size_t gb_cap[24] = {0};   // 18..21 replay (raw states, perfs, edge states, settings)
+  float* gb[48] = {nullptr}; size_t gb_cap[48] = {0};   // 18..21 replay (raw states, perfs, edge states, settings)
+
+  Tape tape;                            // reverse pass (gnnuds_predict_vjp / gnnuds_grad_settings)
+  float* bw_arena = nullptr; size_t bw_cap = 0;
 
   // live streams for debug_fetch
   const float* dbg_ptr[2] = {nullptr, nullptr};
@@ -522,7 +544,7 @@ int act_code(const gnnuds_config& c) { return c.activation; }
 // ---- temporal stack (emulator.py:154-163) ------------------------------------------------
 // in: (Bc,Ts,Nn,cin) at `src`; result (Bc,Td,Nn,H) in *dst (one of t0/t1).
 int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src, int cin, long long Bc, int Nn,
-                 int Ts, int Td, float* t0, float* t1, float** dst) {
+                 int Ts, int Td, float* t0, float* t1, float** dst, float** tape_slots = nullptr) {
   const auto& c = h->c;
   const int H = c.hidden, P = c.n_tp_layer;
   const float* cur = src.p;
@@ -532,6 +554,10 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src
     const bool last = (i == P - 1);
     const int Tdst = last ? Td : Ts;
     float* o = bufs[i & 1];
+    if (h->tape.on && tape_slots) {
+      tape_slots[i] = o = h->tape.alloc((size_t)Bc * Tdst * Nn * H);
+      if (!o) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (temporal layer)");
+    }
     int rc;
     if (c.recurrent == GNNUDS_REC_CONV1D) {
       std::vector<SegH> segs;
@@ -589,22 +615,30 @@ int run_spatial(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) {
   for (int l = 0; l < c.n_sp_layer; ++l) {
     const SpatialW& w = h->sp[blk][l];
     int rc;
+    float *XE = h->XE, *EX = h->EX, *HBx = h->HB, *HBe = h->HB;
+    float* xo = (l & 1) ? h->XB : h->XA;
+    float* eo = (l & 1) ? h->EB : h->EA;
+    if (h->tape.on) {            // reverse pass: these outputs stay alive on the tape
+      SpTape& tp = h->tape.sp[blk][l];
+      tp.XE = XE = h->tape.alloc((size_t)S * M * E2); tp.EX = EX = h->tape.alloc((size_t)S * N * E2);
+      tp.HBx = HBx = h->tape.alloc((size_t)S * N * E); tp.HBe = HBe = h->tape.alloc((size_t)S * M * E);
+      tp.xo = xo = h->tape.alloc((size_t)S * N * E); tp.eo = eo = h->tape.alloc((size_t)S * M * E);
+      if (!XE || !EX || !HBx || !HBe || !xo || !eo) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (spatial layer)");
+    }
     // x_e = Dense(E/2)(e) ; e_x = Dense(E/2)(x)
-    if ((rc = launch_gemm(h, st.e, W(h, w.xe.t[0]), W(h, w.xe.t[1]), h->XE, E2, E2, act, Bc, M, T, T, M, 0))) return rc;
-    if ((rc = launch_gemm(h, st.x, W(h, w.ex.t[0]), W(h, w.ex.t[1]), h->EX, E2, E2, act, Bc, N, T, T, N, 0))) return rc;
+    if ((rc = launch_gemm(h, st.e, W(h, w.xe.t[0]), W(h, w.xe.t[1]), XE, E2, E2, act, Bc, M, T, T, M, 0))) return rc;
+    if ((rc = launch_gemm(h, st.x, W(h, w.ex.t[0]), W(h, w.ex.t[1]), EX, E2, E2, act, Bc, N, T, T, N, 0))) return rc;
     // NodeEdge both directions
     const int li = blk * c.n_sp_layer + l;
-    if ((rc = launch_nodeedge(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, h->XE, h->NX, S, M, N, E2))) return rc;
-    if ((rc = launch_nodeedge(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, h->EX, h->NE, S, N, M, E2))) return rc;
+    if ((rc = launch_nodeedge(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, XE, h->NX, S, M, N, E2))) return rc;
+    if ((rc = launch_nodeedge(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, EX, h->NE, S, N, M, E2))) return rc;
     // conv on [x | NodeEdge(x_e)]
     std::vector<SegH> sx = st.x; sx.push_back({h->NX, E2, E2, 0, N, 0});
     std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
-    float* xo = (l & 1) ? h->XB : h->XA;
-    float* eo = (l & 1) ? h->EB : h->EA;
-    if ((rc = launch_gemm(h, sx, W(h, w.conv_x.t[0]), nullptr, h->HB, E, E, ACT_LINEAR, Bc, N, T, T, N, 0))) return rc;
-    if ((rc = launch_agg(h, h->HB, xo, h->d_rp, h->d_ci, h->d_val, w.conv_x, S, N, act, blk == 1))) return rc;
-    if ((rc = launch_gemm(h, se, W(h, w.conv_e.t[0]), nullptr, h->HB, E, E, ACT_LINEAR, Bc, M, T, T, M, 0))) return rc;
-    if ((rc = launch_agg(h, h->HB, eo, h->d_erp, h->d_eci, h->d_eval, w.conv_e, S, M, act))) return rc;
+    if ((rc = launch_gemm(h, sx, W(h, w.conv_x.t[0]), nullptr, HBx, E, E, ACT_LINEAR, Bc, N, T, T, N, 0))) return rc;
+    if ((rc = launch_agg(h, HBx, xo, h->d_rp, h->d_ci, h->d_val, w.conv_x, S, N, act, blk == 1))) return rc;
+    if ((rc = launch_gemm(h, se, W(h, w.conv_e.t[0]), nullptr, HBe, E, E, ACT_LINEAR, Bc, M, T, T, M, 0))) return rc;
+    if ((rc = launch_agg(h, HBe, eo, h->d_erp, h->d_eci, h->d_eval, w.conv_e, S, M, act))) return rc;
     st.x = {{xo, E, E, 0, N, 0}};
     st.e = {{eo, E, E, 0, M, 0}};
     if (h->debug_stop == (blk ? 40 : 20) + l) return 1;
@@ -695,8 +729,8 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
   if (h->debug_stop == 2) return 0;
   // ---- temporal block 1 (keeps the last To steps, emulator.py:249,256) ----
   float *xt = nullptr, *et = nullptr;
-  if ((rc = run_temporal(h, h->tpx[0], st.x[0], E, Bc, N, Ti, To, h->TX0, h->TX1, &xt))) return rc;
-  if ((rc = run_temporal(h, h->tpe[0], st.e[0], E, Bc, M, Ti, To, h->TE0, h->TE1, &et))) return rc;
+  if ((rc = run_temporal(h, h->tpx[0], st.x[0], E, Bc, N, Ti, To, h->TX0, h->TX1, &xt, h->tape.tp[0][0]))) return rc;
+  if ((rc = run_temporal(h, h->tpe[0], st.e[0], E, Bc, M, Ti, To, h->TE0, h->TE1, &et, h->tape.tp[0][1]))) return rc;
   // ---- boundary / control concat (emulator.py:260-262) ----
   st.x = {{xt, H, H, 0, N, 0}, {h->BEMB, E2, E2, 0, N, 0}};
   st.e = {{et, H, H, 0, M, 0}};
@@ -710,40 +744,49 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
   if (rc) return rc;
   if (h->debug_stop == 4) return 0;
   // ---- temporal block 2 ----
-  if ((rc = run_temporal(h, h->tpx[1], st.x[0], E, Bc, N, To, To, h->TX0, h->TX1, &xt))) return rc;
-  if ((rc = run_temporal(h, h->tpe[1], st.e[0], E, Bc, M, To, To, h->TE0, h->TE1, &et))) return rc;
+  if ((rc = run_temporal(h, h->tpx[1], st.x[0], E, Bc, N, To, To, h->TX0, h->TX1, &xt, h->tape.tp[1][0]))) return rc;
+  if ((rc = run_temporal(h, h->tpe[1], st.e[0], E, Bc, M, To, To, h->TE0, h->TE1, &et, h->tape.tp[1][1]))) return rc;
   st.x = {{xt, H, H, 0, N, 0}};
   st.e = {{et, H, H, 0, M, 0}};
   set_dbg(h, st, Bc * To * N, Bc * To * M);
   if (h->debug_stop == 5) return 0;
   // ---- K8 resnet + heads (emulator.py:312-338) ----
   const int ract = c.resnet ? ACT_LINEAR : act;
-  if ((rc = launch_gemm(h, st.x, W(h, h->resx.t[0]), W(h, h->resx.t[1]), h->XA, E, E, ract, Bc, N, To, To, N, 0))) return rc;
-  if ((rc = launch_gemm(h, st.e, W(h, h->rese.t[0]), W(h, h->rese.t[1]), h->EA, E, E, ract, Bc, M, To, To, M, 0))) return rc;
+  float *XAo = h->XA, *EAo = h->EA;
+  if (h->tape.on) {
+    h->tape.resx = XAo = h->tape.alloc((size_t)Bc * To * N * E); h->tape.rese = EAo = h->tape.alloc((size_t)Bc * To * M * E);
+    if (!XAo || !EAo) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (resnet)");
+  }
+  if ((rc = launch_gemm(h, st.x, W(h, h->resx.t[0]), W(h, h->resx.t[1]), XAo, E, E, ract, Bc, N, To, To, N, 0))) return rc;
+  if ((rc = launch_gemm(h, st.e, W(h, h->rese.t[0]), W(h, h->rese.t[1]), EAo, E, E, ract, Bc, M, To, To, M, 0))) return rc;
   if (c.resnet) {
-    cumsum_res_act_kernel<float><<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(h->XA, h->RES, Bc, To, N, E, act);
-    cumsum_res_act_kernel<float><<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(h->EA, h->RESE, Bc, To, M, E, act);
+    cumsum_res_act_kernel<float><<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(XAo, h->RES, Bc, To, N, E, act);
+    cumsum_res_act_kernel<float><<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(EAo, h->RESE, Bc, To, M, E, act);
     h->launches += 2;
     CU(cudaGetLastError());
   }
-  st.x = {{h->XA, E, E, 0, N, 0}};
-  st.e = {{h->EA, E, E, 0, M, 0}};
+  st.x = {{XAo, E, E, 0, N, 0}};
+  st.e = {{EAo, E, E, 0, M, 0}};
   set_dbg(h, st, Bc * To * N, Bc * To * M);
   if (h->debug_stop == 6) return 0;
   const long long RXo = Bc * To * N, REo = Bc * To * M;
   const int ldn = h->ldn();
-  if ((rc = launch_head(h, h->XA, E, E, h->head_out, h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID, RXo))) return rc;
+  if ((rc = launch_head(h, XAo, E, E, h->head_out, h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID, RXo))) return rc;
   if (c.if_flood) {
     std::vector<SegH> cur = st.x;
     float* bufs[2] = {h->EX, h->NX};
     for (int i = 0; i < c.if_flood; ++i) {
-      if ((rc = launch_gemm(h, cur, W(h, h->flood_chain[i].t[0]), W(h, h->flood_chain[i].t[1]), bufs[i & 1], E2, E2, act, Bc, N,
+      float* fo = bufs[i & 1];
+      if (h->tape.on) {
+        if (i >= 8 || !(h->tape.flood[i] = fo = h->tape.alloc((size_t)RXo * E2))) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (flood chain)");
+      }
+      if ((rc = launch_gemm(h, cur, W(h, h->flood_chain[i].t[0]), W(h, h->flood_chain[i].t[1]), fo, E2, E2, act, Bc, N,
                             To, To, N, 0))) return rc;
-      cur = {{bufs[i & 1], E2, E2, 0, N, 0}};
+      cur = {{fo, E2, E2, 0, N, 0}};
     }
     if ((rc = launch_head(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return rc;
   }
-  if ((rc = launch_head(h, h->EA, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
+  if ((rc = launch_head(h, EAo, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
   return run_postproc(h, x, b, a, Bc, y, ey, normalised_io);
 }
 
@@ -2068,6 +2111,7 @@ int gnnuds_destroy(gnnuds_handle* h) {
   for (int s = 0; s < 2; ++s) for (uint8_t* p : h->d_wa[s]) if (p) cudaFree(p);
   for (int k = 0; k < 2; ++k) { if (h->pin_in[k]) cudaFreeHost(h->pin_in[k]); if (h->pin_out[k]) cudaFreeHost(h->pin_out[k]); }
   for (float* q : h->gb) if (q) cudaFree(q);
+  if (h->bw_arena) cudaFree(h->bw_arena);
   for (auto& e : h->gemm_ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (h->ev_a) cudaEventDestroy(h->ev_a);
   if (h->ev_b) cudaEventDestroy(h->ev_b);
@@ -3109,3 +3153,5 @@ extern "C" int gnnuds_objective_static(gnnuds_handle* h, const float* y, const f
   if (e != cudaSuccess) return fail(h, GNNUDS_E_CUDA, "objective_static: %s", cudaGetErrorString(e));
   return 0;
 }
+
+#include "backward_host.inc"

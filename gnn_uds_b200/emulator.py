@@ -509,6 +509,53 @@ class Emulator:
                                                        _ptr(gm), _ptr(obj), _lib.MEM_HOST))
         return obj
 
+    def predict_vjp(self, states, b, a, edge_state, gy, gey, wrt=("a", "x", "ex")):
+        """Vector-Jacobian product of ``predict_tf`` (what ``tf.GradientTape`` evaluates in mpc.py:596-607): cotangents
+        gy (B,seq_out,N,ny) / gey (B,seq_out,M,e_out) of the two outputs -> dict with the forward results ``y``, ``ey``
+        and the cotangents ``ga`` (B,seq_out,n_act), ``gx`` (B,seq_in,N,n_in), ``gex`` (B,seq_in,M,e_in) asked for in
+        ``wrt``.  fp32 handles, conv models with Conv1D temporal nets (gnnuds_predict_vjp)."""
+        x = _f32(np.asarray(states)[:, -self.seq_in:])
+        ex = _f32(np.asarray(edge_state)[:, -self.seq_in:])
+        b = _f32(b)
+        a = _f32(a) if a is not None else None
+        B = x.shape[0]
+        gy, gey = _f32(gy), _f32(gey)
+        ny = self.y_channels
+        if gy.shape != (B, self.seq_out, self.n_node, ny) or gey.shape != (B, self.seq_out, self.n_edge, self.e_out):
+            raise ValueError("cotangent shapes %s / %s do not match the outputs" % (gy.shape, gey.shape))
+        out = {"y": np.empty(gy.shape, np.float32), "ey": np.empty(gey.shape, np.float32)}
+        if "a" in wrt and self.act:
+            out["ga"] = np.empty((B, self.seq_out, self.n_act), np.float32)
+        if "x" in wrt:
+            out["gx"] = np.empty(x.shape, np.float32)
+        if "ex" in wrt:
+            out["gex"] = np.empty(ex.shape, np.float32)
+        _lib.check(self._h, self._lib.gnnuds_predict_vjp(self._h, _ptr(x), _ptr(b), _ptr(a), _ptr(ex), B, _ptr(gy), _ptr(gey),
+                                                         _ptr(out["y"]), _ptr(out["ey"]), _ptr(out.get("ga")), _ptr(out.get("gx")),
+                                                         _ptr(out.get("gex")), _lib.MEM_HOST))
+        return out
+
+    def grad_settings(self, states, b, a, edge_state, flood_w, wwtp_w, rough_w=None, gamma=None, rule="mpc"):
+        """``mpc_problem_gr.gradient_fn`` (mpc.py:596-607) for the astlingen objective: (obj (B,), d obj / d a
+        (B,T,n_act)) with T = b.shape[1] a multiple of seq_out - one ``predict_tf`` or the autoregressive chunk loop
+        (mpc.py:565-582) differentiated end to end on the device (gnnuds_grad_settings)."""
+        code = {"mpc": _lib.ROLL_MPC, "mbrl": _lib.ROLL_MBRL}[rule]
+        x = _f32(np.asarray(states)[:, -self.seq_in:])
+        ex = _f32(np.asarray(edge_state)[:, -self.seq_in:])
+        b, a = _f32(b), _f32(a)
+        B, T = b.shape[0], b.shape[1]
+        if T % self.seq_out or a.shape != (B, T, self.n_act):
+            raise ValueError("runoff %s / settings %s do not cover whole chunks of %d steps" % (b.shape, a.shape, self.seq_out))
+        fw, ww = _f32(flood_w), _f32(wwtp_w)
+        rw = None if rough_w is None else _f32(rough_w)
+        gm = None if gamma is None else _f32(gamma)
+        if gm is not None and gm.shape != (T,):
+            raise ValueError("gamma must have one entry per horizon step")
+        obj, ga = np.empty(B, np.float32), np.empty(a.shape, np.float32)
+        _lib.check(self._h, self._lib.gnnuds_grad_settings(self._h, code, _ptr(x), _ptr(b), _ptr(a), _ptr(ex), B, T // self.seq_out,
+                                                           _ptr(fw), _ptr(ww), _ptr(rw), _ptr(gm), _ptr(obj), _ptr(ga), _lib.MEM_HOST))
+        return obj, ga
+
     def evaluate(self, state, runoff, edge_state, dec, r_step, horizon, flood_w, wwtp_w, rough_w=None, gamma=None,
                  rule="mpc", obj_ptr=None):
         """MPC population evaluation in one device-resident call (gnnuds_evaluate): ONE observed state

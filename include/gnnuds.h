@@ -204,6 +204,34 @@ int gnnuds_evaluate(gnnuds_handle* h, int32_t rule, const float* x0, const float
                     const float* wwtp_w, const float* rough_w, const float* gamma, float* obj, int32_t where,
                     int32_t obj_where);
 
+/* Reverse pass of predict_tf w.r.t. its INPUTS (no weight gradients): the vector-Jacobian product that
+ * tf.GradientTape evaluates in mpc_problem_gr (mpc.py:511-627: gradient_fn :596-607, pred_fit :512-548 differentiate
+ * objective_pred_tf(predict_tf(state, runoff, settings, edge_state)) w.r.t. the settings).  x, b, a, ex as for
+ * gnnuds_predict; gy (B,seq_out,n_node,y_channels) / gey (B,seq_out,n_edge,e_out) are the cotangents of the two outputs.
+ * Written: y / ey (the forward results, NULL = not wanted), ga (B,seq_out,n_act), gx (B,seq_in,n_node,n_in),
+ * gex (B,seq_in,n_edge,e_in) - each may be NULL.  The forward runs with post_proc_tf (variant 1) and keeps its
+ * activations on a tape (grow-only arena of the handle); sub-gradients as TensorFlow defines them (relu'(0) = 0,
+ * clip_by_value passes the gradient on the closed interval, comparisons carry none).  The flood-flag input channel and
+ * thresholds (flood prob > 0.5, epsilon mask) are treated as constants, as GradientTape does.
+ * Supported: conv models (GCN / GAT), graph_base 0, Conv1D temporal nets, fp32 handles, pump-free / offset-free networks
+ * without use_adj; anything else returns GNNUDS_E_INVALID. */
+int gnnuds_predict_vjp(gnnuds_handle* h, const float* x, const float* b, const float* a, const float* ex, int64_t B,
+                       const float* gy, const float* gey, float* y, float* ey, float* ga, float* gx, float* gex,
+                       int32_t where);
+
+/* mpc_problem_gr.gradient_fn (mpc.py:596-607) for the astlingen objective (envs/scenario/astlingen.py:75-99):
+ * obj (B) and grad_a (B, n_chunks*seq_out, n_act) = d obj_i / d a_i for every candidate i.  n_chunks == 1 is one
+ * predict_tf; n_chunks > 1 differentiates through the autoregressive chunk loop (mpc.py:565-582, feedback `rule`
+ * GNNUDS_ROLL_MPC or GNNUDS_ROLL_MBRL): the forward sweep keeps only every chunk's input state, the reverse sweep
+ * re-runs one chunk at a time with the tape on (checkpointing) and carries the state cotangents across the feedback
+ * (h, q_us, q_ds and the edge outputs; the setting written into the edge state's last channel feeds grad_a; the flood
+ * flag and the runoff carry no gradient).  x0 (B,seq_in,n_node,n_in), b (B,n_chunks*seq_out,n_node,b_in),
+ * a (B,n_chunks*seq_out,n_act), ex0 (B,seq_in,n_edge,e_in) live where `where` says; the weight vectors / gamma
+ * (n_chunks*seq_out) are HOST vectors as for gnnuds_objective. */
+int gnnuds_grad_settings(gnnuds_handle* h, int32_t rule, const float* x0, const float* b, const float* a,
+                         const float* ex0, int64_t B, int32_t n_chunks, const float* flood_w, const float* wwtp_w,
+                         const float* rough_w, const float* gamma, float* obj, float* grad_a, int32_t where);
+
 /* Event replay (main.py:306-382 test loop, dataloader.py:93-95 expand_seq): one rainfall event of T recorded steps -
  * states (T,N,4) = [h, cuminflow, outflow, lateral inflow], perfs (T,N) cumflooding (if_flood models, else NULL),
  * edge_states (T,M,4), settings (T,n_act) (act models, else NULL) - is uploaded ONCE and its T - seq_out teacher-forced

@@ -41,6 +41,11 @@ CASES = {
     "ast_gcn_conv_eps0": dict(net="astlingen", conv="GCN", recurrent="Conv1D", resnet=True, seq_in=8, seq_out=4,
                               embed_size=128, hidden_dim=64, n_sp_layer=2, n_tp_layer=3, length=501, order=1,
                               edge_fusion=True, if_flood=2, epsilon=0.0, tide=True, B=2, seed=48),
+    # reverse-pass coverage (tests/test_grad_gpu.py): GCN + Conv1D, act WITHOUT edge fusion (node-head flows times
+    # a_in / a_out, emulator.py:708-715), no flood head, no resnet, seq_in == seq_out for the chunked roll
+    "ast_gcn_conv_act_nofusion": dict(net="astlingen", conv="GCN", recurrent="Conv1D", resnet=False, seq_in=4, seq_out=4,
+                                      embed_size=64, hidden_dim=64, n_sp_layer=2, n_tp_layer=2, length=0, order=1,
+                                      act="conti", if_flood=1, B=3, seed=60),
     # graph_base=1: one conv over the joint node+edge graph (emulator.py:220-223); needs act so that both
     # streams enter block 2 with H+E/2 channels.  C5 is this architecture on a 100k-node tree.
     "ast_joint_gcn_gru_act": dict(net="astlingen", conv="GCN", recurrent="GRU", resnet=True, seq_in=6, seq_out=6,

@@ -1,0 +1,106 @@
+"""GPU tests of the reverse pass (gnnuds_predict_vjp / gnnuds_grad_settings; mpc.py:511-627): the hand-written VJP
+kernels against the gradient oracle (torch fp64 autograd, oracle/grad_oracle.py, itself pinned against finite
+differences of the NumPy oracle in tests/test_grad_oracle.py).  Tolerance: 1e-4 of the largest gradient entry (fp32
+forward + fp32 VJP against fp64), written below."""
+import numpy as np
+import pytest
+
+import cases
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4
+
+
+def _weights(T):
+    from gnn_uds_b200 import mpc
+    net, _ = cases.load_net("astlingen")
+    fw, ww, rw = mpc.target_weights(list(net.nodes))
+    return fw, ww, rw, (0.9 ** np.arange(T)).astype(np.float32)
+
+
+def _inputs(em, o, B, chunks, seed):
+    from gnn_uds_b200 import synthetic
+    rng = np.random.default_rng(seed)
+    states, b, a, ex = synthetic.make_inputs(em, B, rng, horizon=em.seq_out * chunks)
+    a = rng.uniform(0.15, 0.95, a.shape).astype(np.float32)
+    return states, b, a, ex
+
+
+def _rel(got, ref):
+    return np.abs(got - ref).max() / max(np.abs(ref).max(), 1e-12)
+
+
+@pytest.mark.parametrize("case,chunks", [("c3_ast_act_5", 1), ("c3_ast_act_5", 3), ("ast_gcn_conv_act_nofusion", 1),
+                                         ("ast_gcn_conv_act_nofusion", 2)])
+def test_grad_settings_matches_autograd(case, chunks):
+    from oracle import grad_oracle as go
+    em, _ = cases.setup_product(case)
+    o, _ = cases.make_oracle(case, np.float64)
+    states, b, a, ex = _inputs(em, o, 5, chunks, 31)
+    fw, ww, rw, gm = _weights(em.seq_out * chunks)
+    obj, ga = em.grad_settings(states, b, a, ex, fw, ww, rw, gm)
+    ref_obj, ref_ga = go.grad_settings(o, states.astype(np.float64), b.astype(np.float64), a.astype(np.float64),
+                                       ex.astype(np.float64), fw, ww, rw, gm, chunks=chunks)
+    assert np.abs(ref_ga).max() > 1e-6
+    print("%s chunks=%d: obj rel %.2e, grad rel %.2e (|grad| max %.3g)" % (case, chunks, _rel(obj, ref_obj), _rel(ga, ref_ga),
+                                                                          np.abs(ref_ga).max()))
+    assert np.allclose(obj, ref_obj, rtol=2e-4, atol=2e-4)
+    assert _rel(ga, ref_ga) <= TOL
+    # the objective returned with the gradient is the one the forward-only entry points return
+    if chunks == 1:
+        y, _ = em.predict_tf(states, b, a, ex)
+    else:
+        y, _ = em.rollout(states, b, a, ex, rule="mpc")
+    assert np.array_equal(obj, em.objective(y, states, fw, ww, rw, gm))
+
+
+@pytest.mark.parametrize("case", ["c3_ast_act_5", "ast_gcn_conv_eps0", "c2_shq_gat_conv_10", "ast_gcn_conv_act_nofusion"])
+def test_predict_vjp_matches_autograd(case):
+    """Random cotangents on every output channel; gradients w.r.t. settings, states and edge states."""
+    from oracle import grad_oracle as go
+    em, inp = cases.setup_product(case)
+    o, _ = cases.make_oracle(case, np.float64)
+    states, b, a, ex = [None if v is None else np.asarray(v)[:2] for v in inp]
+    rng = np.random.default_rng(7)
+    y0, ey0 = em.predict_tf(states, b, a, ex)
+    gy = rng.normal(size=y0.shape).astype(np.float32)
+    gey = rng.normal(size=ey0.shape).astype(np.float32)
+    out = em.predict_vjp(states, b, a, ex, gy, gey)
+    f64 = lambda v: None if v is None else np.asarray(v, np.float64)
+    if a is not None:
+        ry, rey, rga, rgx, rgex = go.predict_vjp(o, f64(states), f64(b), f64(a), f64(ex), f64(gy), f64(gey))
+    else:
+        ry, rey, rga, rgx, rgex = _vjp_no_act(go, o, f64(states), f64(b), f64(ex), f64(gy), f64(gey))
+    assert np.array_equal(out["y"], y0) and np.array_equal(out["ey"], ey0)
+    msg = "%s: gx rel %.2e, gex rel %.2e" % (case, _rel(out["gx"], rgx), _rel(out["gex"], rgex))
+    if a is not None:
+        msg += ", ga rel %.2e" % _rel(out["ga"], rga)
+        assert _rel(out["ga"], rga) <= TOL
+    print(msg)
+    assert _rel(out["gx"], rgx) <= TOL
+    assert _rel(out["gex"], rgex) <= TOL
+
+
+def _vjp_no_act(go, o, states, b, ex, gy, gey):
+    import torch
+    te = go.TorchEmulator(o)
+    st = torch.as_tensor(states).clone().requires_grad_(True)
+    et = torch.as_tensor(ex).clone().requires_grad_(True)
+    y, ey = te.predict_tf(st, b, None, et)
+    ((y * torch.as_tensor(gy)).sum() + (ey * torch.as_tensor(gey)).sum()).backward()
+    return y.detach().numpy(), ey.detach().numpy(), None, st.grad.numpy(), et.grad.numpy()
+
+
+def test_reverse_pass_rejects_unsupported():
+    from gnn_uds_b200._lib import GnnUdsError
+    em, inp = cases.setup_product("c1_ast_gcn_gru")              # GRU temporal net
+    states, b, a, ex = inp
+    y, ey = em.predict(states, b, a, ex)
+    with pytest.raises(GnnUdsError):
+        em.predict_vjp(states, b, a, ex, np.ones_like(y), np.ones_like(ey))
+    em2, inp2 = cases.setup_product("c3_ast_act_5", precision="bf16")
+    s2, b2, a2, e2 = inp2
+    fw, ww, rw, gm = _weights(em2.seq_out)
+    with pytest.raises(GnnUdsError):
+        em2.grad_settings(s2, b2, a2, e2, fw, ww, rw, gm)
