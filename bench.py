@@ -342,6 +342,75 @@ def run_mpc(a):
         dist.destroy_process_group()
 
 
+def run_grad(a):
+    """--workload C3grad: the gradient MPC's inner call (mpc.py:596-607 gradient_fn) on BASELINE.json configs[2]'s model -
+    `--batch` decision vectors (default 256) x 60-step horizon = 12 autoregressive chunks of the astlingen 5->5 model,
+    objective AND d objective / d decisions through MpcEvaluator.gradient (gnnuds_grad_settings: forward sweep, taped
+    re-forward and VJP kernels per chunk, fp32).  One GPU; `cpu_baseline` = the gradient oracle (torch fp64 autograd
+    through the dense restatement) on a few candidates."""
+    import torch
+    from gnn_uds_b200 import configs, synthetic, mpc
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    torch.cuda.set_device(local)
+    em, args, rng = configs.make_emulator("C3b", device=local, precision="fp32")
+    net, _ = configs.load_net("astlingen")
+    pop = a.batch or 256
+    chunks = configs.WORKLOADS["C3b"]["chunks"]
+    T = em.seq_out * chunks
+    ev = mpc.MpcEvaluator(em, net.nodes, interval=1, eval_horizon=T, control_horizon=T, setting_duration=5,
+                          gamma=0.99 ** np.arange(T))
+    rng = np.random.default_rng(args.seed)
+    states, b, _, ex = synthetic.make_inputs(em, 1, rng, horizon=T)
+    ev.load_state(states[0], b[0], ex[0])
+    y = mpc.latin_hypercube(pop, np.full(ev.n_var, 0.05), np.ones(ev.n_var), rng)
+    for _ in range(max(a.warmup, 3)):
+        objs, g = ev.gradient(y)
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = em.launch_count()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        objs, g = ev.gradient(y)
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    launches = em.launch_count() - l0
+    clocks = sampler.stop()
+    fwd_ms = []
+    for _ in range(3):
+        t1 = time.perf_counter(); ev.pred_emu(y); fwd_ms.append((time.perf_counter() - t1) * 1e3)
+    units = pop * T * em.n_node
+    ms = wall / a.steps * 1e3
+    # CPU arm: the gradient oracle on a few candidates
+    from oracle.emulator_oracle import OracleEmulator
+    from oracle import grad_oracle as go
+    o = OracleEmulator(args.conv, args.resnet, args.recurrent, args, dtype=np.float64)
+    o.set_weights(em.weights)
+    o.set_norm(em.norm_x, em.norm_b, em.norm_y, em.norm_r, em.norm_e)
+    nc = 4
+    sett = ev.expand_settings(y[:nc]).astype(np.float64)
+    st = np.repeat(states.astype(np.float64), nc, 0); bb = np.repeat(b.astype(np.float64), nc, 0); ee = np.repeat(ex.astype(np.float64), nc, 0)
+    gm = 0.99 ** np.arange(T)
+    t1 = time.perf_counter()
+    ro, rga = go.grad_settings(o, st, bb, sett, ee, ev.fw, ev.ww, ev.rw, gm, chunks=chunks)
+    cpu_s = time.perf_counter() - t1
+    rel = float(np.abs(ev.collapse_settings_grad(rga) - g[:nc]).max() / max(np.abs(rga).max(), 1e-12))
+    emit({"metric": METRIC.replace("shunqing GAT rollout", "astlingen gradient MPC: objective + d/d settings"), "value": units / (ms * 1e-3),
+          "unit": UNIT, "n_gpus": 1, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms, "higher_is_better": True,
+          "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+          "config": {"workload": "C3grad: astlingen GAT+Conv1D act+edge_fusion+resnet+flood 5->5, %d decision vectors x %d-step horizon (%d AR "
+                                 "chunks, MPC feedback), objective and its gradient w.r.t. the %d decisions of every vector" % (pop, T, chunks, ev.n_var),
+                     "l2": "tape of a chunk: %.0f MB (%s the 126 MB L2)" % (pop * 4 * 13.0 * 5 * 59 * 128 / 1e6, "exceeds" if pop * 4 * 13.0 * 5 * 59 * 128 > 126e6 else "fits"), "precision": "fp32"},
+          "e2e": {"value": units / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(pop * T * (em.n_act + em.n_node) * 4),
+                  "d2h_bytes_per_step": int(pop * (T * em.n_act + 1) * 4), "note": "MpcEvaluator.gradient(y) wall clock, NumPy in / NumPy out"},
+          "gpu_launches": int(launches), "clocks": clocks, "forward_only_ms": float(np.median(fwd_ms)),
+          "grad_rel_err_vs_oracle": rel,
+          "cpu_baseline": {"value": nc * T * em.n_node / cpu_s, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+                           "sample": "gradient oracle (torch fp64 autograd, dense formulation) on %d decision vectors, same horizon" % nc}})
+
+
 def run_c4(a):
     """--workload C4: BASELINE.json configs[3] - the C2 model replayed over all 148 shunqing events (lengths from
     events.csv, synthetic recorded series), whole events balanced over the ranks (strong scaling).  Mode A = the reference's
@@ -468,6 +537,8 @@ def main():
         return run_reference(a)
     if a.workload == "C3mpc":
         return run_mpc(a)
+    if a.workload == "C3grad":
+        return run_grad(a)
     if a.workload == "C4":
         return run_c4(a)
 

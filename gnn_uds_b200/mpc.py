@@ -127,6 +127,60 @@ class MpcEvaluator:
                 objs = objs.reshape(hi - lo, self.stochastic).mean(axis=1)
         return sharding.gather_objectives(objs, pop, device=em.device)
 
+    # ---- gradient MPC (mpc.py:511-627, mpc_problem_gr) ----
+    def collapse_settings_grad(self, ga):
+        """Transpose of ``expand_settings`` (mpc.py:211-218 / :550-557): d/d settings (pop, T, n_act) -> d/d y
+        (pop, n_step*n_act).  Every decision is held r_step steps and the last one to the end of the horizon, so its
+        gradient is the sum over the steps it is held."""
+        ga = np.asarray(ga, np.float64)
+        pop, T = ga.shape[0], ga.shape[1]
+        gy = np.zeros((pop, self.n_step, self.n_act))
+        for i in range(self.n_step):
+            lo = i * self.r_step
+            hi = T if i == self.n_step - 1 else min((i + 1) * self.r_step, T)
+            if lo < T:
+                gy[:, i] = ga[:, lo:hi].sum(axis=1)
+        return gy.reshape(pop, self.n_var)
+
+    def project(self, y, xl=0.0, xu=1.0, inverse=False):            # mpc.py:619-625
+        y = np.asarray(y, np.float64)
+        if inverse:
+            y = (y - xl) / (xu - xl)
+            return np.log(y / (1 - y + 1e-6))
+        return 1.0 / (1.0 + np.exp(-y)) * (xu - xl) + xl
+
+    def gradient(self, y, bounded=True, xl=0.0, xu=1.0):
+        """``gradient_fn`` (mpc.py:596-607): (objs (pop,), d obj / d y (pop, n_var)) for decision vectors y
+        (n_var,) or (pop, n_var); with ``bounded=False`` y lives in the unconstrained space of ``project``
+        (sigmoid, mpc.py:601-602).  The rollout, the objective and the whole reverse pass run in
+        ``gnnuds_grad_settings``; only the chain rule of the setting expansion / projection is done here."""
+        if self.stochastic:
+            raise NotImplementedError("gradient with stochastic runoff scenarios")
+        y = np.atleast_2d(np.asarray(y, np.float64))
+        yy = y if bounded else self.project(y, xl, xu)
+        sett = self.expand_settings(yy.astype(np.float32))
+        pop = sett.shape[0]
+        state = np.repeat(np.expand_dims(self.state, 0), pop, axis=0)
+        edge_state = np.repeat(np.expand_dims(self.edge_state, 0), pop, axis=0)
+        runoff = np.repeat(np.expand_dims(self.runoff, 0), pop, axis=0)
+        gamma = None if self.gamma is None else np.asarray(self.gamma, np.float32)
+        objs, ga = self.emul.grad_settings(state, runoff, sett, edge_state, self.fw, self.ww,
+                                           self.rw if self.rough else None, gamma)
+        gy = self.collapse_settings_grad(ga)
+        if not bounded:
+            sg = (yy - xl) / (xu - xl)
+            gy = gy * sg * (1 - sg) * (xu - xl)
+        return objs, gy
+
+    def hessp(self, y, p, eps=1e-3, **kw):
+        """``hessp_fn`` (mpc.py:609-617) by central differences of ``gradient`` along p (the reference differentiates the
+        gradient a second time with a nested tape; the rollout is piecewise linear in long stretches - relu,
+        clipped flows - so a difference quotient of the exact gradient is what a second tape returns up to O(eps^2))."""
+        y, p = np.asarray(y, np.float64), np.asarray(p, np.float64)
+        _, gp = self.gradient(y + eps * p, **kw)
+        _, gm = self.gradient(y - eps * p, **kw)
+        return ((gp - gm) / (2 * eps)).reshape(np.shape(y))
+
     def _evaluate(self, x, out, *args, **kwargs):                   # mpc.py:261-264
         out["F"] = self.pred_emu_device(x) + 1e-6
 

@@ -104,3 +104,38 @@ def test_reverse_pass_rejects_unsupported():
     fw, ww, rw, gm = _weights(em2.seq_out)
     with pytest.raises(GnnUdsError):
         em2.grad_settings(s2, b2, a2, e2, fw, ww, rw, gm)
+
+
+def test_mpc_evaluator_gradient():
+    """MpcEvaluator.gradient (mpc.py:596-607): decision vectors held 2 steps, 3 chunks of the 5->5 model, control horizon
+    shorter than the evaluation horizon (the last decision is held to the end) - against finite differences of the
+    evaluator's own objective in the bounded and the projected (sigmoid) parametrisation."""
+    from gnn_uds_b200 import mpc, synthetic
+    case = "c3_ast_act_5"
+    em, _ = cases.setup_product(case)
+    net, _ = cases.load_net("astlingen")
+    T = em.seq_out * 3
+    ev = mpc.MpcEvaluator(em, net.nodes, interval=1, eval_horizon=T, control_horizon=10, setting_duration=2,
+                          gamma=0.95 ** np.arange(T))
+    rng = np.random.default_rng(9)
+    states, b, _, ex = synthetic.make_inputs(em, 1, rng, horizon=T)
+    ev.load_state(states[0], b[0], ex[0])
+    y = rng.uniform(0.2, 0.9, (3, ev.n_var))
+    objs, g = ev.gradient(y)
+    assert g.shape == y.shape and np.allclose(objs, ev.pred_emu(y.astype(np.float32)), rtol=1e-5, atol=1e-6)
+    # directional derivative along a random direction, fp32 forward: a coarse step and a loose bound
+    d = rng.normal(size=y.shape)
+    eps = 2e-2
+    fp = ev.pred_emu((y + eps * d).astype(np.float32)).astype(np.float64)
+    fm = ev.pred_emu((y - eps * d).astype(np.float32)).astype(np.float64)
+    fd = (fp - fm) / (2 * eps)
+    an = (g * d).sum(axis=1)
+    print("directional derivative: analytic %s, finite differences %s" % (an, fd))
+    assert np.allclose(an, fd, rtol=5e-2, atol=5e-3)
+    # projected parametrisation: chain rule of the sigmoid
+    z = ev.project(y, inverse=True)
+    objs2, gz = ev.gradient(z, bounded=False)
+    yy = ev.project(z)
+    assert np.allclose(gz, ev.gradient(yy)[1] * yy * (1 - yy), rtol=1e-5, atol=1e-7)
+    hv = ev.hessp(y[0], d[0])
+    assert hv.shape == y[0].shape and np.all(np.isfinite(hv))

@@ -88,3 +88,19 @@ def test_gather_objectives_gloo_world2(n_total):
     want = np.arange(n_total, dtype=np.float32) * 0.5 + 1.0
     for r in range(2):
         assert np.array_equal(res[r], want)
+
+
+def test_collapse_settings_grad_is_transpose_of_expand():
+    """MpcEvaluator.collapse_settings_grad (gradient MPC, mpc.py:550-557): <expand(y), g> == <y, collapse(g)>."""
+    import numpy as np
+    from types import SimpleNamespace
+    from gnn_uds_b200 import mpc
+    em = SimpleNamespace(n_act=3)
+    for T, ch, sd in ((15, 10, 2), (10, 10, 5), (12, 12, 3), (7, 4, 2)):
+        ev = mpc.MpcEvaluator(em, ["a"], interval=1, eval_horizon=T, control_horizon=ch, setting_duration=sd, targets=())
+        rng = np.random.default_rng(T)
+        y = rng.normal(size=(4, ev.n_var))
+        g = rng.normal(size=(4, T, 3))
+        s = ev.expand_settings(y)[:, :T]
+        assert s.shape == (4, T, 3)
+        assert np.allclose((s * g).sum(), (y * ev.collapse_settings_grad(g)).sum(), rtol=1e-5)
