@@ -558,6 +558,48 @@ __global__ void __launch_bounds__(256) feedback_bwd_kernel(const float* __restri
   }
 }
 
+// ---------------------------------------------------------------------------
+// NN-cat ends (csrc/nn_cat.cuh).  VJP of nn_unflatten_kernel + the head activation: the per-node cotangents of a head
+// become the flattened row Gflat[r, n*nc + c] = g[(r*Nn+n), col0+c] * act'(out[...]) (zero in the padded columns).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) nn_flatten_bwd_kernel(const float* __restrict__ g, const float* __restrict__ out, int ldo, int col0,
+                                                             int act, float* __restrict__ gflat, int ldi, long long rows, int Nn, int nc) {
+  const long long total = rows * ldi;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / ldi;
+    const int j = (int)(i - r * ldi);
+    float v = 0.f;
+    if (j < Nn * nc) {
+      const int n = j / nc, c = j - n * nc;
+      const long long o = (r * Nn + n) * ldo + col0 + c;
+      v = g[o] * dact_from_out(out[o], act);
+    }
+    gflat[i] = v;
+  }
+}
+
+// VJP of nn_prep_kernel.  mode 0: gin[r, n, c] = gflat[r, n*K + c] / (max - min);  mode 2 (control row, K == 1):
+// ga[r, gather[n]] += gflat[r, n].
+__global__ void __launch_bounds__(256) nn_prep_bwd_kernel(const float* __restrict__ gflat, int Kp, const float* __restrict__ nmax,
+                                                          const float* __restrict__ nmin, int cn, const int* __restrict__ gather, int n_act,
+                                                          float* __restrict__ gin, long long rows, int Nn, int K, int mode) {
+  const int w = Nn * K;
+  const long long total = rows * w;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / w;
+    const int j = (int)(i - r * w);
+    const int n = j / K, c = j - n * K;
+    float v = gflat[r * Kp + j];
+    if (mode == 2) {
+      const int k = gather[n];
+      if (k >= 0) atomicAdd(gin + r * n_act + k, v);
+    } else {
+      if (nmax) v /= (nmax[n * cn + c] - nmin[n * cn + c]);
+      gin[i] = v;
+    }
+  }
+}
+
 // q0[b, n] = x[b, Ti-1, n, 1]: the last observed inflow, objective_pred_tf's q_in[:, 0] (astlingen.py:79)
 __global__ void __launch_bounds__(256) pick_q0_kernel(const float* __restrict__ x, float* __restrict__ q0, long long B, int Ti, int N, int n_in) {
   const long long total = B * N;

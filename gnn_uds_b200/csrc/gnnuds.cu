@@ -846,6 +846,7 @@ int forward_chunk_nn(gnnuds_handle* h, const float* x, const float* b, const flo
       std::vector<SegH> segs = st.x;
       segs.insert(segs.end(), st.e.begin(), st.e.end());
       float* z = (l & 1) ? h->EA : h->XA;
+      if (h->tape.on && !(h->tape.sp[blk][l].xo = z = h->tape.alloc((size_t)Bc * T * 2 * E))) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (NN-cat spatial layer)");
       int r = launch_gemm(h, segs, W(h, w.t[0]), W(h, w.t[1]), z, 2 * E, 2 * E, act, Bc, 1, T, T, 1, 0);
       if (r) return r;
       st.x = {{z, 2 * E, E, 0, 1, 0}};
@@ -855,42 +856,49 @@ int forward_chunk_nn(gnnuds_handle* h, const float* x, const float* b, const flo
   };
   if ((rc = spatial(0, Ti))) return rc;
   float *xt = nullptr, *et = nullptr;
-  if ((rc = run_temporal(h, h->tpx[0], st.x[0], E, Bc, 1, Ti, To, h->TX0, h->TX1, &xt))) return rc;
-  if ((rc = run_temporal(h, h->tpe[0], st.e[0], E, Bc, 1, Ti, To, h->TE0, h->TE1, &et))) return rc;
+  if ((rc = run_temporal(h, h->tpx[0], st.x[0], E, Bc, 1, Ti, To, h->TX0, h->TX1, &xt, h->tape.tp[0][0]))) return rc;
+  if ((rc = run_temporal(h, h->tpe[0], st.e[0], E, Bc, 1, Ti, To, h->TE0, h->TE1, &et, h->tape.tp[0][1]))) return rc;
   st.x = {{xt, H, H, 0, 1, 0}, {h->BEMB, E2, E2, 0, 1, 0}};
   st.e = {{et, H, H, 0, 1, 0}};
   if (c.act) st.e.push_back({h->AEMB, E2, E2, 0, 1, 0});
   if ((rc = spatial(1, To))) return rc;
-  if ((rc = run_temporal(h, h->tpx[1], st.x[0], E, Bc, 1, To, To, h->TX0, h->TX1, &xt))) return rc;
-  if ((rc = run_temporal(h, h->tpe[1], st.e[0], E, Bc, 1, To, To, h->TE0, h->TE1, &et))) return rc;
+  if ((rc = run_temporal(h, h->tpx[1], st.x[0], E, Bc, 1, To, To, h->TX0, h->TX1, &xt, h->tape.tp[1][0]))) return rc;
+  if ((rc = run_temporal(h, h->tpe[1], st.e[0], E, Bc, 1, To, To, h->TE0, h->TE1, &et, h->tape.tp[1][1]))) return rc;
   // ---- resnet + heads (emulator.py:312-338) ----
   const int ract = c.resnet ? ACT_LINEAR : act;
-  if ((rc = launch_gemm(h, {{xt, H, H, 0, 1, 0}}, W(h, h->resx.t[0]), W(h, h->resx.t[1]), h->XB, E, E, ract, Bc, 1, To, To, 1, 0))) return rc;
-  if ((rc = launch_gemm(h, {{et, H, H, 0, 1, 0}}, W(h, h->rese.t[0]), W(h, h->rese.t[1]), h->EB, E, E, ract, Bc, 1, To, To, 1, 0))) return rc;
+  float *XBo = h->XB, *EBo = h->EB;            // reverse pass: the embeddings in XB / EB stay alive, the resnet output goes on the tape
+  if (h->tape.on) {
+    h->tape.resx = XBo = h->tape.alloc((size_t)Bc * To * E); h->tape.rese = EBo = h->tape.alloc((size_t)Bc * To * E);
+    if (!XBo || !EBo) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (NN-cat resnet)");
+  }
+  if ((rc = launch_gemm(h, {{xt, H, H, 0, 1, 0}}, W(h, h->resx.t[0]), W(h, h->resx.t[1]), XBo, E, E, ract, Bc, 1, To, To, 1, 0))) return rc;
+  if ((rc = launch_gemm(h, {{et, H, H, 0, 1, 0}}, W(h, h->rese.t[0]), W(h, h->rese.t[1]), EBo, E, E, ract, Bc, 1, To, To, 1, 0))) return rc;
   if (c.resnet) {
-    cumsum_res_act_kernel<float><<<grid_for(h, Bc * (E / 4), 256, 16), 256, 0, h->stream>>>(h->XB, h->RES, Bc, To, 1, E, act);
-    cumsum_res_act_kernel<float><<<grid_for(h, Bc * (E / 4), 256, 16), 256, 0, h->stream>>>(h->EB, h->RESE, Bc, To, 1, E, act);
+    cumsum_res_act_kernel<float><<<grid_for(h, Bc * (E / 4), 256, 16), 256, 0, h->stream>>>(XBo, h->RES, Bc, To, 1, E, act);
+    cumsum_res_act_kernel<float><<<grid_for(h, Bc * (E / 4), 256, 16), 256, 0, h->stream>>>(EBo, h->RESE, Bc, To, 1, E, act);
     h->launches += 2;
     CU(cudaGetLastError());
   }
   const long long So = Bc * To;
   const int ldn = h->ldn();
-  if ((rc = launch_gemm(h, {{h->XB, E, E, 0, 1, 0}}, P + h->nnp_out.w, P + h->nnp_out.b, h->XA, h->nnp_out.Nop, h->nnp_out.Nop,
+  if ((rc = launch_gemm(h, {{XBo, E, E, 0, 1, 0}}, P + h->nnp_out.w, P + h->nnp_out.b, h->XA, h->nnp_out.Nop, h->nnp_out.Nop,
                         ACT_HARD_SIGMOID, Bc, 1, To, To, 1, 0))) return rc;
   if ((rc = unflat(h->XA, h->nnp_out.Nop, h->OUTN, ldn, 0, So, N, c.n_out))) return rc;
   if (c.if_flood) {
-    std::vector<SegH> cur = {{h->XB, E, E, 0, 1, 0}};
+    std::vector<SegH> cur = {{XBo, E, E, 0, 1, 0}};
     float* bufs[2] = {h->EX, h->NX};
     for (int i = 0; i < c.if_flood; ++i) {
-      if ((rc = launch_gemm(h, cur, W(h, h->flood_chain[i].t[0]), W(h, h->flood_chain[i].t[1]), bufs[i & 1], E2, E2, act, Bc, 1,
+      float* fo = bufs[i & 1];
+      if (h->tape.on && (i >= 8 || !(h->tape.flood[i] = fo = h->tape.alloc((size_t)So * E2)))) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (NN-cat flood chain)");
+      if ((rc = launch_gemm(h, cur, W(h, h->flood_chain[i].t[0]), W(h, h->flood_chain[i].t[1]), fo, E2, E2, act, Bc, 1,
                             To, To, 1, 0))) return rc;
-      cur = {{bufs[i & 1], E2, E2, 0, 1, 0}};
+      cur = {{fo, E2, E2, 0, 1, 0}};
     }
     if ((rc = launch_gemm(h, cur, P + h->nnp_flood.w, P + h->nnp_flood.b, h->XA, h->nnp_flood.Nop, h->nnp_flood.Nop, ACT_SIGMOID,
                           Bc, 1, To, To, 1, 0))) return rc;
     if ((rc = unflat(h->XA, h->nnp_flood.Nop, h->OUTN, ldn, c.n_out, So, N, 1))) return rc;
   }
-  if ((rc = launch_gemm(h, {{h->EB, E, E, 0, 1, 0}}, P + h->nnp_eout.w, P + h->nnp_eout.b, h->EA, h->nnp_eout.Nop, h->nnp_eout.Nop,
+  if ((rc = launch_gemm(h, {{EBo, E, E, 0, 1, 0}}, P + h->nnp_eout.w, P + h->nnp_eout.b, h->EA, h->nnp_eout.Nop, h->nnp_eout.Nop,
                         ACT_TANH, Bc, 1, To, To, 1, 0))) return rc;
   if ((rc = unflat(h->EA, h->nnp_eout.Nop, h->OUTE, c.e_out, 0, So, M, c.e_out))) return rc;
   return run_postproc(h, x, b, a, Bc, y, ey, normalised_io);

@@ -43,7 +43,6 @@ class TorchEmulator:
     """Differentiable twin of ``OracleEmulator`` (conv models; emulator.py:195-340, 604-641, 680-748)."""
 
     def __init__(self, orc):
-        assert orc.conv, "NN-cat has no gradient oracle"
         self.o = orc
         self.w = [[_t(a) for a in ws] for ws in orc.weights]
         self.norm = {k: _t(getattr(orc, "norm_" + k)) for k in "xbye" if hasattr(orc, "norm_" + k)}
@@ -119,6 +118,8 @@ class TorchEmulator:
         """build_network (emulator.py:195-340) on normalised inputs; ``trace`` collects named intermediates
         (with retain_grad) for stage-wise debugging of a VJP."""
         o = self.o
+        if not o.conv:
+            return self._model_nn(X, Bn, E_in, AE)
         it = iter(self.w)
         actv = _act(o.activation)
         N, M, Ti, To, H = o.n_node, o.n_edge, o.seq_in, o.seq_out, o.hidden_dim
@@ -190,6 +191,52 @@ class TorchEmulator:
         w = next(it); e_o = _dense(e, w, "tanh")
         assert next(it, None) is None
         return keep("out_n", out), keep("out_e", e_o)
+
+    def _model_nn(self, X, Bn, E_in, AE=None):
+        """NN-cat graph (emulator.py:195-340 with conv falsy), as OracleEmulator._model_nn."""
+        o = self.o
+        it = iter(self.w)
+        actv = _act(o.activation)
+        N, M, To = o.n_node, o.n_edge, o.seq_out
+        B = X.shape[0]
+        flat = lambda v: v.reshape(v.shape[0], v.shape[1], -1)
+        w = next(it); x = _dense(flat(X), w, "linear")
+        res = x[:, -1:, :]
+        x = actv(x)
+        w = next(it); b = _dense(flat(Bn), w, o.activation)
+        w = next(it); e = _dense(flat(E_in), w, "linear")
+        res_e = e[:, -1:, :]
+        e = actv(e)
+        if o.act:
+            w = next(it); ae = _dense(flat(AE), w, o.activation)
+
+        def spatial(x, e):
+            for _ in range(o.n_sp_layer):
+                w = next(it); z = _dense(torch.cat([x, e], dim=-1), w, o.activation)
+                x, e = torch.chunk(z, 2, dim=-1)
+            return x, e
+
+        x, e = spatial(x, e)
+        x = self._temporal(x, it)[:, -To:, :]
+        e = self._temporal(e, it)[:, -To:, :]
+        x = torch.cat([x, b], dim=-1)
+        if o.act:
+            e = torch.cat([e, ae], dim=-1)
+        x, e = spatial(x, e)
+        x = self._temporal(x, it)
+        e = self._temporal(e, it)
+        w = next(it); x_out = _dense(x, w, "linear")
+        x = actv(torch.cumsum(x_out, dim=1) + res) if o.resnet else actv(x_out)
+        w = next(it); e_out = _dense(e, w, "linear")
+        e = actv(torch.cumsum(e_out, dim=1) + res_e) if o.resnet else actv(e_out)
+        w = next(it); out = _dense(x, w, "hard_sigmoid").reshape(B, To, N, o.n_out)
+        if o.if_flood:
+            for _ in range(o.if_flood):
+                w = next(it); x = _dense(x, w, o.activation)
+            w = next(it); out = torch.cat([out, _dense(x, w, "sigmoid").reshape(B, To, N, 1)], dim=-1)
+        w = next(it); e_o = _dense(e, w, "tanh").reshape(B, To, M, o.e_out)
+        assert next(it, None) is None
+        return out, e_o
 
     def normalize(self, dat, item, inverse=False):                   # emulator.py:803-810
         dim = dat.shape[-1]

@@ -32,7 +32,8 @@ def _rel(got, ref):
 
 
 @pytest.mark.parametrize("case,chunks", [("c3_ast_act_5", 1), ("c3_ast_act_5", 3), ("ast_gcn_conv_act_nofusion", 1),
-                                         ("ast_gcn_conv_act_nofusion", 2)])
+                                         ("ast_gcn_conv_act_nofusion", 2), ("ast_nn_conv_act_fusion", 1),
+                                         ("ast_nn_conv_act_fusion", 2)])
 def test_grad_settings_matches_autograd(case, chunks):
     from oracle import grad_oracle as go
     em, _ = cases.setup_product(case)
@@ -55,7 +56,8 @@ def test_grad_settings_matches_autograd(case, chunks):
     assert np.array_equal(obj, em.objective(y, states, fw, ww, rw, gm))
 
 
-@pytest.mark.parametrize("case", ["c3_ast_act_5", "ast_gcn_conv_eps0", "c2_shq_gat_conv_10", "ast_gcn_conv_act_nofusion"])
+@pytest.mark.parametrize("case", ["c3_ast_act_5", "ast_gcn_conv_eps0", "c2_shq_gat_conv_10", "ast_gcn_conv_act_nofusion",
+                                  "ast_nn_conv_act_fusion"])
 def test_predict_vjp_matches_autograd(case):
     """Random cotangents on every output channel; gradients w.r.t. settings, states and edge states."""
     from oracle import grad_oracle as go

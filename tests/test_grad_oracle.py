@@ -6,7 +6,8 @@ import pytest
 
 import cases
 
-GRAD_CASES = ["c3_ast_act_5", "ast_gcn_lstm_act_nofusion", "ast_joint_gat_conv_act", "ast_head_tide_offset"]
+GRAD_CASES = ["c3_ast_act_5", "ast_gcn_lstm_act_nofusion", "ast_joint_gat_conv_act", "ast_head_tide_offset",
+              "ast_nn_conv_act_fusion"]
 
 
 def _weights(o, seed=3):
@@ -28,7 +29,8 @@ def test_torch_forward_equals_numpy_oracle(case):
     assert np.abs(eyt.numpy() - ey).max() <= 1e-11 * max(1.0, np.abs(ey).max())
 
 
-@pytest.mark.parametrize("case,chunks", [("c3_ast_act_5", 1), ("c3_ast_act_5", 2), ("ast_gcn_lstm_act_nofusion", 1)])
+@pytest.mark.parametrize("case,chunks", [("c3_ast_act_5", 1), ("c3_ast_act_5", 2), ("ast_gcn_lstm_act_nofusion", 1),
+                                         ("ast_nn_conv_act_fusion", 2)])
 def test_autograd_equals_finite_differences(case, chunks):
     from oracle import grad_oracle as go
     from oracle.emulator_oracle import astlingen_objective  # noqa: F401  (same formula, weight-vector form below)
