@@ -389,7 +389,7 @@ def run_grad(a):
     o = OracleEmulator(args.conv, args.resnet, args.recurrent, args, dtype=np.float64)
     o.set_weights(em.weights)
     o.set_norm(em.norm_x, em.norm_b, em.norm_y, em.norm_r, em.norm_e)
-    nc = 4
+    nc = min(4, pop)
     sett = ev.expand_settings(y[:nc]).astype(np.float64)
     st = np.repeat(states.astype(np.float64), nc, 0); bb = np.repeat(b.astype(np.float64), nc, 0); ee = np.repeat(ex.astype(np.float64), nc, 0)
     gm = 0.99 ** np.arange(T)

@@ -20,6 +20,7 @@
 #include <array>
 #include <thread>
 #include <cmath>
+#include <map>
 #include <mutex>
 #include <cstdarg>
 #include <cstdio>
@@ -181,6 +182,21 @@ struct gnnuds_handle {
   // (x0, ex0, b, dec, partial sums, prev_q, obj)
   float* gb[48] = {nullptr}; size_t gb_cap[48] = {0};   // 18..21 replay (raw states, perfs, edge states, settings)
 
+  // CUDA graphs of launch-bound call bodies (small populations: the reverse pass issues ~3 k kernels per 12-chunk gradient).
+  // A graph is keyed by the call's scalars, its caller pointers and buf_gen, which every (re)allocation of a handle buffer
+  // bumps (the graphs bake device addresses in).  GNNUDS_GRAPHS=0 disables them.
+  uint64_t buf_gen = 0;
+  int use_graphs = 1;
+  // Small batches: the node-side and edge-side kernels of a layer are independent and neither fills the GPU, so they run
+  // concurrently - node side on `stream`, edge side on `s_side`, fork / join by events (par2).  Decided per chunk
+  // (side_prepare); large batches keep the single-stream order.  GNNUDS_SIDE_PAR=0 disables it.
+  cudaStream_t s_side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  int side_par = 1;
+  bool side_on = false;
+  float* HB2 = nullptr;                 // the edge side's projection / conv scratch while both sides are in flight
+  std::vector<std::pair<std::string, cudaGraphExec_t>> graphs;
+  std::map<std::string, int64_t> graph_launches;      // kernels per graph (gnnuds_launch_count stays a kernel count)
   Tape tape;                            // reverse pass (gnnuds_predict_vjp / gnnuds_grad_settings)
   float* bw_arena = nullptr; size_t bw_cap = 0;
 
@@ -409,6 +425,61 @@ int prof_end(gnnuds_handle* h, cudaEvent_t e1) {
   return 0;
 }
 
+// Node side (fx) on h->stream and edge side (fe) on h->s_side, concurrently when side_on; joined before returning.
+// Inside fe, h->stream IS the side stream and h->HB the side's own scratch, so every launch helper works unchanged.
+template <class FX, class FE>
+int par2(gnnuds_handle* h, FX fx, FE fe) {
+  if (!h->side_on) { const int rc = fx(); return rc ? rc : fe(); }
+  cudaStream_t main = h->stream;
+  float* hb = h->HB;
+  CU(cudaEventRecord(h->ev_fork, main));
+  CU(cudaStreamWaitEvent(h->s_side, h->ev_fork, 0));
+  const int rc1 = fx();
+  h->stream = h->s_side; h->HB = h->HB2;
+  const int rc2 = rc1 ? 0 : fe();
+  h->stream = main; h->HB = hb;
+  CU(cudaEventRecord(h->ev_join, h->s_side));
+  CU(cudaStreamWaitEvent(main, h->ev_join, 0));
+  return rc1 ? rc1 : rc2;
+}
+
+// Run `body` (stream-ordered work on h->stream only: kernel launches, async memsets / D2D copies on handle or caller
+// device buffers; no allocation, no synchronisation) as a CUDA graph cached under `key`.  First use captures and
+// instantiates; a capture that fails (something in the body is not capturable) switches graphs off for the handle and
+// the body runs eagerly.  The caller has made every buffer the body touches exist BEFORE this call.
+template <class F>
+int run_graphed(gnnuds_handle* h, std::string key, F body) {
+  if (!h->use_graphs || h->profiling || h->debug_stop) return body();
+  char gen[48];
+  snprintf(gen, sizeof gen, "|g%llu|v%d", (unsigned long long)h->buf_gen, h->pp_variant);
+  key += gen;
+  cudaGraphExec_t exec = nullptr;
+  for (auto& g : h->graphs) if (g.first == key) { exec = g.second; break; }
+  if (!exec) {
+    if (cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) { (void)cudaGetLastError(); h->use_graphs = 0; return body(); }
+    const int64_t l0 = h->launches;
+    const int rc = body();
+    cudaGraph_t g = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(h->stream, &g);
+    if (rc || e != cudaSuccess || !g) {
+      (void)cudaGetLastError();
+      if (g) cudaGraphDestroy(g);
+      if (rc) return rc;
+      h->use_graphs = 0; h->launches = l0;
+      return body();
+    }
+    if (cudaGraphInstantiate(&exec, g, 0) != cudaSuccess) { (void)cudaGetLastError(); cudaGraphDestroy(g); h->use_graphs = 0; h->launches = l0; return body(); }
+    cudaGraphDestroy(g);
+    if (h->graphs.size() >= 32) { cudaGraphExecDestroy(h->graphs.front().second); h->graphs.erase(h->graphs.begin()); }
+    h->graphs.push_back({key, exec});
+    h->graph_launches[key] = h->launches - l0;
+  } else {
+    h->launches += h->graph_launches[key];
+  }
+  CU(cudaGraphLaunch(exec, h->stream));
+  return 0;
+}
+
 struct SegH { const float* p; int ld; int width; int shift; int pitch; int off; };
 
 int launch_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, const float* Wp, const float* bias, float* out,
@@ -602,6 +673,7 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src
 }
 
 struct Stream2 { std::vector<SegH> x, e; };   // current node / edge stream as concatenated segments
+int side_prepare(gnnuds_handle* h, int64_t Bc);
 template <bool TC> int run_spatial_joint(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T);
 
 // ---- spatial block (emulator.py:219-235 / 272-288), graph_base == 0 -----------------------
@@ -625,20 +697,29 @@ int run_spatial(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) {
       tp.xo = xo = h->tape.alloc((size_t)S * N * E); tp.eo = eo = h->tape.alloc((size_t)S * M * E);
       if (!XE || !EX || !HBx || !HBe || !xo || !eo) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (spatial layer)");
     }
-    // x_e = Dense(E/2)(e) ; e_x = Dense(E/2)(x)
-    if ((rc = launch_gemm(h, st.e, W(h, w.xe.t[0]), W(h, w.xe.t[1]), XE, E2, E2, act, Bc, M, T, T, M, 0))) return rc;
-    if ((rc = launch_gemm(h, st.x, W(h, w.ex.t[0]), W(h, w.ex.t[1]), EX, E2, E2, act, Bc, N, T, T, N, 0))) return rc;
-    // NodeEdge both directions
+    // x_e = Dense(E/2)(e) ; e_x = Dense(E/2)(x)   (the node side consumes x_e, the edge side e_x)
+    if ((rc = par2(h, [&] { return launch_gemm(h, st.x, W(h, w.ex.t[0]), W(h, w.ex.t[1]), EX, E2, E2, act, Bc, N, T, T, N, 0); },
+                   [&] { return launch_gemm(h, st.e, W(h, w.xe.t[0]), W(h, w.xe.t[1]), XE, E2, E2, act, Bc, M, T, T, M, 0); }))) return rc;
     const int li = blk * c.n_sp_layer + l;
-    if ((rc = launch_nodeedge(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, XE, h->NX, S, M, N, E2))) return rc;
-    if ((rc = launch_nodeedge(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, EX, h->NE, S, N, M, E2))) return rc;
-    // conv on [x | NodeEdge(x_e)]
-    std::vector<SegH> sx = st.x; sx.push_back({h->NX, E2, E2, 0, N, 0});
-    std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
-    if ((rc = launch_gemm(h, sx, W(h, w.conv_x.t[0]), nullptr, HBx, E, E, ACT_LINEAR, Bc, N, T, T, N, 0))) return rc;
-    if ((rc = launch_agg(h, HBx, xo, h->d_rp, h->d_ci, h->d_val, w.conv_x, S, N, act, blk == 1))) return rc;
-    if ((rc = launch_gemm(h, se, W(h, w.conv_e.t[0]), nullptr, HBe, E, E, ACT_LINEAR, Bc, M, T, T, M, 0))) return rc;
-    if ((rc = launch_agg(h, HBe, eo, h->d_erp, h->d_eci, h->d_eval, w.conv_e, S, M, act))) return rc;
+    const bool taped = h->tape.on;
+    // per side: NodeEdge of the other side's Dense, conv on [self | NodeEdge], aggregation
+    auto node_side = [&]() -> int {
+      int r;
+      if ((r = launch_nodeedge(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, XE, h->NX, S, M, N, E2))) return r;
+      std::vector<SegH> sx = st.x; sx.push_back({h->NX, E2, E2, 0, N, 0});
+      float* hb = taped ? HBx : h->HB;
+      if ((r = launch_gemm(h, sx, W(h, w.conv_x.t[0]), nullptr, hb, E, E, ACT_LINEAR, Bc, N, T, T, N, 0))) return r;
+      return launch_agg(h, hb, xo, h->d_rp, h->d_ci, h->d_val, w.conv_x, S, N, act, blk == 1);
+    };
+    auto edge_side = [&]() -> int {
+      int r;
+      if ((r = launch_nodeedge(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, EX, h->NE, S, N, M, E2))) return r;
+      std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
+      float* hb = taped ? HBe : h->HB;                   // inside par2's edge branch h->HB is the side's own scratch
+      if ((r = launch_gemm(h, se, W(h, w.conv_e.t[0]), nullptr, hb, E, E, ACT_LINEAR, Bc, M, T, T, M, 0))) return r;
+      return launch_agg(h, hb, eo, h->d_erp, h->d_eci, h->d_eval, w.conv_e, S, M, act);
+    };
+    if ((rc = par2(h, node_side, edge_side))) return rc;
     st.x = {{xo, E, E, 0, N, 0}};
     st.e = {{eo, E, E, 0, M, 0}};
     if (h->debug_stop == (blk ? 40 : 20) + l) return 1;
@@ -704,17 +785,22 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
   const int E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge, Ti = c.seq_in, To = c.seq_out;
   const int act = act_code(c);
   int rc;
+  if ((rc = side_prepare(h, Bc))) return rc;
   // ---- K1 embedding ----
-  if ((rc = launch_embed(h, x, normalised_io ? nullptr : h->d_nx, h->cx_n, N, nullptr, 0, h->emb_x, h->XB, h->RES, Bc, Ti, N,
-                         c.n_in, E, act, 0))) return rc;
-  if ((rc = launch_embed(h, b, normalised_io ? nullptr : h->d_nb, h->cb_n, N, nullptr, 0, h->emb_b, h->BEMB, nullptr, Bc, To, N,
-                         c.b_in, E2, act, 0))) return rc;
-  if ((rc = launch_embed(h, ex, normalised_io ? nullptr : h->d_ne, h->ce_n, M, nullptr, 0, h->emb_e, h->EB, h->RESE, Bc, Ti, M,
-                         c.e_in, E, act, 0))) return rc;
-  if (c.act) {
-    if ((rc = launch_embed(h, a, nullptr, 0, 0, h->d_act_of_edge, c.n_act, h->emb_a, h->AEMB, nullptr, Bc, To, M, 1, E2, act, 2)))
-      return rc;
-  }
+  if ((rc = par2(h,
+      [&]() -> int {
+        int r;
+        if ((r = launch_embed(h, x, normalised_io ? nullptr : h->d_nx, h->cx_n, N, nullptr, 0, h->emb_x, h->XB, h->RES, Bc, Ti, N,
+                              c.n_in, E, act, 0))) return r;
+        return launch_embed(h, b, normalised_io ? nullptr : h->d_nb, h->cb_n, N, nullptr, 0, h->emb_b, h->BEMB, nullptr, Bc, To, N,
+                            c.b_in, E2, act, 0);
+      },
+      [&]() -> int {
+        int r;
+        if ((r = launch_embed(h, ex, normalised_io ? nullptr : h->d_ne, h->ce_n, M, nullptr, 0, h->emb_e, h->EB, h->RESE, Bc, Ti, M,
+                              c.e_in, E, act, 0))) return r;
+        return c.act ? launch_embed(h, a, nullptr, 0, 0, h->d_act_of_edge, c.n_act, h->emb_a, h->AEMB, nullptr, Bc, To, M, 1, E2, act, 2) : 0;
+      }))) return rc;
   Stream2 st;
   st.x = {{h->XB, E, E, 0, N, 0}};
   st.e = {{h->EB, E, E, 0, M, 0}};
@@ -729,8 +815,8 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
   if (h->debug_stop == 2) return 0;
   // ---- temporal block 1 (keeps the last To steps, emulator.py:249,256) ----
   float *xt = nullptr, *et = nullptr;
-  if ((rc = run_temporal(h, h->tpx[0], st.x[0], E, Bc, N, Ti, To, h->TX0, h->TX1, &xt, h->tape.tp[0][0]))) return rc;
-  if ((rc = run_temporal(h, h->tpe[0], st.e[0], E, Bc, M, Ti, To, h->TE0, h->TE1, &et, h->tape.tp[0][1]))) return rc;
+  if ((rc = par2(h, [&] { return run_temporal(h, h->tpx[0], st.x[0], E, Bc, N, Ti, To, h->TX0, h->TX1, &xt, h->tape.tp[0][0]); },
+                 [&] { return run_temporal(h, h->tpe[0], st.e[0], E, Bc, M, Ti, To, h->TE0, h->TE1, &et, h->tape.tp[0][1]); }))) return rc;
   // ---- boundary / control concat (emulator.py:260-262) ----
   st.x = {{xt, H, H, 0, N, 0}, {h->BEMB, E2, E2, 0, N, 0}};
   st.e = {{et, H, H, 0, M, 0}};
@@ -744,8 +830,8 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
   if (rc) return rc;
   if (h->debug_stop == 4) return 0;
   // ---- temporal block 2 ----
-  if ((rc = run_temporal(h, h->tpx[1], st.x[0], E, Bc, N, To, To, h->TX0, h->TX1, &xt, h->tape.tp[1][0]))) return rc;
-  if ((rc = run_temporal(h, h->tpe[1], st.e[0], E, Bc, M, To, To, h->TE0, h->TE1, &et, h->tape.tp[1][1]))) return rc;
+  if ((rc = par2(h, [&] { return run_temporal(h, h->tpx[1], st.x[0], E, Bc, N, To, To, h->TX0, h->TX1, &xt, h->tape.tp[1][0]); },
+                 [&] { return run_temporal(h, h->tpe[1], st.e[0], E, Bc, M, To, To, h->TE0, h->TE1, &et, h->tape.tp[1][1]); }))) return rc;
   st.x = {{xt, H, H, 0, N, 0}};
   st.e = {{et, H, H, 0, M, 0}};
   set_dbg(h, st, Bc * To * N, Bc * To * M);
@@ -757,36 +843,51 @@ int forward_chunk(gnnuds_handle* h, const float* x, const float* b, const float*
     h->tape.resx = XAo = h->tape.alloc((size_t)Bc * To * N * E); h->tape.rese = EAo = h->tape.alloc((size_t)Bc * To * M * E);
     if (!XAo || !EAo) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (resnet)");
   }
-  if ((rc = launch_gemm(h, st.x, W(h, h->resx.t[0]), W(h, h->resx.t[1]), XAo, E, E, ract, Bc, N, To, To, N, 0))) return rc;
-  if ((rc = launch_gemm(h, st.e, W(h, h->rese.t[0]), W(h, h->rese.t[1]), EAo, E, E, ract, Bc, M, To, To, M, 0))) return rc;
-  if (c.resnet) {
-    cumsum_res_act_kernel<float><<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(XAo, h->RES, Bc, To, N, E, act);
-    cumsum_res_act_kernel<float><<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(EAo, h->RESE, Bc, To, M, E, act);
-    h->launches += 2;
-    CU(cudaGetLastError());
-  }
+  const long long RXo = Bc * To * N, REo = Bc * To * M;
+  const int ldn = h->ldn();
+  // node side: Dense, resnet cumsum, hard_sigmoid head, flood chain + sigmoid head; edge side: Dense, cumsum, tanh head
+  auto node_tail = [&]() -> int {
+    int r;
+    if ((r = launch_gemm(h, st.x, W(h, h->resx.t[0]), W(h, h->resx.t[1]), XAo, E, E, ract, Bc, N, To, To, N, 0))) return r;
+    if (c.resnet) {
+      cumsum_res_act_kernel<float><<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(XAo, h->RES, Bc, To, N, E, act);
+      ++h->launches;
+      CU(cudaGetLastError());
+    }
+    if (h->debug_stop == 6) return 0;
+    if ((r = launch_head(h, XAo, E, E, h->head_out, h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID, RXo))) return r;
+    if (c.if_flood) {
+      std::vector<SegH> cur = {{XAo, E, E, 0, N, 0}};
+      float* bufs[2] = {h->EX, h->NX};
+      for (int i = 0; i < c.if_flood; ++i) {
+        float* fo = bufs[i & 1];
+        if (h->tape.on) {
+          if (i >= 8 || !(h->tape.flood[i] = fo = h->tape.alloc((size_t)RXo * E2))) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (flood chain)");
+        }
+        if ((r = launch_gemm(h, cur, W(h, h->flood_chain[i].t[0]), W(h, h->flood_chain[i].t[1]), fo, E2, E2, act, Bc, N,
+                             To, To, N, 0))) return r;
+        cur = {{fo, E2, E2, 0, N, 0}};
+      }
+      if ((r = launch_head(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return r;
+    }
+    return 0;
+  };
+  auto edge_tail = [&]() -> int {
+    int r;
+    if ((r = launch_gemm(h, st.e, W(h, h->rese.t[0]), W(h, h->rese.t[1]), EAo, E, E, ract, Bc, M, To, To, M, 0))) return r;
+    if (c.resnet) {
+      cumsum_res_act_kernel<float><<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(EAo, h->RESE, Bc, To, M, E, act);
+      ++h->launches;
+      CU(cudaGetLastError());
+    }
+    if (h->debug_stop == 6) return 0;
+    return launch_head(h, EAo, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo);
+  };
+  if ((rc = par2(h, node_tail, edge_tail))) return rc;
   st.x = {{XAo, E, E, 0, N, 0}};
   st.e = {{EAo, E, E, 0, M, 0}};
   set_dbg(h, st, Bc * To * N, Bc * To * M);
   if (h->debug_stop == 6) return 0;
-  const long long RXo = Bc * To * N, REo = Bc * To * M;
-  const int ldn = h->ldn();
-  if ((rc = launch_head(h, XAo, E, E, h->head_out, h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID, RXo))) return rc;
-  if (c.if_flood) {
-    std::vector<SegH> cur = st.x;
-    float* bufs[2] = {h->EX, h->NX};
-    for (int i = 0; i < c.if_flood; ++i) {
-      float* fo = bufs[i & 1];
-      if (h->tape.on) {
-        if (i >= 8 || !(h->tape.flood[i] = fo = h->tape.alloc((size_t)RXo * E2))) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (flood chain)");
-      }
-      if ((rc = launch_gemm(h, cur, W(h, h->flood_chain[i].t[0]), W(h, h->flood_chain[i].t[1]), fo, E2, E2, act, Bc, N,
-                            To, To, N, 0))) return rc;
-      cur = {{fo, E2, E2, 0, N, 0}};
-    }
-    if ((rc = launch_head(h, cur[0].p, E2, E2, h->head_flood, h->OUTN, ldn, c.n_out, 1, ACT_SIGMOID, RXo))) return rc;
-  }
-  if ((rc = launch_head(h, EAo, E, E, h->head_e, h->OUTE, c.e_out, 0, c.e_out, ACT_TANH, REo))) return rc;
   return run_postproc(h, x, b, a, Bc, y, ey, normalised_io);
 }
 
@@ -1565,38 +1666,45 @@ int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) 
   for (int l = 0; l < c.n_sp_layer; ++l) {
     const SpatialW& w = h->sp[blk][l];
     int rc;
-    if ((rc = launch_tc_gemm(h, st.e, w.xe.t[0], W(h, w.xe.t[1]), h->XE, E2, E2, act, Bc, M, T, T, M, 0))) return rc;
-    if ((rc = launch_tc_gemm(h, st.x, w.ex.t[0], W(h, w.ex.t[1]), h->EX, E2, E2, act, Bc, N, T, T, N, 0))) return rc;
+    if ((rc = par2(h, [&] { return launch_tc_gemm(h, st.x, w.ex.t[0], W(h, w.ex.t[1]), h->EX, E2, E2, act, Bc, N, T, T, N, 0); },
+                   [&] { return launch_tc_gemm(h, st.e, w.xe.t[0], W(h, w.xe.t[1]), h->XE, E2, E2, act, Bc, M, T, T, M, 0); }))) return rc;
     const int li = blk * c.n_sp_layer + l;
     float* xo = (l & 1) ? h->XB : h->XA;
     float* eo = (l & 1) ? h->EB : h->EA;
     // fused NodeEdge + conv + aggregation per stream side; layer-by-layer kernels when it does not apply
     const bool dyn_x = blk == 1 && h->use_adj;   // per-sample attention mask: layer-by-layer kernels on the node side
-    rc = dyn_x ? -1 : launch_sp_agg(h, st.x, h->XE, 0, li, w.conv_x, xo, S, N, M, act);
-    if (rc < 0 && !dyn_x) rc = launch_sp_conv(h, st.x, h->XE, 0, li, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, M, act);
-    if (rc > 0) return rc;
-    if (rc < 0) {
-      if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, h->XE, h->NX, S, M, N, E2))) return rc;
-      std::vector<SegH> sx = st.x; sx.push_back({h->NX, E2, E2, 0, N, 0});
-      if (dyn_x) {
-        if ((rc = launch_tc_gemm(h, sx, w.conv_x.t[0], nullptr, h->HB, E, E, ACT_LINEAR, Bc, N, T, T, N, 0))) return rc;
-        if ((rc = launch_agg<bf16>(h, h->HB, xo, h->d_rp, h->d_ci, h->d_val, w.conv_x, S, N, act, true))) return rc;
-      } else {
-        rc = launch_conv_agg(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, act);
-        if (rc > 0) return rc;
-        if (rc < 0 && (rc = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return rc;
+    auto node_side = [&]() -> int {
+      int r = dyn_x ? -1 : launch_sp_agg(h, st.x, h->XE, 0, li, w.conv_x, xo, S, N, M, act);
+      if (r < 0 && !dyn_x) r = launch_sp_conv(h, st.x, h->XE, 0, li, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, M, act);
+      if (r > 0) return r;
+      if (r < 0) {
+        if ((r = launch_nodeedge<bf16>(h, h->d_ne_matT[0][li], h->ldm_n, h->ti_n, h->XE, h->NX, S, M, N, E2))) return r;
+        std::vector<SegH> sx = st.x; sx.push_back({h->NX, E2, E2, 0, N, 0});
+        if (dyn_x) {
+          if ((r = launch_tc_gemm(h, sx, w.conv_x.t[0], nullptr, h->HB, E, E, ACT_LINEAR, Bc, N, T, T, N, 0))) return r;
+          if ((r = launch_agg<bf16>(h, h->HB, xo, h->d_rp, h->d_ci, h->d_val, w.conv_x, S, N, act, true))) return r;
+        } else {
+          r = launch_conv_agg(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, act);
+          if (r > 0) return r;
+          if (r < 0 && (r = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return r;
+        }
       }
-    }
-    rc = launch_sp_agg(h, st.e, h->EX, 1, li, w.conv_e, eo, S, M, N, act);
-    if (rc < 0) rc = launch_sp_conv(h, st.e, h->EX, 1, li, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, S, M, N, act);
-    if (rc > 0) return rc;
-    if (rc < 0) {
-      if ((rc = launch_nodeedge<bf16>(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, h->EX, h->NE, S, N, M, E2))) return rc;
-      std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
-      rc = launch_conv_agg(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, S, M, act);
-      if (rc > 0) return rc;
-      if (rc < 0 && (rc = run_conv_tc(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, Bc, T, M, act))) return rc;
-    }
+      return 0;
+    };
+    auto edge_side = [&]() -> int {
+      int r = launch_sp_agg(h, st.e, h->EX, 1, li, w.conv_e, eo, S, M, N, act);
+      if (r < 0) r = launch_sp_conv(h, st.e, h->EX, 1, li, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, S, M, N, act);
+      if (r > 0) return r;
+      if (r < 0) {
+        if ((r = launch_nodeedge<bf16>(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, h->EX, h->NE, S, N, M, E2))) return r;
+        std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
+        r = launch_conv_agg(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, S, M, act);
+        if (r > 0) return r;
+        if (r < 0 && (r = run_conv_tc(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, Bc, T, M, act))) return r;
+      }
+      return 0;
+    };
+    if ((rc = par2(h, node_side, edge_side))) return rc;
     st.x = {{xo, E, E, 0, N, 0}};
     st.e = {{eo, E, E, 0, M, 0}};
     if (h->debug_stop == (blk ? 40 : 20) + l) return 1;
@@ -1610,16 +1718,21 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
   const int E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge, Ti = c.seq_in, To = c.seq_out;
   const int act = act_code(c);
   int rc;
-  if ((rc = launch_embed<bf16>(h, x, normalised_io ? nullptr : h->d_nx, h->cx_n, N, nullptr, 0, h->emb_x, h->XB, h->RES, Bc, Ti, N,
-                               c.n_in, E, act, 0))) return rc;
-  if ((rc = launch_embed<bf16>(h, b, normalised_io ? nullptr : h->d_nb, h->cb_n, N, nullptr, 0, h->emb_b, h->BEMB, nullptr, Bc, To, N,
-                               c.b_in, E2, act, 0))) return rc;
-  if ((rc = launch_embed<bf16>(h, ex, normalised_io ? nullptr : h->d_ne, h->ce_n, M, nullptr, 0, h->emb_e, h->EB, h->RESE, Bc, Ti, M,
-                               c.e_in, E, act, 0))) return rc;
-  if (c.act) {
-    if ((rc = launch_embed<bf16>(h, a, nullptr, 0, 0, h->d_act_of_edge, c.n_act, h->emb_a, h->AEMB, nullptr, Bc, To, M, 1, E2, act, 2)))
-      return rc;
-  }
+  if ((rc = side_prepare(h, Bc))) return rc;
+  if ((rc = par2(h,
+      [&]() -> int {
+        int r;
+        if ((r = launch_embed<bf16>(h, x, normalised_io ? nullptr : h->d_nx, h->cx_n, N, nullptr, 0, h->emb_x, h->XB, h->RES, Bc, Ti, N,
+                                    c.n_in, E, act, 0))) return r;
+        return launch_embed<bf16>(h, b, normalised_io ? nullptr : h->d_nb, h->cb_n, N, nullptr, 0, h->emb_b, h->BEMB, nullptr, Bc, To, N,
+                                  c.b_in, E2, act, 0);
+      },
+      [&]() -> int {
+        int r;
+        if ((r = launch_embed<bf16>(h, ex, normalised_io ? nullptr : h->d_ne, h->ce_n, M, nullptr, 0, h->emb_e, h->EB, h->RESE, Bc, Ti, M,
+                                    c.e_in, E, act, 0))) return r;
+        return c.act ? launch_embed<bf16>(h, a, nullptr, 0, 0, h->d_act_of_edge, c.n_act, h->emb_a, h->AEMB, nullptr, Bc, To, M, 1, E2, act, 2) : 0;
+      }))) return rc;
   Stream2 st;
   st.x = {{h->XB, E, E, 0, N, 0}};
   st.e = {{h->EB, E, E, 0, M, 0}};
@@ -1631,8 +1744,8 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
   if (rc) return rc;
   if (h->debug_stop == 2) return 0;
   float *xt = nullptr, *et = nullptr;
-  if ((rc = run_temporal_tc(h, h->tpx[0], st.x[0], E, Bc, N, Ti, To, h->TX0, h->TX1, &xt))) return rc;
-  if ((rc = run_temporal_tc(h, h->tpe[0], st.e[0], E, Bc, M, Ti, To, h->TE0, h->TE1, &et))) return rc;
+  if ((rc = par2(h, [&] { return run_temporal_tc(h, h->tpx[0], st.x[0], E, Bc, N, Ti, To, h->TX0, h->TX1, &xt); },
+                 [&] { return run_temporal_tc(h, h->tpe[0], st.e[0], E, Bc, M, Ti, To, h->TE0, h->TE1, &et); }))) return rc;
   st.x = {{xt, H, H, 0, N, 0}, {h->BEMB, E2, E2, 0, N, 0}};
   st.e = {{et, H, H, 0, M, 0}};
   if (c.act) st.e.push_back({h->AEMB, E2, E2, 0, M, 0});
@@ -1660,14 +1773,14 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
     if (frc > 0) return frc;
     tail_e = frc == 0;
   }
-  if (!tail_x && (rc = run_temporal_tc(h, h->tpx[1], st.x[0], E, Bc, N, To, To, h->TX0, h->TX1, &xt))) return rc;
-  if (!tail_e && (rc = run_temporal_tc(h, h->tpe[1], st.e[0], E, Bc, M, To, To, h->TE0, h->TE1, &et))) return rc;
+  if ((rc = par2(h, [&] { return tail_x ? 0 : run_temporal_tc(h, h->tpx[1], st.x[0], E, Bc, N, To, To, h->TX0, h->TX1, &xt); },
+                 [&] { return tail_e ? 0 : run_temporal_tc(h, h->tpe[1], st.e[0], E, Bc, M, To, To, h->TE0, h->TE1, &et); }))) return rc;
   if (!tail_x) st.x = {{xt, H, H, 0, N, 0}};
   if (!tail_e) st.e = {{et, H, H, 0, M, 0}};
   if (!tail_x && !tail_e) set_dbg(h, st, Bc * To * N, Bc * To * M);
   if (h->debug_stop == 5) return 0;
-  if (!tail_x && (rc = launch_tc_gemm(h, st.x, h->resx.t[0], W(h, h->resx.t[1]), XO, E, E, ract, Bc, N, To, To, N, 0))) return rc;
-  if (!tail_e && (rc = launch_tc_gemm(h, st.e, h->rese.t[0], W(h, h->rese.t[1]), EO, E, E, ract, Bc, M, To, To, M, 0))) return rc;
+  if ((rc = par2(h, [&] { return tail_x ? 0 : launch_tc_gemm(h, st.x, h->resx.t[0], W(h, h->resx.t[1]), XO, E, E, ract, Bc, N, To, To, N, 0); },
+                 [&] { return tail_e ? 0 : launch_tc_gemm(h, st.e, h->rese.t[0], W(h, h->rese.t[1]), EO, E, E, ract, Bc, M, To, To, M, 0); }))) return rc;
   const long long RXo = Bc * To * N, REo = Bc * To * M;
   const int ldn = h->ldn();
   // resnet + narrow heads in one pass per stream (E == 128): x = act(cumsum_t(x_out) + res) feeds the hard_sigmoid /
@@ -1677,13 +1790,22 @@ int forward_chunk_tc(gnnuds_handle* h, const float* x, const float* b, const flo
   if (fuse_ch) {
     CumHeadP px{reinterpret_cast<bf16*>(XO), h->RES, Bc, To, N, act, c.if_flood ? 1 : 0,
                 W(h, h->head_out.t[0]), W(h, h->head_out.t[1]), h->OUTN, ldn, 0, c.n_out, ACT_HARD_SIGMOID};
-    if (c.n_out == 1) cumsum_head_bf16_kernel<1, 8><<<grid_for(h, Bc * N, 8, 8), 256, 0, h->stream>>>(px);
-    else cumsum_head_bf16_kernel<4, 4><<<grid_for(h, Bc * N, 8, 8), 256, 0, h->stream>>>(px);
     CumHeadP pe{reinterpret_cast<bf16*>(EO), h->RESE, Bc, To, M, act, 0,
                 W(h, h->head_e.t[0]), W(h, h->head_e.t[1]), h->OUTE, c.e_out, 0, c.e_out, ACT_TANH};
-    cumsum_head_bf16_kernel<4, 4><<<grid_for(h, Bc * M, 8, 8), 256, 0, h->stream>>>(pe);
-    h->launches += 2;
-    CU(cudaGetLastError());
+    if ((rc = par2(h,
+        [&]() -> int {
+          if (c.n_out == 1) cumsum_head_bf16_kernel<1, 8><<<grid_for(h, Bc * N, 8, 8), 256, 0, h->stream>>>(px);
+          else cumsum_head_bf16_kernel<4, 4><<<grid_for(h, Bc * N, 8, 8), 256, 0, h->stream>>>(px);
+          ++h->launches;
+          CU(cudaGetLastError());
+          return 0;
+        },
+        [&]() -> int {
+          cumsum_head_bf16_kernel<4, 4><<<grid_for(h, Bc * M, 8, 8), 256, 0, h->stream>>>(pe);
+          ++h->launches;
+          CU(cudaGetLastError());
+          return 0;
+        }))) return rc;
   } else if (c.resnet) {
     cumsum_res_act_kernel<bf16><<<grid_for(h, Bc * N * (E / 4), 256, 16), 256, 0, h->stream>>>(reinterpret_cast<bf16*>(XO), h->RES, Bc, To, N, E, act);
     cumsum_res_act_kernel<bf16><<<grid_for(h, Bc * M * (E / 4), 256, 16), 256, 0, h->stream>>>(reinterpret_cast<bf16*>(EO), h->RESE, Bc, To, M, E, act);
@@ -1784,6 +1906,7 @@ int64_t floats_per_scenario(const gnnuds_config& c) {
 int ensure_workspace(gnnuds_handle* h, int64_t Bc) {
   if (Bc <= h->ws_chunk && h->d_ws) return 0;
   const auto& c = h->c;
+  ++h->buf_gen;
   if (h->d_ws) { cudaFree(h->d_ws); h->d_ws = nullptr; }
   const int64_t E = c.embed, E2 = E / 2, H = c.hidden, N = c.n_node, M = c.n_edge;
   const int64_t Nw = h->nn() ? nn_rows_equiv(c) : N, Mw = h->nn() ? nn_rows_equiv(c) : M;   // activation rows per (b,t)
@@ -1862,6 +1985,7 @@ int finish_timing(gnnuds_handle* h) {
 
 template <typename T>
 int upload(gnnuds_handle* h, T** dst, const T* src, size_t n) {
+  ++h->buf_gen;
   if (*dst) { cudaFree(*dst); *dst = nullptr; }
   if (!n) return 0;
   CU(cudaMalloc(dst, n * sizeof(T)));
@@ -1926,14 +2050,33 @@ int grow(gnnuds_handle* h, int slot, size_t n, float** out) {
     if (h->gb[slot]) { cudaStreamSynchronize(h->stream); cudaFree(h->gb[slot]); h->gb[slot] = nullptr; h->gb_cap[slot] = 0; }
     if (cudaMalloc(&h->gb[slot], n * sizeof(float)) != cudaSuccess) { (void)cudaGetLastError(); return fail(h, GNNUDS_E_NOMEM, "device buffer of %zu MB", (n * 4) >> 20); }
     h->gb_cap[slot] = n;
+    ++h->buf_gen;
   }
   *out = h->gb[slot];
+  return 0;
+}
+
+// Decide whether this chunk runs its node and edge sides concurrently (par2) and make the side's scratch exist.
+// Called by the entry points BEFORE any graph capture (it may allocate) and again, as a no-op, by the forward itself.
+int side_prepare(gnnuds_handle* h, int64_t Bc) {
+  const auto& c = h->c;
+  const int64_t Tm = std::max(c.seq_in, c.seq_out);
+  const int64_t rows = Bc * Tm * std::max(c.n_node, c.n_edge);
+  h->side_on = h->side_par && h->s_side && h->profiling < 2 && !h->debug_stop && !h->nn() && !c.graph_base && !h->use_adj &&
+               std::max(c.n_node, c.n_edge) <= 256 && rows <= 262144;
+  if (!h->side_on) return 0;
+  const int64_t G = c.recurrent == GNNUDS_REC_GRU ? 3 * c.hidden : c.recurrent == GNNUDS_REC_LSTM ? 4 * c.hidden : 0;
+  float* p = nullptr;
+  const int rc = grow(h, 41, (size_t)(rows * std::max<int64_t>(c.embed, G)), &p);     // fp32-sized: covers both precisions
+  if (rc) { h->side_on = false; return rc; }
+  h->HB2 = p;
   return 0;
 }
 
 int ensure_rollout_state(gnnuds_handle* h, int64_t Bc) {
   const auto& c = h->c;
   if (h->ro_B >= Bc && h->ro_x) return 0;
+  ++h->buf_gen;
   for (float** p : {&h->ro_x, &h->ro_ex, &h->ro_b, &h->ro_a}) if (*p) { cudaFree(*p); *p = nullptr; }
   h->ro_B = 0;
   const int64_t T = c.seq_out;
@@ -1996,6 +2139,9 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   cudaEventCreate(&h->ev_a); cudaEventCreate(&h->ev_b);
   cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking);
   cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking);
+  cudaStreamCreateWithFlags(&h->s_side, cudaStreamNonBlocking);
+  cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
   for (int i = 0; i < 2; ++i) {
     cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->ev_comp[i], cudaEventDisableTiming);
@@ -2005,6 +2151,8 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   if (getenv("GNNUDS_FUSED")) h->fused_mode = atoi(getenv("GNNUDS_FUSED"));
   if (getenv("GNNUDS_GRU_TC")) h->gru_tc = atoi(getenv("GNNUDS_GRU_TC"));
   if (getenv("GNNUDS_SP_AGG")) h->sp_agg = atoi(getenv("GNNUDS_SP_AGG"));
+  if (getenv("GNNUDS_GRAPHS")) h->use_graphs = atoi(getenv("GNNUDS_GRAPHS"));
+  if (getenv("GNNUDS_SIDE_PAR")) h->side_par = atoi(getenv("GNNUDS_SIDE_PAR"));
   if (getenv("GNNUDS_TP_FUSED")) h->tp_fused = atoi(getenv("GNNUDS_TP_FUSED"));
   if (getenv("GNNUDS_SP_AGGT")) h->sp_aggt = atoi(getenv("GNNUDS_SP_AGGT"));
   h->sp_g = std::max(1, std::min(8, 128 / std::max(1, std::max(c.n_node, c.n_edge))));
@@ -2120,6 +2268,7 @@ int gnnuds_destroy(gnnuds_handle* h) {
   for (int k = 0; k < 2; ++k) { if (h->pin_in[k]) cudaFreeHost(h->pin_in[k]); if (h->pin_out[k]) cudaFreeHost(h->pin_out[k]); }
   for (float* q : h->gb) if (q) cudaFree(q);
   if (h->bw_arena) cudaFree(h->bw_arena);
+  for (auto& g : h->graphs) cudaGraphExecDestroy(g.second);
   for (auto& e : h->gemm_ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (h->ev_a) cudaEventDestroy(h->ev_a);
   if (h->ev_b) cudaEventDestroy(h->ev_b);
@@ -2129,6 +2278,9 @@ int gnnuds_destroy(gnnuds_handle* h) {
     if (h->ev_out[i]) cudaEventDestroy(h->ev_out[i]);
   }
   if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
+  if (h->s_side) cudaStreamDestroy(h->s_side);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
   if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
   cudaStreamDestroy(h->stream);
   delete h;

@@ -249,6 +249,16 @@ __global__ void __launch_bounds__(256) embed_bf16_kernel(EmbedP p) {
   const unsigned n_iter = (rows + step - 1) / step;   // uniform trip count: shuffles stay convergent
   const int K = KT ? KT : p.K;
   const float* wcol = Ws + c8 * 8;
+  // a thread keeps its column slice for all its rows: with a compile-time channel count the K x 8 weights and the bias
+  // live in registers (re-reading them from shared memory cost 12 LDS.128 per thread and row = 24 clk per row and SM,
+  // twice what the 16-byte stores of the row need at the HBM rate)
+  float wr[KT ? KT : 1][8], br[8];
+#pragma unroll
+  for (int c = 0; c < (KT ? KT : 1); ++c)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) wr[c][j] = KT ? wcol[c * Eo + j] : 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) br[j] = bs[c8 * 8 + j];
   for (unsigned it = 0; it < n_iter; it += 2) {
     EmbedRow q[2];
     q[0] = cur; advance(cur); q[1] = cur; advance(cur);
@@ -272,12 +282,17 @@ __global__ void __launch_bounds__(256) embed_bf16_kernel(EmbedP p) {
       for (int c = 0; c < (KT ? KT : 8); ++c) {      // warp-uniform trip count
         if (!KT && c >= K) break;
         const float xc = __shfl_sync(0xffffffffu, mine[u], c, LPR);
-        const float4 w0 = *reinterpret_cast<const float4*>(wcol + c * Eo), w1 = *reinterpret_cast<const float4*>(wcol + c * Eo + 4);
-        s[0] = fmaf(xc, w0.x, s[0]); s[1] = fmaf(xc, w0.y, s[1]); s[2] = fmaf(xc, w0.z, s[2]); s[3] = fmaf(xc, w0.w, s[3]);
-        s[4] = fmaf(xc, w1.x, s[4]); s[5] = fmaf(xc, w1.y, s[5]); s[6] = fmaf(xc, w1.z, s[6]); s[7] = fmaf(xc, w1.w, s[7]);
+        if (KT) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) s[j] = fmaf(xc, wr[KT ? c : 0][j], s[j]);
+        } else {
+          const float4 w0 = *reinterpret_cast<const float4*>(wcol + c * Eo), w1 = *reinterpret_cast<const float4*>(wcol + c * Eo + 4);
+          s[0] = fmaf(xc, w0.x, s[0]); s[1] = fmaf(xc, w0.y, s[1]); s[2] = fmaf(xc, w0.z, s[2]); s[3] = fmaf(xc, w0.w, s[3]);
+          s[4] = fmaf(xc, w1.x, s[4]); s[5] = fmaf(xc, w1.y, s[5]); s[6] = fmaf(xc, w1.z, s[6]); s[7] = fmaf(xc, w1.w, s[7]);
+        }
       }
-      const float4 b0 = *reinterpret_cast<const float4*>(bs + c8 * 8), b1 = *reinterpret_cast<const float4*>(bs + c8 * 8 + 4);
-      s[0] += b0.x; s[1] += b0.y; s[2] += b0.z; s[3] += b0.w; s[4] += b1.x; s[5] += b1.y; s[6] += b1.z; s[7] += b1.w;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += br[j];
       if (q[u].r < rows) {
         if (p.res && q[u].t == Tn - 1) {
           float* rp = p.res + ((size_t)(q[u].bt / Tn) * Nn + q[u].n) * Eo + c8 * 8;

@@ -141,3 +141,25 @@ def test_mpc_evaluator_gradient():
     assert np.allclose(gz, ev.gradient(yy)[1] * yy * (1 - yy), rtol=1e-5, atol=1e-7)
     hv = ev.hessp(y[0], d[0])
     assert hv.shape == y[0].shape and np.all(np.isfinite(hv))
+
+
+def test_grad_settings_graph_replay_and_eager_agree(monkeypatch):
+    """The gradient body runs as a cached CUDA graph (captured on the first call of a shape, replayed afterwards);
+    GNNUDS_GRAPHS=0 runs the same launches eagerly.  First call, replays with other inputs, and the eager path agree."""
+    case = "c3_ast_act_5"
+    em, _ = cases.setup_product(case)
+    o, _ = cases.make_oracle(case, np.float64)
+    fw, ww, rw, gm = _weights(em.seq_out * 2)
+    s1, b1, a1, e1 = _inputs(em, o, 4, 2, 3)
+    s2, b2, a2, e2 = _inputs(em, o, 4, 2, 4)
+    o1, g1 = em.grad_settings(s1, b1, a1, e1, fw, ww, rw, gm)          # capture + first launch
+    o2, g2 = em.grad_settings(s2, b2, a2, e2, fw, ww, rw, gm)          # replay, other inputs
+    o1r, g1r = em.grad_settings(s1, b1, a1, e1, fw, ww, rw, gm)        # replay, first inputs again
+    assert np.array_equal(o1, o1r) and np.allclose(g1, g1r, rtol=1e-5, atol=1e-7)
+    assert not np.allclose(g1, g2)
+    monkeypatch.setenv("GNNUDS_GRAPHS", "0")
+    em0, _ = cases.setup_product(case)
+    o1e, g1e = em0.grad_settings(s1, b1, a1, e1, fw, ww, rw, gm)
+    o2e, g2e = em0.grad_settings(s2, b2, a2, e2, fw, ww, rw, gm)
+    assert np.array_equal(o1, o1e) and np.array_equal(o2, o2e)
+    assert np.allclose(g1, g1e, rtol=1e-5, atol=1e-7) and np.allclose(g2, g2e, rtol=1e-5, atol=1e-7)
