@@ -449,7 +449,7 @@ int par2(gnnuds_handle* h, FX fx, FE fe) {
 // the body runs eagerly.  The caller has made every buffer the body touches exist BEFORE this call.
 template <class F>
 int run_graphed(gnnuds_handle* h, std::string key, F body) {
-  if (!h->use_graphs || h->profiling || h->debug_stop) return body();
+  if (!h->use_graphs || h->profiling >= 2 || h->debug_stop) return body();
   char gen[48];
   snprintf(gen, sizeof gen, "|g%llu|v%d", (unsigned long long)h->buf_gen, h->pp_variant);
   key += gen;
@@ -2955,32 +2955,43 @@ int gnnuds_evaluate(gnnuds_handle* h, int32_t rule, const float* x0, const float
   struct Restore { gnnuds_handle* h; int v; ~Restore() { h->pp_variant = v; } } restore{h, saved_variant};
   for (int64_t b0 = 0; b0 < B; b0 += Bc) {
     const int64_t nb = std::min(Bc, B - b0);
+    if ((rc = side_prepare(h, nb))) return rc;            // may allocate: before the capture
+    char key[320];
+    snprintf(key, sizeof key, "eval|%lld|%lld|%d|%d|%d|%d|%d|%d|%p|%p|%p|%p|%p|%p|%p|%p|%p", (long long)nb, (long long)b0, n_b, n_step, r_step, n_chunks,
+             rule, h->side_on ? 1 : 0, (const void*)dx0, (const void*)dex0, (const void*)db, (const void*)ddec, (const void*)dfw, (const void*)dww,
+             (const void*)drw, (const void*)dg, (void*)dobj);
+    // the whole block - broadcasts, n_chunks forwards, feedback, objective - is one cached CUDA graph (a small population
+    // is launch-latency-bound: ~45 kernels per chunk)
+    auto block_body = [&]() -> int {
     // one state broadcast over the candidates of the chunk (mpc.py:237-240); q_in of the last observed step
-    bcast_time_kernel<<<grid_for(h, nb * (long long)nx0, 256, 16), 256, 0, h->stream>>>(dx0, h->ro_x, nb, 0, 1, Ti, 0, Ti, (long long)N * c.n_in);
-    bcast_time_kernel<<<grid_for(h, nb * (long long)nex0, 256, 16), 256, 0, h->stream>>>(dex0, h->ro_ex, nb, 0, 1, Ti, 0, Ti, (long long)M * c.e_in);
-    init_prevq_kernel<<<grid_for(h, nb * N, 256, 16), 256, 0, h->stream>>>(dx0 + (size_t)(Ti - 1) * N * c.n_in, prevq, nb, N, c.n_in);
-    h->launches += 3;
-    for (int k = 0; k < n_chunks; ++k) {
-      bcast_time_kernel<<<grid_for(h, nb * T * (long long)N * c.b_in, 256, 16), 256, 0, h->stream>>>(db, h->ro_b, nb, b0, n_b, (int)Th, k * T, T, (long long)N * c.b_in);
-      dec_slice_kernel<<<grid_for(h, nb * T * c.n_act, 256, 16), 256, 0, h->stream>>>(ddec, h->ro_a, nb, b0, n_step, r_step, k * T, T, c.n_act);
-      h->launches += 2;
-      if ((rc = forward_any(h, h->ro_x, h->ro_b, h->ro_a, h->ro_ex, nb, h->out_y, h->out_ey, false))) return rc;
-      ObjAccP op{h->out_y, nyc, prevq, dfw, dww, drw, dg, part, nb, T, N, k * T, k == 0 ? 1 : 0};
-      obj_acc_kernel<<<grid_for(h, nb, 1, 16), 128, 0, h->stream>>>(op);
-      ++h->launches;
-      if (k + 1 < n_chunks) {
-        FeedP p{};
-        p.y = h->out_y; p.ny = nyc; p.ey = h->out_ey; p.e_out = c.e_out; p.b = h->ro_b; p.b_in = c.b_in;
-        p.a = h->ro_a; p.n_act = c.n_act; p.act_of_edge = h->d_act_of_edge;
-        p.x = h->ro_x; p.n_in = c.n_in; p.ex = h->ro_ex; p.e_in = c.e_in;
-        p.S = nb * T; p.N = N; p.M = M; p.if_flood = 1; p.rule = rule;
-        feedback_kernel<<<grid_for(h, p.S * (N + M), 256, 16), 256, 0, h->stream>>>(p);
+      bcast_time_kernel<<<grid_for(h, nb * (long long)nx0, 256, 16), 256, 0, h->stream>>>(dx0, h->ro_x, nb, 0, 1, Ti, 0, Ti, (long long)N * c.n_in);
+      bcast_time_kernel<<<grid_for(h, nb * (long long)nex0, 256, 16), 256, 0, h->stream>>>(dex0, h->ro_ex, nb, 0, 1, Ti, 0, Ti, (long long)M * c.e_in);
+      init_prevq_kernel<<<grid_for(h, nb * N, 256, 16), 256, 0, h->stream>>>(dx0 + (size_t)(Ti - 1) * N * c.n_in, prevq, nb, N, c.n_in);
+      h->launches += 3;
+      for (int k = 0; k < n_chunks; ++k) {
+        bcast_time_kernel<<<grid_for(h, nb * T * (long long)N * c.b_in, 256, 16), 256, 0, h->stream>>>(db, h->ro_b, nb, b0, n_b, (int)Th, k * T, T, (long long)N * c.b_in);
+        dec_slice_kernel<<<grid_for(h, nb * T * c.n_act, 256, 16), 256, 0, h->stream>>>(ddec, h->ro_a, nb, b0, n_step, r_step, k * T, T, c.n_act);
+        h->launches += 2;
+        if ((rc = forward_any(h, h->ro_x, h->ro_b, h->ro_a, h->ro_ex, nb, h->out_y, h->out_ey, false))) return rc;
+        ObjAccP op{h->out_y, nyc, prevq, dfw, dww, drw, dg, part, nb, T, N, k * T, k == 0 ? 1 : 0};
+        obj_acc_kernel<<<grid_for(h, nb, 1, 16), 128, 0, h->stream>>>(op);
         ++h->launches;
+        if (k + 1 < n_chunks) {
+          FeedP p{};
+          p.y = h->out_y; p.ny = nyc; p.ey = h->out_ey; p.e_out = c.e_out; p.b = h->ro_b; p.b_in = c.b_in;
+          p.a = h->ro_a; p.n_act = c.n_act; p.act_of_edge = h->d_act_of_edge;
+          p.x = h->ro_x; p.n_in = c.n_in; p.ex = h->ro_ex; p.e_in = c.e_in;
+          p.S = nb * T; p.N = N; p.M = M; p.if_flood = 1; p.rule = rule;
+          feedback_kernel<<<grid_for(h, p.S * (N + M), 256, 16), 256, 0, h->stream>>>(p);
+          ++h->launches;
+        }
+        CU(cudaGetLastError());
       }
-      CU(cudaGetLastError());
-    }
-    obj_final_kernel<<<grid_for(h, nb, 1, 16), 128, 0, h->stream>>>(part, dobj + b0, nb);
-    ++h->launches;
+      obj_final_kernel<<<grid_for(h, nb, 1, 16), 128, 0, h->stream>>>(part, dobj + b0, nb);
+      ++h->launches;
+      return 0;
+    };
+    if ((rc = run_graphed(h, key, block_body))) return rc;
   }
   if (obj_where == GNNUDS_MEM_HOST) CU(cudaMemcpyAsync(obj, dobj, B * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
   if (h->profiling) CU(cudaEventRecord(h->ev_b, h->stream));
