@@ -99,7 +99,7 @@ def dominant_kernel(em, B, precision):
     if em.graph_base:
         R, nnz = N + M, em.filter_csr.nnz
         per_sample = (nnz * E + R * E) * es
-        return dict(family=2, kernel="agg_large_kernel (CSR neighbour gather, joint node+edge graph)", bound="hbm",
+        return dict(family=2, kernel="agg_large16_kernel (CSR neighbour gather, joint node+edge graph; agg_large_kernel on the fp32 path)" if precision == "bf16" else "agg_large_kernel (CSR neighbour gather, joint node+edge graph)", bound="hbm",
                     bytes=float(B * (Ti + To) * S * per_sample), unit_note="(nnz*E gathered + (N+M)*E written) * %d B per (b,t) sample and layer" % es)
     if precision != "bf16" or em.conv_kind == "nn":
         return dict(family=0, kernel="rows_gemm_f32 (all Dense/conv-linear/Conv1D launches of a step)", bound="fp32", bytes=None, unit_note="")

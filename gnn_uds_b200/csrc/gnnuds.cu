@@ -194,6 +194,7 @@ struct gnnuds_handle {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int side_par = 1;
   bool side_on = false;
+  int joint_per_sample = 0;             // GNNUDS_JOINT_PER_SAMPLE=1: one (b,t) sample at a time in the large joint conv (diagnostic: no gain at C5)
   float* HB2 = nullptr;                 // the edge side's projection / conv scratch while both sides are in flight
   std::vector<std::pair<std::string, cudaGraphExec_t>> graphs;
   std::map<std::string, int64_t> graph_launches;      // kernels per graph (gnnuds_launch_count stays a kernel count)
@@ -590,7 +591,16 @@ int launch_agg(gnnuds_handle* h, const void* hin, void* out, const int* rp, cons
     AggLargeP p{hin, out, rp, ci, val, h->SS, h->SN, bias, S, R, E, act, gat ? 1 : 0};
     cudaEvent_t e1 = nullptr;
     { int prc = prof_begin(h, GNNUDS_FAM_GATHER, &e1); if (prc) return prc; }
-    agg_large_kernel<T><<<grid_for(h, S * R, 8, 32), 256, 0, h->stream>>>(p);
+    const int agg16 = getenv("GNNUDS_AGG16") ? atoi(getenv("GNNUDS_AGG16")) : 1;
+    if (std::is_same<T, bf16>::value && E == 128 && agg16 == 2) {       // 16-byte gathers, one 128-byte row half per pass (diagnostic)
+      if (gat) agg_large16_kernel<8, true, 4><<<grid_for(h, (S * R + 3) / 4, 8, 32), 256, 0, h->stream>>>(p);
+      else agg_large16_kernel<8, false, 4><<<grid_for(h, (S * R + 3) / 4, 8, 32), 256, 0, h->stream>>>(p);
+    } else if (std::is_same<T, bf16>::value && E == 128 && agg16 == 1) {  // 16-byte gathers, whole rows, half a warp per row
+      if (gat) agg_large16_kernel<16, true, 4><<<grid_for(h, (S * R + 1) / 2, 8, 32), 256, 0, h->stream>>>(p);
+      else if (getenv("GNNUDS_AGG_MINB") && atoi(getenv("GNNUDS_AGG_MINB")) == 4) agg_large16_kernel<16, false, 4><<<grid_for(h, (S * R + 1) / 2, 8, 32), 256, 0, h->stream>>>(p);
+      else agg_large16_kernel<16, false, 5><<<grid_for(h, (S * R + 1) / 2, 8, 40), 256, 0, h->stream>>>(p);   // 5 CTAs per SM: more rows in flight
+    } else
+      agg_large_kernel<T><<<grid_for(h, S * R, 8, 32), 256, 0, h->stream>>>(p);
     ++h->launches;
     { int prc = prof_end(h, e1); if (prc) return prc; }
   }
@@ -1849,7 +1859,22 @@ int run_spatial_joint(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int 
     const SpatialW& w = h->sp[blk][l];
     int rc;
     float* jo = (l & 1) ? h->J1 : h->J0;
-    if (TC) {
+    if (TC && h->joint_per_sample && (size_t)R * E * 2 >= (8u << 20) && !h->use_adj) {
+      // Large joint graph: ONE (b,t) sample at a time - linear part of the sample into a single-sample h buffer, then its
+      // gather.  h (51 MB at C5) is re-read ~4x by the neighbour gather; produced and consumed back to back it is still
+      // in the 126 MB L2, whereas the whole-chunk schedule wrote every sample's h to HBM first and gathered it back cold.
+      auto at = [&](const std::vector<SegH>& sg, long long smp) {
+        std::vector<SegH> o = sg;
+        for (SegH& q : o) q.p = reinterpret_cast<const float*>(reinterpret_cast<const bf16*>(q.p) + (size_t)smp * q.pitch * q.ld);
+        return o;
+      };
+      for (long long smp = 0; smp < S; ++smp) {
+        if ((rc = launch_tc_gemm(h, at(st.x, smp), w.joint.t[0], nullptr, h->HBJ, E, E, ACT_LINEAR, 1, N, 1, 1, R, 0))) return rc;
+        if ((rc = launch_tc_gemm(h, at(st.e, smp), w.joint.t[0], nullptr, h->HBJ, E, E, ACT_LINEAR, 1, M, 1, 1, R, N))) return rc;
+        float* jos = reinterpret_cast<float*>(reinterpret_cast<bf16*>(jo) + (size_t)smp * R * E);
+        if ((rc = launch_agg<bf16>(h, h->HBJ, jos, h->d_rp, h->d_ci, h->d_val, w.joint, 1, R, act, false))) return rc;
+      }
+    } else if (TC) {
       if ((rc = launch_tc_gemm(h, st.x, w.joint.t[0], nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, N, T, T, R, 0))) return rc;
       if ((rc = launch_tc_gemm(h, st.e, w.joint.t[0], nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, M, T, T, R, N))) return rc;
       if ((rc = launch_agg<bf16>(h, h->HBJ, jo, h->d_rp, h->d_ci, h->d_val, w.joint, S, R, act, blk == 1))) return rc;
@@ -2153,6 +2178,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   if (getenv("GNNUDS_SP_AGG")) h->sp_agg = atoi(getenv("GNNUDS_SP_AGG"));
   if (getenv("GNNUDS_GRAPHS")) h->use_graphs = atoi(getenv("GNNUDS_GRAPHS"));
   if (getenv("GNNUDS_SIDE_PAR")) h->side_par = atoi(getenv("GNNUDS_SIDE_PAR"));
+  if (getenv("GNNUDS_JOINT_PER_SAMPLE")) h->joint_per_sample = atoi(getenv("GNNUDS_JOINT_PER_SAMPLE"));
   if (getenv("GNNUDS_TP_FUSED")) h->tp_fused = atoi(getenv("GNNUDS_TP_FUSED"));
   if (getenv("GNNUDS_SP_AGGT")) h->sp_aggt = atoi(getenv("GNNUDS_SP_AGGT"));
   h->sp_g = std::max(1, std::min(8, 128 / std::max(1, std::max(c.n_node, c.n_edge))));

@@ -816,6 +816,100 @@ __global__ void __launch_bounds__(256) agg_large_kernel(AggLargeP p) {
   }
 }
 
+// 16-bit storage, E == 128 (the C5 shape).  LPR lanes per row, a lane owns 8 channels (one 16-byte load per neighbour row
+// and lane; the one-warp-per-row kernel above moves 8 bytes per lane), the neighbour loads of a row are issued four at a
+// time before their FMAs.  LPR = 16: the whole 256-byte row per pass.  LPR = 8: TWO passes over the grid, one per
+// 128-byte half of the rows, so that the gather's working set per sample is half the h matrix (25.6 MB at C5 instead of
+// 51 MB - ncu showed 9.5 % L2 hits with the full rows).  Same order of the per-channel FMAs as agg_large_kernel (bitwise
+// equal for GCN).
+template <int LPR, bool GAT, int MINB>
+__global__ void __launch_bounds__(256, MINB) agg_large16_kernel(AggLargeP p) {
+  constexpr int E = 128, RPW = 32 / LPR, NPASS = 16 / LPR;
+  const int lane = threadIdx.x & 31, hl = lane % LPR, sub = lane / LPR;
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  const long long total = p.S * p.R;
+  for (int pass = 0; pass < NPASS; ++pass) {
+    const int c0 = pass * LPR * 8 + hl * 8;                   // this lane's 8 channels
+    const float4 b0 = *reinterpret_cast<const float4*>(p.bias + c0), b1 = *reinterpret_cast<const float4*>(p.bias + c0 + 4);
+    for (long long gw = w; gw * RPW < total; gw += nw) {        // warp-uniform trip count
+      const long long g = gw * RPW + sub;
+      const bool live = g < total;
+      const long long s = live ? g / p.R : 0;
+      const int i = live ? (int)(g % p.R) : 0;
+      const bf16* hb = static_cast<const bf16*>(p.h) + s * p.R * E;
+      const int beg = live ? __ldg(p.row_ptr + i) : 0, end = live ? __ldg(p.row_ptr + i + 1) : 0;
+      float mx = -INFINITY, si = 0.f;
+      if (GAT) {
+        if (live) si = p.ss[s * p.R + i];
+        for (int q = beg + hl; q < end; q += LPR) {
+          float sc = si + p.sn[s * p.R + p.col_idx[q]];
+          sc = sc > 0.f ? sc : 0.2f * sc;
+          mx = fmaxf(mx, sc);
+        }
+#pragma unroll
+        for (int o = LPR / 2; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o, LPR));
+      }
+      float acc[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+      float den = 0.f;
+      const int len = end - beg;
+      int len_w = len;                                          // every row group of the warp walks the longest row
+#pragma unroll
+      for (int o = LPR; o < 32; o <<= 1) len_w = max(len_w, __shfl_xor_sync(0xffffffffu, len_w, o));
+      for (int q0 = 0; q0 < len_w; q0 += LPR) {
+        const int q = beg + q0 + hl;
+        int cj = 0; float wj = 0.f;
+        if (q < end) {
+          cj = __ldg(p.col_idx + q);
+          if (GAT) {
+            float sc = si + p.sn[s * p.R + cj];
+            sc = sc > 0.f ? sc : 0.2f * sc;
+            wj = expf(sc - mx);
+          } else wj = __ldg(p.val + q);
+        }
+        if (GAT) den += wj;
+        const int cnt_w = min(LPR, len_w - q0);
+        for (int u0 = 0; u0 < cnt_w; u0 += 4) {
+          uint4 raw[4]; float wv[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int src = min(u0 + u, LPR - 1);
+            wv[u] = __shfl_sync(0xffffffffu, wj, src, LPR);
+            const int j = __shfl_sync(0xffffffffu, cj, src, LPR);
+            const bool ok = u0 + u < LPR && q0 + u0 + u < len;
+            raw[u] = ok ? *reinterpret_cast<const uint4*>(hb + (size_t)j * E + c0) : make_uint4(0u, 0u, 0u, 0u);
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (u0 + u < LPR && q0 + u0 + u < len) {           // keep the FMA sequence of agg_large_kernel exactly
+              const float2 f0 = unpack2_16(raw[u].x), f1 = unpack2_16(raw[u].y), f2 = unpack2_16(raw[u].z), f3 = unpack2_16(raw[u].w);
+              acc[0] = fmaf(wv[u], f0.x, acc[0]); acc[1] = fmaf(wv[u], f0.y, acc[1]); acc[2] = fmaf(wv[u], f1.x, acc[2]); acc[3] = fmaf(wv[u], f1.y, acc[3]);
+              acc[4] = fmaf(wv[u], f2.x, acc[4]); acc[5] = fmaf(wv[u], f2.y, acc[5]); acc[6] = fmaf(wv[u], f3.x, acc[6]); acc[7] = fmaf(wv[u], f3.y, acc[7]);
+            }
+          }
+        }
+      }
+      if (GAT) {
+#pragma unroll
+        for (int o = LPR / 2; o > 0; o >>= 1) den += __shfl_xor_sync(0xffffffffu, den, o, LPR);
+        const float inv = 1.f / den;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] *= inv;
+      }
+      if (live) {
+        float v[8] = {acc[0] + b0.x, acc[1] + b0.y, acc[2] + b0.z, acc[3] + b0.w, acc[4] + b1.x, acc[5] + b1.y, acc[6] + b1.z, acc[7] + b1.w};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = apply_act(v[k], p.act);
+        const uint4 o4 = make_uint4(pack2_bf16(v[0], v[1]), pack2_bf16(v[2], v[3]), pack2_bf16(v[4], v[5]), pack2_bf16(v[6], v[7]));
+        bf16* dst = static_cast<bf16*>(p.out) + (s * p.R + i) * E + c0;
+        *reinterpret_cast<uint4*>(dst) = o4;
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // K6 GRU recurrence (keras GRU v2, reset_after=True): mx = x_t@K + b[0] comes from
 // rows_gemm; here h_t = z*h + (1-z)*tanh(mx_h + r*(h@R + b[1])_h) walks t in-kernel.
