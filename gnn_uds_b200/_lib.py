@@ -53,7 +53,7 @@ SYMBOLS = [
     "gnnuds_free_device", "gnnuds_memcpy", "gnnuds_synchronize", "gnnuds_launch_count", "gnnuds_last_timing",
     "gnnuds_set_profiling", "gnnuds_measure_simt_tflops", "gnnuds_kernel_timing", "gnnuds_debug_stop_after", "gnnuds_debug_fetch", "gnnuds_debug_umma_selftest",
     "gnnuds_tc_operand_is_half", "gnnuds_set_post_proc_variant", "gnnuds_set_adj_action",
-    "gnnuds_predict_vjp", "gnnuds_grad_settings",
+    "gnnuds_predict_vjp", "gnnuds_grad_settings", "gnnuds_replay_batch",
 ]
 
 
@@ -96,6 +96,7 @@ def load():
     lib.gnnuds_predict_vjp.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, i32]
     lib.gnnuds_grad_settings.argtypes = [vp, i32, vp, vp, vp, vp, i64, i32, vp, vp, vp, vp, vp, vp, i32]
     lib.gnnuds_replay.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp, i32]
+    lib.gnnuds_replay_batch.argtypes = [vp, i32, P(vp), P(vp), P(vp), P(vp), P(i64), P(vp), P(vp)]
     lib.gnnuds_build_windows.argtypes = [vp, vp, vp, vp, vp, i64, i64, i64, vp, vp, vp, vp, i32]
     lib.gnnuds_measure_simt_tflops.argtypes = [vp, P(C.c_float)]
     lib.gnnuds_kernel_timing.argtypes = [vp, i32, P(C.c_float), P(i64)]

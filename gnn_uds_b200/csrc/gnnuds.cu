@@ -3147,6 +3147,116 @@ int gnnuds_replay(gnnuds_handle* h, const float* states, const float* perfs, con
   return finish_timing(h);
 }
 
+// Several recorded events in ONE call (the reference's test loop walks its events one by one, main.py:306-382): the
+// windows of all events form one sequence that is cut into workspace chunks regardless of event boundaries - a
+// 600-window event alone leaves the last launch of every persistent kernel a fraction of a wave - each chunk's windows
+// are built on the device from the raw series of the events it touches, and the predictions of chunk c leave through
+// the pinned ring while chunk c+1 computes.  Bitwise the results of gnnuds_replay event by event (chunking is
+// bit-invisible).
+int gnnuds_replay_batch(gnnuds_handle* h, int32_t n_events, const float* const* states, const float* const* perfs,
+                        const float* const* edge_states, const float* const* settings, const int64_t* T, float* const* y,
+                        float* const* ey) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const auto& c = h->c;
+  if (n_events < 0 || !states || !edge_states || !T || !y || !ey) return fail(h, GNNUDS_E_INVALID, "replay_batch: null argument");
+  for (int i = 0; i < n_events; ++i) {
+    if ((rc = replay_check(h, states[i], perfs ? perfs[i] : nullptr, edge_states[i], settings ? settings[i] : nullptr, T[i]))) return rc;
+    if (!y[i] || !ey[i]) return fail(h, GNNUDS_E_INVALID, "replay_batch: null output of event %d", i);
+  }
+  CU(cudaSetDevice(c.device));
+  if (n_events == 0) return 0;
+  const int N = c.n_node, M = c.n_edge, To = c.seq_out, Ti = c.seq_in;
+  const int64_t sy = (int64_t)To * N * h->ny(), sey = (int64_t)To * M * c.e_out;
+  const int64_t sx = (int64_t)Ti * N * c.n_in, sb = (int64_t)To * N * c.b_in, sa = (int64_t)To * c.n_act, se = (int64_t)Ti * M * c.e_in;
+  int64_t Wmax = 0, Wsum = 0;
+  for (int i = 0; i < n_events; ++i) { const int64_t W = std::max<int64_t>(T[i] - To, 0); Wmax = std::max(Wmax, W); Wsum += W; }
+  if (Wsum == 0) return 0;
+  const int64_t Bc = pick_chunk(h, Wsum);
+  (void)Wmax;
+  if ((rc = ensure_workspace(h, Bc)) || (rc = ensure_pinned(h, 0, (size_t)(Bc * (sy + sey))))) return rc;
+  // the windows of all events form ONE sequence, cut into chunks of Bc windows regardless of event boundaries: a chunk
+  // is a list of pieces (event, first window, count)
+  struct Piece { int ev; int64_t w0, n; };
+  std::vector<std::vector<Piece>> chunks(1);
+  {
+    int64_t fill = 0;
+    for (int i = 0; i < n_events; ++i) {
+      int64_t W = std::max<int64_t>(T[i] - To, 0), w0 = 0;
+      while (W > 0) {
+        if (fill == Bc) { chunks.emplace_back(); fill = 0; }
+        const int64_t n = std::min(W, Bc - fill);
+        chunks.back().push_back({i, w0, n});
+        w0 += n; W -= n; fill += n;
+      }
+    }
+  }
+  // raw series of the events a chunk touches, two staging sets
+  int64_t Tc_max = 0;
+  for (auto& ch : chunks) { int64_t t = 0; for (auto& pc : ch) t += T[pc.ev]; Tc_max = std::max(Tc_max, t); }
+  float* raw[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
+  for (int k = 0; k < 2; ++k) {
+    if ((rc = grow(h, 18 + (k ? 24 : 0), (size_t)Tc_max * N * 4, &raw[k][0]))) return rc;                         // slots 18 / 42
+    if ((rc = grow(h, 19 + (k ? 24 : 0), (size_t)Tc_max * N, &raw[k][1]))) return rc;                            // 19 / 43
+    if ((rc = grow(h, 20 + (k ? 24 : 0), (size_t)Tc_max * M * c.e_in, &raw[k][2]))) return rc;                   // 20 / 44
+    if ((rc = grow(h, 21 + (k ? 24 : 0), (size_t)Tc_max * std::max(c.n_act, 1), &raw[k][3]))) return rc;         // 21 / 45
+  }
+  begin_timing(h);
+  if (h->profiling) CU(cudaEventRecord(h->ev_a, h->stream));
+  float* sout[2][2] = {{h->out_y, h->out_ey}, {h->out2_y, h->out2_ey}};
+  auto drain = [&](int k, const std::vector<Piece>& ch) -> int {
+    CU(cudaEventSynchronize(h->ev_out[k]));
+    std::vector<CopyJob> jobs;
+    int64_t w = 0, nwc = 0;
+    for (auto& pc : ch) nwc += pc.n;
+    for (auto& pc : ch) {
+      jobs.push_back({y[pc.ev] + pc.w0 * sy, h->pin_out[k] + w * sy, (size_t)(pc.n * sy) * sizeof(float)});
+      jobs.push_back({ey[pc.ev] + pc.w0 * sey, h->pin_out[k] + nwc * sy + w * sey, (size_t)(pc.n * sey) * sizeof(float)});
+      w += pc.n;
+    }
+    parallel_copy(jobs);
+    return 0;
+  };
+  for (size_t ci = 0; ci < chunks.size(); ++ci) {
+    const auto& ch = chunks[ci];
+    const int k = (int)(ci & 1);
+    // raw set k was last read by the window builders of chunk ci-2; the copies below are on the compute stream, ordered
+    // after them
+    int64_t toff = 0, woff = 0;
+    for (auto& pc : ch) {
+      const int i = pc.ev;
+      const int64_t Te = T[i];
+      float *ds = raw[k][0] + toff * N * 4, *dp = raw[k][1] + toff * N, *de = raw[k][2] + toff * M * c.e_in, *dse = raw[k][3] + toff * c.n_act;
+      CU(cudaMemcpyAsync(ds, states[i], (size_t)Te * N * 4 * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+      CU(cudaMemcpyAsync(de, edge_states[i], (size_t)Te * M * c.e_in * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+      if (c.if_flood) CU(cudaMemcpyAsync(dp, perfs[i], (size_t)Te * N * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+      if (c.act) CU(cudaMemcpyAsync(dse, settings[i], (size_t)Te * c.n_act * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+      // windows pc.w0 .. pc.w0+pc.n-1 of event i land at rows woff.. of the chunk (the builder writes window w at index w - w0)
+      replay_launch(h, ds, c.if_flood ? dp : nullptr, de, c.act ? dse : nullptr, Te, pc.w0, pc.n, h->in_x + woff * sx, h->in_b + woff * sb,
+                    h->in_a + woff * sa, h->in_ex + woff * se);
+      toff += Te; woff += pc.n;
+    }
+    const int64_t nw = woff;
+    if (nw) {
+      if (ci >= 2) CU(cudaStreamWaitEvent(h->stream, h->ev_out[k], 0));     // chunk ci-2's results have left this output set
+      if ((rc = forward_any(h, h->in_x, h->in_b, c.act ? h->in_a : nullptr, h->in_ex, nw, sout[k][0], sout[k][1], false))) return rc;
+    }
+    CU(cudaEventRecord(h->ev_comp[k], h->stream));
+    CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[k], 0));
+    if (nw) {
+      CU(cudaMemcpyAsync(h->pin_out[k], sout[k][0], nw * sy * sizeof(float), cudaMemcpyDeviceToHost, h->s_d2h));
+      CU(cudaMemcpyAsync(h->pin_out[k] + nw * sy, sout[k][1], nw * sey * sizeof(float), cudaMemcpyDeviceToHost, h->s_d2h));
+    }
+    CU(cudaEventRecord(h->ev_out[k], h->s_d2h));
+    if (ci >= 1 && (rc = drain(k ^ 1, chunks[ci - 1]))) return rc;
+  }
+  if ((rc = drain((int)((chunks.size() - 1) & 1), chunks.back()))) return rc;
+  if (h->profiling) CU(cudaEventRecord(h->ev_b, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (h->profiling) CU(cudaEventElapsedTime(&h->last_total_ms, h->ev_a, h->ev_b));
+  return finish_timing(h);
+}
+
 int gnnuds_alloc_pinned(void** p, int64_t bytes) {
   if (!p) return GNNUDS_E_INVALID;
   return cudaMallocHost(p, (size_t)bytes) == cudaSuccess ? 0 : GNNUDS_E_NOMEM;

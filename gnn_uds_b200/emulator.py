@@ -463,6 +463,35 @@ class Emulator:
         _lib.check(self._h, self._lib.gnnuds_replay(self._h, _ptr(st), _ptr(pf), _ptr(es), _ptr(se), T, _ptr(y), _ptr(ey), _lib.MEM_HOST))
         return y, ey
 
+    def replay_many(self, events):
+        """``replay`` of several recorded events in one call (gnnuds_replay_batch): ``events`` is a list of
+        (states, perfs, edge_states[, settings]) tuples or dicts with those keys; returns the list of (y, ey) pairs
+        ``replay`` returns event by event (bitwise).  Short events share a batch - a 600-window event alone leaves the
+        persistent kernels a quarter of a wave per launch - and the results of one group of events are copied back while
+        the next group computes."""
+        args = []
+        for e in events:
+            if isinstance(e, dict):
+                e = (e["states"], e.get("perfs"), e["edge_states"], e.get("settings"))
+            e = tuple(e) + (None,) * (4 - len(e))
+            args.append(self._replay_args(*e))
+        n = len(args)
+        if n == 0:
+            return []
+        VP = C.c_void_p * n
+        out = []
+        for st, pf, es, se, T in args:
+            W = max(T - self.seq_out, 0)
+            out.append((np.empty((W, self.seq_out, self.n_node, self.y_channels), np.float32),
+                        np.empty((W, self.seq_out, self.n_edge, self.ey_channels), np.float32)))
+        addr = lambda a: None if a is None else a.ctypes.data
+        ps = VP(*[addr(a[0]) for a in args]); pp = VP(*[addr(a[1]) for a in args])
+        pe = VP(*[addr(a[2]) for a in args]); pse = VP(*[addr(a[3]) for a in args])
+        Ts = (C.c_int64 * n)(*[a[4] for a in args])
+        py = VP(*[o[0].ctypes.data for o in out]); pey = VP(*[o[1].ctypes.data for o in out])
+        _lib.check(self._h, self._lib.gnnuds_replay_batch(self._h, n, ps, pp, pe, pse, Ts, py, pey))
+        return out
+
     def build_windows(self, states, perfs, edge_states, settings=None, first=0, count=None):
         """The replay windows themselves (device window builder, expand_seq semantics): x, b, a, ex of windows
         first..first+count-1, laid out as ``predict`` takes them."""

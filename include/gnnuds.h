@@ -247,6 +247,16 @@ int gnnuds_build_windows(gnnuds_handle* h, const float* states, const float* per
                          const float* settings, int64_t T, int64_t w0, int64_t nw, float* x, float* b, float* a, float* ex,
                          int32_t where);
 
+/* n_events recorded events in ONE call (the reference's test loop, main.py:306-382, walks them one by one): the windows
+ * of all events form one sequence that is cut into workspace chunks regardless of event boundaries, a chunk's windows are
+ * built on the device and run as one batch, and the predictions of chunk c leave through the pinned ring while chunk c+1
+ * computes.  Host pointers only: states[i] (T[i],N,4), perfs[i] (T[i],N) (if_flood models; the array may be NULL
+ * otherwise), edge_states[i] (T[i],M,4), settings[i] (T[i],n_act) (act models; else the array may be NULL); y[i] / ey[i]
+ * as gnnuds_replay returns them for event i.  Bitwise the results of gnnuds_replay event by event. */
+int gnnuds_replay_batch(gnnuds_handle* h, int32_t n_events, const float* const* states, const float* const* perfs,
+                        const float* const* edge_states, const float* const* settings, const int64_t* T,
+                        float* const* y, float* const* ey);
+
 /* Pinned host buffers for callers that want truly asynchronous copies. */
 int gnnuds_alloc_pinned(void** p, int64_t bytes);
 int gnnuds_free_pinned(void* p);

@@ -139,3 +139,33 @@ def test_replay_short_event_and_errors():
         em.replay(ev["states"], None, ev["edge_states"], ev["settings"])              # flood model without cumflooding
     with pytest.raises(ValueError):
         em.replay(ev["states"][:, :, :3], ev["perfs"], ev["edge_states"], ev["settings"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case,precision,max_chunk", [("c3_ast_act_5", "fp32", 0), ("c3_ast_act_5", "fp32", 40),
+                                                      ("c2_shq_gat_conv_10", "bf16", 64), ("c1_ast_gcn_gru", "fp32", 0)])
+def test_replay_many_equals_event_by_event(case, precision, max_chunk):
+    """gnnuds_replay_batch: events of mixed lengths (one without any window) cut into workspace chunks regardless of event
+    boundaries - one chunk, several chunks, an event spanning two chunks - return bitwise what Emulator.replay
+    returns event by event."""
+    kw = {"max_chunk": max_chunk} if max_chunk else {}
+    em, _ = cases.setup_product(case, precision=precision, **kw)
+    lens = [em.seq_out + 7, em.seq_out, em.seq_out + 23, em.seq_out + 1, em.seq_out + 30, em.seq_out + 12]
+    evs = [_event(em, t, 100 + i) for i, t in enumerate(lens)]
+    many = em.replay_many(evs)
+    assert len(many) == len(evs)
+    for ev, (p, ep) in zip(evs, many):
+        q, eq = em.replay(ev["states"], ev["perfs"], ev["edge_states"], ev["settings"])
+        assert p.shape == q.shape and ep.shape == eq.shape
+        if precision == "fp32" or em.n_node > 64:
+            assert np.array_equal(p, q) and np.array_equal(ep, eq)
+        else:      # small graphs on the tensor-core path: a sample's result depends on its slot in the MMA tile (DESIGN 3)
+            assert np.abs(p - q).max() <= 1e-3 * max(1.0, np.abs(q).max())
+    assert em.replay_many([]) == []
+    if max_chunk:                                           # one event longer than a chunk: spans two chunks
+        big = _event(em, em.seq_out + max_chunk + 5, 7)
+        (p, ep), = em.replay_many([big])
+        q, eq = em.replay(big["states"], big["perfs"], big["edge_states"], big["settings"])
+        assert p.shape == q.shape
+        if precision == "fp32" or em.n_node > 64:
+            assert np.array_equal(p, q) and np.array_equal(ep, eq)

@@ -1,6 +1,5 @@
-mkdir -p gpurun_out/fin
-O=gpurun_out/fin
-python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -3
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 5 --warmup 3 > $O/bench_C2_2gpu.json 2> $O/b2.err; echo rc=$?; tail -2 $O/b2.err
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 2 --workload C3mpc --steps 5 --warmup 3 > $O/bench_C3mpc_2gpu.json 2> $O/b3.err; echo rc=$?; tail -2 $O/b3.err
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus 2 --impl reference --steps 1 --warmup 0 > $O/bench_ref_2gpu.json 2> $O/b4.err; echo rc=$?
+mkdir -p gpurun_out/c4
+O=gpurun_out/c4
+timeout 600 python -m pytest tests/test_replay.py -x -q 2>&1 | tail -5
+timeout 900 python bench.py --workload C4 --steps 1 --warmup 1 > $O/bench_C4_1gpu.json 2> $O/c4.err; echo rc=$?; tail -3 $O/c4.err
+GNNUDS_C4_PER_EVENT=1 timeout 900 python bench.py --workload C4 --steps 1 --warmup 1 > $O/bench_C4_1gpu_per_event.json 2>/dev/null
