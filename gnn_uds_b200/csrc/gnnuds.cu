@@ -194,6 +194,7 @@ struct gnnuds_handle {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int side_par = 1;
   bool side_on = false;
+  int default_ws_mb = 8192;             // workspace budget when cfg.workspace_mb == 0 (GNNUDS_WORKSPACE_MB overrides)
   int joint_per_sample = 0;             // GNNUDS_JOINT_PER_SAMPLE=1: one (b,t) sample at a time in the large joint conv (diagnostic: no gain at C5)
   float* HB2 = nullptr;                 // the edge side's projection / conv scratch while both sides are in flight
   std::vector<std::pair<std::string, cudaGraphExec_t>> graphs;
@@ -1979,7 +1980,7 @@ int ensure_workspace(gnnuds_handle* h, int64_t Bc) {
 int64_t pick_chunk(const gnnuds_handle* h, int64_t B) {
   const auto& c = h->c;
   if (c.max_chunk > 0) return std::min<int64_t>(B, c.max_chunk);
-  const int64_t budget = (int64_t)(c.workspace_mb > 0 ? c.workspace_mb : 8192 /* include/gnnuds.h: 0 = 8192 MB */) * 1024 * 1024 / 4;
+  const int64_t budget = (int64_t)(c.workspace_mb > 0 ? c.workspace_mb : h->default_ws_mb /* include/gnnuds.h: 0 = 8192 MB */) * 1024 * 1024 / 4;
   int64_t bc = budget / floats_per_scenario(c) * (h->tc() ? 2 : 1);
   if (bc < 1) bc = 1;
   return std::min(B, bc);
@@ -2178,6 +2179,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   if (getenv("GNNUDS_SP_AGG")) h->sp_agg = atoi(getenv("GNNUDS_SP_AGG"));
   if (getenv("GNNUDS_GRAPHS")) h->use_graphs = atoi(getenv("GNNUDS_GRAPHS"));
   if (getenv("GNNUDS_SIDE_PAR")) h->side_par = atoi(getenv("GNNUDS_SIDE_PAR"));
+  if (getenv("GNNUDS_WORKSPACE_MB") && atoi(getenv("GNNUDS_WORKSPACE_MB")) > 0) h->default_ws_mb = atoi(getenv("GNNUDS_WORKSPACE_MB"));
   if (getenv("GNNUDS_JOINT_PER_SAMPLE")) h->joint_per_sample = atoi(getenv("GNNUDS_JOINT_PER_SAMPLE"));
   if (getenv("GNNUDS_TP_FUSED")) h->tp_fused = atoi(getenv("GNNUDS_TP_FUSED"));
   if (getenv("GNNUDS_SP_AGGT")) h->sp_aggt = atoi(getenv("GNNUDS_SP_AGGT"));

@@ -1,5 +1,5 @@
-mkdir -p gpurun_out/c4
-O=gpurun_out/c4
-timeout 600 python -m pytest tests/test_replay.py -x -q 2>&1 | tail -5
-timeout 900 python bench.py --workload C4 --steps 1 --warmup 1 > $O/bench_C4_1gpu.json 2> $O/c4.err; echo rc=$?; tail -3 $O/c4.err
-GNNUDS_C4_PER_EVENT=1 timeout 900 python bench.py --workload C4 --steps 1 --warmup 1 > $O/bench_C4_1gpu_per_event.json 2>/dev/null
+mkdir -p gpurun_out/emb
+O=gpurun_out/emb
+timeout 900 python -m pytest tests/test_tc_parity_gpu.py tests/test_parity_gpu.py tests/test_full_size_gpu.py tests/test_edge_cases_gpu.py tests/test_large_graph_gpu.py -x -q 2>&1 | tail -4
+timeout 600 python bench.py --steps 8 --warmup 3 --no-cpu > $O/b_mma.json 2> $O/b_mma.err; tail -1 $O/b_mma.err
+GNNUDS_EMBED_MMA=0 timeout 600 python bench.py --steps 8 --warmup 3 --no-cpu > $O/b_simt.json 2>/dev/null
