@@ -123,7 +123,7 @@ struct gnnuds_handle {
   int sw128 = 1;                        // GNNUDS_SW128: 0 = 16-byte panel boxes for every TMA-fed operand tile
   int conv1d_tma = 1;                   // GNNUDS_CONV1D_TMA: 0 = cp.async gathers for time-shifted segments
   int fuse_heads = 1;                   // GNNUDS_FUSE_HEADS: 0 = separate cumsum / head kernels (debugging)
-  int fused_mode = 1;                   // GNNUDS_FUSED: 0 layer-by-layer kernels, 1 sp_conv_kernel (default), 2 conv_agg_kernel (experimental)
+  int fused_mode = 1;                   // GNNUDS_FUSED: 0 layer-by-layer kernels, 1 fused spatial kernels (default)
 
   // graph
   int *d_rp = nullptr, *d_ci = nullptr, *d_erp = nullptr, *d_eci = nullptr;
@@ -1595,79 +1595,6 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
   return 0;
 }
 
-// ---- fused conv + aggregation on tensor cores (csrc/fused_conv.cuh) -------------------------------
-// Returns 0 launched, -1 not applicable, > 0 error.
-int launch_conv_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const LayerW& w, void* out, const int* rp,
-                    const int* ci, const float* val, int nnz, long long S, int R, int act) {
-  const auto& c = h->c;
-  const int E = c.embed;
-  const bool gat = c.conv == GNNUDS_CONV_GAT;
-  if (h->fused_mode != 2 || segs.empty() || segs.size() > 3 || R > 256 || R < 1 || E % 32 || E > 128) return -1;
-  if (S <= 0 || S * (long long)R >= (1ll << 31)) return -1;
-  ConvAggP p{};
-  p.nseg = (int)segs.size();
-  p.Ktot = 0;
-  for (int i = 0; i < p.nseg; ++i) {
-    const SegH& sg = segs[i];
-    if (sg.shift || sg.pitch != R || sg.off || sg.width % 16 || sg.ld % 8 || (reinterpret_cast<uintptr_t>(sg.p) & 15)) return -1;
-    p.segw[i] = sg.width; p.Ktot += sg.width;
-  }
-  if ((long long)p.Ktot * E != h->tens[w.t[0]].numel || h->img_off[w.t[0]] < 0) return -1;
-  p.S = (int)S; p.R = R; p.Nout = E; p.act = act; p.gat = gat ? 1 : 0;
-  p.Rbox = (R + 7) / 8 * 8; p.KpJ = (R + 15) / 16 * 16; p.MT = (R + 127) / 128;
-  p.pstrideA = (uint32_t)p.Rbox * 16u; p.pstrideH = (uint32_t)p.KpJ * 16u;
-  p.Wimg = h->d_wimg + h->img_off[w.t[0]]; p.w_bytes = (uint32_t)p.Ktot * E * 2u;
-  p.bias = W(h, w.t[gat ? 3 : 1]);
-  p.a_self = gat ? W(h, w.t[1]) : nullptr; p.a_neigh = gat ? W(h, w.t[2]) : nullptr;
-  p.row_ptr = rp; p.col_idx = ci; p.val = val; p.nnz = nnz;
-  p.out = static_cast<bf16*>(out);
-  auto al = [](uint32_t v, uint32_t a) { return (v + a - 1) / a * a; };
-  p.off_w = 0;
-  p.off_in = al(p.w_bytes, 1024);
-  p.in_bytes = (uint32_t)(p.Ktot / 8) * p.pstrideA;
-  p.alpha_bytes = (uint32_t)(p.KpJ / 8) * p.pstrideA;
-  p.in_stride = al(std::max(p.in_bytes, p.alpha_bytes), 1024);
-  p.off_h = p.off_in + 2 * p.in_stride;
-  const uint32_t h_bytes = (uint32_t)(E / 8) * p.pstrideH;
-  p.off_sc = al(p.off_h + h_bytes, 128);
-  const uint32_t RP = 128u * p.MT;
-  const uint32_t sc_bytes = (3u * E + 2u * RP) * 4u + ((uint32_t)R + 1u + 2u * (uint32_t)nnz) * 4u;
-  p.off_bar = al(p.off_sc + sc_bytes, 16);
-  const uint32_t reach = p.off_in + p.in_stride + (uint32_t)(std::max(p.Ktot, p.KpJ) / 8 - 1) * p.pstrideA + RP * 16u;
-  const size_t smem = std::max<size_t>(p.off_bar + 11 * 8 + 16, reach);
-  if (smem > 227 * 1024) return -1;
-  for (int i = 0; i < p.nseg; ++i)
-    if (!make_rows_tmap(&p.tm[i], segs[i].p, S * R, segs[i].ld, segs[i].width, p.Rbox, segs[i].width)) return -1;
-  if (!h->attr_done[4]) {
-    CU(cudaFuncSetAttribute(conv_agg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    h->attr_done[4] = true;
-  }
-  const unsigned grid = (unsigned)std::min<long long>(S, h->sm_count);
-  static int traced = 0;
-  const char* tf = getenv("GNNUDS_TRACE_FILE");
-  const int want = getenv("GNNUDS_TRACE_LAUNCH") ? atoi(getenv("GNNUDS_TRACE_LAUNCH")) : 0;
-  const bool do_trace = tf && S >= 64 * (long long)h->sm_count && traced++ == want;
-  p.trace_mode = getenv("GNNUDS_TRACE_MODE") ? atoi(getenv("GNNUDS_TRACE_MODE")) : 0;
-  if (do_trace) { CU(cudaMalloc(&p.trace, 64 * 8 * sizeof(long long))); CU(cudaMemset(p.trace, 0, 64 * 8 * sizeof(long long))); }
-  cudaEvent_t e1 = nullptr;
-  { int prc = prof_begin(h, GNNUDS_FAM_SPATIAL, &e1); if (prc) return prc; }
-  conv_agg_kernel<<<grid, CA_THREADS, smem, h->stream>>>(p);
-  ++h->launches;
-  { int prc = prof_end(h, e1); if (prc) return prc; }
-  CU(cudaGetLastError());
-  if (do_trace) {
-    std::vector<long long> t(64 * 8);
-    CU(cudaStreamSynchronize(h->stream));
-    CU(cudaMemcpy(t.data(), p.trace, t.size() * sizeof(long long), cudaMemcpyDeviceToHost));
-    cudaFree(p.trace);
-    if (FILE* f = fopen(tf, "w")) {
-      fprintf(f, "# conv_agg R=%d Ktot=%d: sample, cycles since first stamp: conv_issue_begin conv_committed drain_conv_begin h_ready alpha_ready agg_committed drain_out_begin out_done\n", R, p.Ktot);
-      for (int i = 0; i < 64; ++i) { fprintf(f, "%d", i); for (int k = 0; k < 8; ++k) fprintf(f, " %lld", t[i * 8 + k] ? t[i * 8 + k] - t[0] : -1); fprintf(f, "\n"); }
-      fclose(f);
-    }
-  }
-  return 0;
-}
 
 int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) {
   const auto& c = h->c;
@@ -1695,9 +1622,7 @@ int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) 
           if ((r = launch_tc_gemm(h, sx, w.conv_x.t[0], nullptr, h->HB, E, E, ACT_LINEAR, Bc, N, T, T, N, 0))) return r;
           if ((r = launch_agg<bf16>(h, h->HB, xo, h->d_rp, h->d_ci, h->d_val, w.conv_x, S, N, act, true))) return r;
         } else {
-          r = launch_conv_agg(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, S, N, act);
-          if (r > 0) return r;
-          if (r < 0 && (r = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return r;
+          if ((r = run_conv_tc(h, sx, w.conv_x, xo, h->d_rp, h->d_ci, h->d_val, h->nnz, Bc, T, N, act))) return r;
         }
       }
       return 0;
@@ -1709,9 +1634,7 @@ int run_spatial_tc(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int T) 
       if (r < 0) {
         if ((r = launch_nodeedge<bf16>(h, h->d_ne_matT[1][li], h->ldm_m, h->ti_m, h->EX, h->NE, S, N, M, E2))) return r;
         std::vector<SegH> se = st.e; se.push_back({h->NE, E2, E2, 0, M, 0});
-        r = launch_conv_agg(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, S, M, act);
-        if (r > 0) return r;
-        if (r < 0 && (r = run_conv_tc(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, Bc, T, M, act))) return r;
+        if ((r = run_conv_tc(h, se, w.conv_e, eo, h->d_erp, h->d_eci, h->d_eval, h->ennz, Bc, T, M, act))) return r;
       }
       return 0;
     };

@@ -275,7 +275,7 @@ int gnnuds_set_profiling(gnnuds_handle* h, int32_t on);
 /* With profiling level 2: summed device time and launch count of one kernel family in the last call.
    No reference counterpart (the reference only prints wall-clock "Emulation time", main.py:362). */
 #define GNNUDS_FAM_GEMM 0     /* tc_rows_kernel / rows_gemm_f32: Dense, conv linear, Conv1D, GRU/LSTM projections */
-#define GNNUDS_FAM_SPATIAL 1  /* sp_conv_kernel / conv_agg_kernel: fused NodeEdge + conv + aggregation */
+#define GNNUDS_FAM_SPATIAL 1  /* sp_agg_kernel / sp_aggt_kernel / sp_conv_kernel: fused NodeEdge + conv + aggregation */
 #define GNNUDS_FAM_GATHER 2   /* agg_large_kernel: CSR neighbour gather of the large-graph path */
 #define GNNUDS_FAM_RECURRENT 3 /* gru_kernel / lstm_kernel: in-kernel time loop */
 int gnnuds_kernel_timing(const gnnuds_handle* h, int32_t family, float* ms, int64_t* launches);
