@@ -559,6 +559,113 @@ __global__ void __launch_bounds__(256) feedback_bwd_kernel(const float* __restri
 }
 
 // ---------------------------------------------------------------------------
+// Back-propagation through time of gru_kernel / lstm_kernel (keras GRU reset_after / LSTM, emulator.py:159-163) w.r.t.
+// the input projection mx = x@K + b and, through it, the layer input.  Same tiling as the forward: a CTA owns 32
+// sequences x 8 column groups, R resident in shared memory; per step the gates are recomputed from the taped mx and
+// h_{t-1} (one H x G mat-vec) and the state cotangent is pushed back through R^T (one G x H mat-vec).
+//   GRU : z = s(mx_z + mh_z), r = s(mx_r + mh_r), hh = tanh(mx_h + r mh_h), h' = z h + (1 - z) hh,  mh = h R + b1
+//   LSTM: z = zx + h R, [i f g o] = [s s tanh s](z), c' = f c + i g, h' = o tanh(c')
+// gout (Bc,Td,Nn,H): cotangent of the last Td hidden states; gmx (Bc,Ts,Nn,G) written for every step.
+// ---------------------------------------------------------------------------
+struct RecBwdP {
+  const float* mx;       // (Bc,Ts,Nn,G) taped input projection
+  const float* hall;     // (Bc,Ts,Nn,H) taped hidden states
+  const float* call;     // LSTM: taped cell states
+  const float* R;        // (H,G)
+  const float* b1;       // GRU: (G) recurrent bias
+  const float* gout;     // (Bc,Td,Nn,H)
+  float* gmx;            // (Bc,Ts,Nn,G)
+  long long nseq; int Nn, Ts, Td, H;
+};
+
+template <bool LSTM>
+__global__ void __launch_bounds__(256) rec_bwd_kernel(RecBwdP p) {
+  extern __shared__ __align__(16) float sm[];
+  const int H = p.H, G = (LSTM ? 4 : 3) * H;
+  float* Rs = sm;                    // H*G
+  float* hp = Rs + (size_t)H * G;    // 32*H  h_{t-1}
+  float* mh = hp + 32 * H;           // 32*G  recurrent pre-activations, then their cotangents
+  float* dh = mh + 32 * G;           // 32*H  state cotangent carried to step t-1
+  float* dc = dh + 32 * H;           // 32*H  LSTM cell cotangent
+  const int tid = threadIdx.x;
+  for (int i = tid * 4; i < H * G; i += 256 * 4)
+    *reinterpret_cast<float4*>(Rs + i) = *reinterpret_cast<const float4*>(p.R + i);
+  for (int i = tid; i < 32 * H; i += 256) { dh[i] = 0.f; dc[i] = 0.f; }
+  const int rr = tid >> 3, gg = tid & 7;
+  const long long q = (long long)blockIdx.x * 32 + rr;
+  const bool live = q < p.nseq;
+  const long long b = live ? q / p.Nn : 0;
+  const int n = live ? (int)(q % p.Nn) : 0;
+  const int ncol4 = G / 32;
+  __syncthreads();
+  for (int t = p.Ts - 1; t >= 0; --t) {
+    const size_t row = (size_t)((b * p.Ts + t) * p.Nn + n);
+    const size_t rowp = (size_t)((b * p.Ts + t - 1) * p.Nn + n);
+    for (int u = gg; u < H; u += 8) hp[rr * H + u] = (live && t > 0) ? p.hall[rowp * H + u] : 0.f;
+    __syncthreads();
+    for (int qq = 0; qq < ncol4; ++qq) {             // mh[rr][:] = hp[rr][:] @ R (+ b1)
+      const int col = qq * 32 + gg * 4;
+      float4 s = LSTM ? make_float4(0.f, 0.f, 0.f, 0.f) : *reinterpret_cast<const float4*>(p.b1 + col);
+      for (int k = 0; k < H; ++k) {
+        const float hv = hp[rr * H + k];
+        const float4 rv = *reinterpret_cast<const float4*>(Rs + (size_t)k * G + col);
+        s.x = fmaf(hv, rv.x, s.x); s.y = fmaf(hv, rv.y, s.y); s.z = fmaf(hv, rv.z, s.z); s.w = fmaf(hv, rv.w, s.w);
+      }
+      *reinterpret_cast<float4*>(mh + rr * G + col) = s;
+    }
+    __syncthreads();
+    const int td = t - (p.Ts - p.Td);
+    if (live) {
+      const float* mxr = p.mx + row * G;
+      float* gm = p.gmx + row * G;
+      for (int u = gg; u < H; u += 8) {
+        const float g = dh[rr * H + u] + (td >= 0 ? p.gout[((size_t)((b * p.Td + td) * p.Nn + n)) * H + u] : 0.f);
+        if (!LSTM) {
+          const float z = 1.f / (1.f + expf(-(mxr[u] + mh[rr * G + u])));
+          const float r = 1.f / (1.f + expf(-(mxr[H + u] + mh[rr * G + H + u])));
+          const float mhh = mh[rr * G + 2 * H + u];
+          const float hh = tanhf(mxr[2 * H + u] + r * mhh);
+          const float dz = g * (hp[rr * H + u] - hh), dhh = g * (1.f - z);
+          const float dah = dhh * (1.f - hh * hh);
+          const float daz = dz * z * (1.f - z), dar = dah * mhh * r * (1.f - r);
+          gm[u] = daz; gm[H + u] = dar; gm[2 * H + u] = dah;
+          mh[rr * G + u] = daz; mh[rr * G + H + u] = dar; mh[rr * G + 2 * H + u] = dah * r;
+          dh[rr * H + u] = g * z;
+        } else {
+          const float ig = 1.f / (1.f + expf(-(mxr[u] + mh[rr * G + u])));
+          const float fg = 1.f / (1.f + expf(-(mxr[H + u] + mh[rr * G + H + u])));
+          const float cg = tanhf(mxr[2 * H + u] + mh[rr * G + 2 * H + u]);
+          const float og = 1.f / (1.f + expf(-(mxr[3 * H + u] + mh[rr * G + 3 * H + u])));
+          const float cprev = t > 0 ? p.call[rowp * H + u] : 0.f;
+          const float tc = tanhf(p.call[row * H + u]);
+          const float dcc = dc[rr * H + u] + g * og * (1.f - tc * tc);
+          const float dzi = dcc * cg * ig * (1.f - ig), dzf = dcc * cprev * fg * (1.f - fg);
+          const float dzg = dcc * ig * (1.f - cg * cg), dzo = g * tc * og * (1.f - og);
+          gm[u] = dzi; gm[H + u] = dzf; gm[2 * H + u] = dzg; gm[3 * H + u] = dzo;
+          mh[rr * G + u] = dzi; mh[rr * G + H + u] = dzf; mh[rr * G + 2 * H + u] = dzg; mh[rr * G + 3 * H + u] = dzo;
+          dc[rr * H + u] = dcc * fg;
+          dh[rr * H + u] = 0.f;
+        }
+      }
+    }
+    __syncthreads();
+    // dh[rr][k] += sum_g dmh[rr][g] R[k][g]
+    for (int k = gg; k < H; k += 8) {
+      const float* rk = Rs + (size_t)k * G;
+      const float* dm = mh + rr * G;
+      float s = 0.f;
+      for (int c = 0; c < G; c += 4) {
+        const float4 rv = *reinterpret_cast<const float4*>(rk + c);
+        const float4 dv = *reinterpret_cast<const float4*>(dm + c);
+        s = fmaf(dv.x, rv.x, fmaf(dv.y, rv.y, fmaf(dv.z, rv.z, fmaf(dv.w, rv.w, s))));
+      }
+      dh[rr * H + k] += s;
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------
 // NN-cat ends (csrc/nn_cat.cuh).  VJP of nn_unflatten_kernel + the head activation: the per-node cotangents of a head
 // become the flattened row Gflat[r, n*nc + c] = g[(r*Nn+n), col0+c] * act'(out[...]) (zero in the padded columns).
 // ---------------------------------------------------------------------------

@@ -55,7 +55,10 @@ struct Tape {
   bool on = false;
   float* base = nullptr; size_t cap = 0, used = 0;     // floats
   SpTape sp[2][16];
-  float* tp[2][2][8];                                  // [block][0 node / 1 edge][layer] Conv1D outputs
+  float* tp[2][2][8];                                  // [block][0 node / 1 edge][layer] temporal layer outputs
+  float* mx[2][2][8];                                  // GRU / LSTM: input projection x@K + b of every step
+  float* hall[2][2][8];                                // GRU / LSTM: hidden state of every step
+  float* call[2][2][8];                                // LSTM: cell state of every step
   float *resx = nullptr, *rese = nullptr;              // activated resnet outputs (the heads' input)
   float* flood[8];
   float* alloc(size_t n) {
@@ -650,14 +653,23 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src
     } else {
       const bool gru = c.recurrent == GNNUDS_REC_GRU;
       const int G = (gru ? 3 : 4) * H;
+      float *mxb = h->HB, *hall = nullptr, *call = nullptr;
+      if (h->tape.on && tape_slots) {            // reverse pass (BPTT): the projection and every step's state stay on the tape
+        const long idx = (long)(tape_slots - &h->tape.tp[0][0][0]) / 8;
+        const size_t rws = (size_t)Bc * Ts * Nn;
+        h->tape.mx[idx / 2][idx % 2][i] = mxb = h->tape.alloc(rws * G);
+        h->tape.hall[idx / 2][idx % 2][i] = hall = h->tape.alloc(rws * H);
+        if (!gru) h->tape.call[idx / 2][idx % 2][i] = call = h->tape.alloc(rws * H);
+        if (!mxb || !hall || (!gru && !call)) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (recurrent layer)");
+      }
       // input projection for every time step
-      rc = launch_gemm(h, {{cur, cld, cw, 0, cpitch, coff}}, W(h, L[i].t[0]), W(h, L[i].t[2]) /* b[0] or b */, h->HB, G, G,
+      rc = launch_gemm(h, {{cur, cld, cw, 0, cpitch, coff}}, W(h, L[i].t[0]), W(h, L[i].t[2]) /* b[0] or b */, mxb, G, G,
                        ACT_LINEAR, Bc, Nn, Ts, Ts, Nn, 0);
       if (rc) return rc;
       const long long nseq = Bc * Nn;
       const int g = (int)((nseq + 31) / 32);
       if (gru) {
-        GruP p{h->HB, W(h, L[i].t[1]), W(h, L[i].t[2]) + G, o, nseq, Nn, Ts, Tdst, H};
+        GruP p{mxb, W(h, L[i].t[1]), W(h, L[i].t[2]) + G, o, nseq, Nn, Ts, Tdst, H, hall};
         const size_t smem = ((size_t)H * G + 32 * H + 32 * G) * sizeof(float);
         CU(cudaFuncSetAttribute(gru_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         cudaEvent_t e1 = nullptr;
@@ -665,7 +677,7 @@ int run_temporal(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& src
         gru_kernel<float><<<g, 256, smem, h->stream>>>(p);
         { int prc = prof_end(h, e1); if (prc) return prc; }
       } else {
-        LstmP p{h->HB, W(h, L[i].t[1]), o, nseq, Nn, Ts, Tdst, H};
+        LstmP p{mxb, W(h, L[i].t[1]), o, nseq, Nn, Ts, Tdst, H, hall, call};
         const size_t smem = ((size_t)H * G + 64 * H + 32 * G) * sizeof(float);
         CU(cudaFuncSetAttribute(lstm_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         cudaEvent_t e1 = nullptr;

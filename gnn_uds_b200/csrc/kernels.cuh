@@ -922,6 +922,7 @@ struct GruP {
   void* out;             // (Bc, Td, Nn, H) last Td steps
   long long nseq;        // Bc*Nn
   int Nn, Ts, Td, H;
+  float* hall;           // reverse-pass tape: the hidden state of EVERY step (Bc, Ts, Nn, H), or null
 };
 
 template <typename T>
@@ -966,6 +967,7 @@ __global__ void __launch_bounds__(256) gru_kernel(GruP p) {
         const float hh = tanhf(ld1(mxr + 2 * H + u) + r * mh[rr * G + 2 * H + u]);
         const float hn = z * hs[rr * H + u] + (1.f - z) * hh;
         hs[rr * H + u] = hn;
+        if (p.hall) p.hall[((b * p.Ts + t) * p.Nn + n) * H + u] = hn;
         const int td = t - (p.Ts - p.Td);
         if (td >= 0) st1(static_cast<T*>(p.out) + ((b * p.Td + td) * p.Nn + n) * H + u, hn);
       }
@@ -977,6 +979,7 @@ __global__ void __launch_bounds__(256) gru_kernel(GruP p) {
 // K6 LSTM recurrence (keras LSTM v2; gate order i,f,c,o): zx = x_t@K + b from rows_gemm.
 struct LstmP {
   const void* zx; const float* R; void* out; long long nseq; int Nn, Ts, Td, H;   // zx/out storage type T
+  float* hall; float* call;   // reverse-pass tape: hidden and cell state of EVERY step (Bc, Ts, Nn, H), or null
 };
 
 template <typename T>
@@ -1021,6 +1024,7 @@ __global__ void __launch_bounds__(256) lstm_kernel(LstmP p) {
         const float cn = fg * cs[rr * H + u] + ig * cg;
         const float hn = og * tanhf(cn);
         cs[rr * H + u] = cn; hs[rr * H + u] = hn;
+        if (p.hall) { p.hall[((b * p.Ts + t) * p.Nn + n) * H + u] = hn; p.call[((b * p.Ts + t) * p.Nn + n) * H + u] = cn; }
         const int td = t - (p.Ts - p.Td);
         if (td >= 0) st1(static_cast<T*>(p.out) + ((b * p.Td + td) * p.Nn + n) * H + u, hn);
       }
