@@ -61,6 +61,8 @@ class Emulator:
     def __init__(self, conv=None, resnet=False, recurrent=None, args=None, device=0, precision="fp32",
                  max_chunk=0, workspace_mb=0):
         g = lambda k, d=None: getattr(args, k, d)
+        self._ctor = (conv, resnet, recurrent, args, device, max_chunk, workspace_mb)   # for the fp32 twin of the reverse pass
+        self._twin = None
         # ---- attribute parsing, emulator.py:49-127 ----
         self.n_node, self.n_in = g("state_shape", (40, 4))
         self.tide = bool(g("tide", False))
@@ -538,11 +540,30 @@ class Emulator:
                                                        _ptr(gm), _ptr(obj), _lib.MEM_HOST))
         return obj
 
+    def _grad_emulator(self):
+        """The reverse pass runs on the fp32 path.  A tensor-core emulator keeps an fp32 twin with the same graph, weights
+        and norms for it (created on first use; the weights are re-synchronised whenever they change)."""
+        if self.precision == "fp32":
+            return self
+        if self._twin is None or self._twin_stamp != (id(self.weights), id(getattr(self, "norm_x", None))):
+            conv, resnet, recurrent, args, device, max_chunk, workspace_mb = self._ctor
+            if self._twin is None:
+                self._twin = Emulator(conv, resnet, recurrent, args, device=device, precision="fp32", max_chunk=max_chunk,
+                                      workspace_mb=workspace_mb)
+            if self.weights is None or not hasattr(self, "norm_x"):
+                raise RuntimeError("set_weights / load and set_norm before asking for gradients")
+            self._twin.set_weights(self.weights)
+            self._twin.set_norm(self.norm_x, self.norm_b, self.norm_y, self.norm_r, getattr(self, "norm_e", None))
+            self._twin_stamp = (id(self.weights), id(self.norm_x))
+        return self._twin
+
     def predict_vjp(self, states, b, a, edge_state, gy, gey, wrt=("a", "x", "ex")):
         """Vector-Jacobian product of ``predict_tf`` (what ``tf.GradientTape`` evaluates in mpc.py:596-607): cotangents
         gy (B,seq_out,N,ny) / gey (B,seq_out,M,e_out) of the two outputs -> dict with the forward results ``y``, ``ey``
         and the cotangents ``ga`` (B,seq_out,n_act), ``gx`` (B,seq_in,N,n_in), ``gex`` (B,seq_in,M,e_in) asked for in
-        ``wrt``.  fp32 handles, conv models with Conv1D temporal nets (gnnuds_predict_vjp)."""
+        ``wrt``.  Runs on the fp32 path (gnnuds_predict_vjp); a tensor-core emulator delegates to its fp32 twin."""
+        if self.precision != "fp32":
+            return self._grad_emulator().predict_vjp(states, b, a, edge_state, gy, gey, wrt)
         x = _f32(np.asarray(states)[:, -self.seq_in:])
         ex = _f32(np.asarray(edge_state)[:, -self.seq_in:])
         b = _f32(b)
@@ -567,7 +588,10 @@ class Emulator:
     def grad_settings(self, states, b, a, edge_state, flood_w, wwtp_w, rough_w=None, gamma=None, rule="mpc"):
         """``mpc_problem_gr.gradient_fn`` (mpc.py:596-607) for the astlingen objective: (obj (B,), d obj / d a
         (B,T,n_act)) with T = b.shape[1] a multiple of seq_out - one ``predict_tf`` or the autoregressive chunk loop
-        (mpc.py:565-582) differentiated end to end on the device (gnnuds_grad_settings)."""
+        (mpc.py:565-582) differentiated end to end on the device (gnnuds_grad_settings, fp32 path; a tensor-core emulator
+        delegates to its fp32 twin, so `obj` is the fp32 objective there)."""
+        if self.precision != "fp32":
+            return self._grad_emulator().grad_settings(states, b, a, edge_state, flood_w, wwtp_w, rough_w, gamma, rule)
         code = {"mpc": _lib.ROLL_MPC, "mbrl": _lib.ROLL_MBRL}[rule]
         x = _f32(np.asarray(states)[:, -self.seq_in:])
         ex = _f32(np.asarray(edge_state)[:, -self.seq_in:])

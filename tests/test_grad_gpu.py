@@ -104,11 +104,28 @@ def test_reverse_pass_rejects_unsupported():
     y, ey = em.predict(states, b, a, ex)
     with pytest.raises(GnnUdsError):
         em.predict_vjp(states, b, a, ex, np.ones_like(y), np.ones_like(ey))
+
+
+def test_tensor_core_emulator_delegates_gradients_to_its_fp32_twin():
+    """A tensor-core Emulator evaluates populations in 16-bit and differentiates on the fp32 path: grad_settings /
+    predict_vjp go to a lazily created fp32 twin with the same weights and norms (the C ABI itself rejects a
+    tensor-core handle)."""
+    from gnn_uds_b200._lib import GnnUdsError
+    import gnn_uds_b200._lib as L
     em2, inp2 = cases.setup_product("c3_ast_act_5", precision="bf16")
+    em1, _ = cases.setup_product("c3_ast_act_5", precision="fp32")
     s2, b2, a2, e2 = inp2
     fw, ww, rw, gm = _weights(em2.seq_out)
-    with pytest.raises(GnnUdsError):
-        em2.grad_settings(s2, b2, a2, e2, fw, ww, rw, gm)
+    o2, g2 = em2.grad_settings(s2, b2, a2, e2, fw, ww, rw, gm)
+    o1, g1 = em1.grad_settings(s2, b2, a2, e2, fw, ww, rw, gm)
+    assert np.array_equal(o1, o2) and np.allclose(g1, g2, rtol=1e-5, atol=1e-7)
+    # the raw entry point on the tensor-core handle: rejected, no silent fallback
+    obj = np.empty(s2.shape[0], np.float32); ga = np.empty(a2.shape, np.float32)
+    f = lambda t: np.ascontiguousarray(t, np.float32)
+    x, bb, aa, ee = f(s2[:, -em2.seq_in:]), f(b2), f(a2), f(e2[:, -em2.seq_in:])
+    rc = em2._lib.gnnuds_grad_settings(em2._h, L.ROLL_MPC, x.ctypes.data, bb.ctypes.data, aa.ctypes.data, ee.ctypes.data, x.shape[0], 1,
+                                       fw.ctypes.data, ww.ctypes.data, rw.ctypes.data, gm.ctypes.data, obj.ctypes.data, ga.ctypes.data, L.MEM_HOST)
+    assert rc == -1
 
 
 def test_mpc_evaluator_gradient():
