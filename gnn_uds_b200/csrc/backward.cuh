@@ -372,17 +372,48 @@ struct PostBwdP {
   PostP f;                 // the forward's parameter block (out_n / out_e / a / norms / graph vectors; y, ey unused)
   const float* gy; const float* gey;
   float* g_out_n; float* g_out_e; float* ga;
+  const float* y_final;    // (S,N,ny) the forward's physical node output (depth after the flood / pumped-storage rules)
+  const int* ps; int n_ps; // pumped-storage nodes: their depth comes from the scan (pump_storage_bwd_kernel), not from the head
 };
 
 __global__ void __launch_bounds__(256) postproc_bwd_kernel(PostBwdP q) {
-  extern __shared__ float sh[];     // gO[N] | gI[N] | gefl[M] | efl[M]
+  extern __shared__ float sh[];     // gO[N] | gI[N] | gefl[M] | efl[M] | vpre[M] | pass[M] | hn[N]
   const PostP& p = q.f;
   float* gO = sh; float* gI = gO + p.N; float* gefl = gI + p.N; float* efl = gefl + p.M;
+  float* vpre = efl + p.M;          // last edge channel after the offset / pump rules, before the setting product
+  float* pass = vpre + p.M;         // 1 where that value still depends on the head output, 0 where a rule replaced it
+  float* hn = pass + p.M;           // normalised node depth (tide applied): input of the rules' gates
+  const bool need_h = p.pump || p.offset;
   for (long long s = blockIdx.x; s < p.S; s += gridDim.x) {
     __syncthreads();
-    // ---- recompute the physical edge flows (forward edge pass, no pump / offset) ----
+    if (need_h) {
+      for (int n = threadIdx.x; n < p.N; n += blockDim.x) {
+        float hN = p.out_n[(s * p.N + n) * p.ldn];
+        if (p.tide) {
+          const float braw = p.b_raw[(s * p.N + n) * p.b_in + p.b_in - 1];
+          const float mx = p.bmax[n * p.cb + p.b_in - 1], mn = p.bmin[n * p.cb + p.b_in - 1];
+          hN = hN * (1.f - p.is_outfall[n]) + (braw - mn) / (mx - mn);
+        }
+        hn[n] = hN;
+      }
+      __syncthreads();
+    }
+    // ---- recompute the physical edge flows (forward edge pass incl. the inlet-offset gate and the rated pump flow) ----
     for (int m = threadIdx.x; m < p.M; m += blockDim.x) {
       float v = p.out_e[(s * p.M + m) * p.lde + p.e_out - 1];
+      float ps_ = 1.f;
+      if (p.offset && p.offset[m] > 0.f) {                       // emulator.py:686-693
+        const int fn = p.edge_from[m];
+        const float mx = p.ymax[fn * p.cy], mn = p.ymin[fn * p.cy];
+        const float inoff = (hn[fn] * (mx - mn) + mn) - p.hmin[fn];
+        if (v > 0.f && !(inoff > p.offset[m])) { v = 0.f; ps_ = 0.f; }
+      }
+      if (p.act && p.pump && p.pump[m] != 0.f) {                 // emulator.py:698-701
+        const float mx = p.emax[m * p.ce + p.e_out - 1];
+        const float fl = p.pump[m] * (hn[p.edge_from[m]] > 0.01f ? 1.f : 0.f) * (mx > 1e-3f ? 1.f / mx : 0.f);
+        if (fl != 0.f) { v = fl; ps_ = 0.f; }
+      }
+      vpre[m] = v; pass[m] = ps_;
       if (p.act) { const int k = p.act_of_edge[m]; if (k >= 0) v *= p.a[s * p.n_act + k]; }
       const float mx = p.emax[m * p.ce + p.e_out - 1], mn = p.emin[m * p.ce + p.e_out - 1];
       efl[m] = v * (mx - mn) + mn;
@@ -402,6 +433,9 @@ __global__ void __launch_bounds__(256) postproc_bwd_kernel(PostBwdP q) {
         hN = hN * (1.f - p.is_outfall[n]) + (braw - mn) / (mx - mn);
       }
       float yn1, yn2, pre1 = 0.f, pre2 = 0.f;      // pre*: node-head flows before the setting product (non-fusion)
+      float pass1 = 1.f, pass2 = 1.f;              // 0 where a rated pump flow replaced the head's value
+      bool is_ps = false;
+      for (int k = 0; k < q.n_ps; ++k) is_ps |= q.ps[k] == n;
       const float m1 = p.ymax[n * p.cy + 1], m2 = p.ymax[n * p.cy + 2];
       const float i1 = m1 > 1e-3f ? 1.f / m1 : 0.f, i2 = m2 > 1e-3f ? 1.f / m2 : 0.f;
       int ko = -1, ki = -1;
@@ -415,6 +449,12 @@ __global__ void __launch_bounds__(256) postproc_bwd_kernel(PostBwdP q) {
         yn2 = (op + on) * i2; yn1 = (ip + in_) * i1;
       } else {
         pre1 = src[1]; pre2 = src[2];
+        if (p.act && p.pump_in) {                                // emulator.py:708-713: rated flows replace the head's
+          const float on = hN > (p.tf_rules ? 0.f : 0.01f) ? 1.f : 0.f;
+          const float fli = p.pump_in[n] * on / p.ymax[n * p.cy + 1], flo = p.pump_out[n] * on / p.ymax[n * p.cy + 2];
+          if (fli != 0.f) { pre1 = fli; pass1 = 0.f; }
+          if (flo != 0.f) { pre2 = flo; pass2 = 0.f; }
+        }
         yn1 = pre1; yn2 = pre2;
         if (p.act) {
           ko = p.act_out_of_node[n]; ki = p.act_in_of_node[n];
@@ -436,6 +476,7 @@ __global__ void __launch_bounds__(256) postproc_bwd_kernel(PostBwdP q) {
       const bool in_clip = yp0 >= p.hmin[n] && yp0 <= p.hmax[n];
       float h = fminf(fmaxf(yp0, p.hmin[n]), p.hmax[n]);
       if (fl) h = p.hmax[n];
+      if (q.y_final) h = q.y_final[(s * p.N + n) * p.ny];          // pumped-storage nodes: the scan's depth
       const float r = p.b_raw[(s * p.N + n) * p.b_in];
       const float qraw = yp1 + r - yp2;
       float mask = 1.f - p.is_outfall[n];
@@ -443,7 +484,7 @@ __global__ void __launch_bounds__(256) postproc_bwd_kernel(PostBwdP q) {
       else if (p.epsilon == 0.f) {}
       else if (p.if_flood) mask *= fl ? 1.f : 0.f;
       const float gqw = g[p.ny - 1] * mask * (qraw >= 0.f ? 1.f : 0.f);
-      const float gyp0 = (fl || !in_clip) ? 0.f : g[0];
+      const float gyp0 = (fl || !in_clip || is_ps) ? 0.f : g[0];
       const float gyp1 = g[1] + gqw, gyp2 = g[2] - gqw;
       if (p.if_flood) go[p.n_out] = g[3] * (p.ymax[n * p.cy + 3] - p.ymin[n * p.cy + 3]);
       go[0] = gyp0 * sc0 * (p.tide ? (1.f - p.is_outfall[n]) : 1.f);
@@ -454,7 +495,7 @@ __global__ void __launch_bounds__(256) postproc_bwd_kernel(PostBwdP q) {
         float a_o = 1.f, a_i = 1.f;
         if (ko >= 0) { a_o = p.a[s * p.n_act + ko]; atomicAdd(q.ga + s * p.n_act + ko, gyn2 * pre2); }
         if (ki >= 0) { a_i = p.a[s * p.n_act + ki]; atomicAdd(q.ga + s * p.n_act + ki, gyn1 * pre1); }
-        go[1] = gyn1 * a_i; go[2] = gyn2 * a_o;
+        go[1] = gyn1 * a_i * pass1; go[2] = gyn2 * a_o * pass2;
       }
     }
     __syncthreads();
@@ -483,21 +524,73 @@ __global__ void __launch_bounds__(256) postproc_bwd_kernel(PostBwdP q) {
       for (int c = 0; c < p.e_out; ++c) {
         const float mx = p.emax[m * p.ce + c], mn = p.emin[m * p.ce + c];
         const bool lastc = c == p.e_out - 1;
-        const float v = src[c] * (lastc ? ae : 1.f);
+        const float v = lastc ? vpre[m] * ae : src[c];
         const float phys = v * (mx - mn) + mn;
         float gp = g[c];
         if (c == 0 && !(phys >= 0.f && phys <= p.ehmax[m])) gp = 0.f;     // emulator.py:624 depth clip
         if (lastc) gp += gefl[m];
         const float gv = gp * (mx - mn);
         if (lastc) {
-          go[c] = gv * ae;
-          if (k >= 0) atomicAdd(q.ga + s * p.n_act + k, gv * src[c]);
+          go[c] = gv * ae * pass[m];
+          if (k >= 0) atomicAdd(q.ga + s * p.n_act + k, gv * vpre[m]);
         } else {
           go[c] = gv;
         }
       }
     }
   }
+}
+
+// ---------------------------------------------------------------------------
+// VJP of pump_storage_kernel (emulator.py:626-637): the depth of a pumped-storage node is integrated from the predicted
+// flows, de_0 = clip(h_in[last]), de_t = clip(de_{t-1} + (q_us - q_ds)_t / (area + 1e-6)), and replaces the head's depth.
+// One thread per (scenario, pumped-storage node): the clip flags are recomputed forwards, then the depth cotangents run
+// backwards through the scan into the flow cotangents gy[...,1] / gy[...,2] (in place) and the input state's depth
+// (gx0 (Bc, n_ps), added to gx by ps_gx_add_kernel).  The node's own gy[...,0] is consumed (zeroed).
+// ---------------------------------------------------------------------------
+struct PumpStoreBwdP {
+  const float* y; int ny;        // (Bc,To,N,ny) forward output
+  const float* x; int n_in;      // (Bc,Ti,N,n_in)
+  float* gy;                     // (Bc,To,N,ny) cotangents, modified in place
+  float* gx0;                    // (Bc,n_ps)
+  const int* ps; int n_ps;
+  const float* area; const float* hmin; const float* hmax;
+  long long Bc; int Ti, To, N, if_flood;
+};
+
+__global__ void __launch_bounds__(128) pump_storage_bwd_kernel(PumpStoreBwdP p) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.Bc * p.n_ps) return;
+  const long long b = i / p.n_ps;
+  const int n = p.ps[i % p.n_ps];
+  const float lo = p.hmin[n], hi = p.hmax[n], ar = p.area[n] + 1e-6f;
+  unsigned long long inclip[4] = {0ull, 0ull, 0ull, 0ull};       // To <= 256
+  float de = 0.f;
+  for (int t = 0; t < p.To; ++t) {
+    const float* yy = p.y + ((b * p.To + t) * p.N + n) * p.ny;
+    const float v = t == 0 ? p.x[((b * p.Ti + p.Ti - 1) * p.N + n) * p.n_in] : de + (yy[1] - yy[2]) / ar;
+    if (v >= lo && v <= hi) inclip[t >> 6] |= 1ull << (t & 63);
+    de = fminf(fmaxf(v, lo), hi);
+  }
+  float carry = 0.f;
+  for (int t = p.To - 1; t >= 0; --t) {
+    const size_t o = (size_t)((b * p.To + t) * p.N + n) * p.ny;
+    const bool f = p.if_flood && p.y[o + 3] > 0.5f;
+    const float g = (f ? 0.f : p.gy[o]) + carry;
+    const float gv = (inclip[t >> 6] >> (t & 63)) & 1ull ? g : 0.f;
+    p.gy[o] = 0.f;
+    if (t > 0) { carry = gv; p.gy[o + 1] += gv / ar; p.gy[o + 2] -= gv / ar; }
+    else p.gx0[i] = gv;
+  }
+}
+
+__global__ void __launch_bounds__(128) ps_gx_add_kernel(float* __restrict__ gx, const float* __restrict__ gx0, const int* __restrict__ ps,
+                                                        int n_ps, long long Bc, int Ti, int N, int n_in) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Bc * n_ps) return;
+  const long long b = i / n_ps;
+  const int n = ps[i % n_ps];
+  gx[((b * Ti + Ti - 1) * N + n) * n_in] += gx0[i];
 }
 
 // ---------------------------------------------------------------------------

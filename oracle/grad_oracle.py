@@ -318,7 +318,6 @@ class TorchEmulator:
 
     def predict_tf(self, states, b, a=None, edge_state=None, trace=None):   # emulator.py:604-641
         o = self.o
-        assert not o.has_pumps(), "pumped-storage scan has no gradient oracle"
         x = _t(states)[:, -o.seq_in:, ...]
         ex = _t(edge_state)[:, -o.seq_in:, ...]
         b = _t(b)
@@ -330,6 +329,16 @@ class TorchEmulator:
         ey = self.normalize(ey, "e", True)
         ey = torch.cat([torch.maximum(torch.minimum(ey[..., 0], _t(o.ehmax)), torch.zeros(()).to(DT))[..., None], ey[..., 1:]], dim=-1)
         y = self.normalize(y, "y", True)
+        if o.has_pumps():                                            # emulator.py:626-637 pumped-storage depth
+            ps = _t((o.area * np.matmul(np.clip(o.node_edge.astype(np.float64), 0, 1), o.pump)) > 0)
+            h, qin, qout = [y[..., i] for i in (0, 1, 2)]
+            lo, hi, ar = _t(o.hmin), _t(o.hmax), _t(o.area + 1e-6)
+            de = []
+            for t in range(o.seq_out):
+                v = x[:, -1, :, 0] if t == 0 else de[-1] + (qin - qout)[:, t, :] / ar
+                de.append(torch.maximum(torch.minimum(v, hi), lo))
+            de = torch.stack(de, dim=1)
+            y = torch.cat([(h * (1 - ps) + de * ps)[..., None], y[..., 1:]], dim=-1)
         q_w, y = self.constrain_tf(y, b[..., :1])
         return torch.cat([y, q_w[..., None]], dim=-1), ey
 

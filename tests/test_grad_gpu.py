@@ -35,7 +35,8 @@ def _rel(got, ref):
 @pytest.mark.parametrize("case,chunks", [("c3_ast_act_5", 1), ("c3_ast_act_5", 3), ("ast_gcn_conv_act_nofusion", 1),
                                          ("ast_gcn_conv_act_nofusion", 2), ("ast_nn_conv_act_fusion", 1),
                                          ("ast_nn_conv_act_fusion", 2), ("ast_gcn_lstm_act_nofusion", 1),
-                                         ("ast_gcn_lstm_act_nofusion", 2)])
+                                         ("ast_gcn_lstm_act_nofusion", 2), ("ast_pump_act_fusion", 1), ("ast_pump_act_fusion", 2),
+                                         ("ast_pump_act_nofusion", 1), ("ast_head_tide_offset", 1)])
 def test_grad_settings_matches_autograd(case, chunks):
     from oracle import grad_oracle as go
     em, _ = cases.setup_product(case)
@@ -60,7 +61,7 @@ def test_grad_settings_matches_autograd(case, chunks):
 
 @pytest.mark.parametrize("case", ["c3_ast_act_5", "ast_gcn_conv_eps0", "c2_shq_gat_conv_10", "ast_gcn_conv_act_nofusion",
                                   "ast_nn_conv_act_fusion", "c1_ast_gcn_gru", "ast_gat_gru_noflood", "ast_gcn_lstm_act_nofusion",
-                                  "shq_nn_gru"])
+                                  "shq_nn_gru", "ast_pump_act_fusion", "ast_pump_act_nofusion", "ast_head_tide_offset"])
 def test_predict_vjp_matches_autograd(case):
     """Random cotangents on every output channel; gradients w.r.t. settings, states and edge states."""
     from oracle import grad_oracle as go

@@ -7,7 +7,7 @@ import pytest
 import cases
 
 GRAD_CASES = ["c3_ast_act_5", "ast_gcn_lstm_act_nofusion", "ast_joint_gat_conv_act", "ast_head_tide_offset",
-              "ast_nn_conv_act_fusion"]
+              "ast_nn_conv_act_fusion", "ast_pump_act_fusion", "ast_pump_act_nofusion"]
 
 
 def _weights(o, seed=3):
@@ -30,7 +30,8 @@ def test_torch_forward_equals_numpy_oracle(case):
 
 
 @pytest.mark.parametrize("case,chunks", [("c3_ast_act_5", 1), ("c3_ast_act_5", 2), ("ast_gcn_lstm_act_nofusion", 1),
-                                         ("ast_nn_conv_act_fusion", 2)])
+                                         ("ast_nn_conv_act_fusion", 2), ("ast_pump_act_fusion", 1), ("ast_pump_act_nofusion", 1),
+                                         ("ast_head_tide_offset", 1)])
 def test_autograd_equals_finite_differences(case, chunks):
     from oracle import grad_oracle as go
     from oracle.emulator_oracle import astlingen_objective  # noqa: F401  (same formula, weight-vector form below)
@@ -70,10 +71,11 @@ def test_autograd_equals_finite_differences(case, chunks):
     assert err <= 1e-5
 
 
-def test_vjp_wrt_inputs_equals_finite_differences():
-    """predict_vjp: random cotangents, gradient w.r.t. a few entries of the state / edge state / settings."""
+@pytest.mark.parametrize("case", ["c3_ast_act_5", "ast_pump_act_fusion", "ast_head_tide_offset"])
+def test_vjp_wrt_inputs_equals_finite_differences(case):
+    """predict_vjp: random cotangents, gradient w.r.t. a few entries of the state / edge state / settings (the pumped case
+    runs the pumped-storage depth scan, emulator.py:626-637, whose depth depends on the input state and the flows)."""
     from oracle import grad_oracle as go
-    case = "c3_ast_act_5"
     o, inp = cases.make_oracle(case, np.float64)
     states, b, a, ex = [np.asarray(v, np.float64)[:2] for v in inp]
     rng = np.random.default_rng(5)
