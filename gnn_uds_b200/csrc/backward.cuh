@@ -38,6 +38,7 @@ struct BwdGemmP {
   int accumulate;
   long long rows_out;           // Bc*Ts*Nn
   int Nn, Td, Ts;
+  int pitch_g, off_g;           // cotangent / output-value rows of a (b,t) sample start at (b*Td+t)*pitch_g + off_g (joint node+edge buffers)
 };
 
 __global__ void __launch_bounds__(256) bwd_gemm_kernel(BwdGemmP p) {
@@ -65,7 +66,7 @@ __global__ void __launch_bounds__(256) bwd_gemm_kernel(BwdGemmP p) {
       const int tp = (int)(bt % p.Ts);
       const long long b = bt / p.Ts;
       const int t = tp - dT + p.tap[j].shift;
-      if (t >= 0 && t < p.Td) r_src = (b * p.Td + t) * p.Nn + n;
+      if (t >= 0 && t < p.Td) r_src = (b * p.Td + t) * p.pitch_g + p.off_g + n;
     }
     const int kk = col0 + lr;                      // W row handled by this loader thread
     for (int c0 = 0; c0 < p.Nout; c0 += BK) {
@@ -153,7 +154,31 @@ struct AggBwdP {
   const int* row_ptr; const int* col_idx; const float* val;
   const float* a_self; const float* a_neigh;
   long long S; int R, E, act, gat;
+  // use_adj (emulator.py:268-271, 343-362): the per-sample attention mask of the forward (AggP), a constant of the VJP
+  const int* act_entry; const unsigned char* keep; const float* a_dyn; int n_act;
 };
+
+__device__ __forceinline__ bool aggb_kept(const AggBwdP& p, long long s, int q, int i, int j) {
+  if (!p.a_dyn || i == j) return true;
+  const int k = p.act_entry[q];
+  return k ? truncf(p.a_dyn[s * p.n_act + k - 1]) != 0.f : p.keep[q] != 0;
+}
+
+// VJP of nothing: packs the node / edge stream cotangents (S,N,E), (S,M,E) into the joint layout (S,N+M,E) of graph_base != 0
+__global__ void __launch_bounds__(256) joint_pack_kernel(const float* __restrict__ gx, const float* __restrict__ ge, float* __restrict__ gj,
+                                                         long long S, int N, int M, int E) {
+  const int R = N + M, e4 = E >> 2;
+  const long long total = S * R * e4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % e4);
+    const long long sr = i / e4;
+    const int r = (int)(sr % R);
+    const long long s = sr / R;
+    const float4 v = r < N ? *reinterpret_cast<const float4*>(gx + ((s * N + r) * E) + c * 4)
+                           : *reinterpret_cast<const float4*>(ge + ((s * M + r - N) * E) + c * 4);
+    *reinterpret_cast<float4*>(gj + sr * E + c * 4) = v;
+  }
+}
 
 __global__ void __launch_bounds__(256) agg_bwd_kernel(AggBwdP p) {
   extern __shared__ __align__(16) float sm[];
@@ -208,14 +233,14 @@ __global__ void __launch_bounds__(256) agg_bwd_kernel(AggBwdP p) {
       for (int q = beg + lane; q < end; q += 32) {
         float z = si + sn[p.col_idx[q]];
         z = z > 0.f ? z : 0.2f * z;
-        mx = fmaxf(mx, z);
+        if (aggb_kept(p, s, q, i, p.col_idx[q])) mx = fmaxf(mx, z);
       }
       mx = warp_max(mx);
       float den = 0.f;
       for (int q = beg + lane; q < end; q += 32) {
         float z = si + sn[p.col_idx[q]];
         z = z > 0.f ? z : 0.2f * z;
-        den += expf(z - mx);
+        if (aggb_kept(p, s, q, i, p.col_idx[q])) den += expf(z - mx);
       }
       den = warp_sum(den);
       const float inv = 1.f / den;
@@ -223,6 +248,7 @@ __global__ void __launch_bounds__(256) agg_bwd_kernel(AggBwdP p) {
       float ti = 0.f;
       for (int q = beg; q < end; ++q) {
         const int j = p.col_idx[q];
+        if (!aggb_kept(p, s, q, i, j)) continue;
         float z = si + sn[j];
         z = z > 0.f ? z : 0.2f * z;
         const float alpha = expf(z - mx) * inv;
@@ -235,6 +261,7 @@ __global__ void __launch_bounds__(256) agg_bwd_kernel(AggBwdP p) {
       float dsi = 0.f;
       for (int q = beg; q < end; ++q) {
         const int j = p.col_idx[q];
+        if (!aggb_kept(p, s, q, i, j)) continue;
         const float zr = si + sn[j];
         const float z = zr > 0.f ? zr : 0.2f * zr;
         const float alpha = expf(z - mx) * inv;

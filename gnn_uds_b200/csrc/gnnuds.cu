@@ -1795,6 +1795,12 @@ int run_spatial_joint(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int 
     const SpatialW& w = h->sp[blk][l];
     int rc;
     float* jo = (l & 1) ? h->J1 : h->J0;
+    float* hbj = h->HBJ;
+    if (!TC && h->tape.on) {            // reverse pass: h = [x ; e] @ W and the layer output stay alive on the tape
+      SpTape& tp = h->tape.sp[blk][l];
+      tp.HBx = hbj = h->tape.alloc((size_t)S * R * E); tp.xo = jo = h->tape.alloc((size_t)S * R * E);
+      if (!hbj || !jo) return fail(h, GNNUDS_E_NOMEM, "activation tape exhausted (joint spatial layer)");
+    }
     if (TC && h->joint_per_sample && (size_t)R * E * 2 >= (8u << 20) && !h->use_adj) {
       // Large joint graph: ONE (b,t) sample at a time - linear part of the sample into a single-sample h buffer, then its
       // gather.  h (51 MB at C5) is re-read ~4x by the neighbour gather; produced and consumed back to back it is still
@@ -1815,9 +1821,9 @@ int run_spatial_joint(gnnuds_handle* h, int blk, Stream2& st, long long Bc, int 
       if ((rc = launch_tc_gemm(h, st.e, w.joint.t[0], nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, M, T, T, R, N))) return rc;
       if ((rc = launch_agg<bf16>(h, h->HBJ, jo, h->d_rp, h->d_ci, h->d_val, w.joint, S, R, act, blk == 1))) return rc;
     } else {
-      if ((rc = launch_gemm(h, st.x, W(h, w.joint.t[0]), nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, N, T, T, R, 0))) return rc;
-      if ((rc = launch_gemm(h, st.e, W(h, w.joint.t[0]), nullptr, h->HBJ, E, E, ACT_LINEAR, Bc, M, T, T, R, N))) return rc;
-      if ((rc = launch_agg<float>(h, h->HBJ, jo, h->d_rp, h->d_ci, h->d_val, w.joint, S, R, act, blk == 1))) return rc;
+      if ((rc = launch_gemm(h, st.x, W(h, w.joint.t[0]), nullptr, hbj, E, E, ACT_LINEAR, Bc, N, T, T, R, 0))) return rc;
+      if ((rc = launch_gemm(h, st.e, W(h, w.joint.t[0]), nullptr, hbj, E, E, ACT_LINEAR, Bc, M, T, T, R, N))) return rc;
+      if ((rc = launch_agg<float>(h, hbj, jo, h->d_rp, h->d_ci, h->d_val, w.joint, S, R, act, blk == 1))) return rc;
     }
     st.x = {{jo, E, E, 0, R, 0}};
     st.e = {{jo, E, E, 0, R, N}};

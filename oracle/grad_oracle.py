@@ -114,7 +114,7 @@ class TorchEmulator:
                 x = self._lstm(x, w[0], w[1], w[2])
         return x
 
-    def model(self, X, Bn, E_in, AE=None, trace=None):
+    def model(self, X, Bn, E_in, AE=None, trace=None, A_dyn=None):
         """build_network (emulator.py:195-340) on normalised inputs; ``trace`` collects named intermediates
         (with retain_grad) for stage-wise debugging of a VJP."""
         o = self.o
@@ -143,7 +143,7 @@ class TorchEmulator:
         if o.act:
             w = next(it); ae = keep("aemb", _dense(AE, w, o.activation))
 
-        def spatial(x, e, blk):
+        def spatial(x, e, blk, filt=filt):
             for l in range(o.n_sp_layer):
                 if o.graph_base:
                     z = self._conv(torch.cat([x, e], dim=-2), filt, next(it))
@@ -171,7 +171,10 @@ class TorchEmulator:
         if o.act:
             e = torch.cat([e, ae], dim=-1)
         x = x.reshape((-1,) + tuple(x.shape[2:])); e = e.reshape((-1,) + tuple(e.shape[2:]))
-        x, e = spatial(x, e, 2)
+        if A_dyn is not None:                                        # use_adj (emulator.py:268-269): per-sample node adjacency
+            x, e = spatial(x, e, 2, _t(A_dyn).reshape((-1,) + tuple(A_dyn.shape[-2:])))
+        else:
+            x, e = spatial(x, e, 2)
         x = x.reshape((B, To, N, -1)); e = e.reshape((B, To, M, -1))
         x = self._temporal(x.permute(0, 2, 1, 3).reshape((B * N, To, -1)), it)
         x = x.reshape((B, N, To, H)).permute(0, 2, 1, 3)
@@ -324,7 +327,10 @@ class TorchEmulator:
         a = _t(a) if a is not None else None
         ae = self.get_edge_action(a) if o.act else None
         nb = self.normalize(b, "b")
-        y, ey = self.model(self.normalize(x, "x"), nb, self.normalize(ex, "e"), ae, trace)
+        adj = None
+        if o.act and getattr(o, "use_adj", False):                   # `adj.astype(int)`: a constant of the differentiation
+            adj = o.get_adj_action(a.detach().numpy()[:, :o.seq_out]).astype(np.float64)
+        y, ey = self.model(self.normalize(x, "x"), nb, self.normalize(ex, "e"), ae, trace, adj)
         y, ey = self.post_proc_tf(y, ey, a, nb)
         ey = self.normalize(ey, "e", True)
         ey = torch.cat([torch.maximum(torch.minimum(ey[..., 0], _t(o.ehmax)), torch.zeros(()).to(DT))[..., None], ey[..., 1:]], dim=-1)

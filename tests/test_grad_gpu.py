@@ -36,7 +36,9 @@ def _rel(got, ref):
                                          ("ast_gcn_conv_act_nofusion", 2), ("ast_nn_conv_act_fusion", 1),
                                          ("ast_nn_conv_act_fusion", 2), ("ast_gcn_lstm_act_nofusion", 1),
                                          ("ast_gcn_lstm_act_nofusion", 2), ("ast_pump_act_fusion", 1), ("ast_pump_act_fusion", 2),
-                                         ("ast_pump_act_nofusion", 1), ("ast_head_tide_offset", 1)])
+                                         ("ast_pump_act_nofusion", 1), ("ast_head_tide_offset", 1),
+                                         ("ast_joint_gat_conv_act", 1), ("ast_gat_use_adj", 1), ("ast_gat_use_adj", 2),
+                                         ("ast_edgebased_gcn_lstm_act", 1), ("ast_edgebased_gcn_lstm_act", 2)])
 def test_grad_settings_matches_autograd(case, chunks):
     from oracle import grad_oracle as go
     em, _ = cases.setup_product(case)
@@ -61,7 +63,8 @@ def test_grad_settings_matches_autograd(case, chunks):
 
 @pytest.mark.parametrize("case", ["c3_ast_act_5", "ast_gcn_conv_eps0", "c2_shq_gat_conv_10", "ast_gcn_conv_act_nofusion",
                                   "ast_nn_conv_act_fusion", "c1_ast_gcn_gru", "ast_gat_gru_noflood", "ast_gcn_lstm_act_nofusion",
-                                  "shq_nn_gru", "ast_pump_act_fusion", "ast_pump_act_nofusion", "ast_head_tide_offset"])
+                                  "shq_nn_gru", "ast_pump_act_fusion", "ast_pump_act_nofusion", "ast_head_tide_offset",
+                                  "ast_joint_gat_conv_act", "ast_joint_gcn_gru_act", "ast_gat_use_adj", "ast_edgebased_gcn_lstm_act"])
 def test_predict_vjp_matches_autograd(case):
     """Random cotangents on every output channel; gradients w.r.t. settings, states and edge states."""
     from oracle import grad_oracle as go
@@ -98,13 +101,20 @@ def _vjp_no_act(go, o, states, b, ex, gy, gey):
     return y.detach().numpy(), ey.detach().numpy(), None, st.grad.numpy(), et.grad.numpy()
 
 
-def test_reverse_pass_rejects_unsupported():
+def test_reverse_pass_argument_errors():
     from gnn_uds_b200._lib import GnnUdsError
-    em, inp = cases.setup_product("ast_joint_gcn_gru_act")       # joint node+edge graph
+    em, inp = cases.setup_product("c1_ast_gcn_gru")              # no control input: no settings gradient to ask for
     states, b, a, ex = inp
-    y, ey = em.predict(states, b, a, ex)
-    with pytest.raises(GnnUdsError):
-        em.predict_vjp(states, b, a, ex, np.ones_like(y), np.ones_like(ey))
+    fw, ww, rw, gm = _weights(em.seq_out)
+    with pytest.raises(Exception):
+        em.grad_settings(states, b, np.ones((states.shape[0], em.seq_out, 1), np.float32), ex, fw, ww, rw, gm)
+    em2, inp2 = cases.setup_product("c3_ast_act_5")
+    s2, b2, a2, e2 = inp2
+    y, ey = em2.predict(s2, b2, a2, e2)
+    with pytest.raises(ValueError):
+        em2.predict_vjp(s2, b2, a2, e2, np.ones_like(y)[:, :-1], np.ones_like(ey))     # cotangent of the wrong shape
+    with pytest.raises(ValueError):
+        em2.grad_settings(s2, b2[:, :-1], a2, e2, fw, ww, rw, gm)                       # horizon not a whole number of chunks
 
 
 def test_tensor_core_emulator_delegates_gradients_to_its_fp32_twin():

@@ -7,7 +7,8 @@ import pytest
 import cases
 
 GRAD_CASES = ["c3_ast_act_5", "ast_gcn_lstm_act_nofusion", "ast_joint_gat_conv_act", "ast_head_tide_offset",
-              "ast_nn_conv_act_fusion", "ast_pump_act_fusion", "ast_pump_act_nofusion"]
+              "ast_nn_conv_act_fusion", "ast_pump_act_fusion", "ast_pump_act_nofusion", "ast_gat_use_adj",
+              "ast_edgebased_gcn_lstm_act"]
 
 
 def _weights(o, seed=3):
