@@ -213,9 +213,10 @@ int gnnuds_evaluate(gnnuds_handle* h, int32_t rule, const float* x0, const float
  * activations on a tape (grow-only arena of the handle); sub-gradients as TensorFlow defines them (relu'(0) = 0,
  * clip_by_value passes the gradient on the closed interval, comparisons carry none).  The flood-flag input channel and
  * thresholds (flood prob > 0.5, epsilon mask) are treated as constants, as GradientTape does.
- * Supported: conv models (GCN / GAT) with graph_base 0 and the NN-cat variant, Conv1D / GRU / LSTM temporal nets, fp32
- * handles, pumped / offset networks included (post_proc_tf rules, pumped-storage scan), without use_adj; anything else
- * returns GNNUDS_E_INVALID. */
+ * Supported: conv models (GCN / GAT; per-side graphs, the joint graph of graph_base != 0, use_adj on the per-side graph)
+ * and the NN-cat variant, Conv1D / GRU / LSTM temporal nets, pumped / offset networks (post_proc_tf rules, pumped-storage
+ * scan), fp32 handles.  GNNUDS_E_INVALID for tensor-core handles and for graphs whose per-sample rows exceed the
+ * aggregation VJP's shared memory (3 * rows * embed floats <= 227 KB). */
 int gnnuds_predict_vjp(gnnuds_handle* h, const float* x, const float* b, const float* a, const float* ex, int64_t B,
                        const float* gy, const float* gey, float* y, float* ey, float* ga, float* gx, float* gex,
                        int32_t where);
