@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(256) embed_bf16_kernel(EmbedP p) {
         mine[u] = __ldg(p.in + (size_t)q[u].r * K + c8);
         if (p.nmax) {
           const float mx = __ldg(p.nmax + q[u].n * p.cn + c8), mn = __ldg(p.nmin + q[u].n * p.cn + c8);
-          mine[u] = (mine[u] - mn) / (mx - mn);
+          mine[u] = __fdividef(mine[u] - mn, mx - mn);      // 2 ulp: far below the 16-bit rounding of this path's output
         }
       }
     }
