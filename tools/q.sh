@@ -1,4 +1,5 @@
-mkdir -p gpurun_out/emb
-O=gpurun_out/emb
-timeout 900 python -m pytest tests/test_tc_parity_gpu.py tests/test_full_size_gpu.py tests/test_edge_cases_gpu.py -x -q 2>&1 | tail -3
-timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu > $O/b_fdiv.json 2> $O/b_fdiv.err; tail -1 $O/b_fdiv.err
+mkdir -p gpurun_out/mpc
+O=gpurun_out/mpc
+for P in 256 1024; do
+timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none --cache-control none --csv --log-file $O/traffic_nc_$P.csv python tools/mpc_traffic.py $P > $O/ncu_nc_$P.log 2>&1; echo rc=$?
+done
