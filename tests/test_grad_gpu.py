@@ -194,3 +194,57 @@ def test_grad_settings_graph_replay_and_eager_agree(monkeypatch):
     o2e, g2e = em0.grad_settings(s2, b2, a2, e2, fw, ww, rw, gm)
     assert np.array_equal(o1, o1e) and np.array_equal(o2, o2e)
     assert np.allclose(g1, g1e, rtol=1e-5, atol=1e-7) and np.allclose(g2, g2e, rtol=1e-5, atol=1e-7)
+
+
+def test_device_pointer_entry_points_equal_host_ones():
+    """gnnuds_grad_settings / gnnuds_predict_vjp with where = GNNUDS_MEM_DEVICE (caller-owned device buffers, allocated here
+    through gnnuds_alloc_device / gnnuds_memcpy): the same results as the host-pointer calls, in place in the caller's
+    buffers; B = 0 is a no-op."""
+    import ctypes as C
+    import gnn_uds_b200._lib as L
+    em, _ = cases.setup_product("c3_ast_act_5")
+    o, _ = cases.make_oracle("c3_ast_act_5", np.float64)
+    chunks = 2
+    states, b, a, ex = _inputs(em, o, 3, chunks, 17)
+    fw, ww, rw, gm = _weights(em.seq_out * chunks)
+    ref_obj, ref_ga = em.grad_settings(states, b, a, ex, fw, ww, rw, gm)
+    ptrs = []
+
+    def put(arr):
+        arr = np.ascontiguousarray(arr, np.float32)
+        p = C.c_void_p()
+        L.check(em._h, em._lib.gnnuds_alloc_device(em._h, C.byref(p), max(arr.nbytes, 4)))
+        L.check(em._h, em._lib.gnnuds_memcpy(em._h, p, arr.ctypes.data_as(C.c_void_p), arr.nbytes, 1))
+        ptrs.append(p)
+        return p
+
+    def get(p, shape):
+        out = np.empty(shape, np.float32)
+        L.check(em._h, em._lib.gnnuds_memcpy(em._h, out.ctypes.data_as(C.c_void_p), p, out.nbytes, 2))
+        return out
+
+    B = states.shape[0]
+    x0, e0 = states[:, -em.seq_in:], ex[:, -em.seq_in:]
+    dx, db, da, de = put(x0), put(b), put(a), put(e0)
+    dobj, dga = put(np.full(B, np.nan)), put(np.full(a.shape, np.nan))
+    vp = lambda t: t.ctypes.data_as(C.c_void_p)
+    for _ in range(2):                                              # second call replays the cached graph
+        L.check(em._h, em._lib.gnnuds_grad_settings(em._h, L.ROLL_MPC, dx, db, da, de, B, chunks, vp(fw), vp(ww), vp(rw), vp(gm), dobj, dga,
+                                                    L.MEM_DEVICE))
+        assert np.array_equal(get(dobj, (B,)), ref_obj)
+        assert np.allclose(get(dga, a.shape), ref_ga, rtol=1e-5, atol=1e-7)
+    assert em._lib.gnnuds_grad_settings(em._h, L.ROLL_MPC, dx, db, da, de, 0, chunks, vp(fw), vp(ww), vp(rw), vp(gm), dobj, dga, L.MEM_DEVICE) == 0
+    # predict_vjp on device pointers (first chunk)
+    b1, a1 = np.ascontiguousarray(b[:, :em.seq_out]), np.ascontiguousarray(a[:, :em.seq_out])
+    y0, ey0 = em.predict_tf(x0, b1, a1, e0)
+    rng = np.random.default_rng(2)
+    gy, gey = rng.normal(size=y0.shape).astype(np.float32), rng.normal(size=ey0.shape).astype(np.float32)
+    ref = em.predict_vjp(x0, b1, a1, e0, gy, gey)
+    db1, da1, dgy, dgey = put(b1), put(a1), put(gy), put(gey)
+    dy, dey, dga1, dgx, dgex = put(np.zeros_like(y0)), put(np.zeros_like(ey0)), put(np.zeros_like(a1)), put(np.zeros_like(x0)), put(np.zeros_like(e0))
+    L.check(em._h, em._lib.gnnuds_predict_vjp(em._h, dx, db1, da1, de, B, dgy, dgey, dy, dey, dga1, dgx, dgex, L.MEM_DEVICE))
+    assert np.array_equal(get(dy, y0.shape), y0) and np.array_equal(get(dey, ey0.shape), ey0)
+    for p, name, shape in ((dga1, "ga", a1.shape), (dgx, "gx", x0.shape), (dgex, "gex", e0.shape)):
+        assert np.allclose(get(p, shape), ref[name], rtol=1e-5, atol=1e-7), name
+    for p in ptrs:
+        em._lib.gnnuds_free_device(em._h, p)
