@@ -64,7 +64,8 @@ def test_grad_settings_matches_autograd(case, chunks):
 @pytest.mark.parametrize("case", ["c3_ast_act_5", "ast_gcn_conv_eps0", "c2_shq_gat_conv_10", "ast_gcn_conv_act_nofusion",
                                   "ast_nn_conv_act_fusion", "c1_ast_gcn_gru", "ast_gat_gru_noflood", "ast_gcn_lstm_act_nofusion",
                                   "shq_nn_gru", "ast_pump_act_fusion", "ast_pump_act_nofusion", "ast_head_tide_offset",
-                                  "ast_joint_gat_conv_act", "ast_joint_gcn_gru_act", "ast_gat_use_adj", "ast_edgebased_gcn_lstm_act"])
+                                  "ast_joint_gat_conv_act", "ast_joint_gcn_gru_act", "ast_gat_use_adj", "ast_edgebased_gcn_lstm_act",
+                                  "c2_shq_gat_conv_60"])
 def test_predict_vjp_matches_autograd(case):
     """Random cotangents on every output channel; gradients w.r.t. settings, states and edge states."""
     from oracle import grad_oracle as go
