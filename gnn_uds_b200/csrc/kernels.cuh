@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(256) embed_kernel(EmbedP p) {
 struct EmbedRow { unsigned r, n, bt, t; };
 
 template <int LPR, int KT>                          // KT: compile-time channel count (full unrolling), 0 = runtime p.K
-__global__ void __launch_bounds__(256) embed_bf16_kernel(EmbedP p) {
+__global__ void __launch_bounds__(256, 4) embed_bf16_kernel(EmbedP p) {
   constexpr int RPB = 256 / LPR;                   // rows per CTA pass
   constexpr int Eo = LPR * 8;
   __shared__ __align__(16) float Ws[8 * LPR * 8];
@@ -1096,7 +1096,7 @@ __device__ __forceinline__ void warp_reduce_spread(float* v, int lane) {
 }
 
 template <int NOUT, int TB>
-__global__ void __launch_bounds__(256) cumsum_head_bf16_kernel(CumHeadP p) {
+__global__ void __launch_bounds__(256, 4) cumsum_head_bf16_kernel(CumHeadP p) {
   constexpr int E = 128, NV = NOUT * TB, DUP = 32 / NV;
   static_assert(NV <= 32 && (NV & (NV - 1)) == 0, "NOUT*TB must be a power of two <= 32");
   const int lane = threadIdx.x & 31;
