@@ -2809,32 +2809,43 @@ int gnnuds_rollout(gnnuds_handle* h, int32_t rule, const float* x0, const float*
     } else {
       db = hb; da = ha; dy = hy; dey = hey;
     }
+    // the chunk loop - slices, n_chunks forwards, scatters, feedback - touches device buffers only: one cached CUDA graph
+    // per shape (a roll of ONE scenario is latency-bound: ~45 kernels per chunk)
+    if ((rc = side_prepare(h, nb))) break;
+    char key[256];
+    snprintf(key, sizeof key, "roll|%lld|%d|%d|%d|%p|%p|%p|%p", (long long)nb, n_chunks, rule, h->side_on ? 1 : 0, (const void*)db, (const void*)da,
+             (void*)dy, (void*)dey);
+    auto chunk_loop = [&]() -> int {
+      int rc = 0;
     for (int k = 0; k < n_chunks && !rc; ++k) {
-      // slice chunk k of b / a into compact (nb,T,...) buffers
-      const long long Lb = (long long)N * c.b_in;
-      slice_time_kernel<<<grid_for(h, nb * T * Lb, 256, 16), 256, 0, h->stream>>>(db, h->ro_b, nb, (int)Th, k * T, T, Lb, 0);
-      ++h->launches;
-      if (da) {
-        slice_time_kernel<<<grid_for(h, nb * T * c.n_act, 256, 16), 256, 0, h->stream>>>(da, h->ro_a, nb, (int)Th, k * T, T, c.n_act, 0);
+        // slice chunk k of b / a into compact (nb,T,...) buffers
+        const long long Lb = (long long)N * c.b_in;
+        slice_time_kernel<<<grid_for(h, nb * T * Lb, 256, 16), 256, 0, h->stream>>>(db, h->ro_b, nb, (int)Th, k * T, T, Lb, 0);
         ++h->launches;
+        if (da) {
+          slice_time_kernel<<<grid_for(h, nb * T * c.n_act, 256, 16), 256, 0, h->stream>>>(da, h->ro_a, nb, (int)Th, k * T, T, c.n_act, 0);
+          ++h->launches;
+        }
+        rc = forward_any(h, h->ro_x, h->ro_b, da ? h->ro_a : nullptr, h->ro_ex, nb, h->out_y, h->out_ey, norm_io);
+        if (rc) break;
+        // scatter outputs into the horizon tensors
+        slice_time_kernel<<<grid_for(h, nb * T * (long long)N * nyc, 256, 16), 256, 0, h->stream>>>(h->out_y, dy, nb, (int)Th, k * T, T, (long long)N * nyc, 1);
+        slice_time_kernel<<<grid_for(h, nb * T * (long long)M * c.e_out, 256, 16), 256, 0, h->stream>>>(h->out_ey, dey, nb, (int)Th, k * T, T, (long long)M * c.e_out, 1);
+        h->launches += 2;
+        if (k + 1 < n_chunks) {
+          FeedP p{};
+          p.y = h->out_y; p.ny = nyc; p.ey = h->out_ey; p.e_out = c.e_out; p.b = h->ro_b; p.b_in = c.b_in;
+          p.a = da ? h->ro_a : nullptr; p.n_act = c.n_act; p.act_of_edge = h->d_act_of_edge;
+          p.x = h->ro_x; p.n_in = c.n_in; p.ex = h->ro_ex; p.e_in = c.e_in;
+          p.S = nb * T; p.N = N; p.M = M; p.if_flood = c.if_flood ? 1 : 0; p.rule = rule;
+          feedback_kernel<<<grid_for(h, p.S * (N + M), 256, 16), 256, 0, h->stream>>>(p);
+          ++h->launches;
+        }
+        if (cudaGetLastError() != cudaSuccess) rc = fail(h, GNNUDS_E_CUDA, "rollout kernel launch failed");
       }
-      rc = forward_any(h, h->ro_x, h->ro_b, da ? h->ro_a : nullptr, h->ro_ex, nb, h->out_y, h->out_ey, norm_io);
-      if (rc) break;
-      // scatter outputs into the horizon tensors
-      slice_time_kernel<<<grid_for(h, nb * T * (long long)N * nyc, 256, 16), 256, 0, h->stream>>>(h->out_y, dy, nb, (int)Th, k * T, T, (long long)N * nyc, 1);
-      slice_time_kernel<<<grid_for(h, nb * T * (long long)M * c.e_out, 256, 16), 256, 0, h->stream>>>(h->out_ey, dey, nb, (int)Th, k * T, T, (long long)M * c.e_out, 1);
-      h->launches += 2;
-      if (k + 1 < n_chunks) {
-        FeedP p{};
-        p.y = h->out_y; p.ny = nyc; p.ey = h->out_ey; p.e_out = c.e_out; p.b = h->ro_b; p.b_in = c.b_in;
-        p.a = da ? h->ro_a : nullptr; p.n_act = c.n_act; p.act_of_edge = h->d_act_of_edge;
-        p.x = h->ro_x; p.n_in = c.n_in; p.ex = h->ro_ex; p.e_in = c.e_in;
-        p.S = nb * T; p.N = N; p.M = M; p.if_flood = c.if_flood ? 1 : 0; p.rule = rule;
-        feedback_kernel<<<grid_for(h, p.S * (N + M), 256, 16), 256, 0, h->stream>>>(p);
-        ++h->launches;
-      }
-      if (cudaGetLastError() != cudaSuccess) rc = fail(h, GNNUDS_E_CUDA, "rollout kernel launch failed");
-    }
+      return rc;
+    };
+    rc = run_graphed(h, key, chunk_loop);
     if (!rc && where == GNNUDS_MEM_HOST) {
       cudaMemcpyAsync(hy, d_y, nb * syh * sizeof(float), cudaMemcpyDeviceToHost, h->stream);
       cudaMemcpyAsync(hey, d_ey, nb * seyh * sizeof(float), cudaMemcpyDeviceToHost, h->stream);
