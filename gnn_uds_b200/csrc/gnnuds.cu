@@ -201,6 +201,8 @@ struct gnnuds_handle {
   int joint_per_sample = 0;             // GNNUDS_JOINT_PER_SAMPLE=1: one (b,t) sample at a time in the large joint conv (diagnostic: no gain at C5)
   float* HB2 = nullptr;                 // the edge side's projection / conv scratch while both sides are in flight
   std::vector<std::pair<std::string, cudaGraphExec_t>> graphs;
+  int64_t n_capture = 0, n_replay = 0;
+  std::set<std::string> graph_seen;                   // keys run once (eagerly): captured when they come back
   std::map<std::string, int64_t> graph_launches;      // kernels per graph (gnnuds_launch_count stays a kernel count)
   Tape tape;                            // reverse pass (gnnuds_predict_vjp / gnnuds_grad_settings)
   float* bw_arena = nullptr; size_t bw_cap = 0;
@@ -461,6 +463,12 @@ int run_graphed(gnnuds_handle* h, std::string key, F body) {
   cudaGraphExec_t exec = nullptr;
   for (auto& g : h->graphs) if (g.first == key) { exec = g.second; break; }
   if (!exec) {
+    // a shape is captured on its SECOND use: capture + instantiation cost more than one eager run, and callers such as the
+    // mode-B event replay see every (length, chunk count) once per pass
+    if (h->graph_seen.insert(key).second) {
+      if (h->graph_seen.size() > 4096) h->graph_seen.clear();
+      return body();
+    }
     if (cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) { (void)cudaGetLastError(); h->use_graphs = 0; return body(); }
     const int64_t l0 = h->launches;
     const int rc = body();
@@ -475,11 +483,14 @@ int run_graphed(gnnuds_handle* h, std::string key, F body) {
     }
     if (cudaGraphInstantiate(&exec, g, 0) != cudaSuccess) { (void)cudaGetLastError(); cudaGraphDestroy(g); h->use_graphs = 0; h->launches = l0; return body(); }
     cudaGraphDestroy(g);
-    if (h->graphs.size() >= 32) { cudaGraphExecDestroy(h->graphs.front().second); h->graphs.erase(h->graphs.begin()); }
+    if (h->graphs.size() >= 256) { cudaGraphExecDestroy(h->graphs.front().second); h->graph_launches.erase(h->graphs.front().first); h->graphs.erase(h->graphs.begin()); }
     h->graphs.push_back({key, exec});
     h->graph_launches[key] = h->launches - l0;
+    // a caller that keeps producing new shapes pays for captures it never replays: give up on graphs for this handle
+    if (++h->n_capture > 128 && h->n_replay < 2 * h->n_capture) h->use_graphs = 0;
   } else {
     h->launches += h->graph_launches[key];
+    ++h->n_replay;
   }
   CU(cudaGraphLaunch(exec, h->stream));
   return 0;

@@ -176,7 +176,7 @@ def test_mpc_evaluator_gradient():
 
 
 def test_grad_settings_graph_replay_and_eager_agree(monkeypatch):
-    """The gradient body runs as a cached CUDA graph (captured on the first call of a shape, replayed afterwards);
+    """The gradient body runs as a cached CUDA graph (a shape runs eagerly once, is captured on its second use and replayed afterwards);
     GNNUDS_GRAPHS=0 runs the same launches eagerly.  First call, replays with other inputs, and the eager path agree."""
     case = "c3_ast_act_5"
     em, _ = cases.setup_product(case)
@@ -184,9 +184,11 @@ def test_grad_settings_graph_replay_and_eager_agree(monkeypatch):
     fw, ww, rw, gm = _weights(em.seq_out * 2)
     s1, b1, a1, e1 = _inputs(em, o, 4, 2, 3)
     s2, b2, a2, e2 = _inputs(em, o, 4, 2, 4)
-    o1, g1 = em.grad_settings(s1, b1, a1, e1, fw, ww, rw, gm)          # capture + first launch
-    o2, g2 = em.grad_settings(s2, b2, a2, e2, fw, ww, rw, gm)          # replay, other inputs
+    o1, g1 = em.grad_settings(s1, b1, a1, e1, fw, ww, rw, gm)          # first use of the shape: eager
+    o2, g2 = em.grad_settings(s2, b2, a2, e2, fw, ww, rw, gm)          # second use: capture + launch, other inputs
     o1r, g1r = em.grad_settings(s1, b1, a1, e1, fw, ww, rw, gm)        # replay, first inputs again
+    o2r, g2r = em.grad_settings(s2, b2, a2, e2, fw, ww, rw, gm)        # replay
+    assert np.array_equal(o2, o2r) and np.allclose(g2, g2r, rtol=1e-5, atol=1e-7)
     assert np.array_equal(o1, o1r) and np.allclose(g1, g1r, rtol=1e-5, atol=1e-7)
     assert not np.allclose(g1, g2)
     monkeypatch.setenv("GNNUDS_GRAPHS", "0")
@@ -229,7 +231,7 @@ def test_device_pointer_entry_points_equal_host_ones():
     dx, db, da, de = put(x0), put(b), put(a), put(e0)
     dobj, dga = put(np.full(B, np.nan)), put(np.full(a.shape, np.nan))
     vp = lambda t: t.ctypes.data_as(C.c_void_p)
-    for _ in range(2):                                              # second call replays the cached graph
+    for _ in range(3):                                              # eager, capture, replay
         L.check(em._h, em._lib.gnnuds_grad_settings(em._h, L.ROLL_MPC, dx, db, da, de, B, chunks, vp(fw), vp(ww), vp(rw), vp(gm), dobj, dga,
                                                     L.MEM_DEVICE))
         assert np.array_equal(get(dobj, (B,)), ref_obj)
