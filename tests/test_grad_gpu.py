@@ -199,6 +199,30 @@ def test_grad_settings_graph_replay_and_eager_agree(monkeypatch):
     assert np.allclose(g1, g1e, rtol=1e-5, atol=1e-7) and np.allclose(g2, g2e, rtol=1e-5, atol=1e-7)
 
 
+@pytest.mark.parametrize("case,chunks", [("c3_ast_act_5", 3), ("ast_nn_conv_act_fusion", 2), ("ast_gcn_lstm_act_nofusion", 2),
+                                         ("ast_pump_act_fusion", 2), ("ast_gat_use_adj", 2), ("ast_edgebased_gcn_lstm_act", 2)])
+def test_grad_settings_kept_tapes_and_checkpointed_sweeps_agree(case, chunks, monkeypatch):
+    """A multi-chunk roll keeps the tapes of all chunks when they fit GNNUDS_TAPE_MB (default 16 GiB: the mode the other tests
+    of this file run) and otherwise re-runs every chunk with the tape on during the reverse sweep (GNNUDS_TAPE_MB=0 forces
+    it).  Both sweeps against the gradient oracle and against each other, first call (eager) and graph replays."""
+    from oracle import grad_oracle as go
+    o, _ = cases.make_oracle(case, np.float64)
+    em, _ = cases.setup_product(case)
+    states, b, a, ex = _inputs(em, o, 5, chunks, 17)
+    fw, ww, rw, gm = _weights(em.seq_out * chunks)
+    ref_obj, ref_ga = go.grad_settings(o, states.astype(np.float64), b.astype(np.float64), a.astype(np.float64),
+                                       ex.astype(np.float64), fw, ww, rw, gm, chunks=chunks)
+    kept = [em.grad_settings(states, b, a, ex, fw, ww, rw, gm) for _ in range(3)]
+    monkeypatch.setenv("GNNUDS_TAPE_MB", "0")
+    em0, _ = cases.setup_product(case)
+    ckpt = [em0.grad_settings(states, b, a, ex, fw, ww, rw, gm) for _ in range(3)]
+    for obj, ga in kept + ckpt:
+        assert np.array_equal(obj, kept[0][0])
+        assert _rel(ga, ref_ga) <= TOL
+        assert np.allclose(ga, kept[0][1], rtol=1e-5, atol=1e-6 * np.abs(ref_ga).max())
+    assert np.allclose(kept[0][0], ref_obj, rtol=2e-4, atol=2e-4)
+
+
 def test_device_pointer_entry_points_equal_host_ones():
     """gnnuds_grad_settings / gnnuds_predict_vjp with where = GNNUDS_MEM_DEVICE (caller-owned device buffers, allocated here
     through gnnuds_alloc_device / gnnuds_memcpy): the same results as the host-pointer calls, in place in the caller's
