@@ -345,8 +345,8 @@ def run_mpc(a):
 def run_grad(a):
     """--workload C3grad: the gradient MPC's inner call (mpc.py:596-607 gradient_fn) on BASELINE.json configs[2]'s model -
     `--batch` decision vectors (default 256) x 60-step horizon = 12 autoregressive chunks of the astlingen 5->5 model,
-    objective AND d objective / d decisions through MpcEvaluator.gradient (gnnuds_grad_settings: forward sweep, taped
-    re-forward and VJP kernels per chunk, fp32).  One GPU; `cpu_baseline` = the gradient oracle (torch fp64 autograd
+    objective AND d objective / d decisions through MpcEvaluator.gradient (gnnuds_grad_settings: taped forward sweep
+    and VJP kernels per chunk, fp32; GNNUDS_TAPE_MB=0 = checkpointed sweep).  One GPU; `cpu_baseline` = the gradient oracle (torch fp64 autograd
     through the dense restatement) on a few candidates."""
     import torch
     from gnn_uds_b200 import configs, synthetic, mpc
