@@ -223,6 +223,22 @@ def test_grad_settings_kept_tapes_and_checkpointed_sweeps_agree(case, chunks, mo
     assert np.allclose(kept[0][0], ref_obj, rtol=2e-4, atol=2e-4)
 
 
+def test_grad_settings_blocks_of_decision_vectors():
+    """More decision vectors than one internal pass holds (max_chunk=2, B=5: blocks of 2, 2 and 1 through the same arena and
+    workspace, kept tapes and checkpointed): every vector's objective and gradient equal the single-block result."""
+    case, chunks = "c3_ast_act_5", 3
+    o, _ = cases.make_oracle(case, np.float64)
+    em, _ = cases.setup_product(case)
+    states, b, a, ex = _inputs(em, o, 5, chunks, 23)
+    fw, ww, rw, gm = _weights(em.seq_out * chunks)
+    obj, ga = em.grad_settings(states, b, a, ex, fw, ww, rw, gm)
+    em2, _ = cases.setup_product(case, max_chunk=2)
+    for _ in range(3):                                       # eager, captured, replayed
+        obj2, ga2 = em2.grad_settings(states, b, a, ex, fw, ww, rw, gm)
+        assert np.array_equal(obj, obj2)
+        assert np.allclose(ga, ga2, rtol=1e-5, atol=1e-6 * np.abs(ga).max())
+
+
 def test_device_pointer_entry_points_equal_host_ones():
     """gnnuds_grad_settings / gnnuds_predict_vjp with where = GNNUDS_MEM_DEVICE (caller-owned device buffers, allocated here
     through gnnuds_alloc_device / gnnuds_memcpy): the same results as the host-pointer calls, in place in the caller's
