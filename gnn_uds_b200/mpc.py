@@ -173,13 +173,14 @@ class MpcEvaluator:
         return objs, gy
 
     def hessp(self, y, p, eps=1e-3, **kw):
-        """``hessp_fn`` (mpc.py:609-617) by central differences of ``gradient`` along p (the reference differentiates the
+        """``hessp_fn`` (mpc.py:616-624) by central differences of ``gradient`` along p (the reference differentiates the
         gradient a second time with a nested tape; the rollout is piecewise linear in long stretches - relu,
         clipped flows - so a difference quotient of the exact gradient is what a second tape returns up to O(eps^2))."""
         y, p = np.asarray(y, np.float64), np.asarray(p, np.float64)
-        _, gp = self.gradient(y + eps * p, **kw)
-        _, gm = self.gradient(y - eps * p, **kw)
-        return ((gp - gm) / (2 * eps)).reshape(np.shape(y))
+        y2, p2 = np.atleast_2d(y), np.atleast_2d(p)
+        n = y2.shape[0]
+        _, g = self.gradient(np.concatenate([y2 + eps * p2, y2 - eps * p2], axis=0), **kw)    # both points in ONE reverse pass
+        return ((g[:n] - g[n:]) / (2 * eps)).reshape(np.shape(y))
 
     def _evaluate(self, x, out, *args, **kwargs):                   # mpc.py:261-264
         out["F"] = self.pred_emu_device(x) + 1e-6

@@ -173,6 +173,8 @@ def test_mpc_evaluator_gradient():
     assert np.allclose(gz, ev.gradient(yy)[1] * yy * (1 - yy), rtol=1e-5, atol=1e-7)
     hv = ev.hessp(y[0], d[0])
     assert hv.shape == y[0].shape and np.all(np.isfinite(hv))
+    hvb = ev.hessp(y, d)                                     # a batch of (y, p) pairs: row i is the product of pair i
+    assert hvb.shape == y.shape and np.allclose(hvb[0], hv, rtol=1e-4, atol=1e-4 * max(np.abs(hv).max(), 1e-12))
 
 
 def test_grad_settings_graph_replay_and_eager_agree(monkeypatch):
