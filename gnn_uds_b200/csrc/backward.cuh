@@ -113,6 +113,80 @@ __global__ void __launch_bounds__(256) bwd_gemm_kernel(BwdGemmP p) {
   }
 }
 
+// Small row counts (the gradient MPC's single decision vector: 150 rows per chunk and side): one round of loads instead of
+// Nout/16 dependent load -> compute rounds per tap.  A CTA owns 16 output rows x 32 source columns, stages the cotangent
+// tile of every tap (already multiplied by act') and the matching weight rows in shared memory, and 128 threads (row x 4
+// interleaved columns cg, cg+8, cg+16, cg+24) accumulate over taps and c in the order of bwd_gemm_kernel: bitwise the
+// same results.  Dynamic smem: ntap * 48 * (Nout + 4) floats.
+__global__ void __launch_bounds__(128) bwd_gemm_skinny_kernel(BwdGemmP p) {
+  extern __shared__ __align__(16) float bws_sm[];
+  const int LD = p.Nout + 4, nq = p.Nout >> 2;
+  float* As = bws_sm;                               // [ntap][16][LD]
+  float* Ws = bws_sm + (size_t)p.ntap * 16 * LD;    // [ntap][32][LD]
+  const int tid = threadIdx.x;
+  const long long row0 = (long long)blockIdx.x * 16;
+  const int col0 = blockIdx.y * 32;
+  const int dT = p.Ts - p.Td;
+  for (int idx = tid; idx < p.ntap * 32 * nq; idx += 128) {
+    const int j = idx / (32 * nq), rem = idx - j * 32 * nq, kk = rem / nq, c = (rem - kk * nq) * 4;
+    float* dst = Ws + ((size_t)j * 32 + kk) * LD + c;
+    if (col0 + kk < p.Kw) cp_async_f4(dst, p.W + (size_t)(p.tap[j].k0 + col0 + kk) * p.Nout + c);
+    else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+#pragma unroll 4
+  for (int idx = tid; idx < p.ntap * 16 * nq; idx += 128) {
+    const int j = idx / (16 * nq), rem = idx - j * 16 * nq, lr = rem / nq, c = (rem - lr * nq) * 4;
+    const long long r_out = row0 + lr;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r_out < p.rows_out) {
+      const long long bt = r_out / p.Nn;
+      const int n = (int)(r_out % p.Nn);
+      const int tp = (int)(bt % p.Ts);
+      const long long b = bt / p.Ts;
+      const int t = tp - dT + p.tap[j].shift;
+      if (t >= 0 && t < p.Td) {
+        const long long r_src = (b * p.Td + t) * p.pitch_g + p.off_g + n;
+        a = *reinterpret_cast<const float4*>(p.G + r_src * p.ldg + c);
+        if (p.Y) {
+          const float4 y = *reinterpret_cast<const float4*>(p.Y + r_src * p.ldy + c);
+          a.x *= dact_from_out(y.x, p.act); a.y *= dact_from_out(y.y, p.act);
+          a.z *= dact_from_out(y.z, p.act); a.w *= dact_from_out(y.w, p.act);
+        }
+      }
+    }
+    *reinterpret_cast<float4*>(As + ((size_t)j * 16 + lr) * LD + c) = a;
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  const int lr = tid >> 3, cg = tid & 7;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int j = 0; j < p.ntap; ++j) {
+    const float* ar = As + ((size_t)j * 16 + lr) * LD;
+    const float* wr = Ws + ((size_t)j * 32 + cg) * LD;
+#pragma unroll 2
+    for (int c = 0; c < p.Nout; c += 4) {
+      const float4 a = *reinterpret_cast<const float4*>(ar + c);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 w = *reinterpret_cast<const float4*>(wr + (size_t)q * 8 * LD + c);
+        acc[q] = fmaf(a.x, w.x, acc[q]); acc[q] = fmaf(a.y, w.y, acc[q]);
+        acc[q] = fmaf(a.z, w.z, acc[q]); acc[q] = fmaf(a.w, w.w, acc[q]);
+      }
+    }
+  }
+  const long long r = row0 + lr;
+  if (r < p.rows_out) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k = col0 + cg + 8 * q;
+      if (k >= p.Kw) continue;
+      float* d = p.out + r * p.ldo + k;
+      *d = p.accumulate ? *d + acc[q] : acc[q];
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // VJP of nodeedge_kernel: out[s] = Mat @ in[s]  ->  gIn[s] = Mat^T @ gOut[s].  matT is the forward's transposed
 // folded matrix (R_in, ldm): matT[j*ldm + i] = Mat[i][j].  One thread per (s, j, 4 features).

@@ -196,6 +196,8 @@ struct gnnuds_handle {
   cudaStream_t s_side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int side_par = 1;
+  // fp32 GEMMs of at most this many rows go to the one-round 16 x 32 tile kernels (rows_gemm_f32_skinny); GNNUDS_SKINNY_ROWS=0 disables
+  long long skinny_rows = 8192;
   bool side_on = false;
   int default_ws_mb = 8192;             // workspace budget when cfg.workspace_mb == 0 (GNNUDS_WORKSPACE_MB overrides)
   int joint_per_sample = 0;             // GNNUDS_JOINT_PER_SAMPLE=1: one (b,t) sample at a time in the large joint conv (diagnostic: no gain at C5)
@@ -513,7 +515,16 @@ int launch_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, const float* Wp
   cudaEvent_t e1 = nullptr;
   { int prc = prof_begin(h, GNNUDS_FAM_GEMM, &e1); if (prc) return prc; }
   const unsigned gx = (unsigned)((p.rows + 127) / 128);
-  if (Nout % 128 == 0) {
+  int Ktot = 0;
+  for (int i = 0; i < p.nseg; ++i) Ktot += p.seg[i].width;
+  const size_t skinny_smem = ((size_t)16 * (Ktot + 4) + (size_t)32 * Ktot) * sizeof(float);
+  if (p.rows <= h->skinny_rows && Nout % 32 == 0 && skinny_smem <= 200 * 1024) {
+    if (!h->attr_done[7]) {
+      CU(cudaFuncSetAttribute(rows_gemm_f32_skinny, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      h->attr_done[7] = true;
+    }
+    rows_gemm_f32_skinny<<<dim3((unsigned)((p.rows + 15) / 16), Nout / 32), 128, skinny_smem, h->stream>>>(p, Ktot);
+  } else if (Nout % 128 == 0) {
     rows_gemm_f32<128><<<dim3(gx, Nout / 128), 256, 0, h->stream>>>(p);
   } else if (Nout % 64 == 0) {
     rows_gemm_f32<64><<<dim3(gx, Nout / 64), 256, 0, h->stream>>>(p);
@@ -2131,6 +2142,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   if (getenv("GNNUDS_SP_AGG")) h->sp_agg = atoi(getenv("GNNUDS_SP_AGG"));
   if (getenv("GNNUDS_GRAPHS")) h->use_graphs = atoi(getenv("GNNUDS_GRAPHS"));
   if (getenv("GNNUDS_SIDE_PAR")) h->side_par = atoi(getenv("GNNUDS_SIDE_PAR"));
+  if (getenv("GNNUDS_SKINNY_ROWS")) h->skinny_rows = atoll(getenv("GNNUDS_SKINNY_ROWS"));
   if (getenv("GNNUDS_WORKSPACE_MB") && atoi(getenv("GNNUDS_WORKSPACE_MB")) > 0) h->default_ws_mb = atoi(getenv("GNNUDS_WORKSPACE_MB"));
   if (getenv("GNNUDS_JOINT_PER_SAMPLE")) h->joint_per_sample = atoi(getenv("GNNUDS_JOINT_PER_SAMPLE"));
   if (getenv("GNNUDS_TP_FUSED")) h->tp_fused = atoi(getenv("GNNUDS_TP_FUSED"));

@@ -457,6 +457,84 @@ __global__ void __launch_bounds__(256) rows_gemm_f32(GemmP p) {
   }
 }
 
+// Small row counts (one scenario of a 5-step chunk is 150 rows: simulate per event, the gradient MPC's single decision
+// vector): the 128-row kernel above runs 2 CTAs through Ktot/16 dependent load -> compute rounds, ~1 us each.  Here a CTA
+// owns 16 rows x 32 columns, brings its whole A tile (16 x Ktot) and W tile (Ktot x 32) into shared memory with ONE
+// round of cp.async, and 128 threads (row x 4 columns) accumulate over k in ascending order with one fmaf chain per
+// output - the same order as rows_gemm_f32, so the results are bitwise the same.  Dynamic smem: (16 (Ktot + 4) + 32 Ktot) floats.
+__device__ __forceinline__ void cp_async_f4(float* dst_smem, const float* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__global__ void __launch_bounds__(128) rows_gemm_f32_skinny(GemmP p, int Ktot) {
+  extern __shared__ __align__(16) float skinny_sm[];
+  const int LDA = Ktot + 4;
+  float* As = skinny_sm;                 // [16][LDA]
+  float* Ws = skinny_sm + 16 * LDA;      // [Ktot][32]
+  const int tid = threadIdx.x;
+  const long long row0 = (long long)blockIdx.x * 16;
+  const int col0 = blockIdx.y * 32;
+  const int kq_n = Ktot >> 2;
+  for (int idx = tid; idx < Ktot * 8; idx += 128) {
+    const int k = idx >> 3, c4 = idx & 7;
+    cp_async_f4(Ws + k * 32 + c4 * 4, p.W + (long long)k * p.Nout + col0 + c4 * 4);
+  }
+  for (int idx = tid; idx < 16 * kq_n; idx += 128) {
+    const int lr = idx / kq_n, k = (idx - lr * kq_n) * 4;
+    const long long r = row0 + lr;
+    const float* src = nullptr;
+    if (r < p.rows) {
+      const int n = (int)(r % p.Nn);
+      const long long bt = r / p.Nn;
+      const int t = (int)(bt % p.Td);
+      const long long b = bt / p.Td;
+      int k0 = 0;
+#pragma unroll
+      for (int s = 0; s < 4; ++s) {
+        if (s < p.nseg) {
+          if (k >= k0 && k < k0 + p.seg[s].width) {
+            const int ts = t + (p.Ts - p.Td) - p.seg[s].shift;
+            if (ts >= 0) src = p.seg[s].p + ((b * p.Ts + ts) * p.seg[s].pitch + p.seg[s].off + n) * p.seg[s].ld + (k - k0);
+          }
+          k0 += p.seg[s].width;
+        }
+      }
+    }
+    float* dst = As + lr * LDA + k;
+    if (src) cp_async_f4(dst, src);
+    else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  const int lr = tid >> 3, cg = tid & 7;
+  const float* ar = As + lr * LDA;
+  const float* wr = Ws + cg * 4;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+  for (int k = 0; k < Ktot; k += 4) {
+    const float4 a = *reinterpret_cast<const float4*>(ar + k);
+    const float4 w0 = *reinterpret_cast<const float4*>(wr + (k + 0) * 32);
+    const float4 w1 = *reinterpret_cast<const float4*>(wr + (k + 1) * 32);
+    const float4 w2 = *reinterpret_cast<const float4*>(wr + (k + 2) * 32);
+    const float4 w3 = *reinterpret_cast<const float4*>(wr + (k + 3) * 32);
+    acc.x = fmaf(a.x, w0.x, acc.x); acc.y = fmaf(a.x, w0.y, acc.y); acc.z = fmaf(a.x, w0.z, acc.z); acc.w = fmaf(a.x, w0.w, acc.w);
+    acc.x = fmaf(a.y, w1.x, acc.x); acc.y = fmaf(a.y, w1.y, acc.y); acc.z = fmaf(a.y, w1.z, acc.z); acc.w = fmaf(a.y, w1.w, acc.w);
+    acc.x = fmaf(a.z, w2.x, acc.x); acc.y = fmaf(a.z, w2.y, acc.y); acc.z = fmaf(a.z, w2.z, acc.z); acc.w = fmaf(a.z, w2.w, acc.w);
+    acc.x = fmaf(a.w, w3.x, acc.x); acc.y = fmaf(a.w, w3.y, acc.y); acc.z = fmaf(a.w, w3.z, acc.z); acc.w = fmaf(a.w, w3.w, acc.w);
+  }
+  const long long rl = row0 + lr;
+  if (rl < p.rows) {
+    const int col = col0 + cg * 4;
+    float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.bias) bb = *reinterpret_cast<const float4*>(p.bias + col);
+    const long long rr = (rl / p.Nn) * p.pitch_d + p.off_d + (rl % p.Nn);
+    float4 v;
+    v.x = apply_act(acc.x + bb.x, p.act); v.y = apply_act(acc.y + bb.y, p.act);
+    v.z = apply_act(acc.z + bb.z, p.act); v.w = apply_act(acc.w + bb.w, p.act);
+    *reinterpret_cast<float4*>(p.out + rr * p.ldo + col) = v;
+  }
+}
+
 // Narrow-output variant (Nout a multiple of 16 or 32 but not 64: E/2 or H of small models).
 // Same row addressing as rows_gemm_f32; 128 rows x BN columns per CTA, BN/8 rows x 4 columns
 // per thread.
