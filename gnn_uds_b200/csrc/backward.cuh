@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(256) joint_pack_kernel(const float* __restrict
   }
 }
 
-__global__ void __launch_bounds__(256) agg_bwd_kernel(AggBwdP p) {
+__global__ void __launch_bounds__(1024) agg_bwd_kernel(AggBwdP p) {      // 256 threads per sample, 1024 when there are few samples
   extern __shared__ __align__(16) float sm[];
   const int R = p.R, E = p.E;
   float* hs = sm;                       // R*E

@@ -606,7 +606,8 @@ int launch_agg(gnnuds_handle* h, const void* hin, void* out, const int* rp, cons
            nullptr, nullptr, nullptr, 0};
     if (dyn && h->use_adj && h->cur_a) { p.act_entry = h->d_adj_act; p.keep = h->d_adj_keep; p.a_dyn = h->cur_a; p.n_act = c.n_act; }
     CU(cudaFuncSetAttribute(agg_small_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    agg_small_kernel<T><<<grid_for(h, S, 1, 16), 256, smem, h->stream>>>(p);
+    const int threads = S <= 2 * (long long)h->sm_count ? 1024 : 256;      // few samples: one warp per graph row at once
+    agg_small_kernel<T><<<grid_for(h, S, 1, 16), threads, smem, h->stream>>>(p);
     ++h->launches;
   } else {
     if (dyn && h->use_adj) return fail(h, GNNUDS_E_INVALID, "use_adj: graph of %d rows does not fit the per-sample aggregation kernel", R);

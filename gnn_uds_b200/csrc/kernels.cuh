@@ -709,7 +709,7 @@ __device__ __forceinline__ bool agg_kept(const AggP& p, long long s, int q, int 
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256) agg_small_kernel(AggP p) {
+__global__ void __launch_bounds__(1024) agg_small_kernel(AggP p) {      // 256 threads per sample, 1024 when there are few samples (same results: a row is one warp's)
   extern __shared__ __align__(16) float sm[];
   float* hs = sm;                          // R*E
   float* ss = sm + (size_t)p.R * p.E;      // R
