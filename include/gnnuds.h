@@ -224,8 +224,9 @@ int gnnuds_predict_vjp(gnnuds_handle* h, const float* x, const float* b, const f
 /* mpc_problem_gr.gradient_fn (mpc.py:596-607) for the astlingen objective (envs/scenario/astlingen.py:75-99):
  * obj (B) and grad_a (B, n_chunks*seq_out, n_act) = d obj_i / d a_i for every candidate i.  n_chunks == 1 is one
  * predict_tf; n_chunks > 1 differentiates through the autoregressive chunk loop (mpc.py:565-582, feedback `rule`
- * GNNUDS_ROLL_MPC or GNNUDS_ROLL_MBRL): the forward sweep keeps only every chunk's input state, the reverse sweep
- * re-runs one chunk at a time with the tape on (checkpointing) and carries the state cotangents across the feedback
+ * GNNUDS_ROLL_MPC or GNNUDS_ROLL_MBRL): the forward sweep keeps the tapes of all chunks when they fit GNNUDS_TAPE_MB
+ * (16 GiB by default), otherwise only every chunk's input state, and the reverse sweep then re-runs one chunk at a
+ * time with the tape on (checkpointing); it carries the state cotangents across the feedback
  * (h, q_us, q_ds and the edge outputs; the setting written into the edge state's last channel feeds grad_a; the flood
  * flag and the runoff carry no gradient).  x0 (B,seq_in,n_node,n_in), b (B,n_chunks*seq_out,n_node,b_in),
  * a (B,n_chunks*seq_out,n_act), ex0 (B,seq_in,n_edge,e_in) live where `where` says; the weight vectors / gamma
