@@ -134,6 +134,7 @@ __global__ void __launch_bounds__(128) bwd_gemm_skinny_kernel(BwdGemmP p) {
     else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");       // programmatic dependent launch: only the weight rows above are independent of the previous kernel
 #pragma unroll 4
   for (int idx = tid; idx < p.ntap * 16 * nq; idx += 128) {
     const int j = idx / (16 * nq), rem = idx - j * 16 * nq, lr = rem / nq, c = (rem - lr * nq) * 4;
@@ -159,6 +160,7 @@ __global__ void __launch_bounds__(128) bwd_gemm_skinny_kernel(BwdGemmP p) {
   }
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int lr = tid >> 3, cg = tid & 7;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
   for (int j = 0; j < p.ntap; ++j) {

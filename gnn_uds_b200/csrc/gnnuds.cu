@@ -198,6 +198,7 @@ struct gnnuds_handle {
   int side_par = 1;
   // fp32 GEMMs of at most this many rows go to the one-round 16 x 32 tile kernels (rows_gemm_f32_skinny); GNNUDS_SKINNY_ROWS=0 disables
   long long skinny_rows = 8192;
+  int pdl = 1;      // small-tile GEMMs are launched with programmatic stream serialization (weight prefetch under the previous kernel's tail); GNNUDS_PDL=0 disables
   bool side_on = false;
   int default_ws_mb = 8192;             // workspace budget when cfg.workspace_mb == 0 (GNNUDS_WORKSPACE_MB overrides)
   int joint_per_sample = 0;             // GNNUDS_JOINT_PER_SAMPLE=1: one (b,t) sample at a time in the large joint conv (diagnostic: no gain at C5)
@@ -523,7 +524,12 @@ int launch_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, const float* Wp
       CU(cudaFuncSetAttribute(rows_gemm_f32_skinny, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       h->attr_done[7] = true;
     }
-    rows_gemm_f32_skinny<<<dim3((unsigned)((p.rows + 15) / 16), Nout / 32), 128, skinny_smem, h->stream>>>(p, Ktot);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)((p.rows + 15) / 16), Nout / 32); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = skinny_smem; cfg.stream = h->stream;
+    cudaLaunchAttribute at{};
+    at.id = cudaLaunchAttributeProgrammaticStreamSerialization; at.val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = &at; cfg.numAttrs = h->pdl ? 1 : 0;
+    CU(cudaLaunchKernelEx(&cfg, rows_gemm_f32_skinny, p, Ktot));
   } else if (Nout % 128 == 0) {
     rows_gemm_f32<128><<<dim3(gx, Nout / 128), 256, 0, h->stream>>>(p);
   } else if (Nout % 64 == 0) {
@@ -2144,6 +2150,7 @@ int gnnuds_create(const gnnuds_config* cfg, gnnuds_handle** out) {
   if (getenv("GNNUDS_GRAPHS")) h->use_graphs = atoi(getenv("GNNUDS_GRAPHS"));
   if (getenv("GNNUDS_SIDE_PAR")) h->side_par = atoi(getenv("GNNUDS_SIDE_PAR"));
   if (getenv("GNNUDS_SKINNY_ROWS")) h->skinny_rows = atoll(getenv("GNNUDS_SKINNY_ROWS"));
+  if (getenv("GNNUDS_PDL")) h->pdl = atoi(getenv("GNNUDS_PDL"));
   if (getenv("GNNUDS_WORKSPACE_MB") && atoi(getenv("GNNUDS_WORKSPACE_MB")) > 0) h->default_ws_mb = atoi(getenv("GNNUDS_WORKSPACE_MB"));
   if (getenv("GNNUDS_JOINT_PER_SAMPLE")) h->joint_per_sample = atoi(getenv("GNNUDS_JOINT_PER_SAMPLE"));
   if (getenv("GNNUDS_TP_FUSED")) h->tp_fused = atoi(getenv("GNNUDS_TP_FUSED"));

@@ -478,6 +478,9 @@ __global__ void __launch_bounds__(128) rows_gemm_f32_skinny(GemmP p, int Ktot) {
     const int k = idx >> 3, c4 = idx & 7;
     cp_async_f4(Ws + k * 32 + c4 * 4, p.W + (long long)k * p.Nout + col0 + c4 * 4);
   }
+  // Programmatic dependent launch (launch_gemm sets the attribute): the weight tile above does not depend on the kernel
+  // before this one in the stream; everything below does.  Without the launch attribute the wait returns at once.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   for (int idx = tid; idx < 16 * kq_n; idx += 128) {
     const int lr = idx / kq_n, k = (idx - lr * kq_n) * 4;
     const long long r = row0 + lr;
@@ -506,6 +509,7 @@ __global__ void __launch_bounds__(128) rows_gemm_f32_skinny(GemmP p, int Ktot) {
   asm volatile("cp.async.commit_group;" ::: "memory");
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");      // a dependent small-tile GEMM may start its weight prefetch
   const int lr = tid >> 3, cg = tid & 7;
   const float* ar = As + lr * LDA;
   const float* wr = Ws + cg * 4;
