@@ -219,6 +219,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_agg_kernel(const __grid_cons
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
+  tc::pdl_sync();
   const uint32_t tmem = *tmem_slot;
   const uint32_t acc_conv = tmem;                                  // MT * NW columns (<= 288)
   const uint32_t acc_agg = p.alias_acc ? tmem : tmem + 160u;       // MT * Nout columns

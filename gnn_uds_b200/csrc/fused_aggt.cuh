@@ -138,6 +138,7 @@ __global__ void __launch_bounds__(SA_THREADS, 1) sp_aggt_kernel(const __grid_con
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
+  tc::pdl_sync();
   const int n_it = p.S > (int)blockIdx.x ? (p.S - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
   const int Nr = pp.Nr;
   const uint32_t h_tile = (uint32_t)p.Nout * 128u;            // one h^T tile [Nout features x 64 rows]

@@ -175,6 +175,7 @@ __global__ void __launch_bounds__(SP_THREADS, 1) sp_conv_kernel(const __grid_con
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
+  tc::pdl_sync();
   const uint32_t tmem = *tmem_slot;
   const uint32_t acc_conv = tmem;              // MT * Nout columns
   const uint32_t acc_ne = tmem + 256u;         // MT * F columns

@@ -75,6 +75,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tp_conv_kernel(const __grid_con
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
+  tc::pdl_sync();
   const uint32_t tmem = *tmem_slot;
   const int n_it = p.n_tiles > blockIdx.x ? (int)((p.n_tiles - 1 - blockIdx.x) / gridDim.x) + 1 : 0;
   const int nchunk = p.cin >> 6, nst = p.k * nchunk;        // layer-1 stages per tile

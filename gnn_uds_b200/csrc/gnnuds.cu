@@ -501,6 +501,20 @@ int run_graphed(gnnuds_handle* h, std::string key, F body) {
 
 struct SegH { const float* p; int ld; int width; int shift; int pitch; int off; };
 
+// Launch of a tensor-core kernel whose set-up (barrier init, TMEM allocation, constant staging) ends in tc::pdl_sync():
+// small grids (at most half the SMs: single events, small MPC populations) are launched as programmatic dependents, so that
+// set-up runs under the tail of the previous kernel of the stream; large grids are plain stream launches.
+template <typename K, typename P>
+cudaError_t launch_pdl(gnnuds_handle* h, K kernel, dim3 grid, unsigned threads, size_t smem, const P& p) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = h->stream;
+  cudaLaunchAttribute at{};
+  at.id = cudaLaunchAttributeProgrammaticStreamSerialization; at.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = &at;
+  cfg.numAttrs = (h->pdl && (long long)grid.x * grid.y * grid.z * 2 <= h->sm_count) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
 int launch_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, const float* Wp, const float* bias, float* out,
                 int ldo, int Nout, int act, long long Bc, int Nn, int Td, int Ts, int pitch_d, int off_d) {
   if (segs.size() > 4) return fail(h, GNNUDS_E_INVALID, "rows_gemm: more than 4 segments (kernel_size > 4?)");
@@ -1229,7 +1243,7 @@ int launch_tc_gemm(gnnuds_handle* h, const std::vector<SegH>& segs, int w_tensor
     h->attr_done[0] = true;
   }
   const unsigned grid = std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count);
-  tc_rows_kernel<<<grid, TC_THREADS, smem, h->stream>>>(p);
+  CU(launch_pdl(h, tc_rows_kernel, dim3(grid), TC_THREADS, smem, p));
   ++h->launches;
   { int prc = prof_end(h, e1); if (prc) return prc; }
   CU(cudaGetLastError());
@@ -1304,7 +1318,7 @@ int launch_tp_conv(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& s
   }
   cudaEvent_t e1 = nullptr;
   { int prc = prof_begin(h, GNNUDS_FAM_GEMM, &e1); if (prc) return prc; }
-  tp_conv_kernel<<<std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count), TP_THREADS, smem, h->stream>>>(p);
+  CU(launch_pdl(h, tp_conv_kernel, dim3(std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count)), TP_THREADS, smem, p));
   ++h->launches;
   { int prc = prof_end(h, e1); if (prc) return prc; }
   CU(cudaGetLastError());
@@ -1348,7 +1362,7 @@ int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& 
         if (!h->attr_done[1]) { CU(cudaFuncSetAttribute(gru_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); h->attr_done[1] = true; }
         cudaEvent_t e1 = nullptr;
         { int prc = prof_begin(h, GNNUDS_FAM_RECURRENT, &e1); if (prc) return prc; }
-        gru_tc_kernel<64><<<std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count), GRU_THREADS, smem, h->stream>>>(p);
+        CU(launch_pdl(h, gru_tc_kernel<64>, dim3(std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count)), GRU_THREADS, smem, p));
         { int prc = prof_end(h, e1); if (prc) return prc; }
       } else if (gru) {
         GruP p{h->HB, W(h, L[i].t[1]), W(h, L[i].t[2]) + G, o, nseq, Nn, Ts, Tdst, H};
@@ -1366,7 +1380,7 @@ int run_temporal_tc(gnnuds_handle* h, const std::vector<LayerW>& L, const SegH& 
         if (!h->attr_done[2]) { CU(cudaFuncSetAttribute(lstm_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); h->attr_done[2] = true; }
         cudaEvent_t e1 = nullptr;
         { int prc = prof_begin(h, GNNUDS_FAM_RECURRENT, &e1); if (prc) return prc; }
-        lstm_tc_kernel<64><<<std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count), GRU_THREADS, smem, h->stream>>>(p);
+        CU(launch_pdl(h, lstm_tc_kernel<64>, dim3(std::min<unsigned>(p.n_tiles, (unsigned)h->sm_count)), GRU_THREADS, smem, p));
         { int prc = prof_end(h, e1); if (prc) return prc; }
       } else {
         LstmP p{h->HB, W(h, L[i].t[1]), o, nseq, Nn, Ts, Tdst, H};
@@ -1494,7 +1508,7 @@ int launch_sp_conv(gnnuds_handle* h, const std::vector<SegH>& segs, const void* 
   if (do_trace) { CU(cudaMalloc(&p.trace, tn * sizeof(long long))); CU(cudaMemset(p.trace, 0, tn * sizeof(long long))); }
   cudaEvent_t e1 = nullptr;
   { int prc = prof_begin(h, GNNUDS_FAM_SPATIAL, &e1); if (prc) return prc; }
-  sp_conv_kernel<<<grid, SP_THREADS, smem, h->stream>>>(p);
+  CU(launch_pdl(h, sp_conv_kernel, dim3(grid), SP_THREADS, smem, p));
   ++h->launches;
   { int prc = prof_end(h, e1); if (prc) return prc; }
   CU(cudaGetLastError());
@@ -1615,9 +1629,9 @@ int launch_sp_agg(gnnuds_handle* h, const std::vector<SegH>& segs, const void* o
   { int prc = prof_begin(h, GNNUDS_FAM_SPATIAL, &e1); if (prc) return prc; }
   if (T) {
     pt.b = p; pt.wa = gat ? h->d_wa[side][li] : nullptr; pt.Nr = p.KpJ;
-    sp_aggt_kernel<<<grid, SA_THREADS, smem, h->stream>>>(pt);
+    CU(launch_pdl(h, sp_aggt_kernel, dim3(grid), SA_THREADS, smem, pt));
   } else {
-    sp_agg_kernel<<<grid, SA_THREADS, smem, h->stream>>>(p);
+    CU(launch_pdl(h, sp_agg_kernel, dim3(grid), SA_THREADS, smem, p));
   }
   ++h->launches;
   { int prc = prof_end(h, e1); if (prc) return prc; }

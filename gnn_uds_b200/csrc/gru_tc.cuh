@@ -65,6 +65,7 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) gru_tc_kernel(const __grid_con
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
+  tc::pdl_sync();
   const uint32_t tmem = *tmem_slot;
   uint32_t ph_h = 0, ph_m = 0;     // phases of h_ready (MMA thread) / mma_done (gate threads)
 
@@ -224,6 +225,7 @@ __global__ void __launch_bounds__(GRU_THREADS, 1) lstm_tc_kernel(const __grid_co
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
+  tc::pdl_sync();
   const uint32_t tmem = *tmem_slot;
   uint32_t ph_h = 0, ph_m = 0;
 

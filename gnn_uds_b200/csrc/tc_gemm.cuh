@@ -191,6 +191,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_rows_kernel(const __grid_con
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
+  tc::pdl_sync();
   const uint32_t tmem = *tmem_slot;
   const int nchunk = p.Ktot / p.kc;           // K chunks (= pipeline stages) per tile
 

@@ -23,6 +23,16 @@
 namespace gu {
 namespace tc {
 
+// Programmatic dependent launch (launched with cudaLaunchAttributeProgrammaticStreamSerialization when the grid is small,
+// gnnuds.cu launch_pdl): called by ALL threads after the set-up that reads only constants (barrier init, TMEM allocation,
+// weight / bias / CSR staging).  launch_dependents lets the next kernel of the stream become resident and run ITS set-up;
+// wait returns when the kernels before this one have completed and their writes are visible.  No-ops without the attribute.
+__device__ __forceinline__ void pdl_sync() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // ---- mbarrier -------------------------------------------------------------------------------
