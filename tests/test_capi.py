@@ -32,6 +32,14 @@ def test_header_symbols_exported(lib_path):
     assert sorted(_lib.SYMBOLS) == declared          # the ctypes shim binds exactly the header
 
 
+def test_integration_doc_names_every_entry_point():
+    """INTEGRATION.md's entry-point table (what each C symbol replaces in the reference) covers the whole header; a
+    `gnnuds_a/_b` shorthand counts for both names."""
+    doc = open(os.path.join(cases.ROOT, "INTEGRATION.md")).read()
+    missing = [s for s in _declared() if s not in doc and not re.search(r"/_%s\b" % re.escape(s.rsplit("_", 1)[-1]), doc)]
+    assert not missing, missing
+
+
 def test_ctypes_load_and_struct_sizes(lib_path):
     lib = _lib.load()
     assert ctypes.sizeof(_lib.Config) == 30 * 4
